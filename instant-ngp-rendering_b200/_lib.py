@@ -1,0 +1,90 @@
+"""ctypes binding of libngp_b200.so (the C ABI in include/ngp_b200.h).
+
+There is no fallback: if the shared library is missing the import fails, and every compute
+entry point fails with the library's own error when no CUDA device is present.
+"""
+import ctypes
+import os
+
+_PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG_DIR, "libngp_b200.so")
+
+c_u32 = ctypes.c_uint32
+c_u64 = ctypes.c_uint64
+c_f32 = ctypes.c_float
+c_vp = ctypes.c_void_p
+c_sz = ctypes.c_size_t
+c_int = ctypes.c_int
+c_cp = ctypes.c_char_p
+
+
+class NgpbError(RuntimeError):
+    """Raised with the message the C ABI stored (same text as the reference's std::runtime_error)."""
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `python instant-ngp-rendering_b200/build.py` "
+            "(there is no CPU or PyTorch fallback)")
+    return ctypes.CDLL(LIB_PATH)
+
+
+lib = _load()
+
+# name -> (restype, argtypes). Kept in one table so tests can check it against the header.
+SIGNATURES = {
+    "ngpb_last_error": (c_cp, []),
+    "ngpb_version": (c_int, []),
+    "ngpb_has_device": (c_int, []),
+    "ngpb_batch_size_granularity": (c_u32, []),
+    "ngpb_default_loss_scale": (c_f32, [c_int]),
+    "ngpb_create_encoding": (c_int, [c_u32, c_cp, c_int, ctypes.POINTER(c_vp)]),
+    "ngpb_create_network_with_input_encoding": (c_int, [c_u32, c_u32, c_cp, c_cp, ctypes.POINTER(c_vp)]),
+    "ngpb_create_network": (c_int, [c_u32, c_u32, c_cp, ctypes.POINTER(c_vp)]),
+    "ngpb_create_nerf_network": (c_int, [c_u32, c_u32, c_u32, c_u32, c_cp, c_cp, c_cp, c_cp, ctypes.POINTER(c_vp)]),
+    "ngpb_module_free": (None, [c_vp]),
+    "ngpb_module_n_input_dims": (c_u32, [c_vp]),
+    "ngpb_module_n_output_dims": (c_u32, [c_vp]),
+    "ngpb_module_n_output_dims_unpadded": (c_u32, [c_vp]),
+    "ngpb_module_n_params": (c_sz, [c_vp]),
+    "ngpb_module_param_precision": (c_int, [c_vp]),
+    "ngpb_module_output_precision": (c_int, [c_vp]),
+    "ngpb_module_hyperparams": (c_sz, [c_vp, c_cp, c_sz]),
+    "ngpb_module_name": (c_sz, [c_vp, c_cp, c_sz]),
+    "ngpb_module_layer_sizes": (c_sz, [c_vp, ctypes.POINTER(c_u32), c_sz]),
+    "ngpb_module_initialize_params": (c_int, [c_vp, c_vp, c_u64, c_vp, c_f32]),
+    "ngpb_module_inference": (c_int, [c_vp, c_vp, c_u32, c_vp, c_vp, c_vp]),
+    "ngpb_module_forward": (c_int, [c_vp, c_vp, c_u32, c_vp, c_vp, c_vp, c_int, ctypes.POINTER(c_vp)]),
+    "ngpb_module_backward": (c_int, [c_vp, c_vp, c_vp, c_u32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "ngpb_context_free": (None, [c_vp]),
+    "ngpb_grid_level_table": (c_u32, [c_vp, ctypes.POINTER(c_u32), ctypes.POINTER(c_f32), ctypes.POINTER(c_u32)]),
+    "ngpb_grid_indices": (c_int, [c_vp, c_vp, c_u32, c_vp, c_vp]),
+    "ngpb_grid_set_max_level": (c_int, [c_vp, c_f32]),
+    "ngpb_random_uniform": (c_int, [c_vp, ctypes.POINTER(c_u64), c_sz, c_vp, c_f32, c_f32]),
+}
+
+
+def _bind():
+    missing = []
+    for name, (res, args) in SIGNATURES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            missing.append(name)
+            continue
+        fn.restype = res
+        fn.argtypes = args
+    return missing
+
+
+MISSING_SYMBOLS = _bind()
+
+
+def check(status):
+    if status != 0:
+        raise NgpbError(lib.ngpb_last_error().decode("utf-8", "replace"))
+
+
+def has_device():
+    return bool(lib.ngpb_has_device())

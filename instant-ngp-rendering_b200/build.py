@@ -1,0 +1,89 @@
+"""Builds libngp_b200.so (CUDA kernels + C ABI, sm_100a only) and the CPU oracle library.
+
+Run as `python instant-ngp-rendering_b200/build.py` or through `__graft_entry__.build()`.
+nvcc cross-compiles without a GPU; objects are cached under build/ by source mtime.
+"""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(PKG_DIR)
+CSRC = os.path.join(PKG_DIR, "csrc")
+BUILD = os.path.join(ROOT, "build")
+LIB_PATH = os.path.join(PKG_DIR, "libngp_b200.so")
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_LIB = os.path.join(ORACLE_DIR, "liboracle.so")
+
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-O3", "-std=c++17", "-lineinfo",
+    "--expt-relaxed-constexpr", "--extended-lambda",
+    "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function",
+    "-Xptxas", "-v" if os.environ.get("NGPB_PTXAS_V") else "-O3",
+]
+
+
+def _newer(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def _run(cmd):
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(" ".join(cmd) + "\n" + res.stdout + res.stderr)
+        raise RuntimeError("build step failed: " + " ".join(cmd[:3]))
+    if os.environ.get("NGPB_PTXAS_V"):
+        sys.stderr.write(res.stderr)
+    return res
+
+
+def build_cuda(verbose=False):
+    os.makedirs(BUILD, exist_ok=True)
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    headers.append(os.path.join(ROOT, "include", "ngp_b200.h"))
+    sources = sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
+    objs, jobs = [], []
+    for s in sources:
+        src = os.path.join(CSRC, s)
+        obj = os.path.join(BUILD, s[:-3] + ".o")
+        objs.append(obj)
+        if _newer(obj, [src] + headers):
+            jobs.append([NVCC] + NVCC_FLAGS + ["-c", src, "-o", obj])
+    if jobs:
+        if verbose:
+            print(f"[build] compiling {len(jobs)} CUDA translation unit(s) for sm_100a")
+        with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
+            list(ex.map(_run, jobs))
+    if jobs or _newer(LIB_PATH, objs):
+        _run([NVCC, "-shared", "-o", LIB_PATH] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart_static", "-ldl", "-lpthread", "-lrt"])
+        if verbose:
+            print(f"[build] linked {LIB_PATH}")
+    return LIB_PATH
+
+
+def build_oracle(verbose=False):
+    srcs = sorted(os.path.join(ORACLE_DIR, f) for f in os.listdir(ORACLE_DIR) if f.endswith((".cpp", ".c")))
+    hdrs = [os.path.join(ORACLE_DIR, f) for f in os.listdir(ORACLE_DIR) if f.endswith(".h")]
+    if not srcs:
+        return None
+    if _newer(ORACLE_LIB, srcs + hdrs):
+        _run(["g++", "-O3", "-march=native", "-std=c++17", "-fopenmp", "-ffp-contract=off", "-fPIC", "-shared",
+              "-o", ORACLE_LIB] + srcs)
+        if verbose:
+            print(f"[build] built {ORACLE_LIB}")
+    return ORACLE_LIB
+
+
+def build_all(verbose=False):
+    build_cuda(verbose)
+    build_oracle(verbose)
+
+
+if __name__ == "__main__":
+    build_all(verbose=True)

@@ -1,0 +1,195 @@
+// Device-side pieces of the grid encoding, shared by the standalone kernels (grid.cu) and
+// the fused encode+MLP kernels (mlp.cu).
+//
+// Arithmetic contract (what must agree with the reference bit for bit):
+//   * cell coordinate and fraction: pos_fract, tcnn common_device.h:856-868
+//   * corner index: grid_index / lcg_hash, tcnn common_device.h:631-707
+//   * interpolation: fp16 FMA chain over corners in ascending corner order,
+//     `result = fma((T)weight, val, result)`, tcnn grid.h:143-163
+// The level-only quantities (scale, resolution, strides, hash-or-dense) come from the
+// GridParams table instead of being recomputed per thread.
+#pragma once
+
+#include "grid.h"
+
+namespace ngpb {
+
+NGPB_D float smoothstep_f(float v) { return v * v * (3.0f - 2.0f * v); }
+NGPB_D float smoothstep_derivative_f(float v) { return 6 * v * (1.0f - v); }
+
+template <uint32_t D>
+struct GridCellT {
+	float w[D];        // interpolation weight toward the +1 corner per dim
+	float dw[D];       // derivative of w w.r.t. the fractional coordinate
+	uint32_t lo[D];    // per-dim index term of the lower corner (dense: pos*stride, hash: pos*prime)
+	uint32_t hi[D];    // same for the +1 corner
+};
+
+// Per-(sample, level) set-up. `x` are the D input coordinates.
+template <uint32_t D, bool WITH_DERIV = false>
+NGPB_D void grid_cell(const GridParams& p, uint32_t level, const float (&x)[D], GridCellT<D>& c) {
+	const float scale = p.scale[level];
+	const bool hashed = p.use_hash[level] != 0;
+#pragma unroll
+	for (uint32_t d = 0; d < D; ++d) {
+		float pos = fmaf(scale, x[d], 0.5f);
+		float fl = floorf(pos);
+		uint32_t pg = (uint32_t)(int)fl;
+		pos -= fl;
+		if (p.interpolation_type == (int)InterpolationType::Smoothstep) {
+			if (WITH_DERIV) c.dw[d] = smoothstep_derivative_f(pos);
+			pos = smoothstep_f(pos);
+		} else if (WITH_DERIV) {
+			c.dw[d] = 1.0f;
+		}
+		c.w[d] = pos;
+		const uint32_t m = hashed ? p.primes[d] : p.stride[level][d];
+		c.lo[d] = pg * m;
+		c.hi[d] = (pg + 1) * m;
+	}
+}
+
+// Entry index (within the level) of corner `corner` (bit d set = +1 along dim d).
+template <uint32_t D>
+NGPB_D uint32_t grid_corner_index(const GridParams& p, uint32_t level, const GridCellT<D>& c, uint32_t corner) {
+	const bool hashed = p.use_hash[level] != 0;
+	uint32_t idx = 0;
+#pragma unroll
+	for (uint32_t d = 0; d < D; ++d) {
+		const uint32_t t = (corner & (1u << d)) ? c.hi[d] : c.lo[d];
+		idx = hashed ? (idx ^ t) : (idx + t);
+	}
+	const uint32_t size = p.size[level];
+	if (p.size_is_pow2[level]) return idx & (size - 1);
+	return idx < size ? idx : idx % size;
+}
+
+template <uint32_t D>
+NGPB_D float grid_corner_weight(const GridCellT<D>& c, uint32_t corner) {
+	float weight = 1;
+#pragma unroll
+	for (uint32_t d = 0; d < D; ++d) {
+		weight *= (corner & (1u << d)) ? c.w[d] : 1 - c.w[d];
+	}
+	return weight;
+}
+
+// One table entry = F halves, loaded with one instruction of F*2 bytes.
+template <uint32_t F> struct GridEntry;
+template <> struct GridEntry<1> { __half v; };
+template <> struct alignas(4) GridEntry<2> { __half2 v[1]; };
+template <> struct alignas(8) GridEntry<4> { __half2 v[2]; };
+template <> struct alignas(16) GridEntry<8> { __half2 v[4]; };
+
+template <uint32_t F>
+NGPB_D GridEntry<F> grid_load(const __half* __restrict__ level_base, uint32_t idx) {
+	GridEntry<F> e;
+	if constexpr (F == 1) {
+		e.v = __ldg(level_base + idx);
+	} else if constexpr (F == 2) {
+		e.v[0] = __ldg(reinterpret_cast<const __half2*>(level_base) + idx);
+	} else if constexpr (F == 4) {
+		uint2 r = __ldg(reinterpret_cast<const uint2*>(level_base) + idx);
+		e.v[0] = *reinterpret_cast<__half2*>(&r.x);
+		e.v[1] = *reinterpret_cast<__half2*>(&r.y);
+	} else {
+		uint4 r = __ldg(reinterpret_cast<const uint4*>(level_base) + idx);
+		e.v[0] = *reinterpret_cast<__half2*>(&r.x);
+		e.v[1] = *reinterpret_cast<__half2*>(&r.y);
+		e.v[2] = *reinterpret_cast<__half2*>(&r.z);
+		e.v[3] = *reinterpret_cast<__half2*>(&r.w);
+	}
+	return e;
+}
+
+// Interpolates level `level` at `x`; writes F halves to res. All 2^D gathers are issued
+// before the FMA chain so that they are in flight together.
+template <uint32_t D, uint32_t F>
+NGPB_D void grid_encode_level(const GridParams& p, uint32_t level, const float (&x)[D],
+	const __half* __restrict__ grid, __half* res)
+{
+	GridCellT<D> c;
+	grid_cell<D>(p, level, x, c);
+	const __half* base = grid + (size_t)p.offset[level] * F;
+
+	if (p.interpolation_type == (int)InterpolationType::Nearest) {
+		GridEntry<F> e = grid_load<F>(base, grid_corner_index<D>(p, level, c, 0));
+		if constexpr (F == 1) res[0] = e.v;
+		else {
+#pragma unroll
+			for (uint32_t f = 0; f < F / 2; ++f) reinterpret_cast<__half2*>(res)[f] = e.v[f];
+		}
+		return;
+	}
+
+	constexpr uint32_t NC = 1u << D;
+	GridEntry<F> e[NC];
+#pragma unroll
+	for (uint32_t k = 0; k < NC; ++k) e[k] = grid_load<F>(base, grid_corner_index<D>(p, level, c, k));
+
+	if constexpr (F == 1) {
+		__half acc = __float2half(0.0f);
+#pragma unroll
+		for (uint32_t k = 0; k < NC; ++k) acc = __hfma(__float2half(grid_corner_weight<D>(c, k)), e[k].v, acc);
+		res[0] = acc;
+	} else {
+		__half2 acc[F / 2];
+#pragma unroll
+		for (uint32_t f = 0; f < F / 2; ++f) acc[f] = __float2half2_rn(0.0f);
+#pragma unroll
+		for (uint32_t k = 0; k < NC; ++k) {
+			const __half2 w = __float2half2_rn(grid_corner_weight<D>(c, k));
+#pragma unroll
+			for (uint32_t f = 0; f < F / 2; ++f) acc[f] = __hfma2(w, e[k].v[f], acc[f]);
+		}
+#pragma unroll
+		for (uint32_t f = 0; f < F / 2; ++f) reinterpret_cast<__half2*>(res)[f] = acc[f];
+	}
+}
+
+// The reference zeroes levels at or above max_level (grid.h:69-92).
+NGPB_D bool grid_level_masked_fwd(const GridParams& p, uint32_t level, float max_level) {
+	const float ml = (max_level * (float)(p.n_levels * p.n_features_per_level)) / (float)p.n_features_per_level;
+	return (float)level >= ml + 1e-3f;
+}
+// ... and skips the scatter for levels strictly above it (grid.h:241-243).
+NGPB_D bool grid_level_masked_bwd(const GridParams& p, uint32_t level, float max_level) {
+	const float ml = (max_level * (float)(p.n_levels * p.n_features_per_level)) / (float)p.n_features_per_level;
+	return (float)level > ml + 1e-3f;
+}
+
+// Gradient scatter of one packed pair: the reference's atomic_add_gmem(__half2*) compiles
+// to the same instruction (tcnn vec.h:326-349).
+NGPB_D void red_add_half2(__half* addr, __half2 v) {
+	asm volatile("red.relaxed.gpu.global.add.noftz.f16x2 [%0], %1;" ::"l"(addr), "r"(*reinterpret_cast<uint32_t*>(&v)) : "memory");
+}
+NGPB_D void red_add_half2x2(__half* addr, __half2 a, __half2 b) {
+	asm volatile("red.relaxed.gpu.global.add.noftz.v2.f16x2 [%0], {%1, %2};" ::"l"(addr),
+		"r"(*reinterpret_cast<uint32_t*>(&a)), "r"(*reinterpret_cast<uint32_t*>(&b)) : "memory");
+}
+NGPB_D void red_add_half2x4(__half* addr, __half2 a, __half2 b, __half2 c, __half2 d) {
+	asm volatile("red.relaxed.gpu.global.add.noftz.v4.f16x2 [%0], {%1, %2, %3, %4};" ::"l"(addr),
+		"r"(*reinterpret_cast<uint32_t*>(&a)), "r"(*reinterpret_cast<uint32_t*>(&b)),
+		"r"(*reinterpret_cast<uint32_t*>(&c)), "r"(*reinterpret_cast<uint32_t*>(&d)) : "memory");
+}
+
+// Scatter w * g (F halves) into one table entry.
+template <uint32_t F>
+NGPB_D void grid_scatter_entry(__half* level_grad, uint32_t idx, float weight, const __half* g) {
+	if constexpr (F == 1) {
+		atomicAdd(level_grad + idx, __hmul(__float2half(weight), g[0]));
+	} else {
+		const __half2 w = __float2half2_rn(weight);
+		const __half2* g2 = reinterpret_cast<const __half2*>(g);
+		__half* addr = level_grad + (size_t)idx * F;
+		if constexpr (F == 2) {
+			red_add_half2(addr, __hmul2(w, g2[0]));
+		} else if constexpr (F == 4) {
+			red_add_half2x2(addr, __hmul2(w, g2[0]), __hmul2(w, g2[1]));
+		} else {
+			red_add_half2x4(addr, __hmul2(w, g2[0]), __hmul2(w, g2[1]), __hmul2(w, g2[2]), __hmul2(w, g2[3]));
+		}
+	}
+}
+
+} // namespace ngpb

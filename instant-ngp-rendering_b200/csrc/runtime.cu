@@ -1,0 +1,49 @@
+// Small runtime pieces: error string, SM count, pcg32 fills.
+#include "module.h"
+
+namespace ngpb {
+
+static thread_local std::string g_last_error;
+
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+const char* last_error() { return g_last_error.c_str(); }
+
+int sm_count() {
+	static int count = -1;
+	if (count < 0) {
+		int dev = 0;
+		cudaDeviceProp prop;
+		if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess) {
+			cudaGetLastError();
+			return 148;
+		}
+		count = prop.multiProcessorCount;
+	}
+	return count;
+}
+
+// The reference fills with generate_random_kernel<T, RNG, 4> (tcnn random.h:39-56): thread t of
+// T = 128 * ceil(ceil(n/4) / 128) threads advances the generator by 4*t and writes elements
+// t, t+T, t+2T, t+3T. So element e takes stream position 4*(e % T) + e / T. One thread per
+// element here (coalesced writes), jumping straight to that position.
+__global__ void random_uniform_kernel(size_t n, size_t n_threads_ref, Pcg32 rng, float* __restrict__ out, float lower, float upper) {
+	const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (e >= n) return;
+	const size_t t = e % n_threads_ref;
+	const size_t j = e / n_threads_ref;
+	rng.advance((int64_t)(t * 4 + j));
+	out[e] = rng.next_float() * (upper - lower) + lower;
+}
+
+void random_uniform(cudaStream_t stream, Pcg32& rng, size_t n, float* out, float lower, float upper) {
+	if (n > 0) {
+		const size_t ref_threads_needed = (n + 3) / 4;
+		const size_t n_threads_ref = 128 * ((ref_threads_needed + 127) / 128);
+		const uint32_t blocks = (uint32_t)((n + 255) / 256);
+		random_uniform_kernel<<<blocks, 256, 0, stream>>>(n, n_threads_ref, rng, out, lower, upper);
+		NGPB_CUDA_CHECK(cudaGetLastError());
+	}
+	rng.advance((int64_t)n);
+}
+
+} // namespace ngpb

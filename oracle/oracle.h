@@ -1,0 +1,74 @@
+/* oracle.h - CPU restatement of the reference's hot-path arithmetic.
+ *
+ * TEST INFRASTRUCTURE ONLY. Nothing under oracle/ is linked into, imported by or called from
+ * the product (libngp_b200.so / the Python package). Only tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs may load liboracle.so, and only as the
+ * checker or the timed CPU baseline.
+ *
+ * PARITY UNPINNED: the reference ships no golden vectors, no known-answer tests and no CPU
+ * implementation for this path, and its CUDA sources cannot run in
+ * the authoring container (no GPU). Each function below restates a cited reference routine;
+ * the only pins are integer invariants derived from the reference code (level tables, hash of
+ * fixed coordinates, Morton round trips) held in tests/golden/.
+ */
+#ifndef NGPB_ORACLE_H
+#define NGPB_ORACLE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Grid configuration (tcnn grid.h:668-730). grid_type: 0 Hash, 1 Dense, 2 Tiled.
+ * hash_type: 0 Prime, 1 CoherentPrime, 2 ReversedPrime. interpolation: 0 Nearest, 1 Linear,
+ * 2 Smoothstep. `scale_override`: optional per-level scales (the library reports the values it
+ * evaluated with the device's exp2f); NULL = host exp2f. */
+typedef struct {
+	uint32_t n_dims;
+	uint32_t n_features_per_level;
+	uint32_t n_levels;
+	uint32_t log2_hashmap_size;
+	uint32_t base_resolution;
+	float per_level_scale;
+	int grid_type;
+	int hash_type;
+	int interpolation;
+	const float* scale_override;
+} oracle_grid_config;
+
+/* offsets[n_levels+1] in entries; returns total entries (grid.h:692-723). */
+uint32_t oracle_grid_offsets(const oracle_grid_config* cfg, uint32_t* offsets);
+/* scales[n_levels], resolutions[n_levels] as the kernels see them (common_device.h:709-718). */
+void oracle_grid_levels(const oracle_grid_config* cfg, float* scales, uint32_t* resolutions);
+/* idx[(i*L + level)*2^D + corner] (common_device.h:690-707, 856-868). */
+void oracle_grid_indices(const oracle_grid_config* cfg, uint32_t n, const float* positions, uint32_t in_stride, uint32_t* idx);
+/* kernel_grid (grid.h:48-170): fp16 params, fp16 FMA chain; out AoS [n][out_stride] halves
+ * (bit patterns); padding columns set to 1.0. max_level as tcnn (1.0 = all). */
+void oracle_grid_forward(const oracle_grid_config* cfg, uint32_t n, const float* positions, uint32_t in_stride,
+	const uint16_t* params, uint16_t* out, uint32_t out_stride, float max_level);
+/* kernel_grid_backward (grid.h:214-320): each contribution is half(weight)*half(dy) rounded to
+ * fp16 as the reference's `(GRAD_T)weight * grad`; contributions are summed in double (the
+ * reference sums them with fp16 atomics in arbitrary order). grad: [entries*F] doubles. */
+void oracle_grid_backward(const oracle_grid_config* cfg, uint32_t n, const float* positions, uint32_t in_stride,
+	const uint16_t* dL_dy, uint32_t dy_stride, double* grad, float max_level);
+/* grid.h:172-211 + 322-349: dL_dx[n][D] in fp32. */
+void oracle_grid_backward_input(const oracle_grid_config* cfg, uint32_t n, const float* positions, uint32_t in_stride,
+	const uint16_t* params, const uint16_t* dL_dy, uint32_t dy_stride, float* dL_dx, float max_level);
+
+/* pcg32 (tcnn/dependencies/pcg32/pcg32.h) helpers for tests. */
+void oracle_pcg32_floats(uint64_t seed, uint64_t advance, uint32_t n, float* out);
+/* generate_random_uniform (tcnn random.h:39-73): element -> stream position mapping. */
+void oracle_random_uniform(uint64_t seed, size_t n, float* out, float lower, float upper);
+
+/* fp16 <-> fp32 (round to nearest even), exposed so tests can build fp16 inputs. */
+uint16_t oracle_float_to_half(float f);
+float oracle_half_to_float(uint16_t h);
+
+int oracle_num_threads(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
