@@ -102,6 +102,11 @@ int ngpb_grid_set_max_level(ngpb_module_t* m, float max_level);
  * advances the caller's generator state (state[0] = state, state[1] = inc). */
 int ngpb_random_uniform(void* stream, uint64_t* rng_state, size_t n, float* out, float lower, float upper);
 
+/* ---- self test of the tcgen05 operand views (tc_device.cuh) --------------------------------
+ * mode 0: D[128xN] = X[128xK] W[NxK]^T; mode 1: D[128xN] = X[128xK] W[KxN];
+ * mode 2: D[64xN] = X[128x64]^T W[128xN]. fp16 row-major inputs, fp32 row-major D (device). */
+int ngpb_selftest_umma(void* stream, int mode, uint32_t K, uint32_t N, const void* X, const void* W, float* D);
+
 #ifdef __cplusplus
 }
 #endif

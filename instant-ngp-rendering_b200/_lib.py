@@ -61,6 +61,7 @@ SIGNATURES = {
     "ngpb_grid_level_table": (c_u32, [c_vp, ctypes.POINTER(c_u32), ctypes.POINTER(c_f32), ctypes.POINTER(c_u32)]),
     "ngpb_grid_indices": (c_int, [c_vp, c_vp, c_u32, c_vp, c_vp]),
     "ngpb_grid_set_max_level": (c_int, [c_vp, c_f32]),
+    "ngpb_selftest_umma": (c_int, [c_vp, c_int, c_u32, c_u32, c_vp, c_vp, c_vp]),
     "ngpb_random_uniform": (c_int, [c_vp, ctypes.POINTER(c_u64), c_sz, c_vp, c_f32, c_f32]),
 }
 

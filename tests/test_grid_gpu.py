@@ -89,8 +89,18 @@ def test_backward_params(ngp, oracle, name):
     assert got.shape == want.shape
     rel = np.linalg.norm(got - want) / max(np.linalg.norm(want), 1e-12)
     assert rel <= 1e-2, rel
-    # entries no sample touches stay exactly zero
-    assert np.all(got[want == 0] == 0)
+    # entries no sample touches stay exactly zero (touch mask from the oracle's corner indices;
+    # a touched entry whose exact sum cancels may keep an fp16 rounding residue, as in the reference)
+    F = cfg.n_features_per_level
+    offs = oracle.grid_offsets(cfg).astype(np.int64)
+    idx = oracle.grid_indices(cfg, x).astype(np.int64)
+    touched = np.zeros(got.size // F, dtype=bool)
+    for level in range(cfg.n_levels):
+        ids = idx[:, level, :1] if cfg.interpolation == 0 else idx[:, level, :]
+        touched[offs[level] + ids.reshape(-1)] = True
+    untouched = np.repeat(~touched, F)
+    assert np.all(got[untouched] == 0)
+    assert np.all(want[untouched] == 0)
 
 
 def test_backward_overwrites_not_accumulates(ngp, oracle):
@@ -126,7 +136,8 @@ def test_max_level_masks_levels(ngp, oracle):
     got = e.inference(torch.from_numpy(x).cuda()).cpu().numpy()
     want = oracle.grid_forward(cfg, x, params, max_level=0.5)
     assert np.array_equal(got.view(np.uint16), want.view(np.uint16))
-    assert np.all(got[:, 16:] == 0) and np.any(got[:, :16] != 0)
+    # max_level 0.5 -> 8 + 1e-3: levels 0..8 stay (grid.h:69-76 compares level >= max_level + 1e-3)
+    assert np.all(got[:, 18:] == 0) and np.any(got[:, 16:18] != 0)
 
 
 def test_full_size_properties(ngp, oracle):
