@@ -193,6 +193,8 @@ Json GridConfig::hyperparams() const {
 
 // =================================== kernels =============================================
 
+NGPB_D uint32_t next_multiple_d(uint32_t a, uint32_t b) { return (a + b - 1) / b * b; }
+
 template <uint32_t D>
 NGPB_D void load_position(const float* __restrict__ positions, uint32_t in_stride, uint32_t i, float (&x)[D]) {
 	const float* src = positions + (size_t)i * in_stride;
@@ -205,16 +207,46 @@ template <uint32_t D, uint32_t F, bool VEC_OUT>
 __global__ void __launch_bounds__(256) grid_forward_kernel(
 	const __grid_constant__ GridParams p, const uint32_t n,
 	const __half* __restrict__ grid, const float* __restrict__ positions, const uint32_t in_stride,
-	__half* __restrict__ out, const uint32_t out_stride, const float max_level)
+	__half* __restrict__ out, const uint32_t out_stride, const float max_level, const uint32_t tiled)
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	constexpr uint32_t C = 8 / F; // levels per 16 B
+	const uint32_t L = p.n_levels;
+
+	if (tiled) {
+		// Tiled output (mlp.h): chunk ch of sample i lives at ((i/128)*(W/8) + ch)*128 + i%128 (in
+		// 16-byte units), so a warp's stores are contiguous. Rows past n (tile padding) are zeroed.
+		if (i >= next_multiple_d(n, 128u)) return;
+		uint4* base = reinterpret_cast<uint4*>(out) + (size_t)(i / 128) * (out_stride / 8) * 128 + (i % 128);
+		if (i >= n) {
+			for (uint32_t ch = 0; ch < out_stride / 8; ++ch) base[ch * 128] = make_uint4(0u, 0u, 0u, 0u);
+			return;
+		}
+		float x[D];
+		load_position<D>(positions, in_stride, i, x);
+		for (uint32_t l0 = 0; l0 < L; l0 += C) {
+			alignas(16) __half vals[8];
+#pragma unroll
+			for (uint32_t c = 0; c < C; ++c) {
+				const uint32_t level = l0 + c;
+				if (level < L && !grid_level_masked_fwd(p, level, max_level)) {
+					grid_encode_level<D, F>(p, level, x, grid, &vals[c * F]);
+				} else {
+#pragma unroll
+					for (uint32_t f = 0; f < F; ++f) vals[c * F + f] = __float2half(level < L ? 0.0f : 1.0f);
+				}
+			}
+			base[(l0 * F / 8) * 128] = *reinterpret_cast<const uint4*>(vals);
+		}
+		for (uint32_t ch = (L * F + 7) / 8; ch < out_stride / 8; ++ch) base[ch * 128] = make_uint4(0x3C003C00u, 0x3C003C00u, 0x3C003C00u, 0x3C003C00u);
+		return;
+	}
+
 	if (i >= n) return;
 
 	float x[D];
 	load_position<D>(positions, in_stride, i, x);
 
-	constexpr uint32_t C = 8 / F; // levels per 16 B
-	const uint32_t L = p.n_levels;
 	__half* dst = out + (size_t)i * out_stride;
 
 	for (uint32_t l0 = 0; l0 < L; l0 += C) {
@@ -247,7 +279,7 @@ template <uint32_t D, uint32_t F, bool VEC_IN>
 __global__ void __launch_bounds__(256) grid_backward_kernel(
 	const __grid_constant__ GridParams p, const uint32_t n,
 	__half* __restrict__ grad, const float* __restrict__ positions, const uint32_t in_stride,
-	const __half* __restrict__ dL_dy, const uint32_t dy_stride, const float max_level)
+	const __half* __restrict__ dL_dy, const uint32_t dy_stride, const float max_level, const uint32_t tiled)
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
@@ -258,10 +290,13 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(
 	constexpr uint32_t C = 8 / F;
 	const uint32_t L = p.n_levels;
 	const __half* src = dL_dy + (size_t)i * dy_stride;
+	const uint4* tbase = reinterpret_cast<const uint4*>(dL_dy) + (size_t)(i / 128) * (dy_stride / 8) * 128 + (i % 128);
 
 	for (uint32_t l0 = 0; l0 < L; l0 += C) {
 		alignas(16) __half g[8];
-		if (VEC_IN && l0 + C <= L) {
+		if (tiled) {
+			*reinterpret_cast<uint4*>(g) = __ldg(tbase + (l0 * F / 8) * 128);
+		} else if (VEC_IN && l0 + C <= L) {
 			*reinterpret_cast<uint4*>(g) = __ldg(reinterpret_cast<const uint4*>(src + l0 * F));
 		} else {
 #pragma unroll
@@ -397,27 +432,33 @@ static bool aligned16(const void* ptr, uint32_t stride_halves) {
 }
 
 void grid_forward(cudaStream_t stream, const GridParams& p, uint32_t n, const __half* grid,
-	const float* positions, uint32_t in_stride, __half* out, uint32_t out_stride, float max_level)
+	const float* positions, uint32_t in_stride, __half* out, uint32_t out_stride, float max_level, bool tiled)
 {
 	if (n == 0) return;
-	const uint32_t blocks = div_round_up(n, 256);
+	const uint32_t blocks = div_round_up(tiled ? next_multiple(n, 128u) : n, 256);
 	const bool vec = aligned16(out, out_stride);
+	if (tiled && (!vec || out_stride % 8 != 0 || (p.n_levels * p.n_features_per_level) % 8 != 0)) {
+		throw std::runtime_error{"GridEncoding: tiled output needs a 16-byte aligned buffer and a feature count that is a multiple of 8"};
+	}
 	NGPB_GRID_DISPATCH(p.n_dims, p.n_features_per_level, {
-		if (vec) grid_forward_kernel<D, F, true><<<blocks, 256, 0, stream>>>(p, n, grid, positions, in_stride, out, out_stride, max_level);
-		else grid_forward_kernel<D, F, false><<<blocks, 256, 0, stream>>>(p, n, grid, positions, in_stride, out, out_stride, max_level);
+		if (vec) grid_forward_kernel<D, F, true><<<blocks, 256, 0, stream>>>(p, n, grid, positions, in_stride, out, out_stride, max_level, tiled ? 1u : 0u);
+		else grid_forward_kernel<D, F, false><<<blocks, 256, 0, stream>>>(p, n, grid, positions, in_stride, out, out_stride, max_level, 0u);
 	});
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }
 
 void grid_backward(cudaStream_t stream, const GridParams& p, uint32_t n, __half* grad,
-	const float* positions, uint32_t in_stride, const __half* dL_dy, uint32_t dy_stride, float max_level)
+	const float* positions, uint32_t in_stride, const __half* dL_dy, uint32_t dy_stride, float max_level, bool tiled)
 {
 	if (n == 0) return;
 	const uint32_t blocks = div_round_up(n, 256);
 	const bool vec = aligned16(dL_dy, dy_stride);
+	if (tiled && (!vec || dy_stride % 8 != 0 || (p.n_levels * p.n_features_per_level) % 8 != 0)) {
+		throw std::runtime_error{"GridEncoding: tiled gradients need a 16-byte aligned buffer and a feature count that is a multiple of 8"};
+	}
 	NGPB_GRID_DISPATCH(p.n_dims, p.n_features_per_level, {
-		if (vec) grid_backward_kernel<D, F, true><<<blocks, 256, 0, stream>>>(p, n, grad, positions, in_stride, dL_dy, dy_stride, max_level);
-		else grid_backward_kernel<D, F, false><<<blocks, 256, 0, stream>>>(p, n, grad, positions, in_stride, dL_dy, dy_stride, max_level);
+		if (vec) grid_backward_kernel<D, F, true><<<blocks, 256, 0, stream>>>(p, n, grad, positions, in_stride, dL_dy, dy_stride, max_level, tiled ? 1u : 0u);
+		else grid_backward_kernel<D, F, false><<<blocks, 256, 0, stream>>>(p, n, grad, positions, in_stride, dL_dy, dy_stride, max_level, 0u);
 	});
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }

@@ -68,14 +68,17 @@ std::string to_string(InterpolationType t);
 //            [L*F, out_stride) are set to `pad_value` (the reference pads with 1,
 //            grid.h:806-811 via Encoding::set_padded_output_width).
 // max_level: as tcnn's m_max_level (1.0 == all levels).
+// tiled:     out / dL_dy use the tile layout of mlp.h ([tile][chunk][128][8 halves], out_stride
+//            = padded feature width) instead of AoS rows; rows up to the next multiple of 128
+//            are written (zeros) so that a consumer may read whole tiles.
 void grid_forward(cudaStream_t stream, const GridParams& p, uint32_t n, const __half* grid,
-	const float* positions, uint32_t in_stride, __half* out, uint32_t out_stride, float max_level);
+	const float* positions, uint32_t in_stride, __half* out, uint32_t out_stride, float max_level, bool tiled = false);
 
 // dL_dy: fp16 AoS with the same layout as `out`. grad: fp16 [entries][F], must be zeroed by
 // the caller when overwrite semantics are wanted (the reference zeroes at grid.h:857-859;
 // ngpb_module_backward does the memset).
 void grid_backward(cudaStream_t stream, const GridParams& p, uint32_t n, __half* grad,
-	const float* positions, uint32_t in_stride, const __half* dL_dy, uint32_t dy_stride, float max_level);
+	const float* positions, uint32_t in_stride, const __half* dL_dy, uint32_t dy_stride, float max_level, bool tiled = false);
 
 // dL_dx[i][d] = sum_k dL_dy[i][k] * dy_k/dx_d, recomputed from the table (the reference
 // stores dy_dx in the forward pass and contracts in kernel_grid_backward_input, grid.h:322-349).

@@ -295,6 +295,29 @@ extern "C" void oracle_pcg32_floats(uint64_t seed, uint64_t advance, uint32_t n,
 	for (uint32_t i = 0; i < n; ++i) out[i] = rng.next_float();
 }
 
+// Same mapping continuing from an arbitrary generator state; advances the state by n
+// (generate_random_uniform, tcnn random.h:66-73).
+extern "C" void oracle_random_uniform_state(uint64_t* rng_state, size_t n, float* out, float lower, float upper) {
+	const size_t n_threads_needed = (n + 3) / 4;
+	const size_t n_threads = 128 * ((n_threads_needed + 127) / 128);
+	for (size_t t = 0; t < n_threads; ++t) {
+		OraclePcg32 rng;
+		rng.state = rng_state[0];
+		rng.inc = rng_state[1];
+		rng.advance((int64_t)(t * 4));
+		for (size_t j = 0; j < 4; ++j) {
+			const size_t idx = t + n_threads * j;
+			if (idx >= n) break;
+			out[idx] = fmaf(rng.next_float(), upper - lower, lower);
+		}
+	}
+	OraclePcg32 rng;
+	rng.state = rng_state[0];
+	rng.inc = rng_state[1];
+	rng.advance((int64_t)n);
+	rng_state[0] = rng.state;
+}
+
 extern "C" void oracle_random_uniform(uint64_t seed, size_t n, float* out, float lower, float upper) {
 	// generate_random_kernel<T, RNG, 4> with 128-thread blocks (tcnn random.h:39-64).
 	const size_t n_threads_needed = (n + 3) / 4;

@@ -61,6 +61,27 @@ void oracle_grid_backward_input(const oracle_grid_config* cfg, uint32_t n, const
 void oracle_pcg32_floats(uint64_t seed, uint64_t advance, uint32_t n, float* out);
 /* generate_random_uniform (tcnn random.h:39-73): element -> stream position mapping. */
 void oracle_random_uniform(uint64_t seed, size_t n, float* out, float lower, float upper);
+void oracle_random_uniform_state(uint64_t* rng_state, size_t n, float* out, float lower, float upper);
+
+/* ---- fused MLP (mlp_oracle.cpp) ------------------------------------------------------------
+ * Weight layout of tcnn FullyFusedMLP (fully_fused_mlp.cu:656-678): W0 [width x in] | hidden
+ * [width x width] x (n_hidden-1) | last [padded_out x width], row-major fp16. */
+size_t oracle_mlp_n_params(uint32_t in_width, uint32_t width, uint32_t n_hidden, uint32_t padded_out);
+/* kernel_mlp_fused (fully_fused_mlp.cu:499-557): x fp16 [n][x_stride], out fp16 [n][out_stride]
+ * (padded_out columns), hidden (optional) fp16 [n_hidden][n][width]. accumulate_fp16: 0 = fp32
+ * accumulator (TMEM), 1 = fp16 accumulator per 16-wide K block (models wmma, :66-68). */
+void oracle_mlp_forward(uint32_t n, uint32_t in_width, uint32_t width, uint32_t n_hidden, uint32_t padded_out, int relu,
+	const uint16_t* weights, const uint16_t* x, uint32_t x_stride, uint16_t* out, uint32_t out_stride, uint16_t* hidden, int accumulate_fp16);
+/* kernel_mlp_fused_backward + weight-gradient GEMMs (fully_fused_mlp.cu:150-259, 735-836). */
+void oracle_mlp_backward(uint32_t n, uint32_t in_width, uint32_t width, uint32_t n_hidden, uint32_t padded_out, int relu,
+	const uint16_t* weights, const uint16_t* x, uint32_t x_stride, const uint16_t* hidden,
+	const uint16_t* dL_dout, uint32_t dy_stride, uint16_t* dL_dx, uint32_t dx_stride, double* dW);
+/* initialize_xavier_uniform per matrix (gpu_matrix.h:284-299); rng_state = {state, inc}, advanced. */
+void oracle_mlp_init(uint64_t* rng_state, uint32_t in_width, uint32_t width, uint32_t n_hidden, uint32_t padded_out, float scale, float* params);
+/* kernel_sh, degree <= 4 (spherical_harmonics.h:46-72, common_device.h:339-365). */
+void oracle_sh_encode(uint32_t n, uint32_t degree, const float* dirs, uint32_t dir_stride, uint16_t* out, uint32_t out_stride);
+void oracle_pcg32_seed(uint64_t seed, uint64_t* rng_state);
+void oracle_pcg32_advance(uint64_t* rng_state, int64_t delta);
 
 /* fp16 <-> fp32 (round to nearest even), exposed so tests can build fp16 inputs. */
 uint16_t oracle_float_to_half(float f);

@@ -130,3 +130,116 @@ def random_uniform(seed, n, lower, upper):
 
 def num_threads():
     return int(olib.oracle_num_threads())
+
+
+# ---- fused MLP / NerfNetwork glue (oracle/mlp_oracle.cpp) ---------------------------------------
+olib.oracle_mlp_n_params.restype = ctypes.c_size_t
+olib.oracle_mlp_n_params.argtypes = [ctypes.c_uint32] * 4
+MLP_WIDTH = 64
+MLP_PADDED_OUT = 16
+
+
+def mlp_n_params(in_width, n_hidden, width=MLP_WIDTH, padded_out=MLP_PADDED_OUT):
+    return int(olib.oracle_mlp_n_params(in_width, width, n_hidden, padded_out))
+
+
+def mlp_forward(weights_f16, x_f16, n_hidden, relu=True, accumulate_fp16=False, width=MLP_WIDTH, padded_out=MLP_PADDED_OUT):
+    """Returns (out [n][padded_out] fp16, hidden [n_hidden][n][width] fp16)."""
+    w = np.ascontiguousarray(weights_f16, dtype=np.float16)
+    x = np.ascontiguousarray(x_f16, dtype=np.float16)
+    n, in_width = x.shape
+    assert w.size == mlp_n_params(in_width, n_hidden, width, padded_out)
+    out = np.zeros((n, padded_out), dtype=np.float16)
+    hidden = np.zeros((n_hidden, n, width), dtype=np.float16)
+    u16 = ctypes.c_uint16
+    olib.oracle_mlp_forward(ctypes.c_uint32(n), ctypes.c_uint32(in_width), ctypes.c_uint32(width), ctypes.c_uint32(n_hidden),
+                            ctypes.c_uint32(padded_out), ctypes.c_int(int(relu)), _p(w.view(np.uint16), u16),
+                            _p(x.view(np.uint16), u16), ctypes.c_uint32(in_width), _p(out.view(np.uint16), u16),
+                            ctypes.c_uint32(padded_out), _p(hidden.view(np.uint16), u16), ctypes.c_int(int(accumulate_fp16)))
+    return out, hidden
+
+
+def mlp_backward(weights_f16, x_f16, hidden_f16, dL_dout_f16, n_hidden, relu=True, width=MLP_WIDTH, padded_out=MLP_PADDED_OUT):
+    """Returns (dL_dx [n][in] fp16, dW [n_params] float64)."""
+    w = np.ascontiguousarray(weights_f16, dtype=np.float16)
+    x = np.ascontiguousarray(x_f16, dtype=np.float16)
+    h = np.ascontiguousarray(hidden_f16, dtype=np.float16)
+    dy = np.ascontiguousarray(dL_dout_f16, dtype=np.float16)
+    n, in_width = x.shape
+    dx = np.zeros((n, in_width), dtype=np.float16)
+    dW = np.zeros(w.size, dtype=np.float64)
+    u16 = ctypes.c_uint16
+    olib.oracle_mlp_backward(ctypes.c_uint32(n), ctypes.c_uint32(in_width), ctypes.c_uint32(width), ctypes.c_uint32(n_hidden),
+                             ctypes.c_uint32(padded_out), ctypes.c_int(int(relu)), _p(w.view(np.uint16), u16),
+                             _p(x.view(np.uint16), u16), ctypes.c_uint32(in_width), _p(h.view(np.uint16), u16),
+                             _p(dy.view(np.uint16), u16), ctypes.c_uint32(dy.shape[1]), _p(dx.view(np.uint16), u16),
+                             ctypes.c_uint32(in_width), _p(dW, ctypes.c_double))
+    return dx, dW
+
+
+class Pcg32State:
+    """pcg32(seed) as {state, inc}; passed to the initialisers which advance it."""
+
+    def __init__(self, seed):
+        self.arr = np.zeros(2, dtype=np.uint64)
+        olib.oracle_pcg32_seed(ctypes.c_uint64(seed), _p(self.arr, ctypes.c_uint64))
+
+    def advance(self, delta):
+        olib.oracle_pcg32_advance(_p(self.arr, ctypes.c_uint64), ctypes.c_int64(delta))
+
+
+def mlp_init(rng, in_width, n_hidden, scale=1.0, width=MLP_WIDTH, padded_out=MLP_PADDED_OUT):
+    out = np.zeros(mlp_n_params(in_width, n_hidden, width, padded_out), dtype=np.float32)
+    olib.oracle_mlp_init(_p(rng.arr, ctypes.c_uint64), ctypes.c_uint32(in_width), ctypes.c_uint32(width), ctypes.c_uint32(n_hidden),
+                         ctypes.c_uint32(padded_out), ctypes.c_float(scale), _p(out, ctypes.c_float))
+    return out
+
+
+def random_uniform_from(rng, n, lower, upper):
+    """generate_random_uniform continuing from a generator state (tcnn random.h:39-73)."""
+    out = np.zeros(n, dtype=np.float32)
+    olib.oracle_random_uniform_state(_p(rng.arr, ctypes.c_uint64), ctypes.c_size_t(n), _p(out, ctypes.c_float), ctypes.c_float(lower), ctypes.c_float(upper))
+    return out
+
+
+def sh_encode(dirs_f32, degree=4):
+    d = np.ascontiguousarray(dirs_f32, dtype=np.float32)
+    out = np.zeros((d.shape[0], 16), dtype=np.float16)
+    olib.oracle_sh_encode(ctypes.c_uint32(d.shape[0]), ctypes.c_uint32(degree), _p(d, ctypes.c_float), ctypes.c_uint32(d.shape[1]),
+                          _p(out.view(np.uint16), ctypes.c_uint16), ctypes.c_uint32(16))
+    return out
+
+
+def nerf_forward(grid_cfg_, params_f16, coords, n_hidden_density, n_hidden_rgb, accumulate_fp16=False, sh_degree=4, dir_offset=4):
+    """NerfNetwork::forward (nerf_network.h:145-187) composed from the oracle pieces.
+    Returns dict with out [n][16] (rgb in 0-2, density-MLP output 0 in channel 3) and the intermediates."""
+    L, F = grid_cfg_.n_levels, grid_cfg_.n_features_per_level
+    pos_w = ((L * F + 15) // 16) * 16
+    nd = mlp_n_params(pos_w, n_hidden_density)
+    nr = mlp_n_params(32, n_hidden_rgb)
+    p = np.ascontiguousarray(params_f16, dtype=np.float16)
+    wd, wr, wg = p[:nd], p[nd:nd + nr], p[nd + nr:]
+    x0 = grid_forward(grid_cfg_, coords[:, :3], wg, out_stride=pos_w)
+    yd, hd = mlp_forward(wd, x0, n_hidden_density, accumulate_fp16=accumulate_fp16)
+    sh = sh_encode(coords[:, dir_offset:dir_offset + 3], sh_degree)
+    x1 = np.concatenate([yd, sh], axis=1)
+    yr, hr = mlp_forward(wr, x1, n_hidden_rgb, accumulate_fp16=accumulate_fp16)
+    out = yr.copy()
+    out[:, 3] = yd[:, 0]
+    return dict(out=out, x0=x0, yd=yd, hd=hd, x1=x1, yr=yr, hr=hr, wd=wd, wr=wr, nd=nd, nr=nr)
+
+
+def nerf_backward(grid_cfg_, fwd, coords, dL_dout_f16, n_hidden_density, n_hidden_rgb):
+    """NerfNetwork::backward (nerf_network.h:189-268). dL_dout [n][>=4] fp16: rgb 0-2, sigma 3.
+    Returns float64 gradients (mlp density, mlp rgb, grid)."""
+    dy = np.ascontiguousarray(dL_dout_f16, dtype=np.float16)
+    n = dy.shape[0]
+    g_rgb = np.zeros((n, 16), dtype=np.float16)
+    g_rgb[:, :3] = dy[:, :3]
+    dx1, dWr = mlp_backward(fwd["wr"], fwd["x1"], fwd["hr"], g_rgb, n_hidden_rgb)
+    g_den = dx1[:, :16].astype(np.float32)
+    g_den[:, 0] += dy[:, 3].astype(np.float32)
+    g_den = g_den.astype(np.float16)
+    dx0, dWd = mlp_backward(fwd["wd"], fwd["x0"], fwd["hd"], g_den, n_hidden_density)
+    gg = grid_backward(grid_cfg_, coords[:, :3], dx0)
+    return dWd, dWr, gg, dx0
