@@ -1,0 +1,273 @@
+// Fused Adam + EMA parameter update (see optimizer.h).
+#include "optimizer.h"
+
+#include <cmath>
+#include <limits>
+
+namespace ngpb {
+
+struct AdamArgs {
+	uint32_t n_elements, n_matrix_weights;
+	float relative_weight_decay, absolute_weight_decay, weight_clipping_magnitude;
+	float loss_scale, learning_rate, non_matrix_learning_rate_factor;
+	uint32_t optimize_matrix_params, optimize_non_matrix_params;
+	float beta1, beta2, epsilon, lower_lr_bound, upper_lr_bound, l2_reg;
+	// EMA
+	uint32_t has_ema, ema_full_precision;
+	float ema_decay, ema_debias_old, ema_debias_new;
+};
+
+// One parameter: the arithmetic of adam_step (adam.h:72-118) followed by ema_step_half_precision /
+// ema_step_full_precision (ema.h:46-78), expression for expression.
+NGPB_D void update_one(const AdamArgs& a, uint32_t i, float grad_h, float& w_fp, __half& w_h, float& m1, float& m2, uint32_t& steps,
+	__half& ema_h, float* ema_tmp)
+{
+	float gradient = grad_h / a.loss_scale;
+	bool skip;
+	if (i >= a.n_matrix_weights) skip = !a.optimize_non_matrix_params || gradient == 0;
+	else skip = !a.optimize_matrix_params;
+
+	if (!skip) {
+		const float weight_fp = w_fp;
+		if (i < a.n_matrix_weights) gradient += a.l2_reg * weight_fp;
+		const float gradient_sq = gradient * gradient;
+		const float first_moment = m1 = a.beta1 * m1 + (1 - a.beta1) * gradient;
+		const float second_moment = m2 = a.beta2 * m2 + (1 - a.beta2) * gradient_sq;
+		float learning_rate = a.learning_rate;
+		if (i >= a.n_matrix_weights) learning_rate *= a.non_matrix_learning_rate_factor;
+		const uint32_t current_step = ++steps;
+		learning_rate *= sqrtf(1 - powf(a.beta2, (float)current_step)) / (1 - powf(a.beta1, (float)current_step));
+		const float effective_learning_rate = fminf(fmaxf(learning_rate / (sqrtf(second_moment) + a.epsilon), a.lower_lr_bound), a.upper_lr_bound);
+		const float decayed_weight = (1 - a.relative_weight_decay * learning_rate) * weight_fp - copysignf(a.absolute_weight_decay * learning_rate, weight_fp);
+		float new_weight = decayed_weight - effective_learning_rate * first_moment;
+		if (a.weight_clipping_magnitude != 0.0f) new_weight = fminf(fmaxf(new_weight, -a.weight_clipping_magnitude), a.weight_clipping_magnitude);
+		w_fp = new_weight;
+		w_h = __float2half(new_weight);
+	}
+	if (a.has_ema) {
+		const float prev = a.ema_full_precision ? *ema_tmp : __half2float(ema_h);
+		const float filtered = (prev * a.ema_decay * a.ema_debias_old + __half2float(w_h) * (1 - a.ema_decay)) * a.ema_debias_new;
+		if (a.ema_full_precision) *ema_tmp = filtered;
+		ema_h = __float2half(filtered);
+	}
+}
+
+// Four parameters per thread: 8/16-byte accesses on every stream. Parameters whose gradient is
+// zero skip the Adam state entirely (only grad + fp16 weight + EMA are touched), as in the
+// reference, so untouched hash-table entries cost 8 bytes instead of 38.
+__global__ void __launch_bounds__(256) adam_ema_step_kernel(const __grid_constant__ AdamArgs a,
+	float* __restrict__ weights_fp32, __half* __restrict__ weights, const __half* __restrict__ gradients,
+	float* __restrict__ first_moments, float* __restrict__ second_moments, uint32_t* __restrict__ param_steps,
+	__half* __restrict__ weights_ema, float* __restrict__ ema_tmp)
+{
+	const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+	if (i0 >= a.n_elements) return;
+	if (i0 + 4 <= a.n_elements) {
+		const uint2 graw = __ldg(reinterpret_cast<const uint2*>(gradients + i0));
+		__half g[4];
+		*reinterpret_cast<uint2*>(g) = graw;
+		bool any_adam = false;
+#pragma unroll
+		for (uint32_t k = 0; k < 4; ++k) {
+			const uint32_t i = i0 + k;
+			const bool skip = i >= a.n_matrix_weights ? (!a.optimize_non_matrix_params || __half2float(g[k]) / a.loss_scale == 0) : !a.optimize_matrix_params;
+			any_adam |= !skip;
+		}
+		if (!any_adam && !a.has_ema) return;
+		__half wh[4], eh[4];
+		*reinterpret_cast<uint2*>(wh) = *reinterpret_cast<const uint2*>(weights + i0);
+		if (a.has_ema) *reinterpret_cast<uint2*>(eh) = *reinterpret_cast<const uint2*>(weights_ema + i0);
+		float wf[4], m1[4], m2[4], et[4];
+		uint32_t st[4];
+		if (any_adam) {
+			*reinterpret_cast<float4*>(wf) = *reinterpret_cast<const float4*>(weights_fp32 + i0);
+			*reinterpret_cast<float4*>(m1) = *reinterpret_cast<const float4*>(first_moments + i0);
+			*reinterpret_cast<float4*>(m2) = *reinterpret_cast<const float4*>(second_moments + i0);
+			*reinterpret_cast<uint4*>(st) = *reinterpret_cast<const uint4*>(param_steps + i0);
+		}
+		if (a.has_ema && a.ema_full_precision) *reinterpret_cast<float4*>(et) = *reinterpret_cast<const float4*>(ema_tmp + i0);
+#pragma unroll
+		for (uint32_t k = 0; k < 4; ++k) update_one(a, i0 + k, __half2float(g[k]), wf[k], wh[k], m1[k], m2[k], st[k], eh[k], &et[k]);
+		if (any_adam) {
+			*reinterpret_cast<float4*>(weights_fp32 + i0) = *reinterpret_cast<const float4*>(wf);
+			*reinterpret_cast<float4*>(first_moments + i0) = *reinterpret_cast<const float4*>(m1);
+			*reinterpret_cast<float4*>(second_moments + i0) = *reinterpret_cast<const float4*>(m2);
+			*reinterpret_cast<uint4*>(param_steps + i0) = *reinterpret_cast<const uint4*>(st);
+			*reinterpret_cast<uint2*>(weights + i0) = *reinterpret_cast<const uint2*>(wh);
+		}
+		if (a.has_ema) {
+			*reinterpret_cast<uint2*>(weights_ema + i0) = *reinterpret_cast<const uint2*>(eh);
+			if (a.ema_full_precision) *reinterpret_cast<float4*>(ema_tmp + i0) = *reinterpret_cast<const float4*>(et);
+		}
+	} else {
+		for (uint32_t i = i0; i < a.n_elements; ++i) {
+			__half eh = a.has_ema ? weights_ema[i] : __float2half(0.0f);
+			float et = (a.has_ema && a.ema_full_precision) ? ema_tmp[i] : 0.0f;
+			update_one(a, i, __half2float(gradients[i]), weights_fp32[i], weights[i], first_moments[i], second_moments[i], param_steps[i], eh, &et);
+			if (a.has_ema) {
+				weights_ema[i] = eh;
+				if (a.ema_full_precision) ema_tmp[i] = et;
+			}
+		}
+	}
+}
+
+// -------------------------------------------------------------------------------------------------
+Optimizer::Optimizer(const Json& config) { parse(config, true); }
+Optimizer::~Optimizer() { release(); }
+
+void Optimizer::release() {
+	cudaFree(m_first_moments); cudaFree(m_second_moments); cudaFree(m_param_steps); cudaFree(m_weights_ema); cudaFree(m_ema_tmp);
+	m_first_moments = m_second_moments = m_ema_tmp = nullptr;
+	m_param_steps = nullptr;
+	m_weights_ema = nullptr;
+	m_capacity = 0;
+}
+
+void Optimizer::parse(const Json& config, bool construct) {
+	const Json* cur = &config;
+	bool seen_adam = false;
+	for (int depth = 0; depth < 8 && cur; ++depth) {
+		const std::string otype = cur->value("otype", "Adam");
+		if (equals_case_insensitive(otype, "Ema")) {
+			if (construct) m_has_ema = true;
+			if (cur->contains("decay")) m_ema_decay = (*cur)["decay"].as_float();
+			if (cur->contains("full_precision")) m_ema_full_precision = (*cur)["full_precision"].as_bool();
+		} else if (equals_case_insensitive(otype, "ExponentialDecay")) {
+			if (construct) m_has_decay = true;
+			if (cur->contains("decay_base")) m_decay_base = (*cur)["decay_base"].as_float();
+			if (cur->contains("decay_interval")) m_decay_interval = (*cur)["decay_interval"].as_uint();
+			if (cur->contains("decay_start")) m_decay_start = (*cur)["decay_start"].as_uint();
+			if (cur->contains("decay_end")) m_decay_end = (*cur)["decay_end"].as_uint();
+		} else if (equals_case_insensitive(otype, "Adam")) {
+			const Json& p = *cur;
+			if (p.contains("beta1")) m_beta1 = p["beta1"].as_float();
+			if (p.contains("beta2")) m_beta2 = p["beta2"].as_float();
+			if (p.contains("epsilon")) m_epsilon = p["epsilon"].as_float();
+			// Under ExponentialDecay the wrapper re-imposes its own base rate every step
+			// (exponential_decay.h:69), so a later "learning_rate" update has no effect there.
+			if (p.contains("learning_rate") && (construct || !m_has_decay)) m_base_learning_rate = p["learning_rate"].as_float();
+			if (p.contains("l2_reg")) m_l2_reg = p["l2_reg"].as_float();
+			if (p.contains("adabound")) m_adabound = p["adabound"].as_bool();
+			if (p.contains("relative_decay")) m_relative_weight_decay = p["relative_decay"].as_float();
+			if (p.contains("absolute_decay")) m_absolute_weight_decay = p["absolute_decay"].as_float();
+			if (p.contains("clipping_magnitude")) m_weight_clipping_magnitude = p["clipping_magnitude"].as_float();
+			if (p.contains("non_matrix_learning_rate_factor")) m_non_matrix_learning_rate_factor = p["non_matrix_learning_rate_factor"].as_float();
+			if (p.contains("optimize_matrix_params")) m_optimize_matrix_params = p["optimize_matrix_params"].as_bool();
+			if (p.contains("optimize_non_matrix_params")) m_optimize_non_matrix_params = p["optimize_non_matrix_params"].as_bool();
+			seen_adam = true;
+			break;
+		} else {
+			const bool reference_type = equals_case_insensitive(otype, "Average") || equals_case_insensitive(otype, "Batched") ||
+				equals_case_insensitive(otype, "Composite") || equals_case_insensitive(otype, "Lookahead") ||
+				equals_case_insensitive(otype, "Novograd") || equals_case_insensitive(otype, "SGD") || equals_case_insensitive(otype, "Shampoo");
+			if (reference_type) throw std::runtime_error{"ngp-b200: optimizer type " + otype + " is not available (Ema, ExponentialDecay and Adam are)"};
+			throw std::runtime_error{"Invalid optimizer type: " + otype};
+		}
+		if (!cur->contains("nested")) { cur = nullptr; break; }
+		cur = &(*cur)["nested"];
+	}
+	if (construct && !seen_adam && cur == nullptr) {
+		// create_optimizer(params.value("nested", json::object())) -> Adam with defaults
+		seen_adam = true;
+	}
+}
+
+void Optimizer::update_hyperparams(const Json& config) { parse(config, false); }
+
+void Optimizer::set_learning_rate(float v) { m_base_learning_rate = v / m_learning_rate_factor; }
+
+Json Optimizer::hyperparams() const {
+	Json adam = Json::object();
+	adam["otype"] = "Adam";
+	adam["beta1"] = m_beta1; adam["beta2"] = m_beta2; adam["epsilon"] = m_epsilon;
+	adam["learning_rate"] = learning_rate(); adam["l2_reg"] = m_l2_reg; adam["adabound"] = m_adabound;
+	adam["relative_decay"] = m_relative_weight_decay; adam["absolute_decay"] = m_absolute_weight_decay;
+	adam["clipping_magnitude"] = m_weight_clipping_magnitude;
+	adam["non_matrix_learning_rate_factor"] = m_non_matrix_learning_rate_factor;
+	adam["optimize_matrix_params"] = m_optimize_matrix_params; adam["optimize_non_matrix_params"] = m_optimize_non_matrix_params;
+	Json cur = adam;
+	if (m_has_decay) {
+		Json d = Json::object();
+		d["otype"] = "ExponentialDecay"; d["nested"] = cur;
+		d["decay_base"] = m_decay_base; d["decay_interval"] = m_decay_interval; d["decay_start"] = m_decay_start; d["decay_end"] = m_decay_end;
+		cur = d;
+	}
+	if (m_has_ema) {
+		Json e = Json::object();
+		e["otype"] = "EMA"; e["nested"] = cur; e["decay"] = m_ema_decay; e["full_precision"] = m_ema_full_precision;
+		cur = e;
+	}
+	return cur;
+}
+
+void Optimizer::allocate(uint32_t n_weights, const std::vector<std::pair<uint32_t, uint32_t>>& layer_sizes) {
+	m_n_weights = n_weights;
+	if (n_weights <= m_capacity) return;
+	release();
+	const size_t n = next_multiple(n_weights, 4u);
+	NGPB_CUDA_CHECK(cudaMalloc(&m_first_moments, n * sizeof(float)));
+	NGPB_CUDA_CHECK(cudaMalloc(&m_second_moments, n * sizeof(float)));
+	NGPB_CUDA_CHECK(cudaMalloc(&m_param_steps, n * sizeof(uint32_t)));
+	NGPB_CUDA_CHECK(cudaMemset(m_first_moments, 0, n * sizeof(float)));
+	NGPB_CUDA_CHECK(cudaMemset(m_second_moments, 0, n * sizeof(float)));
+	NGPB_CUDA_CHECK(cudaMemset(m_param_steps, 0, n * sizeof(uint32_t)));
+	if (m_has_ema) {
+		NGPB_CUDA_CHECK(cudaMalloc(&m_weights_ema, n * sizeof(__half)));
+		NGPB_CUDA_CHECK(cudaMemset(m_weights_ema, 0, n * sizeof(__half)));
+		if (m_ema_full_precision) {
+			NGPB_CUDA_CHECK(cudaMalloc(&m_ema_tmp, n * sizeof(float)));
+			NGPB_CUDA_CHECK(cudaMemset(m_ema_tmp, 0, n * sizeof(float)));
+		}
+	}
+	m_capacity = n_weights;
+	m_n_matrix_weights = 0;
+	for (const auto& l : layer_sizes) m_n_matrix_weights += l.first * l.second;
+}
+
+void Optimizer::step(cudaStream_t stream, float loss_scale, float* weights_fp32, __half* weights, const __half* gradients) {
+	if (m_n_weights == 0) return;
+	// ExponentialDecayOptimizer::step (exponential_decay.h:60-71), evaluated on the step count
+	// *before* Adam increments it.
+	if (m_has_decay) {
+		if (m_current_step == 0) m_learning_rate_factor = 1.0f;
+		if (m_current_step >= m_decay_start && (m_current_step - m_decay_start) % m_decay_interval == 0 && m_current_step <= m_decay_end) {
+			m_learning_rate_factor *= m_decay_base;
+		}
+	}
+	++m_current_step;
+
+	AdamArgs a{};
+	a.n_elements = m_n_weights;
+	a.n_matrix_weights = m_n_matrix_weights;
+	a.relative_weight_decay = m_relative_weight_decay;
+	a.absolute_weight_decay = m_absolute_weight_decay;
+	a.weight_clipping_magnitude = m_weight_clipping_magnitude;
+	a.loss_scale = loss_scale;
+	a.learning_rate = m_base_learning_rate * m_learning_rate_factor;
+	a.non_matrix_learning_rate_factor = m_non_matrix_learning_rate_factor;
+	a.optimize_matrix_params = m_optimize_matrix_params;
+	a.optimize_non_matrix_params = m_optimize_non_matrix_params;
+	a.beta1 = m_beta1; a.beta2 = m_beta2; a.epsilon = m_epsilon;
+	a.lower_lr_bound = 0.0f;
+	a.upper_lr_bound = std::numeric_limits<float>::max();
+	if (m_adabound) { // adam.h:165-168
+		a.lower_lr_bound = 0.1f - 0.1f / ((1 - m_beta2) * (float)m_current_step + 1);
+		a.upper_lr_bound = 0.1f + 0.1f / ((1 - m_beta2) * (float)m_current_step);
+	}
+	a.l2_reg = m_l2_reg;
+	a.has_ema = m_has_ema;
+	a.ema_full_precision = m_ema_full_precision;
+	a.ema_decay = m_ema_decay;
+	a.ema_debias_old = 1 - (float)std::pow(m_ema_decay, m_current_step - 1); // ema.h:106-107
+	a.ema_debias_new = 1.0f / (1 - (float)std::pow(m_ema_decay, m_current_step));
+
+	const bool aligned = ((uintptr_t)weights_fp32 % 16 == 0) && ((uintptr_t)weights % 8 == 0) && ((uintptr_t)gradients % 8 == 0);
+	if (!aligned) throw std::runtime_error{"ngp-b200 optimizer: parameter buffers must be 16-byte (fp32) / 8-byte (fp16) aligned"};
+	const uint32_t n_threads = div_round_up(m_n_weights, 4);
+	adam_ema_step_kernel<<<div_round_up(n_threads, 256), 256, 0, stream>>>(a, weights_fp32, weights, gradients,
+		m_first_moments, m_second_moments, m_param_steps, m_weights_ema, m_ema_tmp);
+	NGPB_CUDA_CHECK(cudaGetLastError());
+}
+
+} // namespace ngpb
