@@ -102,6 +102,122 @@ int ngpb_grid_set_max_level(ngpb_module_t* m, float max_level);
  * advances the caller's generator state (state[0] = state, state[1] = inc). */
 int ngpb_random_uniform(void* stream, uint64_t* rng_state, size_t n, float* out, float lower, float upper);
 
+
+/* ---- optimizer ------------------------------------------------------------------------------
+ * tcnn::create_optimizer<T>(json) (tcnn/src/optimizer.cu:48-82) for the chain the shipped configs
+ * use, [Ema o] [ExponentialDecay o] Adam, and tcnn::Optimizer<T> (tcnn optimizer.h):
+ * allocate / step / learning_rate / step / custom_weights / update_hyperparams / hyperparams. */
+typedef struct ngpb_optimizer ngpb_optimizer_t;
+int ngpb_optimizer_create(const char* optimizer_json, ngpb_optimizer_t** out);
+void ngpb_optimizer_free(ngpb_optimizer_t* o);
+/* layer_rows_cols: n_layers (rows, cols) pairs = ParametricObject::layer_sizes of the model. */
+int ngpb_optimizer_allocate(ngpb_optimizer_t* o, uint32_t n_weights, const uint32_t* layer_rows_cols, size_t n_layers);
+/* weights_fp32 / weights (fp16) / gradients (fp16): device pointers to n_weights elements. */
+int ngpb_optimizer_step(ngpb_optimizer_t* o, void* stream, float loss_scale, float* weights_fp32, void* weights, const void* gradients);
+float ngpb_optimizer_learning_rate(const ngpb_optimizer_t* o);
+int ngpb_optimizer_set_learning_rate(ngpb_optimizer_t* o, float lr);
+uint32_t ngpb_optimizer_step_count(const ngpb_optimizer_t* o);
+/* EMA weights (device, fp16) or NULL when the chain has no Ema stage. */
+void* ngpb_optimizer_custom_weights(const ngpb_optimizer_t* o);
+int ngpb_optimizer_update_hyperparams(ngpb_optimizer_t* o, const char* optimizer_json);
+size_t ngpb_optimizer_hyperparams(const ngpb_optimizer_t* o, char* buf, size_t cap);
+/* Device pointers to the Adam state (first moments, second moments: float; steps: uint32). */
+int ngpb_optimizer_state(const ngpb_optimizer_t* o, float** first_moments, float** second_moments, uint32_t** param_steps);
+
+/* ---- NerfNetwork extras (nerf_network.h:270-279, 356-371) --------------------------------------- */
+/* density-MLP output 0 per sample: input fp32 rows of in_stride floats (position first), output
+ * fp16 [n][out_stride] with out_stride 1 or 16; n multiple of 128. */
+int ngpb_nerf_network_density(ngpb_module_t* m, void* stream, uint32_t n, const float* input, uint32_t in_stride, void* output, uint32_t out_stride, const void* params);
+/* offsets[4] (in parameters) of density MLP, rgb MLP, pos encoding, dir encoding in the flat buffer. */
+int ngpb_nerf_network_param_layout(const ngpb_module_t* m, size_t* offsets);
+
+/* ---- NeRF kernels (src/testbed_nerf.cu) ---------------------------------------------------------
+ * POD views of the buffers the reference passes to generate_training_samples_nerf (:679-838) and
+ * compute_loss_kernel_train_nerf (:841-1160). All pointers are device pointers. */
+typedef struct {
+	const void* pixels;          /* TrainingImageMetadata::pixels */
+	int image_data_type;         /* EImageDataType: 1 Byte (sRGB8, straight alpha), 2 Half, 3 Float (linear, premultiplied) */
+	int lens_mode;               /* ELensMode: 0 Perspective, 1 OpenCV */
+	float lens_params[7];
+	int res_x, res_y;
+	float principal_x, principal_y;
+	float focal_x, focal_y;
+	float xform[12];             /* camera-to-world, column-major 4 columns x 3 (tcnn mat4x3) */
+} ngpb_nerf_image_t;
+
+typedef struct {
+	uint32_t numsteps, numsteps_compacted, rays;
+	float loss_sum;
+} ngpb_nerf_counters_t;
+
+typedef struct {
+	float aabb_min[3], aabb_max[3];
+	uint32_t n_rays, n_rays_total, max_samples, max_samples_compacted, n_training_images, max_mip;
+	float cone_angle_constant, near_distance, loss_scale;
+	int snap_to_pixel_centers, random_bg_color, linear_colors, color_space, loss_type, rgb_activation, density_activation;
+	float background_color[3];
+} ngpb_nerf_train_config_t;
+
+typedef struct {
+	const ngpb_nerf_image_t* metadata;
+	const uint8_t* density_bitfield;
+	const float* mean_density;
+	ngpb_nerf_counters_t* counters;
+	uint32_t* ray_indices;
+	float* rays_unnormalized;    /* [n_rays][6] */
+	uint32_t* numsteps;          /* [n_rays][2] */
+	float* coords;               /* [max_samples][7] NerfCoordinate */
+	const void* rgbsigma;        /* fp16 [max_samples][4] */
+	float* coords_compacted;     /* [max_samples_compacted][7] */
+	void* dloss_doutput;         /* fp16 [max_samples_compacted][4] */
+	float* loss;                 /* [n_rays] */
+} ngpb_nerf_train_buffers_t;
+
+/* rng_state = {state, inc} of the step's pcg32 (m_rng). Counters must be zeroed by the caller. */
+int ngpb_nerf_generate_training_samples(void* stream, const ngpb_nerf_train_config_t* cfg, const ngpb_nerf_train_buffers_t* buf, const uint64_t* rng_state);
+int ngpb_nerf_compute_loss_and_compact(void* stream, const ngpb_nerf_train_config_t* cfg, const ngpb_nerf_train_buffers_t* buf, const uint64_t* rng_state);
+/* update_density_grid_mean_and_bitfield (:2362-2379): grid float [(max_cascade+1) * 128^3] in Morton
+ * order, bitfield uint8 [8 * 128^3 / 8], mean_density 1 float. */
+int ngpb_nerf_update_bitfield(void* stream, uint32_t max_cascade, const float* grid, uint8_t* bitfield, float* mean_density);
+size_t ngpb_nerf_bitfield_bytes(void);
+
+/* ---- Testbed (include/neural-graphics-primitives/testbed.h, src/python_api.cu:383-567) -------------
+ * NeRF mode of ngp::Testbed: dataset set-up as pyngp's create_empty_nerf_dataset / set_image /
+ * set_camera_extrinsics+intrinsics, reload_network_from_json, train(batch), render. */
+typedef struct ngpb_testbed ngpb_testbed_t;
+int ngpb_testbed_create(ngpb_testbed_t** out);
+void ngpb_testbed_free(ngpb_testbed_t* t);
+int ngpb_testbed_create_empty_nerf_dataset(ngpb_testbed_t* t, uint32_t n_images, int aabb_scale, int is_hdr);
+/* pixels: host or device pointer, w*h RGBA texels of image_data_type. */
+int ngpb_testbed_set_nerf_image(ngpb_testbed_t* t, uint32_t idx, const void* pixels, int image_data_type, int width, int height);
+/* xform_3x4: camera-to-world in NGP convention, row-major [3][4]. */
+int ngpb_testbed_set_nerf_camera(ngpb_testbed_t* t, uint32_t idx, const float* xform_3x4, float focal_x, float focal_y,
+	float principal_x, float principal_y, int lens_mode, const float* lens_params);
+int ngpb_testbed_reload_network_from_json(ngpb_testbed_t* t, const char* config_json);
+int ngpb_testbed_reset_network(ngpb_testbed_t* t, int clear_density_grid);
+/* Testbed::train(batch_size), src/testbed.cu:4020-4109. */
+int ngpb_testbed_train(ngpb_testbed_t* t, uint32_t batch_size);
+/* Named scalar properties (the public members pyngp binds, src/python_api.cu:481-566, 645-697):
+ * training_step, loss, rays_per_batch, measured_batch_size, measured_batch_size_before_compaction,
+ * n_params, max_cascade, cone_angle_constant, aabb_scale, seed, random_bg_color, linear_colors,
+ * snap_to_pixel_centers, near_distance, density_grid_decay, render_min_transmittance, loss_type,
+ * rgb_activation, density_activation, color_space, train_network, train_encoding, last_render_samples. */
+int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value);
+int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value);
+/* Device buffers by name: params (fp16), params_fp32, params_inference (fp16), gradients (fp16),
+ * density_grid (float), density_grid_bitfield (uint8), density_grid_mean (float), metadata. */
+int ngpb_testbed_device_ptr(ngpb_testbed_t* t, const char* name, void** ptr, size_t* bytes);
+/* The module (NerfNetwork) owned by the testbed; valid until the next reload / free. */
+ngpb_module_t* ngpb_testbed_network(ngpb_testbed_t* t);
+size_t ngpb_testbed_network_config(const ngpb_testbed_t* t, char* buf, size_t cap);
+/* update_density_grid_nerf(decay, n_uniform, n_nonuniform), src/testbed_nerf.cu:2271-2360. */
+int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_uniform, uint32_t n_nonuniform);
+/* Testbed::render_nerf (src/testbed_nerf.cu:1827-1987) into caller-owned DEVICE buffers: rgba
+ * float4 [h][w] (linear, premultiplied alpha), depth float [h][w] or NULL. Only pixels
+ * [pixel_begin, pixel_end) (row-major) are traced: the unit of tile sharding across GPUs. */
+int ngpb_testbed_render_nerf(ngpb_testbed_t* t, uint32_t width, uint32_t height, const float* camera_3x4, float focal_x, float focal_y,
+	float principal_x, float principal_y, uint32_t spp_index, uint32_t pixel_begin, uint32_t pixel_end, float* rgba, float* depth);
+
 /* ---- self test of the tcgen05 operand views (tc_device.cuh) --------------------------------
  * mode 0: D[128xN] = X[128xK] W[NxK]^T; mode 1: D[128xN] = X[128xK] W[KxN];
  * mode 2: D[64xN] = X[128x64]^T W[128xN]. fp16 row-major inputs, fp32 row-major D (device). */

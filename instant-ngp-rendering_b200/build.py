@@ -21,7 +21,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",
     "--expt-relaxed-constexpr", "--extended-lambda",
-    "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function",
+    "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function,-ffp-contract=off",
     "-Xptxas", "-v" if os.environ.get("NGPB_PTXAS_V") else "-O3",
 ]
 
@@ -54,7 +54,9 @@ def build_cuda(verbose=False):
         obj = os.path.join(BUILD, s[:-3] + ".o")
         objs.append(obj)
         if _newer(obj, [src] + headers):
-            jobs.append([NVCC] + NVCC_FLAGS + ["-c", src, "-o", obj])
+            # NeRF ray set-up / stepping must give the same bits as the host oracle: no FMA contraction
+            extra = ["-fmad=false"] if s.startswith("nerf_") else []
+            jobs.append([NVCC] + NVCC_FLAGS + extra + ["-c", src, "-o", obj])
     if jobs:
         if verbose:
             print(f"[build] compiling {len(jobs)} CUDA translation unit(s) for sm_100a")

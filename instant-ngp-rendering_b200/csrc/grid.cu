@@ -205,11 +205,12 @@ NGPB_D void load_position(const float* __restrict__ positions, uint32_t in_strid
 // Forward: thread per sample, 8/F levels per 16-byte output store.
 template <uint32_t D, uint32_t F, bool VEC_OUT>
 __global__ void __launch_bounds__(256) grid_forward_kernel(
-	const __grid_constant__ GridParams p, const uint32_t n,
+	const __grid_constant__ GridParams p, const uint32_t n_max,
 	const __half* __restrict__ grid, const float* __restrict__ positions, const uint32_t in_stride,
-	__half* __restrict__ out, const uint32_t out_stride, const float max_level, const uint32_t tiled)
+	__half* __restrict__ out, const uint32_t out_stride, const float max_level, const uint32_t tiled, const uint32_t* __restrict__ n_dev)
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t n = n_dev ? min(__ldg(n_dev), n_max) : n_max;
 	constexpr uint32_t C = 8 / F; // levels per 16 B
 	const uint32_t L = p.n_levels;
 
@@ -432,7 +433,7 @@ static bool aligned16(const void* ptr, uint32_t stride_halves) {
 }
 
 void grid_forward(cudaStream_t stream, const GridParams& p, uint32_t n, const __half* grid,
-	const float* positions, uint32_t in_stride, __half* out, uint32_t out_stride, float max_level, bool tiled)
+	const float* positions, uint32_t in_stride, __half* out, uint32_t out_stride, float max_level, bool tiled, const uint32_t* n_dev)
 {
 	if (n == 0) return;
 	const uint32_t blocks = div_round_up(tiled ? next_multiple(n, 128u) : n, 256);
@@ -441,8 +442,8 @@ void grid_forward(cudaStream_t stream, const GridParams& p, uint32_t n, const __
 		throw std::runtime_error{"GridEncoding: tiled output needs a 16-byte aligned buffer and a feature count that is a multiple of 8"};
 	}
 	NGPB_GRID_DISPATCH(p.n_dims, p.n_features_per_level, {
-		if (vec) grid_forward_kernel<D, F, true><<<blocks, 256, 0, stream>>>(p, n, grid, positions, in_stride, out, out_stride, max_level, tiled ? 1u : 0u);
-		else grid_forward_kernel<D, F, false><<<blocks, 256, 0, stream>>>(p, n, grid, positions, in_stride, out, out_stride, max_level, 0u);
+		if (vec) grid_forward_kernel<D, F, true><<<blocks, 256, 0, stream>>>(p, n, grid, positions, in_stride, out, out_stride, max_level, tiled ? 1u : 0u, n_dev);
+		else grid_forward_kernel<D, F, false><<<blocks, 256, 0, stream>>>(p, n, grid, positions, in_stride, out, out_stride, max_level, 0u, n_dev);
 	});
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }

@@ -71,8 +71,9 @@ std::string to_string(InterpolationType t);
 // tiled:     out / dL_dy use the tile layout of mlp.h ([tile][chunk][128][8 halves], out_stride
 //            = padded feature width) instead of AoS rows; rows up to the next multiple of 128
 //            are written (zeros) so that a consumer may read whole tiles.
+// n_dev:     optional device-side count; min(*n_dev, n) samples are encoded.
 void grid_forward(cudaStream_t stream, const GridParams& p, uint32_t n, const __half* grid,
-	const float* positions, uint32_t in_stride, __half* out, uint32_t out_stride, float max_level, bool tiled = false);
+	const float* positions, uint32_t in_stride, __half* out, uint32_t out_stride, float max_level, bool tiled = false, const uint32_t* n_dev = nullptr);
 
 // dL_dy: fp16 AoS with the same layout as `out`. grad: fp16 [entries][F], must be zeroed by
 // the caller when overwrite semantics are wanted (the reference zeroes at grid.h:857-859;

@@ -277,7 +277,7 @@ NGPB_D void store_chain_dw(const TileCtx& c, const Chain& ch, float* __restrict_
 // ---------------------------------------------------------------------------------------------
 template <bool NERF, bool TRAIN, uint32_t TMEM_COLS>
 __global__ void __launch_bounds__(128, TRAIN ? 2 : 4) fused_net_kernel(
-	const __grid_constant__ FusedNet net, const uint32_t n_tiles,
+	const __grid_constant__ FusedNet net, const uint32_t n_tiles_max, const uint32_t* __restrict__ n_dev,
 	const __half* __restrict__ params, const __half* __restrict__ feat,
 	const float* __restrict__ coords, const uint32_t coord_stride,
 	__half* __restrict__ out, const uint32_t out_stride,
@@ -291,6 +291,8 @@ __global__ void __launch_bounds__(128, TRAIN ? 2 : 4) fused_net_kernel(
 
 	const SmemPlan plan = make_plan(net, TRAIN);
 	const uint32_t t = threadIdx.x;
+	uint32_t n_tiles = n_tiles_max;
+	if (n_dev) n_tiles = min(n_tiles_max, (__ldg(n_dev) + kTile - 1) / kTile);
 
 	load_chain_weights(smem + plan.w_a, params + net.a_param_off, net.a_in, net.a_hidden);
 	if (NERF) load_chain_weights(smem + plan.w_b, params + net.b_param_off, net.b_in, net.b_hidden);
@@ -499,11 +501,11 @@ void fused_inference(cudaStream_t stream, const FusedInferenceArgs& a) {
 	if (a.net.nerf) {
 		auto k = fused_net_kernel<true, false, 64>;
 		set_smem(k, plan.total);
-		k<<<grid, 128, plan.total, stream>>>(a.net, n_tiles, a.params, a.feat, a.coords, a.coord_stride, a.out, a.out_stride, nullptr, 0, nullptr, nullptr);
+		k<<<grid, 128, plan.total, stream>>>(a.net, n_tiles, a.n_dev, a.params, a.feat, a.coords, a.coord_stride, a.out, a.out_stride, nullptr, 0, nullptr, nullptr);
 	} else {
 		auto k = fused_net_kernel<false, false, 64>;
 		set_smem(k, plan.total);
-		k<<<grid, 128, plan.total, stream>>>(a.net, n_tiles, a.params, a.feat, a.coords, a.coord_stride, a.out, a.out_stride, nullptr, 0, nullptr, nullptr);
+		k<<<grid, 128, plan.total, stream>>>(a.net, n_tiles, a.n_dev, a.params, a.feat, a.coords, a.coord_stride, a.out, a.out_stride, nullptr, 0, nullptr, nullptr);
 	}
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }
@@ -530,7 +532,7 @@ void fused_train(cudaStream_t stream, const FusedTrainArgs& a) {
 	do { \
 		auto k = fused_net_kernel<NERF_, true, COLS_>; \
 		set_smem(k, plan.total); \
-		k<<<grid, 128, plan.total, stream>>>(a.net, n_tiles, a.params, a.feat, a.coords, a.coord_stride, nullptr, 0, a.dL_dout, a.dy_stride, a.dfeat, a.dw_partials); \
+		k<<<grid, 128, plan.total, stream>>>(a.net, n_tiles, nullptr, a.params, a.feat, a.coords, a.coord_stride, nullptr, 0, a.dL_dout, a.dy_stride, a.dfeat, a.dw_partials); \
 	} while (0)
 	if (a.net.nerf) { if (big) NGPB_LAUNCH_TRAIN(true, 512); else NGPB_LAUNCH_TRAIN(true, 256); }
 	else { if (big) NGPB_LAUNCH_TRAIN(false, 512); else NGPB_LAUNCH_TRAIN(false, 256); }

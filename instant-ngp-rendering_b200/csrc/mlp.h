@@ -53,6 +53,7 @@ inline size_t tiled_bytes(uint32_t n, uint32_t width) { return (size_t)div_round
 struct FusedInferenceArgs {
 	FusedNet net;
 	uint32_t n;                 // samples, multiple of 128
+	const uint32_t* n_dev;      // optional device-side sample count: min(*n_dev, n) samples are processed
 	const __half* params;       // flat parameter buffer (chain offsets inside `net`)
 	const __half* feat;         // tiled chain-A input, a_in columns
 	const float* coords;        // nerf: rows with the view direction at [dir_offset, dir_offset+3)

@@ -81,6 +81,9 @@ public:
 // tcnn random.h:39-73, same element -> stream-position mapping.
 void random_uniform(cudaStream_t stream, Pcg32& rng, size_t n, float* out, float lower, float upper);
 
+// params_fp16[i] = (half)params_fp32[i] (tcnn trainer.h:82-85)
+void cast_fp32_to_fp16(cudaStream_t stream, size_t n, const float* src, __half* dst);
+
 // Factories (tcnn/src/encoding.cu:132, tcnn/src/network.cu:98, tcnn/src/cpp_api.cu:140-165).
 Module* create_encoding_module(uint32_t n_input_dims, const Json& encoding);
 Module* create_network_with_input_encoding_module(uint32_t n_input_dims, uint32_t n_output_dims, const Json& encoding, const Json& network);

@@ -1,0 +1,440 @@
+// Device-side NeRF math shared by the training, occupancy-grid and render kernels.
+//
+// Restates (as arithmetic, not as code) the helpers the reference keeps in
+//   include/neural-graphics-primitives/nerf_device.cuh   (stepping, cascades, activations, losses)
+//   include/neural-graphics-primitives/common_device.cuh (lens, uv_to_ray, read_rgba, sRGB)
+//   include/neural-graphics-primitives/bounding_box.cuh  (ray/box intersection)
+//   tcnn common_device.h:759-785                         (Morton codes)
+//
+// Determinism contract: every function that decides WHERE a sample lies (ray set-up, box
+// clipping, stepping, mip selection, bitfield lookup) is written with IEEE add/mul/div/sqrt
+// only, the files that include this header are compiled with -fmad=false, and the two
+// transcendentals the exponential stepping needs (log, exp) are the fixed polynomial
+// implementations below instead of libm / fast-math intrinsics. The CPU oracle restates the
+// same arithmetic, so sample positions and per-ray sample counts agree bit for bit between
+// the B200 and the host (the reference itself is built with --use_fast_math, CMakeLists.txt:82,
+// so its own last bits are not reproducible across GPUs either).
+#pragma once
+
+#include "common.cuh"
+
+#include <cfloat>
+
+namespace ngpb {
+
+// ---- constants (nerf_device.cuh:20-40, common_device.cuh:32) --------------------------------
+constexpr uint32_t kNerfGridSize = 128;
+constexpr uint32_t kNerfGridCells = kNerfGridSize * kNerfGridSize * kNerfGridSize;
+constexpr uint32_t kNerfSteps = 1024;
+constexpr uint32_t kNerfCascades = 8;
+constexpr float kSqrt3 = 1.73205080757f;
+constexpr float kMinConeStepsize = kSqrt3 / kNerfSteps;
+constexpr float kMaxConeStepsize = kMinConeStepsize * (1 << (kNerfCascades - 1)) * kNerfSteps / kNerfGridSize;
+constexpr uint32_t kMaxRandomSamplesPerRay = 16;
+constexpr float kNerfMinOpticalThickness = 0.01f;
+constexpr float kMaxDepth = 16384.0f;
+
+// ---- small vector type ----------------------------------------------------------------------
+struct V3 {
+	float x, y, z;
+};
+NGPB_HD V3 v3(float x, float y, float z) { return V3{x, y, z}; }
+NGPB_HD V3 v3(float s) { return V3{s, s, s}; }
+NGPB_HD V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+NGPB_HD V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+NGPB_HD V3 operator*(V3 a, V3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
+NGPB_HD V3 operator/(V3 a, V3 b) { return {a.x / b.x, a.y / b.y, a.z / b.z}; }
+NGPB_HD V3 operator*(float s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
+NGPB_HD V3 operator*(V3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+NGPB_HD V3 operator/(V3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+NGPB_HD V3 operator+(V3 a, float s) { return {a.x + s, a.y + s, a.z + s}; }
+NGPB_HD V3 operator-(V3 a, float s) { return {a.x - s, a.y - s, a.z - s}; }
+NGPB_HD V3& operator+=(V3& a, V3 b) { a = a + b; return a; }
+NGPB_HD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+NGPB_HD float length(V3 a) { return sqrtf(dot(a, a)); }
+NGPB_HD V3 normalize(V3 a) { return a / length(a); }
+NGPB_HD float distance(V3 a, V3 b) { return length(a - b); }
+NGPB_HD float mean(V3 a) { return (a.x + a.y + a.z) / 3.0f; }
+
+// 4x3 camera matrix, column-major like tcnn's mat4x3: c[0..2] rotation columns, c[3] origin.
+struct Mat4x3 {
+	V3 c[4];
+};
+NGPB_HD V3 mul3(const Mat4x3& m, V3 v) { return m.c[0] * v.x + m.c[1] * v.y + m.c[2] * v.z; }
+
+struct Ray3 {
+	V3 o, d;
+};
+
+struct Aabb {
+	V3 min, max;
+};
+NGPB_HD bool aabb_contains(const Aabb& b, V3 p) {
+	return p.x >= b.min.x && p.x <= b.max.x && p.y >= b.min.y && p.y <= b.max.y && p.z >= b.min.z && p.z <= b.max.z;
+}
+NGPB_HD V3 aabb_diag(const Aabb& b) { return b.max - b.min; }
+// bounding_box.cuh:172-219
+NGPB_HD void aabb_ray_intersect(const Aabb& b, V3 pos, V3 dir, float& out_tmin, float& out_tmax) {
+	float tmin = (b.min.x - pos.x) / dir.x, tmax = (b.max.x - pos.x) / dir.x;
+	if (tmin > tmax) { float t = tmin; tmin = tmax; tmax = t; }
+	float tymin = (b.min.y - pos.y) / dir.y, tymax = (b.max.y - pos.y) / dir.y;
+	if (tymin > tymax) { float t = tymin; tymin = tymax; tymax = t; }
+	if (tmin > tymax || tymin > tmax) { out_tmin = out_tmax = FLT_MAX; return; }
+	if (tymin > tmin) tmin = tymin;
+	if (tymax < tmax) tmax = tymax;
+	float tzmin = (b.min.z - pos.z) / dir.z, tzmax = (b.max.z - pos.z) / dir.z;
+	if (tzmin > tzmax) { float t = tzmin; tzmin = tzmax; tzmax = t; }
+	if (tmin > tzmax || tzmin > tmax) { out_tmin = out_tmax = FLT_MAX; return; }
+	if (tzmin > tmin) tmin = tzmin;
+	if (tzmax < tmax) tmax = tzmax;
+	out_tmin = tmin;
+	out_tmax = tmax;
+}
+
+// ---- Morton codes (tcnn common_device.h:759-785) ----------------------------------------------
+NGPB_HD uint32_t expand_bits(uint32_t v) {
+	v = (v * 0x00010001u) & 0xFF0000FFu;
+	v = (v * 0x00000101u) & 0x0F00F00Fu;
+	v = (v * 0x00000011u) & 0xC30C30C3u;
+	v = (v * 0x00000005u) & 0x49249249u;
+	return v;
+}
+NGPB_HD uint32_t morton3d(uint32_t x, uint32_t y, uint32_t z) { return expand_bits(x) | (expand_bits(y) << 1) | (expand_bits(z) << 2); }
+NGPB_HD uint32_t morton3d_invert(uint32_t x) {
+	x = x & 0x49249249;
+	x = (x | (x >> 2)) & 0xc30c30c3;
+	x = (x | (x >> 4)) & 0x0f00f00f;
+	x = (x | (x >> 8)) & 0xff0000ff;
+	x = (x | (x >> 16)) & 0x0000ffff;
+	return x;
+}
+
+// ---- deterministic log / exp -------------------------------------------------------------------
+// Single-precision Cephes algorithms (S. Moshier, cephes/single/logf.c, expf.c: range reduction by
+// frexp / round-to-nearest multiple of ln 2 split in two constants, degree-8 / degree-5
+// polynomials). Plain IEEE mul/add in a fixed order: the same bits on the host and on the device.
+NGPB_HD float det_logf(float xx) {
+	int e;
+	float x = frexpf(xx, &e);
+	if (x < 0.707106781186547524f) { e -= 1; x = x + x - 1.0f; } else { x = x - 1.0f; }
+	float z = x * x;
+	float y = 7.0376836292e-2f;
+	y = y * x - 1.1514610310e-1f;
+	y = y * x + 1.1676998740e-1f;
+	y = y * x - 1.2420140846e-1f;
+	y = y * x + 1.4249322787e-1f;
+	y = y * x - 1.6668057665e-1f;
+	y = y * x + 2.0000714765e-1f;
+	y = y * x - 2.4999993993e-1f;
+	y = y * x + 3.3333331174e-1f;
+	y = y * x * z;
+	const float fe = (float)e;
+	if (e) y += -2.12194440e-4f * fe;
+	y += -0.5f * z;
+	z = x + y;
+	if (e) z += 0.693359375f * fe;
+	return z;
+}
+NGPB_HD float det_expf(float x) {
+	if (x > 88.0f) x = 88.0f;
+	if (x < -87.0f) x = -87.0f;
+	float z = floorf(1.44269504088896341f * x + 0.5f);
+	x -= z * 0.693359375f;
+	x -= z * -2.12194440e-4f;
+	const int n = (int)z;
+	z = x * x;
+	float p = 1.9875691500e-4f;
+	p = p * x + 1.3981999507e-3f;
+	p = p * x + 8.3334519073e-3f;
+	p = p * x + 4.1665795894e-2f;
+	p = p * x + 1.6666665459e-1f;
+	p = p * x + 5.0000001201e-1f;
+	z = p * z + x + 1.0f;
+	return scalbnf(z, n);
+}
+
+// ---- exponential stepping (nerf_device.cuh:372-437) ------------------------------------------
+// The reference recomputes log(1+c), a, b, exp(a log(1+c)), exp(b log(1+c)) on every call; they
+// only depend on the cone angle, so they are tabulated once per launch.
+struct Stepping {
+	float cone_angle;
+	float log1p_c, a, b, at, bt;
+};
+NGPB_HD Stepping make_stepping(float cone_angle) {
+	Stepping s{};
+	s.cone_angle = cone_angle;
+	if (cone_angle <= 1e-5f) return s;
+	s.log1p_c = det_logf(1.0f + cone_angle);
+	s.a = (det_logf(kMinConeStepsize) - det_logf(s.log1p_c)) / s.log1p_c;
+	s.b = (det_logf(kMaxConeStepsize) - det_logf(s.log1p_c)) / s.log1p_c;
+	s.at = det_expf(s.a * s.log1p_c);
+	s.bt = det_expf(s.b * s.log1p_c);
+	return s;
+}
+NGPB_HD float to_stepping_space(float t, const Stepping& s) {
+	if (s.cone_angle <= 1e-5f) return t / kMinConeStepsize;
+	if (t <= s.at) return (t - s.at) / kMinConeStepsize + s.a;
+	if (t <= s.bt) return det_logf(t) / s.log1p_c;
+	return (t - s.bt) / kMaxConeStepsize + s.b;
+}
+NGPB_HD float from_stepping_space(float n, const Stepping& s) {
+	if (s.cone_angle <= 1e-5f) return n * kMinConeStepsize;
+	if (n <= s.a) return (n - s.a) * kMinConeStepsize + s.at;
+	if (n <= s.b) return det_expf(n * s.log1p_c);
+	return (n - s.b) * kMaxConeStepsize + s.bt;
+}
+NGPB_HD float advance_n_steps(float t, const Stepping& s, float n) { return from_stepping_space(to_stepping_space(t, s) + n, s); }
+NGPB_HD float calc_dt(float t, const Stepping& s) { return advance_n_steps(t, s, 1.0f) - t; }
+
+NGPB_HD float sign_f(float x) { return copysignf(1.0f, x); }
+// nerf_device.cuh:362-370
+NGPB_HD float distance_to_next_voxel(V3 pos, V3 dir, V3 idir, float res) {
+	const V3 p = res * (pos - 0.5f);
+	const float tx = (floorf(p.x + 0.5f + 0.5f * sign_f(dir.x)) - p.x) * idir.x;
+	const float ty = (floorf(p.y + 0.5f + 0.5f * sign_f(dir.y)) - p.y) * idir.y;
+	const float tz = (floorf(p.z + 0.5f + 0.5f * sign_f(dir.z)) - p.z) * idir.z;
+	const float t = fminf(fminf(tx, ty), tz);
+	return fmaxf(t / res, 0.0f);
+}
+// nerf_device.cuh:426-437
+NGPB_HD float advance_to_next_voxel(float t, const Stepping& s, V3 pos, V3 dir, V3 idir, uint32_t mip) {
+	const float res = scalbnf((float)kNerfGridSize, -(int)mip);
+	float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
+	t = to_stepping_space(t, s);
+	t_target = to_stepping_space(t_target, s);
+	return from_stepping_space(t + ceilf(fmaxf(t_target - t, 0.5f)), s);
+}
+
+// ---- cascaded occupancy grid (nerf_device.cuh:316-340, 439-458) -------------------------------
+NGPB_HD int clamp_i(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+NGPB_HD uint32_t mip_from_pos(V3 pos, uint32_t max_cascade = kNerfCascades - 1) {
+	int exponent;
+	const float maxval = fmaxf(fmaxf(fabsf(pos.x - 0.5f), fabsf(pos.y - 0.5f)), fabsf(pos.z - 0.5f));
+	frexpf(maxval, &exponent);
+	return (uint32_t)clamp_i(exponent + 1, 0, (int)max_cascade);
+}
+NGPB_HD uint32_t mip_from_dt(float dt, V3 pos, uint32_t max_cascade = kNerfCascades - 1) {
+	const uint32_t mip = mip_from_pos(pos, max_cascade);
+	dt *= 2 * kNerfGridSize;
+	if (dt < 1.0f) return mip;
+	int exponent;
+	frexpf(dt, &exponent);
+	return (uint32_t)clamp_i((int)mip, exponent, (int)max_cascade);
+}
+NGPB_HD uint32_t cascaded_grid_idx_at(V3 pos, uint32_t mip) {
+	const float mip_scale = scalbnf(1.0f, -(int)mip);
+	pos = pos - 0.5f;
+	pos = pos * mip_scale;
+	pos = pos + 0.5f;
+	const int ix = (int)(pos.x * (float)kNerfGridSize), iy = (int)(pos.y * (float)kNerfGridSize), iz = (int)(pos.z * (float)kNerfGridSize);
+	if (ix < 0 || ix >= (int)kNerfGridSize || iy < 0 || iy >= (int)kNerfGridSize || iz < 0 || iz >= (int)kNerfGridSize) return 0xFFFFFFFFu;
+	return morton3d((uint32_t)ix, (uint32_t)iy, (uint32_t)iz);
+}
+NGPB_HD uint32_t grid_mip_offset(uint32_t mip) { return kNerfGridCells * mip; }
+NGPB_HD bool density_grid_occupied_at(V3 pos, const uint8_t* __restrict__ bitfield, uint32_t mip) {
+	const uint32_t idx = cascaded_grid_idx_at(pos, mip);
+	if (idx == 0xFFFFFFFFu) return false;
+	return (bitfield[idx / 8 + grid_mip_offset(mip) / 8] & (1u << (idx % 8))) != 0;
+}
+
+// ---- warps (nerf_device.cuh:265-314) -----------------------------------------------------------
+NGPB_HD V3 warp_position(V3 pos, const Aabb& aabb) { return (pos - aabb.min) / aabb_diag(aabb); }
+NGPB_HD V3 unwarp_position(V3 pos, const Aabb& aabb) { return aabb.min + pos * aabb_diag(aabb); }
+NGPB_HD V3 warp_direction(V3 dir) { return (dir + 1.0f) * 0.5f; }
+NGPB_HD float warp_dt(float dt) {
+	const float max_stepsize = kMinConeStepsize * (1 << (kNerfCascades - 1));
+	return (dt - kMinConeStepsize) / (max_stepsize - kMinConeStepsize);
+}
+NGPB_HD float unwarp_dt(float dt) {
+	const float max_stepsize = kMinConeStepsize * (1 << (kNerfCascades - 1));
+	return dt * (max_stepsize - kMinConeStepsize) + kMinConeStepsize;
+}
+
+// ---- activations (nerf_device.cuh:203-263) -----------------------------------------------------
+enum NerfActivation : int { kActNone = 0, kActReLU = 1, kActLogistic = 2, kActExponential = 3 };
+NGPB_HD float logistic_f(float x) { return 1.0f / (1.0f + expf(-x)); }
+NGPB_HD float clamp_f(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
+NGPB_HD float network_to_rgb(float val, int act) {
+	switch (act) {
+		case kActReLU: return val > 0.0f ? val : 0.0f;
+		case kActLogistic: return logistic_f(val);
+		case kActExponential: return expf(clamp_f(val, -10.0f, 10.0f));
+		default: return val;
+	}
+}
+NGPB_HD float network_to_rgb_derivative(float val, int act) {
+	switch (act) {
+		case kActReLU: return val > 0.0f ? 1.0f : 0.0f;
+		case kActLogistic: { const float d = logistic_f(val); return d * (1 - d); }
+		case kActExponential: return expf(clamp_f(val, -10.0f, 10.0f));
+		default: return 1.0f;
+	}
+}
+NGPB_HD float network_to_density(float val, int act) {
+	switch (act) {
+		case kActReLU: return val > 0.0f ? val : 0.0f;
+		case kActLogistic: return logistic_f(val);
+		case kActExponential: return expf(val);
+		default: return val;
+	}
+}
+NGPB_HD float network_to_density_derivative(float val, int act) {
+	switch (act) {
+		case kActReLU: return val > 0.0f ? 1.0f : 0.0f;
+		case kActLogistic: { const float d = logistic_f(val); return d * (1 - d); }
+		case kActExponential: return expf(clamp_f(val, -15.0f, 15.0f));
+		default: return 1.0f;
+	}
+}
+
+// ---- losses (nerf_device.cuh:74-143, 600-615) ---------------------------------------------------
+enum NerfLoss : int { kLossL2 = 0, kLossL1 = 1, kLossMape = 2, kLossSmape = 3, kLossHuber = 4, kLossLogL1 = 5, kLossRelativeL2 = 6 };
+struct LossAndGradient {
+	V3 loss, gradient;
+};
+NGPB_HD void loss1(float target, float pred, int type, float& loss, float& grad) {
+	const float d = pred - target;
+	switch (type) {
+		case kLossRelativeL2: { const float den = pred * pred + 1e-2f; loss = d * d / den; grad = 2.0f * d / den; } break;
+		case kLossL1: loss = fabsf(d); grad = copysignf(1.0f, d); break;
+		case kLossMape: { const float den = fabsf(pred) + 1e-2f; loss = fabsf(d) / den; grad = copysignf(1.0f / den, d); } break;
+		case kLossSmape: { const float den = 0.5f * (fabsf(pred) + fabsf(target)) + 1e-2f; loss = fabsf(d) / den; grad = copysignf(1.0f / den, d); } break;
+		case kLossHuber: {
+			// huber_loss(alpha = 0.1) / 5 (nerf_device.cuh:607-610)
+			const float alpha = 0.1f, ad = fabsf(d);
+			const float sq = 0.5f / alpha * d * d;
+			loss = (ad > alpha ? (ad - 0.5f * alpha) : sq) / 5.0f;
+			grad = (ad > alpha ? (d > 0 ? 1.0f : -1.0f) : (d / alpha)) / 5.0f;
+		} break;
+		case kLossLogL1: { const float div = fabsf(d) + 1.0f; loss = logf(div); grad = copysignf(1.0f / div, d); } break;
+		default: loss = d * d; grad = 2.0f * d; break;
+	}
+}
+NGPB_HD LossAndGradient loss_and_gradient(V3 target, V3 pred, int type) {
+	LossAndGradient lg;
+	loss1(target.x, pred.x, type, lg.loss.x, lg.gradient.x);
+	loss1(target.y, pred.y, type, lg.loss.y, lg.gradient.y);
+	loss1(target.z, pred.z, type, lg.loss.z, lg.gradient.z);
+	return lg;
+}
+
+// ---- colour (common_device.cuh:34-80) -----------------------------------------------------------
+NGPB_HD float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : powf((s + 0.055f) / 1.055f, 2.4f); }
+NGPB_HD float linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
+NGPB_HD V3 srgb_to_linear(V3 c) { return {srgb_to_linear(c.x), srgb_to_linear(c.y), srgb_to_linear(c.z)}; }
+NGPB_HD V3 linear_to_srgb(V3 c) { return {linear_to_srgb(c.x), linear_to_srgb(c.y), linear_to_srgb(c.z)}; }
+
+// ---- training images (nerf_device.cuh:45-61, common_device.cuh:730-806) --------------------------
+enum ImageDataType : int { kImageNone = 0, kImageByte = 1, kImageHalf = 2, kImageFloat = 3 };
+enum LensMode : int { kLensPerspective = 0, kLensOpenCV = 1, kLensFTheta = 2, kLensLatLong = 3, kLensOpenCVFisheye = 4, kLensEquirectangular = 5 };
+enum ColorSpace : int { kColorLinear = 0, kColorSRGB = 1 };
+
+// POD mirrored by the C ABI (ngpb_nerf_image_t) and by TrainingImageMetadata in the reference.
+struct ImageMeta {
+	const void* pixels;
+	int image_data_type;
+	int lens_mode;
+	float lens_params[7];
+	int res_x, res_y;
+	float principal_x, principal_y;
+	float focal_x, focal_y;
+	Mat4x3 xform; // TrainingXForm::start; rolling shutter / motion blur are not supported
+};
+
+struct Rgba {
+	float r, g, b, a;
+};
+NGPB_D Rgba read_rgba(int px, int py, int res_x, const void* pixels, int type) {
+	const size_t idx = (size_t)px + (size_t)py * res_x;
+	switch (type) {
+		case kImageByte: {
+			const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(pixels) + idx);
+			if (v == 0x00FF00FFu) return {-1.0f, -1.0f, -1.0f, -1.0f};
+			const float alpha = (float)(v >> 24) * (1.0f / 255.0f);
+			return {srgb_to_linear((float)(v & 0xFF) * (1.0f / 255.0f)) * alpha, srgb_to_linear((float)((v >> 8) & 0xFF) * (1.0f / 255.0f)) * alpha,
+				srgb_to_linear((float)((v >> 16) & 0xFF) * (1.0f / 255.0f)) * alpha, alpha};
+		}
+		case kImageHalf: {
+			const uint2 v = __ldg(reinterpret_cast<const uint2*>(pixels) + idx);
+			const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&v.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+			return {a.x, a.y, b.x, b.y};
+		}
+		case kImageFloat: {
+			const float4 v = __ldg(reinterpret_cast<const float4*>(pixels) + idx);
+			return {v.x, v.y, v.z, v.w};
+		}
+		default: return {5.0f, 0.0f, 0.0f, 1.0f};
+	}
+}
+NGPB_D Rgba read_rgba_uv(float u, float v, int res_x, int res_y, const void* pixels, int type) {
+	const int px = clamp_i((int)(u * (float)res_x), 0, res_x - 1), py = clamp_i((int)(v * (float)res_y), 0, res_y - 1);
+	return read_rgba(px, py, res_x, pixels, type);
+}
+
+// ---- lens (common_device.cuh:248-338, 393-460) ----------------------------------------------------
+NGPB_HD void opencv_lens_distortion_delta(const float* p, float u, float v, float* du, float* dv) {
+	const float k1 = p[0], k2 = p[1], p1 = p[2], p2 = p[3];
+	const float u2 = u * u, uv = u * v, v2 = v * v, r2 = u2 + v2;
+	const float radial = k1 * r2 + k2 * r2 * r2;
+	*du = u * radial + 2.0f * p1 * uv + p2 * (r2 + 2.0f * u2);
+	*dv = v * radial + 2.0f * p2 * uv + p1 * (r2 + 2.0f * v2);
+}
+// Newton iteration with central differences, 100 iterations max (common_device.cuh:288-329).
+NGPB_HD void iterative_opencv_lens_undistortion(const float* params, float* u, float* v) {
+	const float kMaxStepNorm = 1e-10f, kRelStepSize = 1e-6f;
+	const float x0 = *u, y0 = *v;
+	float x = x0, y = y0;
+	for (uint32_t i = 0; i < 100; ++i) {
+		const float step0 = fmaxf(FLT_EPSILON, fabsf(kRelStepSize * x));
+		const float step1 = fmaxf(FLT_EPSILON, fabsf(kRelStepSize * y));
+		float dx0, dx1, b00, b01, f00, f01, b10, b11, f10, f11;
+		opencv_lens_distortion_delta(params, x, y, &dx0, &dx1);
+		opencv_lens_distortion_delta(params, x - step0, y, &b00, &b01);
+		opencv_lens_distortion_delta(params, x + step0, y, &f00, &f01);
+		opencv_lens_distortion_delta(params, x, y - step1, &b10, &b11);
+		opencv_lens_distortion_delta(params, x, y + step1, &f10, &f11);
+		// J[col][row], as tcnn mat2
+		const float j00 = 1 + (f00 - b00) / (2 * step0);
+		const float j10 = (f10 - b10) / (2 * step1);
+		const float j01 = (f01 - b01) / (2 * step0);
+		const float j11 = 1 + (f11 - b11) / (2 * step1);
+		const float rx = x + dx0 - x0, ry = y + dx1 - y0;
+		// inverse(J) * r with the adjugate / determinant (tcnn vec.h inverse(mat2))
+		const float det = j00 * j11 - j10 * j01;
+		const float sx = (j11 * rx - j10 * ry) / det;
+		const float sy = (-j01 * rx + j00 * ry) / det;
+		x -= sx;
+		y -= sy;
+		if (sx * sx + sy * sy < kMaxStepNorm) break;
+	}
+	*u = x;
+	*v = y;
+}
+
+// uv_to_ray for the training / render cameras: perspective and OpenCV lenses, no foveation, no
+// aperture, no parallax (all zero / identity in the headless paths).
+NGPB_HD Ray3 uv_to_ray(float u, float v, int res_x, int res_y, float focal_x, float focal_y, const Mat4x3& cam, float screen_cx, float screen_cy,
+	int lens_mode, const float* lens_params, float near_distance)
+{
+	V3 dir = {(u - screen_cx) * (float)res_x / focal_x, (v - screen_cy) * (float)res_y / focal_y, 1.0f};
+	if (lens_mode == kLensOpenCV) iterative_opencv_lens_undistortion(lens_params, &dir.x, &dir.y);
+	dir = mul3(cam, dir);
+	V3 origin = cam.c[3];
+	origin = origin + dir * near_distance;
+	return {origin, dir};
+}
+
+// ---- per-ray random choices (nerf_device.cuh:552-598, src/testbed_nerf.cu:712-727) ------------------
+NGPB_HD uint32_t image_idx(uint32_t base_idx, uint32_t n_rays, uint32_t n_training_images) {
+	return (uint32_t)((((uint64_t)base_idx * n_training_images) & 0xFFFFFFFFu) / n_rays) % n_training_images;
+}
+NGPB_HD void random_image_pos_training(Pcg32& rng, int res_x, int res_y, bool snap_to_pixel_centers, float& u, float& v) {
+	u = rng.next_float();
+	v = rng.next_float();
+	if (snap_to_pixel_centers) {
+		u = ((float)clamp_i((int)(u * (float)res_x), 0, res_x - 1) + 0.5f) / (float)res_x;
+		v = ((float)clamp_i((int)(v * (float)res_y), 0, res_y - 1) + 0.5f) / (float)res_y;
+	}
+}
+
+} // namespace ngpb

@@ -281,6 +281,18 @@ void NerfNetworkModule::inference_strided(cudaStream_t stream, uint32_t n, const
 	fused_inference(stream, a);
 }
 
+void NerfNetworkModule::inference_counted(cudaStream_t stream, uint32_t max_n, const uint32_t* n_dev, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params) {
+	if (max_n == 0) return;
+	if (max_n % kTile != 0) throw std::runtime_error{"ngp-b200 NerfNetwork: batch size must be a multiple of 128"};
+	m_scratch_feat.reserve(tiled_bytes(max_n, m_pos_width), stream);
+	grid_forward(stream, m_grid.p, max_n, params + pos_encoding_param_offset(), input, in_stride, m_scratch_feat.as<__half>(), m_pos_width, 1.0f, true, n_dev);
+	FusedInferenceArgs a{};
+	a.net = m_net; a.n = max_n; a.n_dev = n_dev; a.params = params; a.feat = m_scratch_feat.as<__half>();
+	a.coords = input; a.coord_stride = in_stride;
+	a.out = output; a.out_stride = out_stride;
+	fused_inference(stream, a);
+}
+
 void NerfNetworkModule::density(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params) {
 	if (n == 0) return;
 	if (n % kTile != 0) throw std::runtime_error{"ngp-b200 NerfNetwork: batch size must be a multiple of 128"};

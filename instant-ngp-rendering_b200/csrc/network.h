@@ -73,6 +73,8 @@ public:
 	// Strided variants used by the NeRF driver: rows of `in_stride` floats, outputs of `out_stride`
 	// halves per sample (16 = tcnn layout, 4 = packed rgb sigma).
 	void inference_strided(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params);
+	// As inference_strided over min(*n_dev, max_n) samples, *n_dev read on the device.
+	void inference_counted(cudaStream_t stream, uint32_t max_n, const uint32_t* n_dev, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params);
 	void backward_strided(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, const __half* dL_doutput, uint32_t dy_stride,
 		__half* dL_dparams, const __half* params);
 	// NerfNetwork::density (nerf_network.h:270-279): out[i*out_stride] = density-MLP output 0 when

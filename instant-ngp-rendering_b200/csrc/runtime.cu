@@ -46,4 +46,14 @@ void random_uniform(cudaStream_t stream, Pcg32& rng, size_t n, float* out, float
 	rng.advance((int64_t)n);
 }
 
+__global__ void cast_fp32_to_fp16_kernel(size_t n, const float* __restrict__ src, __half* __restrict__ dst) {
+	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) dst[i] = __float2half(src[i]);
+}
+void cast_fp32_to_fp16(cudaStream_t stream, size_t n, const float* src, __half* dst) {
+	if (!n) return;
+	cast_fp32_to_fp16_kernel<<<(uint32_t)((n + 255) / 256), 256, 0, stream>>>(n, src, dst);
+	NGPB_CUDA_CHECK(cudaGetLastError());
+}
+
 } // namespace ngpb

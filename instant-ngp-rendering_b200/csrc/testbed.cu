@@ -1,0 +1,179 @@
+// Testbed host logic: dataset set-up, network construction, the training step schedule.
+#include "testbed.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace ngpb {
+
+static int loss_type_from_string(const std::string& s) {
+	// string_to_loss_type, src/testbed.cu (ELossType)
+	if (equals_case_insensitive(s, "L2")) return kLossL2;
+	if (equals_case_insensitive(s, "RelativeL2")) return kLossRelativeL2;
+	if (equals_case_insensitive(s, "L1")) return kLossL1;
+	if (equals_case_insensitive(s, "Mape")) return kLossMape;
+	if (equals_case_insensitive(s, "Smape")) return kLossSmape;
+	if (equals_case_insensitive(s, "Huber") || equals_case_insensitive(s, "SmoothL1")) return kLossHuber;
+	if (equals_case_insensitive(s, "LogL1")) return kLossLogL1;
+	throw std::runtime_error{"Unknown loss type."};
+}
+
+Testbed::Testbed() {
+	NGPB_CUDA_CHECK(cudaStreamCreateWithFlags(&m_stream, cudaStreamNonBlocking));
+	NGPB_CUDA_CHECK(cudaMallocHost(&m_counters_host, sizeof(NerfStepCounters)));
+	NGPB_CUDA_CHECK(cudaMallocHost(&m_loss_host, sizeof(float)));
+	m_rng = Pcg32{seed};
+}
+
+Testbed::~Testbed() {
+	if (m_stream) cudaStreamSynchronize(m_stream);
+	// stream-ordered buffers must go before the stream
+	m_images.clear();
+	for (DeviceBuffer* b : {&m_params_fp32, &m_params, &m_gradients, &m_metadata_gpu, &m_density_grid, &m_density_grid_tmp, &m_density_bitfield,
+			&m_density_mean, &m_grid_positions, &m_grid_indices, &m_grid_mlp_out, &m_counters, &m_ray_indices, &m_rays, &m_numsteps, &m_coords,
+			&m_rgbsigma, &m_coords_compacted, &m_dloss, &m_loss, &m_render_scratch}) b->release();
+	m_network.reset();
+	m_optimizer.reset();
+	if (m_stream) { cudaStreamSynchronize(m_stream); cudaStreamDestroy(m_stream); }
+	if (m_counters_host) cudaFreeHost(m_counters_host);
+	if (m_loss_host) cudaFreeHost(m_loss_host);
+}
+
+// ---------------------------------------------------------------------------------------------
+void Testbed::create_empty_nerf_dataset(uint32_t n_images, int aabb_scale_, bool is_hdr) {
+	if (aabb_scale_ < 1 || (aabb_scale_ & (aabb_scale_ - 1)) != 0 || aabb_scale_ > 128) throw std::runtime_error{"aabb_scale must be a power of two in [1, 128]"};
+	m_images.clear();
+	m_images.resize(n_images);
+	aabb_scale = aabb_scale_;
+	m_is_hdr = is_hdr;
+	// load_nerf_post (src/testbed_nerf.cu:2151-2238)
+	rgb_activation = is_hdr ? kActExponential : kActLogistic;
+	const float half = 0.5f * (float)std::min(1 << (kNerfCascades - 1), aabb_scale);
+	m_aabb = {{0.5f - half, 0.5f - half, 0.5f - half}, {0.5f + half, 0.5f + half, 0.5f + half}};
+	m_max_cascade = 0;
+	while ((1 << m_max_cascade) < aabb_scale) ++m_max_cascade;
+	m_cone_angle_constant = aabb_scale <= 1 ? 0.0f : (1.0f / 256.0f);
+	m_metadata_dirty = true;
+}
+
+static size_t texel_bytes(int type) {
+	switch (type) {
+		case kImageByte: return 4;
+		case kImageHalf: return 8;
+		case kImageFloat: return 16;
+		default: throw std::runtime_error{"Invalid image data type."};
+	}
+}
+
+void Testbed::set_nerf_image(uint32_t idx, const void* pixels, int image_data_type, int width, int height) {
+	if (idx >= m_images.size()) throw std::runtime_error{"Invalid frame index"};
+	NerfImage& im = m_images[idx];
+	const size_t bytes = (size_t)width * height * texel_bytes(image_data_type);
+	im.pixels.alloc(bytes, m_stream);
+	NGPB_CUDA_CHECK(cudaMemcpyAsync(im.pixels.ptr, pixels, bytes, cudaMemcpyDefault, m_stream));
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	im.meta.pixels = im.pixels.ptr;
+	im.meta.image_data_type = image_data_type;
+	im.meta.res_x = width;
+	im.meta.res_y = height;
+	m_metadata_dirty = true;
+}
+
+void Testbed::set_nerf_camera(uint32_t idx, const float* x, float focal_x, float focal_y, float principal_x, float principal_y, int lens_mode, const float* lens_params) {
+	if (idx >= m_images.size()) throw std::runtime_error{"Invalid frame index"};
+	if (lens_mode != kLensPerspective && lens_mode != kLensOpenCV) throw std::runtime_error{"ngp-b200: lens mode must be Perspective or OpenCV"};
+	ImageMeta& m = m_images[idx].meta;
+	for (int c = 0; c < 4; ++c) m.xform.c[c] = {x[0 * 4 + c], x[1 * 4 + c], x[2 * 4 + c]};
+	m.focal_x = focal_x; m.focal_y = focal_y;
+	m.principal_x = principal_x; m.principal_y = principal_y;
+	m.lens_mode = lens_mode;
+	for (int k = 0; k < 7; ++k) m.lens_params[k] = lens_params ? lens_params[k] : 0.0f;
+	m_metadata_dirty = true;
+}
+
+void Testbed::upload_metadata() {
+	if (!m_metadata_dirty) return;
+	std::vector<ImageMeta> host(m_images.size());
+	for (size_t i = 0; i < m_images.size(); ++i) host[i] = m_images[i].meta;
+	m_metadata_gpu.alloc(std::max<size_t>(1, host.size()) * sizeof(ImageMeta), m_stream);
+	if (!host.empty()) NGPB_CUDA_CHECK(cudaMemcpyAsync(m_metadata_gpu.ptr, host.data(), host.size() * sizeof(ImageMeta), cudaMemcpyHostToDevice, m_stream));
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	m_metadata_dirty = false;
+}
+
+// ---------------------------------------------------------------------------------------------
+void Testbed::reload_network_from_json(const Json& config) {
+	m_network_config = config;
+	reset_network();
+}
+
+void Testbed::reset_network(bool clear_density_grid) {
+	m_rng = Pcg32{seed};
+	rays_per_batch = 1u << 12;
+	measured_batch_size_before_compaction = 0;
+	measured_batch_size = 0;
+	m_density_grid_rng = Pcg32{m_rng.next_uint()};
+
+	const size_t n_grid = (size_t)kNerfGridCells * (m_max_cascade + 1);
+	m_density_grid.alloc(n_grid * sizeof(float), m_stream);
+	m_density_grid_tmp.alloc(n_grid * sizeof(float), m_stream);
+	m_density_bitfield.reserve(nerf_bitfield_bytes(), m_stream);
+	m_density_mean.reserve(sizeof(float), m_stream);
+	if (clear_density_grid) {
+		NGPB_CUDA_CHECK(cudaMemsetAsync(m_density_grid.ptr, 0, n_grid * sizeof(float), m_stream));
+		NGPB_CUDA_CHECK(cudaMemsetAsync(m_density_bitfield.ptr, 0, nerf_bitfield_bytes(), m_stream));
+		NGPB_CUDA_CHECK(cudaMemsetAsync(m_density_mean.ptr, 0, sizeof(float), m_stream));
+	}
+
+	Json config = m_network_config;
+	if (!config.contains("encoding") || !config.contains("network")) throw std::runtime_error{"Network config must contain 'encoding' and 'network'."};
+	Json encoding_config = config["encoding"];
+	const Json loss_config = config.value("loss", Json::object());
+	const Json optimizer_config = config.value("optimizer", Json::object());
+	loss_type = loss_type_from_string(loss_config.value("otype", "L2"));
+
+	// hash-grid hyper-parameters (src/testbed.cu:3679-3725)
+	const uint32_t n_pos = 3;
+	const uint32_t F = encoding_config.value("n_features_per_level", 2u);
+	uint32_t n_levels;
+	if (encoding_config.contains("n_features") && encoding_config["n_features"].as_uint() > 0) n_levels = encoding_config["n_features"].as_uint() / F;
+	else n_levels = encoding_config.value("n_levels", 16u);
+	const uint32_t log2_hashmap_size = encoding_config.value("log2_hashmap_size", 15u);
+	uint32_t base_resolution = encoding_config.value("base_resolution", 0u);
+	if (!base_resolution) {
+		base_resolution = 1u << (log2_hashmap_size / n_pos);
+		encoding_config["base_resolution"] = base_resolution;
+	}
+	const float desired_resolution = 2048.0f;
+	float per_level_scale = encoding_config.value("per_level_scale", 0.0f);
+	if (per_level_scale <= 0.0f && n_levels > 1) {
+		per_level_scale = std::exp(std::log(desired_resolution * (float)aabb_scale / (float)base_resolution) / (n_levels - 1));
+		encoding_config["per_level_scale"] = per_level_scale;
+	}
+	m_network_config["encoding"] = encoding_config;
+
+	const Json dir_encoding = config.value("dir_encoding", Json::parse("{\"otype\":\"Composite\",\"nested\":[{\"n_dims_to_encode\":3,\"otype\":\"SphericalHarmonics\",\"degree\":4},{\"otype\":\"Identity\"}]}"));
+	const Json rgb_network = config.value("rgb_network", Json::parse("{\"otype\":\"FullyFusedMLP\",\"activation\":\"ReLU\",\"output_activation\":\"None\",\"n_neurons\":64,\"n_hidden_layers\":2}"));
+	m_network = std::make_unique<NerfNetworkModule>(n_pos, 3u, 0u, n_pos + 1, encoding_config, dir_encoding, config["network"], rgb_network);
+	m_optimizer = std::make_unique<Optimizer>(optimizer_config);
+
+	// Trainer::initialize_params (tcnn trainer.h:68-87)
+	m_n_params = m_network->n_params();
+	m_optimizer->allocate((uint32_t)m_n_params, m_network->layer_sizes());
+	const size_t n_pad = next_multiple((uint32_t)m_n_params, 8u);
+	m_params_fp32.alloc(n_pad * sizeof(float), m_stream);
+	m_params.alloc(n_pad * sizeof(__half), m_stream);
+	m_gradients.alloc(n_pad * sizeof(__half), m_stream);
+	NGPB_CUDA_CHECK(cudaMemsetAsync(m_params_fp32.ptr, 0, n_pad * sizeof(float), m_stream));
+	NGPB_CUDA_CHECK(cudaMemsetAsync(m_gradients.ptr, 0, n_pad * sizeof(__half), m_stream));
+	Pcg32 trainer_rng{seed};
+	m_network->initialize_params(m_stream, trainer_rng, m_params_fp32.as<float>(), 1.0f);
+	cast_fp32_to_fp16(m_stream, m_n_params, m_params_fp32.as<float>(), m_params.as<__half>());
+	m_training_step = 0;
+	n_rays_total = 0;
+	m_loss_scalar = 0.0f;
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+}
+
+} // namespace ngpb

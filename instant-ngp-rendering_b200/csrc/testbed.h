@@ -1,0 +1,136 @@
+// Testbed: the host object behind the `ngpb_testbed_*` C ABI. Mirrors the train / render entry
+// points of ngp::Testbed for the NeRF mode (include/neural-graphics-primitives/testbed.h:70-655,
+// src/testbed.cu:3624-3868 reset_network, :4020-4109 train, src/testbed_nerf.cu:2271-2946) with
+// the state the hot path needs and nothing of the GUI / camera-path / VR shell.
+#pragma once
+
+#include "nerf.h"
+#include "network.h"
+#include "optimizer.h"
+
+#include <memory>
+#include <vector>
+
+namespace ngpb {
+
+struct NerfImage {
+	DeviceBuffer pixels;
+	ImageMeta meta{};
+};
+
+class Testbed {
+public:
+	Testbed();
+	~Testbed();
+
+	// ---- dataset (Testbed::create_empty_nerf_dataset / set_image / set_camera_*, python_api.cu:383-567)
+	void create_empty_nerf_dataset(uint32_t n_images, int aabb_scale, bool is_hdr);
+	// pixels: HOST or DEVICE pointer to w*h RGBA texels of `image_data_type` (Byte = sRGB8 straight
+	// alpha, Half / Float = linear premultiplied), copied to the device.
+	void set_nerf_image(uint32_t idx, const void* pixels, int image_data_type, int width, int height);
+	// camera-to-world 3x4 in the NGP convention (already passed through nerf_matrix_to_ngp),
+	// row-major [3][4]; focal length in pixels; principal point in [0,1]; lens as ELensMode + params.
+	void set_nerf_camera(uint32_t idx, const float* xform_3x4, float focal_x, float focal_y, float principal_x, float principal_y, int lens_mode, const float* lens_params);
+
+	// ---- network (reload_network_from_json, reset_network)
+	void reload_network_from_json(const Json& config);
+	void reset_network(bool clear_density_grid = true);
+
+	// ---- training (Testbed::train)
+	void train(uint32_t batch_size);
+	float loss() const { return m_loss_scalar; }
+	uint32_t training_step() const { return m_training_step; }
+
+	// ---- introspection for tests / tools
+	NerfNetworkModule* nerf_network() { return m_network.get(); }
+	Optimizer* optimizer() { return m_optimizer.get(); }
+	size_t n_params() const { return m_n_params; }
+	float* params_fp32() { return m_params_fp32.as<float>(); }
+	__half* params() { return m_params.as<__half>(); }
+	__half* params_inference() { return m_optimizer && m_optimizer->custom_weights() ? m_optimizer->custom_weights() : m_params.as<__half>(); }
+	__half* gradients() { return m_gradients.as<__half>(); }
+	float* density_grid() { return m_density_grid.as<float>(); }
+	uint8_t* density_grid_bitfield() { return m_density_bitfield.as<uint8_t>(); }
+	float* density_grid_mean() { return m_density_mean.as<float>(); }
+	const Aabb& aabb() const { return m_aabb; }
+	uint32_t max_cascade() const { return m_max_cascade; }
+	float cone_angle_constant() const { return m_cone_angle_constant; }
+	const ImageMeta* metadata_gpu() const { return m_metadata_gpu.as<ImageMeta>(); }
+	uint32_t n_images() const { return (uint32_t)m_images.size(); }
+	cudaStream_t stream() const { return m_stream; }
+	const Json& network_config() const { return m_network_config; }
+
+	// counters of the last step (NerfCounters)
+	uint32_t rays_per_batch = 1u << 12;
+	uint32_t measured_batch_size = 0;
+	uint32_t measured_batch_size_before_compaction = 0;
+	uint32_t n_rays_total = 0;
+
+	// knobs (testbed.h / nerf.h defaults)
+	uint64_t seed = 1337;
+	int rgb_activation = kActLogistic;
+	int density_activation = kActExponential;
+	int loss_type = kLossL2;
+	int color_space = kColorLinear;
+	bool random_bg_color = true;
+	bool linear_colors = false;
+	bool snap_to_pixel_centers = true;
+	float near_distance = 0.1f;
+	float density_grid_decay = 0.95f;
+	float background_color[4] = {0.0f, 0.0f, 0.0f, 1.0f};
+	bool train_network = true;
+	bool train_encoding = true;
+	float render_min_transmittance = 0.01f;
+	int aabb_scale = 1;
+
+	// Steps of update_density_grid_nerf, exposed for tests.
+	void update_density_grid_nerf(float decay, uint32_t n_uniform, uint32_t n_nonuniform);
+	void update_density_grid_mean_and_bitfield();
+	void upload_metadata();
+
+	// ---- rendering (Testbed::render_nerf via NerfTracer; see nerf_render.cu)
+	// camera 3x4 row-major NGP convention, focal length in pixels of the render resolution.
+	// rgba_out: DEVICE float4 [h][w] (linear, premultiplied); depth_out: DEVICE float [h][w] or null.
+	// Pixels [pixel_begin, pixel_end) in row-major order are rendered (tile sharding).
+	void render_nerf(uint32_t width, uint32_t height, const float* camera_3x4, float focal_x, float focal_y, float principal_x, float principal_y,
+		uint32_t spp_index, uint32_t pixel_begin, uint32_t pixel_end, float* rgba_out, float* depth_out);
+	uint64_t last_render_samples = 0;
+
+private:
+	void training_prep_nerf();
+	void train_nerf(uint32_t target_batch_size, bool get_loss_scalar);
+	void train_nerf_step(uint32_t target_batch_size);
+
+	cudaStream_t m_stream = nullptr;
+	Json m_network_config;
+	std::unique_ptr<NerfNetworkModule> m_network;
+	std::unique_ptr<Optimizer> m_optimizer;
+	size_t m_n_params = 0;
+	DeviceBuffer m_params_fp32, m_params, m_gradients;
+
+	std::vector<NerfImage> m_images;
+	DeviceBuffer m_metadata_gpu;
+	bool m_metadata_dirty = true;
+	bool m_is_hdr = false;
+
+	Aabb m_aabb{{0, 0, 0}, {1, 1, 1}};
+	uint32_t m_max_cascade = 0;
+	float m_cone_angle_constant = 0.0f;
+
+	Pcg32 m_rng;
+	Pcg32 m_density_grid_rng;
+	uint32_t m_density_grid_ema_step = 0;
+	uint32_t m_training_step = 0;
+	float m_loss_scalar = 0.0f;
+
+	DeviceBuffer m_density_grid, m_density_grid_tmp, m_density_bitfield, m_density_mean;
+	DeviceBuffer m_grid_positions, m_grid_indices, m_grid_mlp_out;
+
+	// per-step scratch
+	DeviceBuffer m_counters, m_ray_indices, m_rays, m_numsteps, m_coords, m_rgbsigma, m_coords_compacted, m_dloss, m_loss;
+	DeviceBuffer m_render_scratch;
+	NerfStepCounters* m_counters_host = nullptr; // pinned
+	float* m_loss_host = nullptr;                // pinned
+};
+
+} // namespace ngpb

@@ -1,0 +1,174 @@
+// Testbed::train and the NeRF training step (src/testbed.cu:4020-4109, src/testbed_nerf.cu:2271-2946).
+#include "testbed.h"
+
+#include <algorithm>
+
+namespace ngpb {
+
+__global__ void reduce_loss_kernel(uint32_t n, const float* __restrict__ loss, float* __restrict__ out) {
+	__shared__ float warp_part[8];
+	float s = 0.0f;
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) s += loss[i];
+#pragma unroll
+	for (uint32_t o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+	if (threadIdx.x % 32 == 0) warp_part[threadIdx.x / 32] = s;
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		float t = 0.0f;
+		for (uint32_t w = 0; w < blockDim.x / 32; ++w) t += warp_part[w];
+		atomicAdd(out, t);
+	}
+}
+
+void Testbed::update_density_grid_mean_and_bitfield() {
+	nerf_update_bitfield(m_stream, m_max_cascade, m_density_grid.as<float>(), m_density_bitfield.as<uint8_t>(), m_density_mean.as<float>());
+}
+
+void Testbed::update_density_grid_nerf(float decay, uint32_t n_uniform, uint32_t n_nonuniform) {
+	upload_metadata();
+	const uint32_t n_elements = kNerfGridCells * (m_max_cascade + 1);
+	const uint32_t n_samples = n_uniform + n_nonuniform;
+	const uint32_t n_padded = next_multiple(n_samples, kTile);
+	m_grid_positions.reserve((size_t)n_padded * 4 * sizeof(float), m_stream);
+	m_grid_indices.reserve((size_t)n_padded * sizeof(uint32_t), m_stream);
+	m_grid_mlp_out.reserve((size_t)n_padded * sizeof(__half), m_stream);
+
+	if (m_training_step == 0) {
+		m_density_grid_ema_step = 0;
+		nerf_mark_untrained_density_grid(m_stream, n_elements, m_density_grid.as<float>(), n_images(), metadata_gpu(), true);
+	}
+
+	NGPB_CUDA_CHECK(cudaMemsetAsync(m_density_grid_tmp.ptr, 0, sizeof(float) * n_elements, m_stream));
+	float* positions = m_grid_positions.as<float>();
+	uint32_t* indices = m_grid_indices.as<uint32_t>();
+	nerf_generate_grid_samples(m_stream, n_uniform, m_density_grid_rng, m_density_grid_ema_step, m_aabb, m_density_grid.as<float>(), positions, indices, m_max_cascade + 1, -0.01f);
+	m_density_grid_rng.advance(1ll << 32);
+	nerf_generate_grid_samples(m_stream, n_nonuniform, m_density_grid_rng, m_density_grid_ema_step, m_aabb, m_density_grid.as<float>(),
+		positions + (size_t)n_uniform * 4, indices + n_uniform, m_max_cascade + 1, kNerfMinOpticalThickness);
+	m_density_grid_rng.advance(1ll << 32);
+	if (n_padded > n_samples) NGPB_CUDA_CHECK(cudaMemsetAsync(positions + (size_t)n_samples * 4, 0, (size_t)(n_padded - n_samples) * 4 * sizeof(float), m_stream));
+
+	// density network on the training parameters (use_inference_params = false, :2350)
+	m_network->density(m_stream, n_padded, positions, 4, m_grid_mlp_out.as<__half>(), 1, params());
+	nerf_splat_grid_samples(m_stream, n_samples, indices, m_grid_mlp_out.as<__half>(), m_density_grid_tmp.as<float>(), density_activation);
+	nerf_ema_grid_samples(m_stream, n_elements, decay, m_density_grid.as<float>(), m_density_grid_tmp.as<float>());
+	++m_density_grid_ema_step;
+	update_density_grid_mean_and_bitfield();
+}
+
+void Testbed::training_prep_nerf() {
+	if (n_images() == 0) return;
+	const uint32_t n_cascades = m_max_cascade + 1;
+	if (m_training_step < 256) update_density_grid_nerf(density_grid_decay, kNerfGridCells * n_cascades, 0);
+	else update_density_grid_nerf(density_grid_decay, kNerfGridCells / 4 * n_cascades, kNerfGridCells / 4 * n_cascades);
+}
+
+void Testbed::train(uint32_t batch_size) {
+	if (n_images() == 0) throw std::runtime_error{"Cannot train without training data."};
+	if (!m_network) throw std::runtime_error{"Unable to create a neural network trainer."};
+	if (batch_size == 0 || batch_size % kBatchSizeGranularity != 0) throw std::runtime_error{"ngp-b200: batch size must be a positive multiple of 256"};
+	upload_metadata();
+
+	const uint32_t n_prep_to_skip = std::min(std::max(m_training_step / 16u, 1u), 16u);
+	if (m_training_step % n_prep_to_skip == 0) training_prep_nerf();
+
+	Json leaf = Json::object();
+	leaf["otype"] = "Adam";
+	leaf["optimize_matrix_params"] = train_network;
+	leaf["optimize_non_matrix_params"] = train_encoding;
+	m_optimizer->update_hyperparams(leaf);
+
+	const bool get_loss_scalar = m_training_step % 16 == 0;
+	train_nerf(batch_size, get_loss_scalar);
+}
+
+void Testbed::train_nerf_step(uint32_t target_batch_size) {
+	const uint32_t max_samples = target_batch_size * 16; // "somewhat of a worst case" (:2685)
+	m_counters.reserve(sizeof(NerfStepCounters), m_stream);
+	m_ray_indices.reserve((size_t)(1u << 18) * sizeof(uint32_t), m_stream);
+	m_rays.reserve((size_t)(1u << 18) * 6 * sizeof(float), m_stream);
+	m_numsteps.reserve((size_t)(1u << 18) * 2 * sizeof(uint32_t), m_stream);
+	m_loss.reserve((size_t)(1u << 18) * sizeof(float), m_stream);
+	m_coords.reserve((size_t)max_samples * kCoordFloats * sizeof(float), m_stream);
+	m_rgbsigma.reserve((size_t)max_samples * 4 * sizeof(__half), m_stream);
+	m_coords_compacted.reserve((size_t)target_batch_size * kCoordFloats * sizeof(float), m_stream);
+	m_dloss.reserve((size_t)target_batch_size * 4 * sizeof(__half), m_stream);
+
+	NGPB_CUDA_CHECK(cudaMemsetAsync(m_counters.ptr, 0, sizeof(NerfStepCounters), m_stream));
+	NGPB_CUDA_CHECK(cudaMemsetAsync(m_loss.ptr, 0, sizeof(float) * rays_per_batch, m_stream));
+	// dloss / coords of a batch that the loss kernel does not fill completely and whose roll-over
+	// finds no input must not carry stale gradients
+	NGPB_CUDA_CHECK(cudaMemsetAsync(m_dloss.ptr, 0, (size_t)target_batch_size * 4 * sizeof(__half), m_stream));
+
+	if (m_training_step == 0) n_rays_total = 0;
+	const uint32_t n_rays_total_before = n_rays_total;
+	n_rays_total += rays_per_batch;
+
+	// The reference bounds the generator by last step's measured sample count (:2730-2735) because
+	// its inference batch is sized on the host; here the sample count stays on the device and the
+	// consumers read it there, so the full buffer is available.
+	NerfTrainConfig cfg{};
+	cfg.aabb = m_aabb;
+	cfg.n_rays = rays_per_batch;
+	cfg.n_rays_total = n_rays_total_before;
+	cfg.max_samples = max_samples;
+	cfg.max_samples_compacted = target_batch_size;
+	cfg.n_training_images = n_images();
+	cfg.max_mip = m_max_cascade;
+	cfg.cone_angle_constant = m_cone_angle_constant;
+	cfg.near_distance = near_distance;
+	cfg.loss_scale = kLossScaleFp16;
+	cfg.snap_to_pixel_centers = snap_to_pixel_centers;
+	cfg.random_bg_color = random_bg_color;
+	cfg.linear_colors = linear_colors;
+	cfg.color_space = color_space;
+	cfg.loss_type = loss_type;
+	cfg.rgb_activation = rgb_activation;
+	cfg.density_activation = density_activation;
+	for (int k = 0; k < 3; ++k) cfg.background_color[k] = background_color[k];
+
+	NerfTrainBuffers buf{};
+	buf.metadata = metadata_gpu();
+	buf.density_bitfield = m_density_bitfield.as<uint8_t>();
+	buf.mean_density = m_density_mean.as<float>();
+	buf.counters = m_counters.as<NerfStepCounters>();
+	buf.ray_indices = m_ray_indices.as<uint32_t>();
+	buf.rays_unnormalized = m_rays.as<float>();
+	buf.numsteps = m_numsteps.as<uint32_t>();
+	buf.coords = m_coords.as<float>();
+	buf.rgbsigma = m_rgbsigma.as<__half>();
+	buf.coords_compacted = m_coords_compacted.as<float>();
+	buf.dloss_doutput = m_dloss.as<__half>();
+	buf.loss = m_loss.as<float>();
+
+	nerf_generate_training_samples(m_stream, cfg, buf, m_rng);
+	// network on the training parameters over exactly the generated samples (device-side count)
+	m_network->inference_counted(m_stream, max_samples, &buf.counters->numsteps, m_coords.as<float>(), kCoordFloats, m_rgbsigma.as<__half>(), 4, params());
+	nerf_compute_loss_and_compact(m_stream, cfg, buf, m_rng);
+	m_network->backward_strided(m_stream, target_batch_size, m_coords_compacted.as<float>(), kCoordFloats, m_dloss.as<__half>(), 4, gradients(), params());
+	m_rng.advance(1ll << 32);
+}
+
+void Testbed::train_nerf(uint32_t target_batch_size, bool get_loss_scalar) {
+	train_nerf_step(target_batch_size);
+	m_optimizer->step(m_stream, kLossScaleFp16, params_fp32(), params(), gradients());
+	++m_training_step;
+
+	// NerfCounters::update_after_training (:2422-2446)
+	if (get_loss_scalar) reduce_loss_kernel<<<sm_count(), 256, 0, m_stream>>>(rays_per_batch, m_loss.as<float>(), &m_counters.as<NerfStepCounters>()->loss_sum);
+	NGPB_CUDA_CHECK(cudaMemcpyAsync(m_counters_host, m_counters.ptr, sizeof(NerfStepCounters), cudaMemcpyDeviceToHost, m_stream));
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	measured_batch_size = 0;
+	measured_batch_size_before_compaction = 0;
+	if (m_counters_host->numsteps == 0 || m_counters_host->numsteps_compacted == 0) {
+		m_loss_scalar = 0.0f;
+		throw std::runtime_error{"Nerf training generated 0 samples. Aborting training."};
+	}
+	measured_batch_size_before_compaction = m_counters_host->numsteps;
+	measured_batch_size = m_counters_host->numsteps_compacted;
+	if (get_loss_scalar) m_loss_scalar = m_counters_host->loss_sum * (float)measured_batch_size / (float)target_batch_size;
+	rays_per_batch = (uint32_t)((float)rays_per_batch * (float)target_batch_size / (float)measured_batch_size);
+	rays_per_batch = std::min(next_multiple(rays_per_batch, kBatchSizeGranularity), 1u << 18);
+}
+
+} // namespace ngpb
