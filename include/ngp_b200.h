@@ -207,8 +207,6 @@ int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value);
 /* Device buffers by name: params (fp16), params_fp32, params_inference (fp16), gradients (fp16),
  * density_grid (float), density_grid_bitfield (uint8), density_grid_mean (float), metadata. */
 int ngpb_testbed_device_ptr(ngpb_testbed_t* t, const char* name, void** ptr, size_t* bytes);
-/* The module (NerfNetwork) owned by the testbed; valid until the next reload / free. */
-ngpb_module_t* ngpb_testbed_network(ngpb_testbed_t* t);
 size_t ngpb_testbed_network_config(const ngpb_testbed_t* t, char* buf, size_t cap);
 /* update_density_grid_nerf(decay, n_uniform, n_nonuniform), src/testbed_nerf.cu:2271-2360. */
 int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_uniform, uint32_t n_nonuniform);

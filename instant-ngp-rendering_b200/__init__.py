@@ -8,10 +8,11 @@ aliases it as `ngp_b200`).
 """
 from . import _lib
 from ._lib import NgpbError, has_device, lib, LIB_PATH
+from .testbed import Testbed, nerf_matrix_to_ngp, load_network_config
 from .modules import (Context, Encoding, Module, NerfNetwork, Network, NetworkWithInputEncoding,
                       batch_size_granularity, default_loss_scale)
 
 __all__ = [
-    "NgpbError", "has_device", "lib", "LIB_PATH", "Context", "Encoding", "Module", "NerfNetwork",
+    "NgpbError", "has_device", "Testbed", "nerf_matrix_to_ngp", "load_network_config", "lib", "LIB_PATH", "Context", "Encoding", "Module", "NerfNetwork",
     "Network", "NetworkWithInputEncoding", "batch_size_granularity", "default_loss_scale",
 ]

@@ -61,6 +61,37 @@ SIGNATURES = {
     "ngpb_grid_level_table": (c_u32, [c_vp, ctypes.POINTER(c_u32), ctypes.POINTER(c_f32), ctypes.POINTER(c_u32)]),
     "ngpb_grid_indices": (c_int, [c_vp, c_vp, c_u32, c_vp, c_vp]),
     "ngpb_grid_set_max_level": (c_int, [c_vp, c_f32]),
+    "ngpb_optimizer_create": (c_int, [c_cp, ctypes.POINTER(c_vp)]),
+    "ngpb_optimizer_free": (None, [c_vp]),
+    "ngpb_optimizer_allocate": (c_int, [c_vp, c_u32, ctypes.POINTER(c_u32), c_sz]),
+    "ngpb_optimizer_step": (c_int, [c_vp, c_vp, c_f32, c_vp, c_vp, c_vp]),
+    "ngpb_optimizer_learning_rate": (c_f32, [c_vp]),
+    "ngpb_optimizer_set_learning_rate": (c_int, [c_vp, c_f32]),
+    "ngpb_optimizer_step_count": (c_u32, [c_vp]),
+    "ngpb_optimizer_custom_weights": (c_vp, [c_vp]),
+    "ngpb_optimizer_update_hyperparams": (c_int, [c_vp, c_cp]),
+    "ngpb_optimizer_hyperparams": (c_sz, [c_vp, c_cp, c_sz]),
+    "ngpb_optimizer_state": (c_int, [c_vp, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
+    "ngpb_nerf_network_density": (c_int, [c_vp, c_vp, c_u32, c_vp, c_u32, c_vp, c_u32, c_vp]),
+    "ngpb_nerf_network_param_layout": (c_int, [c_vp, ctypes.POINTER(c_sz)]),
+    "ngpb_nerf_generate_training_samples": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(c_u64)]),
+    "ngpb_nerf_compute_loss_and_compact": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(c_u64)]),
+    "ngpb_nerf_update_bitfield": (c_int, [c_vp, c_u32, c_vp, c_vp, c_vp]),
+    "ngpb_nerf_bitfield_bytes": (c_sz, []),
+    "ngpb_testbed_create": (c_int, [ctypes.POINTER(c_vp)]),
+    "ngpb_testbed_free": (None, [c_vp]),
+    "ngpb_testbed_create_empty_nerf_dataset": (c_int, [c_vp, c_u32, c_int, c_int]),
+    "ngpb_testbed_set_nerf_image": (c_int, [c_vp, c_u32, c_vp, c_int, c_int, c_int]),
+    "ngpb_testbed_set_nerf_camera": (c_int, [c_vp, c_u32, ctypes.POINTER(c_f32), c_f32, c_f32, c_f32, c_f32, c_int, ctypes.POINTER(c_f32)]),
+    "ngpb_testbed_reload_network_from_json": (c_int, [c_vp, c_cp]),
+    "ngpb_testbed_reset_network": (c_int, [c_vp, c_int]),
+    "ngpb_testbed_train": (c_int, [c_vp, c_u32]),
+    "ngpb_testbed_get": (c_int, [c_vp, c_cp, ctypes.POINTER(ctypes.c_double)]),
+    "ngpb_testbed_set": (c_int, [c_vp, c_cp, ctypes.c_double]),
+    "ngpb_testbed_device_ptr": (c_int, [c_vp, c_cp, ctypes.POINTER(c_vp), ctypes.POINTER(c_sz)]),
+    "ngpb_testbed_network_config": (c_sz, [c_vp, c_cp, c_sz]),
+    "ngpb_testbed_update_density_grid": (c_int, [c_vp, c_f32, c_u32, c_u32]),
+    "ngpb_testbed_render_nerf": (c_int, [c_vp, c_u32, c_u32, ctypes.POINTER(c_f32), c_f32, c_f32, c_f32, c_f32, c_u32, c_u32, c_u32, c_vp, c_vp]),
     "ngpb_selftest_umma": (c_int, [c_vp, c_int, c_u32, c_u32, c_vp, c_vp, c_vp]),
     "ngpb_random_uniform": (c_int, [c_vp, ctypes.POINTER(c_u64), c_sz, c_vp, c_f32, c_f32]),
 }

@@ -1,0 +1,155 @@
+// extern "C" surface of the Testbed (include/ngp_b200.h).
+#include "../../include/ngp_b200.h"
+
+#include "testbed.h"
+
+#include <cstring>
+
+using namespace ngpb;
+
+struct ngpb_testbed {
+	std::unique_ptr<Testbed> impl;
+};
+
+#define NGPB_API_BEGIN try {
+#define NGPB_API_END \
+	} catch (const std::exception& e) { set_last_error(e.what()); return NGPB_ERROR; } \
+	catch (...) { set_last_error("unknown error"); return NGPB_ERROR; } \
+	return NGPB_OK;
+
+static size_t copy_out(const std::string& s, char* buf, size_t cap) {
+	if (buf && cap > 0) {
+		const size_t n = s.size() < cap - 1 ? s.size() : cap - 1;
+		memcpy(buf, s.data(), n);
+		buf[n] = 0;
+	}
+	return s.size() + 1;
+}
+static void require_device() {
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+		cudaGetLastError();
+		throw std::runtime_error{"ngp-b200: no CUDA device; this library has no CPU fallback"};
+	}
+}
+
+extern "C" {
+
+int ngpb_testbed_create(ngpb_testbed_t** out) {
+	NGPB_API_BEGIN
+	require_device();
+	if (!out) throw std::runtime_error{"ngpb_testbed_create: null argument"};
+	*out = new ngpb_testbed{std::make_unique<Testbed>()};
+	NGPB_API_END
+}
+void ngpb_testbed_free(ngpb_testbed_t* t) { delete t; }
+
+int ngpb_testbed_create_empty_nerf_dataset(ngpb_testbed_t* t, uint32_t n_images, int aabb_scale, int is_hdr) {
+	NGPB_API_BEGIN
+	t->impl->create_empty_nerf_dataset(n_images, aabb_scale, is_hdr != 0);
+	NGPB_API_END
+}
+int ngpb_testbed_set_nerf_image(ngpb_testbed_t* t, uint32_t idx, const void* pixels, int image_data_type, int width, int height) {
+	NGPB_API_BEGIN
+	t->impl->set_nerf_image(idx, pixels, image_data_type, width, height);
+	NGPB_API_END
+}
+int ngpb_testbed_set_nerf_camera(ngpb_testbed_t* t, uint32_t idx, const float* xform_3x4, float focal_x, float focal_y,
+	float principal_x, float principal_y, int lens_mode, const float* lens_params)
+{
+	NGPB_API_BEGIN
+	t->impl->set_nerf_camera(idx, xform_3x4, focal_x, focal_y, principal_x, principal_y, lens_mode, lens_params);
+	NGPB_API_END
+}
+int ngpb_testbed_reload_network_from_json(ngpb_testbed_t* t, const char* config_json) {
+	NGPB_API_BEGIN
+	if (!config_json) throw std::runtime_error{"ngpb_testbed_reload_network_from_json: null argument"};
+	t->impl->reload_network_from_json(Json::parse(config_json));
+	NGPB_API_END
+}
+int ngpb_testbed_reset_network(ngpb_testbed_t* t, int clear_density_grid) {
+	NGPB_API_BEGIN
+	t->impl->reset_network(clear_density_grid != 0);
+	NGPB_API_END
+}
+int ngpb_testbed_train(ngpb_testbed_t* t, uint32_t batch_size) {
+	NGPB_API_BEGIN
+	t->impl->train(batch_size);
+	NGPB_API_END
+}
+
+#define NGPB_PROPS(X) \
+	X(rays_per_batch) X(measured_batch_size) X(measured_batch_size_before_compaction) X(seed) X(random_bg_color) X(linear_colors) \
+	X(snap_to_pixel_centers) X(near_distance) X(density_grid_decay) X(render_min_transmittance) X(loss_type) X(rgb_activation) \
+	X(density_activation) X(color_space) X(train_network) X(train_encoding) X(aabb_scale)
+
+int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
+	NGPB_API_BEGIN
+	const Testbed& tb = *t->impl;
+	const std::string n = name;
+	if (n == "training_step") *value = tb.training_step();
+	else if (n == "loss") *value = tb.loss();
+	else if (n == "n_params") *value = (double)tb.n_params();
+	else if (n == "max_cascade") *value = tb.max_cascade();
+	else if (n == "cone_angle_constant") *value = tb.cone_angle_constant();
+	else if (n == "n_images") *value = tb.n_images();
+	else if (n == "last_render_samples") *value = (double)tb.last_render_samples;
+#define X(f) else if (n == #f) *value = (double)tb.f;
+	NGPB_PROPS(X)
+#undef X
+	else throw std::runtime_error{"ngpb_testbed_get: unknown property " + n};
+	NGPB_API_END
+}
+int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value) {
+	NGPB_API_BEGIN
+	Testbed& tb = *t->impl;
+	const std::string n = name;
+	if (false) {}
+#define X(f) else if (n == #f) tb.f = (decltype(tb.f))value;
+	NGPB_PROPS(X)
+#undef X
+	else throw std::runtime_error{"ngpb_testbed_set: unknown or read-only property " + n};
+	NGPB_API_END
+}
+
+int ngpb_testbed_device_ptr(ngpb_testbed_t* t, const char* name, void** ptr, size_t* bytes) {
+	NGPB_API_BEGIN
+	Testbed& tb = *t->impl;
+	const std::string n = name;
+	void* p = nullptr;
+	size_t b = 0;
+	const size_t n_grid = (size_t)kNerfGridCells * (tb.max_cascade() + 1);
+	if (n == "params") { p = tb.params(); b = tb.n_params() * 2; }
+	else if (n == "params_fp32") { p = tb.params_fp32(); b = tb.n_params() * 4; }
+	else if (n == "params_inference") { p = tb.params_inference(); b = tb.n_params() * 2; }
+	else if (n == "gradients") { p = tb.gradients(); b = tb.n_params() * 2; }
+	else if (n == "density_grid") { p = tb.density_grid(); b = n_grid * 4; }
+	else if (n == "density_grid_bitfield") { p = tb.density_grid_bitfield(); b = nerf_bitfield_bytes(); }
+	else if (n == "density_grid_mean") { p = tb.density_grid_mean(); b = 4; }
+	else if (n == "metadata") { tb.upload_metadata(); p = (void*)tb.metadata_gpu(); b = tb.n_images() * sizeof(ImageMeta); }
+	else throw std::runtime_error{"ngpb_testbed_device_ptr: unknown buffer " + n};
+	if (ptr) *ptr = p;
+	if (bytes) *bytes = b;
+	NGPB_API_END
+}
+
+size_t ngpb_testbed_network_config(const ngpb_testbed_t* t, char* buf, size_t cap) {
+	try { return copy_out(t->impl->network_config().dump(), buf, cap); } catch (...) { return 0; }
+}
+
+int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_uniform, uint32_t n_nonuniform) {
+	NGPB_API_BEGIN
+	t->impl->update_density_grid_nerf(decay, n_uniform, n_nonuniform);
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(t->impl->stream()));
+	NGPB_API_END
+}
+
+int ngpb_testbed_render_nerf(ngpb_testbed_t* t, uint32_t width, uint32_t height, const float* camera_3x4, float focal_x, float focal_y,
+	float principal_x, float principal_y, uint32_t spp_index, uint32_t pixel_begin, uint32_t pixel_end, float* rgba, float* depth)
+{
+	NGPB_API_BEGIN
+	t->impl->render_nerf(width, height, camera_3x4, focal_x, focal_y, principal_x, principal_y, spp_index, pixel_begin, pixel_end, rgba, depth);
+	NGPB_API_END
+}
+
+} // extern "C"
