@@ -1,0 +1,518 @@
+// CPU oracle for the NeRF driver kernels. TEST INFRASTRUCTURE ONLY (see oracle.h).
+// Restates, routine by routine (paths relative to the reference root):
+//   constants, stepping, cascades, warps      include/neural-graphics-primitives/nerf_device.cuh:20-40, 265-458
+//   activations, losses                       nerf_device.cuh:74-143, 203-263, 600-615
+//   image_idx, random image position          nerf_device.cuh:552-598
+//   lens undistortion, uv_to_ray, read_rgba   include/neural-graphics-primitives/common_device.cuh:248-460, 730-806
+//   sRGB                                      common_device.cuh:34-64
+//   ray/box                                   include/neural-graphics-primitives/bounding_box.cuh:172-230
+//   Morton                                    dependencies/tiny-cuda-nn/include/tiny-cuda-nn/common_device.h:759-785
+//   generate_training_samples_nerf            src/testbed_nerf.cu:679-838
+//   compute_loss_kernel_train_nerf            src/testbed_nerf.cu:841-1160 (no envmap / depth / error map / exposure)
+//   grid_to_bitfield, bitfield_max_pool, mean src/testbed_nerf.cu:284-331, 2362-2379
+// PARITY UNPINNED by the reference (no golden vectors, GPU-only, built with --use_fast_math). log / exp in
+// the exponential stepping are the single-precision Cephes algorithms so that host and device agree bit
+// for bit; everything else that decides where a sample lies is IEEE add/mul/div/sqrt (-ffp-contract=off).
+#include "oracle.h"
+#include "pcg32_oracle.h"
+
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+typedef _Float16 half_t;
+static inline half_t nbits_to_half(uint16_t b) { half_t h; memcpy(&h, &b, 2); return h; }
+
+namespace {
+
+constexpr uint32_t GRIDSIZE = 128, GRID_CELLS = 128 * 128 * 128, NERF_STEPS = 1024, CASCADES = 8;
+constexpr float SQRT3 = 1.73205080757f;
+constexpr float MIN_CONE_STEPSIZE = SQRT3 / NERF_STEPS;
+constexpr float MAX_CONE_STEPSIZE = MIN_CONE_STEPSIZE * (1 << (CASCADES - 1)) * NERF_STEPS / GRIDSIZE;
+constexpr uint32_t MAX_RANDOM_SAMPLES_PER_RAY = 16;
+constexpr float MIN_OPTICAL_THICKNESS = 0.01f;
+
+struct V { float x, y, z; };
+inline V operator+(V a, V b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline V operator-(V a, V b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline V operator*(V a, V b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
+inline V operator/(V a, V b) { return {a.x / b.x, a.y / b.y, a.z / b.z}; }
+inline V operator*(float s, V a) { return {s * a.x, s * a.y, s * a.z}; }
+inline V operator*(V a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+inline V operator/(V a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+inline V operator+(V a, float s) { return {a.x + s, a.y + s, a.z + s}; }
+inline V operator-(V a, float s) { return {a.x - s, a.y - s, a.z - s}; }
+inline float dot(V a, V b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline float length(V a) { return sqrtf(dot(a, a)); }
+inline V normalize(V a) { return a / length(a); }
+
+struct Box { V min, max; };
+inline bool contains(const Box& b, V p) { return p.x >= b.min.x && p.x <= b.max.x && p.y >= b.min.y && p.y <= b.max.y && p.z >= b.min.z && p.z <= b.max.z; }
+inline V diag(const Box& b) { return b.max - b.min; }
+void ray_intersect(const Box& b, V pos, V dir, float& tmin_o, float& tmax_o) {
+	float tmin = (b.min.x - pos.x) / dir.x, tmax = (b.max.x - pos.x) / dir.x;
+	if (tmin > tmax) std::swap(tmin, tmax);
+	float tymin = (b.min.y - pos.y) / dir.y, tymax = (b.max.y - pos.y) / dir.y;
+	if (tymin > tymax) std::swap(tymin, tymax);
+	if (tmin > tymax || tymin > tmax) { tmin_o = tmax_o = FLT_MAX; return; }
+	if (tymin > tmin) tmin = tymin;
+	if (tymax < tmax) tmax = tymax;
+	float tzmin = (b.min.z - pos.z) / dir.z, tzmax = (b.max.z - pos.z) / dir.z;
+	if (tzmin > tzmax) std::swap(tzmin, tzmax);
+	if (tmin > tzmax || tzmin > tmax) { tmin_o = tmax_o = FLT_MAX; return; }
+	if (tzmin > tmin) tmin = tzmin;
+	if (tzmax < tmax) tmax = tzmax;
+	tmin_o = tmin; tmax_o = tmax;
+}
+
+inline uint32_t expand_bits(uint32_t v) {
+	v = (v * 0x00010001u) & 0xFF0000FFu;
+	v = (v * 0x00000101u) & 0x0F00F00Fu;
+	v = (v * 0x00000011u) & 0xC30C30C3u;
+	v = (v * 0x00000005u) & 0x49249249u;
+	return v;
+}
+inline uint32_t morton3D(uint32_t x, uint32_t y, uint32_t z) { return expand_bits(x) | (expand_bits(y) << 1) | (expand_bits(z) << 2); }
+inline uint32_t morton3D_invert(uint32_t x) {
+	x = x & 0x49249249;
+	x = (x | (x >> 2)) & 0xc30c30c3;
+	x = (x | (x >> 4)) & 0x0f00f00f;
+	x = (x | (x >> 8)) & 0xff0000ff;
+	x = (x | (x >> 16)) & 0x0000ffff;
+	return x;
+}
+
+// Cephes single-precision logf / expf (see file header).
+float c_logf(float xx) {
+	int e;
+	float x = frexpf(xx, &e);
+	if (x < 0.707106781186547524f) { e -= 1; x = x + x - 1.0f; } else { x = x - 1.0f; }
+	float z = x * x;
+	float y = 7.0376836292e-2f;
+	y = y * x - 1.1514610310e-1f;
+	y = y * x + 1.1676998740e-1f;
+	y = y * x - 1.2420140846e-1f;
+	y = y * x + 1.4249322787e-1f;
+	y = y * x - 1.6668057665e-1f;
+	y = y * x + 2.0000714765e-1f;
+	y = y * x - 2.4999993993e-1f;
+	y = y * x + 3.3333331174e-1f;
+	y = y * x * z;
+	const float fe = (float)e;
+	if (e) y += -2.12194440e-4f * fe;
+	y += -0.5f * z;
+	z = x + y;
+	if (e) z += 0.693359375f * fe;
+	return z;
+}
+float c_expf(float x) {
+	if (x > 88.0f) x = 88.0f;
+	if (x < -87.0f) x = -87.0f;
+	float z = floorf(1.44269504088896341f * x + 0.5f);
+	x -= z * 0.693359375f;
+	x -= z * -2.12194440e-4f;
+	const int n = (int)z;
+	z = x * x;
+	float p = 1.9875691500e-4f;
+	p = p * x + 1.3981999507e-3f;
+	p = p * x + 8.3334519073e-3f;
+	p = p * x + 4.1665795894e-2f;
+	p = p * x + 1.6666665459e-1f;
+	p = p * x + 5.0000001201e-1f;
+	z = p * z + x + 1.0f;
+	return scalbnf(z, n);
+}
+
+// nerf_device.cuh:372-424, evaluated per call exactly as written there.
+float to_stepping_space(float t, float cone_angle) {
+	if (cone_angle <= 1e-5f) return t / MIN_CONE_STEPSIZE;
+	const float log1p_c = c_logf(1.0f + cone_angle);
+	const float a = (c_logf(MIN_CONE_STEPSIZE) - c_logf(log1p_c)) / log1p_c;
+	const float b = (c_logf(MAX_CONE_STEPSIZE) - c_logf(log1p_c)) / log1p_c;
+	const float at = c_expf(a * log1p_c), bt = c_expf(b * log1p_c);
+	if (t <= at) return (t - at) / MIN_CONE_STEPSIZE + a;
+	if (t <= bt) return c_logf(t) / log1p_c;
+	return (t - bt) / MAX_CONE_STEPSIZE + b;
+}
+float from_stepping_space(float n, float cone_angle) {
+	if (cone_angle <= 1e-5f) return n * MIN_CONE_STEPSIZE;
+	const float log1p_c = c_logf(1.0f + cone_angle);
+	const float a = (c_logf(MIN_CONE_STEPSIZE) - c_logf(log1p_c)) / log1p_c;
+	const float b = (c_logf(MAX_CONE_STEPSIZE) - c_logf(log1p_c)) / log1p_c;
+	const float at = c_expf(a * log1p_c), bt = c_expf(b * log1p_c);
+	if (n <= a) return (n - a) * MIN_CONE_STEPSIZE + at;
+	if (n <= b) return c_expf(n * log1p_c);
+	return (n - b) * MAX_CONE_STEPSIZE + bt;
+}
+float advance_n_steps(float t, float cone_angle, float n) { return from_stepping_space(to_stepping_space(t, cone_angle) + n, cone_angle); }
+float calc_dt(float t, float cone_angle) { return advance_n_steps(t, cone_angle, 1.0f) - t; }
+inline float sgn(float x) { return copysignf(1.0f, x); }
+float distance_to_next_voxel(V pos, V dir, V idir, float res) {
+	const V p = res * (pos - 0.5f);
+	const float tx = (floorf(p.x + 0.5f + 0.5f * sgn(dir.x)) - p.x) * idir.x;
+	const float ty = (floorf(p.y + 0.5f + 0.5f * sgn(dir.y)) - p.y) * idir.y;
+	const float tz = (floorf(p.z + 0.5f + 0.5f * sgn(dir.z)) - p.z) * idir.z;
+	const float t = fminf(fminf(tx, ty), tz);
+	return fmaxf(t / res, 0.0f);
+}
+float advance_to_next_voxel(float t, float cone_angle, V pos, V dir, V idir, uint32_t mip) {
+	const float res = scalbnf((float)GRIDSIZE, -(int)mip);
+	float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
+	t = to_stepping_space(t, cone_angle);
+	t_target = to_stepping_space(t_target, cone_angle);
+	return from_stepping_space(t + ceilf(fmaxf(t_target - t, 0.5f)), cone_angle);
+}
+inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+uint32_t mip_from_pos(V pos, uint32_t max_cascade) {
+	int exponent;
+	const float maxval = fmaxf(fmaxf(fabsf(pos.x - 0.5f), fabsf(pos.y - 0.5f)), fabsf(pos.z - 0.5f));
+	frexpf(maxval, &exponent);
+	return (uint32_t)clampi(exponent + 1, 0, (int)max_cascade);
+}
+uint32_t mip_from_dt(float dt, V pos, uint32_t max_cascade) {
+	const uint32_t mip = mip_from_pos(pos, max_cascade);
+	dt *= 2 * GRIDSIZE;
+	if (dt < 1.0f) return mip;
+	int exponent;
+	frexpf(dt, &exponent);
+	return (uint32_t)clampi((int)mip, exponent, (int)max_cascade);
+}
+uint32_t cascaded_grid_idx_at(V pos, uint32_t mip) {
+	const float mip_scale = scalbnf(1.0f, -(int)mip);
+	pos = pos - 0.5f;
+	pos = pos * mip_scale;
+	pos = pos + 0.5f;
+	const int ix = (int)(pos.x * (float)GRIDSIZE), iy = (int)(pos.y * (float)GRIDSIZE), iz = (int)(pos.z * (float)GRIDSIZE);
+	if (ix < 0 || ix >= (int)GRIDSIZE || iy < 0 || iy >= (int)GRIDSIZE || iz < 0 || iz >= (int)GRIDSIZE) return 0xFFFFFFFFu;
+	return morton3D(ix, iy, iz);
+}
+bool occupied_at(V pos, const uint8_t* bitfield, uint32_t mip) {
+	const uint32_t idx = cascaded_grid_idx_at(pos, mip);
+	if (idx == 0xFFFFFFFFu) return false;
+	return (bitfield[idx / 8 + (size_t)GRID_CELLS * mip / 8] & (1u << (idx % 8))) != 0;
+}
+inline float warp_dt(float dt) {
+	const float max_stepsize = MIN_CONE_STEPSIZE * (1 << (CASCADES - 1));
+	return (dt - MIN_CONE_STEPSIZE) / (max_stepsize - MIN_CONE_STEPSIZE);
+}
+inline float unwarp_dt(float dt) {
+	const float max_stepsize = MIN_CONE_STEPSIZE * (1 << (CASCADES - 1));
+	return dt * (max_stepsize - MIN_CONE_STEPSIZE) + MIN_CONE_STEPSIZE;
+}
+
+// ---- images, lens, rays ------------------------------------------------------------------------------
+inline float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : powf((s + 0.055f) / 1.055f, 2.4f); }
+inline float linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
+
+struct Rgba { float r, g, b, a; };
+Rgba read_rgba(float u, float v, const oracle_nerf_image& m) {
+	const int px = clampi((int)(u * (float)m.res_x), 0, m.res_x - 1), py = clampi((int)(v * (float)m.res_y), 0, m.res_y - 1);
+	const size_t idx = (size_t)px + (size_t)py * m.res_x;
+	switch (m.image_data_type) {
+		case 1: {
+			const uint32_t val = ((const uint32_t*)m.pixels)[idx];
+			if (val == 0x00FF00FFu) return {-1.0f, -1.0f, -1.0f, -1.0f};
+			const float alpha = (float)(val >> 24) * (1.0f / 255.0f);
+			return {srgb_to_linear((float)(val & 0xFF) * (1.0f / 255.0f)) * alpha, srgb_to_linear((float)((val >> 8) & 0xFF) * (1.0f / 255.0f)) * alpha,
+				srgb_to_linear((float)((val >> 16) & 0xFF) * (1.0f / 255.0f)) * alpha, alpha};
+		}
+		case 2: {
+			const uint16_t* p = (const uint16_t*)m.pixels + idx * 4;
+			return {(float)nbits_to_half(p[0]), (float)nbits_to_half(p[1]), (float)nbits_to_half(p[2]), (float)nbits_to_half(p[3])};
+		}
+		case 3: {
+			const float* p = (const float*)m.pixels + idx * 4;
+			return {p[0], p[1], p[2], p[3]};
+		}
+		default: return {5.0f, 0.0f, 0.0f, 1.0f};
+	}
+}
+
+void opencv_lens_distortion_delta(const float* p, float u, float v, float* du, float* dv) {
+	const float k1 = p[0], k2 = p[1], p1 = p[2], p2 = p[3];
+	const float u2 = u * u, uv = u * v, v2 = v * v, r2 = u2 + v2;
+	const float radial = k1 * r2 + k2 * r2 * r2;
+	*du = u * radial + 2.0f * p1 * uv + p2 * (r2 + 2.0f * u2);
+	*dv = v * radial + 2.0f * p2 * uv + p1 * (r2 + 2.0f * v2);
+}
+void iterative_opencv_lens_undistortion(const float* params, float* u, float* v) {
+	const float kMaxStepNorm = 1e-10f, kRelStepSize = 1e-6f;
+	const float x0 = *u, y0 = *v;
+	float x = x0, y = y0;
+	for (uint32_t i = 0; i < 100; ++i) {
+		const float step0 = fmaxf(FLT_EPSILON, fabsf(kRelStepSize * x));
+		const float step1 = fmaxf(FLT_EPSILON, fabsf(kRelStepSize * y));
+		float dx0, dx1, b00, b01, f00, f01, b10, b11, f10, f11;
+		opencv_lens_distortion_delta(params, x, y, &dx0, &dx1);
+		opencv_lens_distortion_delta(params, x - step0, y, &b00, &b01);
+		opencv_lens_distortion_delta(params, x + step0, y, &f00, &f01);
+		opencv_lens_distortion_delta(params, x, y - step1, &b10, &b11);
+		opencv_lens_distortion_delta(params, x, y + step1, &f10, &f11);
+		const float j00 = 1 + (f00 - b00) / (2 * step0);
+		const float j10 = (f10 - b10) / (2 * step1);
+		const float j01 = (f01 - b01) / (2 * step0);
+		const float j11 = 1 + (f11 - b11) / (2 * step1);
+		const float rx = x + dx0 - x0, ry = y + dx1 - y0;
+		const float det = j00 * j11 - j10 * j01;
+		const float sx = (j11 * rx - j10 * ry) / det;
+		const float sy = (-j01 * rx + j00 * ry) / det;
+		x -= sx;
+		y -= sy;
+		if (sx * sx + sy * sy < kMaxStepNorm) break;
+	}
+	*u = x;
+	*v = y;
+}
+struct Cam { V c[4]; };
+Cam cam_of(const oracle_nerf_image& m) {
+	Cam c;
+	for (int k = 0; k < 4; ++k) c.c[k] = {m.xform[3 * k + 0], m.xform[3 * k + 1], m.xform[3 * k + 2]};
+	return c;
+}
+void uv_to_ray(float u, float v, const oracle_nerf_image& m, V& origin, V& dir) {
+	const Cam cam = cam_of(m);
+	V d = {(u - m.principal_x) * (float)m.res_x / m.focal_x, (v - m.principal_y) * (float)m.res_y / m.focal_y, 1.0f};
+	if (m.lens_mode == 1) iterative_opencv_lens_undistortion(m.lens_params, &d.x, &d.y);
+	dir = cam.c[0] * d.x + cam.c[1] * d.y + cam.c[2] * d.z;
+	origin = cam.c[3];
+}
+uint32_t image_idx(uint32_t base_idx, uint32_t n_rays, uint32_t n_images) {
+	return (uint32_t)((uint32_t)(base_idx * n_images) / n_rays) % n_images;
+}
+void random_image_pos(OraclePcg32& rng, int res_x, int res_y, bool snap, float& u, float& v) {
+	u = rng.next_float();
+	v = rng.next_float();
+	if (snap) {
+		u = ((float)clampi((int)(u * (float)res_x), 0, res_x - 1) + 0.5f) / (float)res_x;
+		v = ((float)clampi((int)(v * (float)res_y), 0, res_y - 1) + 0.5f) / (float)res_y;
+	}
+}
+OraclePcg32 rng_of(const uint64_t* s) {
+	OraclePcg32 r;
+	r.state = s[0];
+	r.inc = s[1];
+	return r;
+}
+Box box_of(const oracle_nerf_config& c) { return {{c.aabb_min[0], c.aabb_min[1], c.aabb_min[2]}, {c.aabb_max[0], c.aabb_max[1], c.aabb_max[2]}}; }
+
+} // namespace
+
+// generate_training_samples_nerf for rays [0, n_rays): numsteps[i] (0 = no samples), rays [i][6] and
+// the samples of ray i appended in ray order to coords [..][7] (up to max_samples rows). Returns the
+// total number of samples over all rays (may exceed max_samples; rows beyond it are not written).
+extern "C" uint64_t oracle_nerf_generate_samples(const oracle_nerf_config* cfg, const oracle_nerf_image* images, const uint8_t* bitfield,
+	const uint64_t* rng_state, uint32_t* numsteps, float* rays, float* coords, uint64_t max_samples)
+{
+	const Box aabb = box_of(*cfg);
+	uint64_t total = 0;
+	for (uint32_t i = 0; i < cfg->n_rays; ++i) {
+		numsteps[i] = 0;
+		const uint32_t img = image_idx(i, cfg->n_rays, cfg->n_training_images);
+		const oracle_nerf_image& m = images[img];
+		OraclePcg32 rng = rng_of(rng_state);
+		rng.advance((int64_t)i * MAX_RANDOM_SAMPLES_PER_RAY);
+		float u, v;
+		random_image_pos(rng, m.res_x, m.res_y, cfg->snap_to_pixel_centers != 0, u, v);
+		if (read_rgba(u, v, m).r < 0.0f) continue;
+		rng.next_float(); // motionblur_time
+		V o, d;
+		uv_to_ray(u, v, m, o, d);
+		if (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) { const Cam c = cam_of(m); o = c.c[3]; d = c.c[2]; }
+		const V dn = normalize(d);
+		float tmin, tmax;
+		ray_intersect(aabb, o, dn, tmin, tmax);
+		tmin = fmaxf(tmin, 0.0f);
+		const float cone_angle = cfg->cone_angle_constant;
+		const float startt = advance_n_steps(tmin, cone_angle, rng.next_float());
+		const V idir = V{1.0f, 1.0f, 1.0f} / dn;
+		uint32_t j = 0;
+		float t = startt;
+		V pos;
+		while (contains(aabb, pos = o + t * dn) && j < NERF_STEPS) {
+			const float dt = calc_dt(t, cone_angle);
+			const uint32_t mip = mip_from_dt(dt, pos, cfg->max_mip);
+			if (occupied_at(pos, bitfield, mip)) { ++j; t += dt; }
+			else t = advance_to_next_voxel(t, cone_angle, pos, dn, idir, mip);
+		}
+		if (j == 0) continue;
+		numsteps[i] = j;
+		float* r = rays + (size_t)i * 6;
+		r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = d.x; r[4] = d.y; r[5] = d.z;
+		const V wdir = (dn + 1.0f) * 0.5f;
+		t = startt;
+		uint32_t k = 0;
+		while (contains(aabb, pos = o + t * dn) && k < j) {
+			const float dt = calc_dt(t, cone_angle);
+			const uint32_t mip = mip_from_dt(dt, pos, cfg->max_mip);
+			if (occupied_at(pos, bitfield, mip)) {
+				if (total + k < max_samples) {
+					const V wp = (pos - aabb.min) / diag(aabb);
+					float* c = coords + (size_t)(total + k) * 7;
+					c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt); c[4] = wdir.x; c[5] = wdir.y; c[6] = wdir.z;
+				}
+				++k;
+				t += dt;
+			} else {
+				t = advance_to_next_voxel(t, cone_angle, pos, dn, idir, mip);
+			}
+		}
+		total += j;
+	}
+	return total;
+}
+
+namespace {
+inline float logistic(float x) { return 1.0f / (1.0f + expf(-x)); }
+inline float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
+float net_to_rgb(float v, int act) {
+	switch (act) { case 1: return v > 0 ? v : 0; case 2: return logistic(v); case 3: return expf(clampf(v, -10.0f, 10.0f)); default: return v; }
+}
+float net_to_rgb_d(float v, int act) {
+	switch (act) { case 1: return v > 0 ? 1.0f : 0.0f; case 2: { float d = logistic(v); return d * (1 - d); } case 3: return expf(clampf(v, -10.0f, 10.0f)); default: return 1.0f; }
+}
+float net_to_density(float v, int act) {
+	switch (act) { case 1: return v > 0 ? v : 0; case 2: return logistic(v); case 3: return expf(v); default: return v; }
+}
+float net_to_density_d(float v, int act) {
+	switch (act) { case 1: return v > 0 ? 1.0f : 0.0f; case 2: { float d = logistic(v); return d * (1 - d); } case 3: return expf(clampf(v, -15.0f, 15.0f)); default: return 1.0f; }
+}
+void loss1(float target, float pred, int type, float& loss, float& grad) {
+	const float d = pred - target;
+	switch (type) {
+		case 6: { const float den = pred * pred + 1e-2f; loss = d * d / den; grad = 2.0f * d / den; } break;
+		case 1: loss = fabsf(d); grad = copysignf(1.0f, d); break;
+		case 2: { const float den = fabsf(pred) + 1e-2f; loss = fabsf(d) / den; grad = copysignf(1.0f / den, d); } break;
+		case 3: { const float den = 0.5f * (fabsf(pred) + fabsf(target)) + 1e-2f; loss = fabsf(d) / den; grad = copysignf(1.0f / den, d); } break;
+		case 4: {
+			const float alpha = 0.1f, ad = fabsf(d), sq = 0.5f / alpha * d * d;
+			loss = (ad > alpha ? (ad - 0.5f * alpha) : sq) / 5.0f;
+			grad = (ad > alpha ? (d > 0 ? 1.0f : -1.0f) : (d / alpha)) / 5.0f;
+		} break;
+		case 5: { const float div = fabsf(d) + 1.0f; loss = logf(div); grad = copysignf(1.0f / div, d); } break;
+		default: loss = d * d; grad = 2.0f * d; break;
+	}
+}
+} // namespace
+
+extern "C" void oracle_nerf_compute_loss(const oracle_nerf_config* cfg, const oracle_nerf_image* images, float mean_density, uint32_t n_active,
+	const uint32_t* ray_indices, const uint32_t* numsteps_in, const float* rays, const float* coords, const uint16_t* rgbsigma,
+	const uint64_t* rng_state, uint32_t* compacted_numsteps_out, float* loss_out, float* dloss)
+{
+	const Box aabb = box_of(*cfg);
+	for (uint32_t i = 0; i < n_active; ++i) {
+		const uint32_t numsteps = numsteps_in[i * 2 + 0], base = numsteps_in[i * 2 + 1];
+		const float* c_in = coords + (size_t)base * 7;
+		const uint16_t* out = rgbsigma + (size_t)base * 4;
+		float T = 1.f;
+		const float EPSILON = 1e-4f;
+		V rgb_ray = {0, 0, 0};
+		const V ray_o = {rays[(size_t)i * 6 + 0], rays[(size_t)i * 6 + 1], rays[(size_t)i * 6 + 2]};
+		uint32_t compacted = 0;
+		for (; compacted < numsteps; ++compacted) {
+			if (T < EPSILON) break;
+			const float o[4] = {(float)nbits_to_half(out[compacted * 4 + 0]), (float)nbits_to_half(out[compacted * 4 + 1]), (float)nbits_to_half(out[compacted * 4 + 2]), (float)nbits_to_half(out[compacted * 4 + 3])};
+			const V rgb = {net_to_rgb(o[0], cfg->rgb_activation), net_to_rgb(o[1], cfg->rgb_activation), net_to_rgb(o[2], cfg->rgb_activation)};
+			const float dt = unwarp_dt(c_in[(size_t)compacted * 7 + 3]);
+			const float density = net_to_density(o[3], cfg->density_activation);
+			const float alpha = 1.f - expf(-density * dt);
+			const float weight = alpha * T;
+			rgb_ray = rgb_ray + weight * rgb;
+			T *= (1.f - alpha);
+		}
+		const uint32_t ray_idx = ray_indices[i];
+		OraclePcg32 rng = rng_of(rng_state);
+		rng.advance((int64_t)ray_idx * MAX_RANDOM_SAMPLES_PER_RAY);
+		const uint32_t img = image_idx(ray_idx, cfg->n_rays, cfg->n_training_images);
+		const oracle_nerf_image& m = images[img];
+		float u, v;
+		random_image_pos(rng, m.res_x, m.res_y, cfg->snap_to_pixel_centers != 0, u, v);
+		rng.advance(1);
+		V bg = {cfg->background_color[0], cfg->background_color[1], cfg->background_color[2]};
+		if (cfg->random_bg_color) { bg.x = rng.next_float(); bg.y = rng.next_float(); bg.z = rng.next_float(); }
+		bg = {srgb_to_linear(bg.x), srgb_to_linear(bg.y), srgb_to_linear(bg.z)};
+		const Rgba tex = read_rgba(u, v, m);
+		const V tex_rgb = {tex.r, tex.g, tex.b};
+		V target;
+		if (cfg->linear_colors || cfg->color_space == 0) {
+			target = tex_rgb + (1.0f - tex.a) * bg;
+			if (!cfg->linear_colors) {
+				target = {linear_to_srgb(target.x), linear_to_srgb(target.y), linear_to_srgb(target.z)};
+				bg = {linear_to_srgb(bg.x), linear_to_srgb(bg.y), linear_to_srgb(bg.z)};
+			}
+		} else {
+			bg = {linear_to_srgb(bg.x), linear_to_srgb(bg.y), linear_to_srgb(bg.z)};
+			if (tex.a > 0) {
+				const V t = tex_rgb / tex.a;
+				target = V{linear_to_srgb(t.x), linear_to_srgb(t.y), linear_to_srgb(t.z)} * tex.a + (1.0f - tex.a) * bg;
+			} else target = bg;
+		}
+		if (compacted == numsteps) rgb_ray = rgb_ray + T * bg;
+		compacted_numsteps_out[i] = compacted;
+		loss_out[i] = 0.0f;
+		if (compacted == 0) continue;
+		V l, g;
+		loss1(target.x, rgb_ray.x, cfg->loss_type, l.x, g.x);
+		loss1(target.y, rgb_ray.y, cfg->loss_type, l.y, g.y);
+		loss1(target.z, rgb_ray.z, cfg->loss_type, l.z, g.z);
+		loss_out[i] = ((l.x + l.y + l.z) / 3.0f) / (float)cfg->n_rays;
+		const float loss_scale = cfg->loss_scale / (float)cfg->n_rays;
+		const float output_l2_reg = cfg->rgb_activation == 3 ? 1e-4f : 0.0f;
+		const float output_l1_reg_density = mean_density < MIN_OPTICAL_THICKNESS ? 1e-4f : 0.0f;
+		V rgb_ray2 = {0, 0, 0};
+		T = 1.f;
+		for (uint32_t j = 0; j < compacted; ++j) {
+			const float* c = c_in + (size_t)j * 7;
+			const V pos = aabb.min + V{c[0], c[1], c[2]} * diag(aabb);
+			const float depth = length(pos - ray_o);
+			const float dt = unwarp_dt(c[3]);
+			const float o[4] = {(float)nbits_to_half(out[j * 4 + 0]), (float)nbits_to_half(out[j * 4 + 1]), (float)nbits_to_half(out[j * 4 + 2]), (float)nbits_to_half(out[j * 4 + 3])};
+			const V rgb = {net_to_rgb(o[0], cfg->rgb_activation), net_to_rgb(o[1], cfg->rgb_activation), net_to_rgb(o[2], cfg->rgb_activation)};
+			const float density = net_to_density(o[3], cfg->density_activation);
+			const float alpha = 1.f - expf(-density * dt);
+			const float weight = alpha * T;
+			rgb_ray2 = rgb_ray2 + weight * rgb;
+			T *= (1.f - alpha);
+			const V suffix = rgb_ray - rgb_ray2;
+			const V dl = weight * g;
+			float* d = dloss + (size_t)(base + j) * 4;
+			d[0] = loss_scale * (dl.x * net_to_rgb_d(o[0], cfg->rgb_activation) + fmaxf(0.0f, output_l2_reg * o[0]));
+			d[1] = loss_scale * (dl.y * net_to_rgb_d(o[1], cfg->rgb_activation) + fmaxf(0.0f, output_l2_reg * o[1]));
+			d[2] = loss_scale * (dl.z * net_to_rgb_d(o[2], cfg->rgb_activation) + fmaxf(0.0f, output_l2_reg * o[2]));
+			const float dd = net_to_density_d(o[3], cfg->density_activation);
+			const float dmlp = dd * (dt * dot(g, T * rgb - suffix));
+			d[3] = loss_scale * dmlp + (o[3] < 0.0f ? -output_l1_reg_density : 0.0f) + (o[3] > -10.0f && depth < cfg->near_distance ? 1e-4f : 0.0f);
+		}
+	}
+}
+
+extern "C" void oracle_nerf_bitfield(uint32_t max_cascade, const float* grid, uint8_t* bitfield, float* mean_density) {
+	double sum = 0.0;
+	for (uint32_t i = 0; i < GRID_CELLS; ++i) sum += (double)(fmaxf(grid[i], 0.f) / (float)GRID_CELLS);
+	const float mean = (float)sum;
+	*mean_density = mean;
+	const float thresh = fminf(MIN_OPTICAL_THICKNESS, mean);
+	const uint32_t n = GRID_CELLS / 8 * CASCADES, n_nonzero = GRID_CELLS / 8 * (max_cascade + 1);
+	for (uint32_t i = 0; i < n; ++i) {
+		if (i >= n_nonzero) { bitfield[i] = 0; continue; }
+		uint8_t bits = 0;
+		for (uint8_t j = 0; j < 8; ++j) bits |= grid[(size_t)i * 8 + j] > thresh ? ((uint8_t)1 << j) : 0;
+		bitfield[i] = bits;
+	}
+	for (uint32_t level = 1; level < CASCADES; ++level) {
+		const uint8_t* prev = bitfield + (size_t)GRID_CELLS * (level - 1) / 8;
+		uint8_t* next = bitfield + (size_t)GRID_CELLS * level / 8;
+		for (uint32_t i = 0; i < GRID_CELLS / 64; ++i) {
+			uint8_t bits = 0;
+			for (uint8_t j = 0; j < 8; ++j) bits |= prev[(size_t)i * 8 + j] > 0 ? ((uint8_t)1 << j) : 0;
+			const uint32_t x = morton3D_invert(i >> 0) + GRIDSIZE / 8, y = morton3D_invert(i >> 1) + GRIDSIZE / 8, z = morton3D_invert(i >> 2) + GRIDSIZE / 8;
+			next[morton3D(x, y, z)] |= bits;
+		}
+	}
+}
+
+extern "C" float oracle_det_logf(float x) { return c_logf(x); }
+extern "C" float oracle_det_expf(float x) { return c_expf(x); }
+extern "C" float oracle_advance_n_steps(float t, float cone_angle, float n) { return advance_n_steps(t, cone_angle, n); }
+extern "C" uint32_t oracle_morton3d(uint32_t x, uint32_t y, uint32_t z) { return morton3D(x, y, z); }
+extern "C" uint32_t oracle_morton3d_invert(uint32_t x) { return morton3D_invert(x); }

@@ -83,6 +83,43 @@ void oracle_sh_encode(uint32_t n, uint32_t degree, const float* dirs, uint32_t d
 void oracle_pcg32_seed(uint64_t seed, uint64_t* rng_state);
 void oracle_pcg32_advance(uint64_t* rng_state, int64_t delta);
 
+/* ---- NeRF driver kernels (nerf_oracle.cpp) ------------------------------------------------------- */
+typedef struct {
+	const void* pixels;          /* HOST pixels */
+	int image_data_type;         /* 1 Byte, 2 Half, 3 Float */
+	int lens_mode;               /* 0 Perspective, 1 OpenCV */
+	float lens_params[7];
+	int res_x, res_y;
+	float principal_x, principal_y;
+	float focal_x, focal_y;
+	float xform[12];             /* column-major 4 x 3 */
+} oracle_nerf_image;
+typedef struct {
+	float aabb_min[3], aabb_max[3];
+	uint32_t n_rays, n_rays_total, max_samples, max_samples_compacted, n_training_images, max_mip;
+	float cone_angle_constant, near_distance, loss_scale;
+	int snap_to_pixel_centers, random_bg_color, linear_colors, color_space, loss_type, rgb_activation, density_activation;
+	float background_color[3];
+} oracle_nerf_config;
+/* generate_training_samples_nerf (src/testbed_nerf.cu:679-838), rays in index order. */
+uint64_t oracle_nerf_generate_samples(const oracle_nerf_config* cfg, const oracle_nerf_image* images, const uint8_t* bitfield,
+	const uint64_t* rng_state, uint32_t* numsteps, float* rays, float* coords, uint64_t max_samples);
+/* compute_loss_kernel_train_nerf (src/testbed_nerf.cu:841-1160) for n_active rays given as
+ * (ray_indices, numsteps_in {count, base}, rays, coords, rgbsigma fp16 [..][4]). Outputs per ray:
+ * compacted sample count and loss; per INPUT sample (base + j): dL/d(rgb sigma) as float [..][4]. */
+void oracle_nerf_compute_loss(const oracle_nerf_config* cfg, const oracle_nerf_image* images, float mean_density, uint32_t n_active,
+	const uint32_t* ray_indices, const uint32_t* numsteps_in, const float* rays, const float* coords, const uint16_t* rgbsigma,
+	const uint64_t* rng_state, uint32_t* compacted_numsteps, float* loss, float* dloss);
+/* grid_to_bitfield + bitfield_max_pool + mean (src/testbed_nerf.cu:284-331, 2362-2379). */
+void oracle_nerf_bitfield(uint32_t max_cascade, const float* grid, uint8_t* bitfield, float* mean_density);
+/* deterministic log / exp used by the stepping (Cephes single precision) */
+float oracle_det_logf(float x);
+float oracle_det_expf(float x);
+/* advance_n_steps / calc_dt (nerf_device.cuh:414-424) */
+float oracle_advance_n_steps(float t, float cone_angle, float n);
+uint32_t oracle_morton3d(uint32_t x, uint32_t y, uint32_t z);
+uint32_t oracle_morton3d_invert(uint32_t x);
+
 /* fp16 <-> fp32 (round to nearest even), exposed so tests can build fp16 inputs. */
 uint16_t oracle_float_to_half(float f);
 float oracle_half_to_float(uint16_t h);

@@ -243,3 +243,99 @@ def nerf_backward(grid_cfg_, fwd, coords, dL_dout_f16, n_hidden_density, n_hidde
     dx0, dWd = mlp_backward(fwd["wd"], fwd["x0"], fwd["hd"], g_den, n_hidden_density)
     gg = grid_backward(grid_cfg_, coords[:, :3], dx0)
     return dWd, dWr, gg, dx0
+
+
+# ---- NeRF driver kernels (oracle/nerf_oracle.cpp) -------------------------------------------------
+class NerfImage(ctypes.Structure):
+    """oracle_nerf_image == ngpb_nerf_image_t (same layout; pixels host vs device)."""
+    _fields_ = [("pixels", ctypes.c_void_p), ("image_data_type", ctypes.c_int), ("lens_mode", ctypes.c_int), ("lens_params", ctypes.c_float * 7),
+                ("res_x", ctypes.c_int), ("res_y", ctypes.c_int), ("principal_x", ctypes.c_float), ("principal_y", ctypes.c_float),
+                ("focal_x", ctypes.c_float), ("focal_y", ctypes.c_float), ("xform", ctypes.c_float * 12)]
+
+
+class NerfConfig(ctypes.Structure):
+    """oracle_nerf_config == ngpb_nerf_train_config_t."""
+    _fields_ = [("aabb_min", ctypes.c_float * 3), ("aabb_max", ctypes.c_float * 3),
+                ("n_rays", ctypes.c_uint32), ("n_rays_total", ctypes.c_uint32), ("max_samples", ctypes.c_uint32), ("max_samples_compacted", ctypes.c_uint32),
+                ("n_training_images", ctypes.c_uint32), ("max_mip", ctypes.c_uint32),
+                ("cone_angle_constant", ctypes.c_float), ("near_distance", ctypes.c_float), ("loss_scale", ctypes.c_float),
+                ("snap_to_pixel_centers", ctypes.c_int), ("random_bg_color", ctypes.c_int), ("linear_colors", ctypes.c_int), ("color_space", ctypes.c_int),
+                ("loss_type", ctypes.c_int), ("rgb_activation", ctypes.c_int), ("density_activation", ctypes.c_int), ("background_color", ctypes.c_float * 3)]
+
+
+class NerfBuffers(ctypes.Structure):
+    """ngpb_nerf_train_buffers_t (device pointers)."""
+    _fields_ = [(n, ctypes.c_void_p) for n in ("metadata", "density_bitfield", "mean_density", "counters", "ray_indices", "rays_unnormalized",
+                                               "numsteps", "coords", "rgbsigma", "coords_compacted", "dloss_doutput", "loss")]
+
+
+olib.oracle_nerf_generate_samples.restype = ctypes.c_uint64
+olib.oracle_det_logf.restype = ctypes.c_float
+olib.oracle_det_logf.argtypes = [ctypes.c_float]
+olib.oracle_det_expf.restype = ctypes.c_float
+olib.oracle_det_expf.argtypes = [ctypes.c_float]
+olib.oracle_advance_n_steps.restype = ctypes.c_float
+olib.oracle_advance_n_steps.argtypes = [ctypes.c_float, ctypes.c_float, ctypes.c_float]
+olib.oracle_morton3d.restype = ctypes.c_uint32
+olib.oracle_morton3d.argtypes = [ctypes.c_uint32] * 3
+olib.oracle_morton3d_invert.restype = ctypes.c_uint32
+olib.oracle_morton3d_invert.argtypes = [ctypes.c_uint32]
+
+
+def nerf_image(pixels_np, xform_3x4, focal, principal=(0.5, 0.5), lens=None):
+    """Host-side image record; keeps the pixel array alive. xform_3x4 row-major [3][4] NGP convention."""
+    px = np.ascontiguousarray(pixels_np)
+    kind = {np.dtype(np.uint8): 1, np.dtype(np.float16): 2, np.dtype(np.float32): 3}[px.dtype]
+    im = NerfImage()
+    im._keep = px
+    im.pixels = px.ctypes.data
+    im.image_data_type = kind
+    im.lens_mode = 1 if lens is not None and any(float(v) != 0.0 for v in lens) else 0
+    for k in range(7):
+        im.lens_params[k] = float(lens[k]) if lens is not None and k < len(lens) else 0.0
+    im.res_x, im.res_y = px.shape[1], px.shape[0]
+    im.principal_x, im.principal_y = principal
+    im.focal_x, im.focal_y = (focal, focal) if np.isscalar(focal) else focal
+    x = np.asarray(xform_3x4, dtype=np.float32)
+    for c in range(4):
+        for r in range(3):
+            im.xform[3 * c + r] = float(x[r, c])
+    return im
+
+
+def nerf_generate_samples(cfg, images, bitfield, rng, max_samples):
+    """Returns (numsteps [n_rays], rays [n_rays][6], coords [total][7], total) in ray-index order."""
+    arr = (NerfImage * len(images))(*images)
+    numsteps = np.zeros(cfg.n_rays, dtype=np.uint32)
+    rays = np.zeros((cfg.n_rays, 6), dtype=np.float32)
+    coords = np.zeros((max_samples, 7), dtype=np.float32)
+    bf = np.ascontiguousarray(bitfield, dtype=np.uint8)
+    total = olib.oracle_nerf_generate_samples(ctypes.byref(cfg), arr, _p(bf, ctypes.c_uint8), _p(rng.arr, ctypes.c_uint64),
+                                              _p(numsteps, ctypes.c_uint32), _p(rays, ctypes.c_float), _p(coords, ctypes.c_float), ctypes.c_uint64(max_samples))
+    return numsteps, rays, coords[:min(total, max_samples)], int(total)
+
+
+def nerf_compute_loss(cfg, images, mean_density, ray_indices, numsteps_in, rays, coords, rgbsigma_f16, rng):
+    """Returns (compacted_numsteps [n], loss [n], dloss [n_samples][4] float32 indexed by input sample)."""
+    arr = (NerfImage * len(images))(*images)
+    n = len(ray_indices)
+    ri = np.ascontiguousarray(ray_indices, dtype=np.uint32)
+    ns = np.ascontiguousarray(numsteps_in, dtype=np.uint32)
+    ry = np.ascontiguousarray(rays, dtype=np.float32)
+    co = np.ascontiguousarray(coords, dtype=np.float32)
+    out = np.ascontiguousarray(rgbsigma_f16, dtype=np.float16)
+    comp = np.zeros(n, dtype=np.uint32)
+    loss = np.zeros(n, dtype=np.float32)
+    dloss = np.zeros((co.shape[0], 4), dtype=np.float32)
+    olib.oracle_nerf_compute_loss(ctypes.byref(cfg), arr, ctypes.c_float(mean_density), ctypes.c_uint32(n), _p(ri, ctypes.c_uint32), _p(ns, ctypes.c_uint32),
+                                  _p(ry, ctypes.c_float), _p(co, ctypes.c_float), _p(out.view(np.uint16), ctypes.c_uint16), _p(rng.arr, ctypes.c_uint64),
+                                  _p(comp, ctypes.c_uint32), _p(loss, ctypes.c_float), _p(dloss, ctypes.c_float))
+    return comp, loss, dloss
+
+
+def nerf_bitfield(max_cascade, grid):
+    g = np.ascontiguousarray(grid, dtype=np.float32)
+    bf = np.zeros(128 ** 3 * 8 // 8, dtype=np.uint8)
+    mean = ctypes.c_float()
+    olib.oracle_nerf_bitfield(ctypes.c_uint32(max_cascade), _p(g, ctypes.c_float), _p(bf, ctypes.c_uint8), ctypes.byref(mean))
+    return bf, mean.value
