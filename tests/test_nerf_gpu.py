@@ -137,11 +137,11 @@ def test_training_samples_bit_exact(ngp, oracle, aabb_scale, lens, n_rays):
     assert numsteps[order[0], 1] == 0
     assert np.array_equal(numsteps[order, 1][1:], np.cumsum(numsteps[order, 0])[:-1])
     # coordinates and rays: bit-exact, ray by ray
-    want_base = np.concatenate([[0], np.cumsum(want_n)])[:-1]
+    want_base = np.concatenate([[0], np.cumsum(want_n.astype(np.int64))])[:-1].astype(np.int64)
     coords = dev.coords.cpu().numpy()
     rays = dev.rays.cpu().numpy()
     for k in range(kept):
-        i, n, b = ray_indices[k], numsteps[k, 0], numsteps[k, 1]
+        i, n, b = int(ray_indices[k]), int(numsteps[k, 0]), int(numsteps[k, 1])
         got = coords[b:b + n].view(np.uint32)
         want = want_coords[want_base[i]:want_base[i] + n].view(np.uint32)
         assert np.array_equal(got, want), (k, i)
@@ -198,7 +198,7 @@ def test_loss_and_gradients_match_oracle(ngp, oracle, aabb_scale, loss_type, rgb
     got_c = dev.coords_compacted.cpu().numpy()
     scale = np.abs(dloss).max()
     for k in range(kept):
-        n, cb, b = comp[k], got_ns[k, 1], numsteps_in[k, 1]
+        n, cb, b = int(comp[k]), int(got_ns[k, 1]), int(numsteps_in[k, 1])
         assert np.array_equal(got_c[cb:cb + n].view(np.uint32), coords[b:b + n].view(np.uint32))
         want = dloss[b:b + n]
         tol = 2e-3 * np.abs(want) + 2.0 ** -10 * np.abs(want) + 1e-4 * scale + 6e-8
