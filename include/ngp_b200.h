@@ -39,6 +39,12 @@ uint32_t ngpb_batch_size_granularity(void);
 /* tcnn::cpp::default_loss_scale(), cpp_api.h:75; tcnn common.h:232 (128 for fp16). */
 float ngpb_default_loss_scale(int precision);
 
+/* ---- phase timer (no reference counterpart; the reference keeps wall-clock EMAs, testbed.h:936-940) ----
+ * When enabled, the library brackets its kernel groups with CUDA events on the calling thread.
+ * ngpb_profile_collect writes "name=total_ms:count;..." (call after synchronising the stream). */
+void ngpb_profile_enable(int on);
+size_t ngpb_profile_collect(char* buf, size_t cap, int reset);
+
 /* ---- module factories -----------------------------------------------------------------
  * tcnn::cpp::create_encoding / create_network_with_input_encoding / create_network,
  * cpp_api.h:117-119, implemented at tcnn/src/cpp_api.cu:140-165. JSON strings use the tcnn
@@ -193,6 +199,8 @@ int ngpb_testbed_set_nerf_image(ngpb_testbed_t* t, uint32_t idx, const void* pix
 /* xform_3x4: camera-to-world in NGP convention, row-major [3][4]. */
 int ngpb_testbed_set_nerf_camera(ngpb_testbed_t* t, uint32_t idx, const float* xform_3x4, float focal_x, float focal_y,
 	float principal_x, float principal_y, int lens_mode, const float* lens_params);
+/* The stream every call of this testbed runs on (default: an internal non-blocking stream). */
+int ngpb_testbed_set_stream(ngpb_testbed_t* t, void* stream);
 int ngpb_testbed_reload_network_from_json(ngpb_testbed_t* t, const char* config_json);
 int ngpb_testbed_reset_network(ngpb_testbed_t* t, int clear_density_grid);
 /* Testbed::train(batch_size), src/testbed.cu:4020-4109. */

@@ -78,6 +78,9 @@ SIGNATURES = {
     "ngpb_nerf_compute_loss_and_compact": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(c_u64)]),
     "ngpb_nerf_update_bitfield": (c_int, [c_vp, c_u32, c_vp, c_vp, c_vp]),
     "ngpb_nerf_bitfield_bytes": (c_sz, []),
+    "ngpb_profile_enable": (None, [c_int]),
+    "ngpb_profile_collect": (c_sz, [c_cp, c_sz, c_int]),
+    "ngpb_testbed_set_stream": (c_int, [c_vp, c_vp]),
     "ngpb_testbed_create": (c_int, [ctypes.POINTER(c_vp)]),
     "ngpb_testbed_free": (None, [c_vp]),
     "ngpb_testbed_create_empty_nerf_dataset": (c_int, [c_vp, c_u32, c_int, c_int]),

@@ -44,6 +44,16 @@ int ngpb_testbed_create(ngpb_testbed_t** out) {
 }
 void ngpb_testbed_free(ngpb_testbed_t* t) { delete t; }
 
+void ngpb_profile_enable(int on) { prof_enable(on != 0); }
+size_t ngpb_profile_collect(char* buf, size_t cap, int reset) {
+	try { return copy_out(prof_collect(reset != 0), buf, cap); } catch (...) { return 0; }
+}
+int ngpb_testbed_set_stream(ngpb_testbed_t* t, void* stream) {
+	NGPB_API_BEGIN
+	t->impl->set_stream((cudaStream_t)stream);
+	NGPB_API_END
+}
+
 int ngpb_testbed_create_empty_nerf_dataset(ngpb_testbed_t* t, uint32_t n_images, int aabb_scale, int is_hdr) {
 	NGPB_API_BEGIN
 	t->impl->create_empty_nerf_dataset(n_images, aabb_scale, is_hdr != 0);

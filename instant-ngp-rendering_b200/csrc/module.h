@@ -81,6 +81,16 @@ public:
 // tcnn random.h:39-73, same element -> stream-position mapping.
 void random_uniform(cudaStream_t stream, Pcg32& rng, size_t n, float* out, float lower, float upper);
 
+// ---- phase timer -----------------------------------------------------------------------------
+// When enabled (ngpb_profile_enable), prof_mark(stream, name) records a CUDA event; the time
+// between a mark and the next one on the same thread is charged to the FIRST mark's name when
+// prof_collect() runs (after a stream synchronisation). Disabled: a branch and nothing else.
+void prof_enable(bool on);
+bool prof_enabled();
+void prof_mark(cudaStream_t stream, const char* name);
+// Sums pending intervals into the per-name totals; returns "name=ms;name=ms;..." of the totals.
+std::string prof_collect(bool reset);
+
 // params_fp16[i] = (half)params_fp32[i] (tcnn trainer.h:82-85)
 void cast_fp32_to_fp16(cudaStream_t stream, size_t n, const float* src, __half* dst);
 

@@ -285,11 +285,13 @@ void NerfNetworkModule::inference_counted(cudaStream_t stream, uint32_t max_n, c
 	if (max_n == 0) return;
 	if (max_n % kTile != 0) throw std::runtime_error{"ngp-b200 NerfNetwork: batch size must be a multiple of 128"};
 	m_scratch_feat.reserve(tiled_bytes(max_n, m_pos_width), stream);
+	prof_mark(stream, "infer.grid_forward");
 	grid_forward(stream, m_grid.p, max_n, params + pos_encoding_param_offset(), input, in_stride, m_scratch_feat.as<__half>(), m_pos_width, 1.0f, true, n_dev);
 	FusedInferenceArgs a{};
 	a.net = m_net; a.n = max_n; a.n_dev = n_dev; a.params = params; a.feat = m_scratch_feat.as<__half>();
 	a.coords = input; a.coord_stride = in_stride;
 	a.out = output; a.out_stride = out_stride;
+	prof_mark(stream, "infer.fused_mlp");
 	fused_inference(stream, a);
 }
 
@@ -315,6 +317,7 @@ void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const 
 	m_scratch_feat.reserve(tiled_bytes(n, m_pos_width), stream);
 	m_scratch_dfeat.reserve(tiled_bytes(n, m_pos_width), stream);
 	m_scratch_dw.reserve((size_t)grid * n_mlp_params() * sizeof(float), stream);
+	prof_mark(stream, "train.grid_forward");
 	grid_forward(stream, m_grid.p, n, params + pos_encoding_param_offset(), input, in_stride, m_scratch_feat.as<__half>(), m_pos_width, 1.0f, true);
 	FusedTrainArgs a{};
 	a.net = m_net; a.n = n; a.params = params; a.feat = m_scratch_feat.as<__half>();
@@ -323,7 +326,9 @@ void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const 
 	a.dfeat = m_scratch_dfeat.as<__half>();
 	a.dw_partials = m_scratch_dw.as<float>();
 	a.dL_dparams = dL_dparams;
+	prof_mark(stream, "train.fused_mlp_fwd_bwd");
 	fused_train(stream, a);
+	prof_mark(stream, "train.grid_backward");
 	__half* ggrad = dL_dparams + pos_encoding_param_offset();
 	NGPB_CUDA_CHECK(cudaMemsetAsync(ggrad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
 	grid_backward(stream, m_grid.p, n, ggrad, input, in_stride, m_scratch_dfeat.as<__half>(), m_pos_width, 1.0f, true);

@@ -1,12 +1,56 @@
 // Small runtime pieces: error string, SM count, pcg32 fills.
 #include "module.h"
 
+#include <map>
+#include <sstream>
+#include <vector>
+
 namespace ngpb {
 
 static thread_local std::string g_last_error;
 
 void set_last_error(const std::string& msg) { g_last_error = msg; }
 const char* last_error() { return g_last_error.c_str(); }
+
+// ---- phase timer ---------------------------------------------------------------------------------
+namespace {
+struct ProfState {
+	bool enabled = false;
+	std::vector<std::pair<std::string, cudaEvent_t>> marks;
+	std::vector<cudaEvent_t> pool;
+	std::map<std::string, std::pair<double, uint64_t>> totals; // ms, count
+};
+ProfState& prof() { static thread_local ProfState s; return s; }
+}
+void prof_enable(bool on) { prof().enabled = on; }
+bool prof_enabled() { return prof().enabled; }
+void prof_mark(cudaStream_t stream, const char* name) {
+	ProfState& p = prof();
+	if (!p.enabled) return;
+	cudaEvent_t e;
+	if (!p.pool.empty()) { e = p.pool.back(); p.pool.pop_back(); }
+	else NGPB_CUDA_CHECK(cudaEventCreate(&e));
+	NGPB_CUDA_CHECK(cudaEventRecord(e, stream));
+	p.marks.emplace_back(name, e);
+}
+std::string prof_collect(bool reset) {
+	ProfState& p = prof();
+	for (size_t i = 0; i + 1 < p.marks.size(); ++i) {
+		if (p.marks[i].first == "end") continue;
+		float ms = 0.0f;
+		if (cudaEventElapsedTime(&ms, p.marks[i].second, p.marks[i + 1].second) == cudaSuccess) {
+			auto& t = p.totals[p.marks[i].first];
+			t.first += ms;
+			t.second += 1;
+		} else cudaGetLastError();
+	}
+	for (auto& m : p.marks) p.pool.push_back(m.second);
+	p.marks.clear();
+	std::ostringstream o;
+	for (auto& kv : p.totals) o << kv.first << "=" << kv.second.first << ":" << kv.second.second << ";";
+	if (reset) p.totals.clear();
+	return o.str();
+}
 
 int sm_count() {
 	static int count = -1;

@@ -20,14 +20,16 @@ static int loss_type_from_string(const std::string& s) {
 }
 
 Testbed::Testbed() {
-	NGPB_CUDA_CHECK(cudaStreamCreateWithFlags(&m_stream, cudaStreamNonBlocking));
+	NGPB_CUDA_CHECK(cudaStreamCreateWithFlags(&m_own_stream, cudaStreamNonBlocking));
+	m_stream = m_own_stream;
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_counters_host, sizeof(NerfStepCounters)));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_loss_host, sizeof(float)));
 	m_rng = Pcg32{seed};
 }
 
 Testbed::~Testbed() {
-	if (m_stream) cudaStreamSynchronize(m_stream);
+	cudaStreamSynchronize(m_stream);
+	if (m_own_stream) cudaStreamSynchronize(m_own_stream);
 	// stream-ordered buffers must go before the stream
 	m_images.clear();
 	for (DeviceBuffer* b : {&m_params_fp32, &m_params, &m_gradients, &m_metadata_gpu, &m_density_grid, &m_density_grid_tmp, &m_density_bitfield,
@@ -35,9 +37,17 @@ Testbed::~Testbed() {
 			&m_rgbsigma, &m_coords_compacted, &m_dloss, &m_loss, &m_render_scratch}) b->release();
 	m_network.reset();
 	m_optimizer.reset();
-	if (m_stream) { cudaStreamSynchronize(m_stream); cudaStreamDestroy(m_stream); }
+	cudaStreamSynchronize(m_stream);
+	if (m_own_stream) { cudaStreamSynchronize(m_own_stream); cudaStreamDestroy(m_own_stream); }
 	if (m_counters_host) cudaFreeHost(m_counters_host);
 	if (m_loss_host) cudaFreeHost(m_loss_host);
+}
+
+void Testbed::set_stream(cudaStream_t s) {
+	// Buffers are stream-ordered allocations: drain both streams before switching.
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	m_stream = s ? s : m_own_stream;
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
 }
 
 // ---------------------------------------------------------------------------------------------

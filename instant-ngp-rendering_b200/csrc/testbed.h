@@ -58,6 +58,7 @@ public:
 	const ImageMeta* metadata_gpu() const { return m_metadata_gpu.as<ImageMeta>(); }
 	uint32_t n_images() const { return (uint32_t)m_images.size(); }
 	cudaStream_t stream() const { return m_stream; }
+	void set_stream(cudaStream_t s);
 	const Json& network_config() const { return m_network_config; }
 
 	// counters of the last step (NerfCounters)
@@ -102,6 +103,7 @@ private:
 	void train_nerf_step(uint32_t target_batch_size);
 
 	cudaStream_t m_stream = nullptr;
+	cudaStream_t m_own_stream = nullptr;
 	Json m_network_config;
 	std::unique_ptr<NerfNetworkModule> m_network;
 	std::unique_ptr<Optimizer> m_optimizer;

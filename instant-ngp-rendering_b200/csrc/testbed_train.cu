@@ -70,7 +70,10 @@ void Testbed::train(uint32_t batch_size) {
 	upload_metadata();
 
 	const uint32_t n_prep_to_skip = std::min(std::max(m_training_step / 16u, 1u), 16u);
-	if (m_training_step % n_prep_to_skip == 0) training_prep_nerf();
+	if (m_training_step % n_prep_to_skip == 0) {
+		prof_mark(m_stream, "density_grid_update");
+		training_prep_nerf();
+	}
 
 	Json leaf = Json::object();
 	leaf["otype"] = "Adam";
@@ -141,9 +144,11 @@ void Testbed::train_nerf_step(uint32_t target_batch_size) {
 	buf.dloss_doutput = m_dloss.as<__half>();
 	buf.loss = m_loss.as<float>();
 
+	prof_mark(m_stream, "generate_training_samples");
 	nerf_generate_training_samples(m_stream, cfg, buf, m_rng);
 	// network on the training parameters over exactly the generated samples (device-side count)
 	m_network->inference_counted(m_stream, max_samples, &buf.counters->numsteps, m_coords.as<float>(), kCoordFloats, m_rgbsigma.as<__half>(), 4, params());
+	prof_mark(m_stream, "loss_and_compact");
 	nerf_compute_loss_and_compact(m_stream, cfg, buf, m_rng);
 	m_network->backward_strided(m_stream, target_batch_size, m_coords_compacted.as<float>(), kCoordFloats, m_dloss.as<__half>(), 4, gradients(), params());
 	m_rng.advance(1ll << 32);
@@ -151,7 +156,9 @@ void Testbed::train_nerf_step(uint32_t target_batch_size) {
 
 void Testbed::train_nerf(uint32_t target_batch_size, bool get_loss_scalar) {
 	train_nerf_step(target_batch_size);
+	prof_mark(m_stream, "optimizer");
 	m_optimizer->step(m_stream, kLossScaleFp16, params_fp32(), params(), gradients());
+	prof_mark(m_stream, "end");
 	++m_training_step;
 
 	// NerfCounters::update_after_training (:2422-2446)

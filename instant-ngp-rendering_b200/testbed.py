@@ -151,6 +151,10 @@ class Testbed:
         except Exception:
             pass
 
+    def use_current_stream(self):
+        """Run every call on torch's current stream (so that torch CUDA events bracket the work)."""
+        check(lib.ngpb_testbed_set_stream(self._h, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+
     # -- dataset ---------------------------------------------------------------------------------
     def create_empty_nerf_dataset(self, n_images, aabb_scale=1, is_hdr=False):
         check(lib.ngpb_testbed_create_empty_nerf_dataset(self._h, n_images, int(aabb_scale), int(is_hdr)))
@@ -232,3 +236,21 @@ class Testbed:
         check(lib.ngpb_testbed_render_nerf(self._h, width, height, cam.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), fx, fy,
                                            principal[0], principal[1], spp_index, b, e, ctypes.c_void_p(rgba.data_ptr()), ctypes.c_void_p(depth.data_ptr())))
         return rgba, depth
+
+
+def profile_enable(on=True):
+    lib.ngpb_profile_enable(int(on))
+
+
+def profile_collect(reset=True):
+    """{name: (total_ms, count)} of the library's phase timer."""
+    n = lib.ngpb_profile_collect(None, 0, 0)
+    buf = ctypes.create_string_buffer(n + 1)
+    lib.ngpb_profile_collect(buf, n + 1, int(reset))
+    out = {}
+    for item in buf.value.decode().split(";"):
+        if "=" in item:
+            k, v = item.split("=")
+            ms, cnt = v.split(":")
+            out[k] = (float(ms), int(cnt))
+    return out
