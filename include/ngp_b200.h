@@ -224,6 +224,11 @@ int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_
 int ngpb_testbed_render_nerf(ngpb_testbed_t* t, uint32_t width, uint32_t height, const float* camera_3x4, float focal_x, float focal_y,
 	float principal_x, float principal_y, uint32_t spp_index, uint32_t pixel_begin, uint32_t pixel_end, float* rgba, float* depth);
 
+/* Optional DEVICE buffer [height*width] that render_nerf fills with the number of samples composited
+ * per pixel (NerfPayload::n_steps, the value ERenderMode::Cost shows, src/testbed_nerf.cu:1329-1331);
+ * NULL switches it off. Pixels whose ray never enters occupied space are not written. */
+int ngpb_testbed_set_render_steps_out(ngpb_testbed_t* t, uint32_t* steps);
+
 /* ---- self test of the tcgen05 operand views (tc_device.cuh) --------------------------------
  * mode 0: D[128xN] = X[128xK] W[NxK]^T; mode 1: D[128xN] = X[128xK] W[KxN];
  * mode 2: D[64xN] = X[128x64]^T W[128xN]. fp16 row-major inputs, fp32 row-major D (device). */

@@ -91,7 +91,8 @@ int ngpb_testbed_train(ngpb_testbed_t* t, uint32_t batch_size) {
 #define NGPB_PROPS(X) \
 	X(rays_per_batch) X(measured_batch_size) X(measured_batch_size_before_compaction) X(seed) X(random_bg_color) X(linear_colors) \
 	X(snap_to_pixel_centers) X(near_distance) X(density_grid_decay) X(render_min_transmittance) X(loss_type) X(rgb_activation) \
-	X(density_activation) X(color_space) X(train_network) X(train_encoding) X(aabb_scale)
+	X(density_activation) X(color_space) X(train_network) X(train_encoding) X(aabb_scale) \
+	X(render_target_queries) X(render_min_steps) X(render_max_steps) X(render_windows_per_sync) X(render_snap_to_pixel_centers)
 
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
 	NGPB_API_BEGIN
@@ -151,6 +152,12 @@ int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_
 	NGPB_API_BEGIN
 	t->impl->update_density_grid_nerf(decay, n_uniform, n_nonuniform);
 	NGPB_CUDA_CHECK(cudaStreamSynchronize(t->impl->stream()));
+	NGPB_API_END
+}
+
+int ngpb_testbed_set_render_steps_out(ngpb_testbed_t* t, uint32_t* steps) {
+	NGPB_API_BEGIN
+	t->impl->set_render_steps_out(steps);
 	NGPB_API_END
 }
 

@@ -437,4 +437,67 @@ NGPB_HD void random_image_pos_training(Pcg32& rng, int res_x, int res_y, bool sn
 	}
 }
 
+// ---- render-time marching (nerf_device.cuh:461-494) --------------------------------------------
+// if_unoccupied_advance_to_next_occupied_voxel<MIP_FROM_DT=false>: skip to the next occupied cell,
+// climbing to the coarsest empty cascade around the sample first. Returns kMaxDepth once the ray
+// leaves the box (render_aabb == train aabb, identity render_aabb_to_local in the headless path).
+NGPB_HD float advance_to_next_occupied_voxel(float t, const Stepping& s, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bitfield,
+	uint32_t min_mip, uint32_t max_mip, const Aabb& aabb)
+{
+	while (true) {
+		const V3 pos = o + d * t;
+		if (t >= kMaxDepth || !aabb_contains(aabb, pos)) return kMaxDepth;
+		uint32_t mip = mip_from_pos(pos);
+		mip = mip < min_mip ? min_mip : (mip > max_mip ? max_mip : mip);
+		if (density_grid_occupied_at(pos, bitfield, mip)) return t;
+		while (mip < max_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
+		t = advance_to_next_voxel(t, s, pos, d, idir, mip);
+	}
+}
+
+// ---- low-discrepancy values (random_val.cuh:161-327; Burley 2020, "Practical Hash-based Owen
+// Scrambling", JCGT 9(4)). Only Sobol dimensions 0 and 1 are needed: dimension 0 is the bit
+// reversal of the index, the direction numbers of dimension 1 follow v_k = v_{k-1} ^ (v_{k-1} >> 1).
+NGPB_HD uint32_t reverse_bits32(uint32_t x) {
+	x = ((x & 0xaaaaaaaau) >> 1) | ((x & 0x55555555u) << 1);
+	x = ((x & 0xccccccccu) >> 2) | ((x & 0x33333333u) << 2);
+	x = ((x & 0xf0f0f0f0u) >> 4) | ((x & 0x0f0f0f0fu) << 4);
+	x = ((x & 0xff00ff00u) >> 8) | ((x & 0x00ff00ffu) << 8);
+	return (x >> 16) | (x << 16);
+}
+NGPB_HD uint32_t sobol01(uint32_t index, uint32_t dim) {
+	if (dim == 0) return reverse_bits32(index);
+	uint32_t x = 0, v = 0x80000000u;
+	for (uint32_t bit = 0; bit < 32; ++bit) {
+		if ((index >> bit) & 1u) x ^= v;
+		v ^= v >> 1;
+	}
+	return x;
+}
+NGPB_HD uint32_t laine_karras_permutation(uint32_t x, uint32_t seed) {
+	x += seed;
+	x ^= x * 0x6c50b47cu;
+	x ^= x * 0xb82f1e52u;
+	x ^= x * 0xc7afe638u;
+	x ^= x * 0x8d22f6e6u;
+	return x;
+}
+NGPB_HD uint32_t nested_uniform_scramble_base2(uint32_t x, uint32_t seed) {
+	return reverse_bits32(laine_karras_permutation(reverse_bits32(x), seed));
+}
+NGPB_HD uint32_t hash_combine_u32(uint32_t seed, uint32_t v) { return seed ^ (v + (seed << 6) + (seed >> 2)); }
+NGPB_HD float ld_random_val(uint32_t index, uint32_t seed, uint32_t dim = 0) {
+	const float S = 1.0f / 4294967296.0f;
+	index = nested_uniform_scramble_base2(index, seed);
+	return (float)nested_uniform_scramble_base2(sobol01(index, dim), hash_combine_u32(seed, dim)) * S;
+}
+// ld_random_pixel_offset (random_val.cuh:321-326)
+NGPB_HD void ld_random_pixel_offset(uint32_t spp, float& ox, float& oy) {
+	const uint32_t seed = 0xdeadbeefu;
+	ox = 0.5f - ld_random_val(0, seed, 0) + ld_random_val(spp, seed, 0);
+	oy = 0.5f - ld_random_val(0, seed, 1) + ld_random_val(spp, seed, 1);
+	ox -= floorf(ox);
+	oy -= floorf(oy);
+}
+
 } // namespace ngpb

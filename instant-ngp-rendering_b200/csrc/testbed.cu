@@ -24,6 +24,7 @@ Testbed::Testbed() {
 	m_stream = m_own_stream;
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_counters_host, sizeof(NerfStepCounters)));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_loss_host, sizeof(float)));
+	NGPB_CUDA_CHECK(cudaMallocHost(&m_counters_host_render, 64));
 	m_rng = Pcg32{seed};
 }
 
@@ -41,6 +42,7 @@ Testbed::~Testbed() {
 	if (m_own_stream) { cudaStreamSynchronize(m_own_stream); cudaStreamDestroy(m_own_stream); }
 	if (m_counters_host) cudaFreeHost(m_counters_host);
 	if (m_loss_host) cudaFreeHost(m_loss_host);
+	if (m_counters_host_render) cudaFreeHost(m_counters_host_render);
 }
 
 void Testbed::set_stream(cudaStream_t s) {

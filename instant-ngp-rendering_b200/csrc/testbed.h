@@ -96,6 +96,16 @@ public:
 	void render_nerf(uint32_t width, uint32_t height, const float* camera_3x4, float focal_x, float focal_y, float principal_x, float principal_y,
 		uint32_t spp_index, uint32_t pixel_begin, uint32_t pixel_end, float* rgba_out, float* depth_out);
 	uint64_t last_render_samples = 0;
+	// Window policy of the wavefront: a window marches clamp(target_queries / n_alive, min, max)
+	// samples per ray (reference: 2 Mi queries, 1..8 steps, src/testbed_nerf.cu:36-38,1693-1694)
+	// and the host reads the live count back every `render_windows_per_sync` windows.
+	uint32_t render_target_queries = 2u << 20;
+	uint32_t render_min_steps = 1;
+	uint32_t render_max_steps = 8;
+	uint32_t render_windows_per_sync = 8;
+	bool render_snap_to_pixel_centers = false; // Testbed::m_snap_to_pixel_centers (testbed.h:995)
+	// Optional DEVICE buffer [height * width] receiving the number of samples composited per pixel.
+	void set_render_steps_out(uint32_t* p) { m_render_steps_out = p; }
 
 private:
 	void training_prep_nerf();
@@ -133,6 +143,8 @@ private:
 	DeviceBuffer m_render_scratch;
 	NerfStepCounters* m_counters_host = nullptr; // pinned
 	float* m_loss_host = nullptr;                // pinned
+	void* m_counters_host_render = nullptr;      // pinned
+	uint32_t* m_render_steps_out = nullptr;
 };
 
 } // namespace ngpb

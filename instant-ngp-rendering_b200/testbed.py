@@ -224,18 +224,27 @@ class Testbed:
         check(lib.ngpb_testbed_update_density_grid(self._h, decay, n_uniform, n_nonuniform))
 
     # -- rendering -------------------------------------------------------------------------------
-    def render_nerf(self, width, height, camera_3x4, focal, principal=(0.5, 0.5), spp_index=0, pixel_range=None):
+    def render_nerf(self, width, height, camera_3x4, focal, principal=(0.5, 0.5), spp_index=0, pixel_range=None, return_steps=False):
         """Linear premultiplied RGBA float32 [h][w][4] and depth [h][w] on the device. camera_3x4 in
         NGP convention; focal in pixels. pixel_range=(begin, end) renders a slice of the row-major
-        pixel list (tile sharding); the rest stays zero."""
+        pixel list (tile sharding); the rest stays zero. return_steps adds the per-pixel count of
+        composited samples (int32 [h][w])."""
         rgba = torch.zeros((height, width, 4), dtype=torch.float32, device=self._device)
         depth = torch.zeros((height, width), dtype=torch.float32, device=self._device)
+        steps = torch.zeros((height, width), dtype=torch.int32, device=self._device) if return_steps else None
         cam = np.ascontiguousarray(camera_3x4, dtype=np.float32)
         fx, fy = (focal, focal) if np.isscalar(focal) else focal
         b, e = pixel_range if pixel_range is not None else (0, width * height)
-        check(lib.ngpb_testbed_render_nerf(self._h, width, height, cam.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), fx, fy,
-                                           principal[0], principal[1], spp_index, b, e, ctypes.c_void_p(rgba.data_ptr()), ctypes.c_void_p(depth.data_ptr())))
-        return rgba, depth
+        torch.cuda.current_stream().synchronize()  # the testbed runs on its own stream unless use_current_stream()
+        check(lib.ngpb_testbed_set_render_steps_out(self._h, ctypes.c_void_p(steps.data_ptr()) if return_steps else None))
+        try:
+            check(lib.ngpb_testbed_render_nerf(self._h, width, height, cam.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), fx, fy,
+                                               principal[0], principal[1], spp_index, b, e, ctypes.c_void_p(rgba.data_ptr()), ctypes.c_void_p(depth.data_ptr())))
+        finally:
+            lib.ngpb_testbed_set_render_steps_out(self._h, None)
+        return (rgba, depth, steps) if return_steps else (rgba, depth)
+
+    last_render_samples = property(lambda self: int(self._get("last_render_samples")))
 
 
 def profile_enable(on=True):

@@ -27,6 +27,7 @@ static inline half_t nbits_to_half(uint16_t b) { half_t h; memcpy(&h, &b, 2); re
 namespace {
 
 constexpr uint32_t GRIDSIZE = 128, GRID_CELLS = 128 * 128 * 128, NERF_STEPS = 1024, CASCADES = 8;
+constexpr float MAX_DEPTH = 16384.0f; // common_device.cuh:32
 constexpr float SQRT3 = 1.73205080757f;
 constexpr float MIN_CONE_STEPSIZE = SQRT3 / NERF_STEPS;
 constexpr float MAX_CONE_STEPSIZE = MIN_CONE_STEPSIZE * (1 << (CASCADES - 1)) * NERF_STEPS / GRIDSIZE;
@@ -516,3 +517,154 @@ extern "C" float oracle_det_expf(float x) { return c_expf(x); }
 extern "C" float oracle_advance_n_steps(float t, float cone_angle, float n) { return advance_n_steps(t, cone_angle, n); }
 extern "C" uint32_t oracle_morton3d(uint32_t x, uint32_t y, uint32_t z) { return morton3D(x, y, z); }
 extern "C" uint32_t oracle_morton3d_invert(uint32_t x) { return morton3D_invert(x); }
+
+// ================================== rendering ====================================================
+namespace {
+// random_val.cuh:161-291 (Burley 2020): Sobol dims 0/1 with nested uniform (Owen) scrambling.
+inline uint32_t reverse_bits(uint32_t x) {
+	x = ((x & 0xaaaaaaaau) >> 1) | ((x & 0x55555555u) << 1);
+	x = ((x & 0xccccccccu) >> 2) | ((x & 0x33333333u) << 2);
+	x = ((x & 0xf0f0f0f0u) >> 4) | ((x & 0x0f0f0f0fu) << 4);
+	x = ((x & 0xff00ff00u) >> 8) | ((x & 0x00ff00ffu) << 8);
+	return (x >> 16) | (x << 16);
+}
+uint32_t sobol(uint32_t index, uint32_t dim) {
+	// dimension 0: identity generator matrix (radical inverse); dimension 1: Pascal matrix mod 2
+	uint32_t x = 0, v = 0x80000000u;
+	for (uint32_t bit = 0; bit < 32; ++bit) {
+		if ((index >> bit) & 1u) x ^= dim == 0 ? (0x80000000u >> bit) : v;
+		v ^= v >> 1;
+	}
+	return x;
+}
+inline uint32_t laine_karras(uint32_t x, uint32_t seed) {
+	x += seed;
+	x ^= x * 0x6c50b47cu;
+	x ^= x * 0xb82f1e52u;
+	x ^= x * 0xc7afe638u;
+	x ^= x * 0x8d22f6e6u;
+	return x;
+}
+inline uint32_t owen_scramble(uint32_t x, uint32_t seed) { return reverse_bits(laine_karras(reverse_bits(x), seed)); }
+inline uint32_t hash_combine(uint32_t seed, uint32_t v) { return seed ^ (v + (seed << 6) + (seed >> 2)); }
+float ld_random_val(uint32_t index, uint32_t seed, uint32_t dim) {
+	const float S = 1.0f / 4294967296.0f;
+	index = owen_scramble(index, seed);
+	return (float)owen_scramble(sobol(index, dim), hash_combine(seed, dim)) * S;
+}
+// nerf_device.cuh:461-494 with MIP_FROM_DT = false, min_mip = 0
+float advance_to_next_occupied_voxel(float t, float cone_angle, V o, V d, V idir, const uint8_t* bitfield, uint32_t max_mip, const Box& box) {
+	while (true) {
+		const V pos = o + d * t;
+		if (t >= MAX_DEPTH || !contains(box, pos)) return MAX_DEPTH;
+		uint32_t mip = mip_from_pos(pos, CASCADES - 1);
+		if (mip > max_mip) mip = max_mip;
+		if (occupied_at(pos, bitfield, mip)) return t;
+		while (mip < max_mip && !occupied_at(pos, bitfield, mip + 1)) ++mip;
+		t = advance_to_next_voxel(t, cone_angle, pos, d, idir, mip);
+	}
+}
+Box box_of(const oracle_render_config& c) { return {{c.aabb_min[0], c.aabb_min[1], c.aabb_min[2]}, {c.aabb_max[0], c.aabb_max[1], c.aabb_max[2]}}; }
+} // namespace
+
+extern "C" float oracle_ld_random_val(uint32_t index, uint32_t seed, uint32_t dim) { return ld_random_val(index, seed, dim); }
+
+extern "C" uint64_t oracle_nerf_render_march(const oracle_render_config* cfg, const uint8_t* bitfield, uint32_t* numsteps, float* coords, uint64_t max_samples) {
+	const Box box = box_of(*cfg);
+	const uint32_t n = cfg->pixel_end - cfg->pixel_begin;
+	V cam[4];
+	for (int k = 0; k < 4; ++k) cam[k] = {cfg->camera[3 * k + 0], cfg->camera[3 * k + 1], cfg->camera[3 * k + 2]};
+	// ld_random_pixel_offset (random_val.cuh:320-326)
+	const uint32_t spp = cfg->snap_to_pixel_centers ? 0u : cfg->spp_index;
+	float ox = 0.5f - ld_random_val(0, 0xdeadbeefu, 0) + ld_random_val(spp, 0xdeadbeefu, 0);
+	float oy = 0.5f - ld_random_val(0, 0xdeadbeefu, 1) + ld_random_val(spp, 0xdeadbeefu, 1);
+	ox -= floorf(ox);
+	oy -= floorf(oy);
+	uint64_t total = 0;
+	for (int pass = 0; pass < 2; ++pass) {
+		// pass 0 counts (serial prefix afterwards), pass 1 emits
+		if (pass == 1 && !coords) break;
+#pragma omp parallel for schedule(dynamic, 64)
+		for (uint32_t r = 0; r < n; ++r) {
+			const uint32_t pix = cfg->pixel_begin + r;
+			const uint32_t x = pix % cfg->width, y = pix / cfg->width;
+			const float u = ((float)x + ox) / (float)cfg->width, v = ((float)y + oy) / (float)cfg->height;
+			const V dd = {(u - cfg->screen_cx) * (float)cfg->width / cfg->focal_x, (v - cfg->screen_cy) * (float)cfg->height / cfg->focal_y, 1.0f};
+			const V o = cam[3];
+			const V d = normalize(cam[0] * dd.x + cam[1] * dd.y + cam[2] * dd.z);
+			float tmin, tmax;
+			ray_intersect(box, o, d, tmin, tmax);
+			float t = fmaxf(tmin, 0.0f) + 1e-6f;
+			uint32_t count = 0;
+			if (contains(box, o + d * t)) {
+				const V idir = V{1.0f, 1.0f, 1.0f} / d;
+				const V wd = (d + 1.0f) * 0.5f;
+				t = advance_n_steps(t, cfg->cone_angle_constant, ld_random_val(cfg->spp_index, pix * 786433u, 0));
+				const uint64_t base = pass == 1 ? numsteps[2 * r + 1] : 0;
+				while (count < cfg->max_steps_per_ray) {
+					t = advance_to_next_occupied_voxel(t, cfg->cone_angle_constant, o, d, idir, bitfield, cfg->max_mip, box);
+					if (t >= MAX_DEPTH) break;
+					const float dt = calc_dt(t, cfg->cone_angle_constant);
+					if (pass == 1 && base + count < max_samples) {
+						const V wp = (o + d * t - box.min) / diag(box);
+						float* c = coords + (base + count) * 7;
+						c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+					}
+					++count;
+					t += dt;
+				}
+			}
+			if (pass == 0) numsteps[2 * r] = count;
+		}
+		if (pass == 0) {
+			total = 0;
+			for (uint32_t r = 0; r < n; ++r) { numsteps[2 * r + 1] = (uint32_t)total; total += numsteps[2 * r]; }
+		}
+	}
+	return total;
+}
+
+extern "C" void oracle_nerf_render_composite(const oracle_render_config* cfg, const uint32_t* numsteps, const float* coords, const uint16_t* rgbsigma,
+	float* rgba_out, float* depth_out, uint32_t* steps_out)
+{
+	const Box box = box_of(*cfg);
+	const uint32_t n = cfg->pixel_end - cfg->pixel_begin;
+	const V cam_fwd = {cfg->camera[6], cfg->camera[7], cfg->camera[8]}, cam_o = {cfg->camera[9], cfg->camera[10], cfg->camera[11]};
+#pragma omp parallel for schedule(dynamic, 64)
+	for (uint32_t r = 0; r < n; ++r) {
+		const uint32_t count = numsteps[2 * r];
+		const uint64_t base = numsteps[2 * r + 1];
+		float rgba[4] = {0, 0, 0, 0};
+		float depth = 0.0f, max_weight = 0.0f;
+		uint32_t j = 0, taken = 0;
+		for (; j < count; ++j) {
+			const uint16_t* o16 = rgbsigma + (base + j) * 4;
+			const float* c = coords + (base + j) * 7;
+			const V pos = box.min + V{c[0], c[1], c[2]} * diag(box);
+			const float T = 1.0f - rgba[3];
+			const float dt = unwarp_dt(c[3]);
+			const float alpha = 1.0f - expf(-net_to_density(oracle_half_to_float(o16[3]), cfg->density_activation) * dt);
+			const float weight = alpha * T;
+			for (int k = 0; k < 3; ++k) rgba[k] += net_to_rgb(oracle_half_to_float(o16[k]), cfg->rgb_activation) * weight;
+			rgba[3] += weight;
+			if (weight > max_weight) { max_weight = weight; depth = dot(cam_fwd, pos - cam_o); }
+			taken = j + 1;
+			if (rgba[3] > 1.0f - cfg->min_transmittance) {
+				for (int k = 0; k < 3; ++k) rgba[k] /= rgba[3];
+				rgba[3] = 1.0f;
+				break;
+			}
+		}
+		steps_out[r] = taken;
+		// compact_kernel_nerf keeps rays with alpha > 0.001 (:1365); shade_kernel_nerf (:1341-1348)
+		float out[4] = {0, 0, 0, 0};
+		float dout = MAX_DEPTH;
+		if (rgba[3] > 0.001f) {
+			for (int k = 0; k < 3; ++k) out[k] = cfg->linear_colors ? rgba[k] : srgb_to_linear(rgba[k]);
+			out[3] = rgba[3];
+			if (out[3] > 0.2f) dout = depth;
+		}
+		for (int k = 0; k < 4; ++k) rgba_out[4 * r + k] = out[k];
+		depth_out[r] = dout;
+	}
+}

@@ -120,6 +120,31 @@ float oracle_advance_n_steps(float t, float cone_angle, float n);
 uint32_t oracle_morton3d(uint32_t x, uint32_t y, uint32_t z);
 uint32_t oracle_morton3d_invert(uint32_t x);
 
+/* ---- NeRF rendering (nerf_oracle.cpp) -----------------------------------------------------------
+ * Per-pixel restatement of NerfTracer (src/testbed_nerf.cu:333-677, 1375-1489): a pixel's result
+ * does not depend on how the reference groups rays into windows, so the oracle walks ray by ray. */
+typedef struct {
+	float aabb_min[3], aabb_max[3];
+	float camera[12];            /* column-major 4 x 3, NGP convention */
+	uint32_t width, height;
+	float focal_x, focal_y, screen_cx, screen_cy;
+	uint32_t spp_index, pixel_begin, pixel_end, max_mip;
+	float cone_angle_constant, min_transmittance;
+	int rgb_activation, density_activation, linear_colors, snap_to_pixel_centers;
+	uint32_t max_steps_per_ray;
+} oracle_render_config;
+/* init_rays_with_payload_kernel_nerf + advance_pos_nerf + generate_next_nerf_network_inputs: ALL
+ * samples of every pixel in [pixel_begin, pixel_end) until the ray leaves the box (or
+ * max_steps_per_ray). numsteps[2*(pix - begin)] = {count, base}; coords [..][7] may be NULL to count
+ * only. Returns the total number of samples. */
+uint64_t oracle_nerf_render_march(const oracle_render_config* cfg, const uint8_t* bitfield, uint32_t* numsteps, float* coords, uint64_t max_samples);
+/* composite_kernel_nerf (Shade) + shade_kernel_nerf: rgbsigma fp16 [..][4] per marched sample ->
+ * rgba [n][4] (linear, premultiplied), depth [n], steps [n] (samples composited before termination). */
+void oracle_nerf_render_composite(const oracle_render_config* cfg, const uint32_t* numsteps, const float* coords, const uint16_t* rgbsigma,
+	float* rgba, float* depth, uint32_t* steps);
+/* ld_random_val (random_val.cuh:287-291), dims 0 and 1. */
+float oracle_ld_random_val(uint32_t index, uint32_t seed, uint32_t dim);
+
 /* fp16 <-> fp32 (round to nearest even), exposed so tests can build fp16 inputs. */
 uint16_t oracle_float_to_half(float f);
 float oracle_half_to_float(uint16_t h);

@@ -339,3 +339,68 @@ def nerf_bitfield(max_cascade, grid):
     mean = ctypes.c_float()
     olib.oracle_nerf_bitfield(ctypes.c_uint32(max_cascade), _p(g, ctypes.c_float), _p(bf, ctypes.c_uint8), ctypes.byref(mean))
     return bf, mean.value
+
+
+# ---- NeRF rendering (oracle_nerf_render_*) --------------------------------------------------------
+class RenderConfig(ctypes.Structure):
+    """oracle_render_config."""
+    _fields_ = [("aabb_min", ctypes.c_float * 3), ("aabb_max", ctypes.c_float * 3), ("camera", ctypes.c_float * 12),
+                ("width", ctypes.c_uint32), ("height", ctypes.c_uint32),
+                ("focal_x", ctypes.c_float), ("focal_y", ctypes.c_float), ("screen_cx", ctypes.c_float), ("screen_cy", ctypes.c_float),
+                ("spp_index", ctypes.c_uint32), ("pixel_begin", ctypes.c_uint32), ("pixel_end", ctypes.c_uint32), ("max_mip", ctypes.c_uint32),
+                ("cone_angle_constant", ctypes.c_float), ("min_transmittance", ctypes.c_float),
+                ("rgb_activation", ctypes.c_int), ("density_activation", ctypes.c_int), ("linear_colors", ctypes.c_int), ("snap_to_pixel_centers", ctypes.c_int),
+                ("max_steps_per_ray", ctypes.c_uint32)]
+
+
+olib.oracle_nerf_render_march.restype = ctypes.c_uint64
+olib.oracle_ld_random_val.restype = ctypes.c_float
+olib.oracle_ld_random_val.argtypes = [ctypes.c_uint32] * 3
+
+
+def render_config(aabb_min, aabb_max, camera_3x4, width, height, focal, max_mip, cone_angle_constant, principal=(0.5, 0.5), spp_index=0,
+                  pixel_range=None, min_transmittance=0.01, rgb_activation=2, density_activation=3, linear_colors=False, snap=False, max_steps_per_ray=10000):
+    c = RenderConfig()
+    for k in range(3):
+        c.aabb_min[k], c.aabb_max[k] = float(aabb_min[k]), float(aabb_max[k])
+    x = np.asarray(camera_3x4, dtype=np.float32)
+    for col in range(4):
+        for r in range(3):
+            c.camera[3 * col + r] = float(x[r, col])
+    c.width, c.height = width, height
+    c.focal_x, c.focal_y = (focal, focal) if np.isscalar(focal) else focal
+    c.screen_cx, c.screen_cy = principal
+    c.spp_index = spp_index
+    c.pixel_begin, c.pixel_end = pixel_range if pixel_range is not None else (0, width * height)
+    c.max_mip = max_mip
+    c.cone_angle_constant = cone_angle_constant
+    c.min_transmittance = min_transmittance
+    c.rgb_activation, c.density_activation = rgb_activation, density_activation
+    c.linear_colors, c.snap_to_pixel_centers = int(linear_colors), int(snap)
+    c.max_steps_per_ray = max_steps_per_ray
+    return c
+
+
+def nerf_render_march(cfg, bitfield):
+    """Returns (numsteps [n][2] = count, base; coords [total][7])."""
+    n = cfg.pixel_end - cfg.pixel_begin
+    bf = np.ascontiguousarray(bitfield, dtype=np.uint8)
+    numsteps = np.zeros((n, 2), dtype=np.uint32)
+    total = olib.oracle_nerf_render_march(ctypes.byref(cfg), _p(bf, ctypes.c_uint8), _p(numsteps, ctypes.c_uint32), None, ctypes.c_uint64(0))
+    coords = np.zeros((max(int(total), 1), 7), dtype=np.float32)
+    olib.oracle_nerf_render_march(ctypes.byref(cfg), _p(bf, ctypes.c_uint8), _p(numsteps, ctypes.c_uint32), _p(coords, ctypes.c_float), ctypes.c_uint64(int(total)))
+    return numsteps, coords[:int(total)]
+
+
+def nerf_render_composite(cfg, numsteps, coords, rgbsigma_f16):
+    """Returns (rgba [n][4], depth [n], steps [n])."""
+    n = cfg.pixel_end - cfg.pixel_begin
+    ns = np.ascontiguousarray(numsteps, dtype=np.uint32)
+    co = np.ascontiguousarray(coords, dtype=np.float32)
+    out = np.ascontiguousarray(rgbsigma_f16, dtype=np.float16)
+    rgba = np.zeros((n, 4), dtype=np.float32)
+    depth = np.zeros(n, dtype=np.float32)
+    steps = np.zeros(n, dtype=np.uint32)
+    olib.oracle_nerf_render_composite(ctypes.byref(cfg), _p(ns, ctypes.c_uint32), _p(co, ctypes.c_float), _p(out.view(np.uint16), ctypes.c_uint16),
+                                      _p(rgba, ctypes.c_float), _p(depth, ctypes.c_float), _p(steps, ctypes.c_uint32))
+    return rgba, depth, steps

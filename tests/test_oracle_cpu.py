@@ -149,3 +149,13 @@ def test_random_uniform_mapping(oracle):
         u = oracle.pcg32_floats(1337, 4 * t + j, 1)[0]
         want = np.float32(np.float64(u) * np.float64(np.float32(1e-4) - np.float32(-1e-4)) + np.float64(np.float32(-1e-4)))
         assert abs(got[e] - want) <= 1e-11
+
+
+def test_ld_random_val_is_a_scrambled_sobol_sequence(oracle):
+    # Sobol dimension 0 is the radical inverse: unscrambled values of consecutive indices are k / 2^32 bit-reversed
+    v = [oracle.olib.oracle_ld_random_val(i, 12345, 0) for i in range(256)]
+    assert all(0.0 <= x < 1.0 for x in v)
+    # an Owen-scrambled (0,1)-sequence stays stratified: 256 points hit each of 256 strata exactly once
+    assert sorted(int(x * 256) for x in v) == list(range(256))
+    v1 = [oracle.olib.oracle_ld_random_val(i, 999, 1) for i in range(64)]
+    assert sorted(int(x * 64) for x in v1) == list(range(64))
