@@ -36,11 +36,12 @@ def orbit_poses(n, radius=1.1, center=(0.5, 0.5, 0.5), seed=0):
 class BlobScene:
     """sigma(x) = sum_k a_k exp(-|x - c_k|^2 / (2 s_k^2)); colour = density-weighted mix of blob colours."""
 
-    def __init__(self, n_blobs=6, seed=7, device="cuda"):
+    def __init__(self, n_blobs=6, seed=7, device="cuda", amp_scale=1.0):
         g = np.random.default_rng(seed)
         self.centers = torch.tensor(0.5 + (g.random((n_blobs, 3)) - 0.5) * 0.5, dtype=torch.float32, device=device)
         self.sigmas = torch.tensor(0.04 + g.random(n_blobs) * 0.06, dtype=torch.float32, device=device)
-        self.amps = torch.tensor(30.0 + g.random(n_blobs) * 60.0, dtype=torch.float32, device=device)
+        # amp_scale > 1 sharpens the blobs towards solid objects (earlier ray termination)
+        self.amps = torch.tensor((30.0 + g.random(n_blobs) * 60.0) * amp_scale, dtype=torch.float32, device=device)
         self.colors = torch.tensor(0.15 + 0.85 * g.random((n_blobs, 3)), dtype=torch.float32, device=device)
         self.device = device
 
@@ -87,9 +88,9 @@ def linear_premul_to_srgb8(rgba):
     return (torch.cat([srgb, a], -1) * 255.0 + 0.5).clamp(0, 255).to(torch.uint8)
 
 
-def make_dataset(testbed, n_images=8, width=160, height=120, aabb_scale=1, focal=None, seed=7, radius=None, opaque_background=False):
+def make_dataset(testbed, n_images=8, width=160, height=120, aabb_scale=1, focal=None, seed=7, radius=None, opaque_background=False, amp_scale=1.0, n_blobs=6):
     """Fills `testbed` with a synthetic posed dataset; returns (scene, poses, focal)."""
-    scene = BlobScene(seed=seed, device=testbed._device)
+    scene = BlobScene(n_blobs=n_blobs, seed=seed, device=testbed._device, amp_scale=amp_scale)
     focal = focal or 1.1 * width
     radius = radius or (1.1 if aabb_scale == 1 else 1.4)
     poses = orbit_poses(n_images, radius=radius)

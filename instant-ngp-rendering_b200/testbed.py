@@ -168,6 +168,8 @@ class Testbed:
         assert img.dim() == 3 and img.shape[2] == 4
         kind = {torch.uint8: IMAGE_BYTE, torch.float16: IMAGE_HALF, torch.float32: IMAGE_FLOAT}[img.dtype]
         h, w = int(img.shape[0]), int(img.shape[1])
+        if img.is_cuda:
+            torch.cuda.current_stream().synchronize()  # the library copies on the testbed's own stream
         check(lib.ngpb_testbed_set_nerf_image(self._h, idx, ctypes.c_void_p(img.data_ptr()), kind, w, h))
         self._resolutions[idx] = (w, h)
         self._push_camera(idx)
