@@ -1,12 +1,20 @@
 #!/usr/bin/env python
 """bench.py - throughput of the ngp-b200 hot path on N GPUs of one node.
 
-    python bench.py --gpus N --steps K --warmup W [--workload grid] [--impl reference]
+    python bench.py --gpus N --steps K --warmup W [--workload nerf|grid] [--impl reference]
 
-Prints ONE JSON line (rank 0). See DESIGN.md "Measurement" for what each key means.
+Prints ONE JSON line (rank 0). DESIGN.md "Measurement" says what each key means.
+
 Workloads (BASELINE.json configs):
-  grid   hash-grid encoding forward+backward alone, 3-D L16 F2 T=2^19 N_min=16, 2^20 points
-         (configs[0]); metric "hash-enc fwd+bwd Gpts/s". Replicas only at N>1 (no exchange).
+  nerf   (default) configs[2] + configs[3]: NeRF training with configs/nerf/base.json on a synthetic
+         dataset of the fox shape (50 views 1920x1080 RGBA8, aabb_scale 4), 2^18 samples per batch,
+         through Testbed.train(); headline metric "fox NeRF train samples/s" (compacted samples / s).
+         The same line carries the novel-view render of the trained model at 1920x1080 ("render",
+         Mrays/s) and the hash-grid micro-benchmark ("grid", Gpts/s).
+         N > 1: rays of every step are sharded over the ranks and the gradients all-reduced over
+         NCCL; the render shards pixel tiles with no communication.
+  grid   configs[0]: hash-grid encoding forward+backward alone, 3-D L16 F2 T=2^19, 2^20 points.
+         Replicas only at N > 1 (no exchange).
 """
 import argparse
 import importlib
@@ -27,12 +35,20 @@ GRID_N = 1 << 20
 GRID_BYTES_PER_POINT_FWD = 12 + 512 + 64    # xyz + 16 levels x 8 corners x 4 B + 32 fp16 out
 GRID_BYTES_PER_POINT_BWD = 12 + 64 + 512    # xyz + dL/dy + scatter RMW counted once
 
+# fox shape (data/nerf/fox: 50 views 1080 x 1920, aabb_scale 4) and configs/nerf/base.json
+FOX = {"n_images": 50, "width": 1920, "height": 1080, "aabb_scale": 4, "batch": 1 << 18, "amp_scale": 8.0, "pretrain_steps": 512}
+NERF_MLP_FLOP_TRAIN = 61440      # per trained sample, fwd+bwd
+NERF_MLP_FLOP_INFER = 20480      # per marched sample
+NERF_GRID_BYTES_TRAIN = 1176     # per trained sample (encoder fwd+bwd)
+NERF_GRID_BYTES_INFER = 588      # per marched sample
+
 
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
         return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d.get("bf16_tflops"), "bf16_tflops_sustained": d.get("bf16_tflops_sustained"), "source": "measured"}
+    # fallback stated in /opt/skills/guides/B200_PROFILING.md
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
@@ -56,7 +72,7 @@ class ClockSampler:
                     self.samples.append([s.strip() for s in out.split(",")])
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.05)
 
     def start(self):
         self._t = threading.Thread(target=self._run, daemon=True)
@@ -81,7 +97,7 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def dist_setup(n_gpus):
+def dist_setup():
     import torch
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -90,7 +106,8 @@ def dist_setup(n_gpus):
         torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group(backend="nccl" if torch.cuda.is_available() else "gloo")
+        if not dist.is_initialized():
+            dist.init_process_group(backend="nccl" if torch.cuda.is_available() else "gloo")
     return rank, world, local
 
 
@@ -103,19 +120,21 @@ def barrier(world):
         torch.cuda.synchronize()
 
 
-def max_over_ranks(value, world):
+def reduce_over_ranks(value, world, op="max"):
     import torch
     if world == 1:
         return value
     import torch.distributed as dist
     t = torch.tensor([value], dtype=torch.float64, device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
     return float(t.item())
 
 
 # ------------------------------------------------------------------------------------------
+# CPU baselines: the oracle (a CPU restatement of the reference's kernels; the reference itself has
+# no CPU implementation of this path) timed on the host cores. Used by the
+# `cpu_baseline` object of the GPU arm and by `--impl reference`; never by the product path.
 def cpu_grid_baseline(budget_points):
-    """Times the oracle (the CPU port of the reference's kernels) on the host cores."""
     import numpy as np
     import oracle_binding as oracle
     cfg = oracle.grid_cfg(3, GRID_ENC)
@@ -131,41 +150,114 @@ def cpu_grid_baseline(budget_points):
     return budget_points / dt / 1e9, dt, oracle.num_threads()
 
 
-def run_reference_arm(args):
-    """--impl reference: the reference has no CPU implementation of this path and its
-    CUDA build cannot be produced in the authoring container's time budget, so the arm times the
-    oracle port on all host threads on a bounded sample of the same workload."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
-    sample = 1 << 18
-    vals = []
-    for _ in range(args.warmup):
-        cpu_grid_baseline(1 << 14)
-    t_total = 0.0
-    for _ in range(args.steps):
-        v, dt, cores = cpu_grid_baseline(sample)
-        vals.append(v)
-        t_total += dt
-    value = sample * args.steps / t_total / 1e9
-    line = {
-        "impl": "reference", "metric": "hash-enc fwd+bwd Gpts/s", "value": value, "unit": "Gpts/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / args.steps * (GRID_N / sample),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-        "config": {"workload": "grid_L16F2_T19_2^20pts", "sample": f"2^18 of 2^20 points per step"},
-        "cpu_baseline": {"value": value, "unit": "Gpts/s", "cores": cores, "kind": "port", "sample": "2^18 uniform points, fwd+bwd, OpenMP"},
-        "e2e": {"value": value, "unit": "Gpts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }
-    print(json.dumps(line))
+class CpuNerf:
+    """One NeRF training step of the reference's algorithm on the host, composed from the oracle:
+    generate_training_samples_nerf -> NerfNetwork inference -> compute_loss_kernel_train_nerf ->
+    NerfNetwork forward+backward on the compacted batch -> Adam. Inputs have the fox shape
+    (50 x 1080 x 1920 RGBA8, aabb_scale 4, base.json network); the step is run on a bounded number
+    of rays so that one step costs seconds, and the metric is compacted samples per second."""
+
+    def __init__(self, n_rays):
+        import numpy as np
+        import oracle_binding as oracle
+        self.np, self.oracle = np, oracle
+        syn = importlib.import_module("instant-ngp-rendering_b200.synthetic")
+        rng = np.random.default_rng(1337)
+        n_images, w, h, aabb = FOX["n_images"], FOX["width"], FOX["height"], FOX["aabb_scale"]
+        poses = syn.orbit_poses(n_images, radius=1.4)
+        # procedural host images: one random RGBA8 tile repeated (the kernels only look pixels up)
+        tile = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
+        tile[..., 3] = 255
+        self.images = [oracle.nerf_image(tile, poses[i], focal=1.1 * w) for i in range(n_images)]
+        self.max_cascade = int(np.log2(aabb))
+        # occupancy of a partly trained model: 8x8x8 bricks (contiguous Morton runs) in every cascade
+        grid = np.zeros((self.max_cascade + 1, 128 ** 3), dtype=np.float32)
+        for c in range(self.max_cascade + 1):
+            for s in rng.integers(0, 128 ** 3 // 512, size=400) * 512:
+                grid[c, s:s + 512] = 0.5
+        self.bitfield, self.mean = oracle.nerf_bitfield(self.max_cascade, grid.reshape(-1))
+        enc = dict(syn.NERF_BASE_CONFIG["encoding"])
+        enc["per_level_scale"] = float(np.exp(np.log(2048.0 * aabb / enc["base_resolution"]) / (enc["n_levels"] - 1)))
+        self.gcfg = oracle.grid_cfg(3, enc)
+        n_grid = int(oracle.grid_offsets(self.gcfg)[-1]) * enc["n_features_per_level"]
+        st = oracle.Pcg32State(1337)
+        wd = oracle.mlp_init(st, 32, 1)
+        wr = oracle.mlp_init(st, 32, 2)
+        wg = oracle.random_uniform_from(st, n_grid, -1e-4, 1e-4)
+        self.params32 = np.concatenate([wd, wr, wg]).astype(np.float32)
+        self.n_mlp = len(wd) + len(wr)
+        self.m = np.zeros_like(self.params32)
+        self.v = np.zeros_like(self.params32)
+        self.step_count = 0
+        cfg = oracle.NerfConfig()
+        half = 0.5 * aabb
+        for k in range(3):
+            cfg.aabb_min[k], cfg.aabb_max[k], cfg.background_color[k] = 0.5 - half, 0.5 + half, 0.0
+        cfg.n_rays, cfg.n_rays_total = n_rays, 0
+        cfg.max_samples, cfg.max_samples_compacted = 1 << 22, 1 << 22
+        cfg.n_training_images, cfg.max_mip = n_images, self.max_cascade
+        cfg.cone_angle_constant = 1.0 / 256.0
+        cfg.near_distance, cfg.loss_scale = 0.1, 128.0
+        cfg.snap_to_pixel_centers, cfg.random_bg_color, cfg.linear_colors, cfg.color_space = 1, 1, 0, 0
+        cfg.loss_type, cfg.rgb_activation, cfg.density_activation = 4, 2, 3
+        self.cfg = cfg
+        self.rng = oracle.Pcg32State(1337)
+
+    def step(self):
+        np, oracle, cfg = self.np, self.oracle, self.cfg
+        params16 = self.params32.astype(np.float16)
+        numsteps, rays, coords, total = oracle.nerf_generate_samples(cfg, self.images, self.bitfield, self.rng, cfg.max_samples)
+        ray_idx = np.nonzero(numsteps)[0].astype(np.uint32)
+        base = np.concatenate([[0], np.cumsum(numsteps.astype(np.int64))])[:-1]
+        ns_in = np.stack([numsteps[ray_idx], base[ray_idx].astype(np.uint32)], axis=1).astype(np.uint32)
+        fwd = oracle.nerf_forward(self.gcfg, params16, coords, 1, 2)
+        rgbsigma = np.ascontiguousarray(fwd["out"][:, :4])
+        comp, loss, dloss = oracle.nerf_compute_loss(cfg, self.images, self.mean, ray_idx, ns_in, rays[ray_idx], coords, rgbsigma, self.rng)
+        sel = np.concatenate([np.arange(b, b + c) for b, c in zip(ns_in[:, 1].astype(np.int64), comp.astype(np.int64))]) if len(comp) else np.zeros(0, dtype=np.int64)
+        cc = np.ascontiguousarray(coords[sel])
+        dy = np.ascontiguousarray(dloss[sel]).astype(np.float16)
+        fwd2 = oracle.nerf_forward(self.gcfg, params16, cc, 1, 2)
+        dWd, dWr, gg, _ = oracle.nerf_backward(self.gcfg, fwd2, cc, dy, 1, 2)
+        grad = np.concatenate([dWd.reshape(-1), dWr.reshape(-1), gg.reshape(-1)]).astype(np.float32) / np.float32(cfg.loss_scale)
+        # Adam (tcnn adam.h:48-119): beta 0.9 / 0.99, eps 1e-15, lr 1e-2, L2 1e-6 on the MLP weights
+        self.step_count += 1
+        grad[:self.n_mlp] += np.float32(1e-6) * self.params32[:self.n_mlp]
+        self.m = np.float32(0.9) * self.m + np.float32(0.1) * grad
+        self.v = np.float32(0.99) * self.v + np.float32(0.01) * grad * grad
+        lr = 1e-2 * np.sqrt(1 - 0.99 ** self.step_count) / (1 - 0.9 ** self.step_count)
+        self.params32 -= np.float32(lr) * self.m / (np.sqrt(self.v) + np.float32(1e-15))
+        self.rng.advance(1 << 32)
+        return int(comp.sum()), int(total), float(loss.sum())
 
 
-def run_grid(args):
+def cpu_nerf_baseline(n_rays, steps, warmup=0, budget_s=1e9):
+    """Runs up to `steps` oracle training steps (stops early once `budget_s` of timed work is spent)."""
+    import oracle_binding as oracle
+    c = CpuNerf(n_rays)
+    for _ in range(warmup):
+        c.step()
+    samples, marched, dt, done = 0, 0, 0.0, 0
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        s, m, _ = c.step()
+        dt += time.perf_counter() - t0
+        samples += s
+        marched += m
+        done += 1
+        if dt > budget_s:
+            break
+    return {"samples_per_s": samples / dt, "seconds": dt, "steps_done": done, "samples": samples, "marched": marched, "cores": oracle.num_threads(),
+            "sample": f"{done} oracle training step(s) of {n_rays} rays ({samples // max(done, 1)} compacted / {marched // max(done, 1)} marched samples per step, "
+                      f"{dt:.1f} s) on the fox-shaped inputs"}
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+def grid_measure(ngp, steps, warmup, rank, world, local):
+    """configs[0]: hash-grid forward+backward alone; returns the fields of a bench line."""
+    import ctypes
     import numpy as np
     import torch
-    ngp = importlib.import_module("instant-ngp-rendering_b200")
-    if not ngp.has_device():
-        raise RuntimeError("bench.py needs a CUDA device: ngp-b200 has no CPU fallback")
-    rank, world, local = dist_setup(args.gpus)
     peaks = load_peaks()
     dev = torch.device("cuda", local)
     n = GRID_N
@@ -176,110 +268,335 @@ def run_grid(args):
     dy = (torch.randn((n, 32), generator=g, device=dev) * (128.0 / n)).half()
     e.set_params(params)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-
-    def step():
-        out, ctx = e.forward(x)
-        _, grad = e.backward(ctx, x, out, dy)
-        return out, grad
-
-    for _ in range(max(args.warmup, 3)):
-        step()
-    torch.cuda.synchronize()
-
-    # kernel-level timing (forward / backward separately, L2 flushed in between)
+    lib, check = ngp.lib, ngp._lib.check
     ev = lambda: torch.cuda.Event(enable_timing=True)
-    fwd_ms, bwd_ms, step_ms = [], [], []
-    sampler = ClockSampler(local)
-    barrier(world)
-    if rank == 0:
-        sampler.start()
-    for _ in range(args.steps):
-        flush.fill_(1)
-        e0, e1, e2 = ev(), ev(), ev()
-        out = torch.empty((n, 32), dtype=torch.float16, device=dev)
-        grad = torch.empty(e.n_params, dtype=torch.float16, device=dev)
-        import ctypes
-        from importlib import import_module
-        lib, check = ngp.lib, ngp._lib.check
-        sp = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    out = torch.empty((n, 32), dtype=torch.float16, device=dev)
+    grad = torch.empty(e.n_params, dtype=torch.float16, device=dev)
+    sp = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def fwd_bwd(record=None):
         ctx = ctypes.c_void_p()
-        e0.record()
+        if record: record[0].record()
         check(lib.ngpb_module_forward(e._h, sp, n, x.data_ptr(), out.data_ptr(), params.data_ptr(), 0, ctypes.byref(ctx)))
-        e1.record()
+        if record: record[1].record()
         check(lib.ngpb_module_backward(e._h, sp, ctx, n, None, dy.data_ptr(), grad.data_ptr(), x.data_ptr(), out.data_ptr(), params.data_ptr()))
-        e2.record()
+        if record: record[2].record()
+        return ctx
+
+    for _ in range(max(warmup, 3)):
+        ctx = fwd_bwd()
         torch.cuda.synchronize()
         lib.ngpb_context_free(ctx)
-        fwd_ms.append(e0.elapsed_time(e1))
-        bwd_ms.append(e1.elapsed_time(e2))
-        step_ms.append(e0.elapsed_time(e2))
+    fwd_ms, bwd_ms, step_ms = [], [], []
     barrier(world)
-    clocks = sampler.stop() if rank == 0 else None
-    total_ms = max_over_ranks(sum(step_ms), world)
-    value = n * world * args.steps / (total_ms * 1e-3) / 1e9
+    for _ in range(steps):
+        flush.fill_(1)
+        rec = (ev(), ev(), ev())
+        ctx = fwd_bwd(rec)
+        torch.cuda.synchronize()
+        lib.ngpb_context_free(ctx)
+        fwd_ms.append(rec[0].elapsed_time(rec[1]))
+        bwd_ms.append(rec[1].elapsed_time(rec[2]))
+        step_ms.append(rec[0].elapsed_time(rec[2]))
+    barrier(world)
+    total_ms = reduce_over_ranks(sum(step_ms), world)
+    value = n * world * steps / (total_ms * 1e-3) / 1e9
 
-    # end to end through the module API with host buffers (pinned), copies inside the timed region
-    xh = x.cpu().pin_memory()
-    dyh = dy.cpu().pin_memory()
+    # end to end through the module API with pinned host buffers, copies inside the timed region
+    xh, dyh = x.cpu().pin_memory(), dy.cpu().pin_memory()
     outh = torch.empty((n, 32), dtype=torch.float16).pin_memory()
     gradh = torch.empty(e.n_params, dtype=torch.float16).pin_memory()
+
     def e2e_step():
         xd = xh.to(dev, non_blocking=True)
         dyd = dyh.to(dev, non_blocking=True)
-        out, ctx = e.forward(xd)
-        _, grad = e.backward(ctx, xd, out, dyd)
-        outh.copy_(out, non_blocking=True)
-        gradh.copy_(grad, non_blocking=True)
+        o, c = e.forward(xd)
+        _, gr = e.backward(c, xd, o, dyd)
+        outh.copy_(o, non_blocking=True)
+        gradh.copy_(gr, non_blocking=True)
     for _ in range(3):
         e2e_step()
     barrier(world)
     t0, t1 = ev(), ev()
     t0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         e2e_step()
     t1.record()
     torch.cuda.synchronize()
-    e2e_ms = max_over_ranks(t0.elapsed_time(t1), world)
-    e2e_value = n * world * args.steps / (e2e_ms * 1e-3) / 1e9
-
-    if rank != 0:
-        return
-    f_ms = float(np.mean(fwd_ms))
-    b_ms = float(np.mean(bwd_ms))
-    dom = "grid_backward_kernel" if b_ms >= f_ms else "grid_forward_kernel"
-    dom_ms = max(f_ms, b_ms)
-    dom_bytes = n * (GRID_BYTES_PER_POINT_BWD if b_ms >= f_ms else GRID_BYTES_PER_POINT_FWD)
-    achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
-    cpu_v, cpu_dt, cores = cpu_grid_baseline(1 << 18)
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(dom)
-    line = {
-        "metric": "hash-enc fwd+bwd Gpts/s", "value": value, "unit": "Gpts/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+    e2e_ms = reduce_over_ranks(t0.elapsed_time(t1), world)
+    f_ms, b_ms = float(np.mean(fwd_ms)), float(np.mean(bwd_ms))
+    back = b_ms >= f_ms
+    dom = "grid_backward_kernel" if back else "grid_forward_kernel"
+    achieved = n * (GRID_BYTES_PER_POINT_BWD if back else GRID_BYTES_PER_POINT_FWD) / (max(f_ms, b_ms) * 1e-3) / 1e9
+    return {
+        "metric": "hash-enc fwd+bwd Gpts/s", "value": value, "unit": "Gpts/s", "ms_per_step": total_ms / steps,
         "config": {"workload": "grid_L16F2_T19_2^20pts", "encoding": GRID_ENC, "points_per_step_per_gpu": n,
                    "l2": "flushed between timed steps (256 MiB write)", "parallelism": "replicas only" if world > 1 else "1 GPU"},
         "kernels_ms": {"grid_forward_kernel": f_ms, "memset+grid_backward_kernel": b_ms},
-        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peaks["source"],
-                     "note": "algorithmic bytes 588 B/point per direction; table (24.4 MB) is L2-resident, so the HBM copy peak is a floor, not a ceiling"},
-        "cpu_baseline": {"value": cpu_v, "unit": "Gpts/s", "cores": cores, "kind": "port", "sample": "2^18 uniform points fwd+bwd (oracle, OpenMP)"},
-        "e2e": {"value": e2e_value, "unit": "Gpts/s", "h2d_bytes_per_step": int(xh.numel() * 4 + dyh.numel() * 2),
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
+                     "traffic": load_traffic(dom), "peak_source": peaks["source"],
+                     "note": "algorithmic 588 B/point per direction; the 24.4 MB table is L2-resident, so the HBM copy peak is a floor for the gather roofline, not a ceiling"},
+        "e2e": {"value": n * world * steps / (e2e_ms * 1e-3) / 1e9, "unit": "Gpts/s", "h2d_bytes_per_step": int(xh.numel() * 4 + dyh.numel() * 2),
                 "d2h_bytes_per_step": int(outh.numel() * 2 + gradh.numel() * 2)},
-        "gpu_launches": 2 * args.steps,
-        "clocks": clocks,
+        "gpu_launches": 2 * steps,
     }
+
+
+def load_traffic(kernel):
+    """dram bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json), or None."""
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        return json.load(open(tp)).get(kernel)
+    return None
+
+
+# kernels launched by one Testbed.train step (profiles/r01_nerf_launches.csv lists them): sample
+# generation, encoder + fused MLP (inference), loss/compaction + roll-over, encoder, fused MLP
+# fwd+bwd (+ partial-sum reduction), grid backward, optimizer; the occupancy update adds 9 every
+# 16th step and the loss reduction 1.
+NERF_LAUNCHES_PER_STEP = 11
+
+
+def nerf_phase_costs(prof, n_steps, compacted, marched, n_params, peaks):
+    """Per-kernel-group time, algorithmic work and roofline fraction from the library's phase timer."""
+    work = {  # name -> (bound, algorithmic units per step, unit)
+        "generate_training_samples": ("hbm", marched * 28.0, "B"),
+        "infer.grid_forward": ("hbm", marched * float(NERF_GRID_BYTES_INFER), "B"),
+        "infer.fused_mlp": ("tensor", marched * float(NERF_MLP_FLOP_INFER), "FLOP"),
+        "loss_and_compact": ("hbm", marched * 12.0 + compacted * 64.0, "B"),
+        "train.grid_forward": ("hbm", compacted * float(NERF_GRID_BYTES_INFER), "B"),
+        "train.fused_mlp_fwd_bwd": ("tensor", compacted * float(NERF_MLP_FLOP_TRAIN), "FLOP"),
+        "train.grid_backward": ("hbm", compacted * float(NERF_GRID_BYTES_INFER) + n_params * 2.0, "B"),
+        "optimizer": ("hbm", n_params * 22.0, "B"),
+    }
+    out = {}
+    for name, (ms, cnt) in prof.items():
+        per_step = ms / n_steps
+        entry = {"ms_per_step": per_step}
+        if name in work and per_step > 0:
+            bound, units, _ = work[name]
+            if bound == "hbm":
+                a = units / (per_step * 1e-3) / 1e9
+                entry.update({"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"]})
+            else:
+                a = units / (per_step * 1e-3) / 1e12
+                pk = peaks["bf16_tflops_sustained"] or peaks["bf16_tflops"]
+                entry.update({"bound": "tensor", "achieved": a, "peak": pk, "unit": "TFLOP/s", "frac": a / pk})
+        out[name] = entry
+    return out
+
+
+def run_nerf(args):
+    import numpy as np
+    import torch
+    ngp = importlib.import_module("instant-ngp-rendering_b200")
+    syn = importlib.import_module("instant-ngp-rendering_b200.synthetic")
+    tbm = importlib.import_module("instant-ngp-rendering_b200.testbed")
+    if not ngp.has_device():
+        raise RuntimeError("bench.py needs a CUDA device: ngp-b200 has no CPU fallback")
+    rank, world, local = dist_setup()
+    peaks = load_peaks()
+    dev = torch.device("cuda", local)
+    batch = FOX["batch"] * world   # weak scaling: 2^18 compacted samples per GPU and step
+    K, W = args.steps, max(args.warmup, 3)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    tb = ngp.Testbed(device=dev)
+    tb.use_current_stream()
+    scene, poses, focal = syn.make_dataset(tb, n_images=FOX["n_images"], width=FOX["width"], height=FOX["height"], aabb_scale=FOX["aabb_scale"], amp_scale=FOX["amp_scale"])
+    tb.reload_network_from_json(syn.NERF_BASE_CONFIG)
+    if world > 1:
+        tb.set_shard(rank, world)
+    step = (lambda: tb.train(batch)) if world == 1 else (lambda: tb.train_distributed(batch))
+
+    # untimed: get past the dense-occupancy phase (first 256 steps) into steady state, then warm up
+    for _ in range(FOX["pretrain_steps"]):
+        step()
+    for _ in range(W):
+        step()
+    sampler = ClockSampler(local)
+    barrier(world)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = ev(), ev()
+    compacted = marched = rays = 0
+    e0.record()
+    for _ in range(K):
+        step()
+        compacted += tb.measured_batch_size
+        marched += tb.measured_batch_size_before_compaction
+        rays += tb.rays_per_batch
+    e1.record()
+    torch.cuda.synchronize()
+    barrier(world)
+    clocks = sampler.stop() if rank == 0 else None
+    ms = reduce_over_ranks(e0.elapsed_time(e1), world)
+    value = compacted / (ms * 1e-3)     # counters are global (all-reduced) in a sharded run
+    loss = tb.loss
+
+    # phase breakdown of the same step (library phase timer = CUDA events between kernel groups)
+    P = min(K, 32)
+    tbm.profile_enable(True)
+    pc = pm = 0
+    for _ in range(P):
+        step()
+        pc += tb.measured_batch_size
+        pm += tb.measured_batch_size_before_compaction
+    torch.cuda.synchronize()
+    prof = tbm.profile_collect()
+    tbm.profile_enable(False)
+    phases = nerf_phase_costs(prof, P, pc / P / world, pm / P / world, tb.n_params, peaks)
+    timed = {k: v for k, v in phases.items() if "frac" in v}
+    dom = max(timed, key=lambda k: timed[k]["ms_per_step"]) if timed else None
+
+    # end to end: the dataset comes from pinned host memory (re-uploaded inside the timed region through
+    # set_nerf_image, as load_training_data does once per run), then K Testbed.train calls, each
+    # reading its counters / loss back to the host.
+    host_images = []
+    for i in range(FOX["n_images"]):
+        img = syn.linear_premul_to_srgb8(scene.render(poses[i], FOX["width"], FOX["height"], focal)).cpu().pin_memory()
+        host_images.append(img)
+    torch.cuda.synchronize()
+    barrier(world)
+    t0 = time.perf_counter()
+    for i, img in enumerate(host_images):
+        tb.set_nerf_image(i, img)
+    e2e_samples = 0
+    for _ in range(K):
+        step()
+        e2e_samples += tb.measured_batch_size
+    _ = tb.loss
+    torch.cuda.synchronize()
+    e2e_s = reduce_over_ranks(time.perf_counter() - t0, world)
+    h2d = sum(int(im.numel()) for im in host_images) / K
+    del host_images
+
+    # configs[3]: novel-view render of the trained model, 1920x1080, tiles sharded over the ranks
+    tb._set("render_target_queries", 16 << 20)
+    tb._set("render_min_steps", 4)
+    tb._set("render_windows_per_sync", 16)
+    rw, rh = 1920, 1080
+    shard = (rank, world)
+    view = syn.look_at_ngp(np.array([0.5, 0.5, 0.5]) + 1.4 * np.array([0.62, -0.55, 0.56]))  # not a training pose
+    for _ in range(3):
+        tb.render_nerf(rw, rh, view, focal, shard=shard)
+    frames = 5
+    host_frame = torch.empty((rh, rw, 4), dtype=torch.float32).pin_memory()
+    barrier(world)
+    r0, r1 = ev(), ev()
+    r0.record()
+    for _ in range(frames):
+        rgba, depth = tb.render_nerf(rw, rh, view, focal, shard=shard)
+    r1.record()
+    torch.cuda.synchronize()
+    render_ms = reduce_over_ranks(r0.elapsed_time(r1), world) / frames
+    queries = reduce_over_ranks(float(tb.last_render_samples), world, op="sum")
+    t0 = time.perf_counter()
+    for _ in range(frames):
+        rgba, depth = tb.render_nerf(rw, rh, view, focal, shard=shard)
+        host_frame.copy_(rgba, non_blocking=True)
+        torch.cuda.synchronize()
+    render_e2e_ms = reduce_over_ranks((time.perf_counter() - t0) * 1e3, world) / frames
+    coverage = float((rgba[..., 3] > 0.5).float().mean()) * world
+    render = {"metric": "render Mrays/s", "value": rw * rh / (render_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": render_ms, "resolution": [rw, rh],
+              "queries_per_ray": queries / (rw * rh), "gqueries_per_s": queries / (render_ms * 1e-3) / 1e9, "coverage": coverage,
+              "e2e": {"value": rw * rh / (render_e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "d2h_bytes_per_frame": rw * rh * 16 // world},
+              "sharding": f"256-pixel tiles interleaved over {world} rank(s), no communication"}
+
+    grid = grid_measure(ngp, min(K, 20), 3, rank, world, local)
+    if rank != 0:
+        return
+    cpu = cpu_nerf_baseline(n_rays=256, steps=4, budget_s=20.0)
+    roof = None
+    if dom:
+        d = timed[dom]
+        roof = {"bound": d["bound"], "kernel": dom, "achieved": d["achieved"], "peak": d["peak"], "unit": d["unit"], "frac": d["frac"],
+                "traffic": load_traffic(dom), "peak_source": peaks["source"],
+                "note": "dominant kernel group of the training step by the phase timer; per-group figures in `phases`"}
+    line = {
+        "metric": "fox NeRF train samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+        "config": {"workload": "nerf_train_fox_shape_base.json_batch2^18",
+                   "dataset": f"{FOX['n_images']} views {FOX['width']}x{FOX['height']} RGBA8, aabb_scale {FOX['aabb_scale']}, analytic blob scene rendered on the GPU",
+                   "network": "configs/nerf/base.json (HashGrid L8 F4 T2^19 + 64-wide density/rgb MLPs), Ema(ExponentialDecay(Adam))",
+                   "global_batch": batch, "pretrain_steps": FOX["pretrain_steps"],
+                   "l2": "not flushed: a step streams the 283 MB optimizer state and gathers from 415 MB of images, both larger than the 126 MB L2",
+                   "parallelism": "1 GPU" if world == 1 else f"dp{world}: rays sharded, NCCL all-reduce of {tb.n_params} fp16 gradients per step"},
+        "samples_per_step": compacted / K, "marched_samples_per_step": marched / K, "rays_per_step": rays / K, "loss": loss,
+        "phases": phases, "roofline": roof,
+        "cpu_baseline": {"value": cpu["samples_per_s"], "unit": "samples/s", "cores": cpu["cores"], "kind": "port", "sample": cpu["sample"]},
+        "e2e": {"value": e2e_samples / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 20,
+                "note": "dataset uploaded from pinned host memory inside the timed region, then K Testbed.train calls with their counter read-backs"},
+        "gpu_launches": NERF_LAUNCHES_PER_STEP * K,
+        "render": render, "grid": grid, "clocks": clocks,
+    }
+    print(json.dumps(line))
+
+
+def run_grid(args):
+    ngp = importlib.import_module("instant-ngp-rendering_b200")
+    if not ngp.has_device():
+        raise RuntimeError("bench.py needs a CUDA device: ngp-b200 has no CPU fallback")
+    rank, world, local = dist_setup()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    g = grid_measure(ngp, args.steps, args.warmup, rank, world, local)
+    clocks = sampler.stop() if rank == 0 else None
+    if rank != 0:
+        return
+    cpu_v, cpu_dt, cores = cpu_grid_baseline(1 << 18)
+    line = {"metric": g["metric"], "value": g["value"], "unit": g["unit"], "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": g["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+            "config": g["config"], "kernels_ms": g["kernels_ms"], "roofline": g["roofline"],
+            "cpu_baseline": {"value": cpu_v, "unit": "Gpts/s", "cores": cores, "kind": "port", "sample": "2^18 uniform points fwd+bwd (oracle, OpenMP)"},
+            "e2e": g["e2e"], "gpu_launches": g["gpu_launches"], "clocks": clocks}
+    print(json.dumps(line))
+
+
+def run_reference_arm(args):
+    """--impl reference. The reference has no CPU implementation of this path and its CUDA build
+    needs cmake + a GPU (DESIGN.md "Reference arm"), so the arm times the oracle port of the same
+    workload on all host threads, on a bounded sample per step. Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    if args.workload == "grid":
+        sample = 1 << 18
+        for _ in range(min(args.warmup, 2)):
+            cpu_grid_baseline(1 << 14)
+        t_total, cores = 0.0, 1
+        for _ in range(args.steps):
+            _, dt, cores = cpu_grid_baseline(sample)
+            t_total += dt
+            if t_total > 60:
+                break
+        value = sample * args.steps / t_total / 1e9
+        line = {"impl": "reference", "metric": "hash-enc fwd+bwd Gpts/s", "value": value, "unit": "Gpts/s", "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * t_total / args.steps * (GRID_N / sample), "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": {"workload": "grid_L16F2_T19_2^20pts", "sample": "2^18 of 2^20 points per step"},
+                "cpu_baseline": {"value": value, "unit": "Gpts/s", "cores": cores, "kind": "port", "sample": "2^18 uniform points, fwd+bwd, OpenMP"},
+                "e2e": {"value": value, "unit": "Gpts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+    cpu = cpu_nerf_baseline(n_rays=256, steps=max(args.steps, 1), warmup=min(args.warmup, 1), budget_s=90.0)
+    value = cpu["samples_per_s"]
+    per_step = cpu["samples"] / max(cpu["steps_done"], 1)
+    line = {"impl": "reference", "metric": "fox NeRF train samples/s", "value": value, "unit": "samples/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * cpu["seconds"] / max(cpu["steps_done"], 1) * (FOX["batch"] / max(per_step, 1)),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+            "config": {"workload": "nerf_train_fox_shape_base.json_batch2^18", "sample": cpu["sample"],
+                       "note": "ms_per_step is the measured time per oracle step scaled to the 2^18-sample batch"},
+            "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cpu["cores"], "kind": "port", "sample": cpu["sample"]},
+            "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--workload", default="grid")
+    ap.add_argument("--workload", default="nerf", choices=["nerf", "grid"])
     ap.add_argument("--impl", default="ours")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -288,7 +605,10 @@ def main():
     if args.workload == "grid":
         run_grid(args)
     else:
-        raise SystemExit(f"unknown workload {args.workload}")
+        run_nerf(args)
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -162,6 +162,10 @@ typedef struct {
 	float cone_angle_constant, near_distance, loss_scale;
 	int snap_to_pixel_centers, random_bg_color, linear_colors, color_space, loss_type, rgb_activation, density_activation;
 	float background_color[3];
+	/* Ray sharding for data-parallel training (no reference counterpart: the reference trains on one
+	 * GPU, README.md:250-252): the call handles n_rays_local rays from global index ray_begin of the
+	 * n_rays-ray batch; n_rays_local == 0 means the whole batch. */
+	uint32_t ray_begin, n_rays_local;
 } ngpb_nerf_train_config_t;
 
 typedef struct {
@@ -205,15 +209,28 @@ int ngpb_testbed_reload_network_from_json(ngpb_testbed_t* t, const char* config_
 int ngpb_testbed_reset_network(ngpb_testbed_t* t, int clear_density_grid);
 /* Testbed::train(batch_size), src/testbed.cu:4020-4109. */
 int ngpb_testbed_train(ngpb_testbed_t* t, uint32_t batch_size);
+/* Data-parallel form of ngpb_testbed_train (no reference counterpart; the reference trains on one GPU):
+ * with properties shard_rank / shard_world set, train_begin computes this rank's share of the step
+ * (rays [rank R/P, (rank+1) R/P) of the step's R rays) and leaves gradients in "gradients" and the
+ * step counters in "counters" (ngpb_nerf_counters_t); the caller all-reduces (sum) both over the
+ * ranks on the testbed's stream; train_end applies the optimizer and the ray-count control loop.
+ * batch_size is the global batch in both calls. ngpb_testbed_train == begin + end for one rank. */
+int ngpb_testbed_train_begin(ngpb_testbed_t* t, uint32_t batch_size);
+int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size);
 /* Named scalar properties (the public members pyngp binds, src/python_api.cu:481-566, 645-697):
  * training_step, loss, rays_per_batch, measured_batch_size, measured_batch_size_before_compaction,
  * n_params, max_cascade, cone_angle_constant, aabb_scale, seed, random_bg_color, linear_colors,
  * snap_to_pixel_centers, near_distance, density_grid_decay, render_min_transmittance, loss_type,
- * rgb_activation, density_activation, color_space, train_network, train_encoding, last_render_samples. */
+ * rgb_activation, density_activation, color_space, train_network, train_encoding, last_render_samples,
+ * render_target_queries, render_min_steps, render_max_steps (the window policy of NerfTracer::trace,
+ * src/testbed_nerf.cu:1693-1694), render_windows_per_sync, render_snap_to_pixel_centers,
+ * shard_rank, shard_world (training ray shards), render_shard_rank, render_shard_world (render_nerf
+ * then traces only the 256-pixel tiles t of [pixel_begin, pixel_end) with t % world == rank). */
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value);
 int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value);
 /* Device buffers by name: params (fp16), params_fp32, params_inference (fp16), gradients (fp16),
- * density_grid (float), density_grid_bitfield (uint8), density_grid_mean (float), metadata. */
+ * density_grid (float), density_grid_bitfield (uint8), density_grid_mean (float), metadata,
+ * counters (ngpb_nerf_counters_t of the last step). */
 int ngpb_testbed_device_ptr(ngpb_testbed_t* t, const char* name, void** ptr, size_t* bytes);
 size_t ngpb_testbed_network_config(const ngpb_testbed_t* t, char* buf, size_t cap);
 /* update_density_grid_nerf(decay, n_uniform, n_nonuniform), src/testbed_nerf.cu:2271-2360. */

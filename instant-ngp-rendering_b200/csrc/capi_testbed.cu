@@ -88,11 +88,23 @@ int ngpb_testbed_train(ngpb_testbed_t* t, uint32_t batch_size) {
 	NGPB_API_END
 }
 
+int ngpb_testbed_train_begin(ngpb_testbed_t* t, uint32_t batch_size) {
+	NGPB_API_BEGIN
+	t->impl->train_begin(batch_size);
+	NGPB_API_END
+}
+int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size) {
+	NGPB_API_BEGIN
+	t->impl->train_end(batch_size);
+	NGPB_API_END
+}
+
 #define NGPB_PROPS(X) \
 	X(rays_per_batch) X(measured_batch_size) X(measured_batch_size_before_compaction) X(seed) X(random_bg_color) X(linear_colors) \
 	X(snap_to_pixel_centers) X(near_distance) X(density_grid_decay) X(render_min_transmittance) X(loss_type) X(rgb_activation) \
 	X(density_activation) X(color_space) X(train_network) X(train_encoding) X(aabb_scale) \
-	X(render_target_queries) X(render_min_steps) X(render_max_steps) X(render_windows_per_sync) X(render_snap_to_pixel_centers)
+	X(render_target_queries) X(render_min_steps) X(render_max_steps) X(render_windows_per_sync) X(render_snap_to_pixel_centers) \
+	X(shard_rank) X(shard_world) X(render_shard_rank) X(render_shard_world)
 
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
 	NGPB_API_BEGIN
@@ -137,6 +149,7 @@ int ngpb_testbed_device_ptr(ngpb_testbed_t* t, const char* name, void** ptr, siz
 	else if (n == "density_grid") { p = tb.density_grid(); b = n_grid * 4; }
 	else if (n == "density_grid_bitfield") { p = tb.density_grid_bitfield(); b = nerf_bitfield_bytes(); }
 	else if (n == "density_grid_mean") { p = tb.density_grid_mean(); b = 4; }
+	else if (n == "counters") { p = tb.counters(); b = sizeof(NerfStepCounters); }
 	else if (n == "metadata") { tb.upload_metadata(); p = (void*)tb.metadata_gpu(); b = tb.n_images() * sizeof(ImageMeta); }
 	else throw std::runtime_error{"ngpb_testbed_device_ptr: unknown buffer " + n};
 	if (ptr) *ptr = p;

@@ -37,7 +37,14 @@ struct NerfTrainConfig {
 	int rgb_activation;
 	int density_activation;
 	float background_color[3];
+	// Ray sharding (data-parallel training): this call handles the n_rays_local rays starting at
+	// global index ray_begin of the n_rays-ray batch; image choice, per-ray RNG position and the
+	// 1/n_rays loss normalisation use the GLOBAL index and count, so the union of the shards is the
+	// single-GPU batch. n_rays_local == 0 means the whole batch.
+	uint32_t ray_begin;
+	uint32_t n_rays_local;
 };
+NGPB_HD uint32_t local_ray_count(const NerfTrainConfig& c) { return c.n_rays_local ? c.n_rays_local : c.n_rays; }
 
 struct NerfTrainBuffers {
 	const ImageMeta* metadata;        // [n_training_images]

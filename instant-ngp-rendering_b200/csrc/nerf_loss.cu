@@ -163,8 +163,8 @@ __global__ void fill_rollover_kernel(uint32_t n_elements, const NerfStepCounters
 }
 
 void nerf_compute_loss_and_compact(cudaStream_t stream, const NerfTrainConfig& cfg, const NerfTrainBuffers& buf, Pcg32 rng) {
-	if (cfg.n_rays == 0) return;
-	compute_loss_kernel<<<div_round_up(cfg.n_rays, kRayBlock), kRayBlock, 0, stream>>>(cfg, buf, rng);
+	if (local_ray_count(cfg) == 0) return;
+	compute_loss_kernel<<<div_round_up(local_ray_count(cfg), kRayBlock), kRayBlock, 0, stream>>>(cfg, buf, rng);
 	NGPB_CUDA_CHECK(cudaGetLastError());
 	fill_rollover_kernel<<<div_round_up(cfg.max_samples_compacted, 256), 256, 0, stream>>>(cfg.max_samples_compacted, buf.counters, buf.coords_compacted, buf.dloss_doutput);
 	NGPB_CUDA_CHECK(cudaGetLastError());

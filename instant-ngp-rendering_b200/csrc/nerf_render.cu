@@ -37,13 +37,16 @@ struct RenderParams {
 	uint32_t width, height;
 	float focal_x, focal_y, screen_cx, screen_cy;
 	uint32_t spp_index;
-	uint32_t pixel_begin, pixel_end;
+	uint32_t pixel_begin, pixel_end, n_local;
 	uint32_t max_mip;
+	uint32_t shard_rank, shard_world; // tile interleave over ranks (kRenderTile pixels per tile)
 	uint32_t capacity;        // rays per plane
 	uint32_t target_queries, min_steps, max_steps;
 	float min_transmittance;
 	int rgb_activation, density_activation, linear_colors, snap_to_pixel_centers;
 };
+
+constexpr uint32_t kRenderTile = 256;
 
 NGPB_D uint32_t window_length(const RenderParams& p, uint32_t n_alive) {
 	// clamp(target_n_queries / n_alive, MIN, MAX_STEPS_INBETWEEN_COMPACTION) (:1693-1694)
@@ -58,8 +61,9 @@ __global__ void __launch_bounds__(kRayBlock) render_init_rays_kernel(const __gri
 {
 	__shared__ uint32_t warp_sums[kRayBlock / 32 + 1];
 	__shared__ uint32_t block_base;
-	const uint32_t pix = p.pixel_begin + blockIdx.x * blockDim.x + threadIdx.x;
-	bool alive = pix < p.pixel_end;
+	const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t pix = p.pixel_begin + ((local / kRenderTile) * p.shard_world + p.shard_rank) * kRenderTile + local % kRenderTile;
+	bool alive = local < p.n_local && pix < p.pixel_end;
 	V3 o{}, d{};
 	float t = 0.0f;
 	if (alive) {
@@ -212,7 +216,11 @@ void Testbed::render_nerf(uint32_t width, uint32_t height, const float* camera_3
 	pixel_end = std::min(pixel_end, n_pixels);
 	last_render_samples = 0;
 	if (pixel_begin >= pixel_end) return;
-	const uint32_t n_rays = pixel_end - pixel_begin;
+	if (render_shard_world == 0 || render_shard_rank >= render_shard_world) throw std::runtime_error{"ngp-b200: render_shard_rank must be < render_shard_world"};
+	const uint32_t n_tiles = div_round_up(pixel_end - pixel_begin, kRenderTile);
+	const uint32_t my_tiles = n_tiles > render_shard_rank ? div_round_up(n_tiles - render_shard_rank, render_shard_world) : 0;
+	const uint32_t n_rays = render_shard_world == 1 ? pixel_end - pixel_begin : my_tiles * kRenderTile;
+	if (n_rays == 0) return;
 
 	RenderParams p{};
 	p.aabb = m_aabb;
@@ -222,6 +230,8 @@ void Testbed::render_nerf(uint32_t width, uint32_t height, const float* camera_3
 	p.spp_index = spp_index;
 	p.pixel_begin = pixel_begin; p.pixel_end = pixel_end;
 	p.max_mip = m_max_cascade;
+	p.n_local = n_rays;
+	p.shard_rank = render_shard_rank; p.shard_world = render_shard_world;
 	p.capacity = next_multiple(n_rays, kBatchSizeGranularity);
 	p.target_queries = std::max(render_target_queries, 1u);
 	p.min_steps = std::max(render_min_steps, 1u);

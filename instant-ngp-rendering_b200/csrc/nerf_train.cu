@@ -16,8 +16,9 @@ __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(co
 	__shared__ uint32_t warp_sums[kRayBlock / 32 + 1];
 	__shared__ uint32_t block_base, block_ray_base;
 
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	bool valid = i < cfg.n_rays;
+	const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
+	bool valid = local < local_ray_count(cfg);
+	const uint32_t i = cfg.ray_begin + local; // global ray index
 
 	Ray3 ray{};
 	V3 dir_n{}, idir{};
@@ -101,9 +102,9 @@ __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(co
 }
 
 void nerf_generate_training_samples(cudaStream_t stream, const NerfTrainConfig& cfg, const NerfTrainBuffers& buf, Pcg32 rng) {
-	if (cfg.n_rays == 0) return;
+	if (local_ray_count(cfg) == 0) return;
 	const Stepping stepping = make_stepping(cfg.cone_angle_constant);
-	generate_training_samples_kernel<<<div_round_up(cfg.n_rays, kRayBlock), kRayBlock, 0, stream>>>(cfg, buf, stepping, rng);
+	generate_training_samples_kernel<<<div_round_up(local_ray_count(cfg), kRayBlock), kRayBlock, 0, stream>>>(cfg, buf, stepping, rng);
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }
 

@@ -38,6 +38,15 @@ public:
 
 	// ---- training (Testbed::train)
 	void train(uint32_t batch_size);
+	// Data-parallel form of train(): train_begin leaves this rank's gradients (rays
+	// [rank R/P, (rank+1) R/P) of the step's R rays, batch_size / P compacted samples) in
+	// gradients() and its counters in counters(); the caller sums both over the ranks (NCCL
+	// all-reduce on the same stream); train_end runs the optimizer and the batch-size control loop
+	// on the summed values. batch_size is the GLOBAL batch in both calls.
+	void train_begin(uint32_t batch_size);
+	void train_end(uint32_t batch_size);
+	uint32_t shard_rank = 0, shard_world = 1;
+	NerfStepCounters* counters() { return m_counters.as<NerfStepCounters>(); }
 	float loss() const { return m_loss_scalar; }
 	uint32_t training_step() const { return m_training_step; }
 
@@ -103,13 +112,16 @@ public:
 	uint32_t render_min_steps = 1;
 	uint32_t render_max_steps = 8;
 	uint32_t render_windows_per_sync = 8;
+	// Tile sharding: with render_shard_world > 1 only the 256-pixel tiles t of the pixel range with
+	// t % render_shard_world == render_shard_rank are traced (the others stay untouched).
+	uint32_t render_shard_rank = 0, render_shard_world = 1;
 	bool render_snap_to_pixel_centers = false; // Testbed::m_snap_to_pixel_centers (testbed.h:995)
 	// Optional DEVICE buffer [height * width] receiving the number of samples composited per pixel.
 	void set_render_steps_out(uint32_t* p) { m_render_steps_out = p; }
 
 private:
 	void training_prep_nerf();
-	void train_nerf(uint32_t target_batch_size, bool get_loss_scalar);
+	bool m_get_loss_scalar = false;
 	void train_nerf_step(uint32_t target_batch_size);
 
 	cudaStream_t m_stream = nullptr;

@@ -64,9 +64,17 @@ void Testbed::training_prep_nerf() {
 }
 
 void Testbed::train(uint32_t batch_size) {
+	if (shard_world > 1) throw std::runtime_error{"ngp-b200: a sharded testbed trains with train_begin / all-reduce / train_end"};
+	train_begin(batch_size);
+	train_end(batch_size);
+}
+
+void Testbed::train_begin(uint32_t batch_size) {
 	if (n_images() == 0) throw std::runtime_error{"Cannot train without training data."};
 	if (!m_network) throw std::runtime_error{"Unable to create a neural network trainer."};
 	if (batch_size == 0 || batch_size % kBatchSizeGranularity != 0) throw std::runtime_error{"ngp-b200: batch size must be a positive multiple of 256"};
+	if (shard_world == 0 || shard_rank >= shard_world || (batch_size / shard_world) % kBatchSizeGranularity != 0 || batch_size % shard_world != 0 || kBatchSizeGranularity % shard_world != 0)
+		throw std::runtime_error{"ngp-b200: shard_world must divide 256 and leave a per-rank batch that is a multiple of 256"};
 	upload_metadata();
 
 	const uint32_t n_prep_to_skip = std::min(std::max(m_training_step / 16u, 1u), 16u);
@@ -81,8 +89,9 @@ void Testbed::train(uint32_t batch_size) {
 	leaf["optimize_non_matrix_params"] = train_encoding;
 	m_optimizer->update_hyperparams(leaf);
 
-	const bool get_loss_scalar = m_training_step % 16 == 0;
-	train_nerf(batch_size, get_loss_scalar);
+	m_get_loss_scalar = m_training_step % 16 == 0;
+	train_nerf_step(batch_size / shard_world);
+	if (m_get_loss_scalar) reduce_loss_kernel<<<sm_count(), 256, 0, m_stream>>>(rays_per_batch / shard_world, m_loss.as<float>(), &m_counters.as<NerfStepCounters>()->loss_sum);
 }
 
 void Testbed::train_nerf_step(uint32_t target_batch_size) {
@@ -98,7 +107,8 @@ void Testbed::train_nerf_step(uint32_t target_batch_size) {
 	m_dloss.reserve((size_t)target_batch_size * 4 * sizeof(__half), m_stream);
 
 	NGPB_CUDA_CHECK(cudaMemsetAsync(m_counters.ptr, 0, sizeof(NerfStepCounters), m_stream));
-	NGPB_CUDA_CHECK(cudaMemsetAsync(m_loss.ptr, 0, sizeof(float) * rays_per_batch, m_stream));
+	const uint32_t n_rays_local = rays_per_batch / shard_world; // rays_per_batch is a multiple of 256, shard_world divides 256
+	NGPB_CUDA_CHECK(cudaMemsetAsync(m_loss.ptr, 0, sizeof(float) * n_rays_local, m_stream));
 	// dloss / coords of a batch that the loss kernel does not fill completely and whose roll-over
 	// finds no input must not carry stale gradients
 	NGPB_CUDA_CHECK(cudaMemsetAsync(m_dloss.ptr, 0, (size_t)target_batch_size * 4 * sizeof(__half), m_stream));
@@ -113,6 +123,8 @@ void Testbed::train_nerf_step(uint32_t target_batch_size) {
 	NerfTrainConfig cfg{};
 	cfg.aabb = m_aabb;
 	cfg.n_rays = rays_per_batch;
+	cfg.ray_begin = shard_rank * n_rays_local;
+	cfg.n_rays_local = n_rays_local;
 	cfg.n_rays_total = n_rays_total_before;
 	cfg.max_samples = max_samples;
 	cfg.max_samples_compacted = target_batch_size;
@@ -154,15 +166,16 @@ void Testbed::train_nerf_step(uint32_t target_batch_size) {
 	m_rng.advance(1ll << 32);
 }
 
-void Testbed::train_nerf(uint32_t target_batch_size, bool get_loss_scalar) {
-	train_nerf_step(target_batch_size);
+void Testbed::train_end(uint32_t target_batch_size) {
+	// In a sharded run the caller has all-reduced the gradients and the counters between
+	// train_begin and train_end, so every rank steps the same parameters with the same counts.
+	const bool get_loss_scalar = m_get_loss_scalar;
 	prof_mark(m_stream, "optimizer");
 	m_optimizer->step(m_stream, kLossScaleFp16, params_fp32(), params(), gradients());
 	prof_mark(m_stream, "end");
 	++m_training_step;
 
 	// NerfCounters::update_after_training (:2422-2446)
-	if (get_loss_scalar) reduce_loss_kernel<<<sm_count(), 256, 0, m_stream>>>(rays_per_batch, m_loss.as<float>(), &m_counters.as<NerfStepCounters>()->loss_sum);
 	NGPB_CUDA_CHECK(cudaMemcpyAsync(m_counters_host, m_counters.ptr, sizeof(NerfStepCounters), cudaMemcpyDeviceToHost, m_stream));
 	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
 	measured_batch_size = 0;

@@ -209,6 +209,32 @@ class Testbed:
     def train(self, batch_size=1 << 18):
         check(lib.ngpb_testbed_train(self._h, batch_size))
 
+    # -- data-parallel training (one process per GPU; no reference counterpart) --------------------
+    def set_shard(self, rank, world):
+        """This testbed computes rays [rank R/P, (rank+1) R/P) of every step's R rays."""
+        self._set("shard_world", 1)
+        self._set("shard_rank", 0)
+        self._set("shard_world", world)
+        self._set("shard_rank", rank)
+        self._dp = None
+
+    def train_distributed(self, batch_size=1 << 18, group=None):
+        """Testbed.train for a sharded run: local gradients, all-reduce (sum) of the gradients and
+        the step counters over `group` with torch.distributed (NCCL over NVLink on GPUs, gloo in
+        the CPU tests of the host logic), then the optimizer step on every rank. Needs
+        use_current_stream() so that the collectives are ordered with the kernels."""
+        import torch.distributed as dist
+        check(lib.ngpb_testbed_train_begin(self._h, batch_size))
+        if self._get("shard_world") > 1:
+            if getattr(self, "_dp", None) is None:
+                c = self.device_buffer("counters", torch.int32)
+                self._dp = (self.device_buffer("gradients", torch.float16), c[:3], c[3:4].view(torch.float32))
+            grads, counts, loss_sum = self._dp
+            dist.all_reduce(grads, group=group)
+            dist.all_reduce(counts, group=group)
+            dist.all_reduce(loss_sum, group=group)
+        check(lib.ngpb_testbed_train_end(self._h, batch_size))
+
     def frame(self):
         """Headless Testbed::frame: one training step when shall_train (src/testbed.cu:3380-3479)."""
         if self.shall_train:
@@ -226,10 +252,11 @@ class Testbed:
         check(lib.ngpb_testbed_update_density_grid(self._h, decay, n_uniform, n_nonuniform))
 
     # -- rendering -------------------------------------------------------------------------------
-    def render_nerf(self, width, height, camera_3x4, focal, principal=(0.5, 0.5), spp_index=0, pixel_range=None, return_steps=False):
+    def render_nerf(self, width, height, camera_3x4, focal, principal=(0.5, 0.5), spp_index=0, pixel_range=None, return_steps=False, shard=None):
         """Linear premultiplied RGBA float32 [h][w][4] and depth [h][w] on the device. camera_3x4 in
         NGP convention; focal in pixels. pixel_range=(begin, end) renders a slice of the row-major
-        pixel list (tile sharding); the rest stays zero. return_steps adds the per-pixel count of
+        pixel list; shard=(rank, world) traces only this rank's 256-pixel tiles of that range (tile
+        sharding across GPUs, no communication); the rest stays zero. return_steps adds the per-pixel count of
         composited samples (int32 [h][w])."""
         rgba = torch.zeros((height, width, 4), dtype=torch.float32, device=self._device)
         depth = torch.zeros((height, width), dtype=torch.float32, device=self._device)
@@ -237,6 +264,10 @@ class Testbed:
         cam = np.ascontiguousarray(camera_3x4, dtype=np.float32)
         fx, fy = (focal, focal) if np.isscalar(focal) else focal
         b, e = pixel_range if pixel_range is not None else (0, width * height)
+        rank, world = shard if shard is not None else (0, 1)
+        self._set("render_shard_rank", 0)
+        self._set("render_shard_world", world)
+        self._set("render_shard_rank", rank)
         torch.cuda.current_stream().synchronize()  # the testbed runs on its own stream unless use_current_stream()
         check(lib.ngpb_testbed_set_render_steps_out(self._h, ctypes.c_void_p(steps.data_ptr()) if return_steps else None))
         try:

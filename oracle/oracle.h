@@ -100,6 +100,7 @@ typedef struct {
 	float cone_angle_constant, near_distance, loss_scale;
 	int snap_to_pixel_centers, random_bg_color, linear_colors, color_space, loss_type, rgb_activation, density_activation;
 	float background_color[3];
+	uint32_t ray_begin, n_rays_local; /* layout parity with ngpb_nerf_train_config_t; the oracle always walks the whole batch */
 } oracle_nerf_config;
 /* generate_training_samples_nerf (src/testbed_nerf.cu:679-838), rays in index order. */
 uint64_t oracle_nerf_generate_samples(const oracle_nerf_config* cfg, const oracle_nerf_image* images, const uint8_t* bitfield,

@@ -260,7 +260,8 @@ class NerfConfig(ctypes.Structure):
                 ("n_training_images", ctypes.c_uint32), ("max_mip", ctypes.c_uint32),
                 ("cone_angle_constant", ctypes.c_float), ("near_distance", ctypes.c_float), ("loss_scale", ctypes.c_float),
                 ("snap_to_pixel_centers", ctypes.c_int), ("random_bg_color", ctypes.c_int), ("linear_colors", ctypes.c_int), ("color_space", ctypes.c_int),
-                ("loss_type", ctypes.c_int), ("rgb_activation", ctypes.c_int), ("density_activation", ctypes.c_int), ("background_color", ctypes.c_float * 3)]
+                ("loss_type", ctypes.c_int), ("rgb_activation", ctypes.c_int), ("density_activation", ctypes.c_int), ("background_color", ctypes.c_float * 3),
+                ("ray_begin", ctypes.c_uint32), ("n_rays_local", ctypes.c_uint32)]
 
 
 class NerfBuffers(ctypes.Structure):
