@@ -152,8 +152,11 @@ class Testbed:
             pass
 
     def use_current_stream(self):
-        """Run every call on torch's current stream (so that torch CUDA events bracket the work)."""
-        check(lib.ngpb_testbed_set_stream(self._h, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        """Run every call on torch's current stream (so that torch CUDA events bracket the work and
+        torch.distributed collectives are ordered with it). torch's default stream has handle 0,
+        which the C ABI reads as "the testbed's own stream": pass cudaStreamLegacy (0x1) instead."""
+        handle = torch.cuda.current_stream().cuda_stream or 1
+        check(lib.ngpb_testbed_set_stream(self._h, ctypes.c_void_p(handle)))
 
     # -- dataset ---------------------------------------------------------------------------------
     def create_empty_nerf_dataset(self, n_images, aabb_scale=1, is_hdr=False):
@@ -223,16 +226,13 @@ class Testbed:
         the step counters over `group` with torch.distributed (NCCL over NVLink on GPUs, gloo in
         the CPU tests of the host logic), then the optimizer step on every rank. Needs
         use_current_stream() so that the collectives are ordered with the kernels."""
-        import torch.distributed as dist
         check(lib.ngpb_testbed_train_begin(self._h, batch_size))
         if self._get("shard_world") > 1:
             if getattr(self, "_dp", None) is None:
                 c = self.device_buffer("counters", torch.int32)
                 self._dp = (self.device_buffer("gradients", torch.float16), c[:3], c[3:4].view(torch.float32))
-            grads, counts, loss_sum = self._dp
-            dist.all_reduce(grads, group=group)
-            dist.all_reduce(counts, group=group)
-            dist.all_reduce(loss_sum, group=group)
+            from .sharding import allreduce_step
+            allreduce_step(*self._dp, group=group)
         check(lib.ngpb_testbed_train_end(self._h, batch_size))
 
     def frame(self):

@@ -1,0 +1,109 @@
+"""Data-parallel paths on ONE GPU: ranks are emulated by several testbeds / several calls in one
+process, the all-reduce by adding the buffers. Checks that the union of the shards is the
+single-GPU batch (bit-exact sample sets), that tile-sharded rendering reproduces the frame, and
+that ranks stepping on summed gradients keep bit-identical parameters."""
+import ctypes
+import importlib
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+from test_nerf_gpu import _scene, _config, _Device, _generate  # noqa: E402
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_sharded_sample_generation_is_the_single_gpu_batch(ngp, oracle, world):
+    sharding = importlib.import_module("instant-ngp-rendering_b200.sharding")
+    rng = np.random.default_rng(5)
+    images, grid, max_cascade = _scene(oracle, rng, 5, (64, 48), aabb_scale=4, with_mask=True)
+    bitfield, mean = oracle.nerf_bitfield(max_cascade, grid)
+    n_rays, max_samples = 2048, 1 << 21
+    cfg = _config(oracle, n_rays, len(images), 4, max_cascade, max_samples, 1 << 20)
+    step_rng = oracle.Pcg32State(1337)
+    want_n, want_rays, want_coords, want_total = oracle.nerf_generate_samples(cfg, images, bitfield, step_rng, max_samples)
+    want_base = np.concatenate([[0], np.cumsum(want_n.astype(np.int64))])[:-1]
+    seen, total = [], 0
+    for rank in range(world):
+        b, e = sharding.ray_shard(rank, world, n_rays)
+        cfg.ray_begin, cfg.n_rays_local = b, e - b
+        dev = _Device(ngp, oracle, cfg, images, bitfield, mean)
+        t, kept = _generate(ngp, oracle, cfg, dev, step_rng)
+        total += t
+        ray_indices = dev.ray_indices.cpu().numpy().view(np.uint32)[:kept]
+        numsteps = dev.numsteps.cpu().numpy().view(np.uint32)[:kept]
+        coords = dev.coords.cpu().numpy()
+        assert ((ray_indices >= b) & (ray_indices < e)).all()
+        assert t == int(want_n[b:e].sum())
+        for k in range(kept):
+            i, n, base = int(ray_indices[k]), int(numsteps[k, 0]), int(numsteps[k, 1])
+            assert n == int(want_n[i])
+            assert np.array_equal(coords[base:base + n].view(np.uint32), want_coords[want_base[i]:want_base[i] + n].view(np.uint32))
+        seen += ray_indices.tolist()
+    assert total == want_total
+    assert sorted(seen) == np.nonzero(want_n)[0].tolist()
+
+
+def _make(ngp, syn, rank=0, world=1):
+    tb = ngp.Testbed()
+    tb.use_current_stream()
+    scene, poses, focal = syn.make_dataset(tb, n_images=8, width=96, height=72, aabb_scale=2)
+    tb.reload_network_from_json(dict(syn.NERF_BASE_CONFIG))
+    if world > 1:
+        tb.set_shard(rank, world)
+    return tb, poses, focal
+
+
+def test_emulated_two_rank_training_and_tile_sharded_render(ngp):
+    syn = importlib.import_module("instant-ngp-rendering_b200.synthetic")
+    check, lib = ngp._lib.check, ngp.lib
+    batch = 1 << 14
+    ranks = [_make(ngp, syn, r, 2) for r in range(2)]
+    single, poses, focal = _make(ngp, syn)
+    tbs = [r[0] for r in ranks]
+    grads = [tb.device_buffer("gradients", torch.float16) for tb in tbs]
+    counters = [tb.device_buffer("counters", torch.int32) for tb in tbs]
+    for step in range(60):
+        single.train(batch)
+        for tb in tbs:
+            check(lib.ngpb_testbed_train_begin(tb._h, batch))
+        if step == 0:
+            # same parameters, same step: the two shards see the single-GPU batch between them
+            c = [x.cpu().numpy().view(np.uint32) for x in counters]
+            assert int(c[0][0] + c[1][0]) == single.measured_batch_size_before_compaction
+        # all-reduce (sum) emulated on one device: every rank ends with the same buffers
+        g = grads[0].float() + grads[1].float()
+        cs = counters[0][:3] + counters[1][:3]
+        ls = counters[0][3:4].view(torch.float32) + counters[1][3:4].view(torch.float32)
+        for k in range(2):
+            grads[k].copy_(g.half())
+            counters[k][:3].copy_(cs)
+            counters[k][3:4].view(torch.float32).copy_(ls)
+        for tb in tbs:
+            check(lib.ngpb_testbed_train_end(tb._h, batch))
+        assert tbs[0].rays_per_batch == tbs[1].rays_per_batch
+    p0 = tbs[0].device_buffer("params", torch.float16)
+    p1 = tbs[1].device_buffer("params", torch.float16)
+    assert torch.equal(p0, p1), "ranks stepping on the same summed gradients must stay bit-identical"
+    assert tbs[0].training_step == 60 and tbs[0].loss < 0.5 * 0.03
+    # the sharded run learns like the single-GPU run (same batches up to roll-over padding)
+    assert abs(np.log(tbs[0].loss / single.loss)) < np.log(2.5), (tbs[0].loss, single.loss)
+
+    # tile-sharded rendering: 4 "ranks" each trace their tiles; the sum is the full frame, bit for bit
+    w, h = 96, 72
+    full, full_depth = tbs[0].render_nerf(w, h, poses[2], focal)
+    acc = torch.zeros_like(full)
+    sharding = importlib.import_module("instant-ngp-rendering_b200.sharding")
+    for r in range(4):
+        part, _ = tbs[0].render_nerf(w, h, poses[2], focal, shard=(r, 4))
+        mine = torch.zeros(w * h, dtype=torch.bool, device=part.device)
+        mine[torch.from_numpy(sharding.tile_shard_pixels(r, 4, 0, w * h)).to(part.device)] = True
+        assert (part.reshape(-1, 4)[~mine] == 0).all()
+        acc += part
+    assert torch.equal(acc, full)
+    with pytest.raises(ngp.NgpbError):
+        tbs[0].train(batch)  # a sharded testbed must go through train_begin / train_end
+    for tb in tbs + [single]:
+        tb.close()
