@@ -36,7 +36,8 @@ GRID_BYTES_PER_POINT_FWD = 12 + 512 + 64    # xyz + 16 levels x 8 corners x 4 B 
 GRID_BYTES_PER_POINT_BWD = 12 + 64 + 512    # xyz + dL/dy + scatter RMW counted once
 
 # fox shape (data/nerf/fox: 50 views 1080 x 1920, aabb_scale 4) and configs/nerf/base.json
-FOX = {"n_images": 50, "width": 1920, "height": 1080, "aabb_scale": 4, "batch": 1 << 18, "amp_scale": 8.0, "pretrain_steps": 512}
+FOX = {"n_images": 50, "width": 1920, "height": 1080, "aabb_scale": 4, "batch": 1 << 18, "amp_scale": 8.0,
+       "pretrain_steps": int(os.environ.get("NGPB_BENCH_PRETRAIN", "512"))}  # the override exists for short ncu captures
 NERF_MLP_FLOP_TRAIN = 61440      # per trained sample, fwd+bwd
 NERF_MLP_FLOP_INFER = 20480      # per marched sample
 NERF_GRID_BYTES_TRAIN = 1176     # per trained sample (encoder fwd+bwd)

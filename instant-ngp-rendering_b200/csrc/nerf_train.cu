@@ -5,13 +5,21 @@
 // (src/testbed_nerf.cu:800,807,997). Here a block scans its rays' counts (warp shuffles + one
 // shared-memory step) and claims one contiguous range per block, so a 2^18-ray batch costs 2^11
 // atomics instead of 2^19 and the rays of a block stay contiguous in the sample buffers.
+//
+// Emission: the reference marches every ray twice in the same thread (count, then emit). Here the
+// counting pass also records t at every 32nd sample, and a second kernel re-marches each 32-sample
+// segment from its checkpoint in its own thread, so a 600-sample ray is emitted by 19 threads
+// instead of one. The arithmetic from a checkpoint on is the serial loop's, bit for bit.
 #include "nerf.h"
 #include "block_scan.cuh"
+#include "module.h"
 
 namespace ngpb {
 
+constexpr uint32_t kEmitSegment = 32; // samples per emission thread; kNerfSteps / 32 = 32 checkpoints per ray
+
 __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(const __grid_constant__ NerfTrainConfig cfg, const __grid_constant__ NerfTrainBuffers buf,
-	const __grid_constant__ Stepping stepping, Pcg32 rng)
+	const __grid_constant__ Stepping stepping, Pcg32 rng, float* __restrict__ checkpoints)
 {
 	__shared__ uint32_t warp_sums[kRayBlock / 32 + 1];
 	__shared__ uint32_t block_base, block_ray_base;
@@ -51,8 +59,13 @@ __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(co
 			while (aabb_contains(cfg.aabb, pos = ray.o + t * dir_n) && j < kNerfSteps) {
 				const float dt = calc_dt(t, stepping);
 				const uint32_t mip = mip_from_dt(dt, pos, cfg.max_mip);
-				if (density_grid_occupied_at(pos, buf.density_bitfield, mip)) { ++j; t += dt; }
-				else t = advance_to_next_voxel(t, stepping, pos, dir_n, idir, mip);
+				if (density_grid_occupied_at(pos, buf.density_bitfield, mip)) {
+					if (j % kEmitSegment == 0) checkpoints[(size_t)local * kEmitSegment + j / kEmitSegment] = t;
+					++j;
+					t += dt;
+				} else {
+					t = advance_to_next_voxel(t, stepping, pos, dir_n, idir, mip);
+				}
 			}
 			numsteps = j;
 			if (j == 0) valid = false;
@@ -78,14 +91,29 @@ __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(co
 	ro[0] = ray.o.x; ro[1] = ray.o.y; ro[2] = ray.o.z; ro[3] = ray.d.x; ro[4] = ray.d.y; ro[5] = ray.d.z;
 	buf.numsteps[ray_idx * 2 + 0] = numsteps;
 	buf.numsteps[ray_idx * 2 + 1] = base;
+}
 
-	// second pass: emit the samples
+// Thread per (kept ray, 32-sample segment): samples [32 s, min(32 s + 32, numsteps)) from checkpoint s.
+__global__ void __launch_bounds__(kRayBlock) emit_training_samples_kernel(const __grid_constant__ NerfTrainConfig cfg, const __grid_constant__ NerfTrainBuffers buf,
+	const __grid_constant__ Stepping stepping, const float* __restrict__ checkpoints)
+{
+	const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t ray_idx = tid / kEmitSegment, seg = tid % kEmitSegment;
+	if (ray_idx >= buf.counters->rays) return;
+	const uint32_t numsteps = buf.numsteps[ray_idx * 2 + 0], base = buf.numsteps[ray_idx * 2 + 1];
+	uint32_t j = seg * kEmitSegment;
+	if (j >= numsteps) return;
+	const uint32_t end = min(numsteps, j + kEmitSegment);
+	const uint32_t local = buf.ray_indices[ray_idx] - cfg.ray_begin;
+	const float* ro = buf.rays_unnormalized + (size_t)ray_idx * 6;
+	const V3 o = {ro[0], ro[1], ro[2]};
+	const V3 dir_n = normalize(v3(ro[3], ro[4], ro[5]));
+	const V3 idir = v3(1.0f) / dir_n;
 	const V3 warped_dir = warp_direction(dir_n);
 	float* out = buf.coords + (size_t)base * kCoordFloats;
-	float t = startt;
-	uint32_t j = 0;
+	float t = checkpoints[(size_t)local * kEmitSegment + seg];
 	V3 pos;
-	while (aabb_contains(cfg.aabb, pos = ray.o + t * dir_n) && j < numsteps) {
+	while (aabb_contains(cfg.aabb, pos = o + t * dir_n) && j < end) {
 		const float dt = calc_dt(t, stepping);
 		const uint32_t mip = mip_from_dt(dt, pos, cfg.max_mip);
 		if (density_grid_occupied_at(pos, buf.density_bitfield, mip)) {
@@ -104,7 +132,11 @@ __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(co
 void nerf_generate_training_samples(cudaStream_t stream, const NerfTrainConfig& cfg, const NerfTrainBuffers& buf, Pcg32 rng) {
 	if (local_ray_count(cfg) == 0) return;
 	const Stepping stepping = make_stepping(cfg.cone_angle_constant);
-	generate_training_samples_kernel<<<div_round_up(local_ray_count(cfg), kRayBlock), kRayBlock, 0, stream>>>(cfg, buf, stepping, rng);
+	const uint32_t n_local = local_ray_count(cfg);
+	DeviceBuffer checkpoints((size_t)n_local * kEmitSegment * sizeof(float), stream); // stream-ordered, returned to the pool at scope exit
+	generate_training_samples_kernel<<<div_round_up(n_local, kRayBlock), kRayBlock, 0, stream>>>(cfg, buf, stepping, rng, checkpoints.as<float>());
+	NGPB_CUDA_CHECK(cudaGetLastError());
+	emit_training_samples_kernel<<<(uint32_t)div_round_up64((uint64_t)n_local * kEmitSegment, kRayBlock), kRayBlock, 0, stream>>>(cfg, buf, stepping, checkpoints.as<float>());
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }
 
