@@ -21,6 +21,8 @@ struct Context {
 	virtual ~Context() {}
 };
 
+void keep_pool_memory(); // runtime.cu: sets the default mempool's release threshold once per device
+
 // Device scratch owned by a context or a module call; freed on the stream it was made on.
 struct DeviceBuffer {
 	void* ptr = nullptr;
@@ -43,6 +45,7 @@ struct DeviceBuffer {
 		if (n == 0) return;
 		stream = s;
 		bytes = n;
+		keep_pool_memory();
 		NGPB_CUDA_CHECK(cudaMallocAsync(&ptr, n, s));
 	}
 	// Grows only; contents are not preserved.

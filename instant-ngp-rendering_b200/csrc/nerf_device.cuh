@@ -19,6 +19,7 @@
 #include "common.cuh"
 
 #include <cfloat>
+#include <cstring>
 
 namespace ngpb {
 
@@ -115,9 +116,35 @@ NGPB_HD uint32_t morton3d_invert(uint32_t x) {
 // polynomials), evaluated in Estrin form with explicit fmaf(): a fused multiply-add is correctly
 // rounded on the device (FFMA) and on the host (FMA3 or glibc), so both give the same bits, and
 // the dependent chain is 9 operations instead of 25 - the serial per-ray march is latency bound.
+// Bit-level frexp / ldexp for positive normal numbers (every caller's range): the same values as
+// frexpf / scalbnf without their special-case handling, which dominates the instruction count of
+// the serial march loop.
+NGPB_HD uint32_t f32_bits(float x) {
+#ifdef __CUDA_ARCH__
+	return __float_as_uint(x);
+#else
+	uint32_t u; memcpy(&u, &x, 4); return u;
+#endif
+}
+NGPB_HD float bits_f32(uint32_t u) {
+#ifdef __CUDA_ARCH__
+	return __uint_as_float(u);
+#else
+	float x; memcpy(&x, &u, 4); return x;
+#endif
+}
+NGPB_HD float frexp_pos(float x, int& e) {
+	const uint32_t u = f32_bits(x);
+	e = (int)(u >> 23) - 126;
+	return bits_f32((u & 0x007FFFFFu) | 0x3F000000u);
+}
+NGPB_HD float pow2i(int n) { return bits_f32((uint32_t)(n + 127) << 23); } // 2^n, -126 <= n <= 127
+// exponent frexpf would report, for x >= 0 (0 -> 0; subnormals report -126, callers clamp at 0)
+NGPB_HD int frexp_exponent(float x) { return x == 0.0f ? 0 : (int)(f32_bits(x) >> 23) - 126; }
+
 NGPB_HD float det_logf(float xx) {
 	int e;
-	float x = frexpf(xx, &e);
+	float x = frexp_pos(xx, e);
 	if (x < 0.707106781186547524f) { e -= 1; x = x + x - 1.0f; } else { x = x - 1.0f; }
 	// degree-8 polynomial in Estrin form with explicit fused multiply-adds (4 dependent steps)
 	const float x2 = x * x, x4 = x2 * x2, x8 = x4 * x4;
@@ -145,15 +172,20 @@ NGPB_HD float det_expf(float x) {
 	const float a1 = fmaf(8.3334519073e-3f, x, 4.1665795894e-2f);
 	const float a2 = fmaf(1.9875691500e-4f, x, 1.3981999507e-3f);
 	const float p = fmaf(fmaf(a2, x2, a1), x2, a0);
-	return scalbnf(fmaf(p, x2, x) + 1.0f, n);
+	return (fmaf(p, x2, x) + 1.0f) * pow2i(n);
 }
 
 // ---- exponential stepping (nerf_device.cuh:372-437) ------------------------------------------
 // The reference recomputes log(1+c), a, b, exp(a log(1+c)), exp(b log(1+c)) on every call; they
 // only depend on the cone angle, so they are tabulated once per launch.
+// Divisions by the three per-launch constants are multiplications by their (once rounded)
+// reciprocals, here and in the oracle; the reference is built with --use_fast_math, which makes
+// the same substitution.
+constexpr float kInvMinConeStepsize = 1.0f / kMinConeStepsize;
+constexpr float kInvMaxConeStepsize = 1.0f / kMaxConeStepsize;
 struct Stepping {
 	float cone_angle;
-	float log1p_c, a, b, at, bt;
+	float log1p_c, a, b, at, bt, inv_log1p_c;
 };
 NGPB_HD Stepping make_stepping(float cone_angle) {
 	Stepping s{};
@@ -162,15 +194,16 @@ NGPB_HD Stepping make_stepping(float cone_angle) {
 	s.log1p_c = det_logf(1.0f + cone_angle);
 	s.a = (det_logf(kMinConeStepsize) - det_logf(s.log1p_c)) / s.log1p_c;
 	s.b = (det_logf(kMaxConeStepsize) - det_logf(s.log1p_c)) / s.log1p_c;
+	s.inv_log1p_c = 1.0f / s.log1p_c;
 	s.at = det_expf(s.a * s.log1p_c);
 	s.bt = det_expf(s.b * s.log1p_c);
 	return s;
 }
 NGPB_HD float to_stepping_space(float t, const Stepping& s) {
-	if (s.cone_angle <= 1e-5f) return t / kMinConeStepsize;
-	if (t <= s.at) return (t - s.at) / kMinConeStepsize + s.a;
-	if (t <= s.bt) return det_logf(t) / s.log1p_c;
-	return (t - s.bt) / kMaxConeStepsize + s.b;
+	if (s.cone_angle <= 1e-5f) return t * kInvMinConeStepsize;
+	if (t <= s.at) return (t - s.at) * kInvMinConeStepsize + s.a;
+	if (t <= s.bt) return det_logf(t) * s.inv_log1p_c;
+	return (t - s.bt) * kInvMaxConeStepsize + s.b;
 }
 NGPB_HD float from_stepping_space(float n, const Stepping& s) {
 	if (s.cone_angle <= 1e-5f) return n * kMinConeStepsize;
@@ -183,18 +216,25 @@ NGPB_HD float calc_dt(float t, const Stepping& s) { return advance_n_steps(t, s,
 
 NGPB_HD float sign_f(float x) { return copysignf(1.0f, x); }
 // nerf_device.cuh:362-370
-NGPB_HD float distance_to_next_voxel(V3 pos, V3 dir, V3 idir, float res) {
+NGPB_HD float distance_to_next_voxel(V3 pos, V3 dir, V3 idir, float res, float inv_res) {
 	const V3 p = res * (pos - 0.5f);
 	const float tx = (floorf(p.x + 0.5f + 0.5f * sign_f(dir.x)) - p.x) * idir.x;
 	const float ty = (floorf(p.y + 0.5f + 0.5f * sign_f(dir.y)) - p.y) * idir.y;
 	const float tz = (floorf(p.z + 0.5f + 0.5f * sign_f(dir.z)) - p.z) * idir.z;
 	const float t = fminf(fminf(tx, ty), tz);
-	return fmaxf(t / res, 0.0f);
+	return fmaxf(t * inv_res, 0.0f); // res is a power of two: same bits as t / res
 }
 // nerf_device.cuh:426-437
+// The same with to_stepping_space(t) supplied by the caller (the march loop already has it from
+// calc_dt): identical operations, one logarithm less on the serial path.
+NGPB_HD float advance_to_next_voxel_n(float t, float n, const Stepping& s, V3 pos, V3 dir, V3 idir, uint32_t mip) {
+	const float res = pow2i(7 - (int)mip);
+	const float t_target = to_stepping_space(t + distance_to_next_voxel(pos, dir, idir, res, pow2i((int)mip - 7)), s);
+	return from_stepping_space(n + ceilf(fmaxf(t_target - n, 0.5f)), s);
+}
 NGPB_HD float advance_to_next_voxel(float t, const Stepping& s, V3 pos, V3 dir, V3 idir, uint32_t mip) {
-	const float res = scalbnf((float)kNerfGridSize, -(int)mip);
-	float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
+	const float res = pow2i(7 - (int)mip); // kNerfGridSize / 2^mip
+	float t_target = t + distance_to_next_voxel(pos, dir, idir, res, pow2i((int)mip - 7));
 	t = to_stepping_space(t, s);
 	t_target = to_stepping_space(t_target, s);
 	return from_stepping_space(t + ceilf(fmaxf(t_target - t, 0.5f)), s);
@@ -203,21 +243,17 @@ NGPB_HD float advance_to_next_voxel(float t, const Stepping& s, V3 pos, V3 dir, 
 // ---- cascaded occupancy grid (nerf_device.cuh:316-340, 439-458) -------------------------------
 NGPB_HD int clamp_i(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 NGPB_HD uint32_t mip_from_pos(V3 pos, uint32_t max_cascade = kNerfCascades - 1) {
-	int exponent;
 	const float maxval = fmaxf(fmaxf(fabsf(pos.x - 0.5f), fabsf(pos.y - 0.5f)), fabsf(pos.z - 0.5f));
-	frexpf(maxval, &exponent);
-	return (uint32_t)clamp_i(exponent + 1, 0, (int)max_cascade);
+	return (uint32_t)clamp_i(frexp_exponent(maxval) + 1, 0, (int)max_cascade);
 }
 NGPB_HD uint32_t mip_from_dt(float dt, V3 pos, uint32_t max_cascade = kNerfCascades - 1) {
 	const uint32_t mip = mip_from_pos(pos, max_cascade);
 	dt *= 2 * kNerfGridSize;
 	if (dt < 1.0f) return mip;
-	int exponent;
-	frexpf(dt, &exponent);
-	return (uint32_t)clamp_i((int)mip, exponent, (int)max_cascade);
+	return (uint32_t)clamp_i((int)mip, frexp_exponent(dt), (int)max_cascade);
 }
 NGPB_HD uint32_t cascaded_grid_idx_at(V3 pos, uint32_t mip) {
-	const float mip_scale = scalbnf(1.0f, -(int)mip);
+	const float mip_scale = pow2i(-(int)mip);
 	pos = pos - 0.5f;
 	pos = pos * mip_scale;
 	pos = pos + 0.5f;

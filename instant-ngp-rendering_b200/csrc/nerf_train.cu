@@ -7,31 +7,52 @@
 // atomics instead of 2^19 and the rays of a block stay contiguous in the sample buffers.
 //
 // Emission: the reference marches every ray twice in the same thread (count, then emit). Here the
-// counting pass also records t at every 32nd sample, and a second kernel re-marches each 32-sample
-// segment from its checkpoint in its own thread, so a 600-sample ray is emitted by 19 threads
-// instead of one. The arithmetic from a checkpoint on is the serial loop's, bit for bit.
+// counting pass stores t of every sample it finds (32-sample chunks claimed from a pool, one atomic
+// per chunk), and a second kernel writes the coordinates with one LANE per sample - positions, dt
+// and warps are pure functions of (ray, t), evaluated with the serial loop's arithmetic, so the
+// rows are bit-identical to a second march.
+//
+// Lane packing: a step has a few thousand rays and the march is a serial, divergent loop, so a warp
+// full of rays runs for as long as the union of its 32 loops while most of the GPU idles. The
+// counting pass therefore spreads rays over warps (down to one ray per warp) until the grid fills
+// the machine.
 #include "nerf.h"
 #include "block_scan.cuh"
 #include "module.h"
 
+#include <algorithm>
+#include <cstdlib>
+
 namespace ngpb {
 
-constexpr uint32_t kEmitSegment = 32; // samples per emission thread; kNerfSteps / 32 = 32 checkpoints per ray
+constexpr uint32_t kChunk = 32;                       // samples per pool chunk
+constexpr uint32_t kChunksPerRay = kNerfSteps / kChunk; // 32
+constexpr uint32_t kNoChunk = 0xFFFFFFFFu;
+
+// Scratch of one generate call: chunk pool of sample distances + per-ray chunk table.
+struct MarchScratch {
+	uint32_t* pool_counter;
+	uint32_t n_chunks;
+	float* pool;        // [n_chunks][kChunk]
+	uint32_t* chunks;   // [n_rays_local][kChunksPerRay]
+};
 
 __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(const __grid_constant__ NerfTrainConfig cfg, const __grid_constant__ NerfTrainBuffers buf,
-	const __grid_constant__ Stepping stepping, Pcg32 rng, float* __restrict__ checkpoints)
+	const __grid_constant__ Stepping stepping, Pcg32 rng, const __grid_constant__ MarchScratch scratch, const uint32_t rays_per_warp)
 {
 	__shared__ uint32_t warp_sums[kRayBlock / 32 + 1];
 	__shared__ uint32_t block_base, block_ray_base;
 
-	const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
-	bool valid = local < local_ray_count(cfg);
+	const uint32_t lane = threadIdx.x % 32;
+	const uint32_t local = ((blockIdx.x * blockDim.x + threadIdx.x) / 32) * rays_per_warp + lane;
+	bool valid = lane < rays_per_warp && local < local_ray_count(cfg);
 	const uint32_t i = cfg.ray_begin + local; // global ray index
 
 	Ray3 ray{};
 	V3 dir_n{}, idir{};
 	float startt = 0.0f;
 	uint32_t numsteps = 0;
+	bool pool_ok = true;
 
 	if (valid) {
 		const uint32_t img = image_idx(i, cfg.n_rays, cfg.n_training_images);
@@ -53,18 +74,29 @@ __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(co
 			idir = v3(1.0f) / dir_n;
 
 			// first pass: count the samples
-			uint32_t j = 0;
+			uint32_t j = 0, chunk = kNoChunk;
 			float t = startt;
 			V3 pos;
 			while (aabb_contains(cfg.aabb, pos = ray.o + t * dir_n) && j < kNerfSteps) {
-				const float dt = calc_dt(t, stepping);
+				// Both continuations are computed before the occupancy bit is looked at: the skip target
+				// does not depend on the load, so its logarithm / exponential chain runs under the
+				// load's latency instead of after it.
+				const float n = to_stepping_space(t, stepping);
+				const float dt = from_stepping_space(n + 1.0f, stepping) - t; // calc_dt
 				const uint32_t mip = mip_from_dt(dt, pos, cfg.max_mip);
-				if (density_grid_occupied_at(pos, buf.density_bitfield, mip)) {
-					if (j % kEmitSegment == 0) checkpoints[(size_t)local * kEmitSegment + j / kEmitSegment] = t;
+				const bool occupied = density_grid_occupied_at(pos, buf.density_bitfield, mip);
+				const float t_skip = advance_to_next_voxel_n(t, n, stepping, pos, dir_n, idir, mip);
+				if (occupied) {
+					if (j % kChunk == 0) {
+						chunk = atomicAdd(scratch.pool_counter, 1u);
+						if (chunk >= scratch.n_chunks) { chunk = kNoChunk; pool_ok = false; }
+						scratch.chunks[(size_t)local * kChunksPerRay + j / kChunk] = chunk;
+					}
+					if (chunk != kNoChunk) scratch.pool[(size_t)chunk * kChunk + j % kChunk] = t;
 					++j;
 					t += dt;
 				} else {
-					t = advance_to_next_voxel(t, stepping, pos, dir_n, idir, mip);
+					t = t_skip;
 				}
 			}
 			numsteps = j;
@@ -77,7 +109,9 @@ __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(co
 	if (threadIdx.x == 0) block_base = block_total ? atomicAdd(&buf.counters->numsteps, block_total) : 0u;
 	__syncthreads();
 	const uint32_t base = block_base + prefix;
-	if (valid && base + numsteps > cfg.max_samples) valid = false;
+	// a ray that does not fit the sample buffer (or found the chunk pool exhausted, which only happens
+	// when the batch overflows the buffer anyway) is dropped whole (:804-806)
+	if (valid && (base + numsteps > cfg.max_samples || !pool_ok)) valid = false;
 
 	uint32_t kept_total;
 	const uint32_t ray_prefix = block_exclusive_scan(valid ? 1u : 0u, kept_total, warp_sums);
@@ -93,39 +127,28 @@ __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(co
 	buf.numsteps[ray_idx * 2 + 1] = base;
 }
 
-// Thread per (kept ray, 32-sample segment): samples [32 s, min(32 s + 32, numsteps)) from checkpoint s.
+// Warp per kept ray, lane per sample: coordinates from the stored distances.
 __global__ void __launch_bounds__(kRayBlock) emit_training_samples_kernel(const __grid_constant__ NerfTrainConfig cfg, const __grid_constant__ NerfTrainBuffers buf,
-	const __grid_constant__ Stepping stepping, const float* __restrict__ checkpoints)
+	const __grid_constant__ Stepping stepping, const __grid_constant__ MarchScratch scratch)
 {
-	const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-	const uint32_t ray_idx = tid / kEmitSegment, seg = tid % kEmitSegment;
+	const uint32_t ray_idx = (blockIdx.x * blockDim.x + threadIdx.x) / 32, lane = threadIdx.x % 32;
 	if (ray_idx >= buf.counters->rays) return;
 	const uint32_t numsteps = buf.numsteps[ray_idx * 2 + 0], base = buf.numsteps[ray_idx * 2 + 1];
-	uint32_t j = seg * kEmitSegment;
-	if (j >= numsteps) return;
-	const uint32_t end = min(numsteps, j + kEmitSegment);
 	const uint32_t local = buf.ray_indices[ray_idx] - cfg.ray_begin;
 	const float* ro = buf.rays_unnormalized + (size_t)ray_idx * 6;
 	const V3 o = {ro[0], ro[1], ro[2]};
 	const V3 dir_n = normalize(v3(ro[3], ro[4], ro[5]));
-	const V3 idir = v3(1.0f) / dir_n;
 	const V3 warped_dir = warp_direction(dir_n);
 	float* out = buf.coords + (size_t)base * kCoordFloats;
-	float t = checkpoints[(size_t)local * kEmitSegment + seg];
-	V3 pos;
-	while (aabb_contains(cfg.aabb, pos = o + t * dir_n) && j < end) {
+	for (uint32_t j = lane; j < numsteps; j += 32) {
+		const uint32_t chunk = scratch.chunks[(size_t)local * kChunksPerRay + j / kChunk];
+		const float t = scratch.pool[(size_t)chunk * kChunk + j % kChunk];
+		const V3 pos = o + t * dir_n;
 		const float dt = calc_dt(t, stepping);
-		const uint32_t mip = mip_from_dt(dt, pos, cfg.max_mip);
-		if (density_grid_occupied_at(pos, buf.density_bitfield, mip)) {
-			const V3 wp = warp_position(pos, cfg.aabb);
-			float* c = out + (size_t)j * kCoordFloats;
-			c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt);
-			c[4] = warped_dir.x; c[5] = warped_dir.y; c[6] = warped_dir.z;
-			++j;
-			t += dt;
-		} else {
-			t = advance_to_next_voxel(t, stepping, pos, dir_n, idir, mip);
-		}
+		const V3 wp = warp_position(pos, cfg.aabb);
+		float* c = out + (size_t)j * kCoordFloats;
+		c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt);
+		c[4] = warped_dir.x; c[5] = warped_dir.y; c[6] = warped_dir.z;
 	}
 }
 
@@ -133,10 +156,25 @@ void nerf_generate_training_samples(cudaStream_t stream, const NerfTrainConfig& 
 	if (local_ray_count(cfg) == 0) return;
 	const Stepping stepping = make_stepping(cfg.cone_angle_constant);
 	const uint32_t n_local = local_ray_count(cfg);
-	DeviceBuffer checkpoints((size_t)n_local * kEmitSegment * sizeof(float), stream); // stream-ordered, returned to the pool at scope exit
-	generate_training_samples_kernel<<<div_round_up(n_local, kRayBlock), kRayBlock, 0, stream>>>(cfg, buf, stepping, rng, checkpoints.as<float>());
+	// rays per warp: few enough that the serial loops of a warp's rays do not pile up, many enough
+	// that the warp instructions (one per iteration whatever the lane count) do not saturate issue
+	static const uint32_t max_warps = getenv("NGPB_MARCH_WARPS") ? (uint32_t)atoi(getenv("NGPB_MARCH_WARPS")) : 2048u;
+	uint32_t rays_per_warp = 1;
+	while (rays_per_warp < 32 && n_local / rays_per_warp > max_warps) rays_per_warp *= 2;
+	MarchScratch scratch{};
+	// every ray can hold its kNerfSteps samples: the pool never decides which rays are kept (at most
+	// 2^18 rays x 4 KiB = 1 GiB of address space, touched only where samples exist)
+	scratch.n_chunks = n_local * kChunksPerRay;
+	const size_t pool_bytes = (size_t)scratch.n_chunks * kChunk * sizeof(float), table_bytes = (size_t)n_local * kChunksPerRay * sizeof(uint32_t);
+	DeviceBuffer mem(256 + pool_bytes + table_bytes, stream); // stream-ordered, returned to the pool at scope exit
+	scratch.pool_counter = mem.as<uint32_t>();
+	scratch.pool = reinterpret_cast<float*>(mem.as<char>() + 256);
+	scratch.chunks = reinterpret_cast<uint32_t*>(mem.as<char>() + 256 + pool_bytes);
+	NGPB_CUDA_CHECK(cudaMemsetAsync(scratch.pool_counter, 0, sizeof(uint32_t), stream));
+	const uint32_t n_warps = div_round_up(n_local, rays_per_warp);
+	generate_training_samples_kernel<<<div_round_up(n_warps, kRayBlock / 32), kRayBlock, 0, stream>>>(cfg, buf, stepping, rng, scratch, rays_per_warp);
 	NGPB_CUDA_CHECK(cudaGetLastError());
-	emit_training_samples_kernel<<<(uint32_t)div_round_up64((uint64_t)n_local * kEmitSegment, kRayBlock), kRayBlock, 0, stream>>>(cfg, buf, stepping, checkpoints.as<float>());
+	emit_training_samples_kernel<<<div_round_up(n_local, kRayBlock / 32), kRayBlock, 0, stream>>>(cfg, buf, stepping, scratch);
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }
 

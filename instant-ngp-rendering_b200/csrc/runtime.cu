@@ -52,6 +52,22 @@ std::string prof_collect(bool reset) {
 	return o.str();
 }
 
+// Stream-ordered scratch (DeviceBuffer) is freed and re-taken every step; without a release
+// threshold the driver returns the pool's pages to the OS at every synchronisation and the next
+// cudaMallocAsync maps them again (hundreds of microseconds per step).
+void keep_pool_memory() {
+	static bool done[64] = {};
+	int dev = 0;
+	if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || done[dev]) return;
+	cudaMemPool_t pool;
+	if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+		uint64_t threshold = UINT64_MAX;
+		cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+	}
+	cudaGetLastError();
+	done[dev] = true;
+}
+
 int sm_count() {
 	static int count = -1;
 	if (count < 0) {

@@ -119,15 +119,19 @@ float c_expf(float x) {
 }
 
 // nerf_device.cuh:372-424, evaluated per call exactly as written there.
+// Divisions by MIN/MAX_CONE_STEPSIZE and log1p_c are multiplications by their once-rounded
+// reciprocals (what --use_fast_math does to the reference's own build, CMakeLists.txt:82).
 float to_stepping_space(float t, float cone_angle) {
-	if (cone_angle <= 1e-5f) return t / MIN_CONE_STEPSIZE;
+	const float inv_min = 1.0f / MIN_CONE_STEPSIZE, inv_max = 1.0f / MAX_CONE_STEPSIZE;
+	if (cone_angle <= 1e-5f) return t * inv_min;
 	const float log1p_c = c_logf(1.0f + cone_angle);
+	const float inv_log1p_c = 1.0f / log1p_c;
 	const float a = (c_logf(MIN_CONE_STEPSIZE) - c_logf(log1p_c)) / log1p_c;
 	const float b = (c_logf(MAX_CONE_STEPSIZE) - c_logf(log1p_c)) / log1p_c;
 	const float at = c_expf(a * log1p_c), bt = c_expf(b * log1p_c);
-	if (t <= at) return (t - at) / MIN_CONE_STEPSIZE + a;
-	if (t <= bt) return c_logf(t) / log1p_c;
-	return (t - bt) / MAX_CONE_STEPSIZE + b;
+	if (t <= at) return (t - at) * inv_min + a;
+	if (t <= bt) return c_logf(t) * inv_log1p_c;
+	return (t - bt) * inv_max + b;
 }
 float from_stepping_space(float n, float cone_angle) {
 	if (cone_angle <= 1e-5f) return n * MIN_CONE_STEPSIZE;
