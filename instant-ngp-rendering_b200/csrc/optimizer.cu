@@ -15,14 +15,26 @@ struct AdamArgs {
 	// EMA
 	uint32_t has_ema, ema_full_precision;
 	float ema_decay, ema_debias_old, ema_debias_new;
+	float inv_loss_scale, log2_beta1, log2_beta2;
 };
+
+// beta^step for the bias correction. Every parameter has its own step count (hash-grid entries
+// only step when they receive a gradient, adam.h:76-78,93), so the power cannot be hoisted to the
+// host; powf costs ~60 instructions twice per parameter and made this streaming kernel issue
+// bound (ncu, round 1: 73 % SM / 24 % DRAM throughput). ex2.approx of step * log2(beta) is 2
+// instructions and exact to ~2 ulp over the range that matters (the term vanishes as step grows).
+NGPB_D float pow_beta(float log2_beta, uint32_t step) {
+	float r;
+	asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(log2_beta * (float)step));
+	return r;
+}
 
 // One parameter: the arithmetic of adam_step (adam.h:72-118) followed by ema_step_half_precision /
 // ema_step_full_precision (ema.h:46-78), expression for expression.
 NGPB_D void update_one(const AdamArgs& a, uint32_t i, float grad_h, float& w_fp, __half& w_h, float& m1, float& m2, uint32_t& steps,
 	__half& ema_h, float* ema_tmp)
 {
-	float gradient = grad_h / a.loss_scale;
+	float gradient = grad_h * a.inv_loss_scale;
 	bool skip;
 	if (i >= a.n_matrix_weights) skip = !a.optimize_non_matrix_params || gradient == 0;
 	else skip = !a.optimize_matrix_params;
@@ -36,7 +48,7 @@ NGPB_D void update_one(const AdamArgs& a, uint32_t i, float grad_h, float& w_fp,
 		float learning_rate = a.learning_rate;
 		if (i >= a.n_matrix_weights) learning_rate *= a.non_matrix_learning_rate_factor;
 		const uint32_t current_step = ++steps;
-		learning_rate *= sqrtf(1 - powf(a.beta2, (float)current_step)) / (1 - powf(a.beta1, (float)current_step));
+		learning_rate *= sqrtf(1 - pow_beta(a.log2_beta2, current_step)) / (1 - pow_beta(a.log2_beta1, current_step));
 		const float effective_learning_rate = fminf(fmaxf(learning_rate / (sqrtf(second_moment) + a.epsilon), a.lower_lr_bound), a.upper_lr_bound);
 		const float decayed_weight = (1 - a.relative_weight_decay * learning_rate) * weight_fp - copysignf(a.absolute_weight_decay * learning_rate, weight_fp);
 		float new_weight = decayed_weight - effective_learning_rate * first_moment;
@@ -70,7 +82,7 @@ __global__ void __launch_bounds__(256) adam_ema_step_kernel(const __grid_constan
 #pragma unroll
 		for (uint32_t k = 0; k < 4; ++k) {
 			const uint32_t i = i0 + k;
-			const bool skip = i >= a.n_matrix_weights ? (!a.optimize_non_matrix_params || __half2float(g[k]) / a.loss_scale == 0) : !a.optimize_matrix_params;
+			const bool skip = i >= a.n_matrix_weights ? (!a.optimize_non_matrix_params || __half2float(g[k]) * a.inv_loss_scale == 0) : !a.optimize_matrix_params;
 			any_adam |= !skip;
 		}
 		if (!any_adam && !a.has_ema) return;
@@ -261,6 +273,10 @@ void Optimizer::step(cudaStream_t stream, float loss_scale, float* weights_fp32,
 	a.ema_decay = m_ema_decay;
 	a.ema_debias_old = 1 - (float)std::pow(m_ema_decay, m_current_step - 1); // ema.h:106-107
 	a.ema_debias_new = 1.0f / (1 - (float)std::pow(m_ema_decay, m_current_step));
+
+	a.inv_loss_scale = 1.0f / loss_scale;
+	a.log2_beta1 = std::log2(m_beta1);
+	a.log2_beta2 = std::log2(m_beta2);
 
 	const bool aligned = ((uintptr_t)weights_fp32 % 16 == 0) && ((uintptr_t)weights % 8 == 0) && ((uintptr_t)gradients % 8 == 0);
 	if (!aligned) throw std::runtime_error{"ngp-b200 optimizer: parameter buffers must be 16-byte (fp32) / 8-byte (fp16) aligned"};
