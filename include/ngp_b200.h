@@ -224,13 +224,14 @@ int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size);
  * rgb_activation, density_activation, color_space, train_network, train_encoding, last_render_samples,
  * render_target_queries, render_min_steps, render_max_steps (the window policy of NerfTracer::trace,
  * src/testbed_nerf.cu:1693-1694), render_windows_per_sync, render_snap_to_pixel_centers,
- * shard_rank, shard_world (training ray shards), render_shard_rank, render_shard_world (render_nerf
+ * image_snap_to_pixel_centers, shard_rank, shard_world (training ray shards), render_shard_rank, render_shard_world (render_nerf
  * then traces only the 256-pixel tiles t of [pixel_begin, pixel_end) with t % world == rank). */
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value);
 int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value);
 /* Device buffers by name: params (fp16), params_fp32, params_inference (fp16), gradients (fp16),
  * density_grid (float), density_grid_bitfield (uint8), density_grid_mean (float), metadata,
- * counters (ngpb_nerf_counters_t of the last step). */
+ * counters (ngpb_nerf_counters_t of the last step); image mode: image_positions (float [n][2]),
+ * image_targets (float [n][3]), image_output (fp16 [n][16]), image_dloss (fp16 [n][16]) of the last step. */
 int ngpb_testbed_device_ptr(ngpb_testbed_t* t, const char* name, void** ptr, size_t* bytes);
 size_t ngpb_testbed_network_config(const ngpb_testbed_t* t, char* buf, size_t cap);
 /* update_density_grid_nerf(decay, n_uniform, n_nonuniform), src/testbed_nerf.cu:2271-2360. */
@@ -240,6 +241,16 @@ int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_
  * [pixel_begin, pixel_end) (row-major) are traced: the unit of tile sharding across GPUs. */
 int ngpb_testbed_render_nerf(ngpb_testbed_t* t, uint32_t width, uint32_t height, const float* camera_3x4, float focal_x, float focal_y,
 	float principal_x, float principal_y, uint32_t spp_index, uint32_t pixel_begin, uint32_t pixel_end, float* rgba, float* depth);
+
+/* Neural-image mode (ETestbedMode::Image; Testbed::load_image, train_image, render_image,
+ * src/testbed_image.cu:212-340, 360-410): the image is RGBA Half (2) or Float (3), linear colours,
+ * host or device pointer. After this call reload_network_from_json builds the 2-D
+ * NetworkWithInputEncoding (per_level_scale from max(w, h) / 2, src/testbed.cu:3701-3713),
+ * ngpb_testbed_train runs train_image (stratified positions, snapped / bilinear targets, the
+ * config's loss: L2, RelativeL2 or L1) and render_image evaluates the network at the pixel centres
+ * of a width x height grid into a DEVICE float4 buffer (linear colours, alpha 1). */
+int ngpb_testbed_set_image(ngpb_testbed_t* t, const void* pixels, int image_data_type, int width, int height);
+int ngpb_testbed_render_image(ngpb_testbed_t* t, uint32_t width, uint32_t height, float* rgba);
 
 /* Optional DEVICE buffer [height*width] that render_nerf fills with the number of samples composited
  * per pixel (NerfPayload::n_steps, the value ERenderMode::Cost shows, src/testbed_nerf.cu:1329-1331);

@@ -104,7 +104,7 @@ int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size) {
 	X(snap_to_pixel_centers) X(near_distance) X(density_grid_decay) X(render_min_transmittance) X(loss_type) X(rgb_activation) \
 	X(density_activation) X(color_space) X(train_network) X(train_encoding) X(aabb_scale) \
 	X(render_target_queries) X(render_min_steps) X(render_max_steps) X(render_windows_per_sync) X(render_snap_to_pixel_centers) \
-	X(shard_rank) X(shard_world) X(render_shard_rank) X(render_shard_world)
+	X(shard_rank) X(shard_world) X(render_shard_rank) X(render_shard_world) X(image_snap_to_pixel_centers)
 
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
 	NGPB_API_BEGIN
@@ -149,6 +149,10 @@ int ngpb_testbed_device_ptr(ngpb_testbed_t* t, const char* name, void** ptr, siz
 	else if (n == "density_grid") { p = tb.density_grid(); b = n_grid * 4; }
 	else if (n == "density_grid_bitfield") { p = tb.density_grid_bitfield(); b = nerf_bitfield_bytes(); }
 	else if (n == "density_grid_mean") { p = tb.density_grid_mean(); b = 4; }
+	else if (n == "image_positions") { p = tb.image_buffer(0, &b); }
+	else if (n == "image_targets") { p = tb.image_buffer(1, &b); }
+	else if (n == "image_output") { p = tb.image_buffer(2, &b); }
+	else if (n == "image_dloss") { p = tb.image_buffer(3, &b); }
 	else if (n == "counters") { p = tb.counters(); b = sizeof(NerfStepCounters); }
 	else if (n == "metadata") { tb.upload_metadata(); p = (void*)tb.metadata_gpu(); b = tb.n_images() * sizeof(ImageMeta); }
 	else throw std::runtime_error{"ngpb_testbed_device_ptr: unknown buffer " + n};
@@ -165,6 +169,17 @@ int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_
 	NGPB_API_BEGIN
 	t->impl->update_density_grid_nerf(decay, n_uniform, n_nonuniform);
 	NGPB_CUDA_CHECK(cudaStreamSynchronize(t->impl->stream()));
+	NGPB_API_END
+}
+
+int ngpb_testbed_set_image(ngpb_testbed_t* t, const void* pixels, int image_data_type, int width, int height) {
+	NGPB_API_BEGIN
+	t->impl->set_image(pixels, image_data_type, width, height);
+	NGPB_API_END
+}
+int ngpb_testbed_render_image(ngpb_testbed_t* t, uint32_t width, uint32_t height, float* rgba) {
+	NGPB_API_BEGIN
+	t->impl->render_image(width, height, rgba);
 	NGPB_API_END
 }
 

@@ -35,8 +35,10 @@ Testbed::~Testbed() {
 	m_images.clear();
 	for (DeviceBuffer* b : {&m_params_fp32, &m_params, &m_gradients, &m_metadata_gpu, &m_density_grid, &m_density_grid_tmp, &m_density_bitfield,
 			&m_density_mean, &m_grid_positions, &m_grid_indices, &m_grid_mlp_out, &m_counters, &m_ray_indices, &m_rays, &m_numsteps, &m_coords,
-			&m_rgbsigma, &m_coords_compacted, &m_dloss, &m_loss, &m_render_scratch}) b->release();
+			&m_rgbsigma, &m_coords_compacted, &m_dloss, &m_loss, &m_render_scratch,
+			&m_image_data, &m_image_positions, &m_image_targets, &m_image_output, &m_image_dloss, &m_image_loss_values}) b->release();
 	m_network.reset();
+	m_image_network.reset();
 	m_optimizer.reset();
 	cudaStreamSynchronize(m_stream);
 	if (m_own_stream) { cudaStreamSynchronize(m_own_stream); cudaStreamDestroy(m_own_stream); }
@@ -121,6 +123,13 @@ void Testbed::reload_network_from_json(const Json& config) {
 }
 
 void Testbed::reset_network(bool clear_density_grid) {
+	if (m_mode == kModeImage) {
+		m_rng = Pcg32{seed};
+		const Json loss_config = m_network_config.value("loss", Json::object());
+		loss_type = loss_type_from_string(loss_config.value("otype", "L2"));
+		reset_network_image();
+		return;
+	}
 	m_rng = Pcg32{seed};
 	rays_per_batch = 1u << 12;
 	measured_batch_size_before_compaction = 0;

@@ -32,6 +32,25 @@ public:
 	// row-major [3][4]; focal length in pixels; principal point in [0,1]; lens as ELensMode + params.
 	void set_nerf_camera(uint32_t idx, const float* xform_3x4, float focal_x, float focal_y, float principal_x, float principal_y, int lens_mode, const float* lens_params);
 
+	// ---- neural image mode (Testbed::load_image / train_image / render_image, src/testbed_image.cu)
+	// pixels: HOST or DEVICE RGBA texels (Half or Float, linear colours); switches the testbed to
+	// ETestbedMode::Image: reload_network_from_json then builds the 2-D NetworkWithInputEncoding and
+	// train(batch) runs train_image.
+	void set_image(const void* pixels, int image_data_type, int width, int height);
+	// Network colour at every pixel centre of a width x height grid: DEVICE float4 [h][w], linear.
+	void render_image(uint32_t width, uint32_t height, float* rgba_out);
+	NetworkWithInputEncodingModule* image_network() { return m_image_network.get(); }
+	bool image_snap_to_pixel_centers = true; // Image::Training::snap_to_pixel_centers (testbed.h:878)
+	int mode() const { return m_mode; }
+	// Buffers of the last train_image step, for parity tests: 0 positions fp32 [n][2], 1 targets fp32
+	// [n][3], 2 network output fp16 [n][16], 3 dL/doutput fp16 [n][16].
+	void* image_buffer(int which, size_t* bytes) {
+		DeviceBuffer* b[4] = {&m_image_positions, &m_image_targets, &m_image_output, &m_image_dloss};
+		const size_t per[4] = {8, 12, 32, 32};
+		if (bytes) *bytes = (size_t)measured_batch_size * per[which];
+		return b[which]->ptr;
+	}
+
 	// ---- network (reload_network_from_json, reset_network)
 	void reload_network_from_json(const Json& config);
 	void reset_network(bool clear_density_grid = true);
@@ -120,6 +139,14 @@ public:
 	void set_render_steps_out(uint32_t* p) { m_render_steps_out = p; }
 
 private:
+	enum : int { kModeNerf = 0, kModeImage = 1 };
+	int m_mode = kModeNerf;
+	void reset_network_image();
+	void train_image(uint32_t batch_size, bool get_loss_scalar);
+	std::unique_ptr<NetworkWithInputEncodingModule> m_image_network;
+	DeviceBuffer m_image_data, m_image_positions, m_image_targets, m_image_output, m_image_dloss, m_image_loss_values;
+	int m_image_type = kImageFloat, m_image_res_x = 0, m_image_res_y = 0;
+
 	void training_prep_nerf();
 	bool m_get_loss_scalar = false;
 	void train_nerf_step(uint32_t target_batch_size);

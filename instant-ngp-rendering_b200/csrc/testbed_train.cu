@@ -64,6 +64,17 @@ void Testbed::training_prep_nerf() {
 }
 
 void Testbed::train(uint32_t batch_size) {
+	if (m_mode == kModeImage) {
+		if (!m_image_network) throw std::runtime_error{"Unable to create a neural network trainer."};
+		if (batch_size == 0 || batch_size % kBatchSizeGranularity != 0) throw std::runtime_error{"ngp-b200: batch size must be a positive multiple of 256"};
+		Json leaf = Json::object();
+		leaf["otype"] = "Adam";
+		leaf["optimize_matrix_params"] = train_network;
+		leaf["optimize_non_matrix_params"] = train_encoding;
+		m_optimizer->update_hyperparams(leaf);
+		train_image(batch_size, m_training_step % 16 == 0);
+		return;
+	}
 	if (shard_world > 1) throw std::runtime_error{"ngp-b200: a sharded testbed trains with train_begin / all-reduce / train_end"};
 	train_begin(batch_size);
 	train_end(batch_size);

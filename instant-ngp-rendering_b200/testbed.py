@@ -191,6 +191,25 @@ class Testbed:
         x = np.ascontiguousarray(self._extrinsics[idx], dtype=np.float32)
         check(lib.ngpb_testbed_set_nerf_camera(self._h, idx, x.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), fx, fy, px, py, mode, lens))
 
+    # -- neural image mode (pyngp: load_training_data of an image file, src/python_api.cu:415) -------
+    def set_image(self, img):
+        """img: [h][w][4] float32 or float16, linear colours; numpy array or torch tensor."""
+        if isinstance(img, np.ndarray):
+            img = torch.from_numpy(np.ascontiguousarray(img))
+        img = img.contiguous()
+        assert img.dim() == 3 and img.shape[2] == 4
+        kind = {torch.float16: IMAGE_HALF, torch.float32: IMAGE_FLOAT}[img.dtype]
+        if img.is_cuda:
+            torch.cuda.current_stream().synchronize()
+        check(lib.ngpb_testbed_set_image(self._h, ctypes.c_void_p(img.data_ptr()), kind, int(img.shape[1]), int(img.shape[0])))
+
+    def render_image(self, width, height):
+        """Linear RGBA float32 [h][w][4] of the fitted image at the pixel centres."""
+        rgba = torch.empty((height, width, 4), dtype=torch.float32, device=self._device)
+        torch.cuda.current_stream().synchronize()
+        check(lib.ngpb_testbed_render_image(self._h, width, height, ctypes.c_void_p(rgba.data_ptr())))
+        return rgba
+
     # -- network ---------------------------------------------------------------------------------
     def reload_network_from_json(self, config):
         check(lib.ngpb_testbed_reload_network_from_json(self._h, json.dumps(config).encode()))

@@ -22,7 +22,7 @@ batch = 1 << 18
 
 tb = ngp.Testbed()
 t0 = time.time()
-scene, poses, focal = syn.make_dataset(tb, n_images=n_images, width=w, height=h, aabb_scale=4, opaque_background=True)
+scene, poses, focal = syn.make_dataset(tb, n_images=n_images, width=w, height=h, aabb_scale=4, amp_scale=8.0)
 torch.cuda.synchronize()
 print(f"dataset {n_images}x{w}x{h} in {time.time() - t0:.1f}s", flush=True)
 tb.reload_network_from_json(syn.NERF_BASE_CONFIG)
