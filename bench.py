@@ -13,6 +13,7 @@ Workloads (BASELINE.json configs):
          Mrays/s) and the hash-grid micro-benchmark ("grid", Gpts/s).
          N > 1: rays of every step are sharded over the ranks and the gradients all-reduced over
          NCCL; the render shards pixel tiles with no communication.
+         It also carries configs[1] ("image": neural image of the albert shape, samples/s).
   grid   configs[0]: hash-grid encoding forward+backward alone, 3-D L16 F2 T=2^19, 2^20 points.
          Replicas only at N > 1 (no exchange).
 """
@@ -343,6 +344,49 @@ def grid_measure(ngp, steps, warmup, rank, world, local):
     }
 
 
+IMAGE_CONFIG = {  # configs/image/base.json
+    "loss": {"otype": "L2"},
+    "optimizer": {"otype": "ExponentialDecay", "decay_start": 20000, "decay_interval": 10000, "decay_base": 0.33,
+                  "nested": {"otype": "Adam", "learning_rate": 1e-2, "beta1": 0.9, "beta2": 0.99, "epsilon": 1e-15, "l2_reg": 1e-6}},
+    "encoding": {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 2, "log2_hashmap_size": 24, "base_resolution": 16},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2},
+}
+
+
+def image_measure(ngp, steps, warmup, rank, world, local):
+    """configs[1]: neural image of the albert shape (1024 x 1024 RGBA float), base.json, 2^18 samples per
+    step through Testbed.train; replicas only at N > 1."""
+    import numpy as np
+    import torch
+    dev = torch.device("cuda", local)
+    w = h = 1024
+    ys, xs = torch.meshgrid(torch.arange(h, device=dev), torch.arange(w, device=dev), indexing="ij")
+    g = torch.Generator(device=dev).manual_seed(7)
+    img = torch.stack([0.5 + 0.5 * torch.sin(xs / 37.0) * torch.cos(ys / 23.0), ((xs // 32 + ys // 32) % 2) * 0.8 + 0.1,
+                       (xs / w + 0.05 * torch.randn((h, w), generator=g, device=dev)).clamp(0, 1), torch.ones((h, w), device=dev)], dim=-1).float().contiguous()
+    tb = ngp.Testbed(device=dev)
+    tb.use_current_stream()
+    tb.set_image(img)
+    tb.reload_network_from_json(IMAGE_CONFIG)
+    batch = 1 << 18
+    for _ in range(max(warmup, 3) + 100):
+        tb.train(batch)
+    barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        tb.train(batch)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = reduce_over_ranks(e0.elapsed_time(e1), world)
+    got = tb.render_image(w, h)
+    mse = float(((got[..., :3].clamp(0, 1) - img[..., :3]) ** 2).mean())
+    tb.close()
+    return {"metric": "neural image train samples/s", "value": batch * world * steps / (ms * 1e-3), "unit": "samples/s", "ms_per_step": ms / steps,
+            "config": {"workload": "image_1024x1024_base.json_batch2^18", "parallelism": "replicas only" if world > 1 else "1 GPU"},
+            "mse_linear_after": mse, "steps_trained": steps + max(warmup, 3) + 100}
+
+
 def load_traffic(kernel):
     """dram bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json), or None."""
     tp = os.path.join(ROOT, "profiles", "traffic.json")
@@ -505,6 +549,7 @@ def run_nerf(args):
               "sharding": f"256-pixel tiles interleaved over {world} rank(s), no communication"}
 
     grid = grid_measure(ngp, min(K, 20), 3, rank, world, local)
+    image = image_measure(ngp, min(K, 100), 3, rank, world, local)
     if rank != 0:
         return
     cpu = cpu_nerf_baseline(n_rays=256, steps=4, budget_s=20.0)
@@ -529,7 +574,7 @@ def run_nerf(args):
         "e2e": {"value": e2e_samples / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 20,
                 "note": "dataset uploaded from pinned host memory inside the timed region, then K Testbed.train calls with their counter read-backs"},
         "gpu_launches": NERF_LAUNCHES_PER_STEP * K,
-        "render": render, "grid": grid, "clocks": clocks,
+        "render": render, "grid": grid, "image": image, "clocks": clocks,
     }
     print(json.dumps(line))
 
