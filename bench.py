@@ -326,7 +326,25 @@ def grid_measure(ngp, steps, warmup, rank, world, local):
     t1.record()
     torch.cuda.synchronize()
     e2e_ms = reduce_over_ranks(t0.elapsed_time(t1), world)
+    # gather / scatter rooflines measured in the same run: random 4-byte loads and random
+    # red.f16x2 over a 32 MiB L2-resident table (the encoder's table is 24.4 MB), 2^20 x 128 accesses
+    table = torch.zeros(1 << 23, dtype=torch.int32, device=dev)
+    sink = torch.zeros(4, dtype=torch.int32, device=dev)
+    probe = {}
+    for name, call in (("gather", lambda: lib.ngpb_probe_gather(sp, ctypes.c_void_p(table.data_ptr()), 23, 4, 1 << 20, 128, ctypes.c_void_p(sink.data_ptr()))),
+                       ("scatter", lambda: lib.ngpb_probe_scatter(sp, ctypes.c_void_p(table.data_ptr()), 23, 1 << 20, 128))):
+        for _ in range(2):
+            check(call())
+        t0, t1 = ev(), ev()
+        t0.record()
+        for _ in range(5):
+            check(call())
+        t1.record()
+        torch.cuda.synchronize()
+        probe[name] = 5 * (1 << 20) * 128 / (t0.elapsed_time(t1) * 1e-3) / 1e9   # G accesses / s
     f_ms, b_ms = float(np.mean(fwd_ms)), float(np.mean(bwd_ms))
+    fwd_rate = n * 128 / (f_ms * 1e-3) / 1e9
+    bwd_rate = n * 128 / (b_ms * 1e-3) / 1e9
     back = b_ms >= f_ms
     dom = "grid_backward_kernel" if back else "grid_forward_kernel"
     achieved = n * (GRID_BYTES_PER_POINT_BWD if back else GRID_BYTES_PER_POINT_FWD) / (max(f_ms, b_ms) * 1e-3) / 1e9
@@ -335,6 +353,9 @@ def grid_measure(ngp, steps, warmup, rank, world, local):
         "config": {"workload": "grid_L16F2_T19_2^20pts", "encoding": GRID_ENC, "points_per_step_per_gpu": n,
                    "l2": "flushed between timed steps (256 MiB write)", "parallelism": "replicas only" if world > 1 else "1 GPU"},
         "kernels_ms": {"grid_forward_kernel": f_ms, "memset+grid_backward_kernel": b_ms},
+        "gather_roofline": {"what": "16 levels x 8 corners = 128 random 4-byte accesses per point against the rate of the probe kernels on this GPU",
+                            "forward": {"achieved": fwd_rate, "peak": probe["gather"], "unit": "G loads/s", "frac": fwd_rate / probe["gather"]},
+                            "backward": {"achieved": bwd_rate, "peak": probe["scatter"], "unit": "G red.f16x2/s", "frac": bwd_rate / probe["scatter"]}},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                      "traffic": load_traffic(dom), "peak_source": peaks["source"],
                      "note": "algorithmic 588 B/point per direction; the 24.4 MB table is L2-resident, so the HBM copy peak is a floor for the gather roofline, not a ceiling"},
@@ -517,9 +538,6 @@ def run_nerf(args):
     del host_images
 
     # configs[3]: novel-view render of the trained model, 1920x1080, tiles sharded over the ranks
-    tb._set("render_target_queries", 16 << 20)
-    tb._set("render_min_steps", 4)
-    tb._set("render_windows_per_sync", 16)
     rw, rh = 1920, 1080
     shard = (rank, world)
     view = syn.look_at_ngp(np.array([0.5, 0.5, 0.5]) + 1.4 * np.array([0.62, -0.55, 0.56]))  # not a training pose

@@ -207,7 +207,9 @@ int ngpb_testbed_set_nerf_camera(ngpb_testbed_t* t, uint32_t idx, const float* x
 int ngpb_testbed_set_stream(ngpb_testbed_t* t, void* stream);
 int ngpb_testbed_reload_network_from_json(ngpb_testbed_t* t, const char* config_json);
 int ngpb_testbed_reset_network(ngpb_testbed_t* t, int clear_density_grid);
-/* Testbed::train(batch_size), src/testbed.cu:4020-4109. */
+/* Testbed::train(batch_size), src/testbed.cu:4020-4109. Returns once the step's counters (loss,
+ * measured batch sizes) are on the host; the backward pass and the optimizer may still be running on
+ * the testbed's stream - later calls on this testbed are ordered behind them. */
 int ngpb_testbed_train(ngpb_testbed_t* t, uint32_t batch_size);
 /* Data-parallel form of ngpb_testbed_train (no reference counterpart; the reference trains on one GPU):
  * with properties shard_rank / shard_world set, train_begin computes this rank's share of the step
@@ -225,7 +227,9 @@ int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size);
  * render_target_queries, render_min_steps, render_max_steps (the window policy of NerfTracer::trace,
  * src/testbed_nerf.cu:1693-1694), render_windows_per_sync, render_snap_to_pixel_centers,
  * image_snap_to_pixel_centers, shard_rank, shard_world (training ray shards), render_shard_rank, render_shard_world (render_nerf
- * then traces only the 256-pixel tiles t of [pixel_begin, pixel_end) with t % world == rank). */
+ * then traces only the 256-pixel tiles t of [pixel_begin, pixel_end) with t % world == rank),
+ * train_prefetch (default 1: ngpb_testbed_train marches the rays of the next step on a second stream
+ * while the backward pass and the optimizer of this step run; same samples as the serial order). */
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value);
 int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value);
 /* Device buffers by name: params (fp16), params_fp32, params_inference (fp16), gradients (fp16),
@@ -256,6 +260,14 @@ int ngpb_testbed_render_image(ngpb_testbed_t* t, uint32_t width, uint32_t height
  * per pixel (NerfPayload::n_steps, the value ERenderMode::Cost shows, src/testbed_nerf.cu:1329-1331);
  * NULL switches it off. Pixels whose ray never enters occupied space are not written. */
 int ngpb_testbed_set_render_steps_out(ngpb_testbed_t* t, uint32_t* steps);
+
+/* ---- roofline probes (no reference counterpart) -------------------------------------------------
+ * Random-access micro-kernels that measure what the hash-grid kernels are bounded by on this GPU:
+ * independent random loads of entry_bytes (4, 8, 16) from a table of 2^log2_entries entries, and
+ * random red.global.add.f16x2 into a table of 2^log2_entries 4-byte entries. n_threads x per_thread
+ * accesses per launch (per_thread a multiple of 8 for the gather); time the launch with CUDA events. */
+int ngpb_probe_gather(void* stream, const void* table, uint32_t log2_entries, uint32_t entry_bytes, uint32_t n_threads, uint32_t per_thread, uint32_t* sink);
+int ngpb_probe_scatter(void* stream, void* table, uint32_t log2_entries, uint32_t n_threads, uint32_t per_thread);
 
 /* ---- self test of the tcgen05 operand views (tc_device.cuh) --------------------------------
  * mode 0: D[128xN] = X[128xK] W[NxK]^T; mode 1: D[128xN] = X[128xK] W[KxN];

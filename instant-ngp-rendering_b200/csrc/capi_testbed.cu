@@ -104,7 +104,7 @@ int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size) {
 	X(snap_to_pixel_centers) X(near_distance) X(density_grid_decay) X(render_min_transmittance) X(loss_type) X(rgb_activation) \
 	X(density_activation) X(color_space) X(train_network) X(train_encoding) X(aabb_scale) \
 	X(render_target_queries) X(render_min_steps) X(render_max_steps) X(render_windows_per_sync) X(render_snap_to_pixel_centers) \
-	X(shard_rank) X(shard_world) X(render_shard_rank) X(render_shard_world) X(image_snap_to_pixel_centers)
+	X(shard_rank) X(shard_world) X(render_shard_rank) X(render_shard_world) X(image_snap_to_pixel_centers) X(train_prefetch)
 
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
 	NGPB_API_BEGIN
@@ -142,6 +142,8 @@ int ngpb_testbed_device_ptr(ngpb_testbed_t* t, const char* name, void** ptr, siz
 	void* p = nullptr;
 	size_t b = 0;
 	const size_t n_grid = (size_t)kNerfGridCells * (tb.max_cascade() + 1);
+	// train() returns with the backward pass and the optimizer still in flight on the testbed's stream
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(tb.stream()));
 	if (n == "params") { p = tb.params(); b = tb.n_params() * 2; }
 	else if (n == "params_fp32") { p = tb.params_fp32(); b = tb.n_params() * 4; }
 	else if (n == "params_inference") { p = tb.params_inference(); b = tb.n_params() * 2; }

@@ -211,6 +211,24 @@ NGPB_HD float from_stepping_space(float n, const Stepping& s) {
 	if (n <= s.b) return det_expf(n * s.log1p_c);
 	return (n - s.b) * kMaxConeStepsize + s.bt;
 }
+// Select forms for the march loops: the three regimes are evaluated side by side and selected, so
+// the compiler can interleave independent calls instead of emitting one branchy block per call
+// (the serial march is bound by dependent-issue latency). Each regime is the expression above:
+// same bits. kCone = false is the cone_angle <= 1e-5 case.
+template <bool kCone> NGPB_HD float to_stepping_space_sel(float t, const Stepping& s) {
+	if (!kCone) return t * kInvMinConeStepsize;
+	const float lo = (t - s.at) * kInvMinConeStepsize + s.a;
+	const float mid = det_logf(t) * s.inv_log1p_c;
+	const float hi = (t - s.bt) * kInvMaxConeStepsize + s.b;
+	return t <= s.at ? lo : (t <= s.bt ? mid : hi);
+}
+template <bool kCone> NGPB_HD float from_stepping_space_sel(float n, const Stepping& s) {
+	if (!kCone) return n * kMinConeStepsize;
+	const float lo = (n - s.a) * kMinConeStepsize + s.at;
+	const float mid = det_expf(n * s.log1p_c);
+	const float hi = (n - s.b) * kMaxConeStepsize + s.bt;
+	return n <= s.a ? lo : (n <= s.b ? mid : hi);
+}
 NGPB_HD float advance_n_steps(float t, const Stepping& s, float n) { return from_stepping_space(to_stepping_space(t, s) + n, s); }
 NGPB_HD float calc_dt(float t, const Stepping& s) { return advance_n_steps(t, s, 1.0f) - t; }
 

@@ -37,6 +37,65 @@ struct MarchScratch {
 	uint32_t* chunks;   // [n_rays_local][kChunksPerRay]
 };
 
+#ifdef NGPB_MARCH_STATS
+// Diagnostic build only (scripts/march_stats.py): histogram of loop iterations per ray, 16 per bin.
+__device__ uint32_t g_march_hist[256];
+#endif
+
+// The counting march of one ray (src/testbed_nerf.cu:760-790): distances of its samples into the
+// chunk pool, number of samples returned.
+//
+// The reference's iteration is one serial chain: position -> log -> exp (dt) -> mip -> occupancy bit
+// -> log -> exp (skip target). Here the mip level is predicted from dt ~ t * cone_angle (exact up to
+// rounding), so the occupancy load and the skip target's logarithm start beside log(t) and both
+// exponentials beside each other: two chains per iteration instead of four. The prediction is
+// checked against the real dt and the speculated values are redone when it was wrong, so every
+// value is produced by the reference's operations on the reference's operands.
+template <bool kCone>
+NGPB_D uint32_t march_and_record(const NerfTrainConfig& cfg, const uint8_t* __restrict__ bitfield, const Stepping& stepping, const MarchScratch& scratch,
+	const uint32_t local, const V3 o, const V3 dir_n, const V3 idir, const float startt, bool& pool_ok)
+{
+	uint32_t j = 0, chunk = kNoChunk;
+#ifdef NGPB_MARCH_STATS
+	uint32_t iters = 0;
+#endif
+	float t = startt;
+	V3 pos;
+	while (aabb_contains(cfg.aabb, pos = o + t * dir_n) && j < kNerfSteps) {
+#ifdef NGPB_MARCH_STATS
+		++iters;
+#endif
+		const float dt_guess = kCone ? fminf(fmaxf(t * stepping.cone_angle, kMinConeStepsize), kMaxConeStepsize) : kMinConeStepsize;
+		const uint32_t mip_guess = mip_from_dt(dt_guess, pos, cfg.max_mip);
+		bool occupied = density_grid_occupied_at(pos, bitfield, mip_guess);
+		const float n_target = to_stepping_space_sel<kCone>(t + distance_to_next_voxel(pos, dir_n, idir, pow2i(7 - (int)mip_guess), pow2i((int)mip_guess - 7)), stepping);
+		const float n = to_stepping_space_sel<kCone>(t, stepping);
+		const float dt = from_stepping_space_sel<kCone>(n + 1.0f, stepping) - t; // calc_dt
+		float t_skip = from_stepping_space_sel<kCone>(n + ceilf(fmaxf(n_target - n, 0.5f)), stepping); // advance_to_next_voxel
+		const uint32_t mip = mip_from_dt(dt, pos, cfg.max_mip);
+		if (mip != mip_guess) {
+			occupied = density_grid_occupied_at(pos, bitfield, mip);
+			t_skip = advance_to_next_voxel_n(t, n, stepping, pos, dir_n, idir, mip);
+		}
+		if (occupied) {
+			if (j % kChunk == 0) {
+				chunk = atomicAdd(scratch.pool_counter, 1u);
+				if (chunk >= scratch.n_chunks) { chunk = kNoChunk; pool_ok = false; }
+				scratch.chunks[(size_t)local * kChunksPerRay + j / kChunk] = chunk;
+			}
+			if (chunk != kNoChunk) scratch.pool[(size_t)chunk * kChunk + j % kChunk] = t;
+			++j;
+			t += dt;
+		} else {
+			t = t_skip;
+		}
+	}
+#ifdef NGPB_MARCH_STATS
+	atomicAdd(&g_march_hist[min(iters / 16u, 255u)], 1u);
+#endif
+	return j;
+}
+
 __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(const __grid_constant__ NerfTrainConfig cfg, const __grid_constant__ NerfTrainBuffers buf,
 	const __grid_constant__ Stepping stepping, Pcg32 rng, const __grid_constant__ MarchScratch scratch, const uint32_t rays_per_warp)
 {
@@ -74,33 +133,10 @@ __global__ void __launch_bounds__(kRayBlock) generate_training_samples_kernel(co
 			idir = v3(1.0f) / dir_n;
 
 			// first pass: count the samples
-			uint32_t j = 0, chunk = kNoChunk;
-			float t = startt;
-			V3 pos;
-			while (aabb_contains(cfg.aabb, pos = ray.o + t * dir_n) && j < kNerfSteps) {
-				// Both continuations are computed before the occupancy bit is looked at: the skip target
-				// does not depend on the load, so its logarithm / exponential chain runs under the
-				// load's latency instead of after it.
-				const float n = to_stepping_space(t, stepping);
-				const float dt = from_stepping_space(n + 1.0f, stepping) - t; // calc_dt
-				const uint32_t mip = mip_from_dt(dt, pos, cfg.max_mip);
-				const bool occupied = density_grid_occupied_at(pos, buf.density_bitfield, mip);
-				const float t_skip = advance_to_next_voxel_n(t, n, stepping, pos, dir_n, idir, mip);
-				if (occupied) {
-					if (j % kChunk == 0) {
-						chunk = atomicAdd(scratch.pool_counter, 1u);
-						if (chunk >= scratch.n_chunks) { chunk = kNoChunk; pool_ok = false; }
-						scratch.chunks[(size_t)local * kChunksPerRay + j / kChunk] = chunk;
-					}
-					if (chunk != kNoChunk) scratch.pool[(size_t)chunk * kChunk + j % kChunk] = t;
-					++j;
-					t += dt;
-				} else {
-					t = t_skip;
-				}
-			}
-			numsteps = j;
-			if (j == 0) valid = false;
+			numsteps = stepping.cone_angle <= 1e-5f
+				? march_and_record<false>(cfg, buf.density_bitfield, stepping, scratch, local, ray.o, dir_n, idir, startt, pool_ok)
+				: march_and_record<true>(cfg, buf.density_bitfield, stepping, scratch, local, ray.o, dir_n, idir, startt, pool_ok);
+			if (numsteps == 0) valid = false;
 		}
 	}
 
@@ -154,6 +190,16 @@ __global__ void __launch_bounds__(kRayBlock) emit_training_samples_kernel(const 
 
 void nerf_generate_training_samples(cudaStream_t stream, const NerfTrainConfig& cfg, const NerfTrainBuffers& buf, Pcg32 rng) {
 	if (local_ray_count(cfg) == 0) return;
+	// The testbed runs these two kernels on a second stream under the fused MLP kernels of the
+	// previous step. An SM keeps one shared-memory / L1 split while any block is resident, and the MLP
+	// kernels need nearly all of it as shared memory: ask for the same split here, or the MLP CTAs
+	// wait until the last march block has left the SM.
+	static const bool carveout_set = [] {
+		NGPB_CUDA_CHECK(cudaFuncSetAttribute(generate_training_samples_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+		NGPB_CUDA_CHECK(cudaFuncSetAttribute(emit_training_samples_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+		return true;
+	}();
+	(void)carveout_set;
 	const Stepping stepping = make_stepping(cfg.cone_angle_constant);
 	const uint32_t n_local = local_ray_count(cfg);
 	// rays per warp: few enough that the serial loops of a warp's rays do not pile up, many enough
@@ -177,5 +223,13 @@ void nerf_generate_training_samples(cudaStream_t stream, const NerfTrainConfig& 
 	emit_training_samples_kernel<<<div_round_up(n_local, kRayBlock / 32), kRayBlock, 0, stream>>>(cfg, buf, stepping, scratch);
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }
+
+#ifdef NGPB_MARCH_STATS
+extern "C" int ngpb_debug_march_hist(uint32_t* out256, int reset) {
+	if (cudaMemcpyFromSymbol(out256, g_march_hist, sizeof(g_march_hist)) != cudaSuccess) return 1;
+	if (reset) { static const uint32_t zero[256] = {}; cudaMemcpyToSymbol(g_march_hist, zero, sizeof(zero)); }
+	return 0;
+}
+#endif
 
 } // namespace ngpb

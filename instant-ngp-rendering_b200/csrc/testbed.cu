@@ -22,6 +22,9 @@ static int loss_type_from_string(const std::string& s) {
 Testbed::Testbed() {
 	NGPB_CUDA_CHECK(cudaStreamCreateWithFlags(&m_own_stream, cudaStreamNonBlocking));
 	m_stream = m_own_stream;
+	NGPB_CUDA_CHECK(cudaStreamCreateWithFlags(&m_side_stream, cudaStreamNonBlocking));
+	NGPB_CUDA_CHECK(cudaEventCreateWithFlags(&m_counters_ready, cudaEventDisableTiming));
+	NGPB_CUDA_CHECK(cudaEventCreateWithFlags(&m_prefetch_done, cudaEventDisableTiming));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_counters_host, sizeof(NerfStepCounters)));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_loss_host, sizeof(float)));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_counters_host_render, 64));
@@ -29,6 +32,7 @@ Testbed::Testbed() {
 }
 
 Testbed::~Testbed() {
+	if (m_side_stream) cudaStreamSynchronize(m_side_stream);
 	cudaStreamSynchronize(m_stream);
 	if (m_own_stream) cudaStreamSynchronize(m_own_stream);
 	// stream-ordered buffers must go before the stream
@@ -42,13 +46,17 @@ Testbed::~Testbed() {
 	m_optimizer.reset();
 	cudaStreamSynchronize(m_stream);
 	if (m_own_stream) { cudaStreamSynchronize(m_own_stream); cudaStreamDestroy(m_own_stream); }
+	if (m_side_stream) { cudaStreamSynchronize(m_side_stream); cudaStreamDestroy(m_side_stream); }
+	if (m_counters_ready) cudaEventDestroy(m_counters_ready);
+	if (m_prefetch_done) cudaEventDestroy(m_prefetch_done);
 	if (m_counters_host) cudaFreeHost(m_counters_host);
 	if (m_loss_host) cudaFreeHost(m_loss_host);
 	if (m_counters_host_render) cudaFreeHost(m_counters_host_render);
 }
 
 void Testbed::set_stream(cudaStream_t s) {
-	// Buffers are stream-ordered allocations: drain both streams before switching.
+	// Buffers are stream-ordered allocations: drain the streams before switching.
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_side_stream));
 	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
 	m_stream = s ? s : m_own_stream;
 	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
@@ -57,6 +65,8 @@ void Testbed::set_stream(cudaStream_t s) {
 // ---------------------------------------------------------------------------------------------
 void Testbed::create_empty_nerf_dataset(uint32_t n_images, int aabb_scale_, bool is_hdr) {
 	if (aabb_scale_ < 1 || (aabb_scale_ & (aabb_scale_ - 1)) != 0 || aabb_scale_ > 128) throw std::runtime_error{"aabb_scale must be a power of two in [1, 128]"};
+	join_prefetch();
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
 	m_images.clear();
 	m_images.resize(n_images);
 	aabb_scale = aabb_scale_;
@@ -82,6 +92,7 @@ static size_t texel_bytes(int type) {
 
 void Testbed::set_nerf_image(uint32_t idx, const void* pixels, int image_data_type, int width, int height) {
 	if (idx >= m_images.size()) throw std::runtime_error{"Invalid frame index"};
+	join_prefetch(); // the generator may still be reading the old texels
 	NerfImage& im = m_images[idx];
 	const size_t bytes = (size_t)width * height * texel_bytes(image_data_type);
 	im.pixels.alloc(bytes, m_stream);
@@ -108,6 +119,8 @@ void Testbed::set_nerf_camera(uint32_t idx, const float* x, float focal_x, float
 
 void Testbed::upload_metadata() {
 	if (!m_metadata_dirty) return;
+	join_prefetch();
+	touch_generator_inputs();
 	std::vector<ImageMeta> host(m_images.size());
 	for (size_t i = 0; i < m_images.size(); ++i) host[i] = m_images[i].meta;
 	m_metadata_gpu.alloc(std::max<size_t>(1, host.size()) * sizeof(ImageMeta), m_stream);
@@ -130,6 +143,8 @@ void Testbed::reset_network(bool clear_density_grid) {
 		reset_network_image();
 		return;
 	}
+	join_prefetch();
+	touch_generator_inputs();
 	m_rng = Pcg32{seed};
 	rays_per_batch = 1u << 12;
 	measured_batch_size_before_compaction = 0;
@@ -141,7 +156,7 @@ void Testbed::reset_network(bool clear_density_grid) {
 	m_density_grid_tmp.alloc(n_grid * sizeof(float), m_stream);
 	m_density_bitfield.reserve(nerf_bitfield_bytes(), m_stream);
 	m_density_mean.reserve(sizeof(float), m_stream);
-	m_counters.reserve(sizeof(NerfStepCounters), m_stream);
+	m_counters.reserve(2 * sizeof(NerfStepCounters), m_stream);
 	if (clear_density_grid) {
 		NGPB_CUDA_CHECK(cudaMemsetAsync(m_density_grid.ptr, 0, n_grid * sizeof(float), m_stream));
 		NGPB_CUDA_CHECK(cudaMemsetAsync(m_density_bitfield.ptr, 0, nerf_bitfield_bytes(), m_stream));

@@ -65,7 +65,13 @@ public:
 	void train_begin(uint32_t batch_size);
 	void train_end(uint32_t batch_size);
 	uint32_t shard_rank = 0, shard_world = 1;
-	NerfStepCounters* counters() { return m_counters.as<NerfStepCounters>(); }
+	NerfStepCounters* counters() { return m_counters.as<NerfStepCounters>() + m_counter_slot; }
+	// Sample prefetch (no reference counterpart): once the loss kernel of step k has reported its
+	// counts, train() marches the rays of step k+1 on a second stream, under the backward pass and
+	// the optimizer of step k. The samples depend on the dataset, the occupancy bitfield, the step's
+	// RNG and rays_per_batch only - never on the parameters - so the result is the serial one; a
+	// prefetch whose inputs changed before it is used is dropped and redone (tests/test_nerf_gpu.py).
+	bool train_prefetch = true;
 	float loss() const { return m_loss_scalar; }
 	uint32_t training_step() const { return m_training_step; }
 
@@ -127,10 +133,12 @@ public:
 	// Window policy of the wavefront: a window marches clamp(target_queries / n_alive, min, max)
 	// samples per ray (reference: 2 Mi queries, 1..8 steps, src/testbed_nerf.cu:36-38,1693-1694)
 	// and the host reads the live count back every `render_windows_per_sync` windows.
-	uint32_t render_target_queries = 2u << 20;
-	uint32_t render_min_steps = 1;
-	uint32_t render_max_steps = 8;
-	uint32_t render_windows_per_sync = 8;
+	// A pixel does not depend on the policy (tests/test_render_gpu.py), so the defaults are the
+	// fastest measured on B200 (scripts/profile_render.py), not the reference's.
+	uint32_t render_target_queries = 8u << 20;
+	uint32_t render_min_steps = 4;
+	uint32_t render_max_steps = 32;
+	uint32_t render_windows_per_sync = 4;
 	// Tile sharding: with render_shard_world > 1 only the 256-pixel tiles t of the pixel range with
 	// t % render_shard_world == render_shard_rank are traced (the others stay untouched).
 	uint32_t render_shard_rank = 0, render_shard_world = 1;
@@ -150,6 +158,24 @@ private:
 	void training_prep_nerf();
 	bool m_get_loss_scalar = false;
 	void train_nerf_step(uint32_t target_batch_size);
+	NerfTrainConfig make_train_config(uint32_t target_batch_size) const;
+	NerfTrainBuffers make_train_buffers(uint32_t counter_slot);
+	void reserve_step_buffers(uint32_t target_batch_size);
+	void control_loop(uint32_t target_batch_size);
+	void launch_prefetch(uint32_t target_batch_size);
+	void join_prefetch();   // orders m_stream after an in-flight prefetch
+	void touch_generator_inputs() { ++m_epoch; }
+	struct Prefetch {
+		bool pending = false;
+		NerfTrainConfig cfg{};
+		Pcg32 rng{};
+		uint64_t epoch = 0;
+	} m_prefetch;
+	uint64_t m_epoch = 0;          // bumped whenever something the ray generator reads changes
+	uint32_t m_counter_slot = 0;   // m_counters holds two structs: this step's and the prefetched step's
+	bool m_counters_read = false;  // the step's counters are already on their way to the host
+	cudaStream_t m_side_stream = nullptr;
+	cudaEvent_t m_counters_ready = nullptr, m_prefetch_done = nullptr;
 
 	cudaStream_t m_stream = nullptr;
 	cudaStream_t m_own_stream = nullptr;

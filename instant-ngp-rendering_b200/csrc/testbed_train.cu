@@ -2,6 +2,7 @@
 #include "testbed.h"
 
 #include <algorithm>
+#include <cstring>
 
 namespace ngpb {
 
@@ -21,10 +22,13 @@ __global__ void reduce_loss_kernel(uint32_t n, const float* __restrict__ loss, f
 }
 
 void Testbed::update_density_grid_mean_and_bitfield() {
+	join_prefetch();
+	touch_generator_inputs();
 	nerf_update_bitfield(m_stream, m_max_cascade, m_density_grid.as<float>(), m_density_bitfield.as<uint8_t>(), m_density_mean.as<float>());
 }
 
 void Testbed::update_density_grid_nerf(float decay, uint32_t n_uniform, uint32_t n_nonuniform) {
+	join_prefetch();
 	upload_metadata();
 	const uint32_t n_elements = kNerfGridCells * (m_max_cascade + 1);
 	const uint32_t n_samples = n_uniform + n_nonuniform;
@@ -63,6 +67,8 @@ void Testbed::training_prep_nerf() {
 	else update_density_grid_nerf(density_grid_decay, kNerfGridCells / 4 * n_cascades, kNerfGridCells / 4 * n_cascades);
 }
 
+static uint32_t prep_interval(uint32_t training_step) { return std::min(std::max(training_step / 16u, 1u), 16u); }
+
 void Testbed::train(uint32_t batch_size) {
 	if (m_mode == kModeImage) {
 		if (!m_image_network) throw std::runtime_error{"Unable to create a neural network trainer."};
@@ -88,8 +94,7 @@ void Testbed::train_begin(uint32_t batch_size) {
 		throw std::runtime_error{"ngp-b200: shard_world must divide 256 and leave a per-rank batch that is a multiple of 256"};
 	upload_metadata();
 
-	const uint32_t n_prep_to_skip = std::min(std::max(m_training_step / 16u, 1u), 16u);
-	if (m_training_step % n_prep_to_skip == 0) {
+	if (m_training_step % prep_interval(m_training_step) == 0) {
 		prof_mark(m_stream, "density_grid_update");
 		training_prep_nerf();
 	}
@@ -102,12 +107,11 @@ void Testbed::train_begin(uint32_t batch_size) {
 
 	m_get_loss_scalar = m_training_step % 16 == 0;
 	train_nerf_step(batch_size / shard_world);
-	if (m_get_loss_scalar) reduce_loss_kernel<<<sm_count(), 256, 0, m_stream>>>(rays_per_batch / shard_world, m_loss.as<float>(), &m_counters.as<NerfStepCounters>()->loss_sum);
 }
 
-void Testbed::train_nerf_step(uint32_t target_batch_size) {
+void Testbed::reserve_step_buffers(uint32_t target_batch_size) {
 	const uint32_t max_samples = target_batch_size * 16; // "somewhat of a worst case" (:2685)
-	m_counters.reserve(sizeof(NerfStepCounters), m_stream);
+	m_counters.reserve(2 * sizeof(NerfStepCounters), m_stream);
 	m_ray_indices.reserve((size_t)(1u << 18) * sizeof(uint32_t), m_stream);
 	m_rays.reserve((size_t)(1u << 18) * 6 * sizeof(float), m_stream);
 	m_numsteps.reserve((size_t)(1u << 18) * 2 * sizeof(uint32_t), m_stream);
@@ -116,28 +120,22 @@ void Testbed::train_nerf_step(uint32_t target_batch_size) {
 	m_rgbsigma.reserve((size_t)max_samples * 4 * sizeof(__half), m_stream);
 	m_coords_compacted.reserve((size_t)target_batch_size * kCoordFloats * sizeof(float), m_stream);
 	m_dloss.reserve((size_t)target_batch_size * 4 * sizeof(__half), m_stream);
+}
 
-	NGPB_CUDA_CHECK(cudaMemsetAsync(m_counters.ptr, 0, sizeof(NerfStepCounters), m_stream));
+// Configuration of the step that starts from the current host state (rays_per_batch, n_rays_total).
+NerfTrainConfig Testbed::make_train_config(uint32_t target_batch_size) const {
+	NerfTrainConfig cfg;
+	memset(&cfg, 0, sizeof(cfg));
 	const uint32_t n_rays_local = rays_per_batch / shard_world; // rays_per_batch is a multiple of 256, shard_world divides 256
-	NGPB_CUDA_CHECK(cudaMemsetAsync(m_loss.ptr, 0, sizeof(float) * n_rays_local, m_stream));
-	// dloss / coords of a batch that the loss kernel does not fill completely and whose roll-over
-	// finds no input must not carry stale gradients
-	NGPB_CUDA_CHECK(cudaMemsetAsync(m_dloss.ptr, 0, (size_t)target_batch_size * 4 * sizeof(__half), m_stream));
-
-	if (m_training_step == 0) n_rays_total = 0;
-	const uint32_t n_rays_total_before = n_rays_total;
-	n_rays_total += rays_per_batch;
-
-	// The reference bounds the generator by last step's measured sample count (:2730-2735) because
-	// its inference batch is sized on the host; here the sample count stays on the device and the
-	// consumers read it there, so the full buffer is available.
-	NerfTrainConfig cfg{};
 	cfg.aabb = m_aabb;
 	cfg.n_rays = rays_per_batch;
 	cfg.ray_begin = shard_rank * n_rays_local;
 	cfg.n_rays_local = n_rays_local;
-	cfg.n_rays_total = n_rays_total_before;
-	cfg.max_samples = max_samples;
+	cfg.n_rays_total = m_training_step == 0 ? 0 : n_rays_total;
+	// The reference bounds the generator by last step's measured sample count (:2730-2735) because
+	// its inference batch is sized on the host; here the sample count stays on the device and the
+	// consumers read it there, so the full buffer is available.
+	cfg.max_samples = target_batch_size * 16;
 	cfg.max_samples_compacted = target_batch_size;
 	cfg.n_training_images = n_images();
 	cfg.max_mip = m_max_cascade;
@@ -152,12 +150,15 @@ void Testbed::train_nerf_step(uint32_t target_batch_size) {
 	cfg.rgb_activation = rgb_activation;
 	cfg.density_activation = density_activation;
 	for (int k = 0; k < 3; ++k) cfg.background_color[k] = background_color[k];
+	return cfg;
+}
 
+NerfTrainBuffers Testbed::make_train_buffers(uint32_t counter_slot) {
 	NerfTrainBuffers buf{};
 	buf.metadata = metadata_gpu();
 	buf.density_bitfield = m_density_bitfield.as<uint8_t>();
 	buf.mean_density = m_density_mean.as<float>();
-	buf.counters = m_counters.as<NerfStepCounters>();
+	buf.counters = m_counters.as<NerfStepCounters>() + counter_slot;
 	buf.ray_indices = m_ray_indices.as<uint32_t>();
 	buf.rays_unnormalized = m_rays.as<float>();
 	buf.numsteps = m_numsteps.as<uint32_t>();
@@ -166,13 +167,65 @@ void Testbed::train_nerf_step(uint32_t target_batch_size) {
 	buf.coords_compacted = m_coords_compacted.as<float>();
 	buf.dloss_doutput = m_dloss.as<__half>();
 	buf.loss = m_loss.as<float>();
+	return buf;
+}
+
+void Testbed::join_prefetch() {
+	if (!m_prefetch.pending) return;
+	NGPB_CUDA_CHECK(cudaStreamWaitEvent(m_stream, m_prefetch_done, 0));
+	m_prefetch.pending = false;
+}
+
+// Rays of the NEXT step on the side stream. Called after the host has seen this step's counters,
+// i.e. after the loss kernel - the last reader of the sample buffers - has finished.
+void Testbed::launch_prefetch(uint32_t target_batch_size) {
+	const NerfTrainConfig cfg = make_train_config(target_batch_size);
+	const uint32_t slot = m_counter_slot ^ 1u;
+	const NerfTrainBuffers buf = make_train_buffers(slot);
+	NGPB_CUDA_CHECK(cudaMemsetAsync(buf.counters, 0, sizeof(NerfStepCounters), m_side_stream));
+	nerf_generate_training_samples(m_side_stream, cfg, buf, m_rng);
+	NGPB_CUDA_CHECK(cudaEventRecord(m_prefetch_done, m_side_stream));
+	m_prefetch.pending = true;
+	m_prefetch.cfg = cfg;
+	m_prefetch.rng = m_rng;
+	m_prefetch.epoch = m_epoch;
+}
+
+void Testbed::train_nerf_step(uint32_t target_batch_size) {
+	const uint32_t max_samples = target_batch_size * 16;
+	const NerfTrainConfig cfg = make_train_config(target_batch_size);
+	n_rays_total = cfg.n_rays_total + rays_per_batch;
+
+	// Adopt the prefetched samples when they were made from exactly this step's inputs.
+	const bool adopt = m_prefetch.pending && m_prefetch.epoch == m_epoch && memcmp(&m_prefetch.cfg, &cfg, sizeof(cfg)) == 0
+		&& m_prefetch.rng.state == m_rng.state && m_prefetch.rng.inc == m_rng.inc;
+	join_prefetch(); // either way the side stream is done with the buffers before this stream touches them
+	reserve_step_buffers(target_batch_size);
+	if (adopt) m_counter_slot ^= 1u;
+	const NerfTrainBuffers buf = make_train_buffers(m_counter_slot);
+
+	NGPB_CUDA_CHECK(cudaMemsetAsync(m_loss.ptr, 0, sizeof(float) * cfg.n_rays_local, m_stream));
+	// dloss / coords of a batch that the loss kernel does not fill completely and whose roll-over
+	// finds no input must not carry stale gradients
+	NGPB_CUDA_CHECK(cudaMemsetAsync(m_dloss.ptr, 0, (size_t)target_batch_size * 4 * sizeof(__half), m_stream));
 
 	prof_mark(m_stream, "generate_training_samples");
-	nerf_generate_training_samples(m_stream, cfg, buf, m_rng);
+	if (!adopt) {
+		NGPB_CUDA_CHECK(cudaMemsetAsync(buf.counters, 0, sizeof(NerfStepCounters), m_stream));
+		nerf_generate_training_samples(m_stream, cfg, buf, m_rng);
+	}
 	// network on the training parameters over exactly the generated samples (device-side count)
 	m_network->inference_counted(m_stream, max_samples, &buf.counters->numsteps, m_coords.as<float>(), kCoordFloats, m_rgbsigma.as<__half>(), 4, params());
 	prof_mark(m_stream, "loss_and_compact");
 	nerf_compute_loss_and_compact(m_stream, cfg, buf, m_rng);
+	if (m_get_loss_scalar) reduce_loss_kernel<<<sm_count(), 256, 0, m_stream>>>(cfg.n_rays_local, m_loss.as<float>(), &buf.counters->loss_sum);
+	// Single GPU: the counters are final here; their copy overtakes the backward pass. (Sharded:
+	// they are summed over the ranks first, train_end reads them.)
+	m_counters_read = shard_world == 1;
+	if (m_counters_read) {
+		NGPB_CUDA_CHECK(cudaMemcpyAsync(m_counters_host, buf.counters, sizeof(NerfStepCounters), cudaMemcpyDeviceToHost, m_stream));
+		NGPB_CUDA_CHECK(cudaEventRecord(m_counters_ready, m_stream));
+	}
 	m_network->backward_strided(m_stream, target_batch_size, m_coords_compacted.as<float>(), kCoordFloats, m_dloss.as<__half>(), 4, gradients(), params());
 	m_rng.advance(1ll << 32);
 }
@@ -180,15 +233,27 @@ void Testbed::train_nerf_step(uint32_t target_batch_size) {
 void Testbed::train_end(uint32_t target_batch_size) {
 	// In a sharded run the caller has all-reduced the gradients and the counters between
 	// train_begin and train_end, so every rank steps the same parameters with the same counts.
-	const bool get_loss_scalar = m_get_loss_scalar;
 	prof_mark(m_stream, "optimizer");
 	m_optimizer->step(m_stream, kLossScaleFp16, params_fp32(), params(), gradients());
 	prof_mark(m_stream, "end");
 	++m_training_step;
 
-	// NerfCounters::update_after_training (:2422-2446)
-	NGPB_CUDA_CHECK(cudaMemcpyAsync(m_counters_host, m_counters.ptr, sizeof(NerfStepCounters), cudaMemcpyDeviceToHost, m_stream));
-	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	if (m_counters_read) {
+		// the backward pass and the optimizer stay in flight behind this wait
+		NGPB_CUDA_CHECK(cudaEventSynchronize(m_counters_ready));
+	} else {
+		NGPB_CUDA_CHECK(cudaMemcpyAsync(m_counters_host, counters(), sizeof(NerfStepCounters), cudaMemcpyDeviceToHost, m_stream));
+		NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	}
+	control_loop(target_batch_size);
+	// No prefetch into a step that refreshes the occupancy grid first (its rays must see the new
+	// bitfield), under the phase timer (phases are timed back to back), or for a sharded testbed.
+	const bool next_step_preps = m_training_step % prep_interval(m_training_step) == 0;
+	if (train_prefetch && m_counters_read && !next_step_preps && !prof_enabled()) launch_prefetch(target_batch_size);
+}
+
+// NerfCounters::update_after_training (:2422-2446)
+void Testbed::control_loop(uint32_t target_batch_size) {
 	measured_batch_size = 0;
 	measured_batch_size_before_compaction = 0;
 	if (m_counters_host->numsteps == 0 || m_counters_host->numsteps_compacted == 0) {
@@ -197,7 +262,7 @@ void Testbed::train_end(uint32_t target_batch_size) {
 	}
 	measured_batch_size_before_compaction = m_counters_host->numsteps;
 	measured_batch_size = m_counters_host->numsteps_compacted;
-	if (get_loss_scalar) m_loss_scalar = m_counters_host->loss_sum * (float)measured_batch_size / (float)target_batch_size;
+	if (m_get_loss_scalar) m_loss_scalar = m_counters_host->loss_sum * (float)measured_batch_size / (float)target_batch_size;
 	rays_per_batch = (uint32_t)((float)rays_per_batch * (float)target_batch_size / (float)measured_batch_size);
 	rays_per_batch = std::min(next_multiple(rays_per_batch, kBatchSizeGranularity), 1u << 18);
 }

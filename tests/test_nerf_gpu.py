@@ -201,8 +201,12 @@ def test_loss_and_gradients_match_oracle(ngp, oracle, aabb_scale, loss_type, rgb
         n, cb, b = int(comp[k]), int(got_ns[k, 1]), int(numsteps_in[k, 1])
         assert np.array_equal(got_c[cb:cb + n].view(np.uint32), coords[b:b + n].view(np.uint32))
         want = dloss[b:b + n]
-        tol = 2e-3 * np.abs(want) + 2.0 ** -10 * np.abs(want) + 1e-4 * scale + 6e-8
-        assert (np.abs(got_d[cb:cb + n] - want) <= tol).all(), k
+        # the density gradient is a suffix sum that cancels to exactly 0 at a ray's last sample in the
+        # serial order; the warp-parallel suffix leaves an fp32 rounding residue there (a few 1e-7 of
+        # a loss-scaled gradient), hence the absolute terms
+        tol = 2e-3 * np.abs(want) + 2.0 ** -10 * np.abs(want) + 2e-4 * scale + 1e-6
+        err = np.abs(got_d[cb:cb + n] - want)
+        assert (err <= tol).all(), (k, n, float((err / tol).max()), np.argwhere(err > tol)[:4].tolist(), got_d[cb:cb + n][err > tol][:4].tolist(), want[err > tol][:4].tolist())
     # roll-over: the batch is padded by wrapping around, padded gradients scaled by n / batch
     assert n_compacted < batch
     i = n_compacted + 17
