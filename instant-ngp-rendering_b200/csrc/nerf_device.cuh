@@ -504,6 +504,25 @@ NGPB_HD float advance_to_next_occupied_voxel(float t, const Stepping& s, V3 o, V
 	}
 }
 
+// The same loop on the select forms of the stepping-space maps (the two logarithms of a skip are
+// independent and interleave): same operations, same operands, same t.
+template <bool kCone>
+NGPB_HD float advance_to_next_occupied_voxel_sel(float t, const Stepping& s, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bitfield,
+	uint32_t min_mip, uint32_t max_mip, const Aabb& aabb)
+{
+	while (true) {
+		const V3 pos = o + d * t;
+		if (t >= kMaxDepth || !aabb_contains(aabb, pos)) return kMaxDepth;
+		uint32_t mip = mip_from_pos(pos);
+		mip = mip < min_mip ? min_mip : (mip > max_mip ? max_mip : mip);
+		if (density_grid_occupied_at(pos, bitfield, mip)) return t;
+		while (mip < max_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
+		const float n_target = to_stepping_space_sel<kCone>(t + distance_to_next_voxel(pos, d, idir, pow2i(7 - (int)mip), pow2i((int)mip - 7)), s);
+		const float n = to_stepping_space_sel<kCone>(t, s);
+		t = from_stepping_space_sel<kCone>(n + ceilf(fmaxf(n_target - n, 0.5f)), s);
+	}
+}
+
 // ---- low-discrepancy values (random_val.cuh:161-327; Burley 2020, "Practical Hash-based Owen
 // Scrambling", JCGT 9(4)). Only Sobol dimensions 0 and 1 are needed: dimension 0 is the bit
 // reversal of the index, the direction numbers of dimension 1 follow v_k = v_{k-1} ^ (v_{k-1} >> 1).

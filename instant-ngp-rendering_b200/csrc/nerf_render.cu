@@ -83,7 +83,8 @@ __global__ void __launch_bounds__(kRayBlock) render_init_rays_kernel(const __gri
 		if (alive) {
 			const V3 idir = v3(1.0f) / d;
 			t = advance_n_steps(t, stepping, ld_random_val(p.spp_index, pix * 786433u));
-			t = advance_to_next_occupied_voxel(t, stepping, o, d, idir, bitfield, 0, p.max_mip, p.aabb);
+			t = stepping.cone_angle <= 1e-5f ? advance_to_next_occupied_voxel_sel<false>(t, stepping, o, d, idir, bitfield, 0, p.max_mip, p.aabb)
+			                                 : advance_to_next_occupied_voxel_sel<true>(t, stepping, o, d, idir, bitfield, 0, p.max_mip, p.aabb);
 			if (t >= kMaxDepth) alive = false;
 		}
 	}
@@ -100,6 +101,7 @@ __global__ void __launch_bounds__(kRayBlock) render_init_rays_kernel(const __gri
 }
 
 // generate_next_nerf_network_inputs (:417-470). Sample j of ray i lands at i + j * n_alive.
+template <bool kCone>
 __global__ void __launch_bounds__(kRayBlock) render_march_kernel(const __grid_constant__ RenderParams p, const __grid_constant__ Stepping stepping,
 	const uint8_t* __restrict__ bitfield, const uint32_t cur, float4* __restrict__ rays, uint32_t* __restrict__ ray_steps,
 	RenderCounters* __restrict__ counters, float* __restrict__ coords)
@@ -123,14 +125,25 @@ __global__ void __launch_bounds__(kRayBlock) render_march_kernel(const __grid_co
 	// One flat loop: an iteration either skips one empty voxel or emits one sample. The reference
 	// nests the skip loop inside the step loop (:436-447); in a warp of unrelated rays that shape
 	// serialises every ray's skips at every step (ncu, round 1: 5.6 of 32 lanes active). Flat, a
-	// lane that skips and a lane that emits share the iteration. Same sequence of t per ray.
+	// lane that skips and a lane that emits share the iteration - including its exponential: both
+	// continuations are from_stepping_space of (n + something), evaluated once on a per-lane
+	// argument. Same sequence of t per ray, same operations on the same operands.
 	while (j < n_steps) {
 		const V3 pos = o + d * t;
 		if (t >= kMaxDepth || !aabb_contains(p.aabb, pos)) break;
 		uint32_t mip = min(mip_from_pos(pos), p.max_mip);
-		const float n = to_stepping_space(t, stepping);
-		if (density_grid_occupied_at(pos, bitfield, mip)) {
-			const float dt = from_stepping_space(n + 1.0f, stepping) - t; // calc_dt
+		const float n = to_stepping_space_sel<kCone>(t, stepping);
+		const bool occupied = density_grid_occupied_at(pos, bitfield, mip);
+		float n_next = n + 1.0f; // calc_dt
+		if (!occupied) {
+			// largest empty voxel around the sample (nerf_device.cuh:485-490), then advance_to_next_voxel
+			while (mip < p.max_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
+			const float n_target = to_stepping_space_sel<kCone>(t + distance_to_next_voxel(pos, d, idir, pow2i(7 - (int)mip), pow2i((int)mip - 7)), stepping);
+			n_next = n + ceilf(fmaxf(n_target - n, 0.5f));
+		}
+		const float t_next = from_stepping_space_sel<kCone>(n_next, stepping);
+		if (occupied) {
+			const float dt = t_next - t;
 			const V3 wp = warp_position(pos, p.aabb);
 			float* c = coords + (size_t)(i + j * n_alive) * kCoordFloats;
 			c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt);
@@ -138,9 +151,7 @@ __global__ void __launch_bounds__(kRayBlock) render_march_kernel(const __grid_co
 			t += dt;
 			++j;
 		} else {
-			// largest empty voxel around the sample (nerf_device.cuh:485-490)
-			while (mip < p.max_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
-			t = advance_to_next_voxel_n(t, n, stepping, pos, d, idir, mip);
+			t = t_next;
 		}
 	}
 	ray_steps[i] = j;
@@ -289,7 +300,8 @@ void Testbed::render_nerf(uint32_t width, uint32_t height, const float* camera_3
 		for (uint32_t k = 0; k < chunk && steps_done < kMarchIter; ++k) {
 			const uint32_t blocks = div_round_up(bound, kRayBlock);
 			prof_mark(m_stream, "render.march");
-			render_march_kernel<<<blocks, kRayBlock, 0, m_stream>>>(p, stepping, bitfield, cur, rays[cur], ray_steps, counters, coords);
+			if (stepping.cone_angle <= 1e-5f) render_march_kernel<false><<<blocks, kRayBlock, 0, m_stream>>>(p, stepping, bitfield, cur, rays[cur], ray_steps, counters, coords);
+			else render_march_kernel<true><<<blocks, kRayBlock, 0, m_stream>>>(p, stepping, bitfield, cur, rays[cur], ray_steps, counters, coords);
 			const uint64_t hi = (uint64_t)bound * p.max_steps, lo = std::max<uint64_t>(p.target_queries, (uint64_t)bound * p.min_steps);
 			const uint32_t max_n = next_multiple((uint32_t)std::min<uint64_t>(std::min(hi, lo), max_samples - kTile), kTile);
 			m_network->inference_counted(m_stream, max_n, &counters->n_samples, coords, kCoordFloats, rgbsigma, 4, net_params);

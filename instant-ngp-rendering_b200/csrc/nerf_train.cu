@@ -204,7 +204,7 @@ void nerf_generate_training_samples(cudaStream_t stream, const NerfTrainConfig& 
 	const uint32_t n_local = local_ray_count(cfg);
 	// rays per warp: few enough that the serial loops of a warp's rays do not pile up, many enough
 	// that the warp instructions (one per iteration whatever the lane count) do not saturate issue
-	static const uint32_t max_warps = getenv("NGPB_MARCH_WARPS") ? (uint32_t)atoi(getenv("NGPB_MARCH_WARPS")) : 2048u;
+	static const uint32_t max_warps = getenv("NGPB_MARCH_WARPS") ? (uint32_t)atoi(getenv("NGPB_MARCH_WARPS")) : 512u;
 	uint32_t rays_per_warp = 1;
 	while (rays_per_warp < 32 && n_local / rays_per_warp > max_warps) rays_per_warp *= 2;
 	MarchScratch scratch{};

@@ -309,7 +309,7 @@ void NerfNetworkModule::density(cudaStream_t stream, uint32_t n, const float* in
 }
 
 void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, const __half* dL_doutput, uint32_t dy_stride,
-	__half* dL_dparams, const __half* params)
+	__half* dL_dparams, const __half* params, cudaEvent_t after_mlp)
 {
 	if (n == 0) return;
 	if (n % kTile != 0) throw std::runtime_error{"ngp-b200 NerfNetwork: batch size must be a multiple of 128"};
@@ -328,6 +328,7 @@ void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const 
 	a.dL_dparams = dL_dparams;
 	prof_mark(stream, "train.fused_mlp_fwd_bwd");
 	fused_train(stream, a);
+	if (after_mlp) NGPB_CUDA_CHECK(cudaEventRecord(after_mlp, stream));
 	prof_mark(stream, "train.grid_backward");
 	__half* ggrad = dL_dparams + pos_encoding_param_offset();
 	NGPB_CUDA_CHECK(cudaMemsetAsync(ggrad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));

@@ -25,6 +25,7 @@ Testbed::Testbed() {
 	NGPB_CUDA_CHECK(cudaStreamCreateWithFlags(&m_side_stream, cudaStreamNonBlocking));
 	NGPB_CUDA_CHECK(cudaEventCreateWithFlags(&m_counters_ready, cudaEventDisableTiming));
 	NGPB_CUDA_CHECK(cudaEventCreateWithFlags(&m_prefetch_done, cudaEventDisableTiming));
+	NGPB_CUDA_CHECK(cudaEventCreateWithFlags(&m_mlp_done, cudaEventDisableTiming));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_counters_host, sizeof(NerfStepCounters)));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_loss_host, sizeof(float)));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_counters_host_render, 64));
@@ -49,6 +50,7 @@ Testbed::~Testbed() {
 	if (m_side_stream) { cudaStreamSynchronize(m_side_stream); cudaStreamDestroy(m_side_stream); }
 	if (m_counters_ready) cudaEventDestroy(m_counters_ready);
 	if (m_prefetch_done) cudaEventDestroy(m_prefetch_done);
+	if (m_mlp_done) cudaEventDestroy(m_mlp_done);
 	if (m_counters_host) cudaFreeHost(m_counters_host);
 	if (m_loss_host) cudaFreeHost(m_loss_host);
 	if (m_counters_host_render) cudaFreeHost(m_counters_host_render);
