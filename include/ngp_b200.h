@@ -219,6 +219,13 @@ int ngpb_testbed_train(ngpb_testbed_t* t, uint32_t batch_size);
  * batch_size is the global batch in both calls. ngpb_testbed_train == begin + end for one rank. */
 int ngpb_testbed_train_begin(ngpb_testbed_t* t, uint32_t batch_size);
 int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size);
+/* The same step in three calls, which lets a sharded run keep the sample prefetch (train_prefetch):
+ * train_forward (rays, inference, loss) leaves this rank's counters in "counters"; the caller sums
+ * them over the ranks; train_backward starts their copy to the host and computes this rank's
+ * "gradients"; the caller sums those; train_end steps the optimizer and, with the global counts
+ * already on the host, marches the next step's rays under it. train_begin = forward + backward. */
+int ngpb_testbed_train_forward(ngpb_testbed_t* t, uint32_t batch_size);
+int ngpb_testbed_train_backward(ngpb_testbed_t* t, uint32_t batch_size);
 /* Named scalar properties (the public members pyngp binds, src/python_api.cu:481-566, 645-697):
  * training_step, loss, rays_per_batch, measured_batch_size, measured_batch_size_before_compaction,
  * n_params, max_cascade, cone_angle_constant, aabb_scale, seed, random_bg_color, linear_colors,

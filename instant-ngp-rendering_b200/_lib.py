@@ -100,6 +100,8 @@ SIGNATURES = {
     "ngpb_testbed_render_image": (c_int, [c_vp, c_u32, c_u32, c_vp]),
     "ngpb_testbed_train_begin": (c_int, [c_vp, c_u32]),
     "ngpb_testbed_train_end": (c_int, [c_vp, c_u32]),
+    "ngpb_testbed_train_forward": (c_int, [c_vp, c_u32]),
+    "ngpb_testbed_train_backward": (c_int, [c_vp, c_u32]),
     "ngpb_testbed_set_render_steps_out": (c_int, [c_vp, c_vp]),
     "ngpb_testbed_render_nerf": (c_int, [c_vp, c_u32, c_u32, ctypes.POINTER(c_f32), c_f32, c_f32, c_f32, c_f32, c_u32, c_u32, c_u32, c_vp, c_vp]),
     "ngpb_selftest_umma": (c_int, [c_vp, c_int, c_u32, c_u32, c_vp, c_vp, c_vp]),

@@ -93,6 +93,16 @@ int ngpb_testbed_train_begin(ngpb_testbed_t* t, uint32_t batch_size) {
 	t->impl->train_begin(batch_size);
 	NGPB_API_END
 }
+int ngpb_testbed_train_forward(ngpb_testbed_t* t, uint32_t batch_size) {
+	NGPB_API_BEGIN
+	t->impl->train_forward(batch_size);
+	NGPB_API_END
+}
+int ngpb_testbed_train_backward(ngpb_testbed_t* t, uint32_t batch_size) {
+	NGPB_API_BEGIN
+	t->impl->train_backward(batch_size, true);
+	NGPB_API_END
+}
 int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size) {
 	NGPB_API_BEGIN
 	t->impl->train_end(batch_size);

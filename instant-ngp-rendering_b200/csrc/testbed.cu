@@ -158,7 +158,7 @@ void Testbed::reset_network(bool clear_density_grid) {
 	m_density_grid_tmp.alloc(n_grid * sizeof(float), m_stream);
 	m_density_bitfield.reserve(nerf_bitfield_bytes(), m_stream);
 	m_density_mean.reserve(sizeof(float), m_stream);
-	m_counters.reserve(2 * sizeof(NerfStepCounters), m_stream);
+	m_counters.reserve(3 * sizeof(NerfStepCounters), m_stream);
 	if (clear_density_grid) {
 		NGPB_CUDA_CHECK(cudaMemsetAsync(m_density_grid.ptr, 0, n_grid * sizeof(float), m_stream));
 		NGPB_CUDA_CHECK(cudaMemsetAsync(m_density_bitfield.ptr, 0, nerf_bitfield_bytes(), m_stream));

@@ -64,8 +64,14 @@ public:
 	// on the summed values. batch_size is the GLOBAL batch in both calls.
 	void train_begin(uint32_t batch_size);
 	void train_end(uint32_t batch_size);
+	// The same step in three calls, for sharded runs that want the sample prefetch: train_forward
+	// (rays, inference, loss: counters() final for this rank), the caller sums counters() over the
+	// ranks, train_backward (gradients() final for this rank), the caller sums gradients(),
+	// train_end. train_begin == train_forward + train_backward.
+	void train_forward(uint32_t batch_size);
+	void train_backward(uint32_t batch_size, bool counters_final = true);
 	uint32_t shard_rank = 0, shard_world = 1;
-	NerfStepCounters* counters() { return m_counters.as<NerfStepCounters>() + m_counter_slot; }
+	NerfStepCounters* counters() { return m_counters.as<NerfStepCounters>() + (shard_world > 1 ? 2u : m_counter_slot); }
 	// Sample prefetch (no reference counterpart): once the loss kernel of step k has reported its
 	// counts, train() marches the rays of step k+1 on a second stream, under the backward pass and
 	// the optimizer of step k. The samples depend on the dataset, the occupancy bitfield, the step's
@@ -157,7 +163,7 @@ private:
 
 	void training_prep_nerf();
 	bool m_get_loss_scalar = false;
-	void train_nerf_step(uint32_t target_batch_size);
+	void train_nerf_forward(uint32_t target_batch_size);
 	NerfTrainConfig make_train_config(uint32_t target_batch_size) const;
 	NerfTrainBuffers make_train_buffers(uint32_t counter_slot);
 	void reserve_step_buffers(uint32_t target_batch_size);
@@ -172,7 +178,7 @@ private:
 		uint64_t epoch = 0;
 	} m_prefetch;
 	uint64_t m_epoch = 0;          // bumped whenever something the ray generator reads changes
-	uint32_t m_counter_slot = 0;   // m_counters holds two structs: this step's and the prefetched step's
+	uint32_t m_counter_slot = 0;   // m_counters holds three structs: this step's, the prefetched step's, the sharded sum
 	bool m_counters_read = false;  // the step's counters are already on their way to the host
 	cudaStream_t m_side_stream = nullptr;
 	cudaEvent_t m_counters_ready = nullptr, m_prefetch_done = nullptr, m_mlp_done = nullptr;

@@ -88,6 +88,11 @@ void Testbed::train(uint32_t batch_size) {
 }
 
 void Testbed::train_begin(uint32_t batch_size) {
+	train_forward(batch_size);
+	train_backward(batch_size, shard_world == 1);
+}
+
+void Testbed::train_forward(uint32_t batch_size) {
 	if (n_images() == 0) throw std::runtime_error{"Cannot train without training data."};
 	if (!m_network) throw std::runtime_error{"Unable to create a neural network trainer."};
 	if (batch_size == 0 || batch_size % kBatchSizeGranularity != 0) throw std::runtime_error{"ngp-b200: batch size must be a positive multiple of 256"};
@@ -107,12 +112,12 @@ void Testbed::train_begin(uint32_t batch_size) {
 	m_optimizer->update_hyperparams(leaf);
 
 	m_get_loss_scalar = m_training_step % 16 == 0;
-	train_nerf_step(batch_size / shard_world);
+	train_nerf_forward(batch_size / shard_world);
 }
 
 void Testbed::reserve_step_buffers(uint32_t target_batch_size) {
 	const uint32_t max_samples = target_batch_size * 16; // "somewhat of a worst case" (:2685)
-	m_counters.reserve(2 * sizeof(NerfStepCounters), m_stream);
+	m_counters.reserve(3 * sizeof(NerfStepCounters), m_stream);
 	m_ray_indices.reserve((size_t)(1u << 18) * sizeof(uint32_t), m_stream);
 	m_rays.reserve((size_t)(1u << 18) * 6 * sizeof(float), m_stream);
 	m_numsteps.reserve((size_t)(1u << 18) * 2 * sizeof(uint32_t), m_stream);
@@ -198,7 +203,7 @@ void Testbed::launch_prefetch(uint32_t target_batch_size) {
 	m_prefetch.epoch = m_epoch;
 }
 
-void Testbed::train_nerf_step(uint32_t target_batch_size) {
+void Testbed::train_nerf_forward(uint32_t target_batch_size) {
 	const uint32_t max_samples = target_batch_size * 16;
 	const NerfTrainConfig cfg = make_train_config(target_batch_size);
 	n_rays_total = cfg.n_rays_total + rays_per_batch;
@@ -226,11 +231,18 @@ void Testbed::train_nerf_step(uint32_t target_batch_size) {
 	prof_mark(m_stream, "loss_and_compact");
 	nerf_compute_loss_and_compact(m_stream, cfg, buf, m_rng);
 	if (m_get_loss_scalar) reduce_loss_kernel<<<sm_count(), 256, 0, m_stream>>>(cfg.n_rays_local, m_loss.as<float>(), &buf.counters->loss_sum);
-	// Single GPU: the counters are final here; their copy overtakes the backward pass. (Sharded:
-	// they are summed over the ranks first, train_end reads them.)
-	m_counters_read = shard_world == 1;
+	// Sharded: the caller sums the counters over the ranks in a buffer whose address never changes.
+	if (shard_world > 1) NGPB_CUDA_CHECK(cudaMemcpyAsync(counters(), buf.counters, sizeof(NerfStepCounters), cudaMemcpyDeviceToDevice, m_stream));
+}
+
+void Testbed::train_backward(uint32_t batch_size, bool counters_final) {
+	if (batch_size == 0 || shard_world == 0 || batch_size % shard_world != 0) throw std::runtime_error{"ngp-b200: train_backward after train_forward with the same batch size"};
+	const uint32_t target_batch_size = batch_size / shard_world;
+	// With the step's global counts known (single GPU, or already summed over the ranks) their copy
+	// to the host overtakes the backward pass; otherwise train_end reads them.
+	m_counters_read = counters_final;
 	if (m_counters_read) {
-		NGPB_CUDA_CHECK(cudaMemcpyAsync(m_counters_host, buf.counters, sizeof(NerfStepCounters), cudaMemcpyDeviceToHost, m_stream));
+		NGPB_CUDA_CHECK(cudaMemcpyAsync(m_counters_host, counters(), sizeof(NerfStepCounters), cudaMemcpyDeviceToHost, m_stream));
 		NGPB_CUDA_CHECK(cudaEventRecord(m_counters_ready, m_stream));
 	}
 	m_network->backward_strided(m_stream, target_batch_size, m_coords_compacted.as<float>(), kCoordFloats, m_dloss.as<__half>(), 4, gradients(), params(), m_mlp_done);
@@ -254,7 +266,8 @@ void Testbed::train_end(uint32_t target_batch_size) {
 	}
 	control_loop(target_batch_size);
 	// No prefetch into a step that refreshes the occupancy grid first (its rays must see the new
-	// bitfield), under the phase timer (phases are timed back to back), or for a sharded testbed.
+	// bitfield), under the phase timer (phases are timed back to back), or when the counters were
+	// only read at the end of the step (two-phase sharded protocol).
 	const bool next_step_preps = m_training_step % prep_interval(m_training_step) == 0;
 	if (train_prefetch && m_counters_read && !next_step_preps && !prof_enabled()) launch_prefetch(target_batch_size);
 }

@@ -25,6 +25,21 @@ def tile_shard_pixels(rank, world, begin, end):
     return pix[tile % world == rank]
 
 
+def allreduce_counters(counts, loss_sum=None, group=None):
+    """Sum of the step counters (and, on the steps that report a loss, the loss sum) over the ranks:
+    the first, tiny exchange of a step (Testbed.train_distributed)."""
+    import torch.distributed as dist
+    dist.all_reduce(counts, group=group)
+    if loss_sum is not None:
+        dist.all_reduce(loss_sum, group=group)
+
+
+def allreduce_gradients(gradients, group=None):
+    """Sum of the fp16 gradients of all parameters over the ranks (NCCL over NVLink on GPUs)."""
+    import torch.distributed as dist
+    dist.all_reduce(gradients, group=group)
+
+
 def allreduce_step(gradients, counts, loss_sum, group=None):
     """Sum of one training step over the ranks: fp16 gradients (all parameters), the three integer
     step counters and the loss sum. torch.distributed picks NCCL (NVLink) for CUDA tensors."""

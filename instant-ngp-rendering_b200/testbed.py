@@ -245,13 +245,21 @@ class Testbed:
         the step counters over `group` with torch.distributed (NCCL over NVLink on GPUs, gloo in
         the CPU tests of the host logic), then the optimizer step on every rank. Needs
         use_current_stream() so that the collectives are ordered with the kernels."""
-        check(lib.ngpb_testbed_train_begin(self._h, batch_size))
-        if self._get("shard_world") > 1:
-            if getattr(self, "_dp", None) is None:
-                c = self.device_buffer("counters", torch.int32)
-                self._dp = (self.device_buffer("gradients", torch.float16), c[:3], c[3:4].view(torch.float32))
-            from .sharding import allreduce_step
-            allreduce_step(*self._dp, group=group)
+        if self._get("shard_world") <= 1:
+            check(lib.ngpb_testbed_train(self._h, batch_size))
+            return
+        if getattr(self, "_dp", None) is None:
+            c = self.device_buffer("counters", torch.int32)   # fixed address while the testbed is sharded
+            self._dp = (self.device_buffer("gradients", torch.float16), c[:3], c[3:4].view(torch.float32))
+        from .sharding import allreduce_counters, allreduce_gradients
+        gradients, counts, loss_sum = self._dp
+        with_loss = self.training_step % 16 == 0   # the loss sum is only filled on these steps
+        # counters first: with the global sample count on its way to the host, the next step's rays
+        # are marched under this step's backward pass, gradient all-reduce and optimizer
+        check(lib.ngpb_testbed_train_forward(self._h, batch_size))
+        allreduce_counters(counts, loss_sum if with_loss else None, group=group)
+        check(lib.ngpb_testbed_train_backward(self._h, batch_size))
+        allreduce_gradients(gradients, group=group)
         check(lib.ngpb_testbed_train_end(self._h, batch_size))
 
     def frame(self):

@@ -56,6 +56,49 @@ def _make(ngp, syn, rank=0, world=1):
     return tb, poses, focal
 
 
+def test_emulated_two_rank_training_three_phase_with_prefetch(ngp):
+    """forward -> sum counters -> backward -> sum gradients -> end, the protocol of
+    Testbed.train_distributed: the ranks stay bit-identical, see the single-GPU batch between them,
+    and march the next step's rays early (the prefetch is on by default)."""
+    syn = importlib.import_module("instant-ngp-rendering_b200.synthetic")
+    check, lib = ngp._lib.check, ngp.lib
+    batch = 1 << 14
+    tbs = [_make(ngp, syn, r, 2)[0] for r in range(2)]
+    single = _make(ngp, syn)[0]
+    grads = [tb.device_buffer("gradients", torch.float16) for tb in tbs]
+    counters = [tb.device_buffer("counters", torch.int32) for tb in tbs]
+    for step in range(80):
+        single.train(batch)
+        for tb in tbs:
+            check(lib.ngpb_testbed_train_forward(tb._h, batch))
+        if step in (0, 40):
+            torch.cuda.synchronize()
+        if step == 0:
+            c = [x.cpu().numpy().view(np.uint32) for x in counters]
+            assert int(c[0][0] + c[1][0]) == single.measured_batch_size_before_compaction
+        cs = counters[0][:3] + counters[1][:3]
+        ls = counters[0][3:4].view(torch.float32) + counters[1][3:4].view(torch.float32)
+        for k in range(2):
+            counters[k][:3].copy_(cs)
+            counters[k][3:4].view(torch.float32).copy_(ls)
+        for tb in tbs:
+            check(lib.ngpb_testbed_train_backward(tb._h, batch))
+        g = grads[0].float() + grads[1].float()
+        for k in range(2):
+            grads[k].copy_(g.half())
+        for tb in tbs:
+            check(lib.ngpb_testbed_train_end(tb._h, batch))
+        assert tbs[0].rays_per_batch == tbs[1].rays_per_batch
+        assert tbs[0].measured_batch_size == tbs[1].measured_batch_size > 0
+    p0 = tbs[0].device_buffer("params", torch.float16)
+    p1 = tbs[1].device_buffer("params", torch.float16)
+    assert torch.equal(p0, p1)
+    assert tbs[0].training_step == 80 and tbs[0].loss < 0.7 * 0.03
+    assert abs(np.log(tbs[0].loss / single.loss)) < np.log(4.0), (tbs[0].loss, single.loss)
+    for tb in tbs + [single]:
+        tb.close()
+
+
 def test_emulated_two_rank_training_and_tile_sharded_render(ngp):
     syn = importlib.import_module("instant-ngp-rendering_b200.synthetic")
     check, lib = ngp._lib.check, ngp.lib

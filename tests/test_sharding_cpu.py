@@ -50,6 +50,16 @@ def _worker(rank, world, port, out):
     counts = torch.tensor([100 + rank, 90 + rank, 7 + rank], dtype=torch.int32)
     loss = torch.tensor([0.25 * (rank + 1)], dtype=torch.float32)
     sharding.allreduce_step(grads, counts, loss)
+    # the three-phase protocol of Testbed.train_distributed: counters first, gradients later
+    counts2 = torch.tensor([5 + rank, 4, 3 * rank], dtype=torch.int32)
+    loss2 = torch.tensor([1.5], dtype=torch.float32)
+    untouched = torch.tensor([7.0 + rank], dtype=torch.float32)
+    sharding.allreduce_counters(counts2, loss2)
+    sharding.allreduce_counters(counts2.clone(), None)   # a step that reports no loss
+    grads2 = torch.full((33,), float(rank + 1))
+    sharding.allreduce_gradients(grads2)
+    assert counts2.tolist() == [11, 8, 3] and loss2.item() == 3.0 and untouched.item() == 7.0 + rank
+    assert torch.equal(grads2, torch.full((33,), 3.0))
     out.put((rank, grads.numpy().copy(), counts.numpy().copy(), loss.numpy().copy()))
     dist.destroy_process_group()
 
