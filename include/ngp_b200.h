@@ -236,7 +236,8 @@ int ngpb_testbed_train_backward(ngpb_testbed_t* t, uint32_t batch_size);
  * image_snap_to_pixel_centers, shard_rank, shard_world (training ray shards), render_shard_rank, render_shard_world (render_nerf
  * then traces only the 256-pixel tiles t of [pixel_begin, pixel_end) with t % world == rank),
  * train_prefetch (default 1: ngpb_testbed_train marches the rays of the next step on a second stream
- * while the backward pass and the optimizer of this step run; same samples as the serial order). */
+ * while the backward pass and the optimizer of this step run; same samples as the serial order),
+ * prefetches_adopted (read-only: steps whose rays came from such a prefetch). */
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value);
 int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value);
 /* Device buffers by name: params (fp16), params_fp32, params_inference (fp16), gradients (fp16),

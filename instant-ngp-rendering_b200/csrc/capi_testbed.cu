@@ -127,6 +127,7 @@ int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
 	else if (n == "cone_angle_constant") *value = tb.cone_angle_constant();
 	else if (n == "n_images") *value = tb.n_images();
 	else if (n == "last_render_samples") *value = (double)tb.last_render_samples;
+	else if (n == "prefetches_adopted") *value = (double)tb.prefetches_adopted;
 #define X(f) else if (n == #f) *value = (double)tb.f;
 	NGPB_PROPS(X)
 #undef X

@@ -78,6 +78,7 @@ public:
 	// RNG and rays_per_batch only - never on the parameters - so the result is the serial one; a
 	// prefetch whose inputs changed before it is used is dropped and redone (tests/test_nerf_gpu.py).
 	bool train_prefetch = true;
+	uint64_t prefetches_adopted = 0; // steps whose rays came from a prefetch
 	float loss() const { return m_loss_scalar; }
 	uint32_t training_step() const { return m_training_step; }
 

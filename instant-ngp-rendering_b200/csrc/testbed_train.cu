@@ -213,7 +213,7 @@ void Testbed::train_nerf_forward(uint32_t target_batch_size) {
 		&& m_prefetch.rng.state == m_rng.state && m_prefetch.rng.inc == m_rng.inc;
 	join_prefetch(); // either way the side stream is done with the buffers before this stream touches them
 	reserve_step_buffers(target_batch_size);
-	if (adopt) m_counter_slot ^= 1u;
+	if (adopt) { m_counter_slot ^= 1u; ++prefetches_adopted; }
 	const NerfTrainBuffers buf = make_train_buffers(m_counter_slot);
 
 	NGPB_CUDA_CHECK(cudaMemsetAsync(m_loss.ptr, 0, sizeof(float) * cfg.n_rays_local, m_stream));
@@ -269,7 +269,7 @@ void Testbed::train_end(uint32_t target_batch_size) {
 	// bitfield), under the phase timer (phases are timed back to back), or when the counters were
 	// only read at the end of the step (two-phase sharded protocol).
 	const bool next_step_preps = m_training_step % prep_interval(m_training_step) == 0;
-	if (train_prefetch && m_counters_read && !next_step_preps && !prof_enabled()) launch_prefetch(target_batch_size);
+	if (train_prefetch && m_counters_read && !next_step_preps && !prof_enabled()) launch_prefetch(target_batch_size / shard_world);
 }
 
 // NerfCounters::update_after_training (:2422-2446)

@@ -95,6 +95,8 @@ def test_emulated_two_rank_training_three_phase_with_prefetch(ngp):
     assert torch.equal(p0, p1)
     assert tbs[0].training_step == 80 and tbs[0].loss < 0.7 * 0.03
     assert abs(np.log(tbs[0].loss / single.loss)) < np.log(4.0), (tbs[0].loss, single.loss)
+    # steps 0..31 refresh the occupancy grid every step (no prefetch), then every 2nd, 3rd, ...
+    assert tbs[0]._get("prefetches_adopted") >= 20 and tbs[1]._get("prefetches_adopted") == tbs[0]._get("prefetches_adopted")
     for tb in tbs + [single]:
         tb.close()
 

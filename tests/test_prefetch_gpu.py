@@ -87,6 +87,8 @@ def test_prefetch_with_training(ngp):
         for _ in range(161):
             tb.train(1 << 14)
         losses[prefetch] = tb.loss
+        adopted = tb._get("prefetches_adopted")
+        assert adopted >= 80 if prefetch else adopted == 0, adopted
         tb.close()
     assert losses[1] > 0 and losses[0] > 0
     assert losses[1] < 2.0 * losses[0] and losses[0] < 2.0 * losses[1], losses
