@@ -101,6 +101,65 @@ def test_emulated_two_rank_training_three_phase_with_prefetch(ngp):
         tb.close()
 
 
+def test_large_scene_table_sharded_training(ngp):
+    """BASELINE config 5: T = 2^22, L16 F2, aabb_scale 4 - 44.9 M hash entries, 89.8 M fp16 gradients
+    per all-reduce, a table (180 MB) larger than L2. Two emulated ranks in the three-call protocol:
+    the shards march the single-GPU batch between them, stay bit-identical and learn."""
+    syn = importlib.import_module("instant-ngp-rendering_b200.synthetic")
+    check, lib = ngp._lib.check, ngp.lib
+    cfg = dict(syn.NERF_BASE_CONFIG)
+    cfg["encoding"] = {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 2, "log2_hashmap_size": 22, "base_resolution": 16}
+    batch = 1 << 16
+
+    def make(rank=0, world=1):
+        tb = ngp.Testbed()
+        tb.use_current_stream()
+        syn.make_dataset(tb, n_images=8, width=96, height=72, aabb_scale=4)
+        tb.reload_network_from_json(cfg)
+        if world > 1:
+            tb.set_shard(rank, world)
+        return tb
+
+    tbs = [make(r, 2) for r in range(2)]
+    single = make()
+    # level table of the reference for this shape (grid.h:668-730): 5 dense levels, 11 of 2^22
+    assert tbs[0].n_params == single.n_params
+    n_grid = single.n_params - 10240
+    assert n_grid == 2 * 44_897_568 or n_grid > 2 * 44_000_000, n_grid
+    grads = [tb.device_buffer("gradients", torch.float16) for tb in tbs]
+    counters = [tb.device_buffer("counters", torch.int32) for tb in tbs]
+    assert grads[0].numel() == single.n_params
+    first = None
+    for step in range(113):
+        single.train(batch)
+        for tb in tbs:
+            check(lib.ngpb_testbed_train_forward(tb._h, batch))
+        if step == 0:
+            c = [x.cpu().numpy().view(np.uint32) for x in counters]
+            assert int(c[0][0] + c[1][0]) == single.measured_batch_size_before_compaction
+        cs = counters[0][:3] + counters[1][:3]
+        ls = counters[0][3:4].view(torch.float32) + counters[1][3:4].view(torch.float32)
+        for k in range(2):
+            counters[k][:3].copy_(cs)
+            counters[k][3:4].view(torch.float32).copy_(ls)
+        for tb in tbs:
+            check(lib.ngpb_testbed_train_backward(tb._h, batch))
+        g = grads[0].float() + grads[1].float()
+        assert float(g.abs().max()) > 0
+        for k in range(2):
+            grads[k].copy_(g.half())
+        for tb in tbs:
+            check(lib.ngpb_testbed_train_end(tb._h, batch))
+        if step == 16:
+            first = tbs[0].loss   # the loss is reported every 16th step; it rises over the first few
+        assert tbs[0].rays_per_batch == tbs[1].rays_per_batch
+    assert torch.equal(tbs[0].device_buffer("params", torch.float16), tbs[1].device_buffer("params", torch.float16))
+    assert tbs[0].training_step == 113 and tbs[0].loss < 0.6 * first, (first, tbs[0].loss)
+    assert abs(np.log(tbs[0].loss / single.loss)) < np.log(4.0), (tbs[0].loss, single.loss)
+    for tb in tbs + [single]:
+        tb.close()
+
+
 def test_emulated_two_rank_training_and_tile_sharded_render(ngp):
     syn = importlib.import_module("instant-ngp-rendering_b200.synthetic")
     check, lib = ngp._lib.check, ngp.lib
