@@ -274,6 +274,9 @@ int ngpb_testbed_set_render_steps_out(ngpb_testbed_t* t, uint32_t* steps);
  * independent random loads of entry_bytes (4, 8, 16) from a table of 2^log2_entries entries, and
  * random red.global.add.f16x2 into a table of 2^log2_entries 4-byte entries. n_threads x per_thread
  * accesses per launch (per_thread a multiple of 8 for the gather); time the launch with CUDA events. */
+/* `blocks` x `threads` that stay resident for `nanoseconds` and only sleep: measures what a kernel
+ * loses by sharing its SMs with resident blocks of another stream (scripts/corun_probe.py). */
+int ngpb_probe_resident(void* stream, uint32_t blocks, uint32_t threads, uint64_t nanoseconds);
 int ngpb_probe_gather(void* stream, const void* table, uint32_t log2_entries, uint32_t entry_bytes, uint32_t n_threads, uint32_t per_thread, uint32_t* sink);
 int ngpb_probe_scatter(void* stream, void* table, uint32_t log2_entries, uint32_t n_threads, uint32_t per_thread);
 

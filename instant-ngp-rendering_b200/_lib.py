@@ -94,6 +94,7 @@ SIGNATURES = {
     "ngpb_testbed_device_ptr": (c_int, [c_vp, c_cp, ctypes.POINTER(c_vp), ctypes.POINTER(c_sz)]),
     "ngpb_testbed_network_config": (c_sz, [c_vp, c_cp, c_sz]),
     "ngpb_testbed_update_density_grid": (c_int, [c_vp, c_f32, c_u32, c_u32]),
+    "ngpb_probe_resident": (c_int, [c_vp, c_u32, c_u32, ctypes.c_uint64]),
     "ngpb_probe_gather": (c_int, [c_vp, c_vp, c_u32, c_u32, c_u32, c_u32, c_vp]),
     "ngpb_probe_scatter": (c_int, [c_vp, c_vp, c_u32, c_u32, c_u32]),
     "ngpb_testbed_set_image": (c_int, [c_vp, c_vp, c_int, c_int, c_int]),

@@ -489,6 +489,10 @@ void fused_check_supported(const FusedNet& n) {
 template <typename K>
 static void set_smem(K kernel, uint32_t bytes) {
 	NGPB_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+	// Always the largest shared-memory split: two training CTAs need 196 KB to the byte - exactly one
+	// of the driver's carve-out steps - which would leave no room for a block of the ray-march kernel
+	// that runs beside them on the prefetch stream (an SM keeps its split while any block is resident).
+	NGPB_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 }
 
 void fused_inference(cudaStream_t stream, const FusedInferenceArgs& a) {

@@ -309,7 +309,7 @@ void NerfNetworkModule::density(cudaStream_t stream, uint32_t n, const float* in
 }
 
 void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, const __half* dL_doutput, uint32_t dy_stride,
-	__half* dL_dparams, const __half* params, cudaEvent_t after_mlp)
+	__half* dL_dparams, const __half* params, cudaEvent_t after_mlp, cudaEvent_t before_mlp)
 {
 	if (n == 0) return;
 	if (n % kTile != 0) throw std::runtime_error{"ngp-b200 NerfNetwork: batch size must be a multiple of 128"};
@@ -327,6 +327,7 @@ void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const 
 	a.dw_partials = m_scratch_dw.as<float>();
 	a.dL_dparams = dL_dparams;
 	prof_mark(stream, "train.fused_mlp_fwd_bwd");
+	if (before_mlp) NGPB_CUDA_CHECK(cudaEventRecord(before_mlp, stream));
 	fused_train(stream, a);
 	if (after_mlp) NGPB_CUDA_CHECK(cudaEventRecord(after_mlp, stream));
 	prof_mark(stream, "train.grid_backward");

@@ -75,9 +75,10 @@ public:
 	void inference_strided(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params);
 	// As inference_strided over min(*n_dev, max_n) samples, *n_dev read on the device.
 	void inference_counted(cudaStream_t stream, uint32_t max_n, const uint32_t* n_dev, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params);
-	// after_mlp (optional): recorded once the fused MLP kernel is done, before the grid scatter.
+	// before_mlp / after_mlp (optional): recorded right before the fused MLP kernel is launched (the
+	// encoder pass is done) and once it is done, before the grid scatter.
 	void backward_strided(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, const __half* dL_doutput, uint32_t dy_stride,
-		__half* dL_dparams, const __half* params, cudaEvent_t after_mlp = nullptr);
+		__half* dL_dparams, const __half* params, cudaEvent_t after_mlp = nullptr, cudaEvent_t before_mlp = nullptr);
 	// NerfNetwork::density (nerf_network.h:270-279): out[i*out_stride] = density-MLP output 0 when
 	// out_stride == 1, else the padded 16 outputs.
 	void density(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params);

@@ -37,7 +37,28 @@ __global__ void __launch_bounds__(256) scatter_probe_kernel(__half* __restrict__
 	}
 }
 
+// Blocks that stay resident for `ns` nanoseconds without issuing work (they sleep): what a kernel
+// loses by SHARING its SMs with other blocks, as opposed to competing with them.
+__global__ void resident_probe_kernel(unsigned long long ns) {
+	unsigned long long t0, t;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+	do {
+		__nanosleep(2000);
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+	} while (t - t0 < ns);
+}
+
 } // namespace ngpb
+
+extern "C" int ngpb_probe_resident(void* stream, uint32_t blocks, uint32_t threads, uint64_t nanoseconds) {
+	using namespace ngpb;
+	try {
+		if (blocks == 0 || threads == 0 || threads > 1024 || nanoseconds > 2000000000ull) throw std::runtime_error{"ngpb_probe_resident: 1..1024 threads, at most 2 s"};
+		resident_probe_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(nanoseconds);
+		NGPB_CUDA_CHECK(cudaGetLastError());
+		return NGPB_OK;
+	} catch (const std::exception& e) { set_last_error(e.what()); return NGPB_ERROR; }
+}
 
 extern "C" int ngpb_probe_gather(void* stream, const void* table, uint32_t log2_entries, uint32_t entry_bytes, uint32_t n_threads, uint32_t per_thread, uint32_t* sink) {
 	using namespace ngpb;

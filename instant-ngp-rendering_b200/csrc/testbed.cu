@@ -26,6 +26,7 @@ Testbed::Testbed() {
 	NGPB_CUDA_CHECK(cudaEventCreateWithFlags(&m_counters_ready, cudaEventDisableTiming));
 	NGPB_CUDA_CHECK(cudaEventCreateWithFlags(&m_prefetch_done, cudaEventDisableTiming));
 	NGPB_CUDA_CHECK(cudaEventCreateWithFlags(&m_mlp_done, cudaEventDisableTiming));
+	NGPB_CUDA_CHECK(cudaEventCreateWithFlags(&m_encoder_done, cudaEventDisableTiming));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_counters_host, sizeof(NerfStepCounters)));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_loss_host, sizeof(float)));
 	NGPB_CUDA_CHECK(cudaMallocHost(&m_counters_host_render, 64));
@@ -51,6 +52,7 @@ Testbed::~Testbed() {
 	if (m_counters_ready) cudaEventDestroy(m_counters_ready);
 	if (m_prefetch_done) cudaEventDestroy(m_prefetch_done);
 	if (m_mlp_done) cudaEventDestroy(m_mlp_done);
+	if (m_encoder_done) cudaEventDestroy(m_encoder_done);
 	if (m_counters_host) cudaFreeHost(m_counters_host);
 	if (m_loss_host) cudaFreeHost(m_loss_host);
 	if (m_counters_host_render) cudaFreeHost(m_counters_host_render);

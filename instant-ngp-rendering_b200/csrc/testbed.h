@@ -182,7 +182,7 @@ private:
 	uint32_t m_counter_slot = 0;   // m_counters holds three structs: this step's, the prefetched step's, the sharded sum
 	bool m_counters_read = false;  // the step's counters are already on their way to the host
 	cudaStream_t m_side_stream = nullptr;
-	cudaEvent_t m_counters_ready = nullptr, m_prefetch_done = nullptr, m_mlp_done = nullptr;
+	cudaEvent_t m_counters_ready = nullptr, m_prefetch_done = nullptr, m_mlp_done = nullptr, m_encoder_done = nullptr;
 
 	cudaStream_t m_stream = nullptr;
 	cudaStream_t m_own_stream = nullptr;

@@ -194,6 +194,16 @@ void Testbed::launch_prefetch(uint32_t target_batch_size) {
 	// step to hide the march under: measured 0.61 ms / step against 0.54 for the early start.
 	static const bool after_mlp = getenv("NGPB_PREFETCH_LATE") && atoi(getenv("NGPB_PREFETCH_LATE"));
 	if (after_mlp) NGPB_CUDA_CHECK(cudaStreamWaitEvent(m_side_stream, m_mlp_done, 0));
+	// An SM keeps its shared-memory / L1 split while any block is resident, and a block only sets the
+	// split of an SM it finds idle. March blocks that land on SMs still running the encoder pass
+	// (small split) pin that split for their whole life and keep the fused MLP CTAs (100 KB each) off
+	// those SMs: with sleeping resident blocks on half the SMs (scripts/corun_probe.py) the MLP
+	// kernel takes 1.6x as long, with the march 1.4-1.8x. Starting the march once the encoder pass
+	// has drained (NGPB_PREFETCH_WITH_MLP=1; both kernels ask for the largest split) brings the MLP
+	// kernel back to 93 us, but the march itself is the longer chain of the two (~340 us beside the
+	// other kernels) and the 30 us it starts later cost more: 0.570 against 0.543 ms / step.
+	static const bool with_mlp = getenv("NGPB_PREFETCH_WITH_MLP") && atoi(getenv("NGPB_PREFETCH_WITH_MLP"));
+	if (with_mlp && !after_mlp) NGPB_CUDA_CHECK(cudaStreamWaitEvent(m_side_stream, m_encoder_done, 0));
 	NGPB_CUDA_CHECK(cudaMemsetAsync(buf.counters, 0, sizeof(NerfStepCounters), m_side_stream));
 	nerf_generate_training_samples(m_side_stream, cfg, buf, m_rng);
 	NGPB_CUDA_CHECK(cudaEventRecord(m_prefetch_done, m_side_stream));
@@ -245,7 +255,7 @@ void Testbed::train_backward(uint32_t batch_size, bool counters_final) {
 		NGPB_CUDA_CHECK(cudaMemcpyAsync(m_counters_host, counters(), sizeof(NerfStepCounters), cudaMemcpyDeviceToHost, m_stream));
 		NGPB_CUDA_CHECK(cudaEventRecord(m_counters_ready, m_stream));
 	}
-	m_network->backward_strided(m_stream, target_batch_size, m_coords_compacted.as<float>(), kCoordFloats, m_dloss.as<__half>(), 4, gradients(), params(), m_mlp_done);
+	m_network->backward_strided(m_stream, target_batch_size, m_coords_compacted.as<float>(), kCoordFloats, m_dloss.as<__half>(), 4, gradients(), params(), m_mlp_done, m_encoder_done);
 	m_rng.advance(1ll << 32);
 }
 
