@@ -353,9 +353,12 @@ def grid_measure(ngp, steps, warmup, rank, world, local):
         "config": {"workload": "grid_L16F2_T19_2^20pts", "encoding": GRID_ENC, "points_per_step_per_gpu": n,
                    "l2": "flushed between timed steps (256 MiB write)", "parallelism": "replicas only" if world > 1 else "1 GPU"},
         "kernels_ms": {"grid_forward_kernel": f_ms, "memset+grid_backward_kernel": b_ms},
-        "gather_roofline": {"what": "16 levels x 8 corners = 128 random 4-byte accesses per point against the rate of the probe kernels on this GPU",
+        "gather_roofline": {"what": "16 levels x 8 corners = 128 4-byte accesses per point against the rate of FULLY RANDOM accesses (probe kernels, same run, 32 MiB table); "
+                                    "the encoder beats the random rate forward because the two x-neighbours of a corner pair share a sector and the coarse levels hit L1",
                             "forward": {"achieved": fwd_rate, "peak": probe["gather"], "unit": "G loads/s", "frac": fwd_rate / probe["gather"]},
-                            "backward": {"achieved": bwd_rate, "peak": probe["scatter"], "unit": "G red.f16x2/s", "frac": bwd_rate / probe["scatter"]}},
+                            "backward": {"achieved": bwd_rate, "peak": probe["scatter"], "unit": "G red.f16x2/s", "frac": bwd_rate / probe["scatter"]},
+                            "fwd_bwd": {"ms": f_ms + b_ms, "ms_at_probe_rates": (n * 128 / probe["gather"] + n * 128 / probe["scatter"]) / 1e9 * 1e3,
+                                        "frac": (n * 128 / probe["gather"] + n * 128 / probe["scatter"]) / 1e9 * 1e3 / (f_ms + b_ms)}},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                      "traffic": load_traffic(dom), "peak_source": peaks["source"],
                      "note": "algorithmic 588 B/point per direction; the 24.4 MB table is L2-resident, so the HBM copy peak is a floor for the gather roofline, not a ceiling"},

@@ -195,6 +195,7 @@ void nerf_generate_training_samples(cudaStream_t stream, const NerfTrainConfig& 
 	// kernels need nearly all of it as shared memory: ask for the same split here, or the MLP CTAs
 	// wait until the last march block has left the SM.
 	static const bool carveout_set = [] {
+		if (getenv("NGPB_MARCH_SPLIT_DEFAULT") && atoi(getenv("NGPB_MARCH_SPLIT_DEFAULT"))) return false;
 		NGPB_CUDA_CHECK(cudaFuncSetAttribute(generate_training_samples_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 		NGPB_CUDA_CHECK(cudaFuncSetAttribute(emit_training_samples_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 		return true;
