@@ -190,6 +190,19 @@ int ngpb_nerf_compute_loss_and_compact(void* stream, const ngpb_nerf_train_confi
  * order, bitfield uint8 [8 * 128^3 / 8], mean_density 1 float. */
 int ngpb_nerf_update_bitfield(void* stream, uint32_t max_cascade, const float* grid, uint8_t* bitfield, float* mean_density);
 size_t ngpb_nerf_bitfield_bytes(void);
+/* The kernels of update_density_grid_nerf (src/testbed_nerf.cu:2271-2360), one call each:
+ * mark_untrained_density_grid (:74-147; cells no camera sees become -1), in place on grid [n_elements];
+ * generate_grid_samples_nerf_nonuniform (:149-184): n cells chosen by the (index, step) hash among those
+ *   above `thresh`, a random position in each -> positions float [n][4] (warped xyz, warped dt), indices [n];
+ *   aabb6 = min xyz, max xyz; rng_state = {state, inc} of m_density_grid_rng;
+ * splat_grid_samples_nerf_max_nearest_neighbor (:186-204): grid_tmp[indices[i]] = max(., density * min step),
+ *   density_raw = fp16 density-network output per sample;
+ * ema_grid_samples_nerf (:264-282): grid = grid < 0 ? grid : max(grid * decay, grid_tmp). */
+int ngpb_nerf_mark_untrained_density_grid(void* stream, uint32_t n_elements, float* grid, uint32_t n_images, const ngpb_nerf_image_t* metadata, int clear_visible_voxels);
+int ngpb_nerf_generate_grid_samples(void* stream, uint32_t n, const uint64_t* rng_state, uint32_t step, const float* aabb6, const float* grid_in,
+	float* positions, uint32_t* indices, uint32_t n_cascades, float thresh);
+int ngpb_nerf_splat_grid_samples(void* stream, uint32_t n, const uint32_t* indices, const void* density_raw, float* grid_tmp, int density_activation);
+int ngpb_nerf_ema_grid_samples(void* stream, uint32_t n_elements, float decay, float* grid, const float* grid_tmp);
 
 /* ---- Testbed (include/neural-graphics-primitives/testbed.h, src/python_api.cu:383-567) -------------
  * NeRF mode of ngp::Testbed: dataset set-up as pyngp's create_empty_nerf_dataset / set_image /

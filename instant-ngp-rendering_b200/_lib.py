@@ -74,6 +74,10 @@ SIGNATURES = {
     "ngpb_optimizer_state": (c_int, [c_vp, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
     "ngpb_nerf_network_density": (c_int, [c_vp, c_vp, c_u32, c_vp, c_u32, c_vp, c_u32, c_vp]),
     "ngpb_nerf_network_param_layout": (c_int, [c_vp, ctypes.POINTER(c_sz)]),
+    "ngpb_nerf_mark_untrained_density_grid": (c_int, [c_vp, c_u32, c_vp, c_u32, c_vp, c_int]),
+    "ngpb_nerf_generate_grid_samples": (c_int, [c_vp, c_u32, ctypes.POINTER(c_u64), c_u32, ctypes.POINTER(c_f32), c_vp, c_vp, c_vp, c_u32, c_f32]),
+    "ngpb_nerf_splat_grid_samples": (c_int, [c_vp, c_u32, c_vp, c_vp, c_vp, c_int]),
+    "ngpb_nerf_ema_grid_samples": (c_int, [c_vp, c_u32, c_f32, c_vp, c_vp]),
     "ngpb_nerf_generate_training_samples": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(c_u64)]),
     "ngpb_nerf_compute_loss_and_compact": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(c_u64)]),
     "ngpb_nerf_update_bitfield": (c_int, [c_vp, c_u32, c_vp, c_vp, c_vp]),

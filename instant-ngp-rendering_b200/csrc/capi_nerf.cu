@@ -140,4 +140,34 @@ int ngpb_nerf_update_bitfield(void* stream, uint32_t max_cascade, const float* g
 }
 size_t ngpb_nerf_bitfield_bytes(void) { return nerf_bitfield_bytes(); }
 
+int ngpb_nerf_mark_untrained_density_grid(void* stream, uint32_t n_elements, float* grid, uint32_t n_images, const ngpb_nerf_image_t* metadata, int clear_visible_voxels) {
+	NGPB_API_BEGIN
+	require_device();
+	static_assert(sizeof(ngpb_nerf_image_t) == sizeof(ImageMeta), "ngpb_nerf_image_t must mirror ImageMeta");
+	nerf_mark_untrained_density_grid((cudaStream_t)stream, n_elements, grid, n_images, reinterpret_cast<const ImageMeta*>(metadata), clear_visible_voxels != 0);
+	NGPB_API_END
+}
+int ngpb_nerf_generate_grid_samples(void* stream, uint32_t n, const uint64_t* rng_state, uint32_t step, const float* aabb6, const float* grid_in,
+	float* positions, uint32_t* indices, uint32_t n_cascades, float thresh)
+{
+	NGPB_API_BEGIN
+	require_device();
+	if (n_cascades == 0 || n_cascades > kNerfCascades) throw std::runtime_error{"ngpb_nerf_generate_grid_samples: n_cascades must be 1..8"};
+	const Aabb aabb = {{aabb6[0], aabb6[1], aabb6[2]}, {aabb6[3], aabb6[4], aabb6[5]}};
+	nerf_generate_grid_samples((cudaStream_t)stream, n, rng_from(rng_state), step, aabb, grid_in, positions, indices, n_cascades, thresh);
+	NGPB_API_END
+}
+int ngpb_nerf_splat_grid_samples(void* stream, uint32_t n, const uint32_t* indices, const void* density_raw, float* grid_tmp, int density_activation) {
+	NGPB_API_BEGIN
+	require_device();
+	nerf_splat_grid_samples((cudaStream_t)stream, n, indices, (const __half*)density_raw, grid_tmp, density_activation);
+	NGPB_API_END
+}
+int ngpb_nerf_ema_grid_samples(void* stream, uint32_t n_elements, float decay, float* grid, const float* grid_tmp) {
+	NGPB_API_BEGIN
+	require_device();
+	nerf_ema_grid_samples((cudaStream_t)stream, n_elements, decay, grid, grid_tmp);
+	NGPB_API_END
+}
+
 } // extern "C"

@@ -10,6 +10,8 @@
 //   generate_training_samples_nerf            src/testbed_nerf.cu:679-838
 //   compute_loss_kernel_train_nerf            src/testbed_nerf.cu:841-1160 (no envmap / depth / error map / exposure)
 //   grid_to_bitfield, bitfield_max_pool, mean src/testbed_nerf.cu:284-331, 2362-2379
+//   mark_untrained_density_grid, generate_grid_samples_nerf_nonuniform, splat_grid_samples_nerf_max_nearest_neighbor,
+//   ema_grid_samples_nerf                     src/testbed_nerf.cu:74-282; pos_to_uv common_device.cuh:497-531
 // PARITY UNPINNED by the reference (no golden vectors, GPU-only, built with --use_fast_math). log / exp in
 // the exponential stepping are the single-precision Cephes algorithms so that host and device agree bit
 // for bit; everything else that decides where a sample lies is IEEE add/mul/div/sqrt (-ffp-contract=off).
@@ -506,6 +508,105 @@ extern "C" void oracle_nerf_bitfield(uint32_t max_cascade, const float* grid, ui
 			const uint32_t x = morton3D_invert(i >> 0) + GRIDSIZE / 8, y = morton3D_invert(i >> 1) + GRIDSIZE / 8, z = morton3D_invert(i >> 2) + GRIDSIZE / 8;
 			next[morton3D(x, y, z)] |= bits;
 		}
+	}
+}
+
+// ---- occupancy-grid maintenance (src/testbed_nerf.cu:74-282) ---------------------------------------
+namespace {
+// pos_to_uv (common_device.cuh:497-531) without parallax / foveation: the inverse of the camera's
+// 3x3 part by cofactors, in the operation order of csrc/nerf_grid.cu so that both sides round alike.
+void pos_to_uv(V pos, const oracle_nerf_image& m, float& u, float& v) {
+	const Cam cam = cam_of(m);
+	const V d = pos - cam.c[3];
+	const V c0 = cam.c[0], c1 = cam.c[1], c2 = cam.c[2];
+	const float det = c0.x * (c1.y * c2.z - c2.y * c1.z) - c1.x * (c0.y * c2.z - c2.y * c0.z) + c2.x * (c0.y * c1.z - c1.y * c0.z);
+	const float inv = 1.0f / det;
+	V dir;
+	dir.x = inv * (d.x * (c1.y * c2.z - c2.y * c1.z) - c1.x * (d.y * c2.z - c2.y * d.z) + c2.x * (d.y * c1.z - c1.y * d.z));
+	dir.y = inv * (c0.x * (d.y * c2.z - c2.y * d.z) - d.x * (c0.y * c2.z - c2.y * c0.z) + c2.x * (c0.y * d.z - d.y * c0.z));
+	dir.z = inv * (c0.x * (c1.y * d.z - d.y * c1.z) - c1.x * (c0.y * d.z - d.y * c0.z) + d.x * (c0.y * c1.z - c1.y * c0.z));
+	dir = dir / dir.z;
+	float du = 0.0f, dv = 0.0f;
+	if (m.lens_mode == 1) opencv_lens_distortion_delta(m.lens_params, dir.x, dir.y, &du, &dv);
+	dir.x += du;
+	dir.y += dv;
+	u = dir.x * m.focal_x / (float)m.res_x + m.principal_x;
+	v = dir.y * m.focal_y / (float)m.res_y + m.principal_y;
+}
+} // namespace
+
+// mark_untrained_density_grid (:74-147): a cell no training camera sees is marked -1 (never sampled).
+extern "C" void oracle_nerf_mark_untrained(uint32_t n_elements, float* grid, uint32_t n_images, const oracle_nerf_image* images, int clear_visible_voxels) {
+#pragma omp parallel for schedule(static)
+	for (int64_t ii = 0; ii < (int64_t)n_elements; ++ii) {
+		const uint32_t i = (uint32_t)ii;
+		const uint32_t level = i / GRID_CELLS, pos_idx = i % GRID_CELLS;
+		const uint32_t x = morton3D_invert(pos_idx >> 0), y = morton3D_invert(pos_idx >> 1), z = morton3D_invert(pos_idx >> 2);
+		const float voxel_size = scalbnf(1.0f / GRIDSIZE, (int)level);
+		const V pos = (V{(float)x, (float)y, (float)z} / (float)GRIDSIZE - 0.5f) * scalbnf(1.0f, (int)level) + 0.5f;
+		const uint32_t min_count = 1;
+		uint32_t count = 0;
+		for (uint32_t j = 0; j < n_images && count < min_count; ++j) {
+			const oracle_nerf_image& m = images[j];
+			const Cam cam = cam_of(m);
+			for (uint32_t k = 0; k < 8; ++k) {
+				const V corner = pos + V{(k & 1) ? voxel_size : 0.0f, (k & 2) ? voxel_size : 0.0f, (k & 4) ? voxel_size : 0.0f};
+				const V dir = normalize(corner - cam.c[3]);
+				if (dot(dir, cam.c[2]) < 1e-4f) continue;
+				float u, v;
+				pos_to_uv(corner, m, u, v);
+				V ro, rd;
+				uv_to_ray(u, v, m, ro, rd);
+				if (length(normalize(rd) - dir) < 1e-3f && u > 0.0f && v > 0.0f && u < 1.0f && v < 1.0f) { ++count; break; }
+			}
+		}
+		if (clear_visible_voxels || (grid[i] < 0) != (count < min_count)) grid[i] = (count >= min_count) ? 0.f : -1.f;
+	}
+}
+
+// generate_grid_samples_nerf_nonuniform (:149-184): positions [n][4] (warped xyz, warped dt) and cell indices.
+extern "C" void oracle_nerf_generate_grid_samples(uint32_t n, const uint64_t* rng_state, uint32_t step, const float* aabb6, const float* grid_in,
+	float* positions, uint32_t* indices, uint32_t n_cascades, float thresh)
+{
+	const Box aabb = {{aabb6[0], aabb6[1], aabb6[2]}, {aabb6[3], aabb6[4], aabb6[5]}};
+	for (uint32_t i = 0; i < n; ++i) {
+		OraclePcg32 rng = rng_of(rng_state);
+		rng.advance((int64_t)i * 4);
+		const uint32_t level = (uint32_t)(rng.next_float() * n_cascades) % n_cascades;
+		uint32_t idx = 0;
+		for (uint32_t j = 0; j < 10; ++j) {
+			idx = ((i + step * n) * 56924617u + j * 19349663u + 96925573u) % GRID_CELLS;
+			idx += level * GRID_CELLS;
+			if (grid_in[idx] > thresh) break;
+		}
+		const uint32_t pos_idx = idx % GRID_CELLS;
+		const uint32_t x = morton3D_invert(pos_idx >> 0), y = morton3D_invert(pos_idx >> 1), z = morton3D_invert(pos_idx >> 2);
+		const float rx = rng.next_float(), ry = rng.next_float(), rz = rng.next_float();
+		const V pos = ((V{(float)x, (float)y, (float)z} + V{rx, ry, rz}) / (float)GRIDSIZE - 0.5f) * scalbnf(1.0f, (int)level) + 0.5f;
+		const V wp = (pos - aabb.min) / diag(aabb);
+		positions[(size_t)i * 4 + 0] = wp.x; positions[(size_t)i * 4 + 1] = wp.y; positions[(size_t)i * 4 + 2] = wp.z;
+		positions[(size_t)i * 4 + 3] = warp_dt(MIN_CONE_STEPSIZE);
+		indices[i] = idx;
+	}
+}
+
+// splat_grid_samples_nerf_max_nearest_neighbor (:186-204): running maximum of the optical thickness per cell.
+extern "C" void oracle_nerf_splat_grid_samples(uint32_t n, const uint32_t* indices, const uint16_t* density_raw, float* grid_tmp, int density_activation) {
+	for (uint32_t i = 0; i < n; ++i) {
+		const float mlp = net_to_density(oracle_half_to_float(density_raw[i]), density_activation);
+		const float optical_thickness = mlp * MIN_CONE_STEPSIZE;
+		uint32_t bits, cur;
+		memcpy(&bits, &optical_thickness, 4);
+		memcpy(&cur, &grid_tmp[indices[i]], 4);
+		if (bits > cur) memcpy(&grid_tmp[indices[i]], &bits, 4); // atomicMax on the bit patterns, as the reference does
+	}
+}
+
+// ema_grid_samples_nerf (:264-282)
+extern "C" void oracle_nerf_ema_grid_samples(uint32_t n_elements, float decay, float* grid, const float* grid_tmp) {
+	for (uint32_t i = 0; i < n_elements; ++i) {
+		const float importance = grid_tmp[i], prev_val = grid[i];
+		grid[i] = (prev_val < 0.f) ? prev_val : fmaxf(prev_val * decay, importance);
 	}
 }
 

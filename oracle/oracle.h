@@ -113,6 +113,14 @@ void oracle_nerf_compute_loss(const oracle_nerf_config* cfg, const oracle_nerf_i
 	const uint64_t* rng_state, uint32_t* compacted_numsteps, float* loss, float* dloss);
 /* grid_to_bitfield + bitfield_max_pool + mean (src/testbed_nerf.cu:284-331, 2362-2379). */
 void oracle_nerf_bitfield(uint32_t max_cascade, const float* grid, uint8_t* bitfield, float* mean_density);
+/* Occupancy-grid maintenance (src/testbed_nerf.cu:74-282): mark_untrained_density_grid (in place on `grid`),
+ * generate_grid_samples_nerf_nonuniform (positions [n][4], indices [n]; aabb6 = min xyz, max xyz),
+ * splat_grid_samples_nerf_max_nearest_neighbor (density_raw fp16 bits), ema_grid_samples_nerf. */
+void oracle_nerf_mark_untrained(uint32_t n_elements, float* grid, uint32_t n_images, const oracle_nerf_image* images, int clear_visible_voxels);
+void oracle_nerf_generate_grid_samples(uint32_t n, const uint64_t* rng_state, uint32_t step, const float* aabb6, const float* grid_in,
+	float* positions, uint32_t* indices, uint32_t n_cascades, float thresh);
+void oracle_nerf_splat_grid_samples(uint32_t n, const uint32_t* indices, const uint16_t* density_raw, float* grid_tmp, int density_activation);
+void oracle_nerf_ema_grid_samples(uint32_t n_elements, float decay, float* grid, const float* grid_tmp);
 /* deterministic log / exp used by the stepping (Cephes single precision) */
 float oracle_det_logf(float x);
 float oracle_det_expf(float x);

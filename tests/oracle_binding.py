@@ -342,6 +342,41 @@ def nerf_bitfield(max_cascade, grid):
     return bf, mean.value
 
 
+# ---- occupancy-grid maintenance ------------------------------------------------------------------
+def nerf_mark_untrained(grid, images, clear_visible_voxels=True):
+    """In-place mark_untrained_density_grid on a copy of `grid`; returns the copy."""
+    arr = (NerfImage * len(images))(*images)
+    g = np.array(grid, dtype=np.float32, copy=True)
+    olib.oracle_nerf_mark_untrained(ctypes.c_uint32(g.size), _p(g, ctypes.c_float), ctypes.c_uint32(len(images)), arr, ctypes.c_int(int(clear_visible_voxels)))
+    return g
+
+
+def nerf_generate_grid_samples(n, rng, step, aabb_min, aabb_max, grid_in, n_cascades, thresh):
+    """Returns (positions [n][4] float32, indices [n] uint32)."""
+    g = np.ascontiguousarray(grid_in, dtype=np.float32)
+    aabb = np.array(list(aabb_min) + list(aabb_max), dtype=np.float32)
+    pos = np.zeros((n, 4), dtype=np.float32)
+    idx = np.zeros(n, dtype=np.uint32)
+    olib.oracle_nerf_generate_grid_samples(ctypes.c_uint32(n), _p(rng.arr, ctypes.c_uint64), ctypes.c_uint32(step), _p(aabb, ctypes.c_float), _p(g, ctypes.c_float),
+                                           _p(pos, ctypes.c_float), _p(idx, ctypes.c_uint32), ctypes.c_uint32(n_cascades), ctypes.c_float(thresh))
+    return pos, idx
+
+
+def nerf_splat_grid_samples(indices, density_raw_f16, grid_tmp, density_activation):
+    g = np.array(grid_tmp, dtype=np.float32, copy=True)
+    idx = np.ascontiguousarray(indices, dtype=np.uint32)
+    d = np.ascontiguousarray(density_raw_f16, dtype=np.float16)
+    olib.oracle_nerf_splat_grid_samples(ctypes.c_uint32(len(idx)), _p(idx, ctypes.c_uint32), _p(d.view(np.uint16), ctypes.c_uint16), _p(g, ctypes.c_float), ctypes.c_int(density_activation))
+    return g
+
+
+def nerf_ema_grid_samples(decay, grid, grid_tmp):
+    g = np.array(grid, dtype=np.float32, copy=True)
+    t = np.ascontiguousarray(grid_tmp, dtype=np.float32)
+    olib.oracle_nerf_ema_grid_samples(ctypes.c_uint32(g.size), ctypes.c_float(decay), _p(g, ctypes.c_float), _p(t, ctypes.c_float))
+    return g
+
+
 # ---- NeRF rendering (oracle_nerf_render_*) --------------------------------------------------------
 class RenderConfig(ctypes.Structure):
     """oracle_render_config."""

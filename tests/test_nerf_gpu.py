@@ -231,3 +231,88 @@ def test_bitfield_bit_exact(ngp, oracle, max_cascade):
     assert abs(float(mean.item()) - want_mean) <= 1e-5 * want_mean
     # coarser cascades are supersets (max pooling)
     assert want_bf[128 ** 3 // 8 * 7:].any()
+
+
+def _meta_on_device(oracle, images):
+    meta = (oracle.NerfImage * len(images))()
+    keep = []
+    for i, im in enumerate(images):
+        ctypes.memmove(ctypes.byref(meta[i]), ctypes.byref(im), ctypes.sizeof(oracle.NerfImage))
+        px = _dev(im._keep)
+        keep.append(px)
+        meta[i].pixels = px.data_ptr()
+    return _dev(np.frombuffer(bytes(meta), dtype=np.uint8).copy()), keep
+
+
+@pytest.mark.parametrize("aabb_scale,lens", [(1, None), (4, None), (2, (0.05, -0.02, 0.001, -0.002))])
+def test_mark_untrained_density_grid_bit_exact(ngp, oracle, aabb_scale, lens):
+    """mark_untrained_density_grid (src/testbed_nerf.cu:74-147): which cells any camera sees."""
+    rng = np.random.default_rng(5 + aabb_scale)
+    images, grid, max_cascade = _scene(oracle, rng, 3, (40, 30), lens=lens, aabb_scale=aabb_scale)
+    n = 128 ** 3 * (max_cascade + 1)
+    start = rng.normal(0.0, 1.0, size=n).astype(np.float32)   # both signs: the "keep unless the flag flips" branch is exercised
+    meta, keep = _meta_on_device(oracle, images)
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for clear in (1, 0):
+        g = _dev(start)
+        ngp._lib.check(ngp.lib.ngpb_nerf_mark_untrained_density_grid(stream, n, _ptr(g), len(images), _ptr(meta), clear))
+        torch.cuda.synchronize()
+        want = oracle.nerf_mark_untrained(start, images, clear_visible_voxels=bool(clear))
+        got = g.cpu().numpy()
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (clear, int((got != want).sum()))
+        if clear:
+            frac = float((got == 0).mean())
+            assert 0.02 < frac < 0.98, frac   # three narrow cameras see part of the volume, not all of it
+
+
+@pytest.mark.parametrize("aabb_scale", [1, 4])
+def test_grid_samples_splat_and_ema_match_oracle(ngp, oracle, aabb_scale):
+    """generate_grid_samples_nerf_nonuniform (bit-exact positions and cell indices), then
+    splat_grid_samples_nerf_max_nearest_neighbor and ema_grid_samples_nerf on the same inputs."""
+    rng = np.random.default_rng(17 + aabb_scale)
+    _, grid, max_cascade = _scene(oracle, rng, 1, (8, 8), aabb_scale=aabb_scale)
+    grid[rng.integers(0, grid.size, size=5000)] = -1.0   # untrained cells stay untouched by the EMA
+    n_casc = max_cascade + 1
+    half = 0.5 * aabb_scale
+    aabb_min, aabb_max = [0.5 - half] * 3, [0.5 + half] * 3
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    state = oracle.Pcg32State(4242)
+    st = (ctypes.c_uint64 * 2)(int(state.arr[0]), int(state.arr[1]))
+    aabb = (ctypes.c_float * 6)(*(aabb_min + aabb_max))
+    g_dev = _dev(grid)
+    n = 100_003
+    for step, thresh in ((0, -0.01), (7, 0.01)):
+        pos = torch.zeros((n, 4), dtype=torch.float32, device="cuda")
+        idx = torch.zeros(n, dtype=torch.int32, device="cuda")
+        ngp._lib.check(ngp.lib.ngpb_nerf_generate_grid_samples(stream, n, st, step, aabb, _ptr(g_dev), _ptr(pos), _ptr(idx), n_casc, thresh))
+        torch.cuda.synchronize()
+        want_pos, want_idx = oracle.nerf_generate_grid_samples(n, state, step, aabb_min, aabb_max, grid, n_casc, thresh)
+        assert np.array_equal(idx.cpu().numpy().view(np.uint32), want_idx)
+        assert np.array_equal(pos.cpu().numpy().view(np.uint32), want_pos.view(np.uint32))
+        assert (want_pos[:, :3] >= 0).all() and (want_pos[:, :3] <= 1).all() and (want_pos[:, 3] == 0).all()
+        if thresh > 0:   # the hash retries up to 10 times for an occupied cell
+            assert (grid[want_idx] > thresh).mean() > 0.05
+    # splat: many samples per cell, the maximum wins; exact for None / ReLU, exp within the device's expf
+    raw = rng.normal(0.0, 2.0, size=n).astype(np.float16)
+    for act, exact in ((0, True), (1, True), (3, False)):
+        tmp = torch.zeros(grid.size, dtype=torch.float32, device="cuda")
+        if act == 0:
+            raw_used = np.abs(raw)   # the bit-pattern maximum is only an order for non-negative values
+        else:
+            raw_used = raw
+        ngp._lib.check(ngp.lib.ngpb_nerf_splat_grid_samples(stream, n, _ptr(idx), _ptr(_dev(raw_used)), _ptr(tmp), act))
+        torch.cuda.synchronize()
+        want_tmp = oracle.nerf_splat_grid_samples(want_idx, raw_used, np.zeros(grid.size, dtype=np.float32), act)
+        got_tmp = tmp.cpu().numpy()
+        if exact:
+            assert np.array_equal(got_tmp, want_tmp)
+        else:
+            np.testing.assert_allclose(got_tmp, want_tmp, rtol=2e-6, atol=0)
+        assert (got_tmp > 0).sum() > 1000
+        # EMA on the device's own splat
+        g2 = _dev(grid)
+        ngp._lib.check(ngp.lib.ngpb_nerf_ema_grid_samples(stream, grid.size, 0.95, _ptr(g2), _ptr(tmp)))
+        torch.cuda.synchronize()
+        want_g = oracle.nerf_ema_grid_samples(0.95, grid, got_tmp)
+        assert np.array_equal(g2.cpu().numpy().view(np.uint32), want_g.view(np.uint32))
+        assert (want_g[grid < 0] == -1.0).all()

@@ -159,3 +159,59 @@ def test_ld_random_val_is_a_scrambled_sobol_sequence(oracle):
     assert sorted(int(x * 256) for x in v) == list(range(256))
     v1 = [oracle.olib.oracle_ld_random_val(i, 999, 1) for i in range(64)]
     assert sorted(int(x * 64) for x in v1) == list(range(64))
+
+
+def _morton_xyz(oracle, idx):
+    return np.array([[oracle.olib.oracle_morton3d_invert(int(i) >> s) for s in (0, 1, 2)] for i in idx], dtype=np.int64)
+
+
+def test_occupancy_oracle_properties(oracle):
+    """The occupancy-maintenance restatements (mark_untrained, grid samples, splat, EMA) obey what
+    the reference code implies: samples lie inside the cell they index, only cells above the
+    threshold are chosen when one is found, cells behind every camera are marked -1, the splat is a
+    maximum and the EMA never revives an untrained cell."""
+    rng = np.random.default_rng(3)
+    # one camera at (0.5, -1.5, 0.5) looking along +y at the unit cube (NGP convention: columns right, down, forward, origin)
+    cam = np.array([[1, 0, 0, 0.5], [0, 0, 1, -1.5], [0, -1, 0, 0.5]], dtype=np.float32)
+    im = oracle.nerf_image(np.zeros((30, 40, 4), dtype=np.uint8), cam, focal=60.0)
+    n_casc = 2
+    marked = oracle.nerf_mark_untrained(np.zeros(n_casc * 128 ** 3, dtype=np.float32), [im])
+    assert set(np.unique(marked).tolist()) == {-1.0, 0.0}
+    xyz = _morton_xyz(oracle, np.arange(0, 128 ** 3, 4099))
+    centre = (xyz + 0.5) / 128.0
+    vis0 = marked[np.arange(0, 128 ** 3, 4099)] == 0
+    # cascade 0 = the unit cube, in front of the camera: a cell is visible iff it projects into the image
+    d = centre - np.array([0.5, -1.5, 0.5])
+    u, v = d[:, 0] / d[:, 1] * 60.0 / 40.0 + 0.5, -d[:, 2] / d[:, 1] * 60.0 / 30.0 + 0.5
+    clearly_in = (u > 0.05) & (u < 0.95) & (v > 0.05) & (v < 0.95)
+    clearly_out = (u < -0.05) | (u > 1.05) | (v < -0.05) | (v > 1.05)
+    assert vis0[clearly_in].all() and not vis0[clearly_out].any() and clearly_in.any() and clearly_out.any()
+    # cascade 1 spans [-0.5, 1.5]^3: its cells with y < -1.5 do not exist, but those behind the image plane direction do
+    cells1 = 128 ** 3 + np.arange(0, 128 ** 3, 4099)
+    c1 = (_morton_xyz(oracle, cells1 - 128 ** 3) + 0.5) / 128.0 * 2.0 - 0.5
+    d1 = c1 - np.array([0.5, -1.5, 0.5])
+    assert (d1[:, 1] > 0).all()   # everything in [-0.5, 1.5]^3 is in front of a camera at y = -1.5
+
+    grid = np.zeros(n_casc * 128 ** 3, dtype=np.float32)
+    grid[rng.integers(0, grid.size, size=grid.size // 3)] = 0.5
+    state = oracle.Pcg32State(11)
+    n = 20000
+    pos, idx = oracle.nerf_generate_grid_samples(n, state, 3, [-0.5] * 3, [1.5] * 3, grid, n_casc, 0.01)
+    level = idx // 128 ** 3
+    assert set(np.unique(level).tolist()) == {0, 1}
+    world = pos[:, :3] * 2.0 - 0.5                       # unwarp_position for aabb [-0.5, 1.5]^3
+    cell = np.floor(((world - 0.5) / (2.0 ** level)[:, None] + 0.5) * 128.0).astype(np.int64)
+    want = _morton_xyz(oracle, idx % 128 ** 3)
+    assert (np.abs(cell - want) <= 0).mean() > 0.999      # fp rounding may put a sample on a cell's upper face
+    assert (grid[idx] > 0.01).mean() > 0.95               # ten tries at p = 1/3 find an occupied cell 98 % of the time
+    raw = rng.normal(0, 1, size=n).astype(np.float16)
+    tmp = oracle.nerf_splat_grid_samples(idx, raw, np.zeros_like(grid), 3)
+    best = np.zeros_like(grid)
+    np.maximum.at(best, idx, np.exp(raw.astype(np.float32)) * np.float32(np.sqrt(3.0) / 1024.0))
+    np.testing.assert_allclose(tmp, best, rtol=1e-5)
+    g = grid.copy()
+    g[::7] = -1.0
+    out = oracle.nerf_ema_grid_samples(0.9, g, tmp)
+    assert (out[::7] == -1.0).all()
+    keep = g >= 0
+    np.testing.assert_array_equal(out[keep], np.maximum(g[keep] * np.float32(0.9), tmp[keep]))
