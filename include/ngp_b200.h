@@ -250,7 +250,8 @@ int ngpb_testbed_train_backward(ngpb_testbed_t* t, uint32_t batch_size);
  * then traces only the 256-pixel tiles t of [pixel_begin, pixel_end) with t % world == rank),
  * train_prefetch (default 1: ngpb_testbed_train marches the rays of the next step on a second stream
  * while the backward pass and the optimizer of this step run; same samples as the serial order),
- * prefetches_adopted (read-only: steps whose rays came from such a prefetch). */
+ * prefetches_adopted (read-only: steps whose rays came from such a prefetch), exposure, tonemap_curve,
+ * render_color_space (0 Linear, 1 SRGB: the space samples are averaged in), background_color_r/g/b/a. */
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value);
 int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value);
 /* Device buffers by name: params (fp16), params_fp32, params_inference (fp16), gradients (fp16),
@@ -266,6 +267,15 @@ int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_
  * [pixel_begin, pixel_end) (row-major) are traced: the unit of tile sharding across GPUs. */
 int ngpb_testbed_render_nerf(ngpb_testbed_t* t, uint32_t width, uint32_t height, const float* camera_3x4, float focal_x, float focal_y,
 	float principal_x, float principal_y, uint32_t spp_index, uint32_t pixel_begin, uint32_t pixel_end, float* rgba, float* depth);
+
+/* Testbed::render_to_cpu (src/python_api.cu:124-221) minus camera paths and motion blur, with the
+ * headless CudaRenderBuffer epilogue (src/render_buffer.cu:232-346, 533-565, 635-697): `spp` frames
+ * traced with sample indices 0..spp-1 are averaged, the background colour (properties
+ * background_color_r/g/b/a, given in sRGB) is blended behind the premultiplied result, then
+ * 2^exposure, the tonemap curve (property tonemap_curve: 0 Identity, 1 ACES, 2 Hable, 3 Reinhard) and
+ * the sRGB transfer unless `linear`. rgba: DEVICE float4 [h][w]. */
+int ngpb_testbed_render(ngpb_testbed_t* t, uint32_t width, uint32_t height, uint32_t spp, int linear, const float* camera_3x4, float focal_x, float focal_y,
+	float principal_x, float principal_y, float* rgba);
 
 /* Neural-image mode (ETestbedMode::Image; Testbed::load_image, train_image, render_image,
  * src/testbed_image.cu:212-340, 360-410): the image is RGBA Half (2) or Float (3), linear colours,

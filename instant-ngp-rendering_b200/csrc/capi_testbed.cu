@@ -114,7 +114,8 @@ int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size) {
 	X(snap_to_pixel_centers) X(near_distance) X(density_grid_decay) X(render_min_transmittance) X(loss_type) X(rgb_activation) \
 	X(density_activation) X(color_space) X(train_network) X(train_encoding) X(aabb_scale) \
 	X(render_target_queries) X(render_min_steps) X(render_max_steps) X(render_windows_per_sync) X(render_snap_to_pixel_centers) \
-	X(shard_rank) X(shard_world) X(render_shard_rank) X(render_shard_world) X(image_snap_to_pixel_centers) X(train_prefetch)
+	X(shard_rank) X(shard_world) X(render_shard_rank) X(render_shard_world) X(image_snap_to_pixel_centers) X(train_prefetch) \
+	X(exposure) X(tonemap_curve) X(render_color_space)
 
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
 	NGPB_API_BEGIN
@@ -128,6 +129,10 @@ int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
 	else if (n == "n_images") *value = tb.n_images();
 	else if (n == "last_render_samples") *value = (double)tb.last_render_samples;
 	else if (n == "prefetches_adopted") *value = (double)tb.prefetches_adopted;
+	else if (n == "background_color_r") *value = tb.background_color[0];
+	else if (n == "background_color_g") *value = tb.background_color[1];
+	else if (n == "background_color_b") *value = tb.background_color[2];
+	else if (n == "background_color_a") *value = tb.background_color[3];
 #define X(f) else if (n == #f) *value = (double)tb.f;
 	NGPB_PROPS(X)
 #undef X
@@ -138,7 +143,10 @@ int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value) {
 	NGPB_API_BEGIN
 	Testbed& tb = *t->impl;
 	const std::string n = name;
-	if (false) {}
+	if (n == "background_color_r") tb.background_color[0] = (float)value;
+	else if (n == "background_color_g") tb.background_color[1] = (float)value;
+	else if (n == "background_color_b") tb.background_color[2] = (float)value;
+	else if (n == "background_color_a") tb.background_color[3] = (float)value;
 #define X(f) else if (n == #f) tb.f = (decltype(tb.f))value;
 	NGPB_PROPS(X)
 #undef X
@@ -182,6 +190,15 @@ int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_
 	NGPB_API_BEGIN
 	t->impl->update_density_grid_nerf(decay, n_uniform, n_nonuniform);
 	NGPB_CUDA_CHECK(cudaStreamSynchronize(t->impl->stream()));
+	NGPB_API_END
+}
+
+int ngpb_testbed_render(ngpb_testbed_t* t, uint32_t width, uint32_t height, uint32_t spp, int linear, const float* camera_3x4, float focal_x, float focal_y,
+	float principal_x, float principal_y, float* rgba)
+{
+	NGPB_API_BEGIN
+	if (!camera_3x4 || !rgba) throw std::runtime_error{"ngpb_testbed_render: null argument"};
+	t->impl->render(width, height, spp, linear != 0, camera_3x4, focal_x, focal_y, principal_x, principal_y, rgba);
 	NGPB_API_END
 }
 

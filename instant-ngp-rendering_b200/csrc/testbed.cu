@@ -41,7 +41,7 @@ Testbed::~Testbed() {
 	m_images.clear();
 	for (DeviceBuffer* b : {&m_params_fp32, &m_params, &m_gradients, &m_metadata_gpu, &m_density_grid, &m_density_grid_tmp, &m_density_bitfield,
 			&m_density_mean, &m_grid_positions, &m_grid_indices, &m_grid_mlp_out, &m_counters, &m_ray_indices, &m_rays, &m_numsteps, &m_coords,
-			&m_rgbsigma, &m_coords_compacted, &m_dloss, &m_loss, &m_render_scratch,
+			&m_rgbsigma, &m_coords_compacted, &m_dloss, &m_loss, &m_render_scratch, &m_frame_buffer, &m_accumulate_buffer,
 			&m_image_data, &m_image_positions, &m_image_targets, &m_image_output, &m_image_dloss, &m_image_loss_values}) b->release();
 	m_network.reset();
 	m_image_network.reset();

@@ -150,6 +150,14 @@ public:
 	// t % render_shard_world == render_shard_rank are traced (the others stay untouched).
 	uint32_t render_shard_rank = 0, render_shard_world = 1;
 	bool render_snap_to_pixel_centers = false; // Testbed::m_snap_to_pixel_centers (testbed.h:995)
+	// ---- headless render buffer (CudaRenderBuffer accumulate + tonemap, render_buffer.cu): `spp`
+	// traced frames averaged, background blended in, exposure, tonemap curve, sRGB unless `linear`.
+	// What pyngp's Testbed.render(width, height, spp, linear) returns, in a DEVICE float4 [h][w].
+	void render(uint32_t width, uint32_t height, uint32_t spp, bool linear, const float* camera_3x4, float focal_x, float focal_y,
+		float principal_x, float principal_y, float* rgba_out);
+	float exposure = 0.0f;              // Testbed::m_exposure (testbed.h:735)
+	int tonemap_curve = 0;              // ETonemapCurve: Identity, ACES, Hable, Reinhard (common.h:112-117)
+	int render_color_space = kColorLinear; // CudaRenderBuffer::m_color_space: the space frames are averaged in
 	// Optional DEVICE buffer [height * width] receiving the number of samples composited per pixel.
 	void set_render_steps_out(uint32_t* p) { m_render_steps_out = p; }
 
@@ -212,7 +220,7 @@ private:
 
 	// per-step scratch
 	DeviceBuffer m_counters, m_ray_indices, m_rays, m_numsteps, m_coords, m_rgbsigma, m_coords_compacted, m_dloss, m_loss;
-	DeviceBuffer m_render_scratch;
+	DeviceBuffer m_render_scratch, m_frame_buffer, m_accumulate_buffer;
 	NerfStepCounters* m_counters_host = nullptr; // pinned
 	float* m_loss_host = nullptr;                // pinned
 	void* m_counters_host_render = nullptr;      // pinned

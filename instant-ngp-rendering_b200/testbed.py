@@ -14,7 +14,7 @@ import re
 import numpy as np
 import torch
 
-from ._lib import lib, check
+from ._lib import lib, check, NgpbError
 
 IMAGE_BYTE, IMAGE_HALF, IMAGE_FLOAT = 1, 2, 3
 LENS_PERSPECTIVE, LENS_OPENCV = 0, 1
@@ -305,6 +305,59 @@ class Testbed:
         return (rgba, depth, steps) if return_steps else (rgba, depth)
 
     last_render_samples = property(lambda self: int(self._get("last_render_samples")))
+
+    # -- pyngp's camera and render() (src/python_api.cu:124-221, 416-425, 481-566) ---------------
+    def set_nerf_camera_matrix(self, camera_to_world):
+        """Testbed::set_nerf_camera_matrix (src/testbed.cu:420-422): NeRF-convention 3x4 -> the view camera."""
+        self._camera = nerf_matrix_to_ngp(camera_to_world)
+
+    def set_ngp_camera_matrix(self, camera_3x4):
+        self._camera = np.ascontiguousarray(np.array(camera_3x4, dtype=np.float32)[:3, :4])
+
+    @property
+    def fov(self):
+        """Field of view in degrees along fov_axis (Testbed::fov / set_fov, src/testbed.cu:3526-3536)."""
+        return float(np.degrees(2.0 * np.arctan(0.5 / self._relative_focal_length)))
+
+    @fov.setter
+    def fov(self, degrees):
+        self._relative_focal_length = 0.5 / np.tan(0.5 * np.radians(float(degrees)))
+
+    @property
+    def background_color(self):
+        return [self._get("background_color_" + c) for c in "rgba"]
+
+    @background_color.setter
+    def background_color(self, rgba):
+        for c, v in zip("rgba", rgba):
+            self._set("background_color_" + c, v)
+
+    exposure = property(lambda self: self._get("exposure"), lambda self, v: self._set("exposure", v))
+    tonemap_curve = property(lambda self: int(self._get("tonemap_curve")), lambda self, v: self._set("tonemap_curve", int(v)))
+
+    def render(self, width=1920, height=1080, spp=1, linear=True):
+        """pyngp's Testbed.render: float32 [h][w][4] on the host - `spp` samples per pixel averaged, the
+        background blended in, exposure, tonemap curve, sRGB transfer unless `linear`. The view is the
+        one set by set_nerf_camera_matrix / fov / screen_center (focal length = relative focal length
+        x resolution[fov_axis], Testbed::calc_focal_length)."""
+        if getattr(self, "_camera", None) is None:
+            raise NgpbError("render: set the view with set_nerf_camera_matrix first")
+        focal = float(getattr(self, "_relative_focal_length", 1.0)) * (height if self.fov_axis == 1 else width)
+        cx, cy = self.screen_center
+        rgba = torch.empty((height, width, 4), dtype=torch.float32, device=self._device)
+        cam = np.ascontiguousarray(self._camera, dtype=np.float32)
+        self._set("render_shard_rank", 0)
+        self._set("render_shard_world", 1)
+        torch.cuda.current_stream().synchronize()
+        check(lib.ngpb_testbed_render(self._h, width, height, spp, int(bool(linear)), cam.ctypes.data_as(ctypes.POINTER(ctypes.c_float)),
+                                      focal, focal, cx, cy, ctypes.c_void_p(rgba.data_ptr())))
+        self.device_buffer("counters", torch.int32)   # orders the read below behind the testbed's stream
+        return rgba.cpu().numpy()
+
+    fov_axis = 1
+    screen_center = (0.5, 0.5)
+    _relative_focal_length = 1.0
+    _camera = None
 
 
 def profile_enable(on=True):

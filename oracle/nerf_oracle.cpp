@@ -610,6 +610,58 @@ extern "C" void oracle_nerf_ema_grid_samples(uint32_t n_elements, float decay, f
 	}
 }
 
+// ---- render-buffer epilogue (src/render_buffer.cu:232-346 accumulate_kernel + tonemap, :533-565 tonemap_kernel)
+// frames: spp x n x 4 linear premultiplied RGBA; out: n x 4. color_space / output_color_space: 0 Linear, 1 SRGB;
+// curve: 0 Identity, 1 ACES, 2 Hable, 3 Reinhard; background in sRGB.
+extern "C" void oracle_render_buffer_epilogue(uint32_t n, uint32_t spp, const float* frames, float exposure, const float* background, int color_space,
+	int output_color_space, int curve, float* out)
+{
+	for (uint32_t i = 0; i < n; ++i) {
+		float acc[4] = {0, 0, 0, 0};
+		for (uint32_t s = 0; s < spp; ++s) {
+			const float* f = frames + ((size_t)s * n + i) * 4;
+			float c[3] = {f[0], f[1], f[2]};
+			if (color_space == 1) for (int k = 0; k < 3; ++k) c[k] = linear_to_srgb(c[k]);
+			const float cnt = (float)s;
+			for (int k = 0; k < 3; ++k) acc[k] = (acc[k] * cnt + c[k]) / (cnt + 1);
+			acc[3] = (acc[3] * cnt + f[3]) / (cnt + 1);
+		}
+		float bg[3] = {background[0], background[1], background[2]};
+		if (color_space != 1) for (int k = 0; k < 3; ++k) bg[k] = srgb_to_linear(bg[k]);
+		const float weight = (1 - acc[3]) * background[3];
+		float col[3];
+		for (int k = 0; k < 3; ++k) col[k] = acc[k] + bg[k] * weight;
+		const float alpha = acc[3] + weight;
+		if (color_space == 1) for (int k = 0; k < 3; ++k) col[k] = srgb_to_linear(col[k]);
+		const float gain = powf(2.0f, exposure);
+		for (int k = 0; k < 3; ++k) col[k] *= gain;
+		if (curve != 0) {
+			for (int k = 0; k < 3; ++k) col[k] = fmaxf(col[k], 0.0f);
+			if (curve == 3) {
+				const float Y = 0.2126f * col[0] + 0.7152f * col[1] + 0.0722f * col[2];
+				for (int k = 0; k < 3; ++k) col[k] = col[k] * (1.f / (Y + 1.0f));
+			} else {
+				float k0, k1, k2, k3, k4, k5;
+				if (curve == 1) {
+					k0 = 0.6f * 0.6f * 2.51f; k1 = 0.6f * 0.03f; k2 = 0.0f; k3 = 0.6f * 0.6f * 2.43f; k4 = 0.6f * 0.59f; k5 = 0.14f;
+				} else {
+					const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+					k0 = A * F - A * E; k1 = C * B * F - B * E; k2 = 0.0f; k3 = A * F; k4 = B * F; k5 = D * F * F;
+					const float W = 11.2f;
+					const float white_scale = (k3 * (W * W) + k4 * W + k5) / (k0 * (W * W) + k1 * W + k2);
+					k0 = 4.0f * k0 * white_scale; k1 = 2.0f * k1 * white_scale; k2 = k2 * white_scale; k3 = 4.0f * k3; k4 = 2.0f * k4;
+				}
+				for (int k = 0; k < 3; ++k) {
+					const float sq = col[k] * col[k];
+					col[k] = (sq * k0 + k1 * col[k] + k2) / (k3 * sq + k4 * col[k] + k5);
+				}
+			}
+		}
+		if (output_color_space == 1) for (int k = 0; k < 3; ++k) col[k] = linear_to_srgb(col[k]);
+		out[(size_t)i * 4 + 0] = col[0]; out[(size_t)i * 4 + 1] = col[1]; out[(size_t)i * 4 + 2] = col[2]; out[(size_t)i * 4 + 3] = alpha;
+	}
+}
+
 extern "C" float oracle_det_logf(float x) { return c_logf(x); }
 extern "C" float oracle_det_expf(float x) { return c_expf(x); }
 extern "C" float oracle_advance_n_steps(float t, float cone_angle, float n) { return advance_n_steps(t, cone_angle, n); }

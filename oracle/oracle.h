@@ -121,6 +121,9 @@ void oracle_nerf_generate_grid_samples(uint32_t n, const uint64_t* rng_state, ui
 	float* positions, uint32_t* indices, uint32_t n_cascades, float thresh);
 void oracle_nerf_splat_grid_samples(uint32_t n, const uint32_t* indices, const uint16_t* density_raw, float* grid_tmp, int density_activation);
 void oracle_nerf_ema_grid_samples(uint32_t n_elements, float decay, float* grid, const float* grid_tmp);
+/* CudaRenderBuffer accumulate + tonemap (src/render_buffer.cu:232-346, 533-565): frames [spp][n][4] -> out [n][4]. */
+void oracle_render_buffer_epilogue(uint32_t n, uint32_t spp, const float* frames, float exposure, const float* background, int color_space,
+	int output_color_space, int curve, float* out);
 /* deterministic log / exp used by the stepping (Cephes single precision) */
 float oracle_det_logf(float x);
 float oracle_det_expf(float x);

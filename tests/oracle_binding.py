@@ -377,6 +377,17 @@ def nerf_ema_grid_samples(decay, grid, grid_tmp):
     return g
 
 
+def render_buffer_epilogue(frames, exposure=0.0, background=(0.0, 0.0, 0.0, 1.0), color_space=0, output_color_space=0, curve=0):
+    """frames float32 [spp][n][4] -> [n][4] (accumulate_kernel + tonemap_kernel)."""
+    f = np.ascontiguousarray(frames, dtype=np.float32)
+    spp, n = f.shape[0], f.shape[1]
+    bg = np.array(background, dtype=np.float32)
+    out = np.zeros((n, 4), dtype=np.float32)
+    olib.oracle_render_buffer_epilogue(ctypes.c_uint32(n), ctypes.c_uint32(spp), _p(f, ctypes.c_float), ctypes.c_float(exposure), _p(bg, ctypes.c_float),
+                                       ctypes.c_int(color_space), ctypes.c_int(output_color_space), ctypes.c_int(curve), _p(out, ctypes.c_float))
+    return out
+
+
 # ---- NeRF rendering (oracle_nerf_render_*) --------------------------------------------------------
 class RenderConfig(ctypes.Structure):
     """oracle_render_config."""

@@ -140,3 +140,39 @@ def test_render_independent_of_windows_and_sharding(ngp, trained):
     # empty range: nothing happens
     none, _ = tb.render_nerf(w, h, poses[3], focal, pixel_range=(5, 5))
     assert (none == 0).all()
+
+
+def test_render_buffer_epilogue_matches_oracle(ngp, oracle, trained):
+    """Testbed.render (pyngp's render(width, height, spp, linear)): the traced frames of sample
+    indices 0..spp-1 go through the oracle's accumulate + tonemap restatement; the device result
+    must agree to float rounding (powf of the sRGB transfer: 2e-6)."""
+    tb, poses, focal = trained[1]
+    w, h = 64, 48
+    tb.set_ngp_camera_matrix(poses[2])
+    tb._relative_focal_length = focal * (h / 72) / h
+    frames = []
+    for s in range(3):
+        rgba, _ = tb.render_nerf(w, h, poses[2], focal * h / 72, spp_index=s)
+        frames.append(rgba.cpu().numpy().reshape(-1, 4))
+    frames = np.stack(frames)
+    assert not np.array_equal(frames[0], frames[1]), "different sample indices jitter the pixel positions"
+    try:
+        for spp, linear, curve, exposure, bg, space in ((1, True, 0, 0.0, (0, 0, 0, 1), 0), (3, False, 0, 0.0, (0, 0, 0, 1), 0), (2, False, 1, 0.7, (0.2, 0.4, 0.9, 1.0), 0),
+                                                        (3, True, 2, -0.5, (1.0, 1.0, 1.0, 0.5), 1), (2, False, 3, 1.0, (0.3, 0.3, 0.3, 0.0), 0)):
+            tb.tonemap_curve, tb.exposure, tb.background_color = curve, exposure, bg
+            tb._set("render_color_space", space)
+            got = tb.render(w, h, spp=spp, linear=linear).reshape(-1, 4)
+            want = oracle.render_buffer_epilogue(frames[:spp], exposure, bg, space, 0 if linear else 1, curve)
+            np.testing.assert_allclose(got, want, rtol=2e-5, atol=2e-6, err_msg=str((spp, linear, curve)))
+            assert got[:, :3].max() > 0.05
+            if bg[3] == 1.0:
+                np.testing.assert_allclose(got[:, 3], 1.0, atol=1e-6)   # an opaque background fills the alpha
+        tb.tonemap_curve = 7
+        with pytest.raises(ngp.NgpbError):
+            tb.render(w, h)
+    finally:
+        tb.tonemap_curve, tb.exposure, tb.background_color = 0, 0.0, (0.0, 0.0, 0.0, 1.0)
+        tb._set("render_color_space", 0)
+    # fov <-> focal length (Testbed::set_fov): 90 degrees along y <=> focal = h / 2
+    tb.fov = 90.0
+    assert abs(tb._relative_focal_length - 0.5) < 1e-6 and abs(tb.fov - 90.0) < 1e-4
