@@ -306,6 +306,28 @@ class Testbed:
 
     last_render_samples = property(lambda self: int(self._get("last_render_samples")))
 
+    # -- dataset files (Testbed::load_training_data, src/testbed.cu; load_nerf, src/nerf_loader.cu:273-740)
+    def load_training_data(self, path, max_images=None):
+        """transforms.json (or a directory holding some) -> images, cameras and lens models on the
+        device, as pyngp's load_training_data does for NeRF scenes. Returns the dataset record of
+        loader.describe_dataset (scale, offset, up, render_aabb, frames ...)."""
+        from . import loader
+        ds = loader.describe_dataset(path)
+        frames = ds["frames"][:max_images] if max_images else ds["frames"]
+        self.create_empty_nerf_dataset(len(frames), aabb_scale=ds["aabb_scale"], is_hdr=ds["is_hdr"])
+        for i, fr in enumerate(frames):
+            px = loader.load_frame_pixels(fr, ds)
+            h, w = px.shape[:2]
+            fx, fy = loader.finish_frame(fr, w, h)
+            self.nerf.training.set_image(i, px)
+            cx, cy = fr["principal"]
+            k1, k2, p1, p2 = fr["lens_params"][:4] if fr["lens_mode"] == 1 else (0.0, 0.0, 0.0, 0.0)
+            self.nerf.training.set_camera_intrinsics(i, fx=fx, fy=fy, cx=cx * w, cy=cy * h, k1=k1, k2=k2, p1=p1, p2=p2)
+            self.nerf.training.set_camera_extrinsics(i, fr["xform"], convert_to_ngp=False)
+        self.dataset = ds
+        self.up_dir = ds["up"]
+        return ds
+
     # -- pyngp's camera and render() (src/python_api.cu:124-221, 416-425, 481-566) ---------------
     def set_nerf_camera_matrix(self, camera_to_world):
         """Testbed::set_nerf_camera_matrix (src/testbed.cu:420-422): NeRF-convention 3x4 -> the view camera."""
