@@ -262,6 +262,17 @@ int ngpb_testbed_device_ptr(ngpb_testbed_t* t, const char* name, void** ptr, siz
 size_t ngpb_testbed_network_config(const ngpb_testbed_t* t, char* buf, size_t cap);
 /* update_density_grid_nerf(decay, n_uniform, n_nonuniform), src/testbed_nerf.cu:2271-2360. */
 int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_uniform, uint32_t n_nonuniform);
+/* Snapshot restore, the device side of Testbed::load_snapshot (src/testbed.cu:4841-4955) after the host
+ * has read the msgpack container: Trainer::set_params / set_params_full_precision (tcnn trainer.h:242-269)
+ * from HOST memory (fp16 "__half" or fp32 "float" params_binary, n_params must match the network);
+ * density_grid_binary (fp16, HOST; 128^3 x cascades cells, or 0 cells for a model that never trained)
+ * -> float grid + update_density_grid_mean_and_bitfield; training_step and loss (:4931-4932).
+ * Optimizer state travels through ngpb_testbed_device_ptr ("optimizer_first_moments",
+ * "optimizer_second_moments", "optimizer_param_steps") and the properties "optimizer_step",
+ * "optimizer_base_learning_rate", "optimizer_learning_rate_factor". */
+int ngpb_testbed_set_params(ngpb_testbed_t* t, const void* host_params, int full_precision, size_t n_params);
+int ngpb_testbed_set_density_grid_fp16(ngpb_testbed_t* t, const void* host_grid, size_t n_cells);
+int ngpb_testbed_restore_training_state(ngpb_testbed_t* t, uint32_t training_step, float loss);
 /* Testbed::render_nerf (src/testbed_nerf.cu:1827-1987) into caller-owned DEVICE buffers: rgba
  * float4 [h][w] (linear, premultiplied alpha), depth float [h][w] or NULL. Only pixels
  * [pixel_begin, pixel_end) (row-major) are traced: the unit of tile sharding across GPUs. */

@@ -107,6 +107,9 @@ SIGNATURES = {
     "ngpb_testbed_train_end": (c_int, [c_vp, c_u32]),
     "ngpb_testbed_render": (c_int, [c_vp, c_u32, c_u32, c_u32, c_int, ctypes.POINTER(c_f32), c_f32, c_f32, c_f32, c_f32, c_vp]),
     "ngpb_testbed_train_forward": (c_int, [c_vp, c_u32]),
+    "ngpb_testbed_set_params": (c_int, [c_vp, c_vp, c_int, c_sz]),
+    "ngpb_testbed_set_density_grid_fp16": (c_int, [c_vp, c_vp, c_sz]),
+    "ngpb_testbed_restore_training_state": (c_int, [c_vp, c_u32, c_f32]),
     "ngpb_testbed_train_backward": (c_int, [c_vp, c_u32]),
     "ngpb_testbed_set_render_steps_out": (c_int, [c_vp, c_vp]),
     "ngpb_testbed_render_nerf": (c_int, [c_vp, c_u32, c_u32, ctypes.POINTER(c_f32), c_f32, c_f32, c_f32, c_f32, c_u32, c_u32, c_u32, c_vp, c_vp]),

@@ -129,6 +129,9 @@ int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
 	else if (n == "n_images") *value = tb.n_images();
 	else if (n == "last_render_samples") *value = (double)tb.last_render_samples;
 	else if (n == "prefetches_adopted") *value = (double)tb.prefetches_adopted;
+	else if (n == "optimizer_step") *value = const_cast<Testbed&>(tb).optimizer() ? const_cast<Testbed&>(tb).optimizer()->step_count() : 0;
+	else if (n == "optimizer_learning_rate_factor") *value = const_cast<Testbed&>(tb).optimizer() ? const_cast<Testbed&>(tb).optimizer()->learning_rate_factor() : 1.0;
+	else if (n == "optimizer_base_learning_rate") *value = const_cast<Testbed&>(tb).optimizer() ? const_cast<Testbed&>(tb).optimizer()->base_learning_rate() : 0.0;
 	else if (n == "background_color_r") *value = tb.background_color[0];
 	else if (n == "background_color_g") *value = tb.background_color[1];
 	else if (n == "background_color_b") *value = tb.background_color[2];
@@ -143,7 +146,15 @@ int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value) {
 	NGPB_API_BEGIN
 	Testbed& tb = *t->impl;
 	const std::string n = name;
-	if (n == "background_color_r") tb.background_color[0] = (float)value;
+	if (n == "optimizer_step" || n == "optimizer_learning_rate_factor" || n == "optimizer_base_learning_rate") {
+		// Adam's current_step; ExponentialDecay's learning_rate_factor and learning_rate (tcnn adam.h:288-299, exponential_decay.h:144-148)
+		Optimizer* o = tb.optimizer();
+		if (!o) throw std::runtime_error{"ngpb_testbed_set: no optimizer (reload_network_from_json first)"};
+		if (n == "optimizer_step") o->set_step_count((uint32_t)value, o->learning_rate_factor());
+		else if (n == "optimizer_learning_rate_factor") o->set_step_count(o->step_count(), (float)value);
+		else o->set_base_learning_rate((float)value);
+	}
+	else if (n == "background_color_r") tb.background_color[0] = (float)value;
 	else if (n == "background_color_g") tb.background_color[1] = (float)value;
 	else if (n == "background_color_b") tb.background_color[2] = (float)value;
 	else if (n == "background_color_a") tb.background_color[3] = (float)value;
@@ -167,6 +178,9 @@ int ngpb_testbed_device_ptr(ngpb_testbed_t* t, const char* name, void** ptr, siz
 	else if (n == "params_fp32") { p = tb.params_fp32(); b = tb.n_params() * 4; }
 	else if (n == "params_inference") { p = tb.params_inference(); b = tb.n_params() * 2; }
 	else if (n == "gradients") { p = tb.gradients(); b = tb.n_params() * 2; }
+	else if (n == "optimizer_first_moments" && tb.optimizer()) { p = tb.optimizer()->first_moments(); b = tb.n_params() * 4; }
+	else if (n == "optimizer_second_moments" && tb.optimizer()) { p = tb.optimizer()->second_moments(); b = tb.n_params() * 4; }
+	else if (n == "optimizer_param_steps" && tb.optimizer()) { p = tb.optimizer()->param_steps(); b = tb.n_params() * 4; }
 	else if (n == "density_grid") { p = tb.density_grid(); b = n_grid * 4; }
 	else if (n == "density_grid_bitfield") { p = tb.density_grid_bitfield(); b = nerf_bitfield_bytes(); }
 	else if (n == "density_grid_mean") { p = tb.density_grid_mean(); b = 4; }
@@ -190,6 +204,22 @@ int ngpb_testbed_update_density_grid(ngpb_testbed_t* t, float decay, uint32_t n_
 	NGPB_API_BEGIN
 	t->impl->update_density_grid_nerf(decay, n_uniform, n_nonuniform);
 	NGPB_CUDA_CHECK(cudaStreamSynchronize(t->impl->stream()));
+	NGPB_API_END
+}
+
+int ngpb_testbed_set_params(ngpb_testbed_t* t, const void* host_params, int full_precision, size_t n_params) {
+	NGPB_API_BEGIN
+	t->impl->set_params(host_params, full_precision != 0, n_params);
+	NGPB_API_END
+}
+int ngpb_testbed_set_density_grid_fp16(ngpb_testbed_t* t, const void* host_grid, size_t n_cells) {
+	NGPB_API_BEGIN
+	t->impl->set_density_grid_fp16(host_grid, n_cells);
+	NGPB_API_END
+}
+int ngpb_testbed_restore_training_state(ngpb_testbed_t* t, uint32_t training_step, float loss) {
+	NGPB_API_BEGIN
+	t->impl->restore_training_state(training_step, loss);
 	NGPB_API_END
 }
 

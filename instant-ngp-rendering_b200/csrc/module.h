@@ -96,6 +96,7 @@ std::string prof_collect(bool reset);
 
 // params_fp16[i] = (half)params_fp32[i] (tcnn trainer.h:82-85)
 void cast_fp32_to_fp16(cudaStream_t stream, size_t n, const float* src, __half* dst);
+void cast_fp16_to_fp32(cudaStream_t stream, size_t n, const __half* src, float* dst);
 
 // Factories (tcnn/src/encoding.cu:132, tcnn/src/network.cu:98, tcnn/src/cpp_api.cu:140-165).
 Module* create_encoding_module(uint32_t n_input_dims, const Json& encoding);

@@ -38,6 +38,8 @@ public:
 	uint32_t* param_steps() const { return m_param_steps; }
 	void set_step_count(uint32_t s, float lr_factor) { m_current_step = s; m_learning_rate_factor = lr_factor; }
 	float learning_rate_factor() const { return m_learning_rate_factor; }
+	float base_learning_rate() const { return m_base_learning_rate; }
+	void set_base_learning_rate(float v) { m_base_learning_rate = v; }
 
 private:
 	void parse(const Json& config, bool construct);

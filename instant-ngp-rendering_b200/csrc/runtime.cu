@@ -116,4 +116,15 @@ void cast_fp32_to_fp16(cudaStream_t stream, size_t n, const float* src, __half* 
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }
 
+
+__global__ void cast_fp16_to_fp32_kernel(size_t n, const __half* __restrict__ src, float* __restrict__ dst) {
+	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) dst[i] = __half2float(src[i]);
+}
+void cast_fp16_to_fp32(cudaStream_t stream, size_t n, const __half* src, float* dst) {
+	if (!n) return;
+	cast_fp16_to_fp32_kernel<<<(uint32_t)((n + 255) / 256), 256, 0, stream>>>(n, src, dst);
+	NGPB_CUDA_CHECK(cudaGetLastError());
+}
+
 } // namespace ngpb

