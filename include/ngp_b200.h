@@ -288,6 +288,20 @@ int ngpb_testbed_render_nerf(ngpb_testbed_t* t, uint32_t width, uint32_t height,
 int ngpb_testbed_render(ngpb_testbed_t* t, uint32_t width, uint32_t height, uint32_t spp, int linear, const float* camera_3x4, float focal_x, float focal_y,
 	float principal_x, float principal_y, float* rgba);
 
+/* The ground-truth frame pyngp's render() returns while render_ground_truth is set
+ * (Testbed::render_frame_epilogue, src/testbed.cu:4592-4608 -> CudaRenderBuffer::overlay_image,
+ * src/render_buffer.cu:348-411, 700-733): the training image of `view` resampled (nearest texel) to
+ * width x height along fov_axis (0 = x, 1 = y) at `zoom`, background / exposure / tonemap curve /
+ * transfer as in ngpb_testbed_render, blended with weight `alpha` over rgba (DEVICE float4 [h][w],
+ * read and written; with alpha = 1 its old content does not matter, as in the reference, which
+ * skips the trace, src/testbed.cu:4383). */
+/* Testbed::m_nerf.render_lens (set by set_camera_to_training_view, src/testbed.cu:477-478): lens the
+ * render camera's rays are undistorted with while property render_with_lens_distortion is non-zero.
+ * lens_mode 0 Perspective, 1 OpenCV (k1, k2, p1, p2 in lens_params[0..3]; 7 floats or NULL). */
+int ngpb_testbed_set_render_lens(ngpb_testbed_t* t, int lens_mode, const float* lens_params);
+
+int ngpb_testbed_overlay_ground_truth(ngpb_testbed_t* t, uint32_t width, uint32_t height, int linear, uint32_t view, int fov_axis, float zoom, float alpha, float* rgba);
+
 /* Neural-image mode (ETestbedMode::Image; Testbed::load_image, train_image, render_image,
  * src/testbed_image.cu:212-340, 360-410): the image is RGBA Half (2) or Float (3), linear colours,
  * host or device pointer. After this call reload_network_from_json builds the 2-D

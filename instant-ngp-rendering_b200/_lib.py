@@ -105,6 +105,8 @@ SIGNATURES = {
     "ngpb_testbed_render_image": (c_int, [c_vp, c_u32, c_u32, c_vp]),
     "ngpb_testbed_train_begin": (c_int, [c_vp, c_u32]),
     "ngpb_testbed_train_end": (c_int, [c_vp, c_u32]),
+    "ngpb_testbed_set_render_lens": (c_int, [c_vp, c_int, ctypes.POINTER(c_f32)]),
+    "ngpb_testbed_overlay_ground_truth": (c_int, [c_vp, c_u32, c_u32, c_int, c_u32, c_int, c_f32, c_f32, c_vp]),
     "ngpb_testbed_render": (c_int, [c_vp, c_u32, c_u32, c_u32, c_int, ctypes.POINTER(c_f32), c_f32, c_f32, c_f32, c_f32, c_vp]),
     "ngpb_testbed_train_forward": (c_int, [c_vp, c_u32]),
     "ngpb_testbed_set_params": (c_int, [c_vp, c_vp, c_int, c_sz]),

@@ -115,7 +115,7 @@ int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size) {
 	X(density_activation) X(color_space) X(train_network) X(train_encoding) X(aabb_scale) \
 	X(render_target_queries) X(render_min_steps) X(render_max_steps) X(render_windows_per_sync) X(render_snap_to_pixel_centers) \
 	X(shard_rank) X(shard_world) X(render_shard_rank) X(render_shard_world) X(image_snap_to_pixel_centers) X(train_prefetch) \
-	X(exposure) X(tonemap_curve) X(render_color_space)
+	X(exposure) X(tonemap_curve) X(render_color_space) X(render_with_lens_distortion)
 
 int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
 	NGPB_API_BEGIN
@@ -153,6 +153,10 @@ int ngpb_testbed_set(ngpb_testbed_t* t, const char* name, double value) {
 		if (n == "optimizer_step") o->set_step_count((uint32_t)value, o->learning_rate_factor());
 		else if (n == "optimizer_learning_rate_factor") o->set_step_count(o->step_count(), (float)value);
 		else o->set_base_learning_rate((float)value);
+	}
+	else if (n == "cone_angle_constant") {
+		if (!(value >= 0.0)) throw std::runtime_error{"ngpb_testbed_set: cone_angle_constant must be >= 0"};
+		tb.set_cone_angle_constant((float)value);
 	}
 	else if (n == "background_color_r") tb.background_color[0] = (float)value;
 	else if (n == "background_color_g") tb.background_color[1] = (float)value;
@@ -229,6 +233,18 @@ int ngpb_testbed_render(ngpb_testbed_t* t, uint32_t width, uint32_t height, uint
 	NGPB_API_BEGIN
 	if (!camera_3x4 || !rgba) throw std::runtime_error{"ngpb_testbed_render: null argument"};
 	t->impl->render(width, height, spp, linear != 0, camera_3x4, focal_x, focal_y, principal_x, principal_y, rgba);
+	NGPB_API_END
+}
+
+int ngpb_testbed_set_render_lens(ngpb_testbed_t* t, int lens_mode, const float* lens_params) {
+	NGPB_API_BEGIN
+	t->impl->set_render_lens(lens_mode, lens_params);
+	NGPB_API_END
+}
+
+int ngpb_testbed_overlay_ground_truth(ngpb_testbed_t* t, uint32_t width, uint32_t height, int linear, uint32_t view, int fov_axis, float zoom, float alpha, float* rgba) {
+	NGPB_API_BEGIN
+	t->impl->overlay_ground_truth(width, height, linear != 0, view, fov_axis, zoom, alpha, rgba);
 	NGPB_API_END
 }
 

@@ -44,6 +44,8 @@ struct RenderParams {
 	uint32_t target_queries, min_steps, max_steps;
 	float min_transmittance;
 	int rgb_activation, density_activation, linear_colors, snap_to_pixel_centers;
+	int lens_mode;            // Testbed::m_nerf.render_lens (testbed.h), used when render_with_lens_distortion
+	float lens_params[7];
 };
 
 constexpr uint32_t kRenderTile = 256;
@@ -73,7 +75,7 @@ __global__ void __launch_bounds__(kRayBlock) render_init_rays_kernel(const __gri
 		float ox, oy;
 		ld_random_pixel_offset(p.snap_to_pixel_centers ? 0u : p.spp_index, ox, oy);
 		const float u = ((float)x + ox) / (float)p.width, v = ((float)y + oy) / (float)p.height;
-		const Ray3 ray = uv_to_ray(u, v, (int)p.width, (int)p.height, p.focal_x, p.focal_y, p.camera, p.screen_cx, p.screen_cy, kLensPerspective, nullptr, 0.0f);
+		const Ray3 ray = uv_to_ray(u, v, (int)p.width, (int)p.height, p.focal_x, p.focal_y, p.camera, p.screen_cx, p.screen_cy, p.lens_mode, p.lens_params, 0.0f);
 		o = ray.o;
 		d = normalize(ray.d);
 		float tmin, tmax;
@@ -252,6 +254,8 @@ void Testbed::render_nerf(uint32_t width, uint32_t height, const float* camera_3
 	p.width = width; p.height = height;
 	p.focal_x = focal_x; p.focal_y = focal_y; p.screen_cx = principal_x; p.screen_cy = principal_y;
 	p.spp_index = spp_index;
+	p.lens_mode = render_with_lens_distortion ? render_lens_mode : kLensPerspective;
+	for (int i = 0; i < 7; ++i) p.lens_params[i] = render_lens_params[i];
 	p.pixel_begin = pixel_begin; p.pixel_end = pixel_end;
 	p.max_mip = m_max_cascade;
 	p.n_local = n_rays;

@@ -73,6 +73,67 @@ __global__ void tonemap_kernel(uint32_t n, float exposure, float4 background, co
 	out[i] = make_float4(col.x, col.y, col.z, alpha);
 }
 
+// overlay_image_kernel (src/render_buffer.cu:348-411): the training image of a view resampled
+// (nearest texel) onto the output grid along fov_axis, background, exposure, curve and transfer as in
+// tonemap_kernel, blended over what the buffer holds. With alpha = 1 this IS the frame pyngp returns
+// when render_ground_truth is set (Testbed::render_frame_epilogue, src/testbed.cu:4592-4608; the trace
+// itself is skipped, :4383).
+__global__ void overlay_image_kernel(uint32_t width, uint32_t height, float alpha, float exposure, float4 background, const void* __restrict__ image,
+	int image_data_type, int image_res_x, int image_res_y, int curve, int color_space, int output_color_space, int fov_axis, float zoom,
+	float screen_center_x, float screen_center_y, float4* __restrict__ out)
+{
+	const uint32_t x = threadIdx.x + blockDim.x * blockIdx.x, y = threadIdx.y + blockDim.y * blockIdx.y;
+	if (x >= width || y >= height) return;
+	const float scale = (float)(fov_axis == 0 ? image_res_x : image_res_y) / (float)(fov_axis == 0 ? width : height);
+	float fx = x + 0.5f, fy = y + 0.5f;
+	fx -= width * 0.5f; fx /= zoom; fx += screen_center_x * width;
+	fy -= height * 0.5f; fy /= zoom; fy += screen_center_y * height;
+	const float u = (fx - width * 0.5f) * scale + image_res_x * 0.5f;
+	const float v = (fy - height * 0.5f) * scale + image_res_y * 0.5f;
+	const int srcx = (int)floorf(u), srcy = (int)floorf(v);
+	Rgba val{0.0f, 0.0f, 0.0f, 0.0f};
+	if (srcx < image_res_x && srcy < image_res_y && srcx >= 0 && srcy >= 0) val = read_rgba(srcx, srcy, image_res_x, image, image_data_type);
+	V3 col = {val.r, val.g, val.b};
+	float a = val.a;
+	V3 bg = {background.x, background.y, background.z};
+	if (color_space != kColorSRGB) {
+		bg = srgb_to_linear(bg);
+	} else {
+		col = a > 0 ? linear_to_srgb(col / a) * a : v3(0.0f);
+	}
+	const float weight = (1 - a) * background.w;
+	col = col + bg * weight;
+	a += weight;
+	if (color_space == kColorSRGB) col = srgb_to_linear(col);
+	col = col * powf(2.0f, exposure);
+	col = tonemap_curve(col, curve);
+	if (output_color_space == kColorSRGB) col = linear_to_srgb(col);
+	const float4 prev = alpha < 1.f ? out[(size_t)y * width + x] : make_float4(0.f, 0.f, 0.f, 0.f); // uninitialised memory may hold NaNs
+	out[(size_t)y * width + x] = make_float4(col.x * alpha + prev.x * (1.f - alpha), col.y * alpha + prev.y * (1.f - alpha),
+		col.z * alpha + prev.z * (1.f - alpha), a * alpha + prev.w * (1.f - alpha));
+}
+
+void Testbed::set_render_lens(int lens_mode, const float* params) {
+	if (lens_mode != kLensPerspective && lens_mode != kLensOpenCV) throw std::runtime_error{"ngp-b200: lens mode must be Perspective or OpenCV"};
+	render_lens_mode = lens_mode;
+	for (int i = 0; i < 7; ++i) render_lens_params[i] = params ? params[i] : 0.0f;
+}
+
+void Testbed::overlay_ground_truth(uint32_t width, uint32_t height, bool linear, uint32_t view, int fov_axis, float zoom, float alpha, float* rgba_inout) {
+	if (m_mode != kModeNerf) throw std::runtime_error{"ngp-b200: the ground-truth overlay is implemented for the NeRF mode"};
+	if (view >= m_images.size()) throw std::runtime_error{"ngp-b200: ground-truth view index out of range"};
+	if (width == 0 || height == 0 || !rgba_inout) throw std::runtime_error{"ngp-b200: overlay_ground_truth needs a positive resolution and a buffer"};
+	if (fov_axis != 0 && fov_axis != 1) throw std::runtime_error{"ngp-b200: fov_axis must be 0 or 1"};
+	if (tonemap_curve < kTonemapIdentity || tonemap_curve > kTonemapReinhard) throw std::runtime_error{"Invalid tonemap curve."};
+	const ImageMeta& m = m_images[view].meta;
+	if (!m.pixels) throw std::runtime_error{"ngp-b200: the view has no image"};
+	const float4 bg = make_float4(background_color[0], background_color[1], background_color[2], background_color[3]);
+	const dim3 threads = {16, 8, 1}, blocks = {div_round_up(width, threads.x), div_round_up(height, threads.y), 1};
+	overlay_image_kernel<<<blocks, threads, 0, m_stream>>>(width, height, alpha, exposure, bg, m.pixels, m.image_data_type, m.res_x, m.res_y, tonemap_curve,
+		render_color_space, linear ? kColorLinear : kColorSRGB, fov_axis, zoom, 0.5f, 0.5f, reinterpret_cast<float4*>(rgba_inout));
+	NGPB_CUDA_CHECK(cudaGetLastError());
+}
+
 // render_to_cpu without the camera-path / motion-blur options: `spp` traced frames with sample
 // indices 0..spp-1 averaged, then the epilogue. rgba_out: DEVICE float4 [h][w].
 void Testbed::render(uint32_t width, uint32_t height, uint32_t spp, bool linear, const float* camera_3x4, float focal_x, float focal_y,

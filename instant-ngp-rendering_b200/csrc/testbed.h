@@ -96,6 +96,8 @@ public:
 	const Aabb& aabb() const { return m_aabb; }
 	uint32_t max_cascade() const { return m_max_cascade; }
 	float cone_angle_constant() const { return m_cone_angle_constant; }
+	// Testbed::m_nerf.cone_angle_constant (python_api.cu:640): 0 = uniform steps, as scripts/run.py --nerf_compatibility sets
+	void set_cone_angle_constant(float v) { m_cone_angle_constant = v; ++m_epoch; }
 	const ImageMeta* metadata_gpu() const { return m_metadata_gpu.as<ImageMeta>(); }
 	uint32_t n_images() const { return (uint32_t)m_images.size(); }
 	cudaStream_t stream() const { return m_stream; }
@@ -157,12 +159,21 @@ public:
 	// Tile sharding: with render_shard_world > 1 only the 256-pixel tiles t of the pixel range with
 	// t % render_shard_world == render_shard_rank are traced (the others stay untouched).
 	uint32_t render_shard_rank = 0, render_shard_world = 1;
+	// Testbed::m_nerf.render_with_lens_distortion / render_lens (testbed.h; set_camera_to_training_view, src/testbed.cu:477-478):
+	// the lens the render camera's rays are undistorted with (Perspective or OpenCV).
+	bool render_with_lens_distortion = false;
+	int render_lens_mode = kLensPerspective;
+	float render_lens_params[7] = {};
+	void set_render_lens(int lens_mode, const float* params);
 	bool render_snap_to_pixel_centers = false; // Testbed::m_snap_to_pixel_centers (testbed.h:995)
 	// ---- headless render buffer (CudaRenderBuffer accumulate + tonemap, render_buffer.cu): `spp`
 	// traced frames averaged, background blended in, exposure, tonemap curve, sRGB unless `linear`.
 	// What pyngp's Testbed.render(width, height, spp, linear) returns, in a DEVICE float4 [h][w].
 	void render(uint32_t width, uint32_t height, uint32_t spp, bool linear, const float* camera_3x4, float focal_x, float focal_y,
 		float principal_x, float principal_y, float* rgba_out);
+	// Ground-truth overlay (CudaRenderBuffer::overlay_image, render_buffer.cu:348-411, 700-733): the
+	// training image of `view` blended with weight `alpha` over the DEVICE float4 [h][w] buffer.
+	void overlay_ground_truth(uint32_t width, uint32_t height, bool linear, uint32_t view, int fov_axis, float zoom, float alpha, float* rgba_inout);
 	float exposure = 0.0f;              // Testbed::m_exposure (testbed.h:735)
 	int tonemap_curve = 0;              // ETonemapCurve: Identity, ACES, Hable, Reinhard (common.h:112-117)
 	int render_color_space = kColorLinear; // CudaRenderBuffer::m_color_space: the space frames are averaged in

@@ -275,3 +275,36 @@ def load_frame_pixels(frame, dataset):
     if dataset.get("black_transparent", False):
         img[(img[:, :, :3] == 0).all(axis=-1), 3] = 0
     return img
+
+
+def load_image_file(path):
+    """The image of the neural-image mode as Testbed::load_image makes it (src/testbed_image.cu:362-428):
+    *.exr -> float32 RGBA as stored; *.bin -> int32 height, int32 width, then float16 RGBA texels;
+    anything else -> 8-bit RGBA through from_rgba32 (src/common_host.cu:268-298): sRGB -> linear,
+    colours multiplied by alpha. Returns [h][w][4] float32 or float16."""
+    if not os.path.exists(path):
+        raise ValueError("Image file '%s' does not exist." % path)
+    ext = os.path.splitext(path)[1].lower()
+    if ext == ".bin":
+        with open(path, "rb") as f:
+            h, w = np.frombuffer(f.read(8), dtype=np.int32)
+            px = np.frombuffer(f.read(int(h) * int(w) * 8), dtype=np.float16)
+        if px.size != int(h) * int(w) * 4:
+            raise ValueError("Binary image '%s' is truncated." % path)
+        return np.ascontiguousarray(px.reshape(int(h), int(w), 4))
+    if ext == ".exr":
+        os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+        import cv2
+        img = cv2.imread(path, cv2.IMREAD_UNCHANGED)
+        if img is None:
+            raise ValueError("Could not load image file '%s'." % path)
+        img = img.astype(np.float32)
+        if img.ndim == 2:
+            img = np.stack([img] * 3, axis=-1)
+        a = img[:, :, 3:4] if img.shape[2] == 4 else np.ones(img.shape[:2] + (1,), dtype=np.float32)
+        return np.ascontiguousarray(np.concatenate([img[:, :, 2::-1], a], axis=-1))
+    img = _imread_rgba8(path).astype(np.float32) * np.float32(1.0 / 255.0)
+    if img.shape[0] == 0 or img.shape[1] == 0:
+        raise ValueError("Image has zero pixels.")
+    a = img[:, :, 3:4]
+    return np.ascontiguousarray(np.concatenate([_srgb_to_linear(img[:, :, :3]) * a, a], axis=-1).astype(np.float32))

@@ -18,6 +18,7 @@ from ._lib import lib, check, NgpbError
 
 IMAGE_BYTE, IMAGE_HALF, IMAGE_FLOAT = 1, 2, 3
 LENS_PERSPECTIVE, LENS_OPENCV = 0, 1
+MODE_NERF, MODE_SDF, MODE_IMAGE, MODE_VOLUME, MODE_GEOMETRY, MODE_NONE = 0, 1, 2, 3, 4, 5   # ETestbedMode (common.h:132-139)
 LOSS_TYPES = {"L2": 0, "L1": 1, "Mape": 2, "Smape": 3, "Huber": 4, "LogL1": 5, "RelativeL2": 6}
 ACTIVATIONS = {"None": 0, "ReLU": 1, "Logistic": 2, "Exponential": 3}
 
@@ -64,11 +65,56 @@ def load_network_config(path):
     return cfg
 
 
+class _ImageMetadata:
+    """One entry of testbed.nerf.training.dataset.metadata (TrainingImageMetadata, python_api.cu:578-590)."""
+
+    def __init__(self, tb, idx):
+        w, h = tb._resolutions[idx]
+        fx, fy, cx, cy, k1, k2, p1, p2 = tb._intrinsics.get(idx, (0.0, 0.0, -0.5, -0.5, 0.0, 0.0, 0.0, 0.0))
+        self.resolution = [w, h]
+        self.focal_length = [fx, fy if fy > 0 else fx]
+        self.principal_point = [cx / w if cx >= 0 else 0.5, cy / h if cy >= 0 else 0.5]
+        self.lens_params = [k1, k2, p1, p2]
+        self.lens_mode = LENS_OPENCV if any(v != 0.0 for v in self.lens_params) else LENS_PERSPECTIVE
+
+
+class _Dataset:
+    """testbed.nerf.training.dataset (NerfDataset, python_api.cu:592-612): what scripts/run.py reads."""
+
+    def __init__(self, tb):
+        self._tb = tb
+
+    @property
+    def n_images(self):
+        return int(self._tb._get("n_images"))
+
+    @property
+    def metadata(self):
+        return [_ImageMetadata(self._tb, i) for i in range(self.n_images)]
+
+    @property
+    def aabb_scale(self):
+        return int(self._tb._get("aabb_scale"))
+
+    def _record(self, key, default):
+        ds = getattr(self._tb, "dataset", None)
+        return ds[key] if ds is not None and key in ds else default
+
+    scale = property(lambda self: self._record("scale", NERF_SCALE))
+    offset = property(lambda self: self._record("offset", list(NERF_OFFSET)))
+    is_hdr = property(lambda self: bool(self._record("is_hdr", False)))
+    paths = property(lambda self: [fr.get("path", "") for fr in self._record("frames", [])])
+
+
 class _Training:
     """testbed.nerf.training (src/python_api.cu:645-697)."""
 
     def __init__(self, tb):
         self._tb = tb
+        self._dataset = _Dataset(tb)
+
+    dataset = property(lambda self: self._dataset)
+    n_images_for_training = property(lambda self: self._dataset.n_images)
 
     def set_image(self, frame_idx, img, depth_img=None, depth_scale=1.0):
         self._tb.set_nerf_image(frame_idx, img)
@@ -82,7 +128,7 @@ class _Training:
         self._tb._push_camera(frame_idx)
 
     def __getattr__(self, name):
-        if name in ("random_bg_color", "linear_colors", "snap_to_pixel_centers", "near_distance", "density_grid_decay"):
+        if name in ("random_bg_color", "linear_colors", "snap_to_pixel_centers", "near_distance", "density_grid_decay", "loss_type", "train_network", "train_encoding"):
             return self._tb._get(name)
         raise AttributeError(name)
 
@@ -106,6 +152,26 @@ class _Nerf:
     def render_min_transmittance(self, v):
         self._tb._set("render_min_transmittance", float(v))
 
+    # python_api.cu:622-643
+    cone_angle_constant = property(lambda self: self._tb._get("cone_angle_constant"), lambda self, v: self._tb._set("cone_angle_constant", float(v)))
+    render_with_lens_distortion = property(lambda self: bool(self._tb._get("render_with_lens_distortion")),
+                                           lambda self, v: self._tb._set("render_with_lens_distortion", float(bool(v))))
+    rgb_activation = property(lambda self: int(self._tb._get("rgb_activation")), lambda self, v: self._tb._set("rgb_activation", int(v)))
+    density_activation = property(lambda self: int(self._tb._get("density_activation")), lambda self, v: self._tb._set("density_activation", int(v)))
+
+    @property
+    def sharpen(self):
+        return self._sharpen
+
+    @sharpen.setter
+    def sharpen(self, v):
+        """Dataset sharpening at load time (nerf_loader.cu:762-770). Only 0 (off, the default) is built."""
+        if float(v) != 0.0:
+            raise NgpbError("ngp-b200: nerf.sharpen != 0 is not implemented (out of the path, DESIGN.md section 7)")
+        self._sharpen = 0.0
+
+    _sharpen = 0.0
+
 
 class Testbed:
     def __init__(self, device="cuda"):
@@ -118,6 +184,12 @@ class Testbed:
         self._resolutions = {}
         self.shall_train = True
         self.nerf = _Nerf(self)
+        self.mode = MODE_NONE
+        self.root_dir = ""
+        self.training_batch_size = 1 << 18   # Testbed::m_training_batch_size (testbed.h)
+        self.render_ground_truth = False
+        self.ground_truth_alpha = 1.0
+        self.zoom = 1.0
 
     # -- plumbing --------------------------------------------------------------------------------
     def _get(self, name):
@@ -161,6 +233,8 @@ class Testbed:
     # -- dataset ---------------------------------------------------------------------------------
     def create_empty_nerf_dataset(self, n_images, aabb_scale=1, is_hdr=False):
         check(lib.ngpb_testbed_create_empty_nerf_dataset(self._h, n_images, int(aabb_scale), int(is_hdr)))
+        self.mode = MODE_NERF
+        self._extrinsics, self._intrinsics, self._resolutions = {}, {}, {}
 
     def set_nerf_image(self, idx, img):
         """img: [h][w][4] uint8 (sRGB, straight alpha), float16 or float32 (linear, premultiplied);
@@ -265,8 +339,40 @@ class Testbed:
     def frame(self):
         """Headless Testbed::frame: one training step when shall_train (src/testbed.cu:3380-3479)."""
         if self.shall_train:
-            self.train(1 << 18)
+            self.train(self.training_batch_size)
         return True
+
+    def want_repl(self):
+        return False
+
+    def init_window(self, width, height, hidden=False, second_window=False):
+        raise NgpbError("init_window: no GUI in ngp-b200 (GLFW / OpenGL are unavailable on this box); train() / frame() / render() run headless")
+
+    def init_vr(self):
+        raise NgpbError("init_vr: no VR in ngp-b200 (unavailable on this box)")
+
+    def load_file(self, path):
+        """Testbed::load_file (src/testbed.cu:318-391): snapshot, network config, or training data by what the file is."""
+        path = str(path)
+        ext = os.path.splitext(path)[1].lower()
+        if not os.path.exists(path):
+            if ext == ".json":
+                for cand in (path, os.path.join(self.root_dir, "configs", {MODE_NERF: "nerf", MODE_IMAGE: "image"}.get(self.mode, "nerf"), os.path.basename(path))):
+                    if os.path.exists(cand):
+                        return self.reload_network_from_file(cand)
+            raise NgpbError(f"File '{path}' does not exist.")
+        if ext in (".ingp", ".msgpack"):
+            return self.load_snapshot(path)
+        if ext == ".json":
+            with open(path) as f:
+                doc = json.loads(_strip_json_comments(f.read()))
+            if "snapshot" in doc:
+                raise NgpbError("ngp-b200: snapshots in JSON form are not supported; use .ingp / .msgpack")
+            if "path" in doc and "frames" not in doc:
+                raise NgpbError("ngp-b200: camera paths are not part of the path (DESIGN.md section 7)")
+            if "parent" in doc or "network" in doc or "encoding" in doc or "loss" in doc or "optimizer" in doc:
+                return self.reload_network_from_file(path)
+        return self.load_training_data(path)
 
     training_step = property(lambda self: int(self._get("training_step")))
     loss = property(lambda self: self._get("loss"))
@@ -310,8 +416,21 @@ class Testbed:
     def load_training_data(self, path, max_images=None):
         """transforms.json (or a directory holding some) -> images, cameras and lens models on the
         device, as pyngp's load_training_data does for NeRF scenes. Returns the dataset record of
-        loader.describe_dataset (scale, offset, up, render_aabb, frames ...)."""
+        loader.describe_dataset (scale, offset, up, render_aabb, frames ...). An image file selects
+        the neural-image mode (mode_from_scene, src/testbed.cu:180-200); meshes and volumes are not
+        part of the path."""
         from . import loader
+        path = str(path)
+        ext = os.path.splitext(path)[1].lower()
+        if ext in (".obj", ".stl", ".nvdb"):
+            raise NgpbError("ngp-b200: SDF and volume modes are out of scope (DESIGN.md section 7)")
+        if os.path.isfile(path) and ext not in (".json", ""):
+            img = loader.load_image_file(path)
+            self.set_image(img)
+            self.mode = MODE_IMAGE
+            return None
+        if self.mode == MODE_IMAGE:
+            raise NgpbError("ngp-b200: this testbed is in image mode; create a new Testbed for a NeRF scene")
         ds = loader.describe_dataset(path)
         frames = ds["frames"][:max_images] if max_images else ds["frames"]
         self.create_empty_nerf_dataset(len(frames), aabb_scale=ds["aabb_scale"], is_hdr=ds["is_hdr"])
@@ -326,7 +445,50 @@ class Testbed:
             self.nerf.training.set_camera_extrinsics(i, fr["xform"], convert_to_ngp=False)
         self.dataset = ds
         self.up_dir = ds["up"]
+        self.mode = MODE_NERF
         return ds
+
+    def set_camera_to_training_view(self, trainview):
+        """Testbed::set_camera_to_training_view (src/testbed.cu:472-487): camera, focal length, lens and
+        screen centre of a training view; it also becomes the view render_ground_truth shows."""
+        trainview = int(trainview)
+        if trainview not in self._extrinsics or trainview not in self._resolutions:
+            raise NgpbError("Invalid frame index")
+        md = _ImageMetadata(self, trainview)
+        self._camera = np.ascontiguousarray(self._extrinsics[trainview], dtype=np.float32)
+        self._relative_focal_length = np.array(md.focal_length, dtype=np.float64) / float(md.resolution[self.fov_axis])
+        self.nerf.render_with_lens_distortion = True
+        lens = (ctypes.c_float * 7)(*md.lens_params, 0, 0, 0)
+        check(lib.ngpb_testbed_set_render_lens(self._h, md.lens_mode, lens))
+        self.screen_center = (1.0 - md.principal_point[0], 1.0 - md.principal_point[1])
+        self.training_view = trainview
+
+    training_view = 0
+    snap_to_pixel_centers = property(lambda self: bool(self._get("render_snap_to_pixel_centers")), lambda self, v: self._set("render_snap_to_pixel_centers", float(bool(v))))
+
+    @property
+    def color_space(self):
+        return int(self._get("render_color_space"))
+
+    @color_space.setter
+    def color_space(self, v):
+        """Testbed::m_color_space: the space colours are trained and accumulated in (python_api.cu:503)."""
+        self._set("color_space", int(v))
+        self._set("render_color_space", int(v))
+
+    def reset(self, reset_density_grid=True):
+        self.reset_network(reset_density_grid)
+
+    def n_encoding_params(self):
+        return int(self.n_params) - sum(int(np.prod(sh)) for sh in getattr(self, "_mlp_shapes", []))
+
+    def compute_and_save_marching_cubes_mesh(self, *a, **k):
+        raise NgpbError("ngp-b200: marching-cubes mesh extraction is out of scope (DESIGN.md section 7)")
+
+    compute_marching_cubes_mesh = compute_and_save_marching_cubes_mesh
+
+    def load_camera_path(self, path):
+        raise NgpbError("ngp-b200: camera paths are out of scope (DESIGN.md section 7)")
 
     # -- snapshots (pyngp save_snapshot / load_snapshot, src/python_api.cu:432-434; src/testbed.cu:4775-4972)
     def save_snapshot(self, path, include_optimizer_state=False, compress=True):
@@ -351,7 +513,8 @@ class Testbed:
     @property
     def fov(self):
         """Field of view in degrees along fov_axis (Testbed::fov / set_fov, src/testbed.cu:3526-3536)."""
-        return float(np.degrees(2.0 * np.arctan(0.5 / self._relative_focal_length)))
+        rel = float(np.broadcast_to(np.asarray(self._relative_focal_length, dtype=np.float64), (2,))[self.fov_axis])
+        return float(np.degrees(2.0 * np.arctan(0.5 / rel)))
 
     @fov.setter
     def fov(self, degrees):
@@ -369,22 +532,32 @@ class Testbed:
     exposure = property(lambda self: self._get("exposure"), lambda self, v: self._set("exposure", v))
     tonemap_curve = property(lambda self: int(self._get("tonemap_curve")), lambda self, v: self._set("tonemap_curve", int(v)))
 
-    def render(self, width=1920, height=1080, spp=1, linear=True):
+    def render(self, width=1920, height=1080, spp=1, linear=True, start_t=-1.0, end_t=-1.0, fps=30.0, shutter_fraction=1.0):
         """pyngp's Testbed.render: float32 [h][w][4] on the host - `spp` samples per pixel averaged, the
         background blended in, exposure, tonemap curve, sRGB transfer unless `linear`. The view is the
         one set by set_nerf_camera_matrix / fov / screen_center (focal length = relative focal length
         x resolution[fov_axis], Testbed::calc_focal_length)."""
-        if getattr(self, "_camera", None) is None:
-            raise NgpbError("render: set the view with set_nerf_camera_matrix first")
-        focal = float(getattr(self, "_relative_focal_length", 1.0)) * (height if self.fov_axis == 1 else width)
-        cx, cy = self.screen_center
-        rgba = torch.empty((height, width, 4), dtype=torch.float32, device=self._device)
-        cam = np.ascontiguousarray(self._camera, dtype=np.float32)
-        self._set("render_shard_rank", 0)
-        self._set("render_shard_world", 1)
+        if start_t >= 0.0 or end_t >= 0.0:
+            raise NgpbError("render: camera-path rendering (start_t / end_t) is out of scope (DESIGN.md section 7)")
+        width, height, spp = int(width), int(height), int(spp)
+        rgba = torch.zeros((height, width, 4), dtype=torch.float32, device=self._device)
         torch.cuda.current_stream().synchronize()
-        check(lib.ngpb_testbed_render(self._h, width, height, spp, int(bool(linear)), cam.ctypes.data_as(ctypes.POINTER(ctypes.c_float)),
-                                      focal, focal, cx, cy, ctypes.c_void_p(rgba.data_ptr())))
+        gt = bool(self.render_ground_truth) and self.mode != MODE_IMAGE
+        if not gt or self.ground_truth_alpha < 1.0:   # the reference skips the trace under an opaque overlay (src/testbed.cu:4383)
+            if getattr(self, "_camera", None) is None:
+                raise NgpbError("render: set the view with set_nerf_camera_matrix first")
+            # calc_focal_length and render_screen_center (src/testbed.cu:4111-4118)
+            rel = np.broadcast_to(np.asarray(self._relative_focal_length, dtype=np.float64), (2,))
+            fx, fy = (rel * (height if self.fov_axis == 1 else width) * self.zoom).tolist()
+            cx, cy = ((0.5 - np.asarray(self.screen_center, dtype=np.float64)) * self.zoom + 0.5).tolist()
+            cam = np.ascontiguousarray(self._camera, dtype=np.float32)
+            self._set("render_shard_rank", 0)
+            self._set("render_shard_world", 1)
+            check(lib.ngpb_testbed_render(self._h, width, height, spp, int(bool(linear)), cam.ctypes.data_as(ctypes.POINTER(ctypes.c_float)),
+                                          fx, fy, cx, cy, ctypes.c_void_p(rgba.data_ptr())))
+        if gt:
+            check(lib.ngpb_testbed_overlay_ground_truth(self._h, width, height, int(bool(linear)), int(self.training_view), int(self.fov_axis),
+                                                        float(self.zoom), float(self.ground_truth_alpha), ctypes.c_void_p(rgba.data_ptr())))
         self.device_buffer("counters", torch.int32)   # orders the read below behind the testbed's stream
         return rgba.cpu().numpy()
 

@@ -739,7 +739,8 @@ extern "C" uint64_t oracle_nerf_render_march(const oracle_render_config* cfg, co
 			const uint32_t pix = cfg->pixel_begin + r;
 			const uint32_t x = pix % cfg->width, y = pix / cfg->width;
 			const float u = ((float)x + ox) / (float)cfg->width, v = ((float)y + oy) / (float)cfg->height;
-			const V dd = {(u - cfg->screen_cx) * (float)cfg->width / cfg->focal_x, (v - cfg->screen_cy) * (float)cfg->height / cfg->focal_y, 1.0f};
+			V dd = {(u - cfg->screen_cx) * (float)cfg->width / cfg->focal_x, (v - cfg->screen_cy) * (float)cfg->height / cfg->focal_y, 1.0f};
+			if (cfg->lens_mode == 1) iterative_opencv_lens_undistortion(cfg->lens_params, &dd.x, &dd.y);
 			const V o = cam[3];
 			const V d = normalize(cam[0] * dd.x + cam[1] * dd.y + cam[2] * dd.z);
 			float tmin, tmax;

@@ -144,6 +144,8 @@ typedef struct {
 	float cone_angle_constant, min_transmittance;
 	int rgb_activation, density_activation, linear_colors, snap_to_pixel_centers;
 	uint32_t max_steps_per_ray;
+	int lens_mode;               /* render lens: 0 Perspective, 1 OpenCV (src/testbed.cu:477-478) */
+	float lens_params[7];
 } oracle_render_config;
 /* init_rays_with_payload_kernel_nerf + advance_pos_nerf + generate_next_nerf_network_inputs: ALL
  * samples of every pixel in [pixel_begin, pixel_end) until the ray leaves the box (or

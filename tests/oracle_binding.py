@@ -388,6 +388,36 @@ def render_buffer_epilogue(frames, exposure=0.0, background=(0.0, 0.0, 0.0, 1.0)
     return out
 
 
+def overlay_image(image_rgba8, width, height, fov_axis=1, zoom=1.0, exposure=0.0, background=(0.0, 0.0, 0.0, 1.0), color_space=0, output_color_space=0, curve=0):
+    """numpy restatement of overlay_image_kernel with alpha = 1 (src/render_buffer.cu:348-411) for a
+    Byte image (read_rgba, common_device.cuh:773-790): nearest texel along fov_axis, sRGB8 -> linear
+    premultiplied, background, exposure, curve, transfer (the last three through the oracle's
+    tonemap restatement). image_rgba8 uint8 [ih][iw][4] -> float32 [height*width][4]."""
+    img = np.asarray(image_rgba8, dtype=np.uint8)
+    ih, iw = img.shape[:2]
+    f32 = np.float32
+    scale = f32((iw, ih)[fov_axis]) / f32((width, height)[fov_axis])
+    x = np.arange(width, dtype=np.float32) + f32(0.5)
+    y = np.arange(height, dtype=np.float32) + f32(0.5)
+    fx = (x - f32(width) * f32(0.5)) / f32(zoom) + f32(0.5) * f32(width)
+    fy = (y - f32(height) * f32(0.5)) / f32(zoom) + f32(0.5) * f32(height)
+    u = (fx - f32(width) * f32(0.5)) * scale + f32(iw) * f32(0.5)
+    v = (fy - f32(height) * f32(0.5)) * scale + f32(ih) * f32(0.5)
+    sx, sy = np.floor(u).astype(np.int64), np.floor(v).astype(np.int64)
+    inside = ((sy >= 0) & (sy < ih))[:, None] & ((sx >= 0) & (sx < iw))[None, :]
+    tex = img[np.clip(sy, 0, ih - 1)[:, None], np.clip(sx, 0, iw - 1)[None, :]].astype(np.float32) * f32(1.0 / 255.0)
+    s = tex[..., :3]
+    lin = np.where(s <= f32(0.04045), s / f32(12.92), ((s + f32(0.055)) / f32(1.055)) ** f32(2.4)).astype(np.float32)
+    a = tex[..., 3:4]
+    marker = (img[..., 0] == 0xFF) & (img[..., 1] == 0) & (img[..., 2] == 0xFF) & (img[..., 3] == 0)
+    val = np.concatenate([lin * a, a], axis=-1)
+    val[marker[np.clip(sy, 0, ih - 1)[:, None], np.clip(sx, 0, iw - 1)[None, :]]] = -1.0
+    val[~inside] = 0.0
+    assert color_space == 0, "restated for the linear accumulation space (the default; scripts/run.py's protocol)"
+    # background, exposure, curve and transfer are those of tonemap_kernel: one frame, spp = 1
+    return render_buffer_epilogue(val.reshape(1, -1, 4), exposure, background, color_space, output_color_space, curve)
+
+
 # ---- NeRF rendering (oracle_nerf_render_*) --------------------------------------------------------
 class RenderConfig(ctypes.Structure):
     """oracle_render_config."""
@@ -397,7 +427,7 @@ class RenderConfig(ctypes.Structure):
                 ("spp_index", ctypes.c_uint32), ("pixel_begin", ctypes.c_uint32), ("pixel_end", ctypes.c_uint32), ("max_mip", ctypes.c_uint32),
                 ("cone_angle_constant", ctypes.c_float), ("min_transmittance", ctypes.c_float),
                 ("rgb_activation", ctypes.c_int), ("density_activation", ctypes.c_int), ("linear_colors", ctypes.c_int), ("snap_to_pixel_centers", ctypes.c_int),
-                ("max_steps_per_ray", ctypes.c_uint32)]
+                ("max_steps_per_ray", ctypes.c_uint32), ("lens_mode", ctypes.c_int), ("lens_params", ctypes.c_float * 7)]
 
 
 olib.oracle_nerf_render_march.restype = ctypes.c_uint64
@@ -406,8 +436,12 @@ olib.oracle_ld_random_val.argtypes = [ctypes.c_uint32] * 3
 
 
 def render_config(aabb_min, aabb_max, camera_3x4, width, height, focal, max_mip, cone_angle_constant, principal=(0.5, 0.5), spp_index=0,
-                  pixel_range=None, min_transmittance=0.01, rgb_activation=2, density_activation=3, linear_colors=False, snap=False, max_steps_per_ray=10000):
+                  pixel_range=None, min_transmittance=0.01, rgb_activation=2, density_activation=3, linear_colors=False, snap=False, max_steps_per_ray=10000, lens=None):
     c = RenderConfig()
+    if lens is not None:   # OpenCV k1, k2, p1, p2
+        c.lens_mode = 1
+        for k, val in enumerate(lens):
+            c.lens_params[k] = float(val)
     for k in range(3):
         c.aabb_min[k], c.aabb_max[k] = float(aabb_min[k]), float(aabb_max[k])
     x = np.asarray(camera_3x4, dtype=np.float32)
