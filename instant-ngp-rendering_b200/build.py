@@ -82,9 +82,25 @@ def build_oracle(verbose=False):
     return ORACLE_LIB
 
 
+def build_ref(verbose=False):
+    """oracle/_ref/libref_host.so: the reference's own header functions compiled for the host
+    (oracle/ref_host.cu, oracle/build_ref.sh). Only where /root/reference exists; a checker, like the oracle."""
+    ref = os.environ.get("NGP_REFERENCE", "/root/reference")
+    out = os.path.join(ORACLE_DIR, "_ref", "libref_host.so")
+    src = os.path.join(ORACLE_DIR, "ref_host.cu")
+    if not os.path.isdir(os.path.join(ref, "include", "neural-graphics-primitives")):
+        return out if os.path.exists(out) else None
+    if _newer(out, [src, os.path.join(ORACLE_DIR, "build_ref.sh")]):
+        _run(["bash", os.path.join(ORACLE_DIR, "build_ref.sh")])
+        if verbose:
+            print(f"[build] built {out}")
+    return out
+
+
 def build_all(verbose=False):
     build_cuda(verbose)
     build_oracle(verbose)
+    build_ref(verbose)
 
 
 if __name__ == "__main__":

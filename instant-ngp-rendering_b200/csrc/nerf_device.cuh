@@ -450,8 +450,10 @@ NGPB_HD void iterative_opencv_lens_undistortion(const float* params, float* u, f
 		const float rx = x + dx0 - x0, ry = y + dx1 - y0;
 		// inverse(J) * r with the adjugate / determinant (tcnn vec.h inverse(mat2))
 		const float det = j00 * j11 - j10 * j01;
-		const float sx = (j11 * rx - j10 * ry) / det;
-		const float sy = (-j01 * rx + j00 * ry) / det;
+		// inverse(J) * r as tcnn computes it (vec.h:802-807, 861-863, 587-597): the adjugate divided
+		// by the determinant element by element, then column 0 * r.x + column 1 * r.y
+		const float sx = (j11 / det) * rx + ((-j10) / det) * ry;
+		const float sy = ((-j01) / det) * rx + (j00 / det) * ry;
 		x -= sx;
 		y -= sy;
 		if (sx * sx + sy * sy < kMaxStepNorm) break;

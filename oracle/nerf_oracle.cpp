@@ -21,6 +21,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <string>
 #include <vector>
 
 typedef _Float16 half_t;
@@ -255,8 +256,10 @@ void iterative_opencv_lens_undistortion(const float* params, float* u, float* v)
 		const float j11 = 1 + (f11 - b11) / (2 * step1);
 		const float rx = x + dx0 - x0, ry = y + dx1 - y0;
 		const float det = j00 * j11 - j10 * j01;
-		const float sx = (j11 * rx - j10 * ry) / det;
-		const float sy = (-j01 * rx + j00 * ry) / det;
+		// inverse(J) * r as tcnn computes it (vec.h:802-807, 861-863, 587-597): the adjugate divided
+		// by the determinant element by element, then column 0 * r.x + column 1 * r.y
+		const float sx = (j11 / det) * rx + ((-j10) / det) * ry;
+		const float sy = ((-j01) / det) * rx + (j00 / det) * ry;
 		x -= sx;
 		y -= sy;
 		if (sx * sx + sy * sy < kMaxStepNorm) break;
@@ -818,4 +821,73 @@ extern "C" void oracle_nerf_render_composite(const oracle_render_config* cfg, co
 		for (int k = 0; k < 4; ++k) rgba_out[4 * r + k] = out[k];
 		depth_out[r] = dout;
 	}
+}
+
+// ================================== function-grain probes ========================================
+// The oracle's answer to oracle/ref_host.cu's ref_probe: same names, same rows of 32-bit words in
+// and out (floats by bit pattern). tests/test_ref_pin_cpu.py compares the two word for word - against
+// oracle/_ref/libref_host.so (the reference's own header functions compiled for the host) where
+// it is present, and against the committed vectors it produced (tests/golden/ref_host_vectors.npz).
+namespace {
+inline float wf(uint32_t w) { float v; memcpy(&v, &w, 4); return v; }
+inline uint32_t fw(float v) { uint32_t w; memcpy(&w, &v, 4); return w; }
+} // namespace
+
+extern "C" int oracle_probe(const char* name_c, uint32_t n, const uint32_t* in_all, uint32_t k_in, uint32_t* out_all, uint32_t k_out) {
+	const std::string name = name_c;
+	for (uint32_t i = 0; i < n; ++i) {
+		const uint32_t* in = in_all + (size_t)i * k_in;
+		uint32_t* out = out_all + (size_t)i * k_out;
+		if (name == "cascaded_grid_idx_at") {
+			out[0] = cascaded_grid_idx_at(V{wf(in[0]), wf(in[1]), wf(in[2])}, in[3]);
+		} else if (name == "mip_from_pos") {
+			out[0] = mip_from_pos(V{wf(in[0]), wf(in[1]), wf(in[2])}, in[3]);
+		} else if (name == "mip_from_dt") {
+			out[0] = mip_from_dt(wf(in[0]), V{wf(in[1]), wf(in[2]), wf(in[3])}, in[4]);
+		} else if (name == "distance_to_next_voxel") {
+			const V dir{wf(in[3]), wf(in[4]), wf(in[5])};
+			out[0] = fw(distance_to_next_voxel(V{wf(in[0]), wf(in[1]), wf(in[2])}, dir, V{1.0f, 1.0f, 1.0f} / dir, wf(in[6])));
+		} else if (name == "ray_intersect") {
+			const Box box{V{wf(in[0]), wf(in[1]), wf(in[2])}, V{wf(in[3]), wf(in[4]), wf(in[5])}};
+			float tmin, tmax;
+			ray_intersect(box, V{wf(in[6]), wf(in[7]), wf(in[8])}, V{wf(in[9]), wf(in[10]), wf(in[11])}, tmin, tmax);
+			out[0] = fw(tmin); out[1] = fw(tmax);
+		} else if (name == "opencv_undistort") {
+			const float params[7] = {wf(in[0]), wf(in[1]), wf(in[2]), wf(in[3]), 0, 0, 0};
+			float x = wf(in[4]), y = wf(in[5]);
+			iterative_opencv_lens_undistortion(params, &x, &y);
+			out[0] = fw(x); out[1] = fw(y);
+		} else if (name == "srgb_to_linear") {
+			out[0] = fw(srgb_to_linear(wf(in[0])));
+		} else if (name == "linear_to_srgb") {
+			out[0] = fw(linear_to_srgb(wf(in[0])));
+		} else if (name == "loss") {
+			for (int k = 0; k < 3; ++k) {
+				float l, g;
+				loss1(wf(in[k]), wf(in[3 + k]), (int)in[6], l, g);
+				out[k] = fw(l); out[3 + k] = fw(g);
+			}
+		} else if (name == "network_to_rgb") {
+			out[0] = fw(net_to_rgb(wf(in[0]), (int)in[1])); out[1] = fw(net_to_rgb_d(wf(in[0]), (int)in[1]));
+		} else if (name == "network_to_density") {
+			out[0] = fw(net_to_density(wf(in[0]), (int)in[1])); out[1] = fw(net_to_density_d(wf(in[0]), (int)in[1]));
+		} else if (name == "image_idx") {
+			out[0] = image_idx(in[0], in[1], in[2]);
+		} else if (name == "ld_random_val") {
+			out[0] = fw(ld_random_val(in[0], in[1], in[2]));
+		} else if (name == "warp_dt") {
+			out[0] = fw(warp_dt(wf(in[0]))); out[1] = fw(unwarp_dt(wf(in[0])));
+		} else if (name == "stepping") {
+			const float t = wf(in[0]), cone = wf(in[1]), steps = wf(in[2]);
+			out[0] = fw(to_stepping_space(t, cone)); out[1] = fw(from_stepping_space(steps, cone));
+			out[2] = fw(calc_dt(t, cone)); out[3] = fw(advance_n_steps(t, cone, steps));
+		} else if (name == "morton3D") {
+			out[0] = morton3D(in[0], in[1], in[2]);
+		} else if (name == "morton3D_invert") {
+			out[0] = morton3D_invert(in[0]);
+		} else {
+			return -1;
+		}
+	}
+	return 0;
 }

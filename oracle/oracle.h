@@ -163,6 +163,13 @@ float oracle_ld_random_val(uint32_t index, uint32_t seed, uint32_t dim);
 uint16_t oracle_float_to_half(float f);
 float oracle_half_to_float(uint16_t h);
 
+/* Function-grain probes with the interface of oracle/ref_host.cu's ref_probe (rows of 32-bit words,
+ * floats by bit pattern): cascaded_grid_idx_at, mip_from_pos, mip_from_dt, distance_to_next_voxel,
+ * ray_intersect, opencv_undistort, srgb_to_linear, linear_to_srgb, loss, network_to_rgb,
+ * network_to_density, image_idx, ld_random_val, warp_dt, stepping, morton3D, morton3D_invert.
+ * Returns 0, or -1 for an unknown name. */
+int oracle_probe(const char* name, uint32_t n, const uint32_t* in, uint32_t k_in, uint32_t* out, uint32_t k_out);
+
 int oracle_num_threads(void);
 
 #ifdef __cplusplus
