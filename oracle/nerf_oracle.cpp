@@ -718,6 +718,28 @@ float advance_to_next_occupied_voxel(float t, float cone_angle, V o, V d, V idir
 	}
 }
 Box box_of(const oracle_render_config& c) { return {{c.aabb_min[0], c.aabb_min[1], c.aabb_min[2]}, {c.aabb_max[0], c.aabb_max[1], c.aabb_max[2]}}; }
+// One ray from its first possible sample to the far side of the box: init_rays_with_payload_kernel_nerf
+// (:1475-1488), advance_pos_nerf (:333-362), then the loop of generate_next_nerf_network_inputs (:452-465)
+// run to exhaustion. emit(j, t, dt) sees every sample. d must be normalised.
+template <typename Emit>
+uint32_t march_one_ray(const Box& box, V o, V d, uint32_t pix, uint32_t spp_index, float cone_angle, uint32_t max_mip, const uint8_t* bitfield, uint32_t max_steps, Emit emit) {
+	float tmin, tmax;
+	ray_intersect(box, o, d, tmin, tmax);
+	float t = fmaxf(tmin, 0.0f) + 1e-6f;
+	if (!contains(box, o + d * t)) return 0;
+	const V idir = V{1.0f, 1.0f, 1.0f} / d;
+	t = advance_n_steps(t, cone_angle, ld_random_val(spp_index, pix * 786433u, 0));
+	uint32_t count = 0;
+	while (count < max_steps) {
+		t = advance_to_next_occupied_voxel(t, cone_angle, o, d, idir, bitfield, max_mip, box);
+		if (t >= MAX_DEPTH) break;
+		const float dt = calc_dt(t, cone_angle);
+		emit(count, t, dt);
+		++count;
+		t += dt;
+	}
+	return count;
+}
 } // namespace
 
 extern "C" float oracle_ld_random_val(uint32_t index, uint32_t seed, uint32_t dim) { return ld_random_val(index, seed, dim); }
@@ -746,28 +768,16 @@ extern "C" uint64_t oracle_nerf_render_march(const oracle_render_config* cfg, co
 			if (cfg->lens_mode == 1) iterative_opencv_lens_undistortion(cfg->lens_params, &dd.x, &dd.y);
 			const V o = cam[3];
 			const V d = normalize(cam[0] * dd.x + cam[1] * dd.y + cam[2] * dd.z);
-			float tmin, tmax;
-			ray_intersect(box, o, d, tmin, tmax);
-			float t = fmaxf(tmin, 0.0f) + 1e-6f;
-			uint32_t count = 0;
-			if (contains(box, o + d * t)) {
-				const V idir = V{1.0f, 1.0f, 1.0f} / d;
-				const V wd = (d + 1.0f) * 0.5f;
-				t = advance_n_steps(t, cfg->cone_angle_constant, ld_random_val(cfg->spp_index, pix * 786433u, 0));
-				const uint64_t base = pass == 1 ? numsteps[2 * r + 1] : 0;
-				while (count < cfg->max_steps_per_ray) {
-					t = advance_to_next_occupied_voxel(t, cfg->cone_angle_constant, o, d, idir, bitfield, cfg->max_mip, box);
-					if (t >= MAX_DEPTH) break;
-					const float dt = calc_dt(t, cfg->cone_angle_constant);
-					if (pass == 1 && base + count < max_samples) {
+			const V wd = (d + 1.0f) * 0.5f;
+			const uint64_t base = pass == 1 ? numsteps[2 * r + 1] : 0;
+			const uint32_t count = march_one_ray(box, o, d, pix, cfg->spp_index, cfg->cone_angle_constant, cfg->max_mip, bitfield, cfg->max_steps_per_ray,
+				[&](uint32_t j, float t, float dt) {
+					if (pass == 1 && base + j < max_samples) {
 						const V wp = (o + d * t - box.min) / diag(box);
-						float* c = coords + (base + count) * 7;
+						float* c = coords + (base + j) * 7;
 						c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
 					}
-					++count;
-					t += dt;
-				}
-			}
+				});
 			if (pass == 0) numsteps[2 * r] = count;
 		}
 		if (pass == 0) {
@@ -820,6 +830,22 @@ extern "C" void oracle_nerf_render_composite(const oracle_render_config* cfg, co
 		}
 		for (int k = 0; k < 4; ++k) rgba_out[4 * r + k] = out[k];
 		depth_out[r] = dout;
+	}
+}
+
+// The march of explicit rays (o, d normalised; rays [n][6]), for the comparison with the reference's own functions
+// composed the same way (oracle/ref_host.cu ref_march_rays): per ray the sample count, the first
+// and the last sample distance.
+extern "C" void oracle_march_rays(uint32_t n, const float* rays, const uint32_t* pix, uint32_t spp_index, const float* aabb, float cone_angle,
+	uint32_t max_mip, const uint8_t* bitfield, uint32_t max_steps, uint32_t* counts, float* t_first, float* t_last)
+{
+	const Box box{{aabb[0], aabb[1], aabb[2]}, {aabb[3], aabb[4], aabb[5]}};
+#pragma omp parallel for schedule(dynamic, 64)
+	for (uint32_t r = 0; r < n; ++r) {
+		const V o{rays[6 * r + 0], rays[6 * r + 1], rays[6 * r + 2]}, d{rays[6 * r + 3], rays[6 * r + 4], rays[6 * r + 5]};
+		float first = 0.0f, last = 0.0f;
+		counts[r] = march_one_ray(box, o, d, pix[r], spp_index, cone_angle, max_mip, bitfield, max_steps, [&](uint32_t j, float t, float) { if (j == 0) first = t; last = t; });
+		t_first[r] = first; t_last[r] = last;
 	}
 }
 

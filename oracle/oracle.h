@@ -5,11 +5,17 @@
  * bench.py's cpu_baseline / --impl reference legs may load liboracle.so, and only as the
  * checker or the timed CPU baseline.
  *
- * PARITY UNPINNED: the reference ships no golden vectors, no known-answer tests and no CPU
- * implementation for this path, and its CUDA sources cannot run in
- * the authoring container (no GPU). Each function below restates a cited reference routine;
- * the only pins are integer invariants derived from the reference code (level tables, hash of
- * fixed coordinates, Morton round trips) held in tests/golden/.
+ * PARITY: pinned at function grain against the reference's OWN code - oracle/ref_host.cu compiles
+ * the reference's header functions (hash / index / Morton / cascade / mip / voxel stepping / box /
+ * lens / sRGB / losses / activations / image choice / Sobol / pcg32 / SH) for the host from
+ * /root/reference into oracle/_ref/, tests/golden/ref_host_vectors.npz holds their outputs, and
+ * tests/test_ref_pin_cpu.py compares word for word (bit-exact; the stepping-space maps and the
+ * ray-grain march within the tolerance stated there). PARITY UNPINNED for what only exists as
+ * __global__ kernels in the reference (fp16 grid interpolation / scatter, the fused MLP, the
+ * training-march and loss kernels as wholes, Adam): the reference ships no golden vectors, no
+ * tests and no CPU implementation and its CUDA cannot run in the
+ * authoring container. Those functions restate a cited reference routine and are held by derived
+ * invariants (tests/golden/grid_levels.json, tests/test_oracle_cpu.py).
  */
 #ifndef NGPB_ORACLE_H
 #define NGPB_ORACLE_H
@@ -162,6 +168,12 @@ float oracle_ld_random_val(uint32_t index, uint32_t seed, uint32_t dim);
 /* fp16 <-> fp32 (round to nearest even), exposed so tests can build fp16 inputs. */
 uint16_t oracle_float_to_half(float f);
 float oracle_half_to_float(uint16_t h);
+
+/* The render march of explicit rays [n][6] (origin, normalised direction): count, first and last
+ * sample distance per ray; the body of oracle_nerf_render_march. Compared with the reference's own
+ * functions composed the same way (oracle/ref_host.cu ref_march_rays). aabb = min3, max3. */
+void oracle_march_rays(uint32_t n, const float* rays, const uint32_t* pix, uint32_t spp_index, const float* aabb, float cone_angle,
+	uint32_t max_mip, const uint8_t* bitfield, uint32_t max_steps, uint32_t* counts, float* t_first, float* t_last);
 
 /* Function-grain probes with the interface of oracle/ref_host.cu's ref_probe (rows of 32-bit words,
  * floats by bit pattern): cascaded_grid_idx_at, mip_from_pos, mip_from_dt, distance_to_next_voxel,

@@ -121,3 +121,33 @@ extern "C" int ref_probe(const char* name_c, uint32_t n, const uint32_t* in_all,
 	}
 	return 0;
 }
+
+// The reference's render march of one ray, composed from its own functions exactly as its kernels
+// compose them: init_rays_with_payload_kernel_nerf (src/testbed_nerf.cu:1475-1488: t = max(tmin, 0) + 1e-6,
+// dead if outside), advance_pos_nerf (:333-362: jittered start, skip to the first occupied voxel),
+// generate_next_nerf_network_inputs (:452-465: skip, emit at t with dt = calc_dt, t += dt), run
+// until the ray leaves the box. Same outputs as oracle_march_rays.
+extern "C" void ref_march_rays(uint32_t n, const float* rays, const uint32_t* pix, uint32_t spp_index, const float* aabb, float cone_angle_constant,
+	uint32_t max_mip, const uint8_t* bitfield, uint32_t max_steps, uint32_t* counts, float* t_first, float* t_last)
+{
+	const BoundingBox render_aabb{vec3{aabb[0], aabb[1], aabb[2]}, vec3{aabb[3], aabb[4], aabb[5]}};
+	for (uint32_t r = 0; r < n; ++r) {
+		Ray ray{vec3{rays[6 * r + 0], rays[6 * r + 1], rays[6 * r + 2]}, vec3{rays[6 * r + 3], rays[6 * r + 4], rays[6 * r + 5]}};
+		counts[r] = 0; t_first[r] = 0.0f; t_last[r] = 0.0f;
+		float t = fmaxf(render_aabb.ray_intersect(ray.o, ray.d).x, 0.0f) + 1e-6f;
+		if (!render_aabb.contains(ray(t))) continue;
+		const vec3 idir = vec3(1.0f) / ray.d;
+		const float cone_angle = calc_cone_angle(1.0f, vec2(1.0f), cone_angle_constant);
+		t = advance_n_steps(t, cone_angle, ld_random_val(spp_index, pix[r] * 786433));
+		uint32_t j = 0;
+		for (; j < max_steps; ++j) {
+			t = if_unoccupied_advance_to_next_occupied_voxel(t, cone_angle, ray, idir, bitfield, 0, max_mip, render_aabb);
+			if (t >= MAX_DEPTH()) break;
+			const float dt = calc_dt(t, cone_angle);
+			if (j == 0) t_first[r] = t;
+			t_last[r] = t;
+			t += dt;
+		}
+		counts[r] = j;
+	}
+}

@@ -48,9 +48,32 @@ def grid_rows(n_dims, enc):
     return rows.reshape(n * L, n_dims + 3), n, L
 
 
+def march(fn, bitfield, rays, pix, spp_index, aabb, cone, max_mip, max_steps=4096):
+    n = len(rays)
+    counts, first, last = np.zeros(n, np.uint32), np.zeros(n, np.float32), np.zeros(n, np.float32)
+    P = lambda a, t: a.ctypes.data_as(ctypes.POINTER(t))
+    bf = np.ascontiguousarray(bitfield, dtype=np.uint8)
+    fn.restype = None
+    fn(ctypes.c_uint32(n), P(rays, ctypes.c_float), P(pix, ctypes.c_uint32), ctypes.c_uint32(spp_index), P(aabb, ctypes.c_float), ctypes.c_float(cone),
+       ctypes.c_uint32(max_mip), P(bf, ctypes.c_uint8), ctypes.c_uint32(max_steps), P(counts, ctypes.c_uint32), P(first, ctypes.c_float), P(last, ctypes.c_float))
+    return counts, first, last
+
+
+def march_inputs(aabb_scale):
+    grid, max_cascade, aabb = rp.march_scene(aabb_scale)
+    bitfield, _ = oracle.nerf_bitfield(max_cascade, grid)
+    rays, pix = rp.march_rays(aabb_scale)
+    return bitfield, max_cascade, aabb, rays, pix
+
+
 def main():
     ref = load_ref()
     out = {}
+    for aabb_scale, cone, spp in rp.MARCH_CASES:
+        bitfield, max_cascade, aabb, rays, pix = march_inputs(aabb_scale)
+        counts, first, last = march(ref.ref_march_rays, bitfield, rays, pix, spp, aabb, cone, max_cascade)
+        out["march/%d/counts" % aabb_scale], out["march/%d/first" % aabb_scale], out["march/%d/last" % aabb_scale] = counts, first, last
+        out["march/%d/bitfield_crc" % aabb_scale] = np.array([int(np.frombuffer(bitfield.tobytes(), dtype=np.uint8).astype(np.uint64).sum())], dtype=np.uint64)
     for name, (rows, k_out) in rp.cases().items():
         out[name] = probe(ref.ref_probe, name, rows, k_out)
     for name, (n_dims, enc) in rp.GRID_CONFIGS.items():

@@ -84,3 +84,51 @@ def grid_points(n_dims, n=1024):
     x = g.random((n, n_dims), dtype=np.float32)
     x[:4] = np.array([[0.0] * n_dims, [1.0] * n_dims, [0.5] * n_dims, [np.float32(1.0) - np.float32(2.0 ** -24)] * n_dims], dtype=np.float32)
     return x
+
+
+# ---- the render march of explicit rays (oracle_march_rays / ref_march_rays) -------------------------
+def _morton_compact(v):
+    v = v & np.uint32(0x09249249)
+    v = (v ^ (v >> np.uint32(2))) & np.uint32(0x030C30C3)
+    v = (v ^ (v >> np.uint32(4))) & np.uint32(0x0300F00F)
+    v = (v ^ (v >> np.uint32(8))) & np.uint32(0xFF0000FF)
+    v = (v ^ (v >> np.uint32(16))) & np.uint32(0x000003FF)
+    return v
+
+
+def march_scene(aabb_scale):
+    """(density grid float32 [(max_cascade+1) * 128^3] in Morton order, max_cascade, aabb): a few solid blobs
+    and a thin shell, so that rays see long empty stretches, grazing hits and dense interiors."""
+    max_cascade = int(np.log2(aabb_scale))
+    g = np.random.default_rng(5 + aabb_scale)
+    centers = np.float32(0.5) + (g.random((7, 3)).astype(np.float32) - np.float32(0.5)) * np.float32(0.7 * aabb_scale)
+    radii = (0.04 + 0.1 * g.random(7)).astype(np.float32) * np.float32(aabb_scale ** 0.5)
+    idx = np.arange(128 ** 3, dtype=np.uint32)
+    cell = np.stack([_morton_compact(idx), _morton_compact(idx >> np.uint32(1)), _morton_compact(idx >> np.uint32(2))], axis=1).astype(np.float32)
+    grid = np.zeros((max_cascade + 1, 128 ** 3), dtype=np.float32)
+    for k in range(max_cascade + 1):
+        pos = ((cell + np.float32(0.5)) / np.float32(128.0) - np.float32(0.5)) * np.float32(2.0 ** k) + np.float32(0.5)
+        occ = np.zeros(len(pos), dtype=bool)
+        for c, r in zip(centers, radii):
+            occ |= ((pos - c) ** 2).sum(axis=1) < r * r
+        shell = np.abs(np.sqrt(((pos - np.float32(0.5)) ** 2).sum(axis=1)) - np.float32(0.45 * aabb_scale)) < np.float32(0.01 * aabb_scale)
+        grid[k] = np.where(occ | shell, np.float32(10.0), np.float32(0.0))
+    half = np.float32(0.5 * aabb_scale)
+    aabb = np.array([0.5 - half] * 3 + [0.5 + half] * 3, dtype=np.float32)
+    return grid.reshape(-1), max_cascade, aabb
+
+
+def march_rays(aabb_scale, n=3000):
+    """rays float32 [n][6] (origin, normalised direction) from outside and inside the box, and their pixel ids."""
+    g = np.random.default_rng(31 + aabb_scale)
+    o = np.float32(0.5) + g.standard_normal((n, 3)).astype(np.float32) * np.float32(0.6 * aabb_scale)
+    target = np.float32(0.5) + (g.random((n, 3)).astype(np.float32) - np.float32(0.5)) * np.float32(0.9 * aabb_scale)
+    d = target - o
+    d = (d / np.sqrt((d * d).sum(axis=1, keepdims=True))).astype(np.float32)
+    # renormalise in float32 the way normalize() would leave them: close enough to unit length for both sides, which
+    # are handed the very same bits
+    pix = g.integers(0, 1920 * 1080, size=n).astype(np.uint32)
+    return np.ascontiguousarray(np.concatenate([o, d], axis=1), dtype=np.float32), pix
+
+
+MARCH_CASES = [(1, 0.0, 0), (2, 1.0 / 256.0, 0), (4, 1.0 / 256.0, 3)]   # (aabb_scale, cone_angle_constant, spp_index)
