@@ -883,6 +883,16 @@ extern "C" int oracle_probe(const char* name_c, uint32_t n, const uint32_t* in_a
 			float x = wf(in[4]), y = wf(in[5]);
 			iterative_opencv_lens_undistortion(params, &x, &y);
 			out[0] = fw(x); out[1] = fw(y);
+		} else if (name == "uv_to_ray") {
+			oracle_nerf_image m{};
+			m.res_x = (int)in[2]; m.res_y = (int)in[3];
+			m.focal_x = wf(in[4]); m.focal_y = wf(in[5]); m.principal_x = wf(in[6]); m.principal_y = wf(in[7]);
+			for (int k = 0; k < 12; ++k) m.xform[k] = wf(in[8 + k]);
+			m.lens_mode = (int)in[20];
+			for (int k = 0; k < 4; ++k) m.lens_params[k] = wf(in[21 + k]);
+			V o, d;
+			uv_to_ray(wf(in[0]), wf(in[1]), m, o, d);
+			out[0] = fw(o.x); out[1] = fw(o.y); out[2] = fw(o.z); out[3] = fw(d.x); out[4] = fw(d.y); out[5] = fw(d.z);
 		} else if (name == "srgb_to_linear") {
 			out[0] = fw(srgb_to_linear(wf(in[0])));
 		} else if (name == "linear_to_srgb") {

@@ -177,7 +177,7 @@ void oracle_march_rays(uint32_t n, const float* rays, const uint32_t* pix, uint3
 
 /* Function-grain probes with the interface of oracle/ref_host.cu's ref_probe (rows of 32-bit words,
  * floats by bit pattern): cascaded_grid_idx_at, mip_from_pos, mip_from_dt, distance_to_next_voxel,
- * ray_intersect, opencv_undistort, srgb_to_linear, linear_to_srgb, loss, network_to_rgb,
+ * ray_intersect, opencv_undistort, uv_to_ray, srgb_to_linear, linear_to_srgb, loss, network_to_rgb,
  * network_to_density, image_idx, ld_random_val, warp_dt, stepping, morton3D, morton3D_invert.
  * Returns 0, or -1 for an unknown name. */
 int oracle_probe(const char* name, uint32_t n, const uint32_t* in, uint32_t k_in, uint32_t* out, uint32_t k_out);

@@ -94,6 +94,15 @@ extern "C" int ref_probe(const char* name_c, uint32_t n, const uint32_t* in_all,
 			float x = f(in[4]), y = f(in[5]);
 			iterative_opencv_lens_undistortion(params, &x, &y);
 			out[0] = u(x); out[1] = u(y);
+		} else if (name == "uv_to_ray") { // the training / render camera: uv_to_ray (common_device.cuh:393-461) as generate_training_samples_nerf calls it
+			mat4x3 cam;
+			for (int c = 0; c < 4; ++c) cam[c] = vec3{f(in[8 + 3 * c]), f(in[9 + 3 * c]), f(in[10 + 3 * c])};
+			Lens lens;
+			lens.mode = (ELensMode)in[20];
+			for (int k = 0; k < 4; ++k) lens.params[k] = f(in[21 + k]);
+			const Ray ray = uv_to_ray(0, vec2{f(in[0]), f(in[1])}, ivec2{(int)in[2], (int)in[3]}, vec2{f(in[4]), f(in[5])}, cam, vec2{f(in[6]), f(in[7])},
+				vec3(0.0f), 0.0f, 1.0f, 0.0f, {}, {}, lens);
+			for (int k = 0; k < 3; ++k) { out[k] = u(ray.o[k]); out[3 + k] = u(ray.d[k]); }
 		} else if (name == "srgb_to_linear") {
 			out[0] = u(srgb_to_linear(f(in[0])));
 		} else if (name == "linear_to_srgb") {

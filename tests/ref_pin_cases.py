@@ -39,6 +39,13 @@ def cases():
     lens = (g.standard_normal((n, 4)) * np.array([0.1, 0.03, 0.005, 0.005])).astype(np.float32)
     uv = (g.random((n, 2), dtype=np.float32) - np.float32(0.5)) * np.float32(1.2)
     out["opencv_undistort"] = (_cat(_f(lens), _f(uv)), 2)
+    # cameras: rotation-ish 3x3 (any matrix will do: the map is linear) + origin, fox-like intrinsics, every other row an OpenCV lens
+    cam = np.concatenate([g.standard_normal((n, 9)).astype(np.float32), (np.float32(0.5) + g.standard_normal((n, 3)).astype(np.float32))], axis=1)
+    res = np.stack([g.integers(64, 4000, size=n), g.integers(64, 4000, size=n)], axis=1)
+    focal = (res[:, :1] * g.uniform(0.6, 1.6, size=(n, 2))).astype(np.float32)
+    pp = (0.5 + g.standard_normal((n, 2)) * 0.03).astype(np.float32)
+    mode = (np.arange(n) % 2).astype(np.uint32)
+    out["uv_to_ray"] = (_cat(_f(g.random((n, 2), dtype=np.float32)), _u(res), _f(focal), _f(pp), _f(cam), _u(mode), _f(lens)), 6)
     x01 = np.concatenate([g.random(n - 8, dtype=np.float32), np.array([0, 1, 0.04045, 0.0031308, 0.5, 1e-6, 0.04, 0.0031], np.float32)])
     out["srgb_to_linear"] = (_cat(_f(x01)), 1)
     out["linear_to_srgb"] = (_cat(_f(x01)), 1)
