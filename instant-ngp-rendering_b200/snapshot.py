@@ -224,9 +224,9 @@ def build_snapshot(tb, include_optimizer_state=False):
     snap["exposure"] = float(tb.exposure)
     snap["background_color"] = [float(v) for v in tb.background_color]
     cam = tb._camera if tb._camera is not None else np.float32([[1, 0, 0, 0.5], [0, -1, 0, 0.5], [0, 0, -1, 0.5]])
-    f = float(tb._relative_focal_length)
-    snap["camera"] = {"matrix": _mat(cam), "fov_axis": int(tb.fov_axis), "relative_focal_length": [f, f],
-                      "screen_center": [float(v) for v in tb.screen_center], "zoom": 1.0, "scale": 1.5,
+    fxy = [float(v) for v in np.broadcast_to(np.asarray(tb._relative_focal_length, dtype=np.float64), (2,))]   # m_relative_focal_length is a vec2
+    snap["camera"] = {"matrix": _mat(cam), "fov_axis": int(tb.fov_axis), "relative_focal_length": fxy,
+                      "screen_center": [float(v) for v in tb.screen_center], "zoom": float(getattr(tb, "zoom", 1.0)), "scale": 1.5,
                       "aperture_size": 0.0, "autofocus": False, "autofocus_target": [0.5, 0.5, 0.5], "autofocus_depth": 0.5}
     config["snapshot"] = snap
     return config
@@ -282,7 +282,8 @@ def restore(tb, config):
             tb.set_ngp_camera_matrix(cam["matrix"])
         tb.fov_axis = int(cam.get("fov_axis", tb.fov_axis))
         if "relative_focal_length" in cam:
-            tb._relative_focal_length = float(cam["relative_focal_length"][tb.fov_axis])
+            rf = [float(v) for v in cam["relative_focal_length"]]
+            tb._relative_focal_length = rf[0] if rf[0] == rf[1] else np.array(rf, dtype=np.float64)
         if "screen_center" in cam:
             tb.screen_center = tuple(float(v) for v in cam["screen_center"])
     if "up_dir" in snap:

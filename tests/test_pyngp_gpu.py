@@ -120,7 +120,7 @@ def test_training_view_with_opencv_lens_counts_bit_exact(pyngp, oracle, scene):
         tb.nerf.render_with_lens_distortion = False
 
 
-def test_run_py_evaluation_protocol(pyngp, scene):
+def test_run_py_evaluation_protocol(pyngp, scene, tmp_path):
     """scripts/run.py:216-268: background black, snap to pixel centres, min transmittance 1e-4, then for
     every training view the ground-truth frame and the rendered frame, PSNR of the two."""
     tb, poses, focal, syn = scene
@@ -171,3 +171,15 @@ def test_run_py_evaluation_protocol(pyngp, scene):
     with pytest.raises(pyngp.NgpbError):
         tb.nerf.sharpen = 1.0
     tb.nerf.sharpen = 0.0
+    # a snapshot taken with the camera on a training view (vec2 relative focal length, flipped screen centre) loads back
+    tb.set_camera_to_training_view(1)
+    path = str(tmp_path / "view.ingp")
+    tb.save_snapshot(path, False)
+    other = pyngp.Testbed()
+    try:
+        other.load_file(path)
+        assert other.training_step == tb.training_step
+        np.testing.assert_allclose(np.broadcast_to(other._relative_focal_length, (2,)), np.broadcast_to(tb._relative_focal_length, (2,)), rtol=1e-6)
+        np.testing.assert_allclose(other.screen_center, tb.screen_center, atol=1e-7)
+    finally:
+        other.close()
