@@ -76,6 +76,31 @@ for target in checkpoints:
            "psnr_mean": mean, "psnr_min": lo, "psnr_max": hi, "rays_per_batch": testbed.rays_per_batch}
     print(rec, flush=True)
     out["checkpoints"].append(rec)
+# configs[3]: the trained fox at 1920x1080 from training view 0's pose (landscape frame, fov from the view) and from a
+# pose between two views, 1 spp, render_min_transmittance 0.01: Mrays/s by CUDA events around render_nerf
+testbed.set_camera_to_training_view(0)
+cam_a = np.array(testbed._camera, dtype=np.float32)
+testbed.set_camera_to_training_view(1)
+cam_b = np.array(testbed._camera, dtype=np.float32)
+mid = cam_a.copy()
+mid[:, 3] = 0.5 * (cam_a[:, 3] + cam_b[:, 3])
+rw, rh = 1920, 1080
+focal = float(np.broadcast_to(testbed._relative_focal_length, (2,))[1]) * rh
+out["render"] = []
+for name, cam in (("training view 0", cam_a), ("between views 0 and 1", mid)):
+    for _ in range(3):
+        testbed.render_nerf(rw, rh, cam, focal)
+    torch.cuda.synchronize()
+    frames = 10
+    t0 = time.time()
+    for _ in range(frames):
+        rgba, depth = testbed.render_nerf(rw, rh, cam, focal)
+    torch.cuda.synchronize()
+    ms = 1e3 * (time.time() - t0) / frames
+    rec = {"view": name, "resolution": [rw, rh], "ms_per_frame": ms, "mrays_per_s": rw * rh / ms / 1e3, "queries_per_ray": testbed.last_render_samples / (rw * rh),
+           "coverage": float((rgba[..., 3] > 0.5).float().mean())}
+    print(rec, flush=True)
+    out["render"].append(rec)
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
 with open(os.path.join(ROOT, "gpurun_out", "fox_psnr.json"), "w") as f:
     json.dump(out, f, indent=1)
