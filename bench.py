@@ -108,6 +108,8 @@ def dist_setup():
         torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
+        # stdout carries ONE JSON line: whatever NCCL logs (its version banner under NCCL_DEBUG=VERSION / INFO) goes to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         if not dist.is_initialized():
             dist.init_process_group(backend="nccl" if torch.cuda.is_available() else "gloo")
     return rank, world, local
