@@ -607,7 +607,7 @@ def run_nerf(args):
         "gpu_launches": NERF_LAUNCHES_PER_STEP * K,
         "render": render, "grid": grid, "image": image, "clocks": clocks,
     }
-    print(json.dumps(line))
+    emit_line(line)
 
 
 def run_grid(args):
@@ -628,7 +628,7 @@ def run_grid(args):
             "config": g["config"], "kernels_ms": g["kernels_ms"], "roofline": g["roofline"],
             "cpu_baseline": {"value": cpu_v, "unit": "Gpts/s", "cores": cores, "kind": "port", "sample": "2^18 uniform points fwd+bwd (oracle, OpenMP)"},
             "e2e": g["e2e"], "gpu_launches": g["gpu_launches"], "clocks": clocks}
-    print(json.dumps(line))
+    emit_line(line)
 
 
 def run_reference_arm(args):
@@ -653,7 +653,7 @@ def run_reference_arm(args):
                 "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": {"workload": "grid_L16F2_T19_2^20pts", "sample": "2^18 of 2^20 points per step"},
                 "cpu_baseline": {"value": value, "unit": "Gpts/s", "cores": cores, "kind": "port", "sample": "2^18 uniform points, fwd+bwd, OpenMP"},
                 "e2e": {"value": value, "unit": "Gpts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit_line(line)
         return
     cpu = cpu_nerf_baseline(n_rays=256, steps=max(args.steps, 1), warmup=min(args.warmup, 1), budget_s=90.0)
     value = cpu["samples_per_s"]
@@ -665,10 +665,34 @@ def run_reference_arm(args):
                        "note": "ms_per_step is the measured time per oracle step scaled to the 2^18-sample batch"},
             "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cpu["cores"], "kind": "port", "sample": cpu["sample"]},
             "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit_line(line)
+
+
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """stdout carries ONE JSON line. Libraries print there too (NCCL's version banner under NCCL_DEBUG=VERSION, which
+    the GPU box sets, is a plain printf): point fd 1 at stderr for the run and keep the real stdout for the line."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
