@@ -152,7 +152,7 @@ public:
 	// and the host reads the live count back every `render_windows_per_sync` windows.
 	// A pixel does not depend on the policy (tests/test_render_gpu.py), so the defaults are the
 	// fastest measured on B200 (scripts/profile_render.py), not the reference's.
-	uint32_t render_target_queries = 8u << 20;
+	uint32_t render_target_queries = 12u << 20; // sweep on B200 (scripts/render_shard_sweep.py): 14.7 ms per 1080p frame against 15.5 at 8M; shards of 8 unchanged
 	uint32_t render_min_steps = 4;
 	uint32_t render_max_steps = 32;
 	uint32_t render_windows_per_sync = 4;
