@@ -300,14 +300,19 @@ NGPB_HD float unwarp_dt(float dt) {
 }
 
 // ---- activations (nerf_device.cuh:203-263) -----------------------------------------------------
+// Every exponential on the compositing path is the fixed polynomial det_expf, here and in the oracle:
+// the transmittance a ray has accumulated decides where it stops (T < 1e-4 in training,
+// alpha > 1 - min_transmittance in rendering), so per-ray sample counts can only be bit-exact between
+// B200 and the host if the exponentials are. The reference uses __expf (its build has
+// --use_fast_math, CMakeLists.txt:82), whose bits are not reproducible off the GPU either.
 enum NerfActivation : int { kActNone = 0, kActReLU = 1, kActLogistic = 2, kActExponential = 3 };
-NGPB_HD float logistic_f(float x) { return 1.0f / (1.0f + expf(-x)); }
+NGPB_HD float logistic_f(float x) { return 1.0f / (1.0f + det_expf(-x)); }
 NGPB_HD float clamp_f(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 NGPB_HD float network_to_rgb(float val, int act) {
 	switch (act) {
 		case kActReLU: return val > 0.0f ? val : 0.0f;
 		case kActLogistic: return logistic_f(val);
-		case kActExponential: return expf(clamp_f(val, -10.0f, 10.0f));
+		case kActExponential: return det_expf(clamp_f(val, -10.0f, 10.0f));
 		default: return val;
 	}
 }
@@ -315,7 +320,7 @@ NGPB_HD float network_to_rgb_derivative(float val, int act) {
 	switch (act) {
 		case kActReLU: return val > 0.0f ? 1.0f : 0.0f;
 		case kActLogistic: { const float d = logistic_f(val); return d * (1 - d); }
-		case kActExponential: return expf(clamp_f(val, -10.0f, 10.0f));
+		case kActExponential: return det_expf(clamp_f(val, -10.0f, 10.0f));
 		default: return 1.0f;
 	}
 }
@@ -323,7 +328,7 @@ NGPB_HD float network_to_density(float val, int act) {
 	switch (act) {
 		case kActReLU: return val > 0.0f ? val : 0.0f;
 		case kActLogistic: return logistic_f(val);
-		case kActExponential: return expf(val);
+		case kActExponential: return det_expf(val);
 		default: return val;
 	}
 }
@@ -331,10 +336,13 @@ NGPB_HD float network_to_density_derivative(float val, int act) {
 	switch (act) {
 		case kActReLU: return val > 0.0f ? 1.0f : 0.0f;
 		case kActLogistic: { const float d = logistic_f(val); return d * (1 - d); }
-		case kActExponential: return expf(clamp_f(val, -15.0f, 15.0f));
+		case kActExponential: return det_expf(clamp_f(val, -15.0f, 15.0f));
 		default: return 1.0f;
 	}
 }
+
+// alpha of one sample (src/testbed_nerf.cu:926, :524): 1 - exp(-density dt)
+NGPB_HD float composite_alpha(float density, float dt) { return 1.0f - det_expf(-density * dt); }
 
 // ---- losses (nerf_device.cuh:74-143, 600-615) ---------------------------------------------------
 enum NerfLoss : int { kLossL2 = 0, kLossL1 = 1, kLossMape = 2, kLossSmape = 3, kLossHuber = 4, kLossLogL1 = 5, kLossRelativeL2 = 6 };
@@ -355,7 +363,7 @@ NGPB_HD void loss1(float target, float pred, int type, float& loss, float& grad)
 			loss = (ad > alpha ? (ad - 0.5f * alpha) : sq) / 5.0f;
 			grad = (ad > alpha ? (d > 0 ? 1.0f : -1.0f) : (d / alpha)) / 5.0f;
 		} break;
-		case kLossLogL1: { const float div = fabsf(d) + 1.0f; loss = logf(div); grad = copysignf(1.0f / div, d); } break;
+		case kLossLogL1: { const float div = fabsf(d) + 1.0f; loss = det_logf(div); grad = copysignf(1.0f / div, d); } break;
 		default: loss = d * d; grad = 2.0f * d; break;
 	}
 }

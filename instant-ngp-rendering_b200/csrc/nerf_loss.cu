@@ -37,7 +37,7 @@ NGPB_D SampleEval eval_sample(const NerfTrainConfig& cfg, const __half* out, con
 	e.rgb = {network_to_rgb(e.o.r, cfg.rgb_activation), network_to_rgb(e.o.g, cfg.rgb_activation), network_to_rgb(e.o.b, cfg.rgb_activation)};
 	e.dt = unwarp_dt(__ldg(coords + (size_t)j * kCoordFloats + 3));
 	e.density = network_to_density(e.o.s, cfg.density_activation);
-	e.alpha = 1.f - __expf(-e.density * e.dt);
+	e.alpha = composite_alpha(e.density, e.dt);
 	return e;
 }
 // Transmittance in front of every lane's sample given T in front of the chunk; returns T behind it.

@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(kRayBlock) render_composite_kernel(const __gri
 			const V3 pos = unwarp_position(v3(c[0], c[1], c[2]), p.aabb);
 			const float T = 1.0f - rgba.w;
 			const float dt = unwarp_dt(c[3]);
-			const float alpha = 1.0f - __expf(-network_to_density(bs.y, p.density_activation) * dt);
+			const float alpha = composite_alpha(network_to_density(bs.y, p.density_activation), dt);
 			const float weight = alpha * T;
 			rgba.x += network_to_rgb(rg.x, p.rgb_activation) * weight;
 			rgba.y += network_to_rgb(rg.y, p.rgb_activation) * weight;

@@ -40,6 +40,11 @@ public:
 	float learning_rate_factor() const { return m_learning_rate_factor; }
 	float base_learning_rate() const { return m_base_learning_rate; }
 	void set_base_learning_rate(float v) { m_base_learning_rate = v; }
+	// EmaOptimizer::deserialize (ema.h:197-204): with full_precision the fp32 accumulator restarts from the
+	// restored fp16 EMA weights (otherwise the next step would filter from zero).
+	void reseed_ema_accumulator(cudaStream_t stream) {
+		if (m_has_ema && m_ema_full_precision && m_ema_tmp) cast_fp16_to_fp32(stream, m_n_weights, m_weights_ema, m_ema_tmp);
+	}
 
 private:
 	void parse(const Json& config, bool construct);

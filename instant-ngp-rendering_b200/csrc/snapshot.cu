@@ -24,6 +24,7 @@ void Testbed::set_params(const void* host_params, bool full_precision, size_t n_
 	}
 	if (params_inference() != m_params.as<__half>()) {
 		NGPB_CUDA_CHECK(cudaMemcpyAsync(params_inference(), m_params.ptr, n_params * sizeof(__half), cudaMemcpyDeviceToDevice, m_stream));
+		m_optimizer->reseed_ema_accumulator(m_stream);
 	}
 	NGPB_CUDA_CHECK(cudaMemsetAsync(m_gradients.ptr, 0, n_params * sizeof(__half), m_stream));
 	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream)); // the host buffer may go away after the call

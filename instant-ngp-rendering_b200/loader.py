@@ -69,12 +69,17 @@ def read_lens(j, lens):
         lens["principal"][1] = float(np.float32(j["cy"]) / np.float32(j["h"]))
 
 
-def nerf_matrix_to_ngp(m, scale, offset):
-    """nerf_loader.h:101-120."""
+def nerf_matrix_to_ngp(m, scale, offset, from_mitsuba=False):
+    """nerf_loader.h:101-120: flip the y / z columns, scale + offset the origin, then either cycle the
+    axes xyz <- yzx or, for Mitsuba data (:108-110), negate columns 0 and 2 instead."""
     r = np.array(m, dtype=np.float32)[:3, :4].copy()
     r[:, 1] *= -1
     r[:, 2] *= -1
     r[:, 3] = r[:, 3] * np.float32(scale) + np.asarray(offset, dtype=np.float32)
+    if from_mitsuba:
+        r[:, 0] *= -1
+        r[:, 2] *= -1
+        return np.ascontiguousarray(r)
     return np.ascontiguousarray(r[[1, 2, 0], :])
 
 
@@ -201,7 +206,7 @@ def describe_dataset(path_or_paths):
     # the xforms use the FINAL scale / offset (the reference converts inside the loop with the values
     # of the file being read; a single transforms.json - the usual case - gives the same result)
     for fr in out["frames"]:
-        fr["xform"] = nerf_matrix_to_ngp(fr["xform_nerf"], out["scale"], out["offset"])
+        fr["xform"] = nerf_matrix_to_ngp(fr["xform_nerf"], out["scale"], out["offset"], out["from_mitsuba"])
     out["n_images"] = len(out["frames"])
     return out
 

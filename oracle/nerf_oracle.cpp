@@ -366,19 +366,19 @@ extern "C" uint64_t oracle_nerf_generate_samples(const oracle_nerf_config* cfg, 
 }
 
 namespace {
-inline float logistic(float x) { return 1.0f / (1.0f + expf(-x)); }
+inline float logistic(float x) { return 1.0f / (1.0f + c_expf(-x)); }
 inline float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 float net_to_rgb(float v, int act) {
-	switch (act) { case 1: return v > 0 ? v : 0; case 2: return logistic(v); case 3: return expf(clampf(v, -10.0f, 10.0f)); default: return v; }
+	switch (act) { case 1: return v > 0 ? v : 0; case 2: return logistic(v); case 3: return c_expf(clampf(v, -10.0f, 10.0f)); default: return v; }
 }
 float net_to_rgb_d(float v, int act) {
-	switch (act) { case 1: return v > 0 ? 1.0f : 0.0f; case 2: { float d = logistic(v); return d * (1 - d); } case 3: return expf(clampf(v, -10.0f, 10.0f)); default: return 1.0f; }
+	switch (act) { case 1: return v > 0 ? 1.0f : 0.0f; case 2: { float d = logistic(v); return d * (1 - d); } case 3: return c_expf(clampf(v, -10.0f, 10.0f)); default: return 1.0f; }
 }
 float net_to_density(float v, int act) {
-	switch (act) { case 1: return v > 0 ? v : 0; case 2: return logistic(v); case 3: return expf(v); default: return v; }
+	switch (act) { case 1: return v > 0 ? v : 0; case 2: return logistic(v); case 3: return c_expf(v); default: return v; }
 }
 float net_to_density_d(float v, int act) {
-	switch (act) { case 1: return v > 0 ? 1.0f : 0.0f; case 2: { float d = logistic(v); return d * (1 - d); } case 3: return expf(clampf(v, -15.0f, 15.0f)); default: return 1.0f; }
+	switch (act) { case 1: return v > 0 ? 1.0f : 0.0f; case 2: { float d = logistic(v); return d * (1 - d); } case 3: return c_expf(clampf(v, -15.0f, 15.0f)); default: return 1.0f; }
 }
 void loss1(float target, float pred, int type, float& loss, float& grad) {
 	const float d = pred - target;
@@ -392,7 +392,7 @@ void loss1(float target, float pred, int type, float& loss, float& grad) {
 			loss = (ad > alpha ? (ad - 0.5f * alpha) : sq) / 5.0f;
 			grad = (ad > alpha ? (d > 0 ? 1.0f : -1.0f) : (d / alpha)) / 5.0f;
 		} break;
-		case 5: { const float div = fabsf(d) + 1.0f; loss = logf(div); grad = copysignf(1.0f / div, d); } break;
+		case 5: { const float div = fabsf(d) + 1.0f; loss = c_logf(div); grad = copysignf(1.0f / div, d); } break;
 		default: loss = d * d; grad = 2.0f * d; break;
 	}
 }
@@ -418,7 +418,7 @@ extern "C" void oracle_nerf_compute_loss(const oracle_nerf_config* cfg, const or
 			const V rgb = {net_to_rgb(o[0], cfg->rgb_activation), net_to_rgb(o[1], cfg->rgb_activation), net_to_rgb(o[2], cfg->rgb_activation)};
 			const float dt = unwarp_dt(c_in[(size_t)compacted * 7 + 3]);
 			const float density = net_to_density(o[3], cfg->density_activation);
-			const float alpha = 1.f - expf(-density * dt);
+			const float alpha = 1.f - c_expf(-density * dt);
 			const float weight = alpha * T;
 			rgb_ray = rgb_ray + weight * rgb;
 			T *= (1.f - alpha);
@@ -472,7 +472,7 @@ extern "C" void oracle_nerf_compute_loss(const oracle_nerf_config* cfg, const or
 			const float o[4] = {(float)nbits_to_half(out[j * 4 + 0]), (float)nbits_to_half(out[j * 4 + 1]), (float)nbits_to_half(out[j * 4 + 2]), (float)nbits_to_half(out[j * 4 + 3])};
 			const V rgb = {net_to_rgb(o[0], cfg->rgb_activation), net_to_rgb(o[1], cfg->rgb_activation), net_to_rgb(o[2], cfg->rgb_activation)};
 			const float density = net_to_density(o[3], cfg->density_activation);
-			const float alpha = 1.f - expf(-density * dt);
+			const float alpha = 1.f - c_expf(-density * dt);
 			const float weight = alpha * T;
 			rgb_ray2 = rgb_ray2 + weight * rgb;
 			T *= (1.f - alpha);
@@ -807,7 +807,7 @@ extern "C" void oracle_nerf_render_composite(const oracle_render_config* cfg, co
 			const V pos = box.min + V{c[0], c[1], c[2]} * diag(box);
 			const float T = 1.0f - rgba[3];
 			const float dt = unwarp_dt(c[3]);
-			const float alpha = 1.0f - expf(-net_to_density(oracle_half_to_float(o16[3]), cfg->density_activation) * dt);
+			const float alpha = 1.0f - c_expf(-net_to_density(oracle_half_to_float(o16[3]), cfg->density_activation) * dt);
 			const float weight = alpha * T;
 			for (int k = 0; k < 3; ++k) rgba[k] += net_to_rgb(oracle_half_to_float(o16[k]), cfg->rgb_activation) * weight;
 			rgba[3] += weight;

@@ -172,12 +172,17 @@ def test_loss_and_gradients_match_oracle(ngp, oracle, aabb_scale, loss_type, rgb
     dev = _Device(ngp, oracle, cfg, images, bitfield, mean)
     total, kept = _generate(ngp, oracle, cfg, dev, step_rng)
     # a synthetic network output: moderate densities so that some rays terminate early, some do not
-    out = np.zeros((max_samples, 4), dtype=np.float16)
-    out[:total, :3] = rng.normal(0, 1.0, size=(total, 3)).astype(np.float16)
-    out[:total, 3] = rng.normal(2.0, 2.5, size=total).astype(np.float16)
-    dev.rgbsigma.copy_(_dev(out))
+    # Keyed by (ray index, sample index), not by buffer position: sample slots are handed out by an atomicAdd in
+    # block-arrival order, so a positional fill would give every run a different ray -> density assignment.
     ray_indices = dev.ray_indices.cpu().numpy().view(np.uint32)[:kept].copy()
     numsteps_in = dev.numsteps.cpu().numpy().view(np.uint32)[:kept].copy()
+    out = np.zeros((max_samples, 4), dtype=np.float16)
+    for k in range(kept):
+        n, b = int(numsteps_in[k, 0]), int(numsteps_in[k, 1])
+        r = np.random.default_rng([11 + aabb_scale, int(ray_indices[k])])
+        out[b:b + n, :3] = r.normal(0, 1.0, size=(n, 3)).astype(np.float16)
+        out[b:b + n, 3] = r.normal(2.0, 2.5, size=n).astype(np.float16)
+    dev.rgbsigma.copy_(_dev(out))
     rays = dev.rays.cpu().numpy()[:kept].copy()
     coords = dev.coords.cpu().numpy()[:total].copy()
 
@@ -189,7 +194,8 @@ def test_loss_and_gradients_match_oracle(ngp, oracle, aabb_scale, loss_type, rgb
     comp, loss, dloss = oracle.nerf_compute_loss(cfg, images, mean, ray_indices, numsteps_in, rays, coords, out[:total], step_rng)
     got_ns = dev.numsteps.cpu().numpy().view(np.uint32)[:kept]
     n_compacted = int(dev.counters.cpu().numpy().view(np.uint32)[1])
-    # compacted per-ray counts: bit-exact (early termination happens at the same sample)
+    # compacted per-ray counts: bit-exact (early termination happens at the same sample: the exponentials of the
+    # compositing chain are the same fixed polynomial on both sides, nerf_device.cuh composite_alpha)
     assert np.array_equal(got_ns[:, 0], comp)
     assert n_compacted == int(comp.sum())
     assert (comp < numsteps_in[:, 0]).any()
