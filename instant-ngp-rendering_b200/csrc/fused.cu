@@ -1,0 +1,567 @@
+// Persistent warp-specialised kernel: hash-grid gather -> tcgen05 MLP chain(s) -> (training) backward chain
+// -> warp-aggregated gradient scatter, one launch per pass (see fused.h).
+//
+// One CTA per SM. Warps 0 .. 4G-1 form G worker groups of 128 threads; the last warp is the MMA warp.
+//
+//   worker group g (thread = sample row r of the group's current tile = TMEM lane r):
+//       gathers the tile's features from the hash table into the group's X0 buffer (the chunk-major image a
+//       K-major UMMA descriptor reads), then for every layer: arrive on ready[g] -> wait on done[g] -> epilogue
+//       (tcgen05.ld of the group's own 64-column accumulator, activation, fp16, store of the next operand);
+//       in training the backward chain follows and the tile's dL/d(features) rows go from TMEM straight into
+//       red.global.add.f16x2 on the gradient table.
+//   MMA warp (one elected thread): polls ready[0..G), and for whichever group is ready issues the tcgen05.mma
+//       batch of that group's next layer and commits it to done[g].
+//
+// G tiles are in flight per SM at different stages, so one group's gathers (L2 latency) and epilogues
+// (tcgen05.ld, ALU, st.shared) overlap the other groups' MMAs: the tensor pipe no longer idles behind a single
+// serial chain (round 1: 13 % tensor-pipe active, 12 % warps active). Weight-gradient accumulators live in TMEM
+// columns shared by all groups - one thread issues every MMA, and MMAs of one thread execute in order, so
+// accumulating into the same columns from different groups' tiles is race-free - and leave the SM once.
+#include "fused.h"
+#include "grid_device.cuh"
+#include "mlp_device.cuh"
+
+#include <algorithm>
+#include <cstdlib>
+
+namespace ngpb {
+
+constexpr uint32_t kMaxGroups = 4;
+constexpr uint32_t kFusedMaxThreads = kMaxGroups * 128 + 32;
+constexpr uint32_t kHiddenBytes = kTile * kMlpWidth * 2;
+
+struct FusedLayout {
+	uint32_t groups;
+	uint32_t w_a, w_b;            // smem offsets of the chains' weights
+	uint32_t group0, group_stride;
+	uint32_t x0, ha, x1, hb, gy;  // offsets inside a group's region
+	uint32_t total;
+};
+
+static FusedLayout make_layout(const FusedNet& n, bool train, uint32_t groups) {
+	FusedLayout l{};
+	uint32_t o = 0;
+	l.w_a = o; o += 2 * chain_params(n.a_in, n.a_hidden);
+	l.w_b = o; if (n.nerf) o += 2 * chain_params(n.b_in, n.b_hidden);
+	o = (o + 1023u) & ~1023u;
+	l.group0 = o;
+	uint32_t g = 0;
+	l.x0 = g; g += kTile * n.a_in * 2;
+	l.ha = g; g += train ? n.a_hidden * kHiddenBytes : kHiddenBytes;
+	if (train) {
+		l.x1 = g; if (n.nerf) g += kTile * n.b_in * 2;
+		l.hb = g; if (n.nerf) g += n.b_hidden * kHiddenBytes;
+		l.gy = g; g += kTile * 16 * 2;
+	} else {
+		l.x1 = l.ha; l.hb = l.ha; l.gy = l.ha;
+	}
+	l.group_stride = (g + 1023u) & ~1023u;
+	l.groups = groups;
+	l.total = l.group0 + groups * l.group_stride;
+	return l;
+}
+
+static uint32_t dw_columns(const FusedNet& n) {
+	uint32_t c = n.a_in + (n.a_hidden - 1) * 64 + 16;
+	if (n.nerf) c += n.b_in + (n.b_hidden - 1) * 64 + 16;
+	return c;
+}
+
+static uint32_t pick_groups(const FusedNet& n, bool train) {
+	static const int forced = getenv("NGPB_FUSED_GROUPS") ? atoi(getenv("NGPB_FUSED_GROUPS")) : 0;
+	uint32_t best = 0;
+	for (uint32_t g = 1; g <= kMaxGroups; ++g) {
+		if (make_layout(n, train, g).total > 227u * 1024u - 256u) break;
+		if (64 * g + (train ? dw_columns(n) : 0) > 512) break;
+		best = g;
+	}
+	if (forced > 0) best = std::min(best, (uint32_t)forced);
+	return best;
+}
+
+bool fused_grid_supported(const FusedNet& n, const GridParams& g) {
+	static const bool off = getenv("NGPB_FUSED") && atoi(getenv("NGPB_FUSED")) == 0;
+	if (off) return false;
+	const uint32_t F = g.n_features_per_level;
+	if (!((g.n_dims == 3 && (F == 2 || F == 4)) || (g.n_dims == 2 && F == 2 && !n.nerf))) return false;
+	if (g.interpolation_type != (int)InterpolationType::Linear) return false;
+	if ((g.n_levels * F) % 8 != 0 || g.n_levels * F > n.a_in) return false;
+	return pick_groups(n, true) >= 1 && pick_groups(n, false) >= 1;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+NGPB_D void mbar_arrive(uint64_t* bar) {
+	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+NGPB_D bool mbar_test(uint64_t* bar, uint32_t parity) {
+	uint32_t ok;
+	asm volatile(
+		"{\n"
+		".reg .pred p;\n"
+		"mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+		"selp.u32 %0, 1, 0, p;\n"
+		"}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+	return ok != 0;
+}
+
+struct Chain {
+	uint32_t in_width, n_hidden, relu;
+	uint32_t w;          // smem address of the chain's weights
+	uint32_t h;          // smem address of hidden buffer 0
+	uint32_t h_stride;   // bytes between hidden buffers (0: every layer shares one)
+	uint8_t* h_ptr;      // generic pointer of hidden buffer 0
+	uint32_t dw_col;     // first TMEM column of the chain's dW accumulators
+};
+NGPB_D uint32_t chain_w(const Chain& ch, uint32_t layer) {
+	return ch.w + (layer == 0 ? 0u : 2u * kMlpWidth * ch.in_width + (layer - 1) * 2u * kMlpWidth * kMlpWidth);
+}
+NGPB_D uint32_t chain_dw_col(const Chain& ch, uint32_t layer) {
+	return ch.dw_col + (layer == 0 ? 0u : ch.in_width + (layer - 1) * kMlpWidth);
+}
+
+// ---- MMA warp: the batch of one round -----------------------------------------------------------------
+// forward layer j of a chain whose input tile is at smem address x; result in acc[0, 64) (j < n_hidden) or [0, 16)
+NGPB_D void issue_forward(uint32_t acc, const Chain& ch, uint32_t x, uint32_t j) {
+	if (j == 0) mma_xwT(acc, x, chain_w(ch, 0), ch.in_width, kMlpWidth, false);
+	else if (j < ch.n_hidden) mma_xwT(acc, ch.h + (j - 1) * ch.h_stride, chain_w(ch, j), kMlpWidth, kMlpWidth, false);
+	else mma_xwT(acc, ch.h + (ch.n_hidden - 1) * ch.h_stride, chain_w(ch, ch.n_hidden), kMlpWidth, kMlpPaddedOut, false);
+}
+// backward step s (0 = output layer ... n_hidden = first layer): dW of the layer (accumulated over all tiles of the
+// CTA) and the gradient of the layer's input in acc
+NGPB_D void issue_backward(uint32_t tmem, uint32_t acc, const Chain& ch, uint32_t x, uint32_t gy, uint32_t dx_cols, uint32_t s, uint32_t bit_base, uint32_t& dw_mask) {
+	const uint32_t layer = ch.n_hidden - s;
+	const bool accumulate = (dw_mask >> (bit_base + layer)) & 1u;
+	dw_mask |= 1u << (bit_base + layer);
+	const uint32_t dw = tmem + chain_dw_col(ch, layer);
+	if (s == 0) {
+		mma_pTq(dw, ch.h + (ch.n_hidden - 1) * ch.h_stride, gy, kMlpPaddedOut, accumulate);   // dW_out^T = H^T dY
+		mma_dyW(acc, gy, chain_w(ch, ch.n_hidden), kMlpPaddedOut, kMlpWidth);
+	} else if (s < ch.n_hidden) {
+		const uint32_t d = ch.h + layer * ch.h_stride, hprev = ch.h + (layer - 1) * ch.h_stride;
+		mma_pTq(dw, d, hprev, kMlpWidth, accumulate);                                          // dW_j = D^T H_{j-1}
+		mma_dyW(acc, d, chain_w(ch, layer), kMlpWidth, kMlpWidth);
+	} else {
+		mma_pTq(dw, ch.h, x, ch.in_width, accumulate);                                         // dW_0 = D^T X
+		if (dx_cols) mma_dyW(acc, ch.h, chain_w(ch, 0), kMlpWidth, dx_cols);
+	}
+}
+
+// ---- worker side ----------------------------------------------------------------------------------------
+struct Worker {
+	uint32_t tmem_row;   // TMEM address of this thread's row in the group's accumulator
+	uint32_t row;
+	uint64_t* ready;
+	uint64_t* done;
+	uint32_t phase;
+};
+// publish this thread's smem writes / finished TMEM reads, then hand the group's tile to the MMA warp
+NGPB_D void grp_round(Worker& w) {
+	fence_proxy_async();
+	tc_fence_before();
+	mbar_arrive(w.ready);
+	mbar_wait(w.done, w.phase);
+	w.phase ^= 1;
+	tc_fence_after();
+}
+NGPB_D void epi_store(const Worker& w, uint8_t* dst_tile, uint32_t ncols, bool relu) {
+	for (uint32_t c0 = 0; c0 < ncols; c0 += 16) {
+		uint32_t v[16];
+		tmem_ld16(w.tmem_row + c0, v);
+		tmem_wait_ld();
+		uint32_t h[8];
+#pragma unroll
+		for (uint32_t k = 0; k < 8; ++k) {
+			float a = __uint_as_float(v[2 * k]), b = __uint_as_float(v[2 * k + 1]);
+			if (relu) { a = fmaxf(a, 0.0f); b = fmaxf(b, 0.0f); }
+			h[k] = pack2(a, b);
+		}
+		*reinterpret_cast<uint4*>(dst_tile + chunk_offset(kTile, w.row, c0 / 8)) = make_uint4(h[0], h[1], h[2], h[3]);
+		*reinterpret_cast<uint4*>(dst_tile + chunk_offset(kTile, w.row, c0 / 8 + 1)) = make_uint4(h[4], h[5], h[6], h[7]);
+	}
+}
+// in place: tile row <- acc * (tile row > 0) (ReLU) or acc
+NGPB_D void epi_mask(const Worker& w, uint8_t* act_tile, bool relu) {
+	for (uint32_t c0 = 0; c0 < kMlpWidth; c0 += 16) {
+		uint32_t v[16];
+		tmem_ld16(w.tmem_row + c0, v);
+		uint4* p0 = reinterpret_cast<uint4*>(act_tile + chunk_offset(kTile, w.row, c0 / 8));
+		uint4* p1 = reinterpret_cast<uint4*>(act_tile + chunk_offset(kTile, w.row, c0 / 8 + 1));
+		const uint4 a0 = *p0, a1 = *p1;
+		const uint32_t act[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+		tmem_wait_ld();
+		uint32_t h[8];
+#pragma unroll
+		for (uint32_t k = 0; k < 8; ++k) {
+			float a = __uint_as_float(v[2 * k]), b = __uint_as_float(v[2 * k + 1]);
+			if (relu) {
+				const float2 f = unpack2(act[k]);
+				a = f.x > 0.0f ? a : 0.0f;
+				b = f.y > 0.0f ? b : 0.0f;
+			}
+			h[k] = pack2(a, b);
+		}
+		*p0 = make_uint4(h[0], h[1], h[2], h[3]);
+		*p1 = make_uint4(h[4], h[5], h[6], h[7]);
+	}
+}
+// chain input tile written by the caller -> the chain's 16 output columns in acc[0, 16)
+NGPB_D void worker_forward(Worker& w, const Chain& ch) {
+	for (uint32_t j = 0; j < ch.n_hidden; ++j) {
+		grp_round(w);
+		epi_store(w, ch.h_ptr + j * ch.h_stride, kMlpWidth, ch.relu);
+	}
+	grp_round(w);
+}
+// gradient seed tile written by the caller -> dL/d(chain input) in acc; hidden buffers become their gradients
+NGPB_D void worker_backward(Worker& w, const Chain& ch) {
+	for (uint32_t s = 0; s < ch.n_hidden; ++s) {
+		grp_round(w);
+		epi_mask(w, ch.h_ptr + (ch.n_hidden - 1 - s) * ch.h_stride, ch.relu);
+	}
+	grp_round(w);
+}
+
+// dW accumulators -> this CTA's slice of the partials. M = 64 accumulators keep row r in TMEM lane (r % 16) + 32 (r / 16).
+NGPB_D void store_dw(uint32_t tmem_lane_base, uint32_t t, uint32_t col, uint32_t ncols, float* __restrict__ dst, bool transposed) {
+	const uint32_t warp = t / 32, lane = t % 32;
+	const uint32_t r = warp * 16 + lane;
+	for (uint32_t c0 = 0; c0 < ncols; c0 += 16) {
+		uint32_t v[16];
+		tmem_ld16(tmem_lane_base + col + c0, v);
+		tmem_wait_ld();
+		if (lane < 16) {
+#pragma unroll
+			for (uint32_t k = 0; k < 16; ++k) {
+				if (transposed) dst[(c0 + k) * kMlpWidth + r] = __uint_as_float(v[k]);
+				else dst[r * ncols + c0 + k] = __uint_as_float(v[k]);
+			}
+		}
+	}
+}
+NGPB_D void store_chain_dw(uint32_t tmem_lane_base, uint32_t t, const Chain& ch, float* __restrict__ dst) {
+	store_dw(tmem_lane_base, t, chain_dw_col(ch, 0), ch.in_width, dst, false);
+	dst += kMlpWidth * ch.in_width;
+	for (uint32_t j = 1; j < ch.n_hidden; ++j) {
+		store_dw(tmem_lane_base, t, chain_dw_col(ch, j), kMlpWidth, dst, false);
+		dst += kMlpWidth * kMlpWidth;
+	}
+	store_dw(tmem_lane_base, t, chain_dw_col(ch, ch.n_hidden), kMlpPaddedOut, dst, true);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+template <uint32_t D, uint32_t F, bool NERF, bool TRAIN>
+__global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
+	const __grid_constant__ FusedNet net, const __grid_constant__ GridParams gp, const __grid_constant__ FusedLayout lay,
+	const uint32_t n_max, const uint32_t* __restrict__ n_dev,
+	const __half* __restrict__ params, const __half* __restrict__ table,
+	const float* __restrict__ input, const uint32_t in_stride,
+	__half* __restrict__ out, const uint32_t out_stride,
+	const __half* __restrict__ dL_dout, const uint32_t dy_stride,
+	__half* __restrict__ grid_grad, float* __restrict__ dw_partials)
+{
+	extern __shared__ __align__(1024) uint8_t smem[];
+	__shared__ uint64_t bar_ready[kMaxGroups];
+	__shared__ uint64_t bar_done[kMaxGroups];
+	__shared__ uint32_t tmem_slot;
+
+	const uint32_t G = lay.groups;
+	const uint32_t t = threadIdx.x, warp = t / 32, lane = t % 32;
+	const bool is_mma_warp = warp == 4 * G;
+	const uint32_t n = n_dev ? min(__ldg(n_dev), n_max) : n_max;
+	const uint32_t n_tiles = (n + kTile - 1) / kTile;
+	const uint32_t tile_stride = gridDim.x * G;
+
+	// weights: every thread helps
+	for (uint32_t pass = 0; pass < (NERF ? 2u : 1u); ++pass) {
+		uint8_t* dst = smem + (pass ? lay.w_b : lay.w_a);
+		const __half* src = params + (pass ? net.b_param_off : net.a_param_off);
+		const uint32_t in_w = pass ? net.b_in : net.a_in, n_hidden = pass ? net.b_hidden : net.a_hidden;
+		load_chain_weights(dst, src, in_w, n_hidden);
+	}
+	if (is_mma_warp) tmem_alloc<512>(&tmem_slot);
+	if (t == 0) {
+		for (uint32_t g = 0; g < kMaxGroups; ++g) {
+			mbar_init(&bar_ready[g], 128);
+			mbar_init(&bar_done[g], 1);
+		}
+		fence_barrier_init();
+	}
+	fence_proxy_async();
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+
+	const uint32_t tmem = tmem_slot;
+	const uint32_t sbase = smem_u32(smem);
+	const uint32_t dw_base_col = 64 * G;
+
+	auto make_chains = [&](uint32_t g, Chain& A, Chain& B) {
+		const uint32_t off = lay.group0 + g * lay.group_stride;
+		A.in_width = net.a_in; A.n_hidden = net.a_hidden; A.relu = net.a_relu;
+		A.w = sbase + lay.w_a; A.h = sbase + off + lay.ha; A.h_ptr = smem + off + lay.ha;
+		A.h_stride = TRAIN ? kHiddenBytes : 0;
+		A.dw_col = dw_base_col;
+		B = A;
+		if (NERF) {
+			B.in_width = net.b_in; B.n_hidden = net.b_hidden; B.relu = net.b_relu;
+			B.w = sbase + lay.w_b; B.h = sbase + off + lay.hb; B.h_ptr = smem + off + lay.hb;
+			B.dw_col = dw_base_col + net.a_in + (net.a_hidden - 1) * 64 + 16;
+		}
+	};
+
+	const uint32_t RA = net.a_hidden + 1, RB = NERF ? net.b_hidden + 1 : 0;
+	const uint32_t rounds_per_tile = TRAIN ? 2 * (RA + RB) : RA + RB;
+	const bool want_dx = TRAIN && grid_grad != nullptr;
+
+	if (is_mma_warp) {
+		if (lane == 0) {
+			uint32_t tile[kMaxGroups], round[kMaxGroups], parity[kMaxGroups];
+			uint32_t live = 0, dw_mask = 0;
+#pragma unroll
+			for (uint32_t g = 0; g < kMaxGroups; ++g) {
+				tile[g] = blockIdx.x * G + g;
+				round[g] = 0;
+				parity[g] = 0;
+				if (g < G && tile[g] < n_tiles) live |= 1u << g;
+			}
+			while (live) {
+				bool any = false;
+#pragma unroll
+				for (uint32_t g = 0; g < kMaxGroups; ++g) {
+					if (!((live >> g) & 1u)) continue;
+					if (!mbar_test(&bar_ready[g], parity[g])) continue;
+					any = true;
+					parity[g] ^= 1;
+					tc_fence_after();
+					Chain A, B;
+					make_chains(g, A, B);
+					const uint32_t off = sbase + lay.group0 + g * lay.group_stride;
+					const uint32_t x0 = off + lay.x0, x1 = off + lay.x1, gy = off + lay.gy;
+					const uint32_t acc = tmem + 64 * g;
+					uint32_t r = round[g];
+					if (r < RA) issue_forward(acc, A, x0, r);
+					else if (r < RA + RB) issue_forward(acc, B, x1, r - RA);
+					else {
+						r -= RA + RB;
+						if (NERF) {
+							if (r < RB) issue_backward(tmem, acc, B, x1, gy, 16, r, RA, dw_mask);
+							else issue_backward(tmem, acc, A, x0, x1, want_dx ? net.a_in : 0, r - RB, 0, dw_mask);
+						} else {
+							issue_backward(tmem, acc, A, x0, gy, want_dx ? net.a_in : 0, r, 0, dw_mask);
+						}
+					}
+					umma_commit(&bar_done[g]);
+					if (++round[g] == rounds_per_tile) {
+						round[g] = 0;
+						tile[g] += tile_stride;
+						if (tile[g] >= n_tiles) live &= ~(1u << g);
+					}
+				}
+				if (!any) __nanosleep(32);
+			}
+		}
+		__syncwarp();
+	} else {
+		const uint32_t g = warp / 4;
+		const uint32_t row = t - g * 128;
+		Worker w;
+		w.tmem_row = tmem + ((row & ~31u) << 16) + 64 * g;
+		w.row = row;
+		w.ready = &bar_ready[g];
+		w.done = &bar_done[g];
+		w.phase = 0;
+		Chain A, B;
+		make_chains(g, A, B);
+		uint8_t* gbase = smem + lay.group0 + g * lay.group_stride;
+		uint8_t* x0 = gbase + lay.x0;
+		uint8_t* x1 = gbase + lay.x1;
+		uint8_t* gy = gbase + lay.gy;
+		constexpr uint32_t C = 8 / F;           // levels per 16-byte chunk
+		const uint32_t L = gp.n_levels;
+		const uint32_t n_feat_chunks = L * F / 8;
+
+		for (uint32_t tile = blockIdx.x * G + g; tile < n_tiles; tile += tile_stride) {
+			const uint32_t i = tile * kTile + row;
+			const bool valid = i < n;
+			const float* in_row = input + (size_t)i * in_stride;
+			float x[D];
+#pragma unroll
+			for (uint32_t d = 0; d < D; ++d) x[d] = valid ? __ldg(in_row + d) : 0.0f;
+
+			// ---- gather: the tile's encoded features, straight into the first UMMA operand ----
+#pragma unroll 2
+			for (uint32_t ch = 0; ch < n_feat_chunks; ++ch) {
+				alignas(16) __half vals[8];
+				if (valid) {
+#pragma unroll
+					for (uint32_t c = 0; c < C; ++c) grid_encode_level<D, F>(gp, ch * C + c, x, table, &vals[c * F]);
+				} else {
+					*reinterpret_cast<uint4*>(vals) = make_uint4(0u, 0u, 0u, 0u);
+				}
+				*reinterpret_cast<uint4*>(x0 + chunk_offset(kTile, row, ch)) = *reinterpret_cast<const uint4*>(vals);
+			}
+			for (uint32_t ch = n_feat_chunks; ch < net.a_in / 8; ++ch) {
+				// padding columns carry 1 (tcnn Encoding padding, grid.h:806-811)
+				const uint32_t one2 = valid ? 0x3C003C00u : 0u;
+				*reinterpret_cast<uint4*>(x0 + chunk_offset(kTile, row, ch)) = make_uint4(one2, one2, one2, one2);
+			}
+
+			// ---- forward ----
+			worker_forward(w, A);
+			uint32_t v[16];
+			float sigma_raw = 0.0f;
+			if (NERF) {
+				// chain-B input row: [density-MLP output (16) | SH(dir) (16)]
+				tmem_ld16(w.tmem_row, v);
+				const float* crow = in_row + net.dir_offset;
+				const float dx = valid ? __ldg(crow) * 2.0f - 1.0f : 0.0f, dy = valid ? __ldg(crow + 1) * 2.0f - 1.0f : 0.0f, dz = valid ? __ldg(crow + 2) * 2.0f - 1.0f : 0.0f;
+				float sh[16];
+				sh_encode16(net.sh_degree, dx, dy, dz, sh);
+				tmem_wait_ld();
+				uint32_t h[8];
+#pragma unroll
+				for (uint32_t k = 0; k < 8; ++k) h[k] = pack2(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1]));
+				sigma_raw = unpack2(h[0]).x; // the fp16 value the reference copies out (nerf_network.h:31-43)
+				*reinterpret_cast<uint4*>(x1 + chunk_offset(kTile, row, 0)) = make_uint4(h[0], h[1], h[2], h[3]);
+				*reinterpret_cast<uint4*>(x1 + chunk_offset(kTile, row, 1)) = make_uint4(h[4], h[5], h[6], h[7]);
+#pragma unroll
+				for (uint32_t k = 0; k < 8; ++k) h[k] = pack2(sh[2 * k], sh[2 * k + 1]);
+				*reinterpret_cast<uint4*>(x1 + chunk_offset(kTile, row, 2)) = make_uint4(h[0], h[1], h[2], h[3]);
+				*reinterpret_cast<uint4*>(x1 + chunk_offset(kTile, row, 3)) = make_uint4(h[4], h[5], h[6], h[7]);
+				worker_forward(w, B);
+			}
+
+			if (!TRAIN) {
+				tmem_ld16(w.tmem_row, v);
+				tmem_wait_ld();
+				uint32_t h[8];
+#pragma unroll
+				for (uint32_t k = 0; k < 8; ++k) h[k] = pack2(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1]));
+				if (NERF) {
+					// channel 3 carries the density (nerf_network.h:132-138)
+					const float2 b = unpack2(h[1]);
+					h[1] = pack2(b.x, sigma_raw);
+				}
+				if (valid) {
+					__half* o = out + (size_t)i * out_stride;
+					if (out_stride >= 16) {
+						reinterpret_cast<uint4*>(o)[0] = make_uint4(h[0], h[1], h[2], h[3]);
+						reinterpret_cast<uint4*>(o)[1] = make_uint4(h[4], h[5], h[6], h[7]);
+					} else if (out_stride == 4) {
+						*reinterpret_cast<uint2*>(o) = make_uint2(h[0], h[1]);
+					} else {
+						o[0] = __float2half(unpack2(h[0]).x);
+					}
+				}
+				continue;
+			}
+
+			// ---- backward ----
+			if (NERF) {
+				// dL/d(rgb network output): channels 0-2, rest zero (nerf_network.h:45-60)
+				const uint2 gq = __ldg(reinterpret_cast<const uint2*>(dL_dout + (size_t)i * dy_stride));
+				const float dsigma = unpack2(gq.y).y;
+				*reinterpret_cast<uint4*>(gy + chunk_offset(kTile, row, 0)) = make_uint4(gq.x, gq.y & 0xFFFFu, 0u, 0u);
+				*reinterpret_cast<uint4*>(gy + chunk_offset(kTile, row, 1)) = make_uint4(0u, 0u, 0u, 0u);
+				worker_backward(w, B);
+				// dL/d(density-MLP output) = chain-B input gradient, columns 0-15, + dsigma on column 0
+				// (nerf_network.h:62-74); overwrites the first two chunks of x1 in place.
+				tmem_ld16(w.tmem_row, v);
+				tmem_wait_ld();
+				uint32_t h[8];
+				h[0] = pack2(__uint_as_float(v[0]) + dsigma, __uint_as_float(v[1]));
+#pragma unroll
+				for (uint32_t k = 1; k < 8; ++k) h[k] = pack2(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1]));
+				*reinterpret_cast<uint4*>(x1 + chunk_offset(kTile, row, 0)) = make_uint4(h[0], h[1], h[2], h[3]);
+				*reinterpret_cast<uint4*>(x1 + chunk_offset(kTile, row, 1)) = make_uint4(h[4], h[5], h[6], h[7]);
+				worker_backward(w, A);
+			} else {
+				const uint4* gsrc = reinterpret_cast<const uint4*>(dL_dout + (size_t)i * dy_stride);
+				*reinterpret_cast<uint4*>(gy + chunk_offset(kTile, row, 0)) = __ldg(gsrc);
+				*reinterpret_cast<uint4*>(gy + chunk_offset(kTile, row, 1)) = __ldg(gsrc + 1);
+				worker_backward(w, A);
+			}
+
+			// ---- scatter: this row's dL/d(features) from TMEM into the gradient table ----
+			if (want_dx) {
+				for (uint32_t c0 = 0; c0 < L * F; c0 += 16) {
+					tmem_ld16(w.tmem_row + c0, v);
+					tmem_wait_ld();
+					alignas(16) __half gh[16];
+#pragma unroll
+					for (uint32_t k = 0; k < 8; ++k) reinterpret_cast<uint32_t*>(gh)[k] = pack2(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1]));
+					grid_scatter_chunk<D, F>(gp, (c0 / 8) * C, x, gh, grid_grad, 1.0f, true, lane);
+					if (c0 + 8 < L * F) grid_scatter_chunk<D, F>(gp, (c0 / 8 + 1) * C, x, gh + 8, grid_grad, 1.0f, true, lane);
+				}
+			}
+		}
+	}
+
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+	if (TRAIN && t < 128) {
+		// every MMA of this CTA was waited for by the group that owned it
+		Chain A, B;
+		make_chains(0, A, B);
+		const uint32_t lane_base = tmem + ((t & ~31u) << 16);
+		float* dst = dw_partials + (size_t)blockIdx.x * (chain_params(net.a_in, net.a_hidden) + (NERF ? chain_params(net.b_in, net.b_hidden) : 0u));
+		store_chain_dw(lane_base, t, A, dst);
+		if (NERF) store_chain_dw(lane_base, t, B, dst + chain_params(net.a_in, net.a_hidden));
+	}
+	tc_fence_before();
+	__syncthreads();
+	if (is_mma_warp) tmem_dealloc<512>(tmem);
+}
+
+// Deterministic sum of the per-CTA partials -> fp16 gradients.
+__global__ void fused_reduce_dw_kernel(uint32_t n_params, uint32_t n_parts, const float* __restrict__ partials, __half* __restrict__ grad) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_params) return;
+	float s = 0.0f;
+	for (uint32_t p = 0; p < n_parts; ++p) s += partials[(size_t)p * n_params + i];
+	grad[i] = __float2half(s);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+uint32_t fused_grid_train_ctas(const FusedNet& net, uint32_t n) {
+	const uint32_t G = std::max(1u, pick_groups(net, true));
+	return std::max(1u, std::min((uint32_t)sm_count(), div_round_up(div_round_up(n, kTile), G)));
+}
+
+template <bool TRAIN>
+static void launch(cudaStream_t stream, const FusedGridNetArgs& a) {
+	if (a.n == 0) return;
+	if (a.n % kTile != 0) throw std::runtime_error{"ngp-b200 fused MLP: batch size must be a multiple of 128"};
+	const uint32_t G = pick_groups(a.net, TRAIN);
+	if (G == 0 || !fused_grid_supported(a.net, a.grid)) throw std::runtime_error{"ngp-b200 fused encoder + MLP: unsupported shape"};
+	const FusedLayout lay = make_layout(a.net, TRAIN, G);
+	const uint32_t n_tiles = a.n / kTile;
+	const uint32_t grid = TRAIN ? fused_grid_train_ctas(a.net, a.n) : std::max(1u, std::min((uint32_t)sm_count(), div_round_up(n_tiles, G)));
+	const uint32_t threads = 128 * G + 32;
+#define NGPB_FUSED_LAUNCH(D_, F_, NERF_) \
+	do { \
+		auto k = fused_grid_net_kernel<D_, F_, NERF_, TRAIN>; \
+		NGPB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lay.total)); \
+		NGPB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); \
+		k<<<grid, threads, lay.total, stream>>>(a.net, a.grid, lay, a.n, a.n_dev, a.params, a.grid_params, a.input, a.in_stride, \
+			a.out, a.out_stride, a.dL_dout, a.dy_stride, a.grid_grad, a.dw_partials); \
+	} while (0)
+	const uint32_t D = a.grid.n_dims, F = a.grid.n_features_per_level;
+	if (D == 3 && F == 4) { if (a.net.nerf) NGPB_FUSED_LAUNCH(3, 4, true); else NGPB_FUSED_LAUNCH(3, 4, false); }
+	else if (D == 3 && F == 2) { if (a.net.nerf) NGPB_FUSED_LAUNCH(3, 2, true); else NGPB_FUSED_LAUNCH(3, 2, false); }
+	else if (D == 2 && F == 2 && !a.net.nerf) NGPB_FUSED_LAUNCH(2, 2, false);
+	else throw std::runtime_error{"ngp-b200 fused encoder + MLP: unsupported shape"};
+#undef NGPB_FUSED_LAUNCH
+	NGPB_CUDA_CHECK(cudaGetLastError());
+	if (TRAIN) {
+		const uint32_t n_w = fused_net_mlp_params(a.net);
+		fused_reduce_dw_kernel<<<div_round_up(n_w, 256), 256, 0, stream>>>(n_w, grid, a.dw_partials, a.dL_dparams);
+		NGPB_CUDA_CHECK(cudaGetLastError());
+	}
+}
+
+void fused_grid_inference(cudaStream_t stream, const FusedGridNetArgs& a) { launch<false>(stream, a); }
+void fused_grid_train(cudaStream_t stream, const FusedGridNetArgs& a) { launch<true>(stream, a); }
+
+} // namespace ngpb

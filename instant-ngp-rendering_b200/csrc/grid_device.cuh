@@ -192,4 +192,78 @@ NGPB_D void grid_scatter_entry(__half* level_grad, uint32_t idx, float weight, c
 	}
 }
 
+// Gradient scatter of one 16-byte chunk of dL/dy (levels l0 .. l0 + 8/F - 1) of one sample, warp-aggregated:
+// lanes of a warp whose samples fall into the same cell of a level (runs of consecutive lanes: NeRF batches are
+// ray-ordered) are found with one ballot, their contributions summed in fp32 by a segmented shuffle reduction,
+// and the run's first lane issues one red.global.add.f16x2 per entry. Must be called by all 32 lanes.
+// Each contribution is half(w) * half(dy) rounded to fp16 as in the reference (grid.h:302-311).
+template <uint32_t D, uint32_t F>
+NGPB_D void grid_scatter_chunk(const GridParams& p, uint32_t l0, const float (&x)[D], const __half* g, __half* __restrict__ grad,
+	float max_level, bool active, uint32_t lane)
+{
+	constexpr uint32_t C = 8 / F;
+	constexpr uint32_t NC = 1u << D;
+	constexpr bool kAggregate = NC * F <= 32 && F >= 2;
+	const uint32_t L = p.n_levels;
+#pragma unroll
+	for (uint32_t c = 0; c < C; ++c) {
+		const uint32_t level = l0 + c;
+		if (level >= L || grid_level_masked_bwd(p, level, max_level)) continue; // warp-uniform
+		GridCellT<D> cell;
+		grid_cell<D>(p, level, x, cell);
+		__half* level_grad = grad + (size_t)p.offset[level] * F;
+		if (p.interpolation_type == (int)InterpolationType::Nearest) {
+			if (active) grid_scatter_entry<F>(level_grad, grid_corner_index<D>(p, level, cell, 0), 1.0f, &g[c * F]);
+			continue;
+		}
+		if constexpr (kAggregate) {
+			// runs of equal cells among consecutive lanes
+			bool same = lane != 0;
+#pragma unroll
+			for (uint32_t d = 0; d < D; ++d) same = (__shfl_up_sync(0xFFFFFFFFu, cell.lo[d], 1) == cell.lo[d]) && same;
+			const bool prev_active = __shfl_up_sync(0xFFFFFFFFu, (int)active, 1) != 0;
+			const uint32_t heads = __ballot_sync(0xFFFFFFFFu, !(same && active && prev_active));
+			if (heads != 0xFFFFFFFFu) {
+				// lane takes the partial sum of lane + o while no run starts in (lane, lane + o]
+				const uint32_t later_heads = lane == 31 ? 0xFFFFFFFFu : (heads >> (lane + 1));
+				const __half2* g2 = reinterpret_cast<const __half2*>(&g[c * F]);
+				float2 acc[NC][F / 2];
+#pragma unroll
+				for (uint32_t k = 0; k < NC; ++k) {
+					const __half2 w = __float2half2_rn(active ? grid_corner_weight<D>(cell, k) : 0.0f);
+#pragma unroll
+					for (uint32_t f = 0; f < F / 2; ++f) acc[k][f] = __half22float2(__hmul2(w, g2[f]));
+				}
+#pragma unroll
+				for (uint32_t o = 1; o < 32; o <<= 1) {
+					const bool take = lane + o < 32 && (later_heads & ((1u << o) - 1u)) == 0;
+#pragma unroll
+					for (uint32_t k = 0; k < NC; ++k) {
+#pragma unroll
+						for (uint32_t f = 0; f < F / 2; ++f) {
+							const float tx = __shfl_down_sync(0xFFFFFFFFu, acc[k][f].x, o), ty = __shfl_down_sync(0xFFFFFFFFu, acc[k][f].y, o);
+							if (take) { acc[k][f].x += tx; acc[k][f].y += ty; }
+						}
+					}
+				}
+				if (active && ((heads >> lane) & 1u)) {
+#pragma unroll
+					for (uint32_t k = 0; k < NC; ++k) {
+						__half* addr = level_grad + (size_t)grid_corner_index<D>(p, level, cell, k) * F;
+						if constexpr (F == 2) red_add_half2(addr, __float22half2_rn(acc[k][0]));
+						else if constexpr (F == 4) red_add_half2x2(addr, __float22half2_rn(acc[k][0]), __float22half2_rn(acc[k][1]));
+						else red_add_half2x4(addr, __float22half2_rn(acc[k][0]), __float22half2_rn(acc[k][1]), __float22half2_rn(acc[k][2]), __float22half2_rn(acc[k][3]));
+					}
+				}
+				continue;
+			}
+		}
+		if (!active) continue;
+#pragma unroll
+		for (uint32_t k = 0; k < NC; ++k) {
+			grid_scatter_entry<F>(level_grad, grid_corner_index<D>(p, level, cell, k), grid_corner_weight<D>(cell, k), &g[c * F]);
+		}
+	}
+}
+
 } // namespace ngpb

@@ -1,5 +1,6 @@
 // NetworkWithInputEncoding and NerfNetwork modules (see network.h).
 #include "network.h"
+#include "fused.h"
 
 #include <cmath>
 
@@ -126,6 +127,13 @@ void NetworkWithInputEncodingModule::encode_tiled(cudaStream_t stream, uint32_t 
 void NetworkWithInputEncodingModule::inference(cudaStream_t stream, uint32_t n, const float* input, __half* output, const __half* params) {
 	check_batch(n);
 	if (n == 0) return;
+	if (m_has_grid && fused_grid_supported(m_net, m_grid.p)) {
+		FusedGridNetArgs f{};
+		f.net = m_net; f.grid = m_grid.p; f.n = n; f.params = params; f.grid_params = params + m_mlp.n_params();
+		f.input = input; f.in_stride = m_n_input_dims; f.out = output; f.out_stride = kMlpPaddedOut;
+		fused_grid_inference(stream, f);
+		return;
+	}
 	DeviceBuffer feat{tiled_bytes(n, m_enc_width), stream};
 	encode_tiled(stream, n, input, m_n_input_dims, params, feat.as<__half>());
 	FusedInferenceArgs a{};
@@ -150,6 +158,22 @@ void NetworkWithInputEncodingModule::backward(cudaStream_t stream, const Context
 	check_batch(n);
 	if (n == 0) return;
 	if (dL_dinput && !m_has_grid) throw std::runtime_error{"ngp-b200: input gradients through an Identity-encoded network are not available"};
+	if (m_has_grid && !dL_dinput && fused_grid_supported(m_net, m_grid.p)) {
+		const uint32_t ctas = fused_grid_train_ctas(m_net, n);
+		DeviceBuffer partials{(size_t)ctas * m_mlp.n_params() * sizeof(float), stream};
+		DeviceBuffer dummy_grad{dL_dparams ? 0 : m_mlp.n_params() * sizeof(__half), stream};
+		FusedGridNetArgs f{};
+		f.net = m_net; f.grid = m_grid.p; f.n = n; f.params = params; f.grid_params = params + m_mlp.n_params();
+		f.input = input; f.in_stride = m_n_input_dims; f.dL_dout = dL_doutput; f.dy_stride = kMlpPaddedOut;
+		f.dw_partials = partials.as<float>();
+		f.dL_dparams = dL_dparams ? dL_dparams : dummy_grad.as<__half>();
+		if (dL_dparams) {
+			f.grid_grad = dL_dparams + m_mlp.n_params();
+			NGPB_CUDA_CHECK(cudaMemsetAsync(f.grid_grad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
+		}
+		fused_grid_train(stream, f);
+		return;
+	}
 	const bool need_dfeat = m_has_grid && (dL_dparams || dL_dinput);
 	DeviceBuffer feat{tiled_bytes(n, m_enc_width), stream};
 	DeviceBuffer dfeat{need_dfeat ? tiled_bytes(n, m_enc_width) : 0, stream};
@@ -272,6 +296,13 @@ Json NerfNetworkModule::hyperparams() const {
 void NerfNetworkModule::inference_strided(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params) {
 	if (n == 0) return;
 	if (n % kTile != 0) throw std::runtime_error{"ngp-b200 NerfNetwork: batch size must be a multiple of 128"};
+	if (fused_grid_supported(m_net, m_grid.p)) {
+		FusedGridNetArgs f{};
+		f.net = m_net; f.grid = m_grid.p; f.n = n; f.params = params; f.grid_params = params + pos_encoding_param_offset();
+		f.input = input; f.in_stride = in_stride; f.out = output; f.out_stride = out_stride;
+		fused_grid_inference(stream, f);
+		return;
+	}
 	m_scratch_feat.reserve(tiled_bytes(n, m_pos_width), stream);
 	grid_forward(stream, m_grid.p, n, params + pos_encoding_param_offset(), input, in_stride, m_scratch_feat.as<__half>(), m_pos_width, 1.0f, true);
 	FusedInferenceArgs a{};
@@ -284,6 +315,14 @@ void NerfNetworkModule::inference_strided(cudaStream_t stream, uint32_t n, const
 void NerfNetworkModule::inference_counted(cudaStream_t stream, uint32_t max_n, const uint32_t* n_dev, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params) {
 	if (max_n == 0) return;
 	if (max_n % kTile != 0) throw std::runtime_error{"ngp-b200 NerfNetwork: batch size must be a multiple of 128"};
+	if (fused_grid_supported(m_net, m_grid.p)) {
+		FusedGridNetArgs f{};
+		f.net = m_net; f.grid = m_grid.p; f.n = max_n; f.n_dev = n_dev; f.params = params; f.grid_params = params + pos_encoding_param_offset();
+		f.input = input; f.in_stride = in_stride; f.out = output; f.out_stride = out_stride;
+		prof_mark(stream, "infer.fused_grid_mlp");
+		fused_grid_inference(stream, f);
+		return;
+	}
 	m_scratch_feat.reserve(tiled_bytes(max_n, m_pos_width), stream);
 	prof_mark(stream, "infer.grid_forward");
 	grid_forward(stream, m_grid.p, max_n, params + pos_encoding_param_offset(), input, in_stride, m_scratch_feat.as<__half>(), m_pos_width, 1.0f, true, n_dev);
@@ -298,6 +337,17 @@ void NerfNetworkModule::inference_counted(cudaStream_t stream, uint32_t max_n, c
 void NerfNetworkModule::density(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params) {
 	if (n == 0) return;
 	if (n % kTile != 0) throw std::runtime_error{"ngp-b200 NerfNetwork: batch size must be a multiple of 128"};
+	{
+		FusedNet density_only = m_net;
+		density_only.nerf = 0; // chain A (density network) only
+		if (fused_grid_supported(density_only, m_grid.p)) {
+			FusedGridNetArgs f{};
+			f.net = density_only; f.grid = m_grid.p; f.n = n; f.params = params; f.grid_params = params + pos_encoding_param_offset();
+			f.input = input; f.in_stride = in_stride; f.out = output; f.out_stride = out_stride;
+			fused_grid_inference(stream, f);
+			return;
+		}
+	}
 	m_scratch_feat.reserve(tiled_bytes(n, m_pos_width), stream);
 	grid_forward(stream, m_grid.p, n, params + pos_encoding_param_offset(), input, in_stride, m_scratch_feat.as<__half>(), m_pos_width, 1.0f, true);
 	FusedInferenceArgs a{};
@@ -313,6 +363,23 @@ void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const 
 {
 	if (n == 0) return;
 	if (n % kTile != 0) throw std::runtime_error{"ngp-b200 NerfNetwork: batch size must be a multiple of 128"};
+	if (fused_grid_supported(m_net, m_grid.p)) {
+		const uint32_t ctas = fused_grid_train_ctas(m_net, n);
+		m_scratch_dw.reserve((size_t)ctas * n_mlp_params() * sizeof(float), stream);
+		FusedGridNetArgs f{};
+		f.net = m_net; f.grid = m_grid.p; f.n = n; f.params = params; f.grid_params = params + pos_encoding_param_offset();
+		f.input = input; f.in_stride = in_stride; f.dL_dout = dL_doutput; f.dy_stride = dy_stride;
+		f.grid_grad = dL_dparams + pos_encoding_param_offset();
+		f.dw_partials = m_scratch_dw.as<float>();
+		f.dL_dparams = dL_dparams;
+		prof_mark(stream, "train.grid_grad_memset");
+		NGPB_CUDA_CHECK(cudaMemsetAsync(f.grid_grad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
+		prof_mark(stream, "train.fused_grid_mlp_fwd_bwd_scatter");
+		if (before_mlp) NGPB_CUDA_CHECK(cudaEventRecord(before_mlp, stream));
+		fused_grid_train(stream, f);
+		if (after_mlp) NGPB_CUDA_CHECK(cudaEventRecord(after_mlp, stream));
+		return;
+	}
 	const uint32_t grid = fused_train_grid(m_net, n);
 	m_scratch_feat.reserve(tiled_bytes(n, m_pos_width), stream);
 	m_scratch_dfeat.reserve(tiled_bytes(n, m_pos_width), stream);
