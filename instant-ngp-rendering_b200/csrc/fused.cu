@@ -33,17 +33,30 @@ constexpr uint32_t kHiddenBytes = kTile * kMlpWidth * 2;
 struct FusedLayout {
 	uint32_t groups;
 	uint32_t w_a, w_b;            // smem offsets of the chains' weights
+	uint32_t prog, n_ops_max;     // the tile's MMA program (MmaOp table)
 	uint32_t group0, group_stride;
 	uint32_t x0, ha, x1, hb, gy;  // offsets inside a group's region
 	uint32_t total;
 };
+
+// MMAs of one tile (what the kernel's emit_round() produces, summed over the rounds)
+static uint32_t count_ops(const FusedNet& n, bool train) {
+	auto fwd = [](uint32_t in, uint32_t hidden) { return in / 16 + hidden * 4; };              // layer 0, then hidden-1 layers + output layer
+	auto bwd = [](uint32_t hidden) { return (hidden + 1) * 8 + 1 + (hidden - 1) * 4 + 4; };   // dW per layer + input gradients
+	uint32_t c = fwd(n.a_in, n.a_hidden) + (n.nerf ? fwd(n.b_in, n.b_hidden) : 0);
+	if (train) c += bwd(n.a_hidden) + (n.nerf ? bwd(n.b_hidden) : 0);
+	return c;
+}
 
 static FusedLayout make_layout(const FusedNet& n, bool train, uint32_t groups) {
 	FusedLayout l{};
 	uint32_t o = 0;
 	l.w_a = o; o += 2 * chain_params(n.a_in, n.a_hidden);
 	l.w_b = o; if (n.nerf) o += 2 * chain_params(n.b_in, n.b_hidden);
-	o = (o + 1023u) & ~1023u;
+	l.prog = o;
+	l.n_ops_max = count_ops(n, train);
+	o += l.n_ops_max * 32u;
+	o = (o + 127u) & ~127u;
 	l.group0 = o;
 	uint32_t g = 0;
 	l.x0 = g; g += kTile * n.a_in * 2;
@@ -55,7 +68,7 @@ static FusedLayout make_layout(const FusedNet& n, bool train, uint32_t groups) {
 	} else {
 		l.x1 = l.ha; l.hb = l.ha; l.gy = l.ha;
 	}
-	l.group_stride = (g + 1023u) & ~1023u;
+	l.group_stride = (g + 127u) & ~127u;
 	l.groups = groups;
 	l.total = l.group0 + groups * l.group_stride;
 	return l;
@@ -71,7 +84,7 @@ static uint32_t pick_groups(const FusedNet& n, bool train) {
 	static const int forced = getenv("NGPB_FUSED_GROUPS") ? atoi(getenv("NGPB_FUSED_GROUPS")) : 0;
 	uint32_t best = 0;
 	for (uint32_t g = 1; g <= kMaxGroups; ++g) {
-		if (make_layout(n, train, g).total > 227u * 1024u - 256u) break;
+		if (make_layout(n, train, g).total > 227u * 1024u - 512u) break;   // 227 KB per CTA less the kernel's static shared memory
 		if (64 * g + (train ? dw_columns(n) : 0) > 512) break;
 		best = g;
 	}
@@ -119,32 +132,51 @@ NGPB_D uint32_t chain_dw_col(const Chain& ch, uint32_t layer) {
 	return ch.dw_col + (layer == 0 ? 0u : ch.in_width + (layer - 1) * kMlpWidth);
 }
 
-// ---- MMA warp: the batch of one round -----------------------------------------------------------------
-// forward layer j of a chain whose input tile is at smem address x; result in acc[0, 64) (j < n_hidden) or [0, 16)
-NGPB_D void issue_forward(uint32_t acc, const Chain& ch, uint32_t x, uint32_t j) {
-	if (j == 0) mma_xwT(acc, x, chain_w(ch, 0), ch.in_width, kMlpWidth, false);
-	else if (j < ch.n_hidden) mma_xwT(acc, ch.h + (j - 1) * ch.h_stride, chain_w(ch, j), kMlpWidth, kMlpWidth, false);
-	else mma_xwT(acc, ch.h + (ch.n_hidden - 1) * ch.h_stride, chain_w(ch, ch.n_hidden), kMlpWidth, kMlpPaddedOut, false);
-}
-// backward step s (0 = output layer ... n_hidden = first layer): dW of the layer (accumulated over all tiles of the
-// CTA) and the gradient of the layer's input in acc
-NGPB_D void issue_backward(uint32_t tmem, uint32_t acc, const Chain& ch, uint32_t x, uint32_t gy, uint32_t dx_cols, uint32_t s, uint32_t bit_base, uint32_t& dw_mask) {
-	const uint32_t layer = ch.n_hidden - s;
-	const bool accumulate = (dw_mask >> (bit_base + layer)) & 1u;
-	dw_mask |= 1u << (bit_base + layer);
-	const uint32_t dw = tmem + chain_dw_col(ch, layer);
-	if (s == 0) {
-		mma_pTq(dw, ch.h + (ch.n_hidden - 1) * ch.h_stride, gy, kMlpPaddedOut, accumulate);   // dW_out^T = H^T dY
-		mma_dyW(acc, gy, chain_w(ch, ch.n_hidden), kMlpPaddedOut, kMlpWidth);
-	} else if (s < ch.n_hidden) {
-		const uint32_t d = ch.h + layer * ch.h_stride, hprev = ch.h + (layer - 1) * ch.h_stride;
-		mma_pTq(dw, d, hprev, kMlpWidth, accumulate);                                          // dW_j = D^T H_{j-1}
-		mma_dyW(acc, d, chain_w(ch, layer), kMlpWidth, kMlpWidth);
-	} else {
-		mma_pTq(dw, ch.h, x, ch.in_width, accumulate);                                         // dW_0 = D^T X
-		if (dx_cols) mma_dyW(acc, ch.h, chain_w(ch, 0), kMlpWidth, dx_cols);
+// ---- MMA warp: the program of one tile -------------------------------------------------------------------
+// Building descriptors and walking the layer structure costs a few hundred dependent instructions per round; with
+// one thread issuing for every group that latency would sit on the critical path of every layer of every tile
+// (measured: the first version of this kernel, which did exactly that, ran 10 k cycles per round). So the CTA
+// compiles the tile's MMAs ONCE into a table in shared memory - operand descriptors for group 0, with flags that
+// say which fields move with the group - and the MMA thread's inner loop is load, relocate, tcgen05.mma.
+struct alignas(16) MmaOp {
+	uint64_t desc_a, desc_b;
+	uint32_t tmem_d, idesc;
+	uint32_t flags;      // bit 0/1/2: desc_a / desc_b / tmem_d move with the group; bit 3: accumulate; bit 4: accumulate iff
+	                     // the dW accumulator `layer_bit` (bits 8..15) has been written before; bit 5: this op marks it written
+	uint32_t pad;
+};
+constexpr uint32_t kOpARel = 1u, kOpBRel = 2u, kOpDRel = 4u, kOpAcc = 8u, kOpAccIfStarted = 16u, kOpMarksStarted = 32u;
+constexpr uint32_t kMaxRounds = 24;
+
+struct Emitter {
+	MmaOp* ops;
+	uint32_t n;
+	NGPB_D void emit(uint32_t d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t flags) {
+		MmaOp o;
+		o.desc_a = da; o.desc_b = db; o.tmem_d = d; o.idesc = idesc; o.flags = flags; o.pad = 0;
+		if (ops) ops[n] = o;
+		++n;
 	}
-}
+	// D[128 x N] = X[128 x K] W[N x K]^T  (mma_xwT)
+	NGPB_D void xwT(uint32_t acc, uint32_t x, uint32_t w, uint32_t K, uint32_t N) {
+		const uint32_t idesc = instr_desc(128, N, false, false);
+		for (uint32_t k = 0; k < K / 16; ++k)
+			emit(acc, smem_desc(x + 2 * k * (kTileRows * 16), kTileRows * 16, 128), smem_desc(w + 2 * k * (N * 16), N * 16, 128), idesc, kOpARel | kOpDRel | (k ? kOpAcc : 0u));
+	}
+	// D[128 x Kin] = dY[128 x Nout] W[Nout x Kin]  (mma_dyW)
+	NGPB_D void dyW(uint32_t acc, uint32_t dy, uint32_t w, uint32_t Nout, uint32_t Kin) {
+		const uint32_t idesc = instr_desc(128, Kin, false, true);
+		for (uint32_t k = 0; k < Nout / 16; ++k)
+			emit(acc, smem_desc(dy + 2 * k * (kTileRows * 16), kTileRows * 16, 128), smem_desc(w + 16 * k * 16, 128, Nout * 16), idesc, kOpARel | kOpDRel | (k ? kOpAcc : 0u));
+	}
+	// D[64 x Nf] (+)= P[128 x 64]^T Q[128 x Nf]  (mma_pTq), accumulated over every tile of the CTA
+	NGPB_D void pTq(uint32_t dw, uint32_t p, uint32_t q, uint32_t Nf, uint32_t layer_bit) {
+		const uint32_t idesc = instr_desc(64, Nf, true, true);
+		for (uint32_t k = 0; k < kTileRows / 16; ++k)
+			emit(dw, smem_desc(p + 16 * k * 16, 128, kTileRows * 16), smem_desc(q + 16 * k * 16, 128, kTileRows * 16), idesc,
+				kOpARel | kOpBRel | (layer_bit << 8) | (k ? kOpAcc : (kOpAccIfStarted | kOpMarksStarted)));
+	}
+};
 
 // ---- worker side ----------------------------------------------------------------------------------------
 struct Worker {
@@ -158,7 +190,8 @@ struct Worker {
 NGPB_D void grp_round(Worker& w) {
 	fence_proxy_async();
 	tc_fence_before();
-	mbar_arrive(w.ready);
+	__syncwarp();
+	if ((w.row & 31u) == 0) mbar_arrive(w.ready);   // one arrival per warp (128 serialised arrivals cost ~400 cycles a round)
 	mbar_wait(w.done, w.phase);
 	w.phase ^= 1;
 	tc_fence_after();
@@ -259,10 +292,11 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 	const __half* __restrict__ dL_dout, const uint32_t dy_stride,
 	__half* __restrict__ grid_grad, float* __restrict__ dw_partials)
 {
-	extern __shared__ __align__(1024) uint8_t smem[];
+	extern __shared__ __align__(128) uint8_t smem[];   // SWIZZLE_NONE operands need 16-byte alignment only
 	__shared__ uint64_t bar_ready[kMaxGroups];
 	__shared__ uint64_t bar_done[kMaxGroups];
 	__shared__ uint32_t tmem_slot;
+	__shared__ uint32_t round_begin[kMaxRounds + 1];
 
 	const uint32_t G = lay.groups;
 	const uint32_t t = threadIdx.x, warp = t / 32, lane = t % 32;
@@ -271,30 +305,22 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 	const uint32_t n_tiles = (n + kTile - 1) / kTile;
 	const uint32_t tile_stride = gridDim.x * G;
 
-	// weights: every thread helps
-	for (uint32_t pass = 0; pass < (NERF ? 2u : 1u); ++pass) {
-		uint8_t* dst = smem + (pass ? lay.w_b : lay.w_a);
-		const __half* src = params + (pass ? net.b_param_off : net.a_param_off);
-		const uint32_t in_w = pass ? net.b_in : net.a_in, n_hidden = pass ? net.b_hidden : net.a_hidden;
-		load_chain_weights(dst, src, in_w, n_hidden);
-	}
 	if (is_mma_warp) tmem_alloc<512>(&tmem_slot);
 	if (t == 0) {
 		for (uint32_t g = 0; g < kMaxGroups; ++g) {
-			mbar_init(&bar_ready[g], 128);
+			mbar_init(&bar_ready[g], 4);
 			mbar_init(&bar_done[g], 1);
 		}
 		fence_barrier_init();
 	}
-	fence_proxy_async();
-	tc_fence_before();
-	__syncthreads();
-	tc_fence_after();
 
-	const uint32_t tmem = tmem_slot;
 	const uint32_t sbase = smem_u32(smem);
 	const uint32_t dw_base_col = 64 * G;
+	const uint32_t RA = net.a_hidden + 1, RB = NERF ? net.b_hidden + 1 : 0;
+	const uint32_t rounds_per_tile = TRAIN ? 2 * (RA + RB) : RA + RB;
+	const bool want_dx = TRAIN && grid_grad != nullptr;
 
+	// Chains with group g's buffers. TMEM addresses are relative to the allocation (column 0).
 	auto make_chains = [&](uint32_t g, Chain& A, Chain& B) {
 		const uint32_t off = lay.group0 + g * lay.group_stride;
 		A.in_width = net.a_in; A.n_hidden = net.a_hidden; A.relu = net.a_relu;
@@ -309,9 +335,73 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 		}
 	};
 
-	const uint32_t RA = net.a_hidden + 1, RB = NERF ? net.b_hidden + 1 : 0;
-	const uint32_t rounds_per_tile = TRAIN ? 2 * (RA + RB) : RA + RB;
-	const bool want_dx = TRAIN && grid_grad != nullptr;
+	// The MMAs of round r of a tile, for group 0 with TMEM column 0 as the allocation base (relocated at issue time).
+	auto emit_round = [&](Emitter& em, uint32_t r) {
+		Chain A, B;
+		make_chains(0, A, B);
+		const uint32_t off = sbase + lay.group0;
+		const uint32_t x0 = off + lay.x0, x1 = off + lay.x1, gy = off + lay.gy;
+		auto forward = [&](const Chain& ch, uint32_t x, uint32_t j) {
+			if (j == 0) em.xwT(0, x, chain_w(ch, 0), ch.in_width, kMlpWidth);
+			else if (j < ch.n_hidden) em.xwT(0, ch.h + (j - 1) * ch.h_stride, chain_w(ch, j), kMlpWidth, kMlpWidth);
+			else em.xwT(0, ch.h + (ch.n_hidden - 1) * ch.h_stride, chain_w(ch, ch.n_hidden), kMlpWidth, kMlpPaddedOut);
+		};
+		// backward step s (0 = output layer ... n_hidden = first layer): dW of the layer, then the gradient of its input
+		auto backward = [&](const Chain& ch, uint32_t x, uint32_t g_seed, uint32_t dx_cols, uint32_t s, uint32_t bit_base) {
+			const uint32_t layer = ch.n_hidden - s;
+			const uint32_t dw = chain_dw_col(ch, layer);
+			if (s == 0) {
+				em.pTq(dw, ch.h + (ch.n_hidden - 1) * ch.h_stride, g_seed, kMlpPaddedOut, bit_base + layer);   // dW_out^T = H^T dY
+				em.dyW(0, g_seed, chain_w(ch, ch.n_hidden), kMlpPaddedOut, kMlpWidth);
+			} else if (s < ch.n_hidden) {
+				const uint32_t d = ch.h + layer * ch.h_stride, hprev = ch.h + (layer - 1) * ch.h_stride;
+				em.pTq(dw, d, hprev, kMlpWidth, bit_base + layer);                                           // dW_j = D^T H_{j-1}
+				em.dyW(0, d, chain_w(ch, layer), kMlpWidth, kMlpWidth);
+			} else {
+				em.pTq(dw, ch.h, x, ch.in_width, bit_base + layer);                                          // dW_0 = D^T X
+				if (dx_cols) em.dyW(0, ch.h, chain_w(ch, 0), kMlpWidth, dx_cols);
+			}
+		};
+		if (r < RA) forward(A, x0, r);
+		else if (r < RA + RB) forward(B, x1, r - RA);
+		else {
+			r -= RA + RB;
+			if (NERF) {
+				if (r < RB) backward(B, x1, gy, 16, r, RA);
+				else backward(A, x0, x1, want_dx ? net.a_in : 0, r - RB, 0);
+			} else {
+				backward(A, x0, gy, want_dx ? net.a_in : 0, r, 0);
+			}
+		}
+	};
+
+	MmaOp* ops = reinterpret_cast<MmaOp*>(smem + lay.prog);
+	if (t < rounds_per_tile) {
+		// thread r compiles round r: its first op index is the op count of the rounds before it (dry runs)
+		uint32_t begin = 0;
+		for (uint32_t r = 0; r < t; ++r) {
+			Emitter dry{nullptr, 0};
+			emit_round(dry, r);
+			begin += dry.n;
+		}
+		Emitter em{ops + begin, 0};
+		emit_round(em, t);
+		round_begin[t] = begin;
+		if (t + 1 == rounds_per_tile) round_begin[t + 1] = begin + em.n;
+	}
+	// weights: every thread helps
+	for (uint32_t pass = 0; pass < (NERF ? 2u : 1u); ++pass) {
+		uint8_t* dst = smem + (pass ? lay.w_b : lay.w_a);
+		const __half* src = params + (pass ? net.b_param_off : net.a_param_off);
+		const uint32_t in_w = pass ? net.b_in : net.a_in, n_hidden = pass ? net.b_hidden : net.a_hidden;
+		load_chain_weights(dst, src, in_w, n_hidden);
+	}
+	fence_proxy_async();
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+
+	const uint32_t tmem = tmem_slot;
 
 	if (is_mma_warp) {
 		if (lane == 0) {
@@ -333,22 +423,21 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 					any = true;
 					parity[g] ^= 1;
 					tc_fence_after();
-					Chain A, B;
-					make_chains(g, A, B);
-					const uint32_t off = sbase + lay.group0 + g * lay.group_stride;
-					const uint32_t x0 = off + lay.x0, x1 = off + lay.x1, gy = off + lay.gy;
+					const uint64_t smem_rel = (uint64_t)((g * lay.group_stride) >> 4);   // start-address field of a descriptor
 					const uint32_t acc = tmem + 64 * g;
-					uint32_t r = round[g];
-					if (r < RA) issue_forward(acc, A, x0, r);
-					else if (r < RA + RB) issue_forward(acc, B, x1, r - RA);
-					else {
-						r -= RA + RB;
-						if (NERF) {
-							if (r < RB) issue_backward(tmem, acc, B, x1, gy, 16, r, RA, dw_mask);
-							else issue_backward(tmem, acc, A, x0, x1, want_dx ? net.a_in : 0, r - RB, 0, dw_mask);
-						} else {
-							issue_backward(tmem, acc, A, x0, gy, want_dx ? net.a_in : 0, r, 0, dw_mask);
-						}
+					const uint32_t e1 = round_begin[round[g] + 1];
+					for (uint32_t e = round_begin[round[g]]; e < e1; ++e) {
+						const uint4 lo = *reinterpret_cast<const uint4*>(&ops[e]);
+						const uint4 hi = *(reinterpret_cast<const uint4*>(&ops[e]) + 1);
+						const uint32_t flags = hi.z;
+						uint64_t da = (uint64_t)lo.x | ((uint64_t)lo.y << 32), db = (uint64_t)lo.z | ((uint64_t)lo.w << 32);
+						if (flags & kOpARel) da += smem_rel;
+						if (flags & kOpBRel) db += smem_rel;
+						const uint32_t d = (flags & kOpDRel) ? acc + hi.x : tmem + hi.x;
+						const uint32_t bit = (flags >> 8) & 0xFFu;
+						const bool accumulate = (flags & kOpAcc) || ((flags & kOpAccIfStarted) && ((dw_mask >> bit) & 1u));
+						if (flags & kOpMarksStarted) dw_mask |= 1u << bit;
+						umma_f16(d, da, db, hi.y, accumulate);
 					}
 					umma_commit(&bar_done[g]);
 					if (++round[g] == rounds_per_tile) {
@@ -357,7 +446,7 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 						if (tile[g] >= n_tiles) live &= ~(1u << g);
 					}
 				}
-				if (!any) __nanosleep(32);
+				if (!any) __nanosleep(20);
 			}
 		}
 		__syncwarp();
