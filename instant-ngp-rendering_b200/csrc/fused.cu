@@ -290,7 +290,8 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 	const float* __restrict__ input, const uint32_t in_stride,
 	__half* __restrict__ out, const uint32_t out_stride,
 	const __half* __restrict__ dL_dout, const uint32_t dy_stride,
-	__half* __restrict__ grid_grad, float* __restrict__ dw_partials)
+	__half* __restrict__ grid_grad, float* __restrict__ dw_partials,
+	const __half* __restrict__ feat_tiles, __half* __restrict__ dfeat_tiles)
 {
 	extern __shared__ __align__(128) uint8_t smem[];   // SWIZZLE_NONE operands need 16-byte alignment only
 	__shared__ uint64_t bar_ready[kMaxGroups];
@@ -318,7 +319,7 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 	const uint32_t dw_base_col = 64 * G;
 	const uint32_t RA = net.a_hidden + 1, RB = NERF ? net.b_hidden + 1 : 0;
 	const uint32_t rounds_per_tile = TRAIN ? 2 * (RA + RB) : RA + RB;
-	const bool want_dx = TRAIN && grid_grad != nullptr;
+	const bool want_dx = TRAIN && (grid_grad != nullptr || dfeat_tiles != nullptr);
 
 	// Chains with group g's buffers. TMEM addresses are relative to the allocation (column 0).
 	auto make_chains = [&](uint32_t g, Chain& A, Chain& B) {
@@ -419,25 +420,38 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 #pragma unroll
 				for (uint32_t g = 0; g < kMaxGroups; ++g) {
 					if (!((live >> g) & 1u)) continue;
-					if (!mbar_test(&bar_ready[g], parity[g])) continue;
+					// Training serves the groups in a fixed cyclic order: the weight-gradient accumulators are shared, and a
+					// fixed order of accumulation makes dW bit-reproducible run to run. Inference serves whoever is ready.
+					if (TRAIN) mbar_wait(&bar_ready[g], parity[g]);
+					else if (!mbar_test(&bar_ready[g], parity[g])) continue;
 					any = true;
 					parity[g] ^= 1;
 					tc_fence_after();
 					const uint64_t smem_rel = (uint64_t)((g * lay.group_stride) >> 4);   // start-address field of a descriptor
 					const uint32_t acc = tmem + 64 * g;
 					const uint32_t e1 = round_begin[round[g] + 1];
-					for (uint32_t e = round_begin[round[g]]; e < e1; ++e) {
-						const uint4 lo = *reinterpret_cast<const uint4*>(&ops[e]);
-						const uint4 hi = *(reinterpret_cast<const uint4*>(&ops[e]) + 1);
-						const uint32_t flags = hi.z;
-						uint64_t da = (uint64_t)lo.x | ((uint64_t)lo.y << 32), db = (uint64_t)lo.z | ((uint64_t)lo.w << 32);
-						if (flags & kOpARel) da += smem_rel;
-						if (flags & kOpBRel) db += smem_rel;
-						const uint32_t d = (flags & kOpDRel) ? acc + hi.x : tmem + hi.x;
-						const uint32_t bit = (flags >> 8) & 0xFFu;
-						const bool accumulate = (flags & kOpAcc) || ((flags & kOpAccIfStarted) && ((dw_mask >> bit) & 1u));
-						if (flags & kOpMarksStarted) dw_mask |= 1u << bit;
-						umma_f16(d, da, db, hi.y, accumulate);
+					for (uint32_t e = round_begin[round[g]]; e < e1; e += 4) {
+						// four table entries per trip: the loads are issued together, so their latency is paid once
+						uint4 lo[4], hi[4];
+#pragma unroll
+						for (uint32_t u = 0; u < 4; ++u) {
+							const uint32_t eu = min(e + u, e1 - 1);
+							lo[u] = *reinterpret_cast<const uint4*>(&ops[eu]);
+							hi[u] = *(reinterpret_cast<const uint4*>(&ops[eu]) + 1);
+						}
+#pragma unroll
+						for (uint32_t u = 0; u < 4; ++u) {
+							if (e + u >= e1) break;
+							const uint32_t flags = hi[u].z;
+							uint64_t da = (uint64_t)lo[u].x | ((uint64_t)lo[u].y << 32), db = (uint64_t)lo[u].z | ((uint64_t)lo[u].w << 32);
+							if (flags & kOpARel) da += smem_rel;
+							if (flags & kOpBRel) db += smem_rel;
+							const uint32_t d = (flags & kOpDRel) ? acc + hi[u].x : tmem + hi[u].x;
+							const uint32_t bit = (flags >> 8) & 0xFFu;
+							const bool accumulate = (flags & kOpAcc) || ((flags & kOpAccIfStarted) && ((dw_mask >> bit) & 1u));
+							if (flags & kOpMarksStarted) dw_mask |= 1u << bit;
+							umma_f16(d, da, db, hi[u].y, accumulate);
+						}
 					}
 					umma_commit(&bar_done[g]);
 					if (++round[g] == rounds_per_tile) {
@@ -477,22 +491,34 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 #pragma unroll
 			for (uint32_t d = 0; d < D; ++d) x[d] = valid ? __ldg(in_row + d) : 0.0f;
 
-			// ---- gather: the tile's encoded features, straight into the first UMMA operand ----
-#pragma unroll 2
-			for (uint32_t ch = 0; ch < n_feat_chunks; ++ch) {
-				alignas(16) __half vals[8];
-				if (valid) {
+			if (feat_tiles) {
+				// ---- tile-fed: the features were gathered by grid_forward_kernel at full occupancy into the tiled
+				// layout, which is this buffer's image: one coalesced 16-byte load per chunk ----
+				const uint4* src = reinterpret_cast<const uint4*>(feat_tiles) + (size_t)tile * (net.a_in / 8) * kTile + row;
+				uint4 q[8];
 #pragma unroll
-					for (uint32_t c = 0; c < C; ++c) grid_encode_level<D, F>(gp, ch * C + c, x, table, &vals[c * F]);
-				} else {
-					*reinterpret_cast<uint4*>(vals) = make_uint4(0u, 0u, 0u, 0u);
+				for (uint32_t ch = 0; ch < 8; ++ch) if (ch < net.a_in / 8) q[ch] = __ldg(src + ch * kTile);
+#pragma unroll
+				for (uint32_t ch = 0; ch < 8; ++ch) if (ch < net.a_in / 8) *reinterpret_cast<uint4*>(x0 + chunk_offset(kTile, row, ch)) = q[ch];
+			} else {
+				// ---- gather: the tile's encoded features, straight into the first UMMA operand ----
+#pragma unroll 2
+				for (uint32_t ch = 0; ch < n_feat_chunks; ++ch) {
+					alignas(16) __half vals[8];
+					if (valid) {
+#pragma unroll
+						for (uint32_t c = 0; c < C; ++c) grid_encode_level<D, F>(gp, ch * C + c, x, table, &vals[c * F]);
+					} else {
+						*reinterpret_cast<uint4*>(vals) = make_uint4(0u, 0u, 0u, 0u);
+					}
+					*reinterpret_cast<uint4*>(x0 + chunk_offset(kTile, row, ch)) = *reinterpret_cast<const uint4*>(vals);
 				}
-				*reinterpret_cast<uint4*>(x0 + chunk_offset(kTile, row, ch)) = *reinterpret_cast<const uint4*>(vals);
-			}
-			for (uint32_t ch = n_feat_chunks; ch < net.a_in / 8; ++ch) {
-				// padding columns carry 1 (tcnn Encoding padding, grid.h:806-811)
-				const uint32_t one2 = valid ? 0x3C003C00u : 0u;
-				*reinterpret_cast<uint4*>(x0 + chunk_offset(kTile, row, ch)) = make_uint4(one2, one2, one2, one2);
+				for (uint32_t ch = n_feat_chunks; ch < net.a_in / 8; ++ch) {
+					// padding columns carry 1 (tcnn Encoding padding, grid.h:806-811)
+					const uint32_t one2 = valid ? 0x3C003C00u : 0u;
+					*reinterpret_cast<uint4*>(x0 + chunk_offset(kTile, row, ch)) = make_uint4(one2, one2, one2, one2);
+				}
+
 			}
 
 			// ---- forward ----
@@ -571,8 +597,19 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 				worker_backward(w, A);
 			}
 
-			// ---- scatter: this row's dL/d(features) from TMEM into the gradient table ----
-			if (want_dx) {
+			// ---- dL/d(features): tiled to global memory for grid_backward_kernel, or scattered from here ----
+			if (dfeat_tiles) {
+				uint4* dst = reinterpret_cast<uint4*>(dfeat_tiles) + (size_t)tile * (net.a_in / 8) * kTile + row;
+				for (uint32_t c0 = 0; c0 < net.a_in; c0 += 16) {
+					tmem_ld16(w.tmem_row + c0, v);
+					tmem_wait_ld();
+					uint32_t h[8];
+#pragma unroll
+					for (uint32_t k = 0; k < 8; ++k) h[k] = pack2(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1]));
+					dst[(c0 / 8) * kTile] = make_uint4(h[0], h[1], h[2], h[3]);
+					dst[(c0 / 8 + 1) * kTile] = make_uint4(h[4], h[5], h[6], h[7]);
+				}
+			} else if (grid_grad) {
 				for (uint32_t c0 = 0; c0 < L * F; c0 += 16) {
 					tmem_ld16(w.tmem_row + c0, v);
 					tmem_wait_ld();
@@ -612,6 +649,11 @@ __global__ void fused_reduce_dw_kernel(uint32_t n_params, uint32_t n_parts, cons
 	grad[i] = __float2half(s);
 }
 
+bool fused_grid_gather_in_kernel() {
+	static const bool in_kernel = getenv("NGPB_FUSED_GATHER") && atoi(getenv("NGPB_FUSED_GATHER")) != 0;
+	return in_kernel;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 uint32_t fused_grid_train_ctas(const FusedNet& net, uint32_t n) {
 	const uint32_t G = std::max(1u, pick_groups(net, true));
@@ -634,7 +676,7 @@ static void launch(cudaStream_t stream, const FusedGridNetArgs& a) {
 		NGPB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lay.total)); \
 		NGPB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); \
 		k<<<grid, threads, lay.total, stream>>>(a.net, a.grid, lay, a.n, a.n_dev, a.params, a.grid_params, a.input, a.in_stride, \
-			a.out, a.out_stride, a.dL_dout, a.dy_stride, a.grid_grad, a.dw_partials); \
+			a.out, a.out_stride, a.dL_dout, a.dy_stride, a.grid_grad, a.dw_partials, a.feat_tiles, a.dfeat_tiles); \
 	} while (0)
 	const uint32_t D = a.grid.n_dims, F = a.grid.n_features_per_level;
 	if (D == 3 && F == 4) { if (a.net.nerf) NGPB_FUSED_LAUNCH(3, 4, true); else NGPB_FUSED_LAUNCH(3, 4, false); }

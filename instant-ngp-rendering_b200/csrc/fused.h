@@ -33,6 +33,12 @@ struct FusedGridNetArgs {
 	__half* grid_grad;          // gradient table, zeroed by the caller; null: no scatter
 	float* dw_partials;         // [fused_grid_train_ctas()][mlp params] fp32 scratch
 	__half* dL_dparams;         // MLP part of the gradients, overwritten
+	// Tile-fed mode: chain-A input tiles made by grid_forward(..., tiled = true) instead of the in-kernel gather,
+	// and (training) dL/d(chain-A input) written as tiles for grid_backward(..., tiled = true) instead of the
+	// in-kernel scatter. The gather and the scatter are L2-latency kernels that want 2048 threads per SM; this
+	// kernel keeps 544.
+	const __half* feat_tiles;
+	__half* dfeat_tiles;
 };
 
 // Whether (net, grid) is one of the shapes the fused kernels are built for; otherwise the callers use the
@@ -41,5 +47,7 @@ bool fused_grid_supported(const FusedNet& net, const GridParams& grid);
 void fused_grid_inference(cudaStream_t stream, const FusedGridNetArgs& args);
 void fused_grid_train(cudaStream_t stream, const FusedGridNetArgs& args);
 uint32_t fused_grid_train_ctas(const FusedNet& net, uint32_t n);
+// Default: tile-fed (gather / scatter in their own full-occupancy kernels). NGPB_FUSED_GATHER=1: in-kernel.
+bool fused_grid_gather_in_kernel();
 
 } // namespace ngpb

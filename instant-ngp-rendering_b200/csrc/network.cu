@@ -131,6 +131,11 @@ void NetworkWithInputEncodingModule::inference(cudaStream_t stream, uint32_t n, 
 		FusedGridNetArgs f{};
 		f.net = m_net; f.grid = m_grid.p; f.n = n; f.params = params; f.grid_params = params + m_mlp.n_params();
 		f.input = input; f.in_stride = m_n_input_dims; f.out = output; f.out_stride = kMlpPaddedOut;
+		DeviceBuffer tiles{fused_grid_gather_in_kernel() ? 0 : tiled_bytes(n, m_enc_width), stream};
+		if (!fused_grid_gather_in_kernel()) {
+			encode_tiled(stream, n, input, m_n_input_dims, params, tiles.as<__half>());
+			f.feat_tiles = tiles.as<__half>();
+		}
 		fused_grid_inference(stream, f);
 		return;
 	}
@@ -167,11 +172,20 @@ void NetworkWithInputEncodingModule::backward(cudaStream_t stream, const Context
 		f.input = input; f.in_stride = m_n_input_dims; f.dL_dout = dL_doutput; f.dy_stride = kMlpPaddedOut;
 		f.dw_partials = partials.as<float>();
 		f.dL_dparams = dL_dparams ? dL_dparams : dummy_grad.as<__half>();
-		if (dL_dparams) {
-			f.grid_grad = dL_dparams + m_mlp.n_params();
-			NGPB_CUDA_CHECK(cudaMemsetAsync(f.grid_grad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
+		__half* ggrad = dL_dparams ? dL_dparams + m_mlp.n_params() : nullptr;
+		if (ggrad) NGPB_CUDA_CHECK(cudaMemsetAsync(ggrad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
+		const bool tiles = !fused_grid_gather_in_kernel();
+		DeviceBuffer feat{tiles ? tiled_bytes(n, m_enc_width) : 0, stream};
+		DeviceBuffer dfeat{tiles && ggrad ? tiled_bytes(n, m_enc_width) : 0, stream};
+		if (tiles) {
+			encode_tiled(stream, n, input, m_n_input_dims, params, feat.as<__half>());
+			f.feat_tiles = feat.as<__half>();
+			f.dfeat_tiles = ggrad ? dfeat.as<__half>() : nullptr;
+		} else {
+			f.grid_grad = ggrad;
 		}
 		fused_grid_train(stream, f);
+		if (tiles && ggrad) grid_backward(stream, m_grid.p, n, ggrad, input, m_n_input_dims, dfeat.as<__half>(), m_enc_width, 1.0f, true);
 		return;
 	}
 	const bool need_dfeat = m_has_grid && (dL_dparams || dL_dinput);
@@ -300,6 +314,11 @@ void NerfNetworkModule::inference_strided(cudaStream_t stream, uint32_t n, const
 		FusedGridNetArgs f{};
 		f.net = m_net; f.grid = m_grid.p; f.n = n; f.params = params; f.grid_params = params + pos_encoding_param_offset();
 		f.input = input; f.in_stride = in_stride; f.out = output; f.out_stride = out_stride;
+		if (!fused_grid_gather_in_kernel()) {
+			m_scratch_feat.reserve(tiled_bytes(n, m_pos_width), stream);
+			grid_forward(stream, m_grid.p, n, f.grid_params, input, in_stride, m_scratch_feat.as<__half>(), m_pos_width, 1.0f, true);
+			f.feat_tiles = m_scratch_feat.as<__half>();
+		}
 		fused_grid_inference(stream, f);
 		return;
 	}
@@ -319,7 +338,13 @@ void NerfNetworkModule::inference_counted(cudaStream_t stream, uint32_t max_n, c
 		FusedGridNetArgs f{};
 		f.net = m_net; f.grid = m_grid.p; f.n = max_n; f.n_dev = n_dev; f.params = params; f.grid_params = params + pos_encoding_param_offset();
 		f.input = input; f.in_stride = in_stride; f.out = output; f.out_stride = out_stride;
-		prof_mark(stream, "infer.fused_grid_mlp");
+		if (!fused_grid_gather_in_kernel()) {
+			m_scratch_feat.reserve(tiled_bytes(max_n, m_pos_width), stream);
+			prof_mark(stream, "infer.grid_forward");
+			grid_forward(stream, m_grid.p, max_n, f.grid_params, input, in_stride, m_scratch_feat.as<__half>(), m_pos_width, 1.0f, true, n_dev);
+			f.feat_tiles = m_scratch_feat.as<__half>();
+		}
+		prof_mark(stream, fused_grid_gather_in_kernel() ? "infer.fused_grid_mlp" : "infer.fused_mlp");
 		fused_grid_inference(stream, f);
 		return;
 	}
@@ -344,6 +369,11 @@ void NerfNetworkModule::density(cudaStream_t stream, uint32_t n, const float* in
 			FusedGridNetArgs f{};
 			f.net = density_only; f.grid = m_grid.p; f.n = n; f.params = params; f.grid_params = params + pos_encoding_param_offset();
 			f.input = input; f.in_stride = in_stride; f.out = output; f.out_stride = out_stride;
+			if (!fused_grid_gather_in_kernel()) {
+				m_scratch_feat.reserve(tiled_bytes(n, m_pos_width), stream);
+				grid_forward(stream, m_grid.p, n, f.grid_params, input, in_stride, m_scratch_feat.as<__half>(), m_pos_width, 1.0f, true);
+				f.feat_tiles = m_scratch_feat.as<__half>();
+			}
 			fused_grid_inference(stream, f);
 			return;
 		}
@@ -369,15 +399,31 @@ void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const 
 		FusedGridNetArgs f{};
 		f.net = m_net; f.grid = m_grid.p; f.n = n; f.params = params; f.grid_params = params + pos_encoding_param_offset();
 		f.input = input; f.in_stride = in_stride; f.dL_dout = dL_doutput; f.dy_stride = dy_stride;
-		f.grid_grad = dL_dparams + pos_encoding_param_offset();
+		__half* ggrad = dL_dparams + pos_encoding_param_offset();
 		f.dw_partials = m_scratch_dw.as<float>();
 		f.dL_dparams = dL_dparams;
-		prof_mark(stream, "train.grid_grad_memset");
-		NGPB_CUDA_CHECK(cudaMemsetAsync(f.grid_grad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
-		prof_mark(stream, "train.fused_grid_mlp_fwd_bwd_scatter");
+		const bool tiles = !fused_grid_gather_in_kernel();
+		if (tiles) {
+			m_scratch_feat.reserve(tiled_bytes(n, m_pos_width), stream);
+			m_scratch_dfeat.reserve(tiled_bytes(n, m_pos_width), stream);
+			prof_mark(stream, "train.grid_forward");
+			grid_forward(stream, m_grid.p, n, f.grid_params, input, in_stride, m_scratch_feat.as<__half>(), m_pos_width, 1.0f, true);
+			f.feat_tiles = m_scratch_feat.as<__half>();
+			f.dfeat_tiles = m_scratch_dfeat.as<__half>();
+		} else {
+			f.grid_grad = ggrad;
+			prof_mark(stream, "train.grid_grad_memset");
+			NGPB_CUDA_CHECK(cudaMemsetAsync(ggrad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
+		}
+		prof_mark(stream, tiles ? "train.fused_mlp_fwd_bwd" : "train.fused_grid_mlp_fwd_bwd_scatter");
 		if (before_mlp) NGPB_CUDA_CHECK(cudaEventRecord(before_mlp, stream));
 		fused_grid_train(stream, f);
 		if (after_mlp) NGPB_CUDA_CHECK(cudaEventRecord(after_mlp, stream));
+		if (tiles) {
+			prof_mark(stream, "train.grid_backward");
+			NGPB_CUDA_CHECK(cudaMemsetAsync(ggrad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
+			grid_backward(stream, m_grid.p, n, ggrad, input, in_stride, m_scratch_dfeat.as<__half>(), m_pos_width, 1.0f, true);
+		}
 		return;
 	}
 	const uint32_t grid = fused_train_grid(m_net, n);
