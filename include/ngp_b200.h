@@ -332,6 +332,9 @@ int ngpb_probe_scatter(void* stream, void* table, uint32_t log2_entries, uint32_
  * mode 0: D[128xN] = X[128xK] W[NxK]^T; mode 1: D[128xN] = X[128xK] W[KxN];
  * mode 2: D[64xN] = X[128x64]^T W[128xN]. fp16 row-major inputs, fp32 row-major D (device). */
 int ngpb_selftest_umma(void* stream, int mode, uint32_t K, uint32_t N, const void* X, const void* W, float* D);
+/* Issue-to-completion cycles of `reps` back-to-back batches of one operand view on one SM (same modes):
+ * out[0] = cycles from the first tcgen05.mma to the commit's arrival, out[1] = cycles spent issuing. DEVICE out[2]. */
+int ngpb_probe_umma_rate(void* stream, int mode, uint32_t K, uint32_t N, uint32_t reps, unsigned long long* out);
 
 #ifdef __cplusplus
 }

@@ -116,6 +116,7 @@ SIGNATURES = {
     "ngpb_testbed_set_render_steps_out": (c_int, [c_vp, c_vp]),
     "ngpb_testbed_render_nerf": (c_int, [c_vp, c_u32, c_u32, ctypes.POINTER(c_f32), c_f32, c_f32, c_f32, c_f32, c_u32, c_u32, c_u32, c_vp, c_vp]),
     "ngpb_selftest_umma": (c_int, [c_vp, c_int, c_u32, c_u32, c_vp, c_vp, c_vp]),
+    "ngpb_probe_umma_rate": (c_int, [c_vp, c_int, c_u32, c_u32, c_u32, c_vp]),
     "ngpb_random_uniform": (c_int, [c_vp, ctypes.POINTER(c_u64), c_sz, c_vp, c_f32, c_f32]),
 }
 

@@ -26,8 +26,10 @@
 
 namespace ngpb {
 
-constexpr uint32_t kMaxGroups = 4;
+constexpr uint32_t kMaxGroups = 7;          // inference: 7 x 128 workers + the MMA warp = 928 threads
+constexpr uint32_t kMaxTrainGroups = 4;     // training: shared memory and TMEM hold at most 3-4 tiles
 constexpr uint32_t kFusedMaxThreads = kMaxGroups * 128 + 32;
+constexpr uint32_t kFusedMaxTrainThreads = kMaxTrainGroups * 128 + 32;
 constexpr uint32_t kHiddenBytes = kTile * kMlpWidth * 2;
 
 struct FusedLayout {
@@ -83,7 +85,7 @@ static uint32_t dw_columns(const FusedNet& n) {
 static uint32_t pick_groups(const FusedNet& n, bool train) {
 	static const int forced = getenv("NGPB_FUSED_GROUPS") ? atoi(getenv("NGPB_FUSED_GROUPS")) : 0;
 	uint32_t best = 0;
-	for (uint32_t g = 1; g <= kMaxGroups; ++g) {
+	for (uint32_t g = 1; g <= (train ? kMaxTrainGroups : kMaxGroups); ++g) {
 		if (make_layout(n, train, g).total > 227u * 1024u - 512u) break;   // 227 KB per CTA less the kernel's static shared memory
 		if (64 * g + (train ? dw_columns(n) : 0) > 512) break;
 		best = g;
@@ -185,13 +187,29 @@ struct Worker {
 	uint64_t* ready;
 	uint64_t* done;
 	uint32_t phase;
+	uint32_t group;
+	uint32_t round;      // round of the current tile (self-issuing groups)
+	bool self_issue;     // the group's own thread 0 issues its MMAs (inference: no accumulator is shared between groups)
 };
-// publish this thread's smem writes / finished TMEM reads, then hand the group's tile to the MMA warp
-NGPB_D void grp_round(Worker& w) {
+NGPB_D void group_barrier(uint32_t id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
+// publish this thread's smem writes / finished TMEM reads, then run the round's MMAs: handed to the MMA warp
+// (training), or issued by the group's own thread 0 (inference)
+template <typename I>
+NGPB_D void grp_round(Worker& w, I& issue) {
 	fence_proxy_async();
 	tc_fence_before();
-	__syncwarp();
-	if ((w.row & 31u) == 0) mbar_arrive(w.ready);   // one arrival per warp (128 serialised arrivals cost ~400 cycles a round)
+	if (w.self_issue) {
+		group_barrier(1 + w.group);
+		if (w.row == 0) {
+			tc_fence_after();
+			issue(w.round);
+			umma_commit(w.done);
+		}
+	} else {
+		__syncwarp();
+		if ((w.row & 31u) == 0) mbar_arrive(w.ready);   // one arrival per warp (128 serialised arrivals cost ~400 cycles a round)
+	}
+	++w.round;
 	mbar_wait(w.done, w.phase);
 	w.phase ^= 1;
 	tc_fence_after();
@@ -238,20 +256,22 @@ NGPB_D void epi_mask(const Worker& w, uint8_t* act_tile, bool relu) {
 	}
 }
 // chain input tile written by the caller -> the chain's 16 output columns in acc[0, 16)
-NGPB_D void worker_forward(Worker& w, const Chain& ch) {
+template <typename I>
+NGPB_D void worker_forward(Worker& w, const Chain& ch, I& issue) {
 	for (uint32_t j = 0; j < ch.n_hidden; ++j) {
-		grp_round(w);
+		grp_round(w, issue);
 		epi_store(w, ch.h_ptr + j * ch.h_stride, kMlpWidth, ch.relu);
 	}
-	grp_round(w);
+	grp_round(w, issue);
 }
 // gradient seed tile written by the caller -> dL/d(chain input) in acc; hidden buffers become their gradients
-NGPB_D void worker_backward(Worker& w, const Chain& ch) {
+template <typename I>
+NGPB_D void worker_backward(Worker& w, const Chain& ch, I& issue) {
 	for (uint32_t s = 0; s < ch.n_hidden; ++s) {
-		grp_round(w);
+		grp_round(w, issue);
 		epi_mask(w, ch.h_ptr + (ch.n_hidden - 1 - s) * ch.h_stride, ch.relu);
 	}
-	grp_round(w);
+	grp_round(w, issue);
 }
 
 // dW accumulators -> this CTA's slice of the partials. M = 64 accumulators keep row r in TMEM lane (r % 16) + 32 (r / 16).
@@ -282,9 +302,36 @@ NGPB_D void store_chain_dw(uint32_t tmem_lane_base, uint32_t t, const Chain& ch,
 }
 
 // ---------------------------------------------------------------------------------------------------------
-template <uint32_t D, uint32_t F, bool NERF, bool TRAIN>
-__global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
-	const __grid_constant__ FusedNet net, const __grid_constant__ GridParams gp, const __grid_constant__ FusedLayout lay,
+// SHAPE: 0 = any supported network (the MMA thread runs the precompiled table); 1 = the NeRF network of
+// configs/nerf/base.json (32 -> 64 -> 16 | 32 -> 64 -> 64 -> 16); 2 = the image network of configs/image/base.json
+// (32 -> 64 -> 64 -> 16). For 1 and 2 the widths are compile-time constants, so the MMA thread's code for a round is
+// straight-line: descriptors are a uniform base plus immediates, and an MMA costs its issuer ~10 instructions.
+template <uint32_t SHAPE>
+NGPB_D FusedNet specialise_net(const FusedNet& in) {
+	FusedNet n = in;
+	if (SHAPE == 1) { n.nerf = 1; n.a_in = 32; n.a_hidden = 1; n.b_in = 32; n.b_hidden = 2; }
+	if (SHAPE == 2) { n.nerf = 0; n.a_in = 32; n.a_hidden = 2; }
+	return n;
+}
+
+// Issues a round's MMAs right away for one group (same interface as Emitter, which records them).
+struct DirectIssuer {
+	uint32_t rel;        // byte offset of the group's buffers from group 0's
+	uint32_t acc;        // TMEM address of the group's activation accumulator
+	uint32_t tmem;       // TMEM allocation base (dW accumulators are shared)
+	uint32_t& dw_mask;
+	NGPB_D void xwT(uint32_t acc_col, uint32_t x, uint32_t w, uint32_t K, uint32_t N) { mma_xwT(acc + acc_col, x + rel, w, K, N, false); }
+	NGPB_D void dyW(uint32_t acc_col, uint32_t dy, uint32_t w, uint32_t Nout, uint32_t Kin) { mma_dyW(acc + acc_col, dy + rel, w, Nout, Kin); }
+	NGPB_D void pTq(uint32_t dw_col, uint32_t p, uint32_t q, uint32_t Nf, uint32_t layer_bit) {
+		const bool accumulate = (dw_mask >> layer_bit) & 1u;
+		dw_mask |= 1u << layer_bit;
+		mma_pTq(tmem + dw_col, p + rel, q + rel, Nf, accumulate);
+	}
+};
+
+template <uint32_t D, uint32_t F, bool NERF, bool TRAIN, uint32_t SHAPE>
+__global__ void __launch_bounds__(TRAIN ? kFusedMaxTrainThreads : kFusedMaxThreads, 1) fused_grid_net_kernel(
+	const __grid_constant__ FusedNet net_in, const __grid_constant__ GridParams gp, const __grid_constant__ FusedLayout lay,
 	const uint32_t n_max, const uint32_t* __restrict__ n_dev,
 	const __half* __restrict__ params, const __half* __restrict__ table,
 	const float* __restrict__ input, const uint32_t in_stride,
@@ -299,6 +346,7 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 	__shared__ uint32_t tmem_slot;
 	__shared__ uint32_t round_begin[kMaxRounds + 1];
 
+	const FusedNet net = specialise_net<SHAPE>(net_in);
 	const uint32_t G = lay.groups;
 	const uint32_t t = threadIdx.x, warp = t / 32, lane = t % 32;
 	const bool is_mma_warp = warp == 4 * G;
@@ -337,7 +385,7 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 	};
 
 	// The MMAs of round r of a tile, for group 0 with TMEM column 0 as the allocation base (relocated at issue time).
-	auto emit_round = [&](Emitter& em, uint32_t r) {
+	auto emit_round = [&](auto& em, uint32_t r) {
 		Chain A, B;
 		make_chains(0, A, B);
 		const uint32_t off = sbase + lay.group0;
@@ -377,7 +425,7 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 	};
 
 	MmaOp* ops = reinterpret_cast<MmaOp*>(smem + lay.prog);
-	if (t < rounds_per_tile) {
+	if (TRAIN && SHAPE == 0 && t < rounds_per_tile) {
 		// thread r compiles round r: its first op index is the op count of the rounds before it (dry runs)
 		uint32_t begin = 0;
 		for (uint32_t r = 0; r < t; ++r) {
@@ -405,7 +453,52 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 	const uint32_t tmem = tmem_slot;
 
 	if (is_mma_warp) {
-		if (lane == 0) {
+		if (TRAIN && SHAPE != 0 && lane == 0) {
+			// per-group state packed into registers so that the group index can stay a run-time value (one copy of
+			// the straight-line round code instead of one per group)
+			uint32_t round_pk = 0, parity = 0, live = 0, dw_mask = 0;
+			uint64_t iter_pk = 0;
+			for (uint32_t g = 0; g < G; ++g) if (blockIdx.x * G + g < n_tiles) live |= 1u << g;
+			uint32_t g = 0;
+			while (live) {
+				if ((live >> g) & 1u) {
+					// Training serves the groups in a fixed cyclic order (bit-reproducible dW); inference serves whoever is ready.
+					bool ready = true;
+					if (TRAIN) mbar_wait(&bar_ready[g], (parity >> g) & 1u);
+					else ready = mbar_test(&bar_ready[g], (parity >> g) & 1u);
+					if (ready) {
+						parity ^= 1u << g;
+						tc_fence_after();
+						DirectIssuer di{g * lay.group_stride, tmem + 64 * g, tmem, dw_mask};
+						const uint32_t r = (round_pk >> (8 * g)) & 0xFFu;
+						switch (r) {
+							case 0: emit_round(di, 0); break;
+							case 1: emit_round(di, 1); break;
+							case 2: emit_round(di, 2); break;
+							case 3: emit_round(di, 3); break;
+							case 4: emit_round(di, 4); break;
+							case 5: emit_round(di, 5); break;
+							case 6: emit_round(di, 6); break;
+							case 7: emit_round(di, 7); break;
+							case 8: emit_round(di, 8); break;
+							case 9: emit_round(di, 9); break;
+							default: break;
+						}
+						umma_commit(&bar_done[g]);
+						if (r + 1 == rounds_per_tile) {
+							round_pk &= ~(0xFFu << (8 * g));
+							iter_pk += 1ull << (16 * g);
+							const uint32_t it = (uint32_t)(iter_pk >> (16 * g)) & 0xFFFFu;
+							if (blockIdx.x * G + g + it * tile_stride >= n_tiles) live &= ~(1u << g);
+						} else {
+							round_pk += 1u << (8 * g);
+						}
+					}
+				}
+				g = g + 1 == G ? 0 : g + 1;
+			}
+		}
+		if (TRAIN && SHAPE == 0 && lane == 0) {
 			uint32_t tile[kMaxGroups], round[kMaxGroups], parity[kMaxGroups];
 			uint32_t live = 0, dw_mask = 0;
 #pragma unroll
@@ -460,7 +553,7 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 						if (tile[g] >= n_tiles) live &= ~(1u << g);
 					}
 				}
-				if (!any) __nanosleep(20);
+				(void)any;   // spin: __nanosleep rounds up to about a microsecond, which is a whole round
 			}
 		}
 		__syncwarp();
@@ -473,6 +566,25 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 		w.ready = &bar_ready[g];
 		w.done = &bar_done[g];
 		w.phase = 0;
+		w.group = g;
+		w.round = 0;
+		w.self_issue = !TRAIN;
+		uint32_t unused_mask = 0;
+		DirectIssuer own{g * lay.group_stride, tmem + 64 * g, tmem, unused_mask};
+		auto issue = [&](uint32_t r) {
+			if (SHAPE != 0) {
+				switch (r) {
+					case 0: emit_round(own, 0); break;
+					case 1: emit_round(own, 1); break;
+					case 2: emit_round(own, 2); break;
+					case 3: emit_round(own, 3); break;
+					case 4: emit_round(own, 4); break;
+					default: break;
+				}
+			} else {
+				emit_round(own, r);
+			}
+		};
 		Chain A, B;
 		make_chains(g, A, B);
 		uint8_t* gbase = smem + lay.group0 + g * lay.group_stride;
@@ -486,6 +598,7 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 		for (uint32_t tile = blockIdx.x * G + g; tile < n_tiles; tile += tile_stride) {
 			const uint32_t i = tile * kTile + row;
 			const bool valid = i < n;
+			w.round = 0;
 			const float* in_row = input + (size_t)i * in_stride;
 			float x[D];
 #pragma unroll
@@ -522,7 +635,7 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 			}
 
 			// ---- forward ----
-			worker_forward(w, A);
+			worker_forward(w, A, issue);
 			uint32_t v[16];
 			float sigma_raw = 0.0f;
 			if (NERF) {
@@ -543,7 +656,7 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 				for (uint32_t k = 0; k < 8; ++k) h[k] = pack2(sh[2 * k], sh[2 * k + 1]);
 				*reinterpret_cast<uint4*>(x1 + chunk_offset(kTile, row, 2)) = make_uint4(h[0], h[1], h[2], h[3]);
 				*reinterpret_cast<uint4*>(x1 + chunk_offset(kTile, row, 3)) = make_uint4(h[4], h[5], h[6], h[7]);
-				worker_forward(w, B);
+				worker_forward(w, B, issue);
 			}
 
 			if (!TRAIN) {
@@ -578,7 +691,7 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 				const float dsigma = unpack2(gq.y).y;
 				*reinterpret_cast<uint4*>(gy + chunk_offset(kTile, row, 0)) = make_uint4(gq.x, gq.y & 0xFFFFu, 0u, 0u);
 				*reinterpret_cast<uint4*>(gy + chunk_offset(kTile, row, 1)) = make_uint4(0u, 0u, 0u, 0u);
-				worker_backward(w, B);
+				worker_backward(w, B, issue);
 				// dL/d(density-MLP output) = chain-B input gradient, columns 0-15, + dsigma on column 0
 				// (nerf_network.h:62-74); overwrites the first two chunks of x1 in place.
 				tmem_ld16(w.tmem_row, v);
@@ -589,12 +702,12 @@ __global__ void __launch_bounds__(kFusedMaxThreads, 1) fused_grid_net_kernel(
 				for (uint32_t k = 1; k < 8; ++k) h[k] = pack2(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1]));
 				*reinterpret_cast<uint4*>(x1 + chunk_offset(kTile, row, 0)) = make_uint4(h[0], h[1], h[2], h[3]);
 				*reinterpret_cast<uint4*>(x1 + chunk_offset(kTile, row, 1)) = make_uint4(h[4], h[5], h[6], h[7]);
-				worker_backward(w, A);
+				worker_backward(w, A, issue);
 			} else {
 				const uint4* gsrc = reinterpret_cast<const uint4*>(dL_dout + (size_t)i * dy_stride);
 				*reinterpret_cast<uint4*>(gy + chunk_offset(kTile, row, 0)) = __ldg(gsrc);
 				*reinterpret_cast<uint4*>(gy + chunk_offset(kTile, row, 1)) = __ldg(gsrc + 1);
-				worker_backward(w, A);
+				worker_backward(w, A, issue);
 			}
 
 			// ---- dL/d(features): tiled to global memory for grid_backward_kernel, or scattered from here ----
@@ -649,6 +762,15 @@ __global__ void fused_reduce_dw_kernel(uint32_t n_params, uint32_t n_parts, cons
 	grad[i] = __float2half(s);
 }
 
+// Training: the warp-specialised kernel needs one thread to issue every group's MMAs (the weight-gradient accumulators
+// are shared), and that thread's instruction latency (~9 cycles x ~140 instructions a round) caps it at the rate of
+// the one-tile-per-CTA kernel of mlp.cu with two CTAs per SM (measured: 0.206 vs 0.187 ms for the whole backward pass
+// at 2^18 samples). So mlp.cu stays the default there; NGPB_FUSED_TRAIN=1 selects this kernel.
+bool fused_grid_train_enabled() {
+	static const bool on = getenv("NGPB_FUSED_TRAIN") && atoi(getenv("NGPB_FUSED_TRAIN")) != 0;
+	return on;
+}
+
 bool fused_grid_gather_in_kernel() {
 	static const bool in_kernel = getenv("NGPB_FUSED_GATHER") && atoi(getenv("NGPB_FUSED_GATHER")) != 0;
 	return in_kernel;
@@ -670,18 +792,27 @@ static void launch(cudaStream_t stream, const FusedGridNetArgs& a) {
 	const uint32_t n_tiles = a.n / kTile;
 	const uint32_t grid = TRAIN ? fused_grid_train_ctas(a.net, a.n) : std::max(1u, std::min((uint32_t)sm_count(), div_round_up(n_tiles, G)));
 	const uint32_t threads = 128 * G + 32;
-#define NGPB_FUSED_LAUNCH(D_, F_, NERF_) \
+#define NGPB_FUSED_LAUNCH(D_, F_, NERF_, SHAPE_) \
 	do { \
-		auto k = fused_grid_net_kernel<D_, F_, NERF_, TRAIN>; \
+		auto k = fused_grid_net_kernel<D_, F_, NERF_, TRAIN, SHAPE_>; \
 		NGPB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lay.total)); \
 		NGPB_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); \
 		k<<<grid, threads, lay.total, stream>>>(a.net, a.grid, lay, a.n, a.n_dev, a.params, a.grid_params, a.input, a.in_stride, \
 			a.out, a.out_stride, a.dL_dout, a.dy_stride, a.grid_grad, a.dw_partials, a.feat_tiles, a.dfeat_tiles); \
 	} while (0)
 	const uint32_t D = a.grid.n_dims, F = a.grid.n_features_per_level;
-	if (D == 3 && F == 4) { if (a.net.nerf) NGPB_FUSED_LAUNCH(3, 4, true); else NGPB_FUSED_LAUNCH(3, 4, false); }
-	else if (D == 3 && F == 2) { if (a.net.nerf) NGPB_FUSED_LAUNCH(3, 2, true); else NGPB_FUSED_LAUNCH(3, 2, false); }
-	else if (D == 2 && F == 2 && !a.net.nerf) NGPB_FUSED_LAUNCH(2, 2, false);
+	const bool nerf_base = a.net.nerf && a.net.a_in == 32 && a.net.a_hidden == 1 && a.net.b_in == 32 && a.net.b_hidden == 2;
+	const bool image_base = !a.net.nerf && a.net.a_in == 32 && a.net.a_hidden == 2;
+	static const bool generic_only = getenv("NGPB_FUSED_GENERIC") && atoi(getenv("NGPB_FUSED_GENERIC"));
+	if (D == 3 && F == 4) {
+		if (a.net.nerf) { if (nerf_base && !generic_only) NGPB_FUSED_LAUNCH(3, 4, true, 1); else NGPB_FUSED_LAUNCH(3, 4, true, 0); }
+		else NGPB_FUSED_LAUNCH(3, 4, false, 0);
+	} else if (D == 3 && F == 2) {
+		if (a.net.nerf) { if (nerf_base && !generic_only) NGPB_FUSED_LAUNCH(3, 2, true, 1); else NGPB_FUSED_LAUNCH(3, 2, true, 0); }
+		else NGPB_FUSED_LAUNCH(3, 2, false, 0);
+	} else if (D == 2 && F == 2 && !a.net.nerf) {
+		if (image_base && !generic_only) NGPB_FUSED_LAUNCH(2, 2, false, 2); else NGPB_FUSED_LAUNCH(2, 2, false, 0);
+	}
 	else throw std::runtime_error{"ngp-b200 fused encoder + MLP: unsupported shape"};
 #undef NGPB_FUSED_LAUNCH
 	NGPB_CUDA_CHECK(cudaGetLastError());

@@ -49,5 +49,7 @@ void fused_grid_train(cudaStream_t stream, const FusedGridNetArgs& args);
 uint32_t fused_grid_train_ctas(const FusedNet& net, uint32_t n);
 // Default: tile-fed (gather / scatter in their own full-occupancy kernels). NGPB_FUSED_GATHER=1: in-kernel.
 bool fused_grid_gather_in_kernel();
+// Whether the training pass uses this kernel too (default: no, see fused.cu; NGPB_FUSED_TRAIN=1).
+bool fused_grid_train_enabled();
 
 } // namespace ngpb

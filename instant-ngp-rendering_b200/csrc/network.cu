@@ -163,7 +163,7 @@ void NetworkWithInputEncodingModule::backward(cudaStream_t stream, const Context
 	check_batch(n);
 	if (n == 0) return;
 	if (dL_dinput && !m_has_grid) throw std::runtime_error{"ngp-b200: input gradients through an Identity-encoded network are not available"};
-	if (m_has_grid && !dL_dinput && fused_grid_supported(m_net, m_grid.p)) {
+	if (m_has_grid && !dL_dinput && fused_grid_train_enabled() && fused_grid_supported(m_net, m_grid.p)) {
 		const uint32_t ctas = fused_grid_train_ctas(m_net, n);
 		DeviceBuffer partials{(size_t)ctas * m_mlp.n_params() * sizeof(float), stream};
 		DeviceBuffer dummy_grad{dL_dparams ? 0 : m_mlp.n_params() * sizeof(__half), stream};
@@ -393,7 +393,7 @@ void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const 
 {
 	if (n == 0) return;
 	if (n % kTile != 0) throw std::runtime_error{"ngp-b200 NerfNetwork: batch size must be a multiple of 128"};
-	if (fused_grid_supported(m_net, m_grid.p)) {
+	if (fused_grid_train_enabled() && fused_grid_supported(m_net, m_grid.p)) {
 		const uint32_t ctas = fused_grid_train_ctas(m_net, n);
 		m_scratch_dw.reserve((size_t)ctas * n_mlp_params() * sizeof(float), stream);
 		FusedGridNetArgs f{};

@@ -99,32 +99,44 @@ NGPB_D void umma_commit(uint64_t* bar) {
 NGPB_HD constexpr uint32_t tile_bytes(uint32_t rows, uint32_t width) { return rows * width * 2; }
 NGPB_D uint32_t chunk_offset(uint32_t rows, uint32_t row, uint32_t chunk) { return chunk * (rows * 16) + row * 16; }
 
+// One tcgen05.mma costs its issuing thread as many cycles as the instructions around it: a descriptor built from
+// scratch per K step (shifts, masks, 64-bit ors) made an MMA ~105 cycles of issue time against an 8-32 cycle
+// execution floor (scripts/umma_rate.py), and the issuing thread is the serial resource of these kernels. So each
+// view builds its two descriptors once and steps their 14-bit start-address field with one add per MMA; the K loop
+// is unrolled with predicated tails.
+NGPB_D uint64_t desc_advance(uint64_t d, uint32_t bytes) { return d + (uint64_t)(bytes >> 4); }
+
 // D[128 x N] (+)= X[128 x K] * W[N x K]^T ; X tile has kTileRows rows, W tile has N rows.
 NGPB_D void mma_xwT(uint32_t tmem_d, uint32_t x_saddr, uint32_t w_saddr, uint32_t K, uint32_t N, bool accumulate_first) {
 	const uint32_t idesc = instr_desc(128, N, false, false);
-	for (uint32_t k = 0; k < K / 16; ++k) {
-		const uint64_t da = smem_desc(x_saddr + 2 * k * (kTileRows * 16), kTileRows * 16, 128);
-		const uint64_t db = smem_desc(w_saddr + 2 * k * (N * 16), N * 16, 128);
-		umma_f16(tmem_d, da, db, idesc, accumulate_first || k > 0);
+	const uint64_t da = smem_desc(x_saddr, kTileRows * 16, 128);
+	const uint64_t db = smem_desc(w_saddr, N * 16, 128);
+	const uint32_t nk = K / 16, b_step = 2 * N * 16;
+#pragma unroll
+	for (uint32_t k = 0; k < 4; ++k) {
+		if (k < nk) umma_f16(tmem_d, desc_advance(da, k * 2 * kTileRows * 16), desc_advance(db, k * b_step), idesc, accumulate_first || k > 0);
 	}
 }
 // D[128 x Kin] = dY[128 x Nout] * W[Nout x Kin] ; W tile (Nout rows, Kin cols) read MN-major.
 NGPB_D void mma_dyW(uint32_t tmem_d, uint32_t dy_saddr, uint32_t w_saddr, uint32_t Nout, uint32_t Kin) {
 	const uint32_t idesc = instr_desc(128, Kin, false, true);
-	for (uint32_t k = 0; k < Nout / 16; ++k) {
-		const uint64_t da = smem_desc(dy_saddr + 2 * k * (kTileRows * 16), kTileRows * 16, 128);
-		// B: N = Kin (MN, contiguous), K = Nout rows [16k, 16k+16): start at row 16k.
-		const uint64_t db = smem_desc(w_saddr + 16 * k * 16, 128, Nout * 16);
-		umma_f16(tmem_d, da, db, idesc, k > 0);
+	const uint64_t da = smem_desc(dy_saddr, kTileRows * 16, 128);
+	// B: N = Kin (MN, contiguous), K = Nout rows [16k, 16k+16): start at row 16k.
+	const uint64_t db = smem_desc(w_saddr, 128, Nout * 16);
+	const uint32_t nk = Nout / 16;
+#pragma unroll
+	for (uint32_t k = 0; k < 4; ++k) {
+		if (k < nk) umma_f16(tmem_d, desc_advance(da, k * 2 * kTileRows * 16), desc_advance(db, k * 16 * 16), idesc, k > 0);
 	}
 }
 // D[Mf x Nf] (+)= P[128 x Mf]^T * Q[128 x Nf]  (sum over the tile's 128 samples). Mf == 64.
 NGPB_D void mma_pTq(uint32_t tmem_d, uint32_t p_saddr, uint32_t q_saddr, uint32_t Nf, bool accumulate_first) {
 	const uint32_t idesc = instr_desc(64, Nf, true, true);
+	const uint64_t da = smem_desc(p_saddr, 128, kTileRows * 16);
+	const uint64_t db = smem_desc(q_saddr, 128, kTileRows * 16);
+#pragma unroll
 	for (uint32_t k = 0; k < kTileRows / 16; ++k) {
-		const uint64_t da = smem_desc(p_saddr + 16 * k * 16, 128, kTileRows * 16);
-		const uint64_t db = smem_desc(q_saddr + 16 * k * 16, 128, kTileRows * 16);
-		umma_f16(tmem_d, da, db, idesc, accumulate_first || k > 0);
+		umma_f16(tmem_d, desc_advance(da, k * 16 * 16), desc_advance(db, k * 16 * 16), idesc, accumulate_first || k > 0);
 	}
 }
 

@@ -71,7 +71,56 @@ __global__ void __launch_bounds__(128) umma_selftest_kernel(int mode, uint32_t K
 	if (warp == 0) tc::tmem_dealloc<64>(tmem);
 }
 
+// Rate probe: thread 0 issues `reps` back-to-back batches of one operand view (same operands, same accumulator),
+// commits once and waits. out[0] = cycles from first issue to completion, out[1] = cycles spent issuing.
+__global__ void __launch_bounds__(128) umma_rate_kernel(int mode, uint32_t K, uint32_t N, uint32_t reps, unsigned long long* __restrict__ out) {
+	extern __shared__ __align__(1024) uint8_t smem[];
+	__shared__ uint64_t bar;
+	__shared__ uint32_t tmem_base_slot;
+	uint8_t* xs = smem;
+	uint8_t* ws = smem + 32768;
+	for (uint32_t i = threadIdx.x; i < 65536 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3C003C00u;
+	if (threadIdx.x / 32 == 0) tc::tmem_alloc<64>(&tmem_base_slot);
+	if (threadIdx.x == 0) { tc::mbar_init(&bar, 1); tc::fence_barrier_init(); }
+	tc::fence_proxy_async();
+	tc::tc_fence_before();
+	__syncthreads();
+	tc::tc_fence_after();
+	const uint32_t tmem = tmem_base_slot;
+	if (threadIdx.x == 0) {
+		const unsigned long long t0 = clock64();
+		for (uint32_t r = 0; r < reps; ++r) {
+			if (mode == 0) tc::mma_xwT(tmem, tc::smem_u32(xs), tc::smem_u32(ws), K, N, false);
+			else if (mode == 1) tc::mma_dyW(tmem, tc::smem_u32(xs), tc::smem_u32(ws), K, N);
+			else tc::mma_pTq(tmem, tc::smem_u32(xs), tc::smem_u32(ws), N, false);
+		}
+		const unsigned long long t1 = clock64();
+		tc::umma_commit(&bar);
+		tc::mbar_wait(&bar, 0);
+		const unsigned long long t2 = clock64();
+		out[0] = t2 - t0;
+		out[1] = t1 - t0;
+	}
+	tc::tc_fence_before();
+	__syncthreads();
+	if (threadIdx.x / 32 == 0) tc::tmem_dealloc<64>(tmem);
+}
+
 } // namespace ngpb
+
+extern "C" int ngpb_probe_umma_rate(void* stream, int mode, uint32_t K, uint32_t N, uint32_t reps, unsigned long long* out) {
+	using namespace ngpb;
+	try {
+		if (K % 16 != 0 || N % 16 != 0 || K > 64 || N > 64 || mode < 0 || mode > 2) throw std::runtime_error{"ngpb_probe_umma_rate: bad shape"};
+		NGPB_CUDA_CHECK(cudaFuncSetAttribute(umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+		umma_rate_kernel<<<1, 128, 65536, (cudaStream_t)stream>>>(mode, K, N, reps, out);
+		NGPB_CUDA_CHECK(cudaGetLastError());
+	} catch (const std::exception& e) {
+		set_last_error(e.what());
+		return NGPB_ERROR;
+	}
+	return NGPB_OK;
+}
 
 extern "C" int ngpb_selftest_umma(void* stream, int mode, uint32_t K, uint32_t N, const void* X, const void* W, float* D) {
 	using namespace ngpb;
