@@ -267,6 +267,28 @@ void iterative_opencv_lens_undistortion(const float* params, float* u, float* v)
 	*u = x;
 	*v = y;
 }
+// The lattice march of csrc/nerf_train.cu, serially: the reference's loop (src/testbed_nerf.cu:760-790) with every
+// position written as from(n0 + k), k an integer: an occupied candidate is a sample and k += 1, an empty one skips
+// ceil(max(to(t + distance_to_next_voxel) - n_k, 0.5)) candidates (= advance_to_next_voxel, nerf_device.cuh:426-437).
+void lattice_march(const Box& aabb, uint32_t max_mip, const uint8_t* bitfield, float cone_angle, V o, V dn, V idir, float n0, std::vector<uint32_t>& ks) {
+	uint32_t k = 0;
+	for (;;) {
+		const float nk = n0 + (float)k;
+		const float t = from_stepping_space(nk, cone_angle);
+		const V pos = o + t * dn;
+		if (!contains(aabb, pos) || ks.size() >= NERF_STEPS || k > 65535u - 64u) break;
+		const float dt = from_stepping_space(nk + 1.0f, cone_angle) - t;
+		const uint32_t mip = mip_from_dt(dt, pos, max_mip);
+		if (occupied_at(pos, bitfield, mip)) {
+			ks.push_back(k);
+			k += 1;
+		} else {
+			const float res = scalbnf((float)GRIDSIZE, -(int)mip);
+			const float n_target = to_stepping_space(t + distance_to_next_voxel(pos, dn, idir, res), cone_angle);
+			k += (uint32_t)fminf(ceilf(fmaxf(n_target - nk, 0.5f)), 1048576.0f);
+		}
+	}
+}
 struct Cam { V c[4]; };
 Cam cam_of(const oracle_nerf_image& m) {
 	Cam c;
@@ -329,36 +351,24 @@ extern "C" uint64_t oracle_nerf_generate_samples(const oracle_nerf_config* cfg, 
 		const float cone_angle = cfg->cone_angle_constant;
 		const float startt = advance_n_steps(tmin, cone_angle, rng.next_float());
 		const V idir = V{1.0f, 1.0f, 1.0f} / dn;
-		uint32_t j = 0;
-		float t = startt;
-		V pos;
-		while (contains(aabb, pos = o + t * dn) && j < NERF_STEPS) {
-			const float dt = calc_dt(t, cone_angle);
-			const uint32_t mip = mip_from_dt(dt, pos, cfg->max_mip);
-			if (occupied_at(pos, bitfield, mip)) { ++j; t += dt; }
-			else t = advance_to_next_voxel(t, cone_angle, pos, dn, idir, mip);
-		}
+		// the lattice march (csrc/nerf_train.cu): candidate k sits at n0 + k in stepping space
+		const float n0 = to_stepping_space(startt, cone_angle);
+		std::vector<uint32_t> ks;
+		lattice_march(aabb, cfg->max_mip, bitfield, cone_angle, o, dn, idir, n0, ks);
+		const uint32_t j = (uint32_t)ks.size();
 		if (j == 0) continue;
 		numsteps[i] = j;
 		float* r = rays + (size_t)i * 6;
 		r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = d.x; r[4] = d.y; r[5] = d.z;
 		const V wdir = (dn + 1.0f) * 0.5f;
-		t = startt;
-		uint32_t k = 0;
-		while (contains(aabb, pos = o + t * dn) && k < j) {
-			const float dt = calc_dt(t, cone_angle);
-			const uint32_t mip = mip_from_dt(dt, pos, cfg->max_mip);
-			if (occupied_at(pos, bitfield, mip)) {
-				if (total + k < max_samples) {
-					const V wp = (pos - aabb.min) / diag(aabb);
-					float* c = coords + (size_t)(total + k) * 7;
-					c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt); c[4] = wdir.x; c[5] = wdir.y; c[6] = wdir.z;
-				}
-				++k;
-				t += dt;
-			} else {
-				t = advance_to_next_voxel(t, cone_angle, pos, dn, idir, mip);
-			}
+		for (uint32_t k = 0; k < j; ++k) {
+			if (total + k >= max_samples) break;
+			const float nk = n0 + (float)ks[k];
+			const float t = from_stepping_space(nk, cone_angle);
+			const float dt = from_stepping_space(nk + 1.0f, cone_angle) - t;
+			const V wp = (o + t * dn - aabb.min) / diag(aabb);
+			float* c = coords + (size_t)(total + k) * 7;
+			c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt); c[4] = wdir.x; c[5] = wdir.y; c[6] = wdir.z;
 		}
 		total += j;
 	}
