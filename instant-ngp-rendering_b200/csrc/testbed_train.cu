@@ -188,22 +188,14 @@ void Testbed::launch_prefetch(uint32_t target_batch_size) {
 	const NerfTrainConfig cfg = make_train_config(target_batch_size);
 	const uint32_t slot = m_counter_slot ^ 1u;
 	const NerfTrainBuffers buf = make_train_buffers(slot);
-	// The march is a long serial loop per ray that lives on instruction issue, and the fused MLP
-	// kernel runs 2-3x longer while it shares the SMs' schedulers with it. Starting the march only
-	// after the MLP kernel (NGPB_PREFETCH_LATE=1) keeps that kernel fast but leaves too little of the
-	// step to hide the march under: measured 0.61 ms / step against 0.54 for the early start.
-	static const bool after_mlp = getenv("NGPB_PREFETCH_LATE") && atoi(getenv("NGPB_PREFETCH_LATE"));
-	if (after_mlp) NGPB_CUDA_CHECK(cudaStreamWaitEvent(m_side_stream, m_mlp_done, 0));
-	// An SM keeps its shared-memory / L1 split while any block is resident, and a block only sets the
-	// split of an SM it finds idle. March blocks that land on SMs still running the encoder pass
-	// (small split) pin that split for their whole life and keep the fused MLP CTAs (100 KB each) off
-	// those SMs: with sleeping resident blocks on half the SMs (scripts/corun_probe.py) the MLP
-	// kernel takes 1.6x as long, with the march 1.4-1.8x. Starting the march once the encoder pass
-	// has drained (NGPB_PREFETCH_WITH_MLP=1; both kernels ask for the largest split) brings the MLP
-	// kernel back to 93 us, but the march itself is the longer chain of the two (~340 us beside the
-	// other kernels) and the 30 us it starts later cost more: 0.570 against 0.543 ms / step.
-	static const bool with_mlp = getenv("NGPB_PREFETCH_WITH_MLP") && atoi(getenv("NGPB_PREFETCH_WITH_MLP"));
-	if (with_mlp && !after_mlp) NGPB_CUDA_CHECK(cudaStreamWaitEvent(m_side_stream, m_encoder_done, 0));
+	// The march (a warp per ray, ~70 us) is an issue-bound kernel; beside the fused MLP kernel, which is a latency
+	// chain of small MMAs and epilogues, both lose (measured: the MLP kernel 88 -> 132 us with the march on its SMs).
+	// The gradient scatter and the optimizer that follow are bound by L2 atomics and HBM and leave the issue slots
+	// idle, so the march starts when the MLP kernel has finished and hides under those two (~150 us).
+	// NGPB_PREFETCH_EARLY=1 starts it right after the loss kernel instead (the round-1 schedule, when the march
+	// was a 250-340 us serial loop and needed the whole backward pass to hide under).
+	static const bool early = getenv("NGPB_PREFETCH_EARLY") && atoi(getenv("NGPB_PREFETCH_EARLY"));
+	if (!early) NGPB_CUDA_CHECK(cudaStreamWaitEvent(m_side_stream, m_mlp_done, 0));
 	NGPB_CUDA_CHECK(cudaMemsetAsync(buf.counters, 0, sizeof(NerfStepCounters), m_side_stream));
 	nerf_generate_training_samples(m_side_stream, cfg, buf, m_rng);
 	NGPB_CUDA_CHECK(cudaEventRecord(m_prefetch_done, m_side_stream));
