@@ -47,9 +47,8 @@ def sparse(dense):
     return idx, dense[idx]
 
 
-def main():
-    os.makedirs(OUT, exist_ok=True)
-    vec, timings = {}, {}
+def dump_vectors():
+    vec = {}
     for name in rc.GRID_CASES:
         n_dims, enc, x, params, dy = rc.grid_case(name)
         got, _ = run("grid", {"n_dims": n_dims, "encoding": enc}, {"x.bin": x, "params.bin": params, "dy.bin": dy}, {"y.bin": np.float16, "dparams.bin": np.float16})
@@ -79,19 +78,23 @@ def main():
     np.savez_compressed(os.path.join(OUT, "ref_gpu_vectors.npz"), **vec)
     print("wrote", os.path.join(OUT, "ref_gpu_vectors.npz"), os.path.getsize(os.path.join(OUT, "ref_gpu_vectors.npz")), "bytes", flush=True)
 
-    # ---- the reference's kernels on the benchmark shapes ----------------------------------------
+
+
+def time_kernels(iters=20, out_path=None):
+    """The reference's kernels on the benchmark shapes; returns the timings dict."""
+    timings = {}
     g = np.random.default_rng(1337)
     for name, n in (("L16F2", 1 << 20), ("L8F4", 1 << 20)):
         n_dims, enc, _ = rc.GRID_CASES[name]
         x = g.random((n, n_dims), dtype=np.float32)
         params = (g.standard_normal(rc.grid_n_params(n_dims, enc)) * 0.1).astype(np.float16)
         dy = g.standard_normal((n, 32)).astype(np.float16)
-        _, t = run("grid", {"n_dims": n_dims, "encoding": enc, "time_iters": 20}, {"x.bin": x, "params.bin": params, "dy.bin": dy}, {})
+        _, t = run("grid", {"n_dims": n_dims, "encoding": enc, "time_iters": iters}, {"x.bin": x, "params.bin": params, "dy.bin": dy}, {})
         f, b = float(np.median(t["fwd_ms"])), float(np.median(t["bwd_ms"]))
         timings["grid_" + name] = {"n": n, "fwd_ms": f, "bwd_ms": b, "inference_ms": float(np.median(t["inference_ms"])), "gpts_per_s_fwd_bwd": n / (f + b) / 1e6}
         print("grid", name, timings["grid_" + name], flush=True)
     n = 1 << 18
-    cfg = {"encoding": rc.GRID_L8F4, "dir_encoding": rc.NERF_DIR, "network": rc.NERF_DENSITY, "rgb_network": rc.NERF_RGB, "time_iters": 20}
+    cfg = {"encoding": rc.GRID_L8F4, "dir_encoding": rc.NERF_DIR, "network": rc.NERF_DENSITY, "rgb_network": rc.NERF_RGB, "time_iters": iters}
     x = g.random((n, 7), dtype=np.float32)
     params = np.concatenate([rc.mlp_weights(g, 32, 1), rc.mlp_weights(g, 32, 2), (g.standard_normal(rc.grid_n_params(3, rc.GRID_L8F4)) * 0.1).astype(np.float16)])
     dy = np.zeros((n, 16), dtype=np.float16)
@@ -103,15 +106,24 @@ def main():
     xm = g.uniform(-1, 1, size=(n, n_in)).astype(np.float32)
     dym = np.zeros((n, 16), dtype=np.float16)
     dym[:, :3] = (g.standard_normal((n, 3)) * 0.1).astype(np.float16)
-    _, t = run("mlp", {"n_in": n_in, "n_out": n_out, "network": mcfg, "time_iters": 20}, {"x.bin": xm, "params.bin": w, "dy.bin": dym}, {})
+    _, t = run("mlp", {"n_in": n_in, "n_out": n_out, "network": mcfg, "time_iters": iters}, {"x.bin": xm, "params.bin": w, "dy.bin": dym}, {})
     timings["mlp_32_64x2_3_2e18"] = {"n": n, "fwd_ms": float(np.median(t["fwd_ms"])), "bwd_ms": float(np.median(t["bwd_ms"])), "inference_ms": float(np.median(t["inference_ms"]))}
     print("mlp", timings["mlp_32_64x2_3_2e18"], flush=True)
-    acfg = dict(rc.adam_case()[0], n=12865536, steps=1, time_iters=20, layers=[[64, 32], [16, 64], [64, 32], [64, 64], [16, 64]])
+    acfg = dict(rc.adam_case()[0], n=12865536, steps=1, time_iters=iters, layers=[[64, 32], [16, 64], [64, 32], [64, 64], [16, 64]])
     _, t = run("adam", acfg, {"w.bin": np.zeros(acfg["n"], np.float32), "g.bin": (g.standard_normal(acfg["n"])).astype(np.float16)}, {})
     timings["adam_12.9M"] = {"n": acfg["n"], "step_ms": float(np.median(t["step_ms"]))}
     print("adam", timings["adam_12.9M"], flush=True)
-    with open(os.path.join(OUT, "ref_gpu_timings.json"), "w") as f:
-        json.dump(timings, f, indent=1)
+    if out_path:
+        with open(out_path, "w") as f:
+            json.dump(timings, f, indent=1)
+    return timings
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    if "--timings-only" not in sys.argv:
+        dump_vectors()
+    time_kernels(out_path=os.path.join(OUT, "ref_gpu_timings.json"))
 
 
 if __name__ == "__main__":

@@ -33,6 +33,8 @@ ap.add_argument("--save", default="")
 ap.add_argument("--load", default="")
 ap.add_argument("--out", default="")
 ap.add_argument("--batch", type=int, default=1 << 18)
+ap.add_argument("--eval", type=int, default=1, help="0: skip the PSNR protocol (timing only)")
+ap.add_argument("--frames", type=int, default=10)
 args = ap.parse_args()
 
 sys.path.insert(0, os.path.join(ROOT, "baseline", "_ref") if args.impl == "reference" else os.path.join(ROOT, "instant-ngp-rendering_b200"))
@@ -71,7 +73,8 @@ def evaluate(testbed, stride=5, spp=4):
     return {"psnr_mean": float(np.mean(psnrs)), "psnr_min": float(np.min(psnrs)), "psnr_max": float(np.max(psnrs)), "views": len(psnrs)}
 
 
-def time_render(testbed, frames=10):
+def time_render(testbed, frames=None):
+    frames = frames or args.frames
     testbed.shall_train = False
     testbed.set_camera_to_training_view(0)
     for _ in range(3):
@@ -118,7 +121,8 @@ def run_fox(out):
         if hasattr(testbed, "measured_batch_size"):
             c["measured_batch_size"] = int(testbed.measured_batch_size)
         done = target
-        c.update(evaluate(testbed))
+        if args.eval:
+            c.update(evaluate(testbed))
         print(c, flush=True)
         rec["checkpoints"].append(c)
     rec["render"] = time_render(testbed)
@@ -128,6 +132,12 @@ def run_fox(out):
         rec["saved"] = args.save
         rec["snapshot_bytes"] = os.path.getsize(args.save)
     out["fox"] = rec
+    # samples per second over the last segment: the step trains min(measured_batch_size, batch) samples (the compacted
+    # batch is clamped to the batch size, src/testbed_nerf.cu:2862-2870); the reference's binding does not expose the
+    # counter, so its runs are credited with the full batch, which is an upper bound for it
+    last = rec["checkpoints"][-1]
+    mb = min(int(last.get("measured_batch_size", args.batch)), args.batch)
+    rec["samples_per_s"] = mb / (last["ms_per_step"] * 1e-3)
 
 
 def run_albert(out):

@@ -29,6 +29,15 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "baseline"))
+import configs as ref_configs  # noqa: E402  the reference's shipped configs restated; imports nothing of the product
+
+# torchrun pins OMP_NUM_THREADS=1 in its workers; the CPU legs (oracle, OpenMP) are meant to use the host's cores.
+# libgomp reads the variable when it is loaded, which happens with the oracle library, after this line.
+if os.environ.get("OMP_NUM_THREADS", "") in ("", "1"):
+    os.environ["OMP_NUM_THREADS"] = str(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
+
+FOX_DIR = os.path.join(ROOT, "data_stage", "fox")   # the reference's data/nerf/fox, staged (git-ignored); absent -> synthetic fox-shaped set
 
 GRID_ENC = {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 2, "log2_hashmap_size": 19,
             "base_resolution": 16, "per_level_scale": 1.3819}
@@ -165,7 +174,7 @@ class CpuNerf:
         import numpy as np
         import oracle_binding as oracle
         self.np, self.oracle = np, oracle
-        syn = importlib.import_module("instant-ngp-rendering_b200.synthetic")
+        syn = ref_configs   # poses and configs only: the CPU arm must not load the product library
         rng = np.random.default_rng(1337)
         n_images, w, h, aabb = FOX["n_images"], FOX["width"], FOX["height"], FOX["aabb_scale"]
         poses = syn.orbit_poses(n_images, radius=1.4)
@@ -392,6 +401,14 @@ def image_measure(ngp, steps, warmup, rank, world, local):
                        (xs / w + 0.05 * torch.randn((h, w), generator=g, device=dev)).clamp(0, 1), torch.ones((h, w), device=dev)], dim=-1).float().contiguous()
     tb = ngp.Testbed(device=dev)
     tb.use_current_stream()
+    albert = os.path.join(ROOT, "data_stage", "albert.exr")   # the reference's data/image/albert.exr, staged
+    if os.path.exists(albert) and not os.environ.get("NGPB_BENCH_SYNTHETIC"):
+        loader = importlib.import_module("instant-ngp-rendering_b200.loader")
+        img = torch.from_numpy(loader.load_image_file(albert)).to(dev).float().contiguous()
+        h, w = int(img.shape[0]), int(img.shape[1])
+        name = "albert.exr"
+    else:
+        name = "synthetic 1024x1024"
     tb.set_image(img)
     tb.reload_network_from_json(IMAGE_CONFIG)
     batch = 1 << 18
@@ -408,8 +425,13 @@ def image_measure(ngp, steps, warmup, rank, world, local):
     got = tb.render_image(w, h)
     mse = float(((got[..., :3].clamp(0, 1) - img[..., :3]) ** 2).mean())
     tb.close()
+    peaks = load_peaks()
+    pk = peaks["bf16_tflops_sustained"] or peaks["bf16_tflops"]
+    tf = batch * 43008.0 / (ms / steps * 1e-3) / 1e12     # 32 -> 64 -> 64 -> 16 forward + backward, per GPU
     return {"metric": "neural image train samples/s", "value": batch * world * steps / (ms * 1e-3), "unit": "samples/s", "ms_per_step": ms / steps,
-            "config": {"workload": "image_1024x1024_base.json_batch2^18", "parallelism": "replicas only" if world > 1 else "1 GPU"},
+            "config": {"workload": "image_%s_base.json_batch2^18" % name, "parallelism": "replicas only" if world > 1 else "1 GPU"},
+            "roofline": {"bound": "tensor", "achieved": tf, "peak": pk, "unit": "TFLOP/s", "frac": tf / pk, "traffic": None,
+                         "note": "whole step (positions, 2-D grid fwd+bwd, MLP fwd+bwd, loss, Adam) against the MLP's 43 008 FLOP per sample"},
             "mse_linear_after": mse, "steps_trained": steps + max(warmup, 3) + 100}
 
 
@@ -426,6 +448,59 @@ def load_traffic(kernel):
 # fwd+bwd (+ partial-sum reduction), grid backward, optimizer; the occupancy update adds 9 every
 # 16th step and the loss reduction 1.
 NERF_LAUNCHES_PER_STEP = 11
+# kernels behind one mark of the library's phase timer (csrc: nerf_train.cu, network.cu, nerf_loss.cu, optimizer.cu, testbed_train.cu);
+# gpu_launches = sum over the phases of (marks counted by the timer in the profiled steps) x (kernels per mark), scaled to K steps
+KERNELS_PER_PHASE = {"generate_training_samples": 1, "infer.grid_forward": 1, "infer.fused_mlp": 1, "infer.fused_grid_mlp": 1, "loss_and_compact": 2,
+                     "train.grid_forward": 1, "train.fused_mlp_fwd_bwd": 2, "train.fused_grid_mlp_fwd_bwd_scatter": 2, "train.grid_backward": 1,
+                     "optimizer": 1, "density_grid_update": 9}
+
+
+def count_launches(prof, profiled_steps, steps):
+    n = sum(cnt * KERNELS_PER_PHASE.get(name, 1) for name, (_, cnt) in prof.items())
+    return int(round(n * steps / max(profiled_steps, 1)))
+
+
+def gpu_baseline(timeout_s=240):
+    """The reference's OWN CUDA build (baseline/_ref, built by baseline/build_ref.sh from the unmodified sources, native
+    sm_100 SASS) on this GPU, through its own Python binding / C++ API, in child processes: fox training at 2^18 samples
+    per step (steps 300..1300 timed), the 1920x1080 render of the trained model through render(), albert at 2^18, and
+    its kernels on the benchmark shapes (baseline/harness.cu). None when the build or the staged data is absent."""
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    if not (os.path.exists(os.path.join(ref, "ref_harness")) and any(f.startswith("pyngp") and f.endswith(".so") for f in os.listdir(ref))):
+        return {"unavailable": "baseline/_ref is not built here (baseline/build_ref.sh needs /root/reference)"}
+    out = {"build": "unmodified reference sources, nvcc 12.9 -gencode arch=compute_100,code=sm_100 (tcnn's arch cap at 90 lifted), --use_fast_math, headless",
+           "how": "child processes; CUDA events / device-synchronised wall clock inside them (baseline/run_pyngp.py, baseline/dump_ref_gpu.py)"}
+    tmp = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(tmp, exist_ok=True)
+    env = dict(os.environ)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    try:
+        if os.path.isdir(FOX_DIR):
+            what = "fox,albert" if os.path.exists(os.path.join(ROOT, "data_stage", "albert.exr")) else "fox"
+            jp = os.path.join(tmp, "bench_ref_pyngp.json")
+            subprocess.run([sys.executable, os.path.join(ROOT, "baseline", "run_pyngp.py"), "--impl", "reference", "--what", what, "--steps", "300,1300",
+                            "--eval", "0", "--frames", "5", "--out", jp], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=timeout_s, env=env, check=True)
+            r = json.load(open(jp))
+            last = r["fox"]["checkpoints"][-1]
+            out["train"] = {"workload": "data/nerf/fox, configs/nerf/base.json, batch 2^18, steps 300..1300", "ms_per_step": last["ms_per_step"],
+                            "samples_per_s": r["fox"]["samples_per_s"], "note": "credited with the full 2^18 batch per step (its binding does not expose the compacted count)"}
+            out["render"] = {"workload": "trained fox, training view 0, 1920x1080, 1 spp, through render() incl. the copy to the host", "ms_per_frame": r["fox"]["render"]["ms_per_frame_e2e"],
+                             "mrays_per_s": r["fox"]["render"]["mrays_per_s_e2e"]}
+            if "albert" in r:
+                out["image"] = {"workload": "data/image/albert.exr, configs/image/base.json, batch 2^18, steps 1000..2000", "ms_per_step": r["albert"]["checkpoints"][-1]["ms_per_step"],
+                                "samples_per_s": r["albert"]["checkpoints"][-1]["samples_per_s"]}
+        else:
+            out["train"] = {"unavailable": "data_stage/fox is not staged on this box"}
+        jp = os.path.join(tmp, "ref_gpu_timings.json")
+        subprocess.run([sys.executable, os.path.join(ROOT, "baseline", "dump_ref_gpu.py"), "--timings-only"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=timeout_s, env=env, check=True)
+        t = json.load(open(jp))
+        out["grid"] = {"workload": "L16 F2 T=2^19, 2^20 uniform points, L2 flushed per iteration", "fwd_ms": t["grid_L16F2"]["fwd_ms"], "bwd_ms": t["grid_L16F2"]["bwd_ms"],
+                       "gpts_per_s": t["grid_L16F2"]["gpts_per_s_fwd_bwd"], "L8F4_gpts_per_s": t["grid_L8F4"]["gpts_per_s_fwd_bwd"]}
+        out["kernels"] = {"nerf_network_2^18": t["nerfnet_2e18"], "fully_fused_mlp_2^18": t["mlp_32_64x2_3_2e18"], "adam_12.9M": t["adam_12.9M"]}
+    except Exception as e:  # the baseline is a report, never a reason for the bench to fail
+        out["error"] = "%s: %s" % (type(e).__name__, str(e)[:200])
+    return out
 
 
 def nerf_phase_costs(prof, n_steps, compacted, marched, n_params, peaks):
@@ -479,7 +554,32 @@ def run_nerf(args):
 
     tb = ngp.Testbed(device=dev)
     tb.use_current_stream()
-    scene, poses, focal = syn.make_dataset(tb, n_images=FOX["n_images"], width=FOX["width"], height=FOX["height"], aabb_scale=FOX["aabb_scale"], amp_scale=FOX["amp_scale"])
+    use_fox = os.path.isdir(FOX_DIR) and not os.environ.get("NGPB_BENCH_SYNTHETIC")
+    host_images = []
+    if use_fox:
+        # the reference's own scene (configs[2]): 50 JPEGs 1080x1920, OpenCV lens, aabb_scale 4; decoded on the host once,
+        # kept in pinned memory for the end-to-end leg
+        loader = importlib.import_module("instant-ngp-rendering_b200.loader")
+        ds = loader.describe_dataset(FOX_DIR)
+        tb.create_empty_nerf_dataset(len(ds["frames"]), aabb_scale=ds["aabb_scale"], is_hdr=ds["is_hdr"])
+        for i, fr in enumerate(ds["frames"]):
+            px = torch.from_numpy(np.ascontiguousarray(loader.load_frame_pixels(fr, ds))).pin_memory()
+            h_, w_ = px.shape[:2]
+            fx, fy = loader.finish_frame(fr, w_, h_)
+            tb.nerf.training.set_image(i, px)
+            cx, cy = fr["principal"]
+            k1, k2, p1, p2 = fr["lens_params"][:4] if fr["lens_mode"] == 1 else (0.0, 0.0, 0.0, 0.0)
+            tb.nerf.training.set_camera_intrinsics(i, fx=fx, fy=fy, cx=cx * w_, cy=cy * h_, k1=k1, k2=k2, p1=p1, p2=p2)
+            tb.nerf.training.set_camera_extrinsics(i, fr["xform"], convert_to_ngp=False)
+            host_images.append(px)
+        tb.dataset, tb.up_dir, tb.mode = ds, ds["up"], tbm.MODE_NERF
+        tb.nerf.training.near_distance = 0.1   # scripts/run.py default for real scenes
+        data_name = "fox"
+        dataset_desc = "data/nerf/fox of the reference (staged under data_stage/): %d JPEG views %dx%d, OpenCV lens, aabb_scale %d" % (len(host_images), w_, h_, ds["aabb_scale"])
+    else:
+        scene, poses, focal = syn.make_dataset(tb, n_images=FOX["n_images"], width=FOX["width"], height=FOX["height"], aabb_scale=FOX["aabb_scale"], amp_scale=FOX["amp_scale"])
+        data_name = "synthetic"
+        dataset_desc = f"{FOX['n_images']} views {FOX['width']}x{FOX['height']} RGBA8, aabb_scale {FOX['aabb_scale']}, analytic blob scene rendered on the GPU (data_stage/fox absent)"
     tb.reload_network_from_json(syn.NERF_BASE_CONFIG)
     if world > 1:
         tb.set_shard(rank, world)
@@ -528,10 +628,10 @@ def run_nerf(args):
     # end to end: the dataset comes from pinned host memory (re-uploaded inside the timed region through
     # set_nerf_image, as load_training_data does once per run), then K Testbed.train calls, each
     # reading its counters / loss back to the host.
-    host_images = []
-    for i in range(FOX["n_images"]):
-        img = syn.linear_premul_to_srgb8(scene.render(poses[i], FOX["width"], FOX["height"], focal)).cpu().pin_memory()
-        host_images.append(img)
+    if not use_fox:
+        for i in range(FOX["n_images"]):
+            img = syn.linear_premul_to_srgb8(scene.render(poses[i], FOX["width"], FOX["height"], focal)).cpu().pin_memory()
+            host_images.append(img)
     torch.cuda.synchronize()
     barrier(world)
     t0 = time.perf_counter()
@@ -550,7 +650,16 @@ def run_nerf(args):
     # configs[3]: novel-view render of the trained model, 1920x1080, tiles sharded over the ranks
     rw, rh = 1920, 1080
     shard = (rank, world)
-    view = syn.look_at_ngp(np.array([0.5, 0.5, 0.5]) + 1.4 * np.array([0.62, -0.55, 0.56]))  # not a training pose
+    if use_fox:
+        # a pose between training views 0 and 1 (not a training pose), the views' own field of view on the landscape frame
+        tb.set_camera_to_training_view(0)
+        cam_a = np.array(tb._camera, dtype=np.float32)
+        tb.set_camera_to_training_view(1)
+        view = cam_a.copy()
+        view[:, 3] = 0.5 * (cam_a[:, 3] + np.array(tb._camera, dtype=np.float32)[:, 3])
+        focal = float(np.broadcast_to(tb._relative_focal_length, (2,))[1]) * rh
+    else:
+        view = syn.look_at_ngp(np.array([0.5, 0.5, 0.5]) + 1.4 * np.array([0.62, -0.55, 0.56]))  # not a training pose
     for _ in range(3):
         tb.render_nerf(rw, rh, view, focal, shard=shard)
     frames = 5
@@ -575,12 +684,21 @@ def run_nerf(args):
               "queries_per_ray": queries / (rw * rh), "gqueries_per_s": queries / (render_ms * 1e-3) / 1e9, "coverage": coverage,
               "e2e": {"value": rw * rh / (render_e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "d2h_bytes_per_frame": rw * rh * 16 // world},
               "sharding": f"256-pixel tiles interleaved over {world} rank(s), no communication"}
+    # per query 588 B of encoder traffic (L2-resident table: HBM is the floor) and 20 480 FLOP of MLP
+    r_t = queries * NERF_MLP_FLOP_INFER / (render_ms * 1e-3) / 1e12 / world
+    r_b = queries * NERF_GRID_BYTES_INFER / (render_ms * 1e-3) / 1e9 / world
+    pk_t = peaks["bf16_tflops_sustained"] or peaks["bf16_tflops"]
+    render["roofline"] = {"bound": "tensor", "achieved": r_t, "peak": pk_t, "unit": "TFLOP/s", "frac": r_t / pk_t, "traffic": None,
+                          "gather": {"achieved": r_b, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": r_b / peaks["hbm_gbs"]},
+                          "note": "whole frame (march + encoder + MLP + composite) against the MLP's tensor peak and the encoder's algorithmic bytes against the HBM copy peak, per GPU"}
 
     grid = grid_measure(ngp, min(K, 20), 3, rank, world, local)
     image = image_measure(ngp, min(K, 100), 3, rank, world, local)
     if rank != 0:
         return
     cpu = cpu_nerf_baseline(n_rays=256, steps=4, budget_s=20.0)
+    gb = gpu_baseline() if world == 1 else None
+    ref_train = (gb or {}).get("train", {}).get("samples_per_s")
     roof = None
     if dom:
         d = timed[dom]
@@ -589,9 +707,13 @@ def run_nerf(args):
                 "note": "largest roofline-bound kernel group of the training step by the phase timer (the ray march is issue-latency bound and overlapped, see phases.generate_training_samples); per-group figures in `phases`"}
     line = {
         "metric": "fox NeRF train samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-        "config": {"workload": "nerf_train_fox_shape_base.json_batch2^18",
-                   "dataset": f"{FOX['n_images']} views {FOX['width']}x{FOX['height']} RGBA8, aabb_scale {FOX['aabb_scale']}, analytic blob scene rendered on the GPU",
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+        # the reference's own CUDA build on this GPU (measured in this run when baseline/_ref and the staged fox
+        # are present, else the figure recorded in BASELINE.md from profiles/r02_reference_pyngp.json: 105.4 M samples/s)
+        "vs_baseline": (value / ref_train) if (ref_train and use_fox) else ((value / 105.4e6) if use_fox else None),
+        "dtype": "f16", "data": data_name,
+        "config": {"workload": "nerf_train_fox_base.json_batch2^18" if use_fox else "nerf_train_fox_shape_base.json_batch2^18",
+                   "dataset": dataset_desc,
                    "network": "configs/nerf/base.json (HashGrid L8 F4 T2^19 + 64-wide density/rgb MLPs), Ema(ExponentialDecay(Adam))",
                    "global_batch": batch, "pretrain_steps": FOX["pretrain_steps"],
                    "l2": "not flushed: a step streams the 283 MB optimizer state and gathers from 415 MB of images, both larger than the 126 MB L2",
@@ -604,7 +726,8 @@ def run_nerf(args):
         "cpu_baseline": {"value": cpu["samples_per_s"], "unit": "samples/s", "cores": cpu["cores"], "kind": "port", "sample": cpu["sample"]},
         "e2e": {"value": e2e_samples / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 20,
                 "note": "dataset uploaded from pinned host memory inside the timed region, then K Testbed.train calls with their counter read-backs"},
-        "gpu_launches": NERF_LAUNCHES_PER_STEP * K,
+        "gpu_launches": count_launches(prof, P, K),
+        "gpu_baseline": gb,
         "render": render, "grid": grid, "image": image, "clocks": clocks,
     }
     emit_line(line)

@@ -97,10 +97,30 @@ def build_ref(verbose=False):
     return out
 
 
+def build_baseline(verbose=False):
+    """baseline/_ref: the UNMODIFIED reference (instant-ngp + tiny-cuda-nn) compiled headless for sm_100 by
+    baseline/build_ref.sh (direct nvcc recipe; ~25 min of CPU from scratch), the GPU baseline and GPU oracle of
+    DESIGN.md section 4. Relinked here when its libraries exist; a from-scratch build needs NGPB_BUILD_REFERENCE=1
+    (or run baseline/build_ref.sh). Never part of the product."""
+    base = os.path.join(ROOT, "baseline")
+    ref = os.environ.get("NGP_REFERENCE", "/root/reference")
+    if not os.path.isdir(os.path.join(ref, "src")):
+        return
+    if os.path.exists(os.path.join(base, "_ref", "obj", "libtcnn_ref.a")) and os.path.exists(os.path.join(base, "_ref", "obj", "libngp_ref.a")):
+        _run(["bash", os.path.join(base, "build_harness.sh")])
+        if verbose:
+            print("[build] baseline/_ref up to date (ref_harness, pyngp)")
+    elif os.environ.get("NGPB_BUILD_REFERENCE"):
+        _run(["bash", os.path.join(base, "build_ref.sh")])
+    elif verbose:
+        print("[build] baseline/_ref not built (NGPB_BUILD_REFERENCE=1 or baseline/build_ref.sh builds the reference: ~25 min)")
+
+
 def build_all(verbose=False):
     build_cuda(verbose)
     build_oracle(verbose)
     build_ref(verbose)
+    build_baseline(verbose)
 
 
 if __name__ == "__main__":
