@@ -237,6 +237,14 @@ int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size);
  * them over the ranks; train_backward starts their copy to the host and computes this rank's
  * "gradients"; the caller sums those; train_end steps the optimizer and, with the global counts
  * already on the host, marches the next step's rays under it. train_begin = forward + backward. */
+/* Data-parallel training inside the library (csrc/dist.cu): one process per GPU, NCCL bound at run time from the
+ * process's libnccl.so.2. Rank 0 obtains two unique ids (128 bytes each) with ngpb_nccl_get_unique_id and hands them to
+ * every rank over the caller's bootstrap (torch.distributed store, MPI, a file); every rank then calls
+ * ngpb_testbed_init_data_parallel with the same ids, and ngpb_testbed_train(global batch) runs the sharded step: rays
+ * [rank R/P, (rank+1) R/P), the step counters all-reduced beside the backward pass, gradients reduce-scattered, Adam +
+ * EMA on this rank's 1/P of the parameters, fp16 weights all-gathered. world == 1 returns to single-GPU training. */
+int ngpb_nccl_get_unique_id(void* out128);
+int ngpb_testbed_init_data_parallel(ngpb_testbed_t* t, const void* id_main, const void* id_aux, int rank, int world);
 int ngpb_testbed_train_forward(ngpb_testbed_t* t, uint32_t batch_size);
 int ngpb_testbed_train_backward(ngpb_testbed_t* t, uint32_t batch_size);
 /* Named scalar properties (the public members pyngp binds, src/python_api.cu:481-566, 645-697):

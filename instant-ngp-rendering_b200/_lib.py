@@ -116,6 +116,8 @@ SIGNATURES = {
     "ngpb_testbed_set_render_steps_out": (c_int, [c_vp, c_vp]),
     "ngpb_testbed_render_nerf": (c_int, [c_vp, c_u32, c_u32, ctypes.POINTER(c_f32), c_f32, c_f32, c_f32, c_f32, c_u32, c_u32, c_u32, c_vp, c_vp]),
     "ngpb_selftest_umma": (c_int, [c_vp, c_int, c_u32, c_u32, c_vp, c_vp, c_vp]),
+    "ngpb_nccl_get_unique_id": (c_int, [c_vp]),
+    "ngpb_testbed_init_data_parallel": (c_int, [c_vp, c_vp, c_vp, c_int, c_int]),
     "ngpb_probe_umma_rate": (c_int, [c_vp, c_int, c_u32, c_u32, c_u32, c_vp]),
     "ngpb_random_uniform": (c_int, [c_vp, ctypes.POINTER(c_u64), c_sz, c_vp, c_f32, c_f32]),
 }

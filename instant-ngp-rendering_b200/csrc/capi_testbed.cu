@@ -2,6 +2,7 @@
 #include "../../include/ngp_b200.h"
 
 #include "testbed.h"
+#include "dist.h"
 
 #include <cstring>
 
@@ -101,6 +102,21 @@ int ngpb_testbed_train_forward(ngpb_testbed_t* t, uint32_t batch_size) {
 int ngpb_testbed_train_backward(ngpb_testbed_t* t, uint32_t batch_size) {
 	NGPB_API_BEGIN
 	t->impl->train_backward(batch_size, true);
+	NGPB_API_END
+}
+int ngpb_nccl_get_unique_id(void* out128) {
+	NGPB_API_BEGIN
+	if (!out128) throw std::runtime_error{"ngpb_nccl_get_unique_id: null argument"};
+	static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+	ncclUniqueId id;
+	NGPB_NCCL_CHECK(NcclApi::get().GetUniqueId(&id));
+	memcpy(out128, &id, sizeof(id));
+	NGPB_API_END
+}
+int ngpb_testbed_init_data_parallel(ngpb_testbed_t* t, const void* id_main, const void* id_aux, int rank, int world) {
+	NGPB_API_BEGIN
+	if (world > 1 && (!id_main || !id_aux)) throw std::runtime_error{"ngpb_testbed_init_data_parallel: null unique id"};
+	t->impl->init_data_parallel(id_main, id_aux, rank, world);
 	NGPB_API_END
 }
 int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size) {

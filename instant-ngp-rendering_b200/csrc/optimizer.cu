@@ -13,6 +13,8 @@ struct AdamArgs {
 	uint32_t optimize_matrix_params, optimize_non_matrix_params;
 	float beta1, beta2, epsilon, lower_lr_bound, upper_lr_bound, l2_reg;
 	// EMA
+	uint32_t begin;          // first element of the launch (multiple of 4); n_elements is one past the last
+	uint32_t adam;           // 0: EMA only (elements whose Adam step another rank ran, after the all-gather of the weights)
 	uint32_t has_ema, ema_full_precision;
 	float ema_decay, ema_debias_old, ema_debias_new;
 	float inv_loss_scale, log2_beta1, log2_beta2;
@@ -38,6 +40,7 @@ NGPB_D void update_one(const AdamArgs& a, uint32_t i, float grad_h, float& w_fp,
 	bool skip;
 	if (i >= a.n_matrix_weights) skip = !a.optimize_non_matrix_params || gradient == 0;
 	else skip = !a.optimize_matrix_params;
+	if (!a.adam) skip = true;
 
 	if (!skip) {
 		const float weight_fp = w_fp;
@@ -72,7 +75,7 @@ __global__ void __launch_bounds__(256) adam_ema_step_kernel(const __grid_constan
 	float* __restrict__ first_moments, float* __restrict__ second_moments, uint32_t* __restrict__ param_steps,
 	__half* __restrict__ weights_ema, float* __restrict__ ema_tmp)
 {
-	const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+	const uint32_t i0 = a.begin + (blockIdx.x * blockDim.x + threadIdx.x) * 4;
 	if (i0 >= a.n_elements) return;
 	if (i0 + 4 <= a.n_elements) {
 		const uint2 graw = __ldg(reinterpret_cast<const uint2*>(gradients + i0));
@@ -83,7 +86,7 @@ __global__ void __launch_bounds__(256) adam_ema_step_kernel(const __grid_constan
 		for (uint32_t k = 0; k < 4; ++k) {
 			const uint32_t i = i0 + k;
 			const bool skip = i >= a.n_matrix_weights ? (!a.optimize_non_matrix_params || __half2float(g[k]) * a.inv_loss_scale == 0) : !a.optimize_matrix_params;
-			any_adam |= !skip;
+			any_adam |= !skip && a.adam;
 		}
 		if (!any_adam && !a.has_ema) return;
 		__half wh[4], eh[4];
@@ -238,7 +241,19 @@ void Optimizer::allocate(uint32_t n_weights, const std::vector<std::pair<uint32_
 }
 
 void Optimizer::step(cudaStream_t stream, float loss_scale, float* weights_fp32, __half* weights, const __half* gradients) {
-	if (m_n_weights == 0) return;
+	step_range(stream, loss_scale, weights_fp32, weights, gradients, 0, m_n_weights, true, true);
+}
+
+// Elements [begin, end) of the step (begin a multiple of 4): the whole of Optimizer::step when the range is everything.
+// `advance`: this call opens a new step (learning-rate schedule, step count, EMA debias factors); later calls of the
+// same step pass false. `adam` false runs the EMA filter only - for weights another rank has stepped (sharded
+// optimizer, Testbed::train_dp): every rank filters the same fp16 weights, so the EMA copies stay bit-identical.
+void Optimizer::step_range(cudaStream_t stream, float loss_scale, float* weights_fp32, __half* weights, const __half* gradients,
+	uint32_t begin, uint32_t end, bool adam, bool advance)
+{
+	if (m_n_weights == 0 || begin >= end) { if (!advance) return; }
+	if (begin % 4 != 0 || end > m_n_weights) throw std::runtime_error{"ngp-b200 optimizer: step range must start at a multiple of 4 inside the weights"};
+	if (advance) {
 	// ExponentialDecayOptimizer::step (exponential_decay.h:60-71), evaluated on the step count
 	// *before* Adam increments it.
 	if (m_has_decay) {
@@ -248,9 +263,13 @@ void Optimizer::step(cudaStream_t stream, float loss_scale, float* weights_fp32,
 		}
 	}
 	++m_current_step;
+	}
+	if (begin >= end) return;
 
 	AdamArgs a{};
-	a.n_elements = m_n_weights;
+	a.n_elements = end;
+	a.begin = begin;
+	a.adam = adam ? 1u : 0u;
 	a.n_matrix_weights = m_n_matrix_weights;
 	a.relative_weight_decay = m_relative_weight_decay;
 	a.absolute_weight_decay = m_absolute_weight_decay;
@@ -280,7 +299,7 @@ void Optimizer::step(cudaStream_t stream, float loss_scale, float* weights_fp32,
 
 	const bool aligned = ((uintptr_t)weights_fp32 % 16 == 0) && ((uintptr_t)weights % 8 == 0) && ((uintptr_t)gradients % 8 == 0);
 	if (!aligned) throw std::runtime_error{"ngp-b200 optimizer: parameter buffers must be 16-byte (fp32) / 8-byte (fp16) aligned"};
-	const uint32_t n_threads = div_round_up(m_n_weights, 4);
+	const uint32_t n_threads = div_round_up(end - begin, 4);
 	adam_ema_step_kernel<<<div_round_up(n_threads, 256), 256, 0, stream>>>(a, weights_fp32, weights, gradients,
 		m_first_moments, m_second_moments, m_param_steps, m_weights_ema, m_ema_tmp);
 	NGPB_CUDA_CHECK(cudaGetLastError());

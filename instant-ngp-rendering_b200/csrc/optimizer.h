@@ -22,6 +22,8 @@ public:
 	void allocate(uint32_t n_weights, const std::vector<std::pair<uint32_t, uint32_t>>& layer_sizes);
 	// Optimizer::step (adam.h:159-197 inside ema.h:103-137 inside exponential_decay.h:60-71).
 	void step(cudaStream_t stream, float loss_scale, float* weights_fp32, __half* weights, const __half* gradients);
+	void step_range(cudaStream_t stream, float loss_scale, float* weights_fp32, __half* weights, const __half* gradients,
+		uint32_t begin, uint32_t end, bool adam, bool advance);
 
 	float learning_rate() const { return m_base_learning_rate * m_learning_rate_factor; }
 	void set_learning_rate(float v);

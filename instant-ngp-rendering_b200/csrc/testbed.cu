@@ -1,5 +1,6 @@
 // Testbed host logic: dataset set-up, network construction, the training step schedule.
 #include "testbed.h"
+#include "dist.h"
 
 #include <algorithm>
 #include <cmath>
@@ -202,7 +203,7 @@ void Testbed::reset_network(bool clear_density_grid) {
 	// Trainer::initialize_params (tcnn trainer.h:68-87)
 	m_n_params = m_network->n_params();
 	m_optimizer->allocate((uint32_t)m_n_params, m_network->layer_sizes());
-	const size_t n_pad = next_multiple((uint32_t)m_n_params, 8u);
+	const size_t n_pad = next_multiple((uint32_t)m_n_params, kParamPadding);
 	m_params_fp32.alloc(n_pad * sizeof(float), m_stream);
 	m_params.alloc(n_pad * sizeof(__half), m_stream);
 	m_gradients.alloc(n_pad * sizeof(__half), m_stream);

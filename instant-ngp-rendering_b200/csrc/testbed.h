@@ -13,6 +13,10 @@
 
 namespace ngpb {
 
+struct DistContext;
+// Parameter buffers are padded to a multiple of this, so that any rank count dividing 256 gets 16-byte aligned shards.
+constexpr uint32_t kParamPadding = 2048;
+
 struct NerfImage {
 	DeviceBuffer pixels;
 	ImageMeta meta{};
@@ -71,6 +75,11 @@ public:
 	void train_forward(uint32_t batch_size);
 	void train_backward(uint32_t batch_size, bool counters_final = true);
 	uint32_t shard_rank = 0, shard_world = 1;
+	// The whole sharded step inside the library (dist.cu): NCCL communicators from two unique ids, then train() runs
+	// forward / counter all-reduce / backward / reduce-scatter / sharded Adam / all-gather on every rank.
+	void init_data_parallel(const void* id_main, const void* id_aux, int rank, int world);
+	void train_dp(uint32_t batch_size);
+	bool data_parallel() const { return (bool)m_dist; }
 	NerfStepCounters* counters() { return m_counters.as<NerfStepCounters>() + (shard_world > 1 ? 2u : m_counter_slot); }
 	// Sample prefetch (no reference counterpart): once the loss kernel of step k has reported its
 	// counts, train() marches the rays of step k+1 on a second stream, under the backward pass and
@@ -211,6 +220,7 @@ private:
 	cudaStream_t m_side_stream = nullptr;
 	cudaEvent_t m_counters_ready = nullptr, m_prefetch_done = nullptr, m_mlp_done = nullptr, m_encoder_done = nullptr;
 
+	std::unique_ptr<DistContext> m_dist;
 	cudaStream_t m_stream = nullptr;
 	cudaStream_t m_own_stream = nullptr;
 	Json m_network_config;

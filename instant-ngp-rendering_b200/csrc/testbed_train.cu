@@ -1,5 +1,6 @@
 // Testbed::train and the NeRF training step (src/testbed.cu:4020-4109, src/testbed_nerf.cu:2271-2946).
 #include "testbed.h"
+#include "dist.h"
 
 #include <algorithm>
 #include <cstdlib>
@@ -82,7 +83,8 @@ void Testbed::train(uint32_t batch_size) {
 		train_image(batch_size, m_training_step % 16 == 0);
 		return;
 	}
-	if (shard_world > 1) throw std::runtime_error{"ngp-b200: a sharded testbed trains with train_begin / all-reduce / train_end"};
+	if (m_dist) { train_dp(batch_size); return; }
+	if (shard_world > 1) throw std::runtime_error{"ngp-b200: a sharded testbed trains with train_begin / all-reduce / train_end (or init_data_parallel, then train)"};
 	train_begin(batch_size);
 	train_end(batch_size);
 }

@@ -314,22 +314,42 @@ class Testbed:
         self._set("shard_rank", rank)
         self._dp = None
 
+    def init_data_parallel(self, group=None):
+        """Sharded training inside the library (csrc/dist.cu): rank 0 makes two NCCL unique ids, torch.distributed carries
+        them to the other ranks (bootstrap only), every rank builds its communicators, and from then on train() /
+        train_distributed() run the data-parallel step - reduce-scatter, sharded Adam, all-gather - without Python in
+        the data path. A C++ host does the same through ngpb_nccl_get_unique_id / ngpb_testbed_init_data_parallel."""
+        import torch.distributed as dist
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        ids = torch.zeros(256, dtype=torch.uint8)
+        if rank == 0:
+            buf = (ctypes.c_uint8 * 256)()
+            check(lib.ngpb_nccl_get_unique_id(ctypes.byref(buf)))
+            check(lib.ngpb_nccl_get_unique_id(ctypes.byref(buf, 128)))
+            ids = torch.frombuffer(bytearray(buf), dtype=torch.uint8).clone()
+        dev = ids.to(self._device) if dist.get_backend(group) == "nccl" else ids
+        dist.broadcast(dev, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        raw = bytes(dev.cpu().numpy().tobytes())
+        a, b = ctypes.create_string_buffer(raw[:128], 128), ctypes.create_string_buffer(raw[128:], 128)
+        torch.cuda.synchronize()
+        check(lib.ngpb_testbed_init_data_parallel(self._h, a, b, rank, world))
+        self._dp = None
+        self._dp_native = world > 1
+
     def train_distributed(self, batch_size=1 << 18, group=None):
-        """Testbed.train for a sharded run: local gradients, all-reduce (sum) of the gradients and
-        the step counters over `group` with torch.distributed (NCCL over NVLink on GPUs, gloo in
-        the CPU tests of the host logic), then the optimizer step on every rank. Needs
-        use_current_stream() so that the collectives are ordered with the kernels."""
-        if self._get("shard_world") <= 1:
+        """Testbed.train for a sharded run. After init_data_parallel() this is train(): the library runs the whole step.
+        Without it (the CPU tests of the host logic use gloo, which NCCL cannot replace) the protocol is driven from
+        here: local gradients, all-reduce (sum) of the counters and the gradients over `group` with torch.distributed,
+        the full optimizer step on every rank. Needs use_current_stream() so that the collectives are ordered with the
+        kernels."""
+        if getattr(self, "_dp_native", False) or self._get("shard_world") <= 1:
             check(lib.ngpb_testbed_train(self._h, batch_size))
             return
-        if getattr(self, "_dp", None) is None:
-            c = self.device_buffer("counters", torch.int32)   # fixed address while the testbed is sharded
-            self._dp = (self.device_buffer("gradients", torch.float16), c[:3], c[3:4].view(torch.float32))
+        # buffers are looked up every step: reload_network_from_json / load_snapshot / mode changes reallocate them
+        c = self.device_buffer("counters", torch.int32)
+        gradients, counts, loss_sum = self.device_buffer("gradients", torch.float16), c[:3], c[3:4].view(torch.float32)
         from .sharding import allreduce_counters, allreduce_gradients
-        gradients, counts, loss_sum = self._dp
         with_loss = self.training_step % 16 == 0   # the loss sum is only filled on these steps
-        # counters first: with the global sample count on its way to the host, the next step's rays
-        # are marched under this step's backward pass, gradient all-reduce and optimizer
         check(lib.ngpb_testbed_train_forward(self._h, batch_size))
         allreduce_counters(counts, loss_sum if with_loss else None, group=group)
         check(lib.ngpb_testbed_train_backward(self._h, batch_size))
