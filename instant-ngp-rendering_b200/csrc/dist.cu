@@ -19,6 +19,9 @@
 
 #include <dlfcn.h>
 
+#include <cstdlib>
+#include <vector>
+
 namespace ngpb {
 
 const NcclApi& NcclApi::get() {
@@ -53,8 +56,62 @@ DistContext::~DistContext() {
 		if (main) n.CommDestroy(main);
 		if (aux) n.CommDestroy(aux);
 	}
+	for (int r = 0; r < world && r < 8; ++r) {
+		if (r == rank) continue;
+		if (peer_grads[r]) cudaIpcCloseMemHandle(peer_grads[r]);
+		if (peer_params[r]) cudaIpcCloseMemHandle(peer_params[r]);
+		if (peer_flags[r]) cudaIpcCloseMemHandle(peer_flags[r]);
+	}
+	if (flags) cudaFree(flags);
 	if (aux_stream) cudaStreamDestroy(aux_stream);
 	if (forward_done) cudaEventDestroy(forward_done);
+}
+
+// Maps every rank's gradient buffer, fp16 weight buffer and flag array into this process (cudaIpc; the handles travel
+// through an all-gather on the aux communicator). The two buffers move to plain cudaMalloc memory first: pool memory
+// (cudaMallocAsync) cannot be exported. Returns false - and the step stays on NCCL - when a peer cannot be mapped.
+static bool setup_p2p(Testbed& tb, DistContext& d, DeviceBuffer& params, DeviceBuffer& grads, size_t n_pad, cudaStream_t stream) {
+	static const bool off = getenv("NGPB_DP_P2P") && atoi(getenv("NGPB_DP_P2P")) == 0;
+	if (off || d.world > 8) return false;
+	const NcclApi& n = NcclApi::get();
+	for (DeviceBuffer* b : {&params, &grads}) {
+		DeviceBuffer fresh;
+		fresh.alloc_plain(n_pad * sizeof(__half), stream);
+		NGPB_CUDA_CHECK(cudaMemcpyAsync(fresh.ptr, b->ptr, n_pad * sizeof(__half), cudaMemcpyDeviceToDevice, stream));
+		NGPB_CUDA_CHECK(cudaStreamSynchronize(stream));
+		*b = std::move(fresh);
+	}
+	NGPB_CUDA_CHECK(cudaMalloc(&d.flags, 256));
+	NGPB_CUDA_CHECK(cudaMemset(d.flags, 0, 256));
+	struct Handles { cudaIpcMemHandle_t grads, params, flags; };
+	Handles mine{};
+	NGPB_CUDA_CHECK(cudaIpcGetMemHandle(&mine.grads, grads.ptr));
+	NGPB_CUDA_CHECK(cudaIpcGetMemHandle(&mine.params, params.ptr));
+	NGPB_CUDA_CHECK(cudaIpcGetMemHandle(&mine.flags, d.flags));
+	DeviceBuffer all((size_t)d.world * sizeof(Handles), stream);
+	NGPB_CUDA_CHECK(cudaMemcpyAsync(all.as<char>() + (size_t)d.rank * sizeof(Handles), &mine, sizeof(Handles), cudaMemcpyHostToDevice, stream));
+	NGPB_NCCL_CHECK(n.AllGather(all.as<char>() + (size_t)d.rank * sizeof(Handles), all.ptr, sizeof(Handles), ncclUint8, d.aux, stream));
+	std::vector<Handles> host(d.world);
+	NGPB_CUDA_CHECK(cudaMemcpyAsync(host.data(), all.ptr, host.size() * sizeof(Handles), cudaMemcpyDeviceToHost, stream));
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(stream));
+	bool ok = true;
+	for (int r = 0; r < d.world; ++r) {
+		if (r == d.rank) { d.peer_grads[r] = grads.ptr; d.peer_params[r] = params.ptr; d.peer_flags[r] = d.flags; continue; }
+		ok = ok && cudaIpcOpenMemHandle(&d.peer_grads[r], host[r].grads, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+		ok = ok && cudaIpcOpenMemHandle(&d.peer_params[r], host[r].params, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+		ok = ok && cudaIpcOpenMemHandle(&d.peer_flags[r], host[r].flags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+	}
+	if (!ok) cudaGetLastError();
+	// every rank must take the same path: agree on the minimum
+	DeviceBuffer vote(sizeof(uint32_t), stream);
+	const uint32_t v = ok ? 1u : 0u;
+	NGPB_CUDA_CHECK(cudaMemcpyAsync(vote.ptr, &v, sizeof(v), cudaMemcpyHostToDevice, stream));
+	NGPB_NCCL_CHECK(n.AllReduce(vote.ptr, vote.ptr, 1, ncclUint32, ncclMin, d.aux, stream));
+	uint32_t agreed = 0;
+	NGPB_CUDA_CHECK(cudaMemcpyAsync(&agreed, vote.ptr, sizeof(agreed), cudaMemcpyDeviceToHost, stream));
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(stream));
+	(void)tb;
+	return agreed == 1u;
 }
 
 void Testbed::init_data_parallel(const void* id_main, const void* id_aux, int rank, int world) {
@@ -75,6 +132,8 @@ void Testbed::init_data_parallel(const void* id_main, const void* id_aux, int ra
 	NGPB_NCCL_CHECK(n.CommInitRank(&d->aux, world, b, rank));
 	NGPB_CUDA_CHECK(cudaStreamCreateWithFlags(&d->aux_stream, cudaStreamNonBlocking));
 	NGPB_CUDA_CHECK(cudaEventCreateWithFlags(&d->forward_done, cudaEventDisableTiming));
+	if (m_n_params == 0) throw std::runtime_error{"ngp-b200: init_data_parallel needs a network (reload_network_from_json first)"};
+	d->p2p = setup_p2p(*this, *d, m_params, m_gradients, next_multiple((uint32_t)m_n_params, kParamPadding), m_stream);
 	m_dist = std::move(d);
 	shard_rank = (uint32_t)rank; shard_world = (uint32_t)world;
 	touch_generator_inputs();
@@ -106,12 +165,26 @@ void Testbed::train_dp(uint32_t batch_size) {
 	const uint32_t n_pad = next_multiple((uint32_t)m_n_params, kParamPadding);
 	const uint32_t shard = n_pad / shard_world;
 	const uint32_t begin = shard_rank * shard, end = std::min(begin + shard, (uint32_t)m_n_params);
-	prof_mark(m_stream, "dp.reduce_scatter");
-	NGPB_NCCL_CHECK(n.ReduceScatter(gradients(), gradients() + begin, shard, ncclFloat16, ncclSum, d.main, m_stream));
-	prof_mark(m_stream, "optimizer");
-	m_optimizer->step_range(m_stream, kLossScaleFp16, params_fp32(), params(), gradients(), std::min(begin, (uint32_t)m_n_params), end, true, true);
-	prof_mark(m_stream, "dp.all_gather");
-	NGPB_NCCL_CHECK(n.AllGather(params() + begin, params(), shard, ncclFloat16, d.main, m_stream));
+	if (d.p2p) {
+		// reduce-scatter + Adam + all-gather in one kernel over NVLink peer memory (optimizer.cu adam_ema_step_p2p_kernel)
+		P2PPeers peers{};
+		peers.rank = d.rank; peers.world = d.world; peers.epoch = ++d.epoch;
+		for (int r = 0; r < d.world; ++r) {
+			peers.grads[r] = (const __half*)d.peer_grads[r];
+			peers.params[r] = (__half*)d.peer_params[r];
+			peers.flags[r] = (uint32_t*)d.peer_flags[r];
+		}
+		peers.error = (uint32_t*)d.flags + 32;
+		prof_mark(m_stream, "dp.fused_reduce_scatter_adam_all_gather");
+		m_optimizer->step_p2p(m_stream, kLossScaleFp16, params_fp32(), peers, std::min(begin, (uint32_t)m_n_params), end);
+	} else {
+		prof_mark(m_stream, "dp.reduce_scatter");
+		NGPB_NCCL_CHECK(n.ReduceScatter(gradients(), gradients() + begin, shard, ncclFloat16, ncclSum, d.main, m_stream));
+		prof_mark(m_stream, "optimizer");
+		m_optimizer->step_range(m_stream, kLossScaleFp16, params_fp32(), params(), gradients(), std::min(begin, (uint32_t)m_n_params), end, true, true);
+		prof_mark(m_stream, "dp.all_gather");
+		NGPB_NCCL_CHECK(n.AllGather(params() + begin, params(), shard, ncclFloat16, d.main, m_stream));
+	}
 	if (m_optimizer->custom_weights()) {
 		prof_mark(m_stream, "optimizer.ema_of_other_shards");
 		m_optimizer->step_range(m_stream, kLossScaleFp16, params_fp32(), params(), gradients(), 0, std::min(begin, (uint32_t)m_n_params), false, false);

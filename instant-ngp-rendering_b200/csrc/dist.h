@@ -38,6 +38,13 @@ struct DistContext {
 	int rank = 0, world = 1;
 	cudaStream_t aux_stream = nullptr;
 	cudaEvent_t forward_done = nullptr;
+	// peer-to-peer path (one node): every rank's gradients / fp16 weights / flags mapped here (dist.cu)
+	bool p2p = false;
+	void* peer_grads[8] = {};
+	void* peer_params[8] = {};
+	void* peer_flags[8] = {};
+	void* flags = nullptr;       // this rank's uint32 [2][8] + error word
+	uint32_t epoch = 0;
 	~DistContext();
 };
 

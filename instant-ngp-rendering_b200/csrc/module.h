@@ -28,6 +28,7 @@ struct DeviceBuffer {
 	void* ptr = nullptr;
 	size_t bytes = 0;
 	cudaStream_t stream = nullptr;
+	bool plain = false;   // cudaMalloc instead of the stream-ordered pool: memory that is exported to peer processes (cudaIpc)
 	DeviceBuffer() {}
 	DeviceBuffer(size_t n, cudaStream_t s) { alloc(n, s); }
 	DeviceBuffer(const DeviceBuffer&) = delete;
@@ -35,7 +36,7 @@ struct DeviceBuffer {
 	DeviceBuffer(DeviceBuffer&& o) noexcept { *this = std::move(o); }
 	DeviceBuffer& operator=(DeviceBuffer&& o) noexcept {
 		release();
-		ptr = o.ptr; bytes = o.bytes; stream = o.stream;
+		ptr = o.ptr; bytes = o.bytes; stream = o.stream; plain = o.plain;
 		o.ptr = nullptr; o.bytes = 0;
 		return *this;
 	}
@@ -50,8 +51,17 @@ struct DeviceBuffer {
 	}
 	// Grows only; contents are not preserved.
 	void reserve(size_t n, cudaStream_t s) { if (n > bytes) alloc(n, s); }
+	void alloc_plain(size_t n, cudaStream_t s) {
+		release();
+		if (n == 0) return;
+		stream = s;
+		bytes = n;
+		plain = true;
+		NGPB_CUDA_CHECK(cudaMalloc(&ptr, n));
+	}
 	void release() {
-		if (ptr) cudaFreeAsync(ptr, stream);
+		if (ptr) { if (plain) cudaFree(ptr); else cudaFreeAsync(ptr, stream); }
+		plain = false;
 		ptr = nullptr;
 		bytes = 0;
 	}

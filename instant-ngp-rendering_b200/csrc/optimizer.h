@@ -10,6 +10,19 @@
 
 namespace ngpb {
 
+struct AdamArgs;
+
+// Peer views of a sharded step over NVLink (Optimizer::step_p2p): base pointers of every rank's gradient buffer, fp16
+// weight buffer and rendezvous flags (uint32 [2][8], zero-initialised), mapped into this process with cudaIpc.
+struct P2PPeers {
+	int rank, world;
+	const __half* grads[8];
+	__half* params[8];
+	uint32_t* flags[8];
+	uint32_t epoch;      // 1, 2, 3 ... one per step, the same on every rank
+	uint32_t* error;     // device word of this rank, set when a rendezvous timed out
+};
+
 class Optimizer {
 public:
 	explicit Optimizer(const Json& config);
@@ -24,6 +37,8 @@ public:
 	void step(cudaStream_t stream, float loss_scale, float* weights_fp32, __half* weights, const __half* gradients);
 	void step_range(cudaStream_t stream, float loss_scale, float* weights_fp32, __half* weights, const __half* gradients,
 		uint32_t begin, uint32_t end, bool adam, bool advance);
+	// The step of shard [begin, end) fused with the gradient reduce-scatter and the weight all-gather over peer memory.
+	void step_p2p(cudaStream_t stream, float loss_scale, float* weights_fp32, const P2PPeers& peers, uint32_t begin, uint32_t end);
 
 	float learning_rate() const { return m_base_learning_rate * m_learning_rate_factor; }
 	void set_learning_rate(float v);
@@ -49,6 +64,7 @@ public:
 	}
 
 private:
+	AdamArgs make_args(float loss_scale, uint32_t begin, uint32_t end, bool adam) const;
 	void parse(const Json& config, bool construct);
 	void release();
 

@@ -141,6 +141,7 @@ void Testbed::reload_network_from_json(const Json& config) {
 }
 
 void Testbed::reset_network(bool clear_density_grid) {
+	if (m_dist) throw std::runtime_error{"ngp-b200: the network cannot be rebuilt while data parallelism is initialised (its parameter buffers are mapped by the other ranks); call init_data_parallel(world = 1) first, reload, then initialise again"};
 	if (m_mode == kModeImage) {
 		m_rng = Pcg32{seed};
 		const Json loss_config = m_network_config.value("loss", Json::object());
