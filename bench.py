@@ -678,7 +678,6 @@ def run_nerf(args):
     for _ in range(3):
         tb.render_nerf(rw, rh, view, focal, shard=shard)
     frames = 5
-    host_frame = torch.empty((rh, rw, 4), dtype=torch.float32).pin_memory()
     barrier(world)
     r0, r1 = ev(), ev()
     r0.record()
@@ -688,10 +687,13 @@ def run_nerf(args):
     torch.cuda.synchronize()
     render_ms = reduce_over_ranks(r0.elapsed_time(r1), world) / frames
     queries = reduce_over_ranks(float(tb.last_render_samples), world, op="sum")
+    # end to end: this rank's tiles (256-pixel runs, interleaved over the ranks) to pinned host memory
+    n_tiles_frame = rw * rh // 256
+    host_tiles = torch.empty((len(range(rank, n_tiles_frame, world)), 256, 4), dtype=torch.float32).pin_memory()
     t0 = time.perf_counter()
     for _ in range(frames):
         rgba, depth = tb.render_nerf(rw, rh, view, focal, shard=shard)
-        host_frame.copy_(rgba, non_blocking=True)
+        host_tiles.copy_(rgba.view(n_tiles_frame, 256, 4)[rank::world], non_blocking=True)
         torch.cuda.synchronize()
     render_e2e_ms = reduce_over_ranks((time.perf_counter() - t0) * 1e3, world) / frames
     coverage = float((rgba[..., 3] > 0.5).float().mean()) * world

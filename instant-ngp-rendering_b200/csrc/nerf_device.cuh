@@ -496,6 +496,15 @@ NGPB_HD void random_image_pos_training(Pcg32& rng, int res_x, int res_y, bool sn
 	}
 }
 
+// Empty-space skipping climbs past the scene's last cascade. The bitfield holds all 8 cascades whatever aabb_scale is,
+// and update_density_grid_mean_and_bitfield max-pools every one from the next finer (src/testbed_nerf.cu:2362-2379), so
+// cascade m > max_mip is a valid, coarser occupancy of the same scene: a 2^m / 128 voxel that is empty there contains no
+// occupied finer voxel. The reference stops the climb at max_mip (nerf_device.cuh:485-490) and crosses a large empty
+// region in steps of its coarsest voxel - up to ~220 dependent iterations on a ray through an aabb_scale 4 box, which
+// is what a render window waits for. The samples are the same: a skipped stretch holds no occupied candidate either
+// way, and both routes land on the first lattice point behind it.
+constexpr uint32_t kSkipMaxMip = kNerfCascades - 1;
+
 // ---- render-time marching (nerf_device.cuh:461-494) --------------------------------------------
 // if_unoccupied_advance_to_next_occupied_voxel<MIP_FROM_DT=false>: skip to the next occupied cell,
 // climbing to the coarsest empty cascade around the sample first. Returns kMaxDepth once the ray
@@ -509,7 +518,7 @@ NGPB_HD float advance_to_next_occupied_voxel(float t, const Stepping& s, V3 o, V
 		uint32_t mip = mip_from_pos(pos);
 		mip = mip < min_mip ? min_mip : (mip > max_mip ? max_mip : mip);
 		if (density_grid_occupied_at(pos, bitfield, mip)) return t;
-		while (mip < max_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
+		while (mip < kSkipMaxMip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
 		t = advance_to_next_voxel(t, s, pos, d, idir, mip);
 	}
 }
@@ -526,7 +535,7 @@ NGPB_HD float advance_to_next_occupied_voxel_sel(float t, const Stepping& s, V3 
 		uint32_t mip = mip_from_pos(pos);
 		mip = mip < min_mip ? min_mip : (mip > max_mip ? max_mip : mip);
 		if (density_grid_occupied_at(pos, bitfield, mip)) return t;
-		while (mip < max_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
+		while (mip < kSkipMaxMip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
 		const float n_target = to_stepping_space_sel<kCone>(t + distance_to_next_voxel(pos, d, idir, pow2i(7 - (int)mip), pow2i((int)mip - 7)), s);
 		const float n = to_stepping_space_sel<kCone>(t, s);
 		t = from_stepping_space_sel<kCone>(n + ceilf(fmaxf(n_target - n, 0.5f)), s);

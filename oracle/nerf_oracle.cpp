@@ -723,7 +723,7 @@ float advance_to_next_occupied_voxel(float t, float cone_angle, V o, V d, V idir
 		uint32_t mip = mip_from_pos(pos, CASCADES - 1);
 		if (mip > max_mip) mip = max_mip;
 		if (occupied_at(pos, bitfield, mip)) return t;
-		while (mip < max_mip && !occupied_at(pos, bitfield, mip + 1)) ++mip;
+		while (mip < CASCADES - 1 && !occupied_at(pos, bitfield, mip + 1)) ++mip;   // past the scene's last cascade: csrc/nerf_device.cuh kSkipMaxMip
 		t = advance_to_next_voxel(t, cone_angle, pos, d, idir, mip);
 	}
 }

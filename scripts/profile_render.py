@@ -22,7 +22,7 @@ for i in range(steps):
     tb.train(1 << 18)
 view = syn.look_at_ngp(np.array([0.5, 0.5, 0.5]) + 1.4 * np.array([0.62, -0.55, 0.56]))
 for shard in ((0, 1), (0, 8)):
-    for policy in ((16 << 20, 4, 8, 16), (8 << 20, 4, 32, 4), (8 << 20, 8, 64, 4), (4 << 20, 4, 32, 2)):
+    for policy in ((12 << 20, 4, 32, 4), (12 << 20, 4, 32, 8), (16 << 20, 4, 32, 4), (8 << 20, 4, 32, 4)):
         tb._set("render_target_queries", policy[0]); tb._set("render_min_steps", policy[1]); tb._set("render_max_steps", policy[2]); tb._set("render_windows_per_sync", policy[3])
         tb.render_nerf(1920, 1080, view, focal, shard=shard)
         tbm.profile_enable(True)
