@@ -129,7 +129,7 @@ int ngpb_testbed_train_end(ngpb_testbed_t* t, uint32_t batch_size) {
 	X(rays_per_batch) X(measured_batch_size) X(measured_batch_size_before_compaction) X(seed) X(random_bg_color) X(linear_colors) \
 	X(snap_to_pixel_centers) X(near_distance) X(density_grid_decay) X(render_min_transmittance) X(loss_type) X(rgb_activation) \
 	X(density_activation) X(color_space) X(train_network) X(train_encoding) X(aabb_scale) \
-	X(render_target_queries) X(render_min_steps) X(render_max_steps) X(render_windows_per_sync) X(render_snap_to_pixel_centers) \
+	X(render_target_queries) X(render_min_steps) X(render_max_steps) X(render_windows_per_sync) X(render_skip_past_last_cascade) X(render_snap_to_pixel_centers) \
 	X(shard_rank) X(shard_world) X(render_shard_rank) X(render_shard_world) X(image_snap_to_pixel_centers) X(train_prefetch) \
 	X(exposure) X(tonemap_curve) X(render_color_space) X(render_with_lens_distortion)
 

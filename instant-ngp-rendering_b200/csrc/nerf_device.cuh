@@ -527,7 +527,7 @@ NGPB_HD float advance_to_next_occupied_voxel(float t, const Stepping& s, V3 o, V
 // independent and interleave): same operations, same operands, same t.
 template <bool kCone>
 NGPB_HD float advance_to_next_occupied_voxel_sel(float t, const Stepping& s, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bitfield,
-	uint32_t min_mip, uint32_t max_mip, const Aabb& aabb)
+	uint32_t min_mip, uint32_t max_mip, const Aabb& aabb, uint32_t skip_mip = kSkipMaxMip)
 {
 	while (true) {
 		const V3 pos = o + d * t;
@@ -535,7 +535,7 @@ NGPB_HD float advance_to_next_occupied_voxel_sel(float t, const Stepping& s, V3 
 		uint32_t mip = mip_from_pos(pos);
 		mip = mip < min_mip ? min_mip : (mip > max_mip ? max_mip : mip);
 		if (density_grid_occupied_at(pos, bitfield, mip)) return t;
-		while (mip < kSkipMaxMip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
+		while (mip < skip_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
 		const float n_target = to_stepping_space_sel<kCone>(t + distance_to_next_voxel(pos, d, idir, pow2i(7 - (int)mip), pow2i((int)mip - 7)), s);
 		const float n = to_stepping_space_sel<kCone>(t, s);
 		t = from_stepping_space_sel<kCone>(n + ceilf(fmaxf(n_target - n, 0.5f)), s);

@@ -39,6 +39,7 @@ struct RenderParams {
 	uint32_t spp_index;
 	uint32_t pixel_begin, pixel_end, n_local;
 	uint32_t max_mip;
+	uint32_t skip_mip;        // coarsest cascade the empty-space skip may climb to (kSkipMaxMip; max_mip = the reference's rule)
 	uint32_t shard_rank, shard_world; // tile interleave over ranks (kRenderTile pixels per tile)
 	uint32_t capacity;        // rays per plane
 	uint32_t target_queries, min_steps, max_steps;
@@ -85,8 +86,8 @@ __global__ void __launch_bounds__(kRayBlock) render_init_rays_kernel(const __gri
 		if (alive) {
 			const V3 idir = v3(1.0f) / d;
 			t = advance_n_steps(t, stepping, ld_random_val(p.spp_index, pix * 786433u));
-			t = stepping.cone_angle <= 1e-5f ? advance_to_next_occupied_voxel_sel<false>(t, stepping, o, d, idir, bitfield, 0, p.max_mip, p.aabb)
-			                                 : advance_to_next_occupied_voxel_sel<true>(t, stepping, o, d, idir, bitfield, 0, p.max_mip, p.aabb);
+			t = stepping.cone_angle <= 1e-5f ? advance_to_next_occupied_voxel_sel<false>(t, stepping, o, d, idir, bitfield, 0, p.max_mip, p.aabb, p.skip_mip)
+			                                 : advance_to_next_occupied_voxel_sel<true>(t, stepping, o, d, idir, bitfield, 0, p.max_mip, p.aabb, p.skip_mip);
 			if (t >= kMaxDepth) alive = false;
 		}
 	}
@@ -139,7 +140,7 @@ __global__ void __launch_bounds__(kRayBlock) render_march_kernel(const __grid_co
 		float n_next = n + 1.0f; // calc_dt
 		if (!occupied) {
 			// largest empty voxel around the sample (nerf_device.cuh:485-490), then advance_to_next_voxel
-			while (mip < kSkipMaxMip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
+			while (mip < p.skip_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
 			const float n_target = to_stepping_space_sel<kCone>(t + distance_to_next_voxel(pos, d, idir, pow2i(7 - (int)mip), pow2i((int)mip - 7)), stepping);
 			n_next = n + ceilf(fmaxf(n_target - n, 0.5f));
 		}
@@ -258,6 +259,7 @@ void Testbed::render_nerf(uint32_t width, uint32_t height, const float* camera_3
 	for (int i = 0; i < 7; ++i) p.lens_params[i] = render_lens_params[i];
 	p.pixel_begin = pixel_begin; p.pixel_end = pixel_end;
 	p.max_mip = m_max_cascade;
+	p.skip_mip = render_skip_past_last_cascade ? kSkipMaxMip : m_max_cascade;
 	p.n_local = n_rays;
 	p.shard_rank = render_shard_rank; p.shard_world = render_shard_world;
 	p.capacity = next_multiple(n_rays, kBatchSizeGranularity);

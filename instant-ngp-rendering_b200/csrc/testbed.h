@@ -165,6 +165,7 @@ public:
 	uint32_t render_min_steps = 4;
 	uint32_t render_max_steps = 32;
 	uint32_t render_windows_per_sync = 4;
+	bool render_skip_past_last_cascade = true;   // nerf_device.cuh kSkipMaxMip; false = the reference's climb, up to max_cascade
 	// Tile sharding: with render_shard_world > 1 only the 256-pixel tiles t of the pixel range with
 	// t % render_shard_world == render_shard_rank are traced (the others stay untouched).
 	uint32_t render_shard_rank = 0, render_shard_world = 1;
