@@ -32,10 +32,13 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 sys.path.insert(0, os.path.join(ROOT, "baseline"))
 import configs as ref_configs  # noqa: E402  the reference's shipped configs restated; imports nothing of the product
 
-# torchrun pins OMP_NUM_THREADS=1 in its workers; the CPU legs (oracle, OpenMP) are meant to use the host's cores.
-# libgomp reads the variable when it is loaded, which happens with the oracle library, after this line.
-if os.environ.get("OMP_NUM_THREADS", "") in ("", "1"):
-    os.environ["OMP_NUM_THREADS"] = str(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
+def use_host_cores(oracle):
+    """torchrun pins OMP_NUM_THREADS=1 in its workers; the timed CPU legs (the oracle's OpenMP loops) are meant to use the
+    host's cores. Set on the oracle library only: raising the variable for the whole process made every rank's torch
+    thread pool spin on all cores and doubled the 8-GPU render time."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    oracle.set_num_threads(n)
+
 
 FOX_DIR = os.path.join(ROOT, "data_stage", "fox")   # the reference's data/nerf/fox, staged (git-ignored); absent -> synthetic fox-shaped set
 
@@ -150,6 +153,7 @@ def reduce_over_ranks(value, world, op="max"):
 def cpu_grid_baseline(budget_points):
     import numpy as np
     import oracle_binding as oracle
+    use_host_cores(oracle)
     cfg = oracle.grid_cfg(3, GRID_ENC)
     n_entries = int(oracle.grid_offsets(cfg)[-1])
     rng = np.random.default_rng(1337)
@@ -246,6 +250,7 @@ class CpuNerf:
 def cpu_nerf_baseline(n_rays, steps, warmup=0, budget_s=1e9):
     """Runs up to `steps` oracle training steps (stops early once `budget_s` of timed work is spent)."""
     import oracle_binding as oracle
+    use_host_cores(oracle)
     c = CpuNerf(n_rays)
     for _ in range(warmup):
         c.step()

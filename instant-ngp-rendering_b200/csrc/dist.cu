@@ -187,8 +187,8 @@ void Testbed::train_dp(uint32_t batch_size) {
 	}
 	if (m_optimizer->custom_weights()) {
 		prof_mark(m_stream, "optimizer.ema_of_other_shards");
-		m_optimizer->step_range(m_stream, kLossScaleFp16, params_fp32(), params(), gradients(), 0, std::min(begin, (uint32_t)m_n_params), false, false);
-		m_optimizer->step_range(m_stream, kLossScaleFp16, params_fp32(), params(), gradients(), end, (uint32_t)m_n_params, false, false);
+		m_optimizer->ema_range(m_stream, params(), 0, std::min(begin, (uint32_t)m_n_params));
+		m_optimizer->ema_range(m_stream, params(), end, (uint32_t)m_n_params);
 	}
 	prof_mark(m_stream, "end");
 	++m_training_step;

@@ -33,6 +33,12 @@ NGPB_D float pow_beta(float log2_beta, uint32_t step) {
 	return r;
 }
 
+// ema_step_half_precision / ema_step_full_precision (ema.h:46-78) with every rounding spelled out: the owner of a shard
+// (update_one) and the other ranks (ema_only_kernel) must produce the same bits, whatever the compiler would contract.
+NGPB_D float ema_filter(float prev, float w, float decay, float debias_old, float debias_new) {
+	return __fmul_rn(__fadd_rn(__fmul_rn(__fmul_rn(prev, decay), debias_old), __fmul_rn(w, __fsub_rn(1.0f, decay))), debias_new);
+}
+
 // One parameter: the arithmetic of adam_step (adam.h:72-118) followed by ema_step_half_precision /
 // ema_step_full_precision (ema.h:46-78), expression for expression.
 NGPB_D void update_one(const AdamArgs& a, uint32_t i, float grad_h, float& w_fp, __half& w_h, float& m1, float& m2, uint32_t& steps,
@@ -63,7 +69,7 @@ NGPB_D void update_one(const AdamArgs& a, uint32_t i, float grad_h, float& w_fp,
 	}
 	if (a.has_ema) {
 		const float prev = a.ema_full_precision ? *ema_tmp : __half2float(ema_h);
-		const float filtered = (prev * a.ema_decay * a.ema_debias_old + __half2float(w_h) * (1 - a.ema_decay)) * a.ema_debias_new;
+		const float filtered = ema_filter(prev, __half2float(w_h), a.ema_decay, a.ema_debias_old, a.ema_debias_new);
 		if (a.ema_full_precision) *ema_tmp = filtered;
 		ema_h = __float2half(filtered);
 	}
@@ -127,6 +133,44 @@ __global__ void __launch_bounds__(256) adam_ema_step_kernel(const __grid_constan
 			}
 		}
 	}
+}
+
+// EMA filter alone over [begin, end) (begin a multiple of 8), eight parameters per thread with 16-byte accesses: the pass a
+// rank of a sharded run makes over the shards it does not own (6 bytes per parameter: weight read, EMA read + write).
+__global__ void __launch_bounds__(256) ema_only_kernel(uint32_t begin, uint32_t end, float decay, float debias_old, float debias_new,
+	const __half* __restrict__ weights, __half* __restrict__ weights_ema)
+{
+	const uint32_t i0 = begin + (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+	if (i0 >= end) return;
+	if (i0 + 8 <= end) {
+		const uint4 w = *reinterpret_cast<const uint4*>(weights + i0);
+		uint4 e = *reinterpret_cast<const uint4*>(weights_ema + i0);
+		const __half2* w2 = reinterpret_cast<const __half2*>(&w);
+		__half2* e2 = reinterpret_cast<__half2*>(&e);
+#pragma unroll
+		for (uint32_t k = 0; k < 4; ++k) {
+			const float2 wf = __half22float2(w2[k]), ef = __half22float2(e2[k]);
+			// ema_step_half_precision (ema.h:63-78), expression for expression as in update_one
+			e2[k] = __floats2half2_rn(ema_filter(ef.x, wf.x, decay, debias_old, debias_new), ema_filter(ef.y, wf.y, decay, debias_old, debias_new));
+		}
+		*reinterpret_cast<uint4*>(weights_ema + i0) = e;
+	} else {
+		for (uint32_t i = i0; i < end; ++i) {
+			weights_ema[i] = __float2half(ema_filter(__half2float(weights_ema[i]), __half2float(weights[i]), decay, debias_old, debias_new));
+		}
+	}
+}
+
+void Optimizer::ema_range(cudaStream_t stream, const __half* weights, uint32_t begin, uint32_t end) {
+	if (!m_has_ema || begin >= end) return;
+	if (m_ema_full_precision || begin % 8 != 0 || (uintptr_t)weights % 16 != 0) {   // rare shapes take the general kernel
+		step_range(stream, 1.0f, nullptr, const_cast<__half*>(weights), weights, begin & ~3u, end, false, false);
+		return;
+	}
+	const float debias_old = 1 - (float)std::pow(m_ema_decay, m_current_step - 1), debias_new = 1.0f / (1 - (float)std::pow(m_ema_decay, m_current_step));
+	const uint32_t n_threads = div_round_up(end - begin, 8);
+	ema_only_kernel<<<div_round_up(n_threads, 256), 256, 0, stream>>>(begin, end, m_ema_decay, debias_old, debias_new, weights, m_weights_ema);
+	NGPB_CUDA_CHECK(cudaGetLastError());
 }
 
 // -------------------------------------------------------------------------------------------------

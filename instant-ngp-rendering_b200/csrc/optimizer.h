@@ -37,6 +37,8 @@ public:
 	void step(cudaStream_t stream, float loss_scale, float* weights_fp32, __half* weights, const __half* gradients);
 	void step_range(cudaStream_t stream, float loss_scale, float* weights_fp32, __half* weights, const __half* gradients,
 		uint32_t begin, uint32_t end, bool adam, bool advance);
+	// EMA filter of [begin, end) alone, for weights another rank has stepped (after the step has been opened on this rank).
+	void ema_range(cudaStream_t stream, const __half* weights, uint32_t begin, uint32_t end);
 	// The step of shard [begin, end) fused with the gradient reduce-scatter and the weight all-gather over peer memory.
 	void step_p2p(cudaStream_t stream, float loss_scale, float* weights_fp32, const P2PPeers& peers, uint32_t begin, uint32_t end);
 

@@ -29,6 +29,9 @@ static inline half_t half_mul(half_t a, half_t b) { return (half_t)((double)a * 
 extern "C" uint16_t oracle_float_to_half(float f) { return half_to_bits((half_t)f); }
 extern "C" float oracle_half_to_float(uint16_t h) { return (float)bits_to_half(h); }
 extern "C" int oracle_num_threads(void) { return omp_get_max_threads(); }
+// The thread count of the oracle's OpenMP loops (torchrun pins OMP_NUM_THREADS=1 for its workers; the timed CPU legs of
+// bench.py want the host's cores without changing the variable for the rest of the process).
+extern "C" void oracle_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 namespace {
 

@@ -183,6 +183,7 @@ void oracle_march_rays(uint32_t n, const float* rays, const uint32_t* pix, uint3
 int oracle_probe(const char* name, uint32_t n, const uint32_t* in, uint32_t k_in, uint32_t* out, uint32_t k_out);
 
 int oracle_num_threads(void);
+void oracle_set_num_threads(int n);
 
 #ifdef __cplusplus
 }

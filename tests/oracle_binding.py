@@ -132,6 +132,10 @@ def num_threads():
     return int(olib.oracle_num_threads())
 
 
+def set_num_threads(n):
+    olib.oracle_set_num_threads(ctypes.c_int(int(n)))
+
+
 # ---- fused MLP / NerfNetwork glue (oracle/mlp_oracle.cpp) ---------------------------------------
 olib.oracle_mlp_n_params.restype = ctypes.c_size_t
 olib.oracle_mlp_n_params.argtypes = [ctypes.c_uint32] * 4
