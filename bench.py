@@ -719,7 +719,7 @@ def run_nerf(args):
     if rank != 0:
         return
     cpu = cpu_nerf_baseline(n_rays=256, steps=4, budget_s=20.0)
-    gb = gpu_baseline() if world == 1 else None
+    gb = gpu_baseline() if (world == 1 and not os.environ.get("NGPB_BENCH_NO_BASELINE")) else None   # the switch exists for short ncu captures
     ref_train = (gb or {}).get("train", {}).get("samples_per_s")
     roof = None
     if dom:

@@ -148,6 +148,36 @@ def test_training_samples_bit_exact(ngp, oracle, aabb_scale, lens, n_rays):
         assert np.array_equal(rays[k].view(np.uint32), want_rays[i].view(np.uint32))
 
 
+def test_training_samples_bit_exact_at_the_bench_shape(ngp, oracle):
+    """configs[2] shape: 1080 x 1920 portrait views with the fox dataset's OpenCV lens and focal length, aabb_scale 4, the
+    exponential stepping of cone angle 1/256, a 4096-ray slice of a 2^18-sample step: per-ray counts and coordinates
+    bit-exact against the oracle (the small-image cases above cannot see index arithmetic that only overflows or rounds
+    differently at full resolution)."""
+    rng = np.random.default_rng(2024)
+    fox_lens = (0.0578421, -0.0805099, -0.000980296, 0.00015575)   # data/nerf/fox/transforms.json k1 k2 p1 p2
+    images, grid, max_cascade = _scene(oracle, rng, 3, (1080, 1920), lens=fox_lens, aabb_scale=4)
+    for im in images:   # fox intrinsics (fl_x 1375.52, fl_y 1374.49, cx 554.558 / 1080, cy 965.268 / 1920)
+        im.focal_x, im.focal_y, im.principal_x, im.principal_y = 1375.52, 1374.49, 554.558 / 1080, 965.268 / 1920
+    bitfield, mean = oracle.nerf_bitfield(max_cascade, grid)
+    n_rays, max_samples = 4096, 1 << 22
+    cfg = _config(oracle, n_rays, len(images), 4, max_cascade, max_samples, 1 << 18)
+    step_rng = oracle.Pcg32State(1337)
+    step_rng.advance(77 << 32)   # a later training step
+    want_n, want_rays, want_coords, want_total = oracle.nerf_generate_samples(cfg, images, bitfield, step_rng, max_samples)
+    assert want_total > 50000 and want_n.max() > 100
+    dev = _Device(ngp, oracle, cfg, images, bitfield, mean)
+    total, kept = _generate(ngp, oracle, cfg, dev, step_rng)
+    assert total == want_total and kept == int((want_n > 0).sum())
+    ray_indices = dev.ray_indices.cpu().numpy().view(np.uint32)[:kept]
+    numsteps = dev.numsteps.cpu().numpy().view(np.uint32)[:kept]
+    assert np.array_equal(numsteps[:, 0], want_n[ray_indices])
+    want_base = np.concatenate([[0], np.cumsum(want_n.astype(np.int64))])[:-1].astype(np.int64)
+    coords = dev.coords.cpu().numpy()
+    for k in range(kept):
+        i, n, b = int(ray_indices[k]), int(numsteps[k, 0]), int(numsteps[k, 1])
+        assert np.array_equal(coords[b:b + n].view(np.uint32), want_coords[want_base[i]:want_base[i] + n].view(np.uint32)), (k, i)
+
+
 def test_training_samples_overflow_drops_whole_rays(ngp, oracle):
     rng = np.random.default_rng(3)
     images, grid, max_cascade = _scene(oracle, rng, 3, (32, 32))
