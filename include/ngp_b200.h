@@ -93,6 +93,18 @@ int ngpb_module_backward(ngpb_module_t* m, void* stream, const ngpb_context_t* c
 	const float* input, const void* output, const void* params);
 void ngpb_context_free(ngpb_context_t* ctx);
 
+/* ngpb_module_inference without any allocation, for callers that cannot call cudaMalloc (CUDA graph capture,
+ * tight serving loops). NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same kernels, same result as ngpb_module_inference for a module made by
+ * ngpb_create_network_with_input_encoding or ngpb_create_network; the encoder's feature tiles live in a
+ * file-scope device array of NGPB_STATIC_SCRATCH_BYTES (held by every GPU that loads the library, until
+ * exit) instead of a per-call stream-ordered allocation. Limit: ceil(n / 128) * 128 * padded_encoding_width * 2 bytes must fit
+ * (n <= 65536 samples at 32 encoded features); larger batches are rejected with NGPB_ERROR and a message.
+ * All calls on one device share the array: calls that overlap on the GPU (two streams) race. */
+#define NGPB_STATIC_SCRATCH_BYTES (4u << 20)
+size_t ngpb_static_scratch_bytes(void);
+int ngpb_module_inference_static_scratch(ngpb_module_t* m, void* stream, uint32_t n, const float* input, void* output, const void* params);
+
 /* ---- grid introspection for parity tests ----------------------------------------------
  * GridOffsetTable (grid_interface.h:84-88) and per-level scale/resolution
  * (common_device.h:709-718). Arrays must hold n_levels+1 / n_levels / n_levels items.

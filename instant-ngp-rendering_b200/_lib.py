@@ -55,6 +55,8 @@ SIGNATURES = {
     "ngpb_module_layer_sizes": (c_sz, [c_vp, ctypes.POINTER(c_u32), c_sz]),
     "ngpb_module_initialize_params": (c_int, [c_vp, c_vp, c_u64, c_vp, c_f32]),
     "ngpb_module_inference": (c_int, [c_vp, c_vp, c_u32, c_vp, c_vp, c_vp]),
+    "ngpb_static_scratch_bytes": (c_sz, []),
+    "ngpb_module_inference_static_scratch": (c_int, [c_vp, c_vp, c_u32, c_vp, c_vp, c_vp]),
     "ngpb_module_forward": (c_int, [c_vp, c_vp, c_u32, c_vp, c_vp, c_vp, c_int, ctypes.POINTER(c_vp)]),
     "ngpb_module_backward": (c_int, [c_vp, c_vp, c_vp, c_u32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "ngpb_context_free": (None, [c_vp]),

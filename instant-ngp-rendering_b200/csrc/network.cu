@@ -147,6 +147,29 @@ void NetworkWithInputEncodingModule::inference(cudaStream_t stream, uint32_t n, 
 	fused_inference(stream, a);
 }
 
+// Same kernels as inference() in its default (tile-fed) mode; the only difference is where the tiles live.
+void NetworkWithInputEncodingModule::inference_with_scratch(cudaStream_t stream, uint32_t n, const float* input, __half* output, const __half* params,
+	void* scratch, size_t scratch_bytes)
+{
+	check_batch(n);
+	if (n == 0) return;
+	if (!scratch || scratch_bytes < inference_scratch_bytes(n)) throw std::runtime_error{"ngp-b200: inference_with_scratch: scratch too small"};
+	__half* tiles = (__half*)scratch;
+	encode_tiled(stream, n, input, m_n_input_dims, params, tiles);
+	if (m_has_grid && fused_grid_supported(m_net, m_grid.p)) {
+		FusedGridNetArgs f{};
+		f.net = m_net; f.grid = m_grid.p; f.n = n; f.params = params; f.grid_params = params + m_mlp.n_params();
+		f.input = input; f.in_stride = m_n_input_dims; f.out = output; f.out_stride = kMlpPaddedOut;
+		f.feat_tiles = tiles;
+		fused_grid_inference(stream, f);
+		return;
+	}
+	FusedInferenceArgs a{};
+	a.net = m_net; a.n = n; a.params = params; a.feat = tiles;
+	a.out = output; a.out_stride = kMlpPaddedOut;
+	fused_inference(stream, a);
+}
+
 std::unique_ptr<Context> NetworkWithInputEncodingModule::forward(cudaStream_t stream, uint32_t n, const float* input, __half* output,
 	const __half* params, bool /*prepare_input_gradients*/)
 {

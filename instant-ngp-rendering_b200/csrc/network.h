@@ -40,6 +40,11 @@ public:
 	// features in the tile layout of mlp.h; n is rounded up to whole tiles inside.
 	void encode_tiled(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, const __half* params, __half* feat);
 
+	// inference() with the feature-tile scratch supplied by the caller instead of a stream-ordered allocation
+	// (capi_static_scratch.cu). scratch must hold inference_scratch_bytes(n) bytes, 256-byte aligned.
+	size_t inference_scratch_bytes(uint32_t n) const { return tiled_bytes(n, m_enc_width); }
+	void inference_with_scratch(cudaStream_t stream, uint32_t n, const float* input, __half* output, const __half* params, void* scratch, size_t scratch_bytes);
+
 private:
 	uint32_t m_n_input_dims;
 	bool m_has_grid = false;
