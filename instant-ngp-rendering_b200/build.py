@@ -116,11 +116,33 @@ def build_baseline(verbose=False):
         print("[build] baseline/_ref not built (NGPB_BUILD_REFERENCE=1 or baseline/build_ref.sh builds the reference: ~25 min)")
 
 
+def stage_data(verbose=False):
+    """Copies the reference's sample inputs that bench.py measures on (data/nerf/fox, data/image/albert.exr) to the
+    git-ignored data_stage/, so that they travel to the GPU box; a no-op where /root/reference does not exist."""
+    import shutil
+    ref_data = "/root/reference/data"
+    stage = os.path.join(ROOT, "data_stage")
+    if not os.path.isdir(ref_data):
+        return
+    fox_src, fox_dst = os.path.join(ref_data, "nerf", "fox"), os.path.join(stage, "fox")
+    if os.path.isdir(fox_src) and not os.path.exists(os.path.join(fox_dst, "transforms.json")):
+        shutil.copytree(fox_src, fox_dst, dirs_exist_ok=True)
+        if verbose:
+            print(f"[build] staged {fox_dst}")
+    alb_src, alb_dst = os.path.join(ref_data, "image", "albert.exr"), os.path.join(stage, "albert.exr")
+    if os.path.exists(alb_src) and not os.path.exists(alb_dst):
+        os.makedirs(stage, exist_ok=True)
+        shutil.copyfile(alb_src, alb_dst)
+        if verbose:
+            print(f"[build] staged {alb_dst}")
+
+
 def build_all(verbose=False):
     build_cuda(verbose)
     build_oracle(verbose)
     build_ref(verbose)
     build_baseline(verbose)
+    stage_data(verbose)
 
 
 if __name__ == "__main__":
