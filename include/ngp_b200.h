@@ -347,6 +347,10 @@ int ngpb_testbed_set_render_steps_out(ngpb_testbed_t* t, uint32_t* steps);
 int ngpb_probe_resident(void* stream, uint32_t blocks, uint32_t threads, uint64_t nanoseconds);
 int ngpb_probe_gather(void* stream, const void* table, uint32_t log2_entries, uint32_t entry_bytes, uint32_t n_threads, uint32_t per_thread, uint32_t* sink);
 int ngpb_probe_scatter(void* stream, void* table, uint32_t log2_entries, uint32_t n_threads, uint32_t per_thread);
+/* vec packed f16x2 words (1, 2 or 4: 4 / 8 / 16 aligned bytes) per reduction instruction */
+int ngpb_probe_scatter_vec(void* stream, void* table, uint32_t log2_entries, uint32_t vec, uint32_t n_threads, uint32_t per_thread);
+/* `passes` coalesced 16-byte-per-lane reads of buf through L2 only (ld.global.cg): the L2 -> SM bandwidth peak */
+int ngpb_probe_l2_stream(void* stream, const void* buf, size_t bytes, uint32_t passes, uint32_t blocks, uint32_t* sink);
 
 /* ---- self test of the tcgen05 operand views (tc_device.cuh) --------------------------------
  * mode 0: D[128xN] = X[128xK] W[NxK]^T; mode 1: D[128xN] = X[128xK] W[KxN];

@@ -103,6 +103,8 @@ SIGNATURES = {
     "ngpb_probe_resident": (c_int, [c_vp, c_u32, c_u32, ctypes.c_uint64]),
     "ngpb_probe_gather": (c_int, [c_vp, c_vp, c_u32, c_u32, c_u32, c_u32, c_vp]),
     "ngpb_probe_scatter": (c_int, [c_vp, c_vp, c_u32, c_u32, c_u32]),
+    "ngpb_probe_scatter_vec": (c_int, [c_vp, c_vp, c_u32, c_u32, c_u32, c_u32]),
+    "ngpb_probe_l2_stream": (c_int, [c_vp, c_vp, c_sz, c_u32, c_u32, c_vp]),
     "ngpb_testbed_set_image": (c_int, [c_vp, c_vp, c_int, c_int, c_int]),
     "ngpb_testbed_render_image": (c_int, [c_vp, c_u32, c_u32, c_vp]),
     "ngpb_testbed_train_begin": (c_int, [c_vp, c_u32]),

@@ -145,6 +145,8 @@ int ngpb_testbed_get(const ngpb_testbed_t* t, const char* name, double* value) {
 	else if (n == "n_images") *value = tb.n_images();
 	else if (n == "last_render_samples") *value = (double)tb.last_render_samples;
 	else if (n == "prefetches_adopted") *value = (double)tb.prefetches_adopted;
+	else if (n == "l2_window_bytes") *value = tb.l2_window_bytes;
+	else if (n == "l2_window_hit_ratio") *value = tb.l2_window_hit_ratio;
 	else if (n == "optimizer_step") *value = const_cast<Testbed&>(tb).optimizer() ? const_cast<Testbed&>(tb).optimizer()->step_count() : 0;
 	else if (n == "optimizer_learning_rate_factor") *value = const_cast<Testbed&>(tb).optimizer() ? const_cast<Testbed&>(tb).optimizer()->learning_rate_factor() : 1.0;
 	else if (n == "optimizer_base_learning_rate") *value = const_cast<Testbed&>(tb).optimizer() ? const_cast<Testbed&>(tb).optimizer()->base_learning_rate() : 0.0;

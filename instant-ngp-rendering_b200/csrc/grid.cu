@@ -11,7 +11,9 @@
 // transposes (grid_interface.h:41-83).
 #include "grid_device.cuh"
 
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <limits>
 
 namespace ngpb {
@@ -290,7 +292,7 @@ template <uint32_t D, uint32_t F, bool VEC_IN>
 __global__ void __launch_bounds__(256) grid_backward_kernel(
 	const __grid_constant__ GridParams p, const uint32_t n,
 	__half* __restrict__ grad, const float* __restrict__ positions, const uint32_t in_stride,
-	const __half* __restrict__ dL_dy, const uint32_t dy_stride, const float max_level, const uint32_t tiled)
+	const __half* __restrict__ dL_dy, const uint32_t dy_stride, const float max_level, const uint32_t tiled, const uint32_t first_level)
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	const uint32_t lane = threadIdx.x % 32;
@@ -309,7 +311,7 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(
 	const __half* src = dL_dy + (size_t)i * dy_stride;
 	const uint4* tbase = reinterpret_cast<const uint4*>(dL_dy) + (size_t)(i / 128) * (dy_stride / 8) * 128 + (i % 128);
 
-	for (uint32_t l0 = 0; l0 < L; l0 += C) {
+	for (uint32_t l0 = (first_level / C) * C; l0 < L; l0 += C) {
 		alignas(16) __half g[8];
 		if (!active) {
 			*reinterpret_cast<uint4*>(g) = make_uint4(0u, 0u, 0u, 0u);
@@ -321,8 +323,104 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(
 #pragma unroll
 			for (uint32_t k = 0; k < 8; ++k) g[k] = (l0 * F + k < L * F) ? src[l0 * F + k] : __float2half(0.0f);
 		}
-		grid_scatter_chunk<D, F>(p, l0, x, g, grad, max_level, active, lane);
+		grid_scatter_chunk<D, F>(p, l0, x, g, grad, max_level, active, lane, first_level);
 	}
+}
+
+// Coarse dense levels, privatised in shared memory. On unordered batches (config 1: 2^20 uniform points) every
+// sample sends 2^D reductions into the few thousand entries of each of the coarsest levels, and the L2 serialises
+// reductions to one address: levels 0 and 1 of the L16 grid cost 0.21 ms of a 0.78 ms backward pass, five times a
+// fine level (scripts/grid_probe.py). Here a block keeps an fp32 copy of the leading `n_coarse` dense levels in its
+// shared memory (level 0: 17^3 x F floats; together at most kCoarseSmemBytes), its threads add their samples'
+// contributions there with shared-memory atomics, and at the end the block sends each touched group of 8 values to
+// the gradient table with one 16-byte vector reduction. grid_backward_kernel then starts at level n_coarse.
+// Each contribution is half(w) * half(dy) rounded to fp16 as everywhere else; the block's sum is fp32, rounded once.
+// Shared memory has native atomics for 32-bit integers only; a float add is a compare-and-swap loop either way
+// (ATOMS.CAST.SPIN). One 64-bit loop carries a feature pair, which halves the number of loops.
+NGPB_D void smem_add_float2(float2* addr, float2 v) {
+	unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
+	unsigned long long old = *a, assumed;
+	do {
+		assumed = old;
+		const float2 cur = make_float2(__uint_as_float((uint32_t)assumed), __uint_as_float((uint32_t)(assumed >> 32)));
+		const unsigned long long next = (unsigned long long)__float_as_uint(cur.x + v.x) | ((unsigned long long)__float_as_uint(cur.y + v.y) << 32);
+		old = atomicCAS(a, assumed, next);
+	} while (old != assumed);
+}
+
+constexpr uint32_t kCoarseSmemBytes = 200u * 1024u;
+constexpr uint32_t kCoarseThreads = 1024;
+
+template <uint32_t D, uint32_t F>
+__global__ void __launch_bounds__(kCoarseThreads) grid_backward_coarse_kernel(
+	const __grid_constant__ GridParams p, const uint32_t n, const uint32_t n_coarse,
+	__half* __restrict__ grad, const float* __restrict__ positions, const uint32_t in_stride,
+	const __half* __restrict__ dL_dy, const uint32_t dy_stride, const float max_level, const uint32_t tiled)
+{
+	extern __shared__ __align__(16) float coarse_acc[];
+	constexpr uint32_t NC = 1u << D;
+	const uint32_t total = (p.offset[n_coarse - 1] + p.size[n_coarse - 1]) * F;   // floats; a multiple of 8
+	for (uint32_t e = threadIdx.x; e < total / 4; e += blockDim.x) reinterpret_cast<float4*>(coarse_acc)[e] = make_float4(0.f, 0.f, 0.f, 0.f);
+	__syncthreads();
+
+	const uint32_t lane = threadIdx.x % 32;
+	for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < n; i0 += gridDim.x * blockDim.x) {   // block-uniform trip count
+		const uint32_t i = i0 + threadIdx.x;
+		const bool active = i < n;
+		float x[D];
+#pragma unroll
+		for (uint32_t d = 0; d < D; ++d) x[d] = 0.0f;
+		if (active) load_position<D>(positions, in_stride, i, x);
+		for (uint32_t level = 0; level < n_coarse; ++level) {
+			if (grid_level_masked_bwd(p, level, max_level)) continue;
+			__half2 g2[F / 2];
+#pragma unroll
+			for (uint32_t f = 0; f < F / 2; ++f) g2[f] = __float2half2_rn(0.0f);
+			if (active) {
+				const __half* src = tiled ? dL_dy + (((size_t)(i / 128) * (dy_stride / 8) + (level * F) / 8) * 128 + (i % 128)) * 8 + (level * F) % 8
+				                          : dL_dy + (size_t)i * dy_stride + level * F;
+#pragma unroll
+				for (uint32_t f = 0; f < F / 2; ++f) g2[f] = __halves2half2(src[2 * f], src[2 * f + 1]);
+			}
+			GridCellT<D> cell;
+			grid_cell<D>(p, level, x, cell);
+			float2 acc[NC][F / 2];
+#pragma unroll
+			for (uint32_t k = 0; k < NC; ++k) {
+				const __half2 w = __float2half2_rn(active ? grid_corner_weight<D>(cell, k) : 0.0f);
+#pragma unroll
+				for (uint32_t f = 0; f < F / 2; ++f) acc[k][f] = __half22float2(__hmul2(w, g2[f]));
+			}
+			// ordered batches (stratified image samples, rays): neighbouring lanes share a cell; one lane adds the run's sum
+			const uint32_t heads = grid_run_heads<D>(cell, active, lane);
+			if (heads != 0xFFFFFFFFu) grid_run_reduce<NC, F / 2>(acc, heads, lane);
+			if (active && ((heads >> lane) & 1u)) {
+				float* level_acc = coarse_acc + (size_t)p.offset[level] * F;
+#pragma unroll
+				for (uint32_t k = 0; k < NC; ++k) {
+					float* dst = level_acc + (size_t)grid_corner_index<D>(p, level, cell, k) * F;
+#pragma unroll
+					for (uint32_t f = 0; f < F / 2; ++f) smem_add_float2(reinterpret_cast<float2*>(dst) + f, acc[k][f]);
+				}
+			}
+		}
+	}
+	__syncthreads();
+
+	for (uint32_t e = threadIdx.x; e < total / 8; e += blockDim.x) {
+		const float4 a = reinterpret_cast<const float4*>(coarse_acc)[2 * e], b = reinterpret_cast<const float4*>(coarse_acc)[2 * e + 1];
+		if (a.x == 0.f && a.y == 0.f && a.z == 0.f && a.w == 0.f && b.x == 0.f && b.y == 0.f && b.z == 0.f && b.w == 0.f) continue;
+		red_add_half2x4(grad + (size_t)e * 8, __floats2half2_rn(a.x, a.y), __floats2half2_rn(a.z, a.w), __floats2half2_rn(b.x, b.y), __floats2half2_rn(b.z, b.w));
+	}
+}
+
+// Leading dense levels that fit the block's shared memory together (0: the coarse kernel is not used).
+static uint32_t coarse_levels(const GridParams& p, uint32_t n) {
+	static const bool off = getenv("NGPB_GRID_COARSE") && atoi(getenv("NGPB_GRID_COARSE")) == 0;
+	if (off || n < (1u << 16) || p.interpolation_type == (int)InterpolationType::Nearest || p.n_features_per_level == 1) return 0;
+	uint32_t k = 0;
+	while (k < p.n_levels && !p.use_hash[k] && (size_t)(p.offset[k] + p.size[k]) * p.n_features_per_level * sizeof(float) <= kCoarseSmemBytes) ++k;
+	return k;
 }
 
 // Input gradient, recomputing dy/dx from the table (fp32 math as grid.h:172-211, 322-349).
@@ -452,7 +550,7 @@ void grid_forward(cudaStream_t stream, const GridParams& p, uint32_t n, const __
 }
 
 void grid_backward(cudaStream_t stream, const GridParams& p, uint32_t n, __half* grad,
-	const float* positions, uint32_t in_stride, const __half* dL_dy, uint32_t dy_stride, float max_level, bool tiled)
+	const float* positions, uint32_t in_stride, const __half* dL_dy, uint32_t dy_stride, float max_level, bool tiled, bool ordered)
 {
 	if (n == 0) return;
 	const uint32_t blocks = div_round_up(n, 256);
@@ -460,9 +558,23 @@ void grid_backward(cudaStream_t stream, const GridParams& p, uint32_t n, __half*
 	if (tiled && (!vec || dy_stride % 8 != 0 || (p.n_levels * p.n_features_per_level) % 8 != 0)) {
 		throw std::runtime_error{"GridEncoding: tiled gradients need a 16-byte aligned buffer and a feature count that is a multiple of 8"};
 	}
+	static const bool coarse_for_ordered = getenv("NGPB_GRID_COARSE_ORDERED") && atoi(getenv("NGPB_GRID_COARSE_ORDERED")) != 0;
+	const uint32_t n_coarse = (ordered && !coarse_for_ordered) ? 0u : coarse_levels(p, n);
 	NGPB_GRID_DISPATCH(p.n_dims, p.n_features_per_level, {
-		if (vec) grid_backward_kernel<D, F, true><<<blocks, 256, 0, stream>>>(p, n, grad, positions, in_stride, dL_dy, dy_stride, max_level, tiled ? 1u : 0u);
-		else grid_backward_kernel<D, F, false><<<blocks, 256, 0, stream>>>(p, n, grad, positions, in_stride, dL_dy, dy_stride, max_level, 0u);
+		if constexpr (F >= 2) {
+			if (n_coarse > 0) {
+				const uint32_t smem = (p.offset[n_coarse - 1] + p.size[n_coarse - 1]) * F * (uint32_t)sizeof(float);
+				static bool attr_set = false;   // per instantiation
+				if (!attr_set) {
+					NGPB_CUDA_CHECK(cudaFuncSetAttribute(grid_backward_coarse_kernel<D, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCoarseSmemBytes));
+					attr_set = true;
+				}
+				const uint32_t coarse_blocks = std::min((uint32_t)sm_count(), div_round_up(n, kCoarseThreads));
+				grid_backward_coarse_kernel<D, F><<<coarse_blocks, kCoarseThreads, smem, stream>>>(p, n, n_coarse, grad, positions, in_stride, dL_dy, dy_stride, max_level, tiled ? 1u : 0u);
+			}
+		}
+		if (vec) grid_backward_kernel<D, F, true><<<blocks, 256, 0, stream>>>(p, n, grad, positions, in_stride, dL_dy, dy_stride, max_level, tiled ? 1u : 0u, n_coarse);
+		else grid_backward_kernel<D, F, false><<<blocks, 256, 0, stream>>>(p, n, grad, positions, in_stride, dL_dy, dy_stride, max_level, 0u, n_coarse);
 	});
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }

@@ -78,8 +78,10 @@ void grid_forward(cudaStream_t stream, const GridParams& p, uint32_t n, const __
 // dL_dy: fp16 AoS with the same layout as `out`. grad: fp16 [entries][F], must be zeroed by
 // the caller when overwrite semantics are wanted (the reference zeroes at grid.h:857-859;
 // ngpb_module_backward does the memset).
+// ordered: consecutive samples are neighbours in space (ray-ordered NeRF batches): the warp-aggregated scatter alone is
+// used. Otherwise (uniform / stratified points) the coarsest dense levels are accumulated in shared memory first.
 void grid_backward(cudaStream_t stream, const GridParams& p, uint32_t n, __half* grad,
-	const float* positions, uint32_t in_stride, const __half* dL_dy, uint32_t dy_stride, float max_level, bool tiled = false);
+	const float* positions, uint32_t in_stride, const __half* dL_dy, uint32_t dy_stride, float max_level, bool tiled = false, bool ordered = false);
 
 // dL_dx[i][d] = sum_k dL_dy[i][k] * dy_k/dx_d, recomputed from the table (the reference
 // stores dy_dx in the forward pass and contracts in kernel_grid_backward_input, grid.h:322-349).

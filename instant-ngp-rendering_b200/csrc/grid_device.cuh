@@ -74,6 +74,11 @@ NGPB_D float grid_corner_weight(const GridCellT<D>& c, uint32_t corner) {
 	return weight;
 }
 
+#ifndef NGPB_GRID_PAIR_LOADS
+#define NGPB_GRID_PAIR_LOADS 1
+#endif
+constexpr bool kGridPairLoads = NGPB_GRID_PAIR_LOADS != 0;
+
 // One table entry = F halves, loaded with one instruction of F*2 bytes.
 template <uint32_t F> struct GridEntry;
 template <> struct GridEntry<1> { __half v; };
@@ -124,8 +129,33 @@ NGPB_D void grid_encode_level(const GridParams& p, uint32_t level, const float (
 
 	constexpr uint32_t NC = 1u << D;
 	GridEntry<F> e[NC];
+	if constexpr (kGridPairLoads && (F == 2 || F == 4)) {
+		// x-neighbours that form one aligned entry pair (see grid_red_pair) come with one load of 2 F halves
 #pragma unroll
-	for (uint32_t k = 0; k < NC; ++k) e[k] = grid_load<F>(base, grid_corner_index<D>(p, level, c, k));
+		for (uint32_t k = 0; k < NC; k += 2) {
+			const uint32_t i0 = grid_corner_index<D>(p, level, c, k), i1 = grid_corner_index<D>(p, level, c, k + 1);
+			if ((i0 ^ i1) == 1u) {
+				const bool swap = i0 > i1;
+				if constexpr (F == 2) {
+					const uint2 r = __ldg(reinterpret_cast<const uint2*>(base) + (i0 >> 1));
+					e[k].v[0] = *reinterpret_cast<const __half2*>(swap ? &r.y : &r.x);
+					e[k + 1].v[0] = *reinterpret_cast<const __half2*>(swap ? &r.x : &r.y);
+				} else {
+					const uint4 r = __ldg(reinterpret_cast<const uint4*>(base) + (i0 >> 1));
+					const uint2 lo = make_uint2(r.x, r.y), hi = make_uint2(r.z, r.w);
+					const uint2 a = swap ? hi : lo, b = swap ? lo : hi;
+					e[k].v[0] = *reinterpret_cast<const __half2*>(&a.x); e[k].v[1] = *reinterpret_cast<const __half2*>(&a.y);
+					e[k + 1].v[0] = *reinterpret_cast<const __half2*>(&b.x); e[k + 1].v[1] = *reinterpret_cast<const __half2*>(&b.y);
+				}
+			} else {
+				e[k] = grid_load<F>(base, i0);
+				e[k + 1] = grid_load<F>(base, i1);
+			}
+		}
+	} else {
+#pragma unroll
+		for (uint32_t k = 0; k < NC; ++k) e[k] = grid_load<F>(base, grid_corner_index<D>(p, level, c, k));
+	}
 
 	if constexpr (F == 1) {
 		__half acc = __float2half(0.0f);
@@ -192,14 +222,75 @@ NGPB_D void grid_scatter_entry(__half* level_grad, uint32_t idx, float weight, c
 	}
 }
 
+// The two x-neighbours of a corner pair. Under the coherent-prime hash (x is multiplied by 1 and XORed in) and in the
+// dense layout (x has stride 1) they are the two halves of one ALIGNED entry pair whenever the lower x is even - half
+// of all cells: idx0 ^ idx1 == 1. Then one vector reduction carries both entries. The L2 retires vector reductions
+// at the rate of scalar ones (scripts/grid_probe.py: 208-219 G instr/s for 4-, 8- and 16-byte reds alike), so this
+// removes a quarter of the scatter's L2 operations. Values and rounding are those of two separate reductions.
+template <uint32_t F>
+NGPB_D void grid_red_pair(__half* level_grad, uint32_t idx0, uint32_t idx1, const __half2* v0, const __half2* v1) {
+	if constexpr (F == 2 || F == 4) {
+		if ((idx0 ^ idx1) == 1u) {
+			const bool swap = idx0 > idx1;
+			const __half2* lo = swap ? v1 : v0;
+			const __half2* hi = swap ? v0 : v1;
+			__half* addr = level_grad + (size_t)(idx0 & ~1u) * F;
+			if constexpr (F == 2) red_add_half2x2(addr, lo[0], hi[0]);
+			else red_add_half2x4(addr, lo[0], lo[1], hi[0], hi[1]);
+			return;
+		}
+	}
+	if constexpr (F == 2) {
+		red_add_half2(level_grad + (size_t)idx0 * F, v0[0]);
+		red_add_half2(level_grad + (size_t)idx1 * F, v1[0]);
+	} else if constexpr (F == 4) {
+		red_add_half2x2(level_grad + (size_t)idx0 * F, v0[0], v0[1]);
+		red_add_half2x2(level_grad + (size_t)idx1 * F, v1[0], v1[1]);
+	} else {
+		red_add_half2x4(level_grad + (size_t)idx0 * F, v0[0], v0[1], v0[2], v0[3]);
+		red_add_half2x4(level_grad + (size_t)idx1 * F, v1[0], v1[1], v1[2], v1[3]);
+	}
+}
+
+// Runs of consecutive lanes whose samples fall into the same cell of a level: bit l of the result is set when lane l
+// starts a run (inactive lanes are runs of their own). Must be called by all 32 lanes.
+template <uint32_t D>
+NGPB_D uint32_t grid_run_heads(const GridCellT<D>& cell, bool active, uint32_t lane) {
+	bool same = lane != 0;
+#pragma unroll
+	for (uint32_t d = 0; d < D; ++d) same = (__shfl_up_sync(0xFFFFFFFFu, cell.lo[d], 1) == cell.lo[d]) && same;
+	const bool prev_active = __shfl_up_sync(0xFFFFFFFFu, (int)active, 1) != 0;
+	return __ballot_sync(0xFFFFFFFFu, !(same && active && prev_active));
+}
+
+// Segmented shuffle reduction over those runs: on exit the first lane of every run holds the run's sums.
+template <uint32_t NC, uint32_t H>
+NGPB_D void grid_run_reduce(float2 (&acc)[NC][H], uint32_t heads, uint32_t lane) {
+	// lane takes the partial sum of lane + o while no run starts in (lane, lane + o]
+	const uint32_t later_heads = lane == 31 ? 0xFFFFFFFFu : (heads >> (lane + 1));
+#pragma unroll
+	for (uint32_t o = 1; o < 32; o <<= 1) {
+		const bool take = lane + o < 32 && (later_heads & ((1u << o) - 1u)) == 0;
+#pragma unroll
+		for (uint32_t k = 0; k < NC; ++k) {
+#pragma unroll
+			for (uint32_t f = 0; f < H; ++f) {
+				const float tx = __shfl_down_sync(0xFFFFFFFFu, acc[k][f].x, o), ty = __shfl_down_sync(0xFFFFFFFFu, acc[k][f].y, o);
+				if (take) { acc[k][f].x += tx; acc[k][f].y += ty; }
+			}
+		}
+	}
+}
+
 // Gradient scatter of one 16-byte chunk of dL/dy (levels l0 .. l0 + 8/F - 1) of one sample, warp-aggregated:
 // lanes of a warp whose samples fall into the same cell of a level (runs of consecutive lanes: NeRF batches are
 // ray-ordered) are found with one ballot, their contributions summed in fp32 by a segmented shuffle reduction,
 // and the run's first lane issues one red.global.add.f16x2 per entry. Must be called by all 32 lanes.
 // Each contribution is half(w) * half(dy) rounded to fp16 as in the reference (grid.h:302-311).
+// Levels below first_level are skipped (grid_backward_coarse_kernel has taken them).
 template <uint32_t D, uint32_t F>
 NGPB_D void grid_scatter_chunk(const GridParams& p, uint32_t l0, const float (&x)[D], const __half* g, __half* __restrict__ grad,
-	float max_level, bool active, uint32_t lane)
+	float max_level, bool active, uint32_t lane, uint32_t first_level = 0)
 {
 	constexpr uint32_t C = 8 / F;
 	constexpr uint32_t NC = 1u << D;
@@ -208,7 +299,7 @@ NGPB_D void grid_scatter_chunk(const GridParams& p, uint32_t l0, const float (&x
 #pragma unroll
 	for (uint32_t c = 0; c < C; ++c) {
 		const uint32_t level = l0 + c;
-		if (level >= L || grid_level_masked_bwd(p, level, max_level)) continue; // warp-uniform
+		if (level >= L || level < first_level || grid_level_masked_bwd(p, level, max_level)) continue; // warp-uniform
 		GridCellT<D> cell;
 		grid_cell<D>(p, level, x, cell);
 		__half* level_grad = grad + (size_t)p.offset[level] * F;
@@ -218,14 +309,8 @@ NGPB_D void grid_scatter_chunk(const GridParams& p, uint32_t l0, const float (&x
 		}
 		if constexpr (kAggregate) {
 			// runs of equal cells among consecutive lanes
-			bool same = lane != 0;
-#pragma unroll
-			for (uint32_t d = 0; d < D; ++d) same = (__shfl_up_sync(0xFFFFFFFFu, cell.lo[d], 1) == cell.lo[d]) && same;
-			const bool prev_active = __shfl_up_sync(0xFFFFFFFFu, (int)active, 1) != 0;
-			const uint32_t heads = __ballot_sync(0xFFFFFFFFu, !(same && active && prev_active));
+			const uint32_t heads = grid_run_heads<D>(cell, active, lane);
 			if (heads != 0xFFFFFFFFu) {
-				// lane takes the partial sum of lane + o while no run starts in (lane, lane + o]
-				const uint32_t later_heads = lane == 31 ? 0xFFFFFFFFu : (heads >> (lane + 1));
 				const __half2* g2 = reinterpret_cast<const __half2*>(&g[c * F]);
 				float2 acc[NC][F / 2];
 #pragma unroll
@@ -234,34 +319,35 @@ NGPB_D void grid_scatter_chunk(const GridParams& p, uint32_t l0, const float (&x
 #pragma unroll
 					for (uint32_t f = 0; f < F / 2; ++f) acc[k][f] = __half22float2(__hmul2(w, g2[f]));
 				}
-#pragma unroll
-				for (uint32_t o = 1; o < 32; o <<= 1) {
-					const bool take = lane + o < 32 && (later_heads & ((1u << o) - 1u)) == 0;
-#pragma unroll
-					for (uint32_t k = 0; k < NC; ++k) {
-#pragma unroll
-						for (uint32_t f = 0; f < F / 2; ++f) {
-							const float tx = __shfl_down_sync(0xFFFFFFFFu, acc[k][f].x, o), ty = __shfl_down_sync(0xFFFFFFFFu, acc[k][f].y, o);
-							if (take) { acc[k][f].x += tx; acc[k][f].y += ty; }
-						}
-					}
-				}
+				grid_run_reduce<NC, F / 2>(acc, heads, lane);
 				if (active && ((heads >> lane) & 1u)) {
 #pragma unroll
-					for (uint32_t k = 0; k < NC; ++k) {
-						__half* addr = level_grad + (size_t)grid_corner_index<D>(p, level, cell, k) * F;
-						if constexpr (F == 2) red_add_half2(addr, __float22half2_rn(acc[k][0]));
-						else if constexpr (F == 4) red_add_half2x2(addr, __float22half2_rn(acc[k][0]), __float22half2_rn(acc[k][1]));
-						else red_add_half2x4(addr, __float22half2_rn(acc[k][0]), __float22half2_rn(acc[k][1]), __float22half2_rn(acc[k][2]), __float22half2_rn(acc[k][3]));
+					for (uint32_t k = 0; k < NC; k += 2) {
+						__half2 v0[F / 2], v1[F / 2];
+#pragma unroll
+						for (uint32_t f = 0; f < F / 2; ++f) { v0[f] = __float22half2_rn(acc[k][f]); v1[f] = __float22half2_rn(acc[k + 1][f]); }
+						grid_red_pair<F>(level_grad, grid_corner_index<D>(p, level, cell, k), grid_corner_index<D>(p, level, cell, k + 1), v0, v1);
 					}
 				}
 				continue;
 			}
 		}
 		if (!active) continue;
+		if constexpr (F >= 2) {
+			const __half2* g2 = reinterpret_cast<const __half2*>(&g[c * F]);
 #pragma unroll
-		for (uint32_t k = 0; k < NC; ++k) {
-			grid_scatter_entry<F>(level_grad, grid_corner_index<D>(p, level, cell, k), grid_corner_weight<D>(cell, k), &g[c * F]);
+			for (uint32_t k = 0; k < NC; k += 2) {
+				const __half2 w0 = __float2half2_rn(grid_corner_weight<D>(cell, k)), w1 = __float2half2_rn(grid_corner_weight<D>(cell, k + 1));
+				__half2 v0[F / 2], v1[F / 2];
+#pragma unroll
+				for (uint32_t f = 0; f < F / 2; ++f) { v0[f] = __hmul2(w0, g2[f]); v1[f] = __hmul2(w1, g2[f]); }
+				grid_red_pair<F>(level_grad, grid_corner_index<D>(p, level, cell, k), grid_corner_index<D>(p, level, cell, k + 1), v0, v1);
+			}
+		} else {
+#pragma unroll
+			for (uint32_t k = 0; k < NC; ++k) {
+				grid_scatter_entry<F>(level_grad, grid_corner_index<D>(p, level, cell, k), grid_corner_weight<D>(cell, k), &g[c * F]);
+			}
 		}
 	}
 }

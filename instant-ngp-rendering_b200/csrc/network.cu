@@ -208,7 +208,7 @@ void NetworkWithInputEncodingModule::backward(cudaStream_t stream, const Context
 			f.grid_grad = ggrad;
 		}
 		fused_grid_train(stream, f);
-		if (tiles && ggrad) grid_backward(stream, m_grid.p, n, ggrad, input, m_n_input_dims, dfeat.as<__half>(), m_enc_width, 1.0f, true);
+		if (tiles && ggrad) grid_backward(stream, m_grid.p, n, ggrad, input, m_n_input_dims, dfeat.as<__half>(), m_enc_width, 1.0f, true, m_ordered_batches);
 		return;
 	}
 	const bool need_dfeat = m_has_grid && (dL_dparams || dL_dinput);
@@ -228,7 +228,7 @@ void NetworkWithInputEncodingModule::backward(cudaStream_t stream, const Context
 	if (m_has_grid && dL_dparams) {
 		__half* ggrad = dL_dparams + m_mlp.n_params();
 		NGPB_CUDA_CHECK(cudaMemsetAsync(ggrad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
-		grid_backward(stream, m_grid.p, n, ggrad, input, m_n_input_dims, dfeat.as<__half>(), m_enc_width, 1.0f, true);
+		grid_backward(stream, m_grid.p, n, ggrad, input, m_n_input_dims, dfeat.as<__half>(), m_enc_width, 1.0f, true, m_ordered_batches);
 	}
 	if (dL_dinput) {
 		DeviceBuffer aos{(size_t)n * m_enc_width * sizeof(__half), stream};
@@ -445,7 +445,7 @@ void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const 
 		if (tiles) {
 			prof_mark(stream, "train.grid_backward");
 			NGPB_CUDA_CHECK(cudaMemsetAsync(ggrad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
-			grid_backward(stream, m_grid.p, n, ggrad, input, in_stride, m_scratch_dfeat.as<__half>(), m_pos_width, 1.0f, true);
+			grid_backward(stream, m_grid.p, n, ggrad, input, in_stride, m_scratch_dfeat.as<__half>(), m_pos_width, 1.0f, true, true);
 		}
 		return;
 	}
@@ -469,7 +469,7 @@ void NerfNetworkModule::backward_strided(cudaStream_t stream, uint32_t n, const 
 	prof_mark(stream, "train.grid_backward");
 	__half* ggrad = dL_dparams + pos_encoding_param_offset();
 	NGPB_CUDA_CHECK(cudaMemsetAsync(ggrad, 0, (size_t)m_grid.n_params * sizeof(__half), stream));
-	grid_backward(stream, m_grid.p, n, ggrad, input, in_stride, m_scratch_dfeat.as<__half>(), m_pos_width, 1.0f, true);
+	grid_backward(stream, m_grid.p, n, ggrad, input, in_stride, m_scratch_dfeat.as<__half>(), m_pos_width, 1.0f, true, true);
 }
 
 void NerfNetworkModule::inference(cudaStream_t stream, uint32_t n, const float* input, __half* output, const __half* params) {

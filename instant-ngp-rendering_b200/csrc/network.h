@@ -36,6 +36,8 @@ public:
 	const GridConfig* grid_config() const { return m_has_grid ? &m_grid : nullptr; }
 	size_t encoding_param_offset() const { return m_mlp.n_params(); }
 	const FusedNet& net() const { return m_net; }
+	// Consecutive samples of a batch are neighbours in space (stratified image positions): grid_backward's `ordered`.
+	void set_ordered_batches(bool ordered) { m_ordered_batches = ordered; }
 
 	// features in the tile layout of mlp.h; n is rounded up to whole tiles inside.
 	void encode_tiled(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, const __half* params, __half* feat);
@@ -48,6 +50,7 @@ public:
 private:
 	uint32_t m_n_input_dims;
 	bool m_has_grid = false;
+	bool m_ordered_batches = false;
 	GridConfig m_grid;
 	uint32_t m_enc_width = 0; // padded to 16
 	MlpShape m_mlp;

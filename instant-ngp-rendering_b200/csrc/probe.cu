@@ -37,6 +37,42 @@ __global__ void __launch_bounds__(256) scatter_probe_kernel(__half* __restrict__
 	}
 }
 
+// Vector reductions: V packed f16x2 words (4 V bytes, aligned) per instruction - what merging the two x-neighbours of
+// a corner pair (adjacent entries under the coherent-prime hash when the lower x is even) buys at the L2.
+template <uint32_t V>
+__global__ void __launch_bounds__(256) scatter_vec_probe_kernel(__half* __restrict__ table, uint32_t mask, uint32_t per_thread) {
+	const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t idx = tid * 2654435761u + 12345u;
+	const uint32_t one = 0x00010001u;
+	for (uint32_t k = 0; k < per_thread; ++k) {
+		idx = idx * 1664525u + 1013904223u;
+		const uint32_t j = ((idx >> 7) & mask) & ~(V - 1u);
+		__half* addr = table + 2 * (size_t)j;
+		if constexpr (V == 1) asm volatile("red.relaxed.gpu.global.add.noftz.f16x2 [%0], %1;" ::"l"(addr), "r"(one) : "memory");
+		else if constexpr (V == 2) asm volatile("red.relaxed.gpu.global.add.noftz.v2.f16x2 [%0], {%1, %1};" ::"l"(addr), "r"(one) : "memory");
+		else asm volatile("red.relaxed.gpu.global.add.noftz.v4.f16x2 [%0], {%1, %1, %1, %1};" ::"l"(addr), "r"(one) : "memory");
+	}
+}
+
+// Streaming read of an L2-resident buffer (ld.global.cg: no L1), 16 bytes per lane, fully coalesced: the L2 -> SM
+// bandwidth peak that a sector count is measured against (grid.roofline in bench.py).
+__global__ void __launch_bounds__(256) l2_stream_probe_kernel(const uint4* __restrict__ buf, uint32_t n_vec, uint32_t passes, uint32_t* __restrict__ sink) {
+	uint32_t acc = 0;
+	for (uint32_t pass = 0; pass < passes; ++pass) {
+		for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += 4 * gridDim.x * blockDim.x) {
+			uint4 v[4];
+#pragma unroll
+			for (uint32_t u = 0; u < 4; ++u) {
+				const uint32_t j = i + u * gridDim.x * blockDim.x;
+				v[u] = j < n_vec ? __ldcg(buf + j) : make_uint4(0u, 0u, 0u, 0u);
+			}
+#pragma unroll
+			for (uint32_t u = 0; u < 4; ++u) acc ^= v[u].x ^ v[u].y ^ v[u].z ^ v[u].w;
+		}
+	}
+	if (acc == 0x9E3779B9u) sink[0] = acc;
+}
+
 // Blocks that stay resident for `ns` nanoseconds without issuing work (they sleep): what a kernel
 // loses by SHARING its SMs with other blocks, as opposed to competing with them.
 __global__ void resident_probe_kernel(unsigned long long ns) {
@@ -80,6 +116,31 @@ extern "C" int ngpb_probe_scatter(void* stream, void* table, uint32_t log2_entri
 	try {
 		if (log2_entries == 0 || log2_entries > 30) throw std::runtime_error{"ngpb_probe_scatter: log2_entries in 1..30"};
 		scatter_probe_kernel<<<div_round_up(n_threads, 256), 256, 0, (cudaStream_t)stream>>>((__half*)table, (1u << log2_entries) - 1, per_thread);
+		NGPB_CUDA_CHECK(cudaGetLastError());
+		return NGPB_OK;
+	} catch (const std::exception& e) { set_last_error(e.what()); return NGPB_ERROR; }
+}
+
+extern "C" int ngpb_probe_scatter_vec(void* stream, void* table, uint32_t log2_entries, uint32_t vec, uint32_t n_threads, uint32_t per_thread) {
+	using namespace ngpb;
+	try {
+		if (log2_entries < 2 || log2_entries > 30) throw std::runtime_error{"ngpb_probe_scatter_vec: log2_entries in 2..30"};
+		const uint32_t mask = (1u << log2_entries) - 1, blocks = div_round_up(n_threads, 256);
+		cudaStream_t s = (cudaStream_t)stream;
+		if (vec == 1) scatter_vec_probe_kernel<1><<<blocks, 256, 0, s>>>((__half*)table, mask, per_thread);
+		else if (vec == 2) scatter_vec_probe_kernel<2><<<blocks, 256, 0, s>>>((__half*)table, mask, per_thread);
+		else if (vec == 4) scatter_vec_probe_kernel<4><<<blocks, 256, 0, s>>>((__half*)table, mask, per_thread);
+		else throw std::runtime_error{"ngpb_probe_scatter_vec: vec must be 1, 2 or 4"};
+		NGPB_CUDA_CHECK(cudaGetLastError());
+		return NGPB_OK;
+	} catch (const std::exception& e) { set_last_error(e.what()); return NGPB_ERROR; }
+}
+
+extern "C" int ngpb_probe_l2_stream(void* stream, const void* buf, size_t bytes, uint32_t passes, uint32_t blocks, uint32_t* sink) {
+	using namespace ngpb;
+	try {
+		if (bytes < 16 || bytes > (1ull << 32) || passes == 0 || blocks == 0) throw std::runtime_error{"ngpb_probe_l2_stream: 16 B .. 4 GiB, passes and blocks >= 1"};
+		l2_stream_probe_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)buf, (uint32_t)(bytes / 16), passes, sink);
 		NGPB_CUDA_CHECK(cudaGetLastError());
 		return NGPB_OK;
 	} catch (const std::exception& e) { set_last_error(e.what()); return NGPB_ERROR; }

@@ -216,7 +216,42 @@ void Testbed::reset_network(bool clear_density_grid) {
 	m_training_step = 0;
 	n_rays_total = 0;
 	m_loss_scalar = 0.0f;
+	apply_l2_access_policy();
 	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+}
+
+// Hash tables larger than L2 (config 5: T = 2^22, 202 MB of fp16 features against 126 MB): an access-policy window over
+// the table of the fp16 working copy asks L2 to keep as much of it as its persisting carve-out holds and to stream the
+// rest, instead of letting the optimizer pass and the gradient table push all of it out every step.
+// MEASURED (B200, bench.py --workload large, round 2): the step gets SLOWER with the window, 0.999 -> 1.192 ms - the
+// carve-out is taken from the gradient table's reductions (0.158 -> 0.216 ms) and the optimizer's stream (0.445 ->
+// 0.535 ms), and the gathers do not gain what those lose (0.058 -> 0.075 ms: half of the window is marked streaming).
+// So the window is OFF unless NGPB_L2_WINDOW=1 asks for it; plain LRU serves this access pattern better.
+void Testbed::apply_l2_access_policy() {
+	static const int mode = getenv("NGPB_L2_WINDOW") ? atoi(getenv("NGPB_L2_WINDOW")) : -1;
+	cudaStreamAttrValue attr{};
+	attr.accessPolicyWindow.num_bytes = 0;   // clears a window left by a previous network
+	const size_t table_bytes = m_network ? m_network->grid_config().n_params * sizeof(__half) : 0;
+	if (mode == 1 && m_network && table_bytes > 0) {
+		int dev = 0, max_persist = 0, max_window = 0;
+		NGPB_CUDA_CHECK(cudaGetDevice(&dev));
+		NGPB_CUDA_CHECK(cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev));
+		NGPB_CUDA_CHECK(cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev));
+		if (max_persist > 0 && max_window > 0) {
+			NGPB_CUDA_CHECK(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)max_persist));
+			const size_t bytes = std::min(table_bytes, (size_t)max_window);
+			attr.accessPolicyWindow.base_ptr = m_params.as<__half>() + m_network->pos_encoding_param_offset();
+			attr.accessPolicyWindow.num_bytes = bytes;
+			attr.accessPolicyWindow.hitRatio = std::min(1.0f, (float)max_persist / (float)bytes);
+			attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+			attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+			l2_window_bytes = (double)bytes;
+			l2_window_hit_ratio = attr.accessPolicyWindow.hitRatio;
+		}
+	}
+	if (attr.accessPolicyWindow.num_bytes == 0) { l2_window_bytes = 0; l2_window_hit_ratio = 0; }
+	NGPB_CUDA_CHECK(cudaStreamSetAttribute(m_stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+	if (m_side_stream) NGPB_CUDA_CHECK(cudaStreamSetAttribute(m_side_stream, cudaStreamAttributeAccessPolicyWindow, &attr));
 }
 
 } // namespace ngpb

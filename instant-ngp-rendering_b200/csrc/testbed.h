@@ -95,6 +95,8 @@ public:
 	NerfNetworkModule* nerf_network() { return m_network.get(); }
 	Optimizer* optimizer() { return m_optimizer.get(); }
 	size_t n_params() const { return m_n_params; }
+	void apply_l2_access_policy();           // testbed.cu; readable as properties l2_window_bytes / l2_window_hit_ratio
+	double l2_window_bytes = 0, l2_window_hit_ratio = 0;
 	float* params_fp32() { return m_params_fp32.as<float>(); }
 	__half* params() { return m_params.as<__half>(); }
 	__half* params_inference() { return m_optimizer && m_optimizer->custom_weights() ? m_optimizer->custom_weights() : m_params.as<__half>(); }

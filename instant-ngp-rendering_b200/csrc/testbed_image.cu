@@ -169,6 +169,7 @@ void Testbed::reset_network_image() {
 	}
 	m_network_config["encoding"] = encoding_config;
 	m_image_network = std::make_unique<NetworkWithInputEncodingModule>(2u, 3u, encoding_config, config["network"]);
+	m_image_network->set_ordered_batches(true);   // stratified positions walk the image in order (stratify2)
 	m_optimizer = std::make_unique<Optimizer>(optimizer_config);
 
 	m_n_params = m_image_network->n_params();
