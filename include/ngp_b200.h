@@ -232,6 +232,36 @@ int ngpb_testbed_set_nerf_camera(ngpb_testbed_t* t, uint32_t idx, const float* x
 int ngpb_testbed_set_stream(ngpb_testbed_t* t, void* stream);
 int ngpb_testbed_reload_network_from_json(ngpb_testbed_t* t, const char* config_json);
 int ngpb_testbed_reset_network(ngpb_testbed_t* t, int clear_density_grid);
+
+/* ---- file-level entry points, host C++ as in the reference (csrc/host_io.cu, host_snapshot.cu, host_dataset.cu) ----
+ * Testbed::reload_network_from_file (src/testbed.cu:274-308): *.json with comments and "parent" inheritance
+ * (load_network_config + merge_parent_network_config, :86-97, :246-272), or a snapshot file whose network config is used. */
+int ngpb_testbed_reload_network_from_file(ngpb_testbed_t* t, const char* path);
+/* Testbed::load_training_data for NeRF scenes (src/testbed.cu:125-152 -> load_nerf, src/nerf_loader.cu:273-740): a
+ * transforms.json or a directory of them. JPEG frames are decoded on the GPU (nvjpeg), PNG frames on the host;
+ * Perspective and OpenCV lenses; alpha files, dynamic masks, white / black_transparent. max_images 0 = all. */
+int ngpb_testbed_load_training_data(ngpb_testbed_t* t, const char* path, uint32_t max_images);
+/* Testbed::save_snapshot(path, include_optimizer_state, compress) / load_snapshot(path), src/testbed.cu:4775-4972:
+ * json::to_msgpack of the network config with a "snapshot" object (json_binding.h key names), zlib stream for *.ingp.
+ * Files interchange with the reference's for the shipped NeRF configs. */
+int ngpb_testbed_save_snapshot(ngpb_testbed_t* t, const char* path, int include_optimizer_state, int compress);
+int ngpb_testbed_load_snapshot(ngpb_testbed_t* t, const char* path);
+/* TrainingImageMetadata of one view as the testbed holds it (python_api.cu:578-590); `pixels` is the device pointer. */
+int ngpb_testbed_image_metadata(const ngpb_testbed_t* t, uint32_t idx, ngpb_nerf_image_t* out);
+/* The interactive camera a snapshot carries (m_camera 3x4 rows [0..12), relative_focal_length [12..14), screen_center
+ * [14..16), zoom [16], up_dir [17..20), sun_dir [20..23), fov_axis [23]); set != 0 writes, else reads. */
+int ngpb_testbed_view_state(ngpb_testbed_t* t, float* values24, int set);
+/* NerfDataset's scalar members as JSON (scale, offset, up, paths, from_mitsuba, is_hdr, render_aabb); returns the size needed. */
+size_t ngpb_testbed_dataset_info(const ngpb_testbed_t* t, char* buf, size_t cap);
+/* The same record written (keys that are present): for hosts that fill the dataset through set_nerf_image / set_nerf_camera. */
+int ngpb_testbed_set_dataset_info(ngpb_testbed_t* t, const char* info_json);
+/* Host-only helpers of the same layer (no device needed). load_network_config as JSON text (binaries print as nlohmann's
+ * {"bytes": [...]}); returns the size needed incl. NUL, 0 on failure (ngpb_last_error). */
+size_t ngpb_host_load_network_config(const char* path, char* buf, size_t cap);
+/* msgpack -> value tree -> msgpack with nlohmann's encoding choices; returns the size needed, 0 on failure. */
+size_t ngpb_host_msgpack_reencode(const void* in, size_t n, void* out, size_t cap);
+/* The loader's PNG decoder: 8-bit RGBA rows top to bottom into rgba (width * height * 4 bytes when cap allows). */
+int ngpb_host_decode_png(const char* path, void* rgba, size_t cap, int* width, int* height);
 /* Testbed::train(batch_size), src/testbed.cu:4020-4109. Returns once the step's counters (loss,
  * measured batch sizes) are on the host; the backward pass and the optimizer may still be running on
  * the testbed's stream - later calls on this testbed are ordered behind them. */

@@ -94,6 +94,17 @@ SIGNATURES = {
     "ngpb_testbed_set_nerf_camera": (c_int, [c_vp, c_u32, ctypes.POINTER(c_f32), c_f32, c_f32, c_f32, c_f32, c_int, ctypes.POINTER(c_f32)]),
     "ngpb_testbed_reload_network_from_json": (c_int, [c_vp, c_cp]),
     "ngpb_testbed_reset_network": (c_int, [c_vp, c_int]),
+    "ngpb_testbed_reload_network_from_file": (c_int, [c_vp, c_cp]),
+    "ngpb_testbed_load_training_data": (c_int, [c_vp, c_cp, c_u32]),
+    "ngpb_testbed_save_snapshot": (c_int, [c_vp, c_cp, c_int, c_int]),
+    "ngpb_testbed_load_snapshot": (c_int, [c_vp, c_cp]),
+    "ngpb_testbed_image_metadata": (c_int, [c_vp, c_u32, c_vp]),
+    "ngpb_testbed_view_state": (c_int, [c_vp, ctypes.POINTER(c_f32), c_int]),
+    "ngpb_testbed_dataset_info": (c_sz, [c_vp, c_vp, c_sz]),
+    "ngpb_testbed_set_dataset_info": (c_int, [c_vp, c_cp]),
+    "ngpb_host_load_network_config": (c_sz, [c_cp, c_vp, c_sz]),
+    "ngpb_host_msgpack_reencode": (c_sz, [c_vp, c_sz, c_vp, c_sz]),
+    "ngpb_host_decode_png": (c_int, [c_cp, c_vp, c_sz, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "ngpb_testbed_train": (c_int, [c_vp, c_u32]),
     "ngpb_testbed_get": (c_int, [c_vp, c_cp, ctypes.POINTER(ctypes.c_double)]),
     "ngpb_testbed_set": (c_int, [c_vp, c_cp, ctypes.c_double]),

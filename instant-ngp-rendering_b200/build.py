@@ -63,7 +63,7 @@ def build_cuda(verbose=False):
         with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(_run, jobs))
     if jobs or _newer(LIB_PATH, objs):
-        _run([NVCC, "-shared", "-o", LIB_PATH] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart_static", "-ldl", "-lpthread", "-lrt"])
+        _run([NVCC, "-shared", "-o", LIB_PATH] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart_static", "-lnvjpeg_static", "-lculibos", "-lz", "-ldl", "-lpthread", "-lrt"])
         if verbose:
             print(f"[build] linked {LIB_PATH}")
     return LIB_PATH

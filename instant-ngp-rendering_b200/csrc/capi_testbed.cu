@@ -78,6 +78,87 @@ int ngpb_testbed_reload_network_from_json(ngpb_testbed_t* t, const char* config_
 	t->impl->reload_network_from_json(Json::parse(config_json));
 	NGPB_API_END
 }
+int ngpb_testbed_reload_network_from_file(ngpb_testbed_t* t, const char* path) {
+	NGPB_API_BEGIN
+	if (!path) throw std::runtime_error{"ngpb_testbed_reload_network_from_file: null argument"};
+	t->impl->reload_network_from_file(path);
+	NGPB_API_END
+}
+int ngpb_testbed_load_training_data(ngpb_testbed_t* t, const char* path, uint32_t max_images) {
+	NGPB_API_BEGIN
+	if (!path) throw std::runtime_error{"ngpb_testbed_load_training_data: null argument"};
+	t->impl->load_training_data(path, max_images);
+	NGPB_API_END
+}
+int ngpb_testbed_save_snapshot(ngpb_testbed_t* t, const char* path, int include_optimizer_state, int compress) {
+	NGPB_API_BEGIN
+	if (!path) throw std::runtime_error{"ngpb_testbed_save_snapshot: null argument"};
+	t->impl->save_snapshot(path, include_optimizer_state != 0, compress != 0);
+	NGPB_API_END
+}
+int ngpb_testbed_load_snapshot(ngpb_testbed_t* t, const char* path) {
+	NGPB_API_BEGIN
+	if (!path) throw std::runtime_error{"ngpb_testbed_load_snapshot: null argument"};
+	t->impl->load_snapshot(std::string{path});
+	NGPB_API_END
+}
+int ngpb_testbed_image_metadata(const ngpb_testbed_t* t, uint32_t idx, ngpb_nerf_image_t* out) {
+	NGPB_API_BEGIN
+	if (!out) throw std::runtime_error{"ngpb_testbed_image_metadata: null argument"};
+	const ImageMeta m = t->impl->image_meta(idx);
+	static_assert(sizeof(ngpb_nerf_image_t) == sizeof(ImageMeta), "ngpb_nerf_image_t must mirror ImageMeta");
+	memcpy(out, &m, sizeof(m));
+	NGPB_API_END
+}
+int ngpb_testbed_view_state(ngpb_testbed_t* t, float* values24, int set) {
+	NGPB_API_BEGIN
+	if (!values24) throw std::runtime_error{"ngpb_testbed_view_state: null argument"};
+	ViewState& v = t->impl->view;
+	float* fields[] = {v.camera, v.relative_focal_length, v.screen_center, &v.zoom, v.up_dir, v.sun_dir};
+	const int counts[] = {12, 2, 2, 1, 3, 3};
+	int k = 0;
+	for (int f = 0; f < 6; ++f) for (int i = 0; i < counts[f]; ++i, ++k) { if (set) fields[f][i] = values24[k]; else values24[k] = fields[f][i]; }
+	if (set) v.fov_axis = (int)values24[23]; else values24[23] = (float)v.fov_axis;
+	NGPB_API_END
+}
+size_t ngpb_testbed_dataset_info(const ngpb_testbed_t* t, char* buf, size_t cap) {
+	try {
+		const DatasetInfo& d = t->impl->dataset_info;
+		Json j = Json::object();
+		j["scale"] = (double)d.scale;
+		Json off = Json::array(), up = Json::array(), paths = Json::array();
+		for (int k = 0; k < 3; ++k) { off.push_back(Json{(double)d.offset[k]}); up.push_back(Json{(double)d.up[k]}); }
+		for (const std::string& p : d.paths) paths.push_back(Json{p});
+		j["offset"] = off; j["up"] = up; j["paths"] = paths;
+		j["from_mitsuba"] = d.from_mitsuba; j["is_hdr"] = d.is_hdr;
+		if (d.has_render_aabb) {
+			Json a = Json::array();
+			for (int k = 0; k < 6; ++k) a.push_back(Json{(double)d.render_aabb[k]});
+			j["render_aabb"] = a;
+		}
+		const std::string s = j.dump();
+		if (buf && cap > 0) { const size_t n = s.size() < cap - 1 ? s.size() : cap - 1; memcpy(buf, s.data(), n); buf[n] = 0; }
+		return s.size() + 1;
+	} catch (...) { return 0; }
+}
+int ngpb_testbed_set_dataset_info(ngpb_testbed_t* t, const char* info_json) {
+	NGPB_API_BEGIN
+	if (!info_json) throw std::runtime_error{"ngpb_testbed_set_dataset_info: null argument"};
+	const Json j = Json::parse(info_json);
+	DatasetInfo d = t->impl->dataset_info;
+	if (j.contains("scale")) d.scale = j["scale"].as_float();
+	for (int k = 0; k < 3; ++k) {
+		if (j.contains("offset")) d.offset[k] = j["offset"][k].as_float();
+		if (j.contains("up")) d.up[k] = j["up"][k].as_float();
+	}
+	if (j.contains("paths")) { d.paths.clear(); for (const Json& p : j["paths"].elements()) d.paths.push_back(p.as_string()); }
+	if (j.contains("from_mitsuba")) d.from_mitsuba = j["from_mitsuba"].as_bool();
+	if (j.contains("is_hdr")) d.is_hdr = j["is_hdr"].as_bool();
+	if (j.contains("render_aabb") && j["render_aabb"].is_array()) { d.has_render_aabb = true; for (int k = 0; k < 6; ++k) d.render_aabb[k] = j["render_aabb"][k].as_float(); }
+	else if (j.contains("render_aabb")) d.has_render_aabb = false;
+	t->impl->dataset_info = d;
+	NGPB_API_END
+}
 int ngpb_testbed_reset_network(ngpb_testbed_t* t, int clear_density_grid) {
 	NGPB_API_BEGIN
 	t->impl->reset_network(clear_density_grid != 0);

@@ -1,0 +1,32 @@
+// Host-side file helpers shared by host_io.cu (config files, containers), host_snapshot.cu and host_dataset.cu.
+#pragma once
+
+#include "json.h"
+
+#include <string>
+#include <vector>
+
+namespace ngpb {
+
+bool file_exists(const std::string& path);
+bool is_directory(const std::string& path);
+std::string path_dirname(const std::string& path);
+std::string path_basename(const std::string& path);
+std::string path_extension(const std::string& path);   // lower case, without the dot
+std::string path_join(const std::string& dir, const std::string& rel);
+std::vector<uint8_t> read_file(const std::string& path);
+
+// load_network_config (src/testbed.cu:246-272): *.json (comments, "parent"), *.msgpack, *.ingp (zlib + msgpack)
+Json load_network_config(const std::string& path);
+// json::to_msgpack into the file; *.ingp gets the zlib stream (level 0 when not `compress`), src/testbed.cu:4826-4836
+void write_snapshot_container(const std::string& path, const Json& config, bool compress);
+
+// Decoded image: 8-bit RGBA, rows top to bottom.
+struct HostImage {
+	int width = 0, height = 0;
+	std::vector<uint8_t> rgba;
+};
+// PNG (8 / 16 bit, grey / grey-alpha / RGB / RGBA / palette, non-interlaced) decoded on the host with zlib.
+HostImage decode_png(const std::vector<uint8_t>& file, const std::string& name_for_errors);
+
+} // namespace ngpb

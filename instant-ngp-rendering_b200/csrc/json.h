@@ -20,20 +20,24 @@ namespace ngpb {
 
 class Json {
 public:
-	enum class Type { Null, Bool, Number, String, Array, Object };
+	enum class Type { Null, Bool, Number, String, Array, Object, Binary };
 
 	Json() : m_type(Type::Null) {}
 	Json(bool b) : m_type(Type::Bool), m_bool(b) {}
 	Json(double d) : m_type(Type::Number), m_num(d) {}
 	Json(float d) : m_type(Type::Number), m_num(d) {}
-	Json(int d) : m_type(Type::Number), m_num(d) {}
-	Json(uint32_t d) : m_type(Type::Number), m_num(d) {}
-	Json(uint64_t d) : m_type(Type::Number), m_num((double)d) {}
+	Json(int d) : m_type(Type::Number), m_num(d), m_is_int(true) {}
+	Json(uint32_t d) : m_type(Type::Number), m_num(d), m_is_int(true) {}
+	Json(uint64_t d) : m_type(Type::Number), m_num((double)d), m_is_int(true) {}
+	Json(int64_t d) : m_type(Type::Number), m_num((double)d), m_is_int(true) {}
 	Json(const char* s) : m_type(Type::String), m_str(s) {}
 	Json(const std::string& s) : m_type(Type::String), m_str(s) {}
 
 	static Json object() { Json j; j.m_type = Type::Object; return j; }
 	static Json array() { Json j; j.m_type = Type::Array; return j; }
+	// nlohmann::json::binary_t (msgpack `bin`): shared, so copying a config does not copy its blobs
+	static Json binary(std::vector<uint8_t> bytes) { Json j; j.m_type = Type::Binary; j.m_bin = std::make_shared<std::vector<uint8_t>>(std::move(bytes)); return j; }
+	static Json binary(const void* data, size_t n) { return binary(std::vector<uint8_t>((const uint8_t*)data, (const uint8_t*)data + n)); }
 
 	Type type() const { return m_type; }
 	bool is_null() const { return m_type == Type::Null; }
@@ -42,6 +46,13 @@ public:
 	bool is_number() const { return m_type == Type::Number; }
 	bool is_string() const { return m_type == Type::String; }
 	bool is_bool() const { return m_type == Type::Bool; }
+	bool is_binary() const { return m_type == Type::Binary; }
+	// number written without a fraction (an int in the source, or a JSON literal without '.', 'e'): msgpack keeps the distinction
+	bool is_integer() const { return m_type == Type::Number && m_is_int; }
+	const std::vector<uint8_t>& as_binary() const {
+		if (m_type != Type::Binary) throw std::runtime_error{"json: value is not binary"};
+		return *m_bin;
+	}
 
 	bool contains(const std::string& key) const {
 		return m_type == Type::Object && m_obj.count(key) > 0;
@@ -58,16 +69,24 @@ public:
 		return m_obj[key];
 	}
 	const Json& operator[](const std::string& key) const { return at(key); }
+	const Json& operator[](const char* key) const { return at(std::string{key}); }
+	Json& operator[](const char* key) { return (*this)[std::string{key}]; }
 	const Json& operator[](size_t i) const {
 		if (m_type != Type::Array || i >= m_arr.size()) throw std::runtime_error{"json: bad array index"};
 		return m_arr[i];
 	}
+	const Json& operator[](int i) const { return (*this)[(size_t)i]; }   // a literal 0 would otherwise also match the string overload
+	const Json& operator[](uint32_t i) const { return (*this)[(size_t)i]; }
 	size_t size() const { return m_type == Type::Array ? m_arr.size() : (m_type == Type::Object ? m_obj.size() : 0); }
 	void push_back(const Json& v) {
 		if (m_type == Type::Null) m_type = Type::Array;
 		m_arr.push_back(v);
 	}
 	void erase(const std::string& key) { m_obj.erase(key); }
+	Json& element(size_t i) {
+		if (m_type != Type::Array || i >= m_arr.size()) throw std::runtime_error{"json: bad array index"};
+		return m_arr[i];
+	}
 	const std::map<std::string, Json>& items() const { return m_obj; }
 	const std::vector<Json>& elements() const { return m_arr; }
 
@@ -130,6 +149,11 @@ private:
 				else { o.precision(9); o << m_num; }
 				break;
 			case Type::String: write_string(o, m_str); break;
+			case Type::Binary: { // nlohmann's text form of a binary
+				o << "{\"bytes\":[";
+				for (size_t i = 0; i < m_bin->size(); ++i) { if (i) o << ","; o << (int)(*m_bin)[i]; }
+				o << "],\"subtype\":null}";
+			} break;
 			case Type::Array: {
 				o << "[";
 				for (size_t i = 0; i < m_arr.size(); ++i) { if (i) o << ","; m_arr[i].write(o); }
@@ -191,7 +215,12 @@ private:
 			size_t start = pos;
 			while (pos < s.size() && (isdigit((unsigned char)s[pos]) || s[pos] == '-' || s[pos] == '+' || s[pos] == '.' || s[pos] == 'e' || s[pos] == 'E')) ++pos;
 			if (start == pos) fail("unexpected character");
-			try { return Json{std::stod(s.substr(start, pos - start))}; } catch (...) { fail("bad number"); }
+			const std::string lit = s.substr(start, pos - start);
+			try {
+				Json v{std::stod(lit)};
+				v.m_is_int = lit.find_first_of(".eE") == std::string::npos;
+				return v;
+			} catch (...) { fail("bad number"); }
 		}
 		std::string parse_string() {
 			++pos; // opening quote
@@ -262,6 +291,8 @@ private:
 	Type m_type;
 	bool m_bool = false;
 	double m_num = 0;
+	bool m_is_int = false;
+	std::shared_ptr<std::vector<uint8_t>> m_bin;
 	std::string m_str;
 	std::vector<Json> m_arr;
 	std::map<std::string, Json> m_obj;

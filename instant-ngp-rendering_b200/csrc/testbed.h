@@ -9,6 +9,7 @@
 #include "optimizer.h"
 
 #include <memory>
+#include <string>
 #include <vector>
 
 namespace ngpb {
@@ -20,6 +21,31 @@ constexpr uint32_t kParamPadding = 2048;
 struct NerfImage {
 	DeviceBuffer pixels;
 	ImageMeta meta{};
+};
+
+// Host-side facts about the loaded scene that only the file-level entry points need (NerfDataset's scalar members,
+// include/neural-graphics-primitives/nerf_loader.h:60-99): written by load_training_data / load_snapshot, saved by save_snapshot.
+struct DatasetInfo {
+	std::vector<std::string> paths;
+	float scale = 0.33f;                 // NERF_SCALE
+	float offset[3] = {0.5f, 0.5f, 0.5f};
+	float up[3] = {0.0f, 1.0f, 0.0f};
+	bool has_render_aabb = false;
+	float render_aabb[6] = {};           // min xyz, max xyz
+	bool from_mitsuba = false;
+	bool is_hdr = false;
+};
+
+// The interactive camera of the reference's Testbed (m_camera, m_fov_axis, m_relative_focal_length, m_screen_center, m_zoom,
+// m_up_dir, m_sun_dir; testbed.h:700-740), kept because snapshots carry it (src/testbed.cu:4806-4822, :4935-4950).
+struct ViewState {
+	float camera[12] = {1.0f, 0.0f, 0.0f, 0.5f, 0.0f, -1.0f, 0.0f, 0.5f, 0.0f, 0.0f, -1.0f, 0.5f};   // 3x4, rows
+	int fov_axis = 1;
+	float relative_focal_length[2] = {1.0f, 1.0f};
+	float screen_center[2] = {0.5f, 0.5f};
+	float zoom = 1.0f;
+	float up_dir[3] = {0.0f, 1.0f, 0.0f};
+	float sun_dir[3] = {0.57735027f, 0.57735027f, 0.57735027f};
 };
 
 class Testbed {
@@ -111,6 +137,10 @@ public:
 	void set_cone_angle_constant(float v) { m_cone_angle_constant = v; ++m_epoch; }
 	const ImageMeta* metadata_gpu() const { return m_metadata_gpu.as<ImageMeta>(); }
 	uint32_t n_images() const { return (uint32_t)m_images.size(); }
+	ImageMeta image_meta(uint32_t idx) const {
+		if (idx >= m_images.size()) throw std::runtime_error{"Invalid frame index"};
+		return m_images[idx].meta;
+	}
 	cudaStream_t stream() const { return m_stream; }
 	void set_stream(cudaStream_t s);
 	const Json& network_config() const { return m_network_config; }
@@ -150,6 +180,20 @@ public:
 	// the density grid as the snapshot holds it (fp16, HOST) -> float grid, mean and bitfield
 	void set_density_grid_fp16(const void* host_grid, size_t n_cells);
 	void restore_training_state(uint32_t training_step, float loss);
+
+	// ---- file-level entry points, host C++ as in the reference (host_io.cu, host_dataset.cu)
+	// Testbed::reload_network_from_file (src/testbed.cu:274-308) with load_network_config / "parent" merge (:86-97, :246-272)
+	void reload_network_from_file(const std::string& path);
+	// Testbed::save_snapshot / load_snapshot (src/testbed.cu:4775-4972): msgpack, zlib stream for *.ingp
+	void save_snapshot(const std::string& path, bool include_optimizer_state, bool compress);
+	void load_snapshot(const std::string& path);
+	void load_snapshot(const Json& config);
+	Json snapshot_config(bool include_optimizer_state);
+	// Testbed::load_training_data for NeRF scenes (src/testbed.cu:125-152, src/nerf_loader.cu:273-740): transforms.json
+	// (or a directory of them); JPEG decoded on the GPU by nvjpeg, PNG on the host. max_images 0 = all.
+	void load_training_data(const std::string& path, uint32_t max_images = 0);
+	DatasetInfo dataset_info;
+	ViewState view;
 
 	// ---- rendering (Testbed::render_nerf via NerfTracer; see nerf_render.cu)
 	// camera 3x4 row-major NGP convention, focal length in pixels of the render resolution.

@@ -9,6 +9,7 @@ torch owns device buffers only; all compute is in libngp_b200.so.
 import ctypes
 import json
 import os
+import struct
 import re
 
 import numpy as np
@@ -37,7 +38,9 @@ def nerf_matrix_to_ngp(m, scale=NERF_SCALE, offset=NERF_OFFSET):
 
 
 def _strip_json_comments(text):
-    return re.sub(r"//[^\n]*", "", text)
+    # nlohmann::json::parse(..., ignore_comments = true): /* */ and // comments
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return re.sub(r"(^|[^:\"])//[^\n]*", r"\1", text)
 
 
 def merge_patch(target, patch):
@@ -521,6 +524,95 @@ class Testbed:
     def load_snapshot(self, path):
         from . import snapshot
         snapshot.load(self, path)
+
+    # -- the same file-level entry points in the library's host C++ (csrc/host_io.cu, host_snapshot.cu, host_dataset.cu) --
+    def image_metadata_native(self, idx):
+        """ngpb_nerf_image_t of view idx as the C++ testbed holds it."""
+        buf = (ctypes.c_uint8 * 128)()
+        check(lib.ngpb_testbed_image_metadata(self._h, int(idx), ctypes.cast(buf, ctypes.c_void_p)))
+        raw = bytes(buf)
+        pixels, = struct.unpack_from("<Q", raw, 0)
+        image_type, lens_mode = struct.unpack_from("<ii", raw, 8)
+        lens = struct.unpack_from("<7f", raw, 16)
+        res = struct.unpack_from("<ii", raw, 44)
+        principal = struct.unpack_from("<ff", raw, 52)
+        focal = struct.unpack_from("<ff", raw, 60)
+        cols = np.array(struct.unpack_from("<12f", raw, 68), dtype=np.float32).reshape(4, 3)   # Mat4x3: four columns
+        return {"pixels": pixels, "image_data_type": image_type, "lens_mode": lens_mode, "lens_params": list(lens), "resolution": list(res),
+                "principal_point": list(principal), "focal_length": list(focal), "xform": np.ascontiguousarray(cols.T)}
+
+    def _sync_from_native(self):
+        """The Python mirror's per-view records and dataset dict, read back from the C++ testbed."""
+        n = int(self._get("n_images"))
+        self._extrinsics, self._intrinsics, self._resolutions = {}, {}, {}
+        for i in range(n):
+            m = self.image_metadata_native(i)
+            w, h = m["resolution"]
+            self._resolutions[i] = (w, h)
+            k = m["lens_params"][:4] if m["lens_mode"] == LENS_OPENCV else [0.0] * 4
+            self._intrinsics[i] = (m["focal_length"][0], m["focal_length"][1], m["principal_point"][0] * w, m["principal_point"][1] * h, *k)
+            self._extrinsics[i] = m["xform"]
+        size = lib.ngpb_testbed_dataset_info(self._h, None, 0)
+        buf = ctypes.create_string_buffer(size)
+        lib.ngpb_testbed_dataset_info(self._h, buf, size)
+        info = json.loads(buf.value.decode())
+        ra = info.get("render_aabb")
+        self.dataset = {"n_images": n, "aabb_scale": int(self._get("aabb_scale")), "scale": info["scale"], "offset": info["offset"], "up": info["up"],
+                        "render_aabb": {"min": ra[:3], "max": ra[3:]} if ra else None, "is_hdr": info["is_hdr"], "from_mitsuba": info["from_mitsuba"],
+                        "frames": [{"path": p} for p in info["paths"]]}
+        self.up_dir = info["up"]
+        view = (ctypes.c_float * 24)()
+        check(lib.ngpb_testbed_view_state(self._h, view, 0))
+        v = list(view)
+        self._camera = np.array(v[:12], dtype=np.float32).reshape(3, 4)
+        self._relative_focal_length = v[12] if v[12] == v[13] else np.array(v[12:14], dtype=np.float64)
+        self.screen_center = (v[14], v[15])
+        self.zoom = v[16]
+        self.fov_axis = int(v[23])
+
+    def _push_dataset_to_native(self):
+        """NerfDataset's scalar members of the Python mirror -> the C++ testbed (what its save_snapshot writes)."""
+        ds = getattr(self, "dataset", None)
+        if not ds:
+            return
+        info = {"scale": float(ds.get("scale", 0.33)), "offset": [float(v) for v in ds.get("offset", (0.5, 0.5, 0.5))], "up": [float(v) for v in ds.get("up", (0.0, 1.0, 0.0))],
+                "paths": [str(fr.get("path", "")) for fr in ds.get("frames", [])][: int(self._get("n_images"))],
+                "from_mitsuba": bool(ds.get("from_mitsuba", False)), "is_hdr": bool(ds.get("is_hdr", False))}
+        ra = ds.get("render_aabb")
+        if isinstance(ra, dict):
+            info["render_aabb"] = [float(v) for v in ra["min"]] + [float(v) for v in ra["max"]]
+        elif ra:
+            info["render_aabb"] = [float(v) for v in ra[0]] + [float(v) for v in ra[1]]
+        check(lib.ngpb_testbed_set_dataset_info(self._h, json.dumps(info).encode()))
+
+    def _push_view_to_native(self):
+        cam = self._camera if self._camera is not None else np.float32([[1, 0, 0, 0.5], [0, -1, 0, 0.5], [0, 0, -1, 0.5]])
+        rf = np.broadcast_to(np.asarray(self._relative_focal_length, dtype=np.float64), (2,))
+        up = getattr(self, "up_dir", (0.0, 1.0, 0.0))
+        sun = getattr(self, "sun_dir", np.float32([1.0, 1.0, 1.0]) / np.sqrt(np.float32(3.0)))
+        vals = [float(x) for x in np.asarray(cam, dtype=np.float32).reshape(-1)] + [float(rf[0]), float(rf[1])] + [float(x) for x in self.screen_center] + \
+               [float(self.zoom)] + [float(x) for x in up] + [float(x) for x in sun] + [float(self.fov_axis)]
+        check(lib.ngpb_testbed_view_state(self._h, (ctypes.c_float * 24)(*vals), 1))
+
+    def load_training_data_native(self, path, max_images=0):
+        """ngpb_testbed_load_training_data: the C++ loader (JPEG on the GPU through nvjpeg, PNG on the host)."""
+        check(lib.ngpb_testbed_load_training_data(self._h, str(path).encode(), int(max_images)))
+        self.mode = MODE_NERF
+        self._sync_from_native()
+        return self.dataset
+
+    def reload_network_from_file_native(self, path):
+        check(lib.ngpb_testbed_reload_network_from_file(self._h, str(path).encode()))
+
+    def save_snapshot_native(self, path, include_optimizer_state=False, compress=True):
+        self._push_dataset_to_native()
+        self._push_view_to_native()
+        check(lib.ngpb_testbed_save_snapshot(self._h, str(path).encode(), int(include_optimizer_state), int(compress)))
+
+    def load_snapshot_native(self, path):
+        check(lib.ngpb_testbed_load_snapshot(self._h, str(path).encode()))
+        self.mode = MODE_NERF
+        self._sync_from_native()
 
     # -- pyngp's camera and render() (src/python_api.cu:124-221, 416-425, 481-566) ---------------
     def set_nerf_camera_matrix(self, camera_to_world):

@@ -1,0 +1,185 @@
+"""Host C++ of the file-level entry points (csrc/host_io.cu, msgpack.h, host_png.cu), through the C ABI, without a GPU:
+config files with "parent" inheritance against the Python mirror, the msgpack reader / writer against the msgpack
+package (what snapshot.py uses, and nlohmann's encoding choices), the PNG decoder against OpenCV.
+"""
+import ctypes
+import json
+import os
+import struct
+import zlib
+
+import numpy as np
+import pytest
+
+
+def _config_text(lib, path):
+    n = lib.ngpb_host_load_network_config(str(path).encode(), None, 0)
+    assert n > 0, lib.ngpb_last_error().decode()
+    buf = ctypes.create_string_buffer(n)
+    lib.ngpb_host_load_network_config(str(path).encode(), buf, n)
+    return json.loads(buf.value.decode())
+
+
+def _reencode(lib, blob):
+    n = lib.ngpb_host_msgpack_reencode(blob, len(blob), None, 0)
+    assert n > 0, lib.ngpb_last_error().decode()
+    out = ctypes.create_string_buffer(n)
+    assert lib.ngpb_host_msgpack_reencode(blob, len(blob), out, n) == n
+    return out.raw
+
+
+def test_config_file_with_parent_and_comments(ngp, tmp_path):
+    lib = ngp._lib.lib
+    (tmp_path / "base.json").write_text("""{
+        // the reference's configs carry comments (configs/image/base.json:6-9)
+        "loss": {"otype": "L2"},
+        "optimizer": {"otype": "Ema", "decay": 0.95, "nested": {"otype": "Adam", "learning_rate": 1e-2, "beta1": 0.9}},
+        "encoding": {"otype": "HashGrid", "n_levels": 16, "log2_hashmap_size": 19},
+        "network": {"otype": "FullyFusedMLP", "n_neurons": 64, "n_hidden_layers": 1}
+    }""")
+    os.makedirs(tmp_path / "sub")
+    (tmp_path / "sub" / "big.json").write_text('{"parent": "../base.json", "encoding": {"log2_hashmap_size": 21}, /* drop */ "loss": null}')
+    (tmp_path / "sub" / "bigger.json").write_text('{"parent": "big.json", "encoding": {"n_levels": 8}, "network": {"n_hidden_layers": 2}}')
+    got = _config_text(lib, tmp_path / "sub" / "bigger.json")
+    from importlib import import_module
+    want = import_module("instant-ngp-rendering_b200.testbed").load_network_config(str(tmp_path / "sub" / "bigger.json"))
+    assert got == want
+    assert got["encoding"] == {"otype": "HashGrid", "n_levels": 8, "log2_hashmap_size": 21}
+    assert "loss" not in got and "parent" not in got and got["network"]["n_hidden_layers"] == 2
+    # missing file: the reference's text
+    assert lib.ngpb_host_load_network_config(str(tmp_path / "nope.json").encode(), None, 0) == 0
+    assert "does not exist" in lib.ngpb_last_error().decode()
+
+
+def test_msgpack_round_trip_against_the_msgpack_package(ngp):
+    msgpack = pytest.importorskip("msgpack")
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(1)
+    doc = {
+        "ints": [0, 1, 127, 128, 255, 256, 65535, 65536, 2 ** 32 - 1, 2 ** 32, 2 ** 53, -1, -32, -33, -128, -129, -32768, -32769, -2 ** 31, -2 ** 31 - 1],
+        "floats": [0.5, 1.0 / 3.0, 1e-8, -2.25, 3.4e38, 1e300, float(np.float32(0.95)), 0.1],
+        "strings": ["", "a", "x" * 31, "y" * 32, "z" * 255, "w" * 256, "v" * 70000],
+        "nested": {"k%d" % i: {"list": list(range(i)), "flag": bool(i % 2), "none": None} for i in range(20)},
+        "small_bin": b"\x00\x01\x02", "bin16": rng.bytes(300), "bin32": rng.bytes(70000),
+        "long_list": list(range(70000)),
+    }
+    blob = msgpack.packb(doc, use_bin_type=True, use_single_float=False)
+    back = msgpack.unpackb(_reencode(lib, blob), raw=False, strict_map_key=False)
+    assert back == doc
+    # nlohmann's choices: float32 when exact, the smallest integer type, keys in map order (std::map: sorted)
+    assert _reencode(lib, msgpack.packb({"b": 0.5, "a": 0.1})) == b"\x82\xa1a\xcb" + struct.pack(">d", 0.1) + b"\xa1b\xca" + struct.pack(">f", 0.5)
+    assert _reencode(lib, msgpack.packb([300, -200])) == b"\x92\xcd\x01\x2c\xd1\xff\x38"
+    # truncated input and ext types fail loudly
+    assert lib.ngpb_host_msgpack_reencode(blob[:-5], len(blob) - 5, None, 0) == 0
+    assert "unexpected end" in lib.ngpb_last_error().decode()
+    ext = msgpack.packb(msgpack.ExtType(5, b"abcd"))
+    assert lib.ngpb_host_msgpack_reencode(ext, len(ext), None, 0) == 0
+
+
+def test_snapshot_container_of_the_python_mirror_reads_here(ngp, tmp_path):
+    """A *.ingp written by snapshot.py's container (zlib + msgpack) parses in C++ to the same tree; gzip framing too."""
+    msgpack = pytest.importorskip("msgpack")
+    lib = ngp._lib.lib
+    snap = importlib_snapshot()
+    cfg = {"encoding": {"otype": "HashGrid", "n_levels": 8}, "snapshot": {"version": 1, "n_params": 3, "params_binary": b"\x01\x02\x03\x04\x05\x06",
+                                                                          "nerf": {"rgb": {"rays_per_batch": 4096}}, "loss": 0.125}}
+    for name, compress in (("a.ingp", True), ("b.ingp", False), ("c.msgpack", True)):
+        snap.write_container(str(tmp_path / name), cfg, compress)
+        got = _config_text(lib, tmp_path / name)
+        assert got["snapshot"]["params_binary"] == {"bytes": [1, 2, 3, 4, 5, 6], "subtype": None}
+        assert got["snapshot"]["nerf"]["rgb"]["rays_per_batch"] == 4096 and got["snapshot"]["loss"] == 0.125
+        assert got["encoding"] == cfg["encoding"]
+    import gzip
+    with open(tmp_path / "g.ingp", "wb") as f:
+        f.write(gzip.compress(msgpack.packb(cfg, use_bin_type=True)))
+    assert _config_text(lib, tmp_path / "g.ingp")["snapshot"]["n_params"] == 3
+    # a *.ingp without a zlib header passes through (zstr)
+    with open(tmp_path / "raw.ingp", "wb") as f:
+        f.write(msgpack.packb(cfg, use_bin_type=True))
+    assert _config_text(lib, tmp_path / "raw.ingp")["snapshot"]["version"] == 1
+
+
+def importlib_snapshot():
+    from importlib import import_module
+    return import_module("instant-ngp-rendering_b200.snapshot")
+
+
+@pytest.mark.parametrize("kind", ["rgb8", "rgba8", "grey8", "grey_alpha8", "rgb16", "palette", "grey1"])
+def test_png_decoder_matches_opencv(ngp, tmp_path, kind):
+    cv2 = pytest.importorskip("cv2")
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(len(kind))
+    h, w = 37, 53
+    path = str(tmp_path / (kind + ".png"))
+    if kind == "rgb8":
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8); cv2.imwrite(path, img)
+        want = np.dstack([img[:, :, ::-1], np.full((h, w), 255, np.uint8)])
+    elif kind == "rgba8":
+        img = rng.integers(0, 256, (h, w, 4), dtype=np.uint8); cv2.imwrite(path, img)
+        want = img[:, :, [2, 1, 0, 3]]
+    elif kind == "grey8":
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8); cv2.imwrite(path, img)
+        want = np.dstack([img, img, img, np.full((h, w), 255, np.uint8)])
+    elif kind == "rgb16":
+        img = rng.integers(0, 65536, (h, w, 3), dtype=np.uint16); cv2.imwrite(path, img)
+        hi = (img >> 8).astype(np.uint8)
+        want = np.dstack([hi[:, :, ::-1], np.full((h, w), 255, np.uint8)])
+    else:
+        want = _write_raw_png(path, kind, h, w, rng)
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+    out = np.zeros((h, w, 4), dtype=np.uint8)
+    rc = lib.ngpb_host_decode_png(path.encode(), out.ctypes.data_as(ctypes.c_void_p), out.nbytes, ctypes.byref(cw), ctypes.byref(ch))
+    assert rc == 0, lib.ngpb_last_error().decode()
+    assert (cw.value, ch.value) == (w, h)
+    assert np.array_equal(out, want)
+
+
+def _write_raw_png(path, kind, h, w, rng):
+    """PNG kinds OpenCV does not write: built by hand (filter type 0..4 cycled over the rows)."""
+    import struct
+
+    def chunk(t, d):
+        return struct.pack(">I", len(d)) + t + d + struct.pack(">I", zlib.crc32(t + d) & 0xFFFFFFFF)
+    extra = b""
+    if kind == "grey_alpha8":
+        px = rng.integers(0, 256, (h, w, 2), dtype=np.uint8)
+        rows, depth, color, bpp = px.reshape(h, -1), 8, 4, 2
+        want = np.dstack([px[:, :, 0]] * 3 + [px[:, :, 1]])
+    elif kind == "palette":
+        pal = rng.integers(0, 256, (16, 3), dtype=np.uint8)
+        alpha = rng.integers(0, 256, 10, dtype=np.uint8)
+        idx = rng.integers(0, 16, (h, w), dtype=np.uint8)
+        packed = np.zeros((h, (w + 1) // 2), dtype=np.uint8)
+        for x in range(w):
+            packed[:, x // 2] |= idx[:, x] << (4 if x % 2 == 0 else 0)
+        rows, depth, color, bpp = packed, 4, 3, 1
+        extra = chunk(b"PLTE", pal.tobytes()) + chunk(b"tRNS", alpha.tobytes())
+        a = np.where(idx < 10, alpha[np.minimum(idx, 9)], 255).astype(np.uint8)
+        want = np.dstack([pal[idx][:, :, 0], pal[idx][:, :, 1], pal[idx][:, :, 2], a])
+    else:  # grey1
+        bits = rng.integers(0, 2, (h, w), dtype=np.uint8)
+        packed = np.packbits(bits, axis=1)
+        rows, depth, color, bpp = packed, 1, 0, 1
+        want = np.dstack([bits * 255] * 3 + [np.full((h, w), 255, np.uint8)])
+    raw = bytearray()
+    prev = np.zeros(rows.shape[1], dtype=np.int32)
+    for y in range(h):
+        cur = rows[y].astype(np.int32)
+        ft = y % 5
+        left = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]])
+        upleft = np.concatenate([np.zeros(bpp, np.int32), prev[:-bpp]])
+        if ft == 0: pred = 0
+        elif ft == 1: pred = left
+        elif ft == 2: pred = prev
+        elif ft == 3: pred = (left + prev) // 2
+        else:
+            p = left + prev - upleft
+            pa, pb, pc = abs(p - left), abs(p - prev), abs(p - upleft)
+            pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, upleft))
+        raw += bytes([ft]) + ((cur - pred) & 0xFF).astype(np.uint8).tobytes()
+        prev = cur
+    data = zlib.compress(bytes(raw))
+    ihdr = struct.pack(">IIBBBBB", w, h, depth, color, 0, 0, 0)
+    with open(path, "wb") as f:   # two IDAT chunks: the decoder must concatenate them
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", ihdr) + extra + chunk(b"IDAT", data[:len(data) // 2]) + chunk(b"IDAT", data[len(data) // 2:]) + chunk(b"IEND", b""))
+    return want.astype(np.uint8)
