@@ -137,11 +137,26 @@ def stage_data(verbose=False):
             print(f"[build] staged {alb_dst}")
 
 
+def build_examples(verbose=False):
+    """examples/ngp_host: a C++ host of the C ABI with no Python in the process (load scene, load config file, train, snapshot, frame)."""
+    src = os.path.join(ROOT, "examples", "ngp_host.cpp")
+    exe = os.path.join(ROOT, "examples", "ngp_host")
+    if not os.path.exists(src):
+        return None
+    if _newer(exe, [src, LIB_PATH, os.path.join(ROOT, "include", "ngp_b200.h")]):
+        _run(["g++", "-std=c++17", "-O2", src, "-I" + os.path.join(ROOT, "include"), "-I/usr/local/cuda/include", "-L" + PKG_DIR, "-lngp_b200",
+              "-L/usr/local/cuda/lib64", "-lcudart", "-Wl,-rpath,$ORIGIN/../instant-ngp-rendering_b200", "-Wl,-rpath,/usr/local/cuda/lib64", "-o", exe])
+        if verbose:
+            print(f"[build] built {exe}")
+    return exe
+
+
 def build_all(verbose=False):
     build_cuda(verbose)
     build_oracle(verbose)
     build_ref(verbose)
     build_baseline(verbose)
+    build_examples(verbose)
     stage_data(verbose)
 
 

@@ -202,3 +202,29 @@ def test_snapshots_interchange_between_the_two_hosts(ngp, tmp_path, writer, read
         else:
             assert x == y, (where, x if not isinstance(x, bytes) else len(x))
     same(ta, tb_)
+
+
+def test_cpp_host_program_trains_snapshots_and_renders(ngp, tmp_path):
+    """examples/ngp_host: a C++ process with no Python in it does what `instant-ngp scene --network config.json` does headless."""
+    import subprocess
+    exe = os.path.join(ROOT, "examples", "ngp_host")
+    if not os.path.exists(exe):
+        pytest.skip("examples/ngp_host is not built")
+    scene = _write_scene(tmp_path, "png")
+    with open(tmp_path / "base.json", "w") as f:
+        json.dump(CONFIG, f)
+    with open(tmp_path / "small.json", "w") as f:
+        f.write('{"parent": "base.json", /* smaller table */ "encoding": {"log2_hashmap_size": 14}}')
+    snap, frame = str(tmp_path / "out.ingp"), str(tmp_path / "frame.ppm")
+    res = subprocess.run([exe, scene, str(tmp_path / "small.json"), "60", snap, frame], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    assert "6 views" in res.stdout and "wrote " + snap in res.stdout
+    # the snapshot loads in the Python mirror and carries the trained model
+    tb = ngp.Testbed()
+    tb.load_snapshot(snap)
+    assert tb.training_step == 60 and tb.network_config["encoding"]["log2_hashmap_size"] == 14
+    assert int(tb._get("n_images")) == 6 and np.isfinite(tb.loss)
+    with open(frame, "rb") as f:
+        head = f.readline() + f.readline() + f.readline()
+        px = np.frombuffer(f.read(), dtype=np.uint8)
+    assert head == b"P6\n24 16\n255\n" and px.size == 24 * 16 * 3 and px.std() > 1.0
