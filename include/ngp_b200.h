@@ -193,6 +193,7 @@ typedef struct {
 	float* coords_compacted;     /* [max_samples_compacted][7] */
 	void* dloss_doutput;         /* fp16 [max_samples_compacted][4] */
 	float* loss;                 /* [n_rays] */
+	uint32_t* compact_src;       /* [max_samples_compacted] or NULL: row of `coords` each compacted sample was copied from (no reference counterpart) */
 } ngpb_nerf_train_buffers_t;
 
 /* rng_state = {state, inc} of the step's pcg32 (m_rng). Counters must be zeroed by the caller. */

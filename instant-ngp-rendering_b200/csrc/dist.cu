@@ -158,7 +158,7 @@ void Testbed::train_dp(uint32_t batch_size) {
 	m_counters_read = true;
 
 	const uint32_t target = batch_size / shard_world;
-	m_network->backward_strided(m_stream, target, m_coords_compacted.as<float>(), kCoordFloats, m_dloss.as<__half>(), 4, gradients(), params(), m_mlp_done, m_encoder_done);
+	m_network->backward_strided(m_stream, target, m_coords_compacted.as<float>(), kCoordFloats, m_dloss.as<__half>(), 4, gradients(), params(), m_mlp_done, m_encoder_done, m_compact_src.as<uint32_t>());
 	m_rng.advance(1ll << 32);
 
 	// sharded optimizer

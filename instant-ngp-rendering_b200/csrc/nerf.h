@@ -59,6 +59,7 @@ struct NerfTrainBuffers {
 	float* coords_compacted;          // [max_samples_compacted][7]
 	__half* dloss_doutput;            // [max_samples_compacted][4]
 	float* loss;                      // [n_rays]
+	uint32_t* compact_src;            // [max_samples_compacted] or null: index in `coords` each compacted sample was copied from
 };
 
 // src/testbed_nerf.cu:679-838. `rng` is the step's generator (m_rng); ray i uses rng.advance(16 i).

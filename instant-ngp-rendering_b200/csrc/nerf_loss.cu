@@ -182,6 +182,7 @@ __global__ void __launch_bounds__(kRayBlock) compute_loss_kernel(const __grid_co
 
 	// the compacted copy of the coordinates: the ray's rows are contiguous on both sides
 	for (uint32_t k = lane; k < compacted_numsteps * kCoordFloats; k += 32) coords_out[k] = coords_in[k];
+	if (buf.compact_src) for (uint32_t k = lane; k < compacted_numsteps; k += 32) buf.compact_src[compacted_base + k] = base + k;
 
 	V3 rgb_ray2 = v3(0.0f); // colour accumulated in front of the chunk
 	T = 1.f;
@@ -223,7 +224,7 @@ __global__ void __launch_bounds__(kRayBlock) compute_loss_kernel(const __grid_co
 // fill_rollover_and_rescale on the gradients, fill_rollover on the coordinates: the compacted
 // batch is padded to the full batch size by wrapping around; gradients of the padding (and only
 // of the padding, as in the reference) are scaled by n_input / n_elements.
-__global__ void fill_rollover_kernel(uint32_t n_elements, const NerfStepCounters* __restrict__ counters, float* __restrict__ coords, __half* __restrict__ dout) {
+__global__ void fill_rollover_kernel(uint32_t n_elements, const NerfStepCounters* __restrict__ counters, float* __restrict__ coords, __half* __restrict__ dout, uint32_t* __restrict__ compact_src) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	const uint32_t n_in = min(counters->numsteps_compacted, n_elements);
 	if (i < n_in || i >= n_elements || n_in == 0) return;
@@ -232,13 +233,14 @@ __global__ void fill_rollover_kernel(uint32_t n_elements, const NerfStepCounters
 	for (uint32_t k = 0; k < kCoordFloats; ++k) coords[(size_t)i * kCoordFloats + k] = coords[(size_t)src * kCoordFloats + k];
 #pragma unroll
 	for (uint32_t k = 0; k < 4; ++k) dout[(size_t)i * 4 + k] = __float2half(__half2float(dout[(size_t)src * 4 + k]) * n_in / n_elements);
+	if (compact_src) compact_src[i] = compact_src[src];
 }
 
 void nerf_compute_loss_and_compact(cudaStream_t stream, const NerfTrainConfig& cfg, const NerfTrainBuffers& buf, Pcg32 rng) {
 	if (local_ray_count(cfg) == 0) return;
 	compute_loss_kernel<<<div_round_up(local_ray_count(cfg), kRaysPerBlock), kRayBlock, 0, stream>>>(cfg, buf, rng);
 	NGPB_CUDA_CHECK(cudaGetLastError());
-	fill_rollover_kernel<<<div_round_up(cfg.max_samples_compacted, 256), 256, 0, stream>>>(cfg.max_samples_compacted, buf.counters, buf.coords_compacted, buf.dloss_doutput);
+	fill_rollover_kernel<<<div_round_up(cfg.max_samples_compacted, 256), 256, 0, stream>>>(cfg.max_samples_compacted, buf.counters, buf.coords_compacted, buf.dloss_doutput, buf.compact_src);
 	NGPB_CUDA_CHECK(cudaGetLastError());
 }
 

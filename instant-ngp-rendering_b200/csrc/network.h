@@ -86,7 +86,10 @@ public:
 	// before_mlp / after_mlp (optional): recorded right before the fused MLP kernel is launched (the
 	// encoder pass is done) and once it is done, before the grid scatter.
 	void backward_strided(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, const __half* dL_doutput, uint32_t dy_stride,
-		__half* dL_dparams, const __half* params, cudaEvent_t after_mlp = nullptr, cudaEvent_t before_mlp = nullptr);
+		__half* dL_dparams, const __half* params, cudaEvent_t after_mlp = nullptr, cudaEvent_t before_mlp = nullptr, const uint32_t* reuse_src = nullptr);
+	// reuse_src (optional, DEVICE [n]): sample i of this batch is a copy of row reuse_src[i] of the batch the LAST inference_counted
+	// call ran on, with the same parameters. Its encoded features are then copied out of that call's feature tiles instead of
+	// being gathered from the hash table again (the training step: the compacted batch is a subset of the marched samples).
 	// NerfNetwork::density (nerf_network.h:270-279): out[i*out_stride] = density-MLP output 0 when
 	// out_stride == 1, else the padded 16 outputs.
 	void density(cudaStream_t stream, uint32_t n, const float* input, uint32_t in_stride, __half* output, uint32_t out_stride, const __half* params);
@@ -104,7 +107,8 @@ private:
 	MlpShape m_density, m_rgb;
 	FusedNet m_net{};
 	Json m_pos_json, m_dir_json, m_density_json, m_rgb_json;
-	DeviceBuffer m_scratch_feat, m_scratch_dfeat, m_scratch_dw;
+	DeviceBuffer m_scratch_feat, m_scratch_dfeat, m_scratch_dw, m_scratch_feat_train;
+	uint32_t m_infer_tiles_rows = 0;   // rows of the feature tiles inference_counted left in m_scratch_feat (0: none)
 };
 
 } // namespace ngpb

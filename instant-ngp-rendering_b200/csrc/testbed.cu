@@ -42,7 +42,7 @@ Testbed::~Testbed() {
 	m_images.clear();
 	for (DeviceBuffer* b : {&m_params_fp32, &m_params, &m_gradients, &m_metadata_gpu, &m_density_grid, &m_density_grid_tmp, &m_density_bitfield,
 			&m_density_mean, &m_grid_positions, &m_grid_indices, &m_grid_mlp_out, &m_counters, &m_ray_indices, &m_rays, &m_numsteps, &m_coords,
-			&m_rgbsigma, &m_coords_compacted, &m_dloss, &m_loss, &m_render_scratch, &m_frame_buffer, &m_accumulate_buffer,
+			&m_rgbsigma, &m_coords_compacted, &m_dloss, &m_loss, &m_compact_src, &m_render_scratch, &m_frame_buffer, &m_accumulate_buffer,
 			&m_image_data, &m_image_positions, &m_image_targets, &m_image_output, &m_image_dloss, &m_image_loss_values}) b->release();
 	m_network.reset();
 	m_image_network.reset();
@@ -229,6 +229,7 @@ void Testbed::reset_network(bool clear_density_grid) {
 // So the window is OFF unless NGPB_L2_WINDOW=1 asks for it; plain LRU serves this access pattern better.
 void Testbed::apply_l2_access_policy() {
 	static const int mode = getenv("NGPB_L2_WINDOW") ? atoi(getenv("NGPB_L2_WINDOW")) : -1;
+	if (mode != 1) return;   // the default path makes no stream-attribute call at all
 	cudaStreamAttrValue attr{};
 	attr.accessPolicyWindow.num_bytes = 0;   // clears a window left by a previous network
 	const size_t table_bytes = m_network ? m_network->grid_config().n_params * sizeof(__half) : 0;

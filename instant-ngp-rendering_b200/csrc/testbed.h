@@ -275,6 +275,7 @@ private:
 	std::unique_ptr<Optimizer> m_optimizer;
 	size_t m_n_params = 0;
 	DeviceBuffer m_params_fp32, m_params, m_gradients;
+	DeviceBuffer m_compact_src;   // [batch] marched row each compacted sample was copied from (feature-tile reuse, network.h)
 
 	std::vector<NerfImage> m_images;
 	DeviceBuffer m_metadata_gpu;

@@ -128,6 +128,7 @@ void Testbed::reserve_step_buffers(uint32_t target_batch_size) {
 	m_rgbsigma.reserve((size_t)max_samples * 4 * sizeof(__half), m_stream);
 	m_coords_compacted.reserve((size_t)target_batch_size * kCoordFloats * sizeof(float), m_stream);
 	m_dloss.reserve((size_t)target_batch_size * 4 * sizeof(__half), m_stream);
+	m_compact_src.reserve((size_t)target_batch_size * sizeof(uint32_t), m_stream);
 }
 
 // Configuration of the step that starts from the current host state (rays_per_batch, n_rays_total).
@@ -175,6 +176,7 @@ NerfTrainBuffers Testbed::make_train_buffers(uint32_t counter_slot) {
 	buf.coords_compacted = m_coords_compacted.as<float>();
 	buf.dloss_doutput = m_dloss.as<__half>();
 	buf.loss = m_loss.as<float>();
+	buf.compact_src = m_compact_src.as<uint32_t>();
 	return buf;
 }
 
@@ -224,6 +226,7 @@ void Testbed::train_nerf_forward(uint32_t target_batch_size) {
 	// dloss / coords of a batch that the loss kernel does not fill completely and whose roll-over
 	// finds no input must not carry stale gradients
 	NGPB_CUDA_CHECK(cudaMemsetAsync(m_dloss.ptr, 0, (size_t)target_batch_size * 4 * sizeof(__half), m_stream));
+	NGPB_CUDA_CHECK(cudaMemsetAsync(m_compact_src.ptr, 0, (size_t)target_batch_size * sizeof(uint32_t), m_stream));   // slots nothing is compacted into carry zero gradients; their source must still be a valid row
 
 	prof_mark(m_stream, "generate_training_samples");
 	if (!adopt) {
@@ -249,7 +252,7 @@ void Testbed::train_backward(uint32_t batch_size, bool counters_final) {
 		NGPB_CUDA_CHECK(cudaMemcpyAsync(m_counters_host, counters(), sizeof(NerfStepCounters), cudaMemcpyDeviceToHost, m_stream));
 		NGPB_CUDA_CHECK(cudaEventRecord(m_counters_ready, m_stream));
 	}
-	m_network->backward_strided(m_stream, target_batch_size, m_coords_compacted.as<float>(), kCoordFloats, m_dloss.as<__half>(), 4, gradients(), params(), m_mlp_done, m_encoder_done);
+	m_network->backward_strided(m_stream, target_batch_size, m_coords_compacted.as<float>(), kCoordFloats, m_dloss.as<__half>(), 4, gradients(), params(), m_mlp_done, m_encoder_done, m_compact_src.as<uint32_t>());
 	m_rng.advance(1ll << 32);
 }
 

@@ -271,7 +271,7 @@ class NerfConfig(ctypes.Structure):
 class NerfBuffers(ctypes.Structure):
     """ngpb_nerf_train_buffers_t (device pointers)."""
     _fields_ = [(n, ctypes.c_void_p) for n in ("metadata", "density_bitfield", "mean_density", "counters", "ray_indices", "rays_unnormalized",
-                                               "numsteps", "coords", "rgbsigma", "coords_compacted", "dloss_doutput", "loss")]
+                                               "numsteps", "coords", "rgbsigma", "coords_compacted", "dloss_doutput", "loss", "compact_src")]
 
 
 olib.oracle_nerf_generate_samples.restype = ctypes.c_uint64

@@ -99,6 +99,8 @@ class _Device:
         b.counters, b.ray_indices, b.rays_unnormalized = self.counters.data_ptr(), self.ray_indices.data_ptr(), self.rays.data_ptr()
         b.numsteps, b.coords, b.rgbsigma = self.numsteps.data_ptr(), self.coords.data_ptr(), self.rgbsigma.data_ptr()
         b.coords_compacted, b.dloss_doutput, b.loss = self.coords_compacted.data_ptr(), self.dloss.data_ptr(), self.loss.data_ptr()
+        self.compact_src = z(mc, torch.int32)
+        b.compact_src = self.compact_src.data_ptr()
         self.buf = b
 
 
@@ -232,10 +234,12 @@ def test_loss_and_gradients_match_oracle(ngp, oracle, aabb_scale, loss_type, rgb
     np.testing.assert_allclose(dev.loss.cpu().numpy()[:kept], loss, rtol=2e-3, atol=1e-9)
     got_d = dev.dloss.cpu().numpy().astype(np.float32)
     got_c = dev.coords_compacted.cpu().numpy()
+    got_src = dev.compact_src.cpu().numpy().view(np.uint32)
     scale = np.abs(dloss).max()
     for k in range(kept):
         n, cb, b = int(comp[k]), int(got_ns[k, 1]), int(numsteps_in[k, 1])
         assert np.array_equal(got_c[cb:cb + n].view(np.uint32), coords[b:b + n].view(np.uint32))
+        assert np.array_equal(got_src[cb:cb + n], np.arange(b, b + n)), k   # the row each compacted sample was copied from (feature-tile reuse)
         want = dloss[b:b + n]
         # the density gradient is a suffix sum that cancels to exactly 0 at a ray's last sample in the
         # serial order; the warp-parallel suffix leaves an fp32 rounding residue there (a few 1e-7 of
@@ -248,6 +252,7 @@ def test_loss_and_gradients_match_oracle(ngp, oracle, aabb_scale, loss_type, rgb
     assert n_compacted < batch
     i = n_compacted + 17
     assert np.array_equal(got_c[i].view(np.uint32), got_c[i % n_compacted].view(np.uint32))
+    assert got_src[i] == got_src[i % n_compacted]
     np.testing.assert_allclose(got_d[i], got_d[i % n_compacted] * n_compacted / batch, rtol=2e-3, atol=1e-7)
 
 
