@@ -140,6 +140,8 @@ __global__ void __launch_bounds__(kRayBlock) render_march_kernel(const __grid_co
 		float n_next = n + 1.0f; // calc_dt
 		if (!occupied) {
 			// largest empty voxel around the sample (nerf_device.cuh:485-490), then advance_to_next_voxel
+			// (measured and not kept: the up-to-seven coarser-mip loads issued together instead of this early-exit chain - the
+			// chain usually ends at its first load, and the extra loads cost more than the latency they hide: march 1.88 -> 2.46 ms)
 			while (mip < p.skip_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
 			const float n_target = to_stepping_space_sel<kCone>(t + distance_to_next_voxel(pos, d, idir, pow2i(7 - (int)mip), pow2i((int)mip - 7)), stepping);
 			n_next = n + ceilf(fmaxf(n_target - n, 0.5f));
@@ -263,10 +265,13 @@ void Testbed::render_nerf(uint32_t width, uint32_t height, const float* camera_3
 	p.n_local = n_rays;
 	p.shard_rank = render_shard_rank; p.shard_world = render_shard_world;
 	p.capacity = next_multiple(n_rays, kBatchSizeGranularity);
-	// A shard holds 1 / world of the frame's rays: with the frame's query budget its windows would be `world` times
-	// longer and rays would be marched far past their termination (measured at 8 shards: 41 queries per ray against 36).
-	// The budget follows the ray count, so a shard runs the window lengths the whole frame runs.
-	p.target_queries = std::max(render_target_queries / render_shard_world, 1u);
+	// A shard holds 1 / world of the frame's rays. Its windows are latency-bound (a march kernel over 1/8 of the rays
+	// takes a third of the whole frame's, not an eighth), so what a shard wants is FEW windows, not the whole frame's
+	// window lengths: measured on one of 8 shards of the 1080p fox frame (scripts/profile_render.py), budget / 8 runs 20
+	// windows = 3.33 ms, the frame's budget 8 windows = 2.44 ms, twice the budget 4 windows = 2.24 ms at 33.6 instead of
+	// 30.5 queries per ray (max_steps caps a window at 32 steps). The whole frame on one GPU is best at 1x (12.2 ms
+	// against 12.6 at 2x), so only shards take the doubled budget.
+	p.target_queries = std::max(render_target_queries * (render_shard_world > 1 ? 2u : 1u), 1u);
 	p.min_steps = std::max(render_min_steps, 1u);
 	p.max_steps = std::max(render_max_steps, p.min_steps);
 	p.min_transmittance = render_min_transmittance;

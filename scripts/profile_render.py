@@ -34,8 +34,10 @@ if fox:
     focal = float(np.broadcast_to(tb._relative_focal_length, (2,))[1]) * 1080
 else:
     view = syn.look_at_ngp(np.array([0.5, 0.5, 0.5]) + 1.4 * np.array([0.62, -0.55, 0.56]))
+policies = {(0, 1): ((12 << 20, 4, 32, 4), (24 << 20, 4, 32, 4), (48 << 20, 8, 32, 4)),
+            (0, 8): ((12 << 17, 4, 32, 4), (12 << 18, 4, 32, 4), (12 << 19, 4, 32, 4), (12 << 20, 4, 32, 4), (24 << 20, 4, 32, 4), (24 << 20, 8, 64, 4), (24 << 20, 16, 64, 8))}
 for shard in ((0, 1), (0, 8)):
-    for policy in ((12 << 20, 4, 32, 4), (24 << 20, 4, 32, 4), (48 << 20, 8, 32, 4), (96 << 20, 8, 32, 4)):
+    for policy in policies[shard]:
         tb._set("render_target_queries", policy[0]); tb._set("render_min_steps", policy[1]); tb._set("render_max_steps", policy[2]); tb._set("render_windows_per_sync", policy[3])
         tb.render_nerf(1920, 1080, view, focal, shard=shard)
         tbm.profile_enable(True)
