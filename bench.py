@@ -181,11 +181,29 @@ class CpuNerf:
         syn = ref_configs   # poses and configs only: the CPU arm must not load the product library
         rng = np.random.default_rng(1337)
         n_images, w, h, aabb = FOX["n_images"], FOX["width"], FOX["height"], FOX["aabb_scale"]
-        poses = syn.orbit_poses(n_images, radius=1.4)
-        # procedural host images: one random RGBA8 tile repeated (the kernels only look pixels up)
-        tile = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
-        tile[..., 3] = 255
-        self.images = [oracle.nerf_image(tile, poses[i], focal=1.1 * w) for i in range(n_images)]
+        self.data = "synthetic"
+        if os.path.isdir(FOX_DIR) and not os.environ.get("NGPB_BENCH_SYNTHETIC"):
+            # the reference's own fox scene (staged), read by the loader's host logic loaded by PATH: the package itself
+            # would map libngp_b200.so, which the CPU arm must not do
+            import importlib.util
+            spec = importlib.util.spec_from_file_location("ngpb_loader_host", os.path.join(ROOT, "instant-ngp-rendering_b200", "loader.py"))
+            loader = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(loader)
+            ds = loader.describe_dataset(FOX_DIR)
+            self.images = []
+            for fr in ds["frames"]:
+                px = loader.load_frame_pixels(fr, ds)
+                fx, fy = loader.finish_frame(fr, px.shape[1], px.shape[0])
+                self.images.append(oracle.nerf_image(px, fr["xform"], focal=(fx, fy), principal=tuple(fr["principal"]),
+                                                     lens=fr["lens_params"][:4] if fr["lens_mode"] == 1 else None))
+            n_images, aabb = len(self.images), int(ds["aabb_scale"])
+            self.data = "fox"
+        else:
+            poses = syn.orbit_poses(n_images, radius=1.4)
+            # procedural host images: one random RGBA8 tile repeated (the kernels only look pixels up)
+            tile = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
+            tile[..., 3] = 255
+            self.images = [oracle.nerf_image(tile, poses[i], focal=1.1 * w) for i in range(n_images)]
         self.max_cascade = int(np.log2(aabb))
         # occupancy of a partly trained model: 8x8x8 bricks (contiguous Morton runs) in every cascade
         grid = np.zeros((self.max_cascade + 1, 128 ** 3), dtype=np.float32)
@@ -264,9 +282,9 @@ def cpu_nerf_baseline(n_rays, steps, warmup=0, budget_s=1e9):
         done += 1
         if dt > budget_s:
             break
-    return {"samples_per_s": samples / dt, "seconds": dt, "steps_done": done, "samples": samples, "marched": marched, "cores": oracle.num_threads(),
+    return {"samples_per_s": samples / dt, "seconds": dt, "steps_done": done, "samples": samples, "marched": marched, "cores": oracle.num_threads(), "data": c.data,
             "sample": f"{done} oracle training step(s) of {n_rays} rays ({samples // max(done, 1)} compacted / {marched // max(done, 1)} marched samples per step, "
-                      f"{dt:.1f} s) on the fox-shaped inputs"}
+                      f"{dt:.1f} s) on the {'reference fox scene (data/nerf/fox, staged)' if c.data == 'fox' else 'fox-shaped synthetic inputs'}"}
 
 
 # ------------------------------------------------------------------------------------------
@@ -846,8 +864,8 @@ def run_reference_arm(args):
     per_step = cpu["samples"] / max(cpu["steps_done"], 1)
     line = {"impl": "reference", "metric": "fox NeRF train samples/s", "value": value, "unit": "samples/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * cpu["seconds"] / max(cpu["steps_done"], 1) * (FOX["batch"] / max(per_step, 1)),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-            "config": {"workload": "nerf_train_fox_shape_base.json_batch2^18", "sample": cpu["sample"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": cpu["data"],
+            "config": {"workload": "nerf_train_fox_base.json_batch2^18" if cpu["data"] == "fox" else "nerf_train_fox_shape_base.json_batch2^18", "sample": cpu["sample"],
                        "note": "ms_per_step is the measured time per oracle step scaled to the 2^18-sample batch"},
             "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cpu["cores"], "kind": "port", "sample": cpu["sample"]},
             "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
