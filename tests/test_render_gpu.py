@@ -180,3 +180,43 @@ def test_render_buffer_epilogue_matches_oracle(ngp, oracle, trained):
     # fov <-> focal length (Testbed::set_fov): 90 degrees along y <=> focal = h / 2
     tb.fov = 90.0
     assert abs(tb._relative_focal_length - 0.5) < 1e-6 and abs(tb.fov - 90.0) < 1e-4
+
+
+def test_render_at_the_bench_shape(ngp, oracle):
+    """configs[3] at its own size: a 1920 x 1080 frame of an aabb_scale-4 scene (the fox shape), of which the oracle walks
+    a 4096-pixel slice. The small frames above cannot see index arithmetic that only rounds or overflows at 2 M rays
+    (pixel -> ray, tile interleave, the sample slots of a 12 M-query window). Bars as above: counts bit-exact with an
+    identical network, >= 98 % with the trained one, colours within the fp16 tolerance."""
+    syn = importlib.import_module("instant-ngp-rendering_b200.synthetic")
+    tb = ngp.Testbed()
+    scene, poses, focal = syn.make_dataset(tb, n_images=8, width=96, height=72, aabb_scale=4, amp_scale=8.0)
+    tb.reload_network_from_json(dict(syn.NERF_BASE_CONFIG))
+    for _ in range(200):
+        tb.train(1 << 15)
+    w, h = 1920, 1080
+    f = focal * w / 96
+    begin = (h // 2) * w + 700            # a run in the middle of the frame, not aligned to a 256-pixel tile
+    slice_ = (begin, begin + 4096)
+    try:
+        rgba, depth, steps = tb.render_nerf(w, h, poses[1], f, return_steps=True)
+        assert tb.last_render_samples > 5 * w * h, "the frame must put real work on the rays"
+        got_rgba = rgba.reshape(-1, 4)[slice_[0]:slice_[1]].cpu().numpy()
+        got_steps = steps.reshape(-1)[slice_[0]:slice_[1]].cpu().numpy().astype(np.uint32)
+        want_rgba, want_depth, want_steps, numsteps = _oracle_render(oracle, tb, poses[1], w, h, f, 4, pixel_range=slice_)
+        assert want_steps.sum() > 10 * 4096 / 4
+        assert (got_steps == want_steps).mean() >= 0.98, (got_steps == want_steps).mean()
+        d = np.abs(got_rgba - want_rgba).max(axis=1)
+        assert d.mean() <= 2e-3 and (d <= 2e-2).mean() >= 0.995, (d.mean(), (d <= 2e-2).mean())
+        # identical network on both sides: the counts must agree exactly
+        params = tb.device_buffer("params", torch.float16)
+        ema = tb.device_buffer("params_inference", torch.float16)
+        params.zero_(); ema.zero_()
+        torch.cuda.synchronize()
+        rgba, depth, steps = tb.render_nerf(w, h, poses[1], f, return_steps=True)
+        got_steps = steps.reshape(-1)[slice_[0]:slice_[1]].cpu().numpy().astype(np.uint32)
+        want_rgba, _, want_steps, _ = _oracle_render(oracle, tb, poses[1], w, h, f, 4, params=np.zeros(tb.n_params, dtype=np.float16), pixel_range=slice_)
+        assert want_steps.max() > 20
+        assert np.array_equal(got_steps, want_steps)
+        np.testing.assert_allclose(rgba.reshape(-1, 4)[slice_[0]:slice_[1]].cpu().numpy(), want_rgba, atol=1e-5)
+    finally:
+        tb.close()
