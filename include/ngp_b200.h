@@ -239,8 +239,9 @@ int ngpb_testbed_reset_network(ngpb_testbed_t* t, int clear_density_grid);
  * (load_network_config + merge_parent_network_config, :86-97, :246-272), or a snapshot file whose network config is used. */
 int ngpb_testbed_reload_network_from_file(ngpb_testbed_t* t, const char* path);
 /* Testbed::load_training_data for NeRF scenes (src/testbed.cu:125-152 -> load_nerf, src/nerf_loader.cu:273-740): a
- * transforms.json or a directory of them. JPEG frames are decoded on the GPU (nvjpeg), PNG frames on the host;
- * Perspective and OpenCV lenses; alpha files, dynamic masks, white / black_transparent. max_images 0 = all. */
+ * transforms.json or a directory of them. JPEG frames are decoded on the GPU (nvjpeg), PNG and EXR frames on the host;
+ * Perspective and OpenCV lenses; alpha files, dynamic masks, white / black_transparent. max_images 0 = all.
+ * An image file (*.exr, *.png, *.jpg) instead selects the neural-image mode (Testbed::load_image, src/testbed_image.cu:362-428). */
 int ngpb_testbed_load_training_data(ngpb_testbed_t* t, const char* path, uint32_t max_images);
 /* Testbed::save_snapshot(path, include_optimizer_state, compress) / load_snapshot(path), src/testbed.cu:4775-4972:
  * json::to_msgpack of the network config with a "snapshot" object (json_binding.h key names), zlib stream for *.ingp.
@@ -263,6 +264,8 @@ size_t ngpb_host_load_network_config(const char* path, char* buf, size_t cap);
 size_t ngpb_host_msgpack_reencode(const void* in, size_t n, void* out, size_t cap);
 /* The loader's PNG decoder: 8-bit RGBA rows top to bottom into rgba (width * height * 4 bytes when cap allows). */
 int ngpb_host_decode_png(const char* path, void* rgba, size_t cap, int* width, int* height);
+/* The loader's OpenEXR reader (single-part scanline, HALF / FLOAT, NONE / ZIPS / ZIP): float RGBA rows top to bottom. */
+int ngpb_host_decode_exr(const char* path, float* rgba, size_t cap_floats, int* width, int* height);
 /* Testbed::train(batch_size), src/testbed.cu:4020-4109. Returns once the step's counters (loss,
  * measured batch sizes) are on the host; the backward pass and the optimizer may still be running on
  * the testbed's stream - later calls on this testbed are ordered behind them. */

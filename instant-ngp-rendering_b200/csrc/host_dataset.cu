@@ -5,7 +5,8 @@
 //
 // B200 side of it: JPEG files - the fox scene is 50 of them - are decoded ON THE GPU by nvjpeg straight into device
 // memory and expanded to the RGBA8 training image by a kernel, so the pixels never exist on the host; PNG files are
-// inflated on the host (host_png.cu) and uploaded. EXR scenes stay with the Python loader (OpenEXR is not in this image).
+// inflated on the host (host_png.cu) and uploaded, EXR files (HDR scenes, the image mode's albert.exr) are read by
+// host_exr.cu. An image file instead of a scene selects the neural-image mode, as Testbed::load_file does.
 // The Python mirror (loader.py) is a second implementation of the same rules; tests compare the two.
 #include "testbed.h"
 #include "host_io.h"
@@ -344,19 +345,54 @@ static void decode_to_device(JpegDecoder& jpeg, const std::string& path, DeviceB
 		NGPB_CUDA_CHECK(cudaStreamSynchronize(stream));   // the host image goes away
 		return;
 	}
-	throw std::runtime_error{"ngp-b200: the C++ loader decodes JPEG and PNG files; '" + path + "' is neither (EXR scenes load through the Python loader)"};
+	throw std::runtime_error{"ngp-b200: the C++ loader decodes JPEG, PNG and EXR files; '" + path + "' is none of them"};
+}
+
+// from_rgba32 (src/common_host.cu:268-298): sRGB8 straight alpha -> linear float, colours multiplied by alpha
+__global__ void rgba8_to_linear_premultiplied_kernel(uint32_t n, const uint32_t* __restrict__ rgba8, float4* __restrict__ out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint32_t v = rgba8[i];
+	const float a = (float)(v >> 24) * (1.0f / 255.0f);
+	out[i] = make_float4(srgb_to_linear_host_rule((float)(v & 0xFFu) * (1.0f / 255.0f)) * a, srgb_to_linear_host_rule((float)((v >> 8) & 0xFFu) * (1.0f / 255.0f)) * a,
+		srgb_to_linear_host_rule((float)((v >> 16) & 0xFFu) * (1.0f / 255.0f)) * a, a);
+}
+
+// Testbed::load_image (src/testbed_image.cu:362-428): *.exr -> float RGBA as stored; 8-bit files through from_rgba32
+void Testbed::load_image_file(const std::string& path) {
+	const std::string ext = path_extension(path);
+	if (ext == "exr") {
+		const HostImageF img = decode_exr(read_file(path), path);
+		set_image(img.rgba.data(), kImageFloat, img.width, img.height);
+		return;
+	}
+	JpegDecoder jpeg;
+	DeviceBuffer rgb_scratch, rgba8, linear;
+	int w = 0, h = 0;
+	decode_to_device(jpeg, path, rgb_scratch, rgba8, w, h, m_stream);
+	if (w == 0 || h == 0) throw std::runtime_error{"Image has zero pixels."};
+	const uint32_t n = (uint32_t)w * (uint32_t)h;
+	linear.alloc((size_t)n * sizeof(float4), m_stream);
+	rgba8_to_linear_premultiplied_kernel<<<div_round_up(n, 256u), 256, 0, m_stream>>>(n, rgba8.as<uint32_t>(), linear.as<float4>());
+	NGPB_CUDA_CHECK(cudaGetLastError());
+	NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	set_image(linear.ptr, kImageFloat, w, h);
 }
 
 void Testbed::load_training_data(const std::string& path, uint32_t max_images) {
 	const std::string ext = path_extension(path);
 	if (ext == "obj" || ext == "stl" || ext == "nvdb") throw std::runtime_error{"ngp-b200: SDF and volume modes are out of scope (DESIGN.md section 7)"};
 	if (!file_exists(path)) throw std::runtime_error{"Data path '" + path + "' does not exist."};
-	if (!is_directory(path) && ext != "json") throw std::runtime_error{"ngp-b200: the C++ loader takes NeRF scenes (a transforms.json or a directory of them); image files load through set_image"};
+	if (!is_directory(path) && ext != "json") {
+		// mode_from_scene (src/testbed.cu:180-200): an image file selects the neural-image mode
+		if (n_images() > 0) throw std::runtime_error{"ngp-b200: this testbed holds a NeRF scene; create a new Testbed for an image"};
+		load_image_file(path);
+		return;
+	}
 	if (m_mode == kModeImage) throw std::runtime_error{"ngp-b200: this testbed is in image mode; create a new Testbed for a NeRF scene"};
 
 	std::vector<Json> jsons;
 	DatasetDesc ds = describe_dataset(json_paths(path), jsons);
-	if (ds.info.is_hdr) throw std::runtime_error{"ngp-b200: EXR scenes load through the Python loader (OpenEXR is not part of this image)"};
 	if (max_images && ds.frames.size() > max_images) { ds.frames.resize(max_images); ds.info.paths.resize(max_images); }
 
 	create_empty_nerf_dataset((uint32_t)ds.frames.size(), ds.aabb_scale, ds.info.is_hdr);
@@ -365,6 +401,18 @@ void Testbed::load_training_data(const std::string& path, uint32_t max_images) {
 	for (size_t i = 0; i < ds.frames.size(); ++i) {
 		const FrameDesc& fr = ds.frames[i];
 		int w = 0, h = 0;
+		if (path_extension(fr.path) == "exr") {
+			// load_exr_to_gpu (src/tinyexr_wrapper.cu): linear RGBA halves; fix_premult turns straight colours into premultiplied ones
+			const HostImageF img = decode_exr(read_file(fr.path), fr.path);
+			w = img.width; h = img.height;
+			std::vector<__half> texels((size_t)w * h * 4);
+			for (size_t p = 0; p < (size_t)w * h; ++p) {
+				const float a = img.rgba[p * 4 + 3];
+				for (int c = 0; c < 3; ++c) texels[p * 4 + c] = __float2half(ds.fix_premult ? img.rgba[p * 4 + c] * a : img.rgba[p * 4 + c]);
+				texels[p * 4 + 3] = __float2half(a);
+			}
+			set_nerf_image((uint32_t)i, texels.data(), kImageHalf, w, h);
+		} else {
 		decode_to_device(jpeg, fr.path, rgb_scratch, pixels, w, h, m_stream);
 		const uint32_t n = (uint32_t)w * (uint32_t)h;
 		const uint32_t* alpha_px = nullptr;
@@ -387,6 +435,7 @@ void Testbed::load_training_data(const std::string& path, uint32_t max_images) {
 		}
 		NGPB_CUDA_CHECK(cudaStreamSynchronize(m_stream));
 		set_nerf_image((uint32_t)i, pixels.ptr, kImageByte, w, h);
+		}
 
 		// focal length once the resolution is known (:686-690): file-level keys, then per-frame keys
 		float fx = 0.0f, fy = 0.0f, pfx, pfy;

@@ -26,6 +26,14 @@ struct HostImage {
 	int width = 0, height = 0;
 	std::vector<uint8_t> rgba;
 };
+// Decoded HDR image: float RGBA, rows top to bottom.
+struct HostImageF {
+	int width = 0, height = 0;
+	std::vector<float> rgba;
+};
+// OpenEXR, single-part scanline, HALF / FLOAT channels, compression NONE / ZIPS / ZIP (host_exr.cu).
+HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name_for_errors);
+
 // PNG (8 / 16 bit, grey / grey-alpha / RGB / RGBA / palette, non-interlaced) decoded on the host with zlib.
 HostImage decode_png(const std::vector<uint8_t>& file, const std::string& name_for_errors);
 

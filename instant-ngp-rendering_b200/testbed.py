@@ -597,6 +597,9 @@ class Testbed:
     def load_training_data_native(self, path, max_images=0):
         """ngpb_testbed_load_training_data: the C++ loader (JPEG on the GPU through nvjpeg, PNG on the host)."""
         check(lib.ngpb_testbed_load_training_data(self._h, str(path).encode(), int(max_images)))
+        if os.path.isfile(str(path)) and os.path.splitext(str(path))[1].lower() not in (".json", ""):
+            self.mode = MODE_IMAGE   # an image file selects the neural-image mode (mode_from_scene, src/testbed.cu:180-200)
+            return None
         self.mode = MODE_NERF
         self._sync_from_native()
         return self.dataset

@@ -228,3 +228,33 @@ def test_cpp_host_program_trains_snapshots_and_renders(ngp, tmp_path):
         head = f.readline() + f.readline() + f.readline()
         px = np.frombuffer(f.read(), dtype=np.uint8)
     assert head == b"P6\n24 16\n255\n" and px.size == 24 * 16 * 3 and px.std() > 1.0
+
+
+def test_cpp_loader_image_mode(ngp, tmp_path):
+    """An image file selects the neural-image mode: albert.exr (when staged) and an 8-bit PNG through from_rgba32 give the
+    training targets the Python loader's image gives (same seed, same stratified positions): bit for bit for the EXR, to the last bits of powf for the PNG."""
+    import cv2
+    cfgs = __import__("importlib").import_module("baseline.configs")
+    files = []
+    albert = os.path.join(ROOT, "data_stage", "albert.exr")
+    if os.path.exists(albert):
+        files.append(albert)
+    rng = np.random.default_rng(3)
+    png = str(tmp_path / "img.png")
+    cv2.imwrite(png, rng.integers(0, 256, (200, 300, 4), dtype=np.uint8))
+    files.append(png)
+    for path in files:
+        a, b = ngp.Testbed(), ngp.Testbed()
+        a.load_training_data(path)
+        b.load_training_data_native(path)
+        for tb in (a, b):
+            tb.reload_network_from_json(cfgs.IMAGE_BASE_CONFIG)
+            tb.train(1 << 16)
+        for name, dt in (("image_positions", torch.float32), ("image_targets", torch.float32)):
+            x, y = a.device_buffer(name, dt).cpu().numpy(), b.device_buffer(name, dt).cpu().numpy()
+            assert x.size > 0
+            if path.endswith(".exr") or name == "image_positions":
+                assert np.array_equal(x.view(np.uint32), y.view(np.uint32)), (path, name)
+            else:   # sRGB -> linear: powf on the device here, numpy's float32 pow in the Python loader (last-bit differences)
+                np.testing.assert_allclose(x, y, rtol=4e-6, atol=1e-7)
+        assert np.isfinite(b.loss)

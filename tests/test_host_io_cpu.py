@@ -183,3 +183,91 @@ def _write_raw_png(path, kind, h, w, rng):
     with open(path, "wb") as f:   # two IDAT chunks: the decoder must concatenate them
         f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", ihdr) + extra + chunk(b"IDAT", data[:len(data) // 2]) + chunk(b"IDAT", data[len(data) // 2:]) + chunk(b"IEND", b""))
     return want.astype(np.uint8)
+
+
+def _decode_exr(lib, path):
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+    assert lib.ngpb_host_decode_exr(str(path).encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) == 0, lib.ngpb_last_error().decode()
+    out = np.zeros((ch.value, cw.value, 4), dtype=np.float32)
+    assert lib.ngpb_host_decode_exr(str(path).encode(), out.ctypes.data_as(ctypes.c_void_p), out.size, ctypes.byref(cw), ctypes.byref(ch)) == 0
+    return out
+
+
+def _cv2_exr(path):
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    import cv2
+    img = cv2.imread(str(path), cv2.IMREAD_UNCHANGED)
+    if img is None:
+        pytest.skip("this OpenCV build cannot read EXR")
+    img = img.astype(np.float32)
+    a = img[:, :, 3:4] if img.shape[2] == 4 else np.ones(img.shape[:2] + (1,), dtype=np.float32)
+    return np.concatenate([img[:, :, 2::-1], a], axis=-1)
+
+
+def test_exr_decoder_on_the_reference_image(ngp):
+    """data/image/albert.exr (FLOAT RGBA, ZIP, decreasing line order): the same floats OpenCV's OpenEXR reads."""
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "data_stage", "albert.exr")
+    if not os.path.exists(path):
+        pytest.skip("data_stage/albert.exr is not staged")
+    got = _decode_exr(ngp._lib.lib, path)
+    want = _cv2_exr(path)
+    assert got.shape == want.shape == (1024, 1024, 4)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("kind", ["half_rgb_zip", "float_rgba_zips", "half_y_none"])
+def test_exr_decoder_on_hand_written_files(ngp, tmp_path, kind):
+    """HALF / FLOAT channels, NONE / ZIPS / ZIP, missing alpha, luminance only: files written here chunk by chunk."""
+    rng = np.random.default_rng(len(kind))
+    h, w = 37, 29
+    if kind == "half_rgb_zip":
+        names, dtype, comp, lines = ["B", "G", "R"], np.float16, 3, 16
+    elif kind == "float_rgba_zips":
+        names, dtype, comp, lines = ["A", "B", "G", "R"], np.float32, 2, 1
+    else:
+        names, dtype, comp, lines = ["Y"], np.float16, 0, 1
+    data = {n: rng.standard_normal((h, w)).astype(dtype) for n in names}
+    path = tmp_path / (kind + ".exr")
+    chlist = b"".join(n.encode() + b"\0" + struct.pack("<iBBBBii", 1 if dtype == np.float16 else 2, 0, 0, 0, 0, 1, 1) for n in names) + b"\0"
+
+    def attr(name, typ, val):
+        return name.encode() + b"\0" + typ.encode() + b"\0" + struct.pack("<I", len(val)) + val
+    header = struct.pack("<II", 20000630, 2) + attr("channels", "chlist", chlist) + attr("compression", "compression", bytes([comp])) + \
+        attr("dataWindow", "box2i", struct.pack("<4i", 0, 0, w - 1, h - 1)) + attr("displayWindow", "box2i", struct.pack("<4i", 0, 0, w - 1, h - 1)) + \
+        attr("lineOrder", "lineOrder", b"\0") + attr("pixelAspectRatio", "float", struct.pack("<f", 1.0)) + \
+        attr("screenWindowCenter", "v2f", struct.pack("<2f", 0, 0)) + attr("screenWindowWidth", "float", struct.pack("<f", 1.0)) + b"\0"
+    chunks = []
+    for y0 in range(0, h, lines):
+        raw = b"".join(data[n][y].tobytes() for y in range(y0, min(y0 + lines, h)) for n in names)
+        if comp == 0:
+            packed = raw
+        else:
+            b = np.frombuffer(raw, dtype=np.uint8)
+            inter = np.concatenate([b[0::2], b[1::2]]).astype(np.int32)
+            pred = inter.copy()
+            pred[1:] = (inter[1:] - inter[:-1] + 128 + 256) & 0xFF
+            packed = zlib.compress(pred.astype(np.uint8).tobytes())
+            if len(packed) >= len(raw):
+                packed = raw
+        chunks.append(struct.pack("<iI", y0, len(packed)) + packed)
+    table_at = len(header)
+    offs, pos = [], table_at + 8 * len(chunks)
+    for c in chunks:
+        offs.append(pos)
+        pos += len(c)
+    path.write_bytes(header + struct.pack("<%dQ" % len(offs), *offs) + b"".join(chunks))
+    got = _decode_exr(ngp._lib.lib, path)
+    want = np.zeros((h, w, 4), dtype=np.float32)
+    want[..., 3] = data["A"].astype(np.float32) if "A" in data else 1.0
+    if "Y" in data:
+        want[..., :3] = data["Y"].astype(np.float32)[..., None]
+    else:
+        for k, n in enumerate("RGB"):
+            want[..., k] = data[n].astype(np.float32)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    # unsupported compression is refused, not misread
+    bad = header.replace(attr("compression", "compression", bytes([comp])), attr("compression", "compression", bytes([4])))
+    (tmp_path / "piz.exr").write_bytes(bad + b"\0" * 64)
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+    assert ngp._lib.lib.ngpb_host_decode_exr(str(tmp_path / "piz.exr").encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0
+    assert "not supported" in ngp._lib.lib.ngpb_last_error().decode()
