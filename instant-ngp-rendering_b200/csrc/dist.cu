@@ -63,8 +63,61 @@ DistContext::~DistContext() {
 		if (peer_flags[r]) cudaIpcCloseMemHandle(peer_flags[r]);
 	}
 	if (flags) cudaFree(flags);
+	if (peer_flags_dev) cudaFree(peer_flags_dev);
 	if (aux_stream) cudaStreamDestroy(aux_stream);
 	if (forward_done) cudaEventDestroy(forward_done);
+}
+
+// Layout of a rank's flag allocation (uint32 words): [0, 16) the two rendezvous rows of the fused optimizer kernel
+// (optimizer.cu), [32] its error word, [64, 192) the counter mailbox: [parity][source rank][8] = 4 payload words
+// (the 16-byte NerfStepCounters) + a stamp word.
+constexpr size_t kFlagBytes = 1024;
+constexpr uint32_t kMailboxWord = 64;
+
+// All-reduce of the 16-byte step counters over peer memory, one warp: lane q writes this rank's counters into rank q's
+// mailbox and then the step's stamp (system-scope release), polls its own mailbox for rank q's stamp (acquire), and lane
+// 0 adds the payloads in rank order - every rank computes the same sums, the float one included. The mailbox is double
+// buffered by step parity: a rank cannot be two steps ahead of a peer, because each step needs every peer's stamp.
+// Replaces a grouped ncclAllReduce pair whose kernel ran beside the fused MLP kernel and took SMs from it.
+__global__ void counters_allreduce_p2p_kernel(NerfStepCounters* __restrict__ counters, uint32_t* const* __restrict__ peer_flags_dev, int rank, int world,
+	uint32_t epoch, uint32_t* __restrict__ error)
+{
+	const uint32_t lane = threadIdx.x;
+	const uint32_t parity = epoch & 1u;
+	uint32_t mine[4];
+	{
+		const uint32_t* c = reinterpret_cast<const uint32_t*>(counters);
+		for (int k = 0; k < 4; ++k) mine[k] = c[k];
+	}
+	if (lane < (uint32_t)world) {
+		uint32_t* slot = peer_flags_dev[lane] + kMailboxWord + (parity * 8 + (uint32_t)rank) * 8;
+		for (int k = 0; k < 4; ++k) asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(slot + k), "r"(mine[k]) : "memory");
+		asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(slot + 4), "r"(epoch) : "memory");
+		const uint32_t* from = peer_flags_dev[rank] + kMailboxWord + (parity * 8 + lane) * 8;
+		const long long t0 = clock64();
+		for (;;) {
+			uint32_t stamp;
+			asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(stamp) : "l"(from + 4) : "memory");
+			if (stamp == epoch) break;
+			if (clock64() - t0 > 8000000000ll) { atomicExch(error, 3u); break; }   // ~4 s: a peer died; never hang the GPU
+		}
+	}
+	__syncwarp();
+	if (lane == 0) {
+		uint32_t sum[3] = {0, 0, 0};
+		float loss = 0.0f;
+		for (int q = 0; q < world; ++q) {
+			const uint32_t* from = peer_flags_dev[rank] + kMailboxWord + (parity * 8 + (uint32_t)q) * 8;
+			uint32_t v[4];
+			for (int k = 0; k < 4; ++k) asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v[k]) : "l"(from + k) : "memory");
+			sum[0] += v[0]; sum[1] += v[1]; sum[2] += v[2];
+			loss += __uint_as_float(v[3]);
+		}
+		counters->numsteps = sum[0];
+		counters->numsteps_compacted = sum[1];
+		counters->rays = sum[2];
+		counters->loss_sum = loss;
+	}
 }
 
 // Maps every rank's gradient buffer, fp16 weight buffer and flag array into this process (cudaIpc; the handles travel
@@ -81,8 +134,8 @@ static bool setup_p2p(Testbed& tb, DistContext& d, DeviceBuffer& params, DeviceB
 		NGPB_CUDA_CHECK(cudaStreamSynchronize(stream));
 		*b = std::move(fresh);
 	}
-	NGPB_CUDA_CHECK(cudaMalloc(&d.flags, 256));
-	NGPB_CUDA_CHECK(cudaMemset(d.flags, 0, 256));
+	NGPB_CUDA_CHECK(cudaMalloc(&d.flags, kFlagBytes));
+	NGPB_CUDA_CHECK(cudaMemset(d.flags, 0, kFlagBytes));
 	struct Handles { cudaIpcMemHandle_t grads, params, flags; };
 	Handles mine{};
 	NGPB_CUDA_CHECK(cudaIpcGetMemHandle(&mine.grads, grads.ptr));
@@ -102,6 +155,10 @@ static bool setup_p2p(Testbed& tb, DistContext& d, DeviceBuffer& params, DeviceB
 		ok = ok && cudaIpcOpenMemHandle(&d.peer_flags[r], host[r].flags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
 	}
 	if (!ok) cudaGetLastError();
+	if (ok) {
+		NGPB_CUDA_CHECK(cudaMalloc(&d.peer_flags_dev, sizeof(d.peer_flags)));
+		NGPB_CUDA_CHECK(cudaMemcpy(d.peer_flags_dev, d.peer_flags, sizeof(d.peer_flags), cudaMemcpyHostToDevice));
+	}
 	// every rank must take the same path: agree on the minimum
 	DeviceBuffer vote(sizeof(uint32_t), stream);
 	const uint32_t v = ok ? 1u : 0u;
@@ -149,10 +206,16 @@ void Testbed::train_dp(uint32_t batch_size) {
 	NerfStepCounters* c = counters();
 	NGPB_CUDA_CHECK(cudaEventRecord(d.forward_done, m_stream));
 	NGPB_CUDA_CHECK(cudaStreamWaitEvent(d.aux_stream, d.forward_done, 0));
-	NGPB_NCCL_CHECK(n.GroupStart());
-	NGPB_NCCL_CHECK(n.AllReduce(c, c, 3, ncclUint32, ncclSum, d.aux, d.aux_stream));
-	NGPB_NCCL_CHECK(n.AllReduce(&c->loss_sum, &c->loss_sum, 1, ncclFloat32, ncclSum, d.aux, d.aux_stream));
-	NGPB_NCCL_CHECK(n.GroupEnd());
+	static const bool counters_nccl = getenv("NGPB_DP_COUNTERS_NCCL") && atoi(getenv("NGPB_DP_COUNTERS_NCCL")) != 0;
+	if (d.p2p && !counters_nccl) {
+		counters_allreduce_p2p_kernel<<<1, 32, 0, d.aux_stream>>>(c, (uint32_t* const*)d.peer_flags_dev, d.rank, d.world, ++d.counter_epoch, (uint32_t*)d.flags + 32);
+		NGPB_CUDA_CHECK(cudaGetLastError());
+	} else {
+		NGPB_NCCL_CHECK(n.GroupStart());
+		NGPB_NCCL_CHECK(n.AllReduce(c, c, 3, ncclUint32, ncclSum, d.aux, d.aux_stream));
+		NGPB_NCCL_CHECK(n.AllReduce(&c->loss_sum, &c->loss_sum, 1, ncclFloat32, ncclSum, d.aux, d.aux_stream));
+		NGPB_NCCL_CHECK(n.GroupEnd());
+	}
 	NGPB_CUDA_CHECK(cudaMemcpyAsync(m_counters_host, c, sizeof(NerfStepCounters), cudaMemcpyDeviceToHost, d.aux_stream));
 	NGPB_CUDA_CHECK(cudaEventRecord(m_counters_ready, d.aux_stream));
 	m_counters_read = true;

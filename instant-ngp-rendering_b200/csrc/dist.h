@@ -45,6 +45,8 @@ struct DistContext {
 	void* peer_flags[8] = {};
 	void* flags = nullptr;       // this rank's uint32 [2][8] + error word
 	uint32_t epoch = 0;
+	uint32_t counter_epoch = 0;   // step stamp of the counter mailbox (dist.cu)
+	void* peer_flags_dev = nullptr; // device copy of peer_flags[] for kernels that index it by lane
 	~DistContext();
 };
 
