@@ -270,8 +270,9 @@ void Testbed::render_nerf(uint32_t width, uint32_t height, const float* camera_3
 	// window lengths: measured on one of 8 shards of the 1080p fox frame (scripts/profile_render.py), budget / 8 runs 20
 	// windows = 3.33 ms, the frame's budget 8 windows = 2.44 ms, twice the budget 4 windows = 2.24 ms at 33.6 instead of
 	// 30.5 queries per ray (max_steps caps a window at 32 steps). The whole frame on one GPU is best at 1x (12.2 ms
-	// against 12.6 at 2x), so only shards take the doubled budget.
-	p.target_queries = std::max(render_target_queries * (render_shard_world > 1 ? 2u : 1u), 1u);
+	// against 12.6 at 2x) and so is half a frame (2 shards: 7.76 ms at 1x, 7.94 at 2x), so the doubled budget goes to ray sets
+	// of at most 2^19 rays - a quarter of a 1080p frame or less (4 shards: 4.83 ms, 8 shards: 2.92 ms).
+	p.target_queries = std::max(render_target_queries * (n_rays <= (1u << 19) ? 2u : 1u), 1u);
 	p.min_steps = std::max(render_min_steps, 1u);
 	p.max_steps = std::max(render_max_steps, p.min_steps);
 	p.min_transmittance = render_min_transmittance;
@@ -280,7 +281,8 @@ void Testbed::render_nerf(uint32_t width, uint32_t height, const float* camera_3
 	const Stepping stepping = make_stepping(m_cone_angle_constant);
 
 	// one allocation: 2 x 4 ray planes | per-ray window steps | coords | rgb sigma | counters
-	const size_t max_samples = next_multiple((uint32_t)std::max<size_t>(p.target_queries, (size_t)p.capacity * p.min_steps) + kTile, kTile);
+	// (a window holds n_alive * clamp(target / n_alive, min_steps, max_steps) samples: never more than capacity * max_steps)
+	const size_t max_samples = next_multiple((uint32_t)std::min<size_t>(std::max<size_t>(p.target_queries, (size_t)p.capacity * p.min_steps), (size_t)p.capacity * p.max_steps) + kTile, kTile);
 	const size_t plane_bytes = (size_t)p.capacity * sizeof(float4);
 	size_t off = 0;
 	auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) / 256 * 256; return o; };
