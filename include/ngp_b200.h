@@ -243,6 +243,8 @@ int ngpb_testbed_reload_network_from_file(ngpb_testbed_t* t, const char* path);
  * Perspective and OpenCV lenses; alpha files, dynamic masks, white / black_transparent. max_images 0 = all.
  * An image file (*.exr, *.png, *.jpg) instead selects the neural-image mode (Testbed::load_image, src/testbed_image.cu:362-428). */
 int ngpb_testbed_load_training_data(ngpb_testbed_t* t, const char* path, uint32_t max_images);
+/* Testbed::load_file (src/testbed.cu:318-391): *.ingp / *.msgpack -> snapshot, a network config *.json -> network, anything else -> training data. */
+int ngpb_testbed_load_file(ngpb_testbed_t* t, const char* path);
 /* Testbed::save_snapshot(path, include_optimizer_state, compress) / load_snapshot(path), src/testbed.cu:4775-4972:
  * json::to_msgpack of the network config with a "snapshot" object (json_binding.h key names), zlib stream for *.ingp.
  * Files interchange with the reference's for the shipped NeRF configs. */

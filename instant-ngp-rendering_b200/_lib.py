@@ -96,6 +96,7 @@ SIGNATURES = {
     "ngpb_testbed_reset_network": (c_int, [c_vp, c_int]),
     "ngpb_testbed_reload_network_from_file": (c_int, [c_vp, c_cp]),
     "ngpb_testbed_load_training_data": (c_int, [c_vp, c_cp, c_u32]),
+    "ngpb_testbed_load_file": (c_int, [c_vp, c_cp]),
     "ngpb_testbed_save_snapshot": (c_int, [c_vp, c_cp, c_int, c_int]),
     "ngpb_testbed_load_snapshot": (c_int, [c_vp, c_cp]),
     "ngpb_testbed_image_metadata": (c_int, [c_vp, c_u32, c_vp]),

@@ -84,6 +84,12 @@ int ngpb_testbed_reload_network_from_file(ngpb_testbed_t* t, const char* path) {
 	t->impl->reload_network_from_file(path);
 	NGPB_API_END
 }
+int ngpb_testbed_load_file(ngpb_testbed_t* t, const char* path) {
+	NGPB_API_BEGIN
+	if (!path) throw std::runtime_error{"ngpb_testbed_load_file: null argument"};
+	t->impl->load_file(path);
+	NGPB_API_END
+}
 int ngpb_testbed_load_training_data(ngpb_testbed_t* t, const char* path, uint32_t max_images) {
 	NGPB_API_BEGIN
 	if (!path) throw std::runtime_error{"ngpb_testbed_load_training_data: null argument"};

@@ -132,6 +132,24 @@ void Testbed::reload_network_from_file(const std::string& path) {
 	reload_network_from_json(cfg);
 }
 
+// Testbed::load_file (src/testbed.cu:318-391): snapshot, network config, or training data by what the file is.
+void Testbed::load_file(const std::string& path) {
+	const std::string ext = path_extension(path);
+	if (!file_exists(path)) throw std::runtime_error{"File '" + path + "' does not exist."};
+	if (ext == "ingp" || ext == "msgpack") { load_snapshot(path); return; }
+	if (ext == "json") {
+		const std::vector<uint8_t> text = read_file(path);
+		const Json doc = Json::parse(std::string{text.begin(), text.end()});
+		if (doc.contains("snapshot")) throw std::runtime_error{"ngp-b200: snapshots in JSON form are not supported; use .ingp / .msgpack"};
+		if (doc.contains("path") && !doc.contains("frames")) throw std::runtime_error{"ngp-b200: camera paths are not part of the path (DESIGN.md section 7)"};
+		if (doc.contains("parent") || doc.contains("network") || doc.contains("encoding") || doc.contains("loss") || doc.contains("optimizer")) {
+			reload_network_from_file(path);
+			return;
+		}
+	}
+	load_training_data(path);
+}
+
 void write_snapshot_container(const std::string& path, const Json& config, bool compress) {
 	std::vector<uint8_t> blob = to_msgpack(config);
 	if (path_extension(path) == "ingp") blob = zlib_deflate(blob, compress ? Z_DEFAULT_COMPRESSION : 0);

@@ -192,7 +192,8 @@ public:
 	// Testbed::load_training_data for NeRF scenes (src/testbed.cu:125-152, src/nerf_loader.cu:273-740): transforms.json
 	// (or a directory of them); JPEG decoded on the GPU by nvjpeg, PNG on the host. max_images 0 = all.
 	void load_training_data(const std::string& path, uint32_t max_images = 0);
-	void load_image_file(const std::string& path);   // Testbed::load_image (src/testbed_image.cu:362-428): *.exr, *.png, *.jpg
+	void load_image_file(const std::string& path);
+	void load_file(const std::string& path);         // Testbed::load_file (src/testbed.cu:318-391)   // Testbed::load_image (src/testbed_image.cu:362-428): *.exr, *.png, *.jpg
 	DatasetInfo dataset_info;
 	ViewState view;
 

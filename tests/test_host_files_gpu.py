@@ -258,3 +258,25 @@ def test_cpp_loader_image_mode(ngp, tmp_path):
             else:   # sRGB -> linear: powf on the device here, numpy's float32 pow in the Python loader (last-bit differences)
                 np.testing.assert_allclose(x, y, rtol=4e-6, atol=1e-7)
         assert np.isfinite(b.loss)
+
+
+def test_load_file_dispatches_by_content(ngp, tmp_path):
+    """ngpb_testbed_load_file = Testbed::load_file: a scene description, a network config and a snapshot through one entry point."""
+    lib, check = ngp._lib.lib, ngp._lib.check
+    scene = _write_scene(tmp_path, "png")
+    with open(tmp_path / "net.json", "w") as f:
+        json.dump(CONFIG, f)
+    tb = ngp.Testbed()
+    check(lib.ngpb_testbed_load_file(tb._h, scene.encode()))
+    assert int(tb._get("n_images")) == 6
+    check(lib.ngpb_testbed_load_file(tb._h, str(tmp_path / "net.json").encode()))
+    assert tb.n_params > 0
+    for _ in range(10):
+        tb.train(1 << 14)
+    snap = str(tmp_path / "s.msgpack")
+    tb.save_snapshot_native(snap)
+    other = ngp.Testbed()
+    check(lib.ngpb_testbed_load_file(other._h, snap.encode()))
+    assert int(other._get("training_step")) == 10 and int(other._get("n_images")) == 6
+    assert lib.ngpb_testbed_load_file(other._h, str(tmp_path / "missing.ingp").encode()) != 0
+    assert "does not exist" in lib.ngpb_last_error().decode()
