@@ -35,6 +35,7 @@ ap.add_argument("--out", default="")
 ap.add_argument("--batch", type=int, default=1 << 18)
 ap.add_argument("--eval", type=int, default=1, help="0: skip the PSNR protocol (timing only)")
 ap.add_argument("--frames", type=int, default=10)
+ap.add_argument("--native", type=int, default=0, help="ours only: 1 = scene, snapshots through the library's host C++ (ngpb_testbed_load_training_data / save_snapshot / load_snapshot)")
 args = ap.parse_args()
 
 sys.path.insert(0, os.path.join(ROOT, "baseline", "_ref") if args.impl == "reference" else os.path.join(ROOT, "instant-ngp-rendering_b200"))
@@ -94,10 +95,11 @@ def run_fox(out):
     testbed = ngp.Testbed()
     testbed.root_dir = ROOT
     t0 = time.time()
-    testbed.load_training_data(scene)
-    rec = {"scene": scene, "load_s": time.time() - t0, "n_images": int(testbed.nerf.training.dataset.n_images), "checkpoints": []}
+    native = bool(args.native) and args.impl == "ours"
+    (testbed.load_training_data_native if native else testbed.load_training_data)(scene)
+    rec = {"scene": scene, "host": "c++" if native else "python binding", "load_s": time.time() - t0, "n_images": int(testbed.nerf.training.dataset.n_images), "checkpoints": []}
     if args.load:
-        testbed.load_snapshot(args.load)
+        (testbed.load_snapshot_native if native else testbed.load_snapshot)(args.load)
         rec["loaded"] = args.load
         rec["training_step"] = int(testbed.training_step)
         rec["eval"] = evaluate(testbed)
@@ -128,7 +130,7 @@ def run_fox(out):
     rec["render"] = time_render(testbed)
     print(rec["render"], flush=True)
     if args.save:
-        testbed.save_snapshot(args.save, False)
+        (testbed.save_snapshot_native if native else testbed.save_snapshot)(args.save, False)
         rec["saved"] = args.save
         rec["snapshot_bytes"] = os.path.getsize(args.save)
     out["fox"] = rec
