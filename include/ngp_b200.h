@@ -265,6 +265,10 @@ size_t ngpb_host_load_network_config(const char* path, char* buf, size_t cap);
 /* msgpack -> value tree -> msgpack with nlohmann's encoding choices; returns the size needed, 0 on failure. */
 size_t ngpb_host_msgpack_reencode(const void* in, size_t n, void* out, size_t cap);
 /* The loader's PNG decoder: 8-bit RGBA rows top to bottom into rgba (width * height * 4 bytes when cap allows). */
+/* What ngpb_testbed_load_training_data decides before it touches a pixel, as JSON: frame order after natural sort and
+ * sharpness culling, resolved image / alpha / mask paths, NGP camera matrices, lens, scale / offset / up / aabb_scale, flags.
+ * Returns the size needed incl. NUL, 0 on failure. */
+size_t ngpb_host_describe_dataset(const char* path, char* buf, size_t cap);
 int ngpb_host_decode_png(const char* path, void* rgba, size_t cap, int* width, int* height);
 /* The loader's OpenEXR reader (single-part scanline, HALF / FLOAT, NONE / ZIPS / ZIP): float RGBA rows top to bottom. */
 int ngpb_host_decode_exr(const char* path, float* rgba, size_t cap_floats, int* width, int* height);

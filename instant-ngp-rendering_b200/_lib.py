@@ -104,6 +104,7 @@ SIGNATURES = {
     "ngpb_testbed_dataset_info": (c_sz, [c_vp, c_vp, c_sz]),
     "ngpb_testbed_set_dataset_info": (c_int, [c_vp, c_cp]),
     "ngpb_host_load_network_config": (c_sz, [c_cp, c_vp, c_sz]),
+    "ngpb_host_describe_dataset": (c_sz, [c_cp, c_vp, c_sz]),
     "ngpb_host_msgpack_reencode": (c_sz, [c_vp, c_sz, c_vp, c_sz]),
     "ngpb_host_decode_png": (c_int, [c_cp, c_vp, c_sz, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "ngpb_host_decode_exr": (c_int, [c_cp, c_vp, c_sz, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),

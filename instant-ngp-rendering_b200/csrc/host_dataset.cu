@@ -15,6 +15,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <dirent.h>
 
 namespace ngpb {
@@ -454,3 +455,53 @@ void Testbed::load_training_data(const std::string& path, uint32_t max_images) {
 }
 
 } // namespace ngpb
+
+// ---- host-only view of the loader's decisions (no device, no pixels): what the CPU tests compare with loader.py ----------
+#include "../../include/ngp_b200.h"
+
+extern "C" size_t ngpb_host_describe_dataset(const char* path, char* buf, size_t cap) {
+	using namespace ngpb;
+	try {
+		if (!path) throw std::runtime_error{"ngpb_host_describe_dataset: null argument"};
+		std::vector<Json> jsons;
+		const DatasetDesc ds = describe_dataset(json_paths(path), jsons);
+		auto vec = [](const float* v, int n) { Json a = Json::array(); for (int i = 0; i < n; ++i) a.push_back(Json{(double)v[i]}); return a; };
+		Json j = Json::object();
+		j["n_images"] = (uint32_t)ds.frames.size();
+		j["aabb_scale"] = ds.aabb_scale;
+		j["scale"] = (double)ds.info.scale;
+		j["offset"] = vec(ds.info.offset, 3);
+		j["up"] = vec(ds.info.up, 3);
+		j["from_mitsuba"] = ds.info.from_mitsuba;
+		j["is_hdr"] = ds.info.is_hdr;
+		j["white_transparent"] = ds.white_transparent;
+		j["black_transparent"] = ds.black_transparent;
+		j["fix_premult"] = ds.fix_premult;
+		if (ds.info.has_render_aabb) j["render_aabb"] = vec(ds.info.render_aabb, 6);
+		Json frames = Json::array();
+		for (const FrameDesc& fr : ds.frames) {
+			Json f = Json::object();
+			f["path"] = fr.path;
+			f["alpha_path"] = fr.alpha_path;
+			f["mask_path"] = fr.mask_path;
+			float xform[12];
+			nerf_matrix_to_ngp(fr.xform_nerf, ds.info.scale, ds.info.offset, ds.info.from_mitsuba, xform);
+			f["xform"] = vec(xform, 12);
+			f["lens_mode"] = fr.lens.mode;
+			f["lens_params"] = vec(fr.lens.params, 7);
+			f["principal"] = vec(fr.lens.principal, 2);
+			// focal length at a nominal resolution given by the caller's json ("w", "h") when present, else 0: the real one needs the decoded image
+			const int w = fr.file_json->value("w", 0), h = fr.file_json->value("h", 0);
+			float fx = 0.0f, fy = 0.0f, pfx, pfy;
+			bool have = w > 0 && h > 0 && read_focal_length(*fr.file_json, w, h, fx, fy);
+			if (w > 0 && h > 0 && read_focal_length(fr.frame_json, w, h, pfx, pfy)) { fx = pfx; fy = pfy; have = true; }
+			const float focal[2] = {have ? fx : 0.0f, have ? fy : 0.0f};
+			f["focal_at_json_resolution"] = vec(focal, 2);
+			frames.push_back(f);
+		}
+		j["frames"] = frames;
+		const std::string text = j.dump();
+		if (buf && cap > 0) { const size_t n = text.size() < cap - 1 ? text.size() : cap - 1; memcpy(buf, text.data(), n); buf[n] = 0; }
+		return text.size() + 1;
+	} catch (const std::exception& e) { ngpb::set_last_error(e.what()); return 0; }
+}
