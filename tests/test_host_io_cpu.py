@@ -271,3 +271,46 @@ def test_exr_decoder_on_hand_written_files(ngp, tmp_path, kind):
     cw, ch = ctypes.c_int(), ctypes.c_int()
     assert ngp._lib.lib.ngpb_host_decode_exr(str(tmp_path / "piz.exr").encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0
     assert "not supported" in ngp._lib.lib.ngpb_last_error().decode()
+
+
+def _ref_json_vectors():
+    import gzip
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_json_vectors.json.gz")
+    with gzip.open(path, "rb") as f:
+        return json.loads(f.read().decode())
+
+
+def test_msgpack_writer_against_the_references_json_library(ngp):
+    """tests/golden/ref_json_vectors.json.gz holds json::to_msgpack of the reference's own nlohmann json (oracle/ref_json.cpp):
+    reading those bytes and writing them again must reproduce them exactly - integer widths, float32-when-exact, size classes of
+    str / bin / array / map, key order - which is what makes a snapshot written here byte-compatible with one written there."""
+    msgpack = pytest.importorskip("msgpack")
+    lib = ngp._lib.lib
+    vec = _ref_json_vectors()["to_msgpack"]
+    assert set(vec) >= {"integers", "floats", "strings", "containers", "binaries", "key_order", "snapshot_shaped"}
+    for name, v in vec.items():
+        want = bytes.fromhex(v["msgpack_hex"])
+        assert _reencode(lib, want) == want, name
+        # and the bytes mean what the JSON says (binaries are written as "bin:<hex>" in the JSON text)
+        def expect(x):
+            if isinstance(x, str) and x.startswith("bin:"):
+                return bytes.fromhex(x[4:])
+            if isinstance(x, list):
+                return [expect(e) for e in x]
+            if isinstance(x, dict):
+                return {k: expect(e) for k, e in x.items()}
+            return x
+        got = msgpack.unpackb(want, raw=False, strict_map_key=False)
+        doc = expect(json.loads(v["json"]))
+        assert got == doc, name   # float32-encoded values are exactly representable, so they decode to the same doubles
+
+
+def test_merge_patch_against_the_references_json_library(ngp, tmp_path):
+    """parent.merge_patch(child) of the reference's nlohmann json (merge_parent_network_config) = load_network_config here."""
+    lib = ngp._lib.lib
+    for name, v in _ref_json_vectors()["merge_patch"].items():
+        (tmp_path / "parent.json").write_text(v["parent"])
+        child = json.loads(__import__("re").sub(r"/\*.*?\*/|//[^\n]*", "", v["child"]))
+        child["parent"] = "parent.json"
+        (tmp_path / "child.json").write_text(json.dumps(child))
+        assert _config_text(lib, tmp_path / "child.json") == json.loads(v["merged"]), name
