@@ -59,7 +59,7 @@ merges = {
     "replace_non_object": ('{"optimizer": {"otype": "Adam", "learning_rate": 0.01}, "envmap": [1, 2, 3]}', '{"optimizer": "none", "envmap": {"resolution": [4, 4]}, "new": {"a": {"b": null, "c": 1}}}'),
     "with_comments": ('{ // parent\n "a": {"x": 1, "y": 2} /* c */ }', '{"a": {"y": null, "z": [1, {"k": null}]}}'),
 }
-out = {"_source": "nlohmann json vendored by the reference (tiny-cuda-nn/dependencies/json/json.hpp) through oracle/ref_json.cpp; strings 'bin:<hex>' stand for json::binary_t",
+out = {"_source": "nlohmann json vendored by the reference (tiny-cuda-nn/dependencies/json/json.hpp) through oracle/ref_json.cc; strings 'bin:<hex>' stand for json::binary_t",
        "to_msgpack": {k: {"json": v, "msgpack_hex": to_msgpack(v).hex()} for k, v in docs.items()},
        "merge_patch": {k: {"parent": p, "child": c, "merged": merge(p, c)} for k, (p, c) in merges.items()}}
 import gzip

@@ -281,7 +281,7 @@ def _ref_json_vectors():
 
 
 def test_msgpack_writer_against_the_references_json_library(ngp):
-    """tests/golden/ref_json_vectors.json.gz holds json::to_msgpack of the reference's own nlohmann json (oracle/ref_json.cpp):
+    """tests/golden/ref_json_vectors.json.gz holds json::to_msgpack of the reference's own nlohmann json (oracle/ref_json.cc):
     reading those bytes and writing them again must reproduce them exactly - integer widths, float32-when-exact, size classes of
     str / bin / array / map, key order - which is what makes a snapshot written here byte-compatible with one written there."""
     msgpack = pytest.importorskip("msgpack")
