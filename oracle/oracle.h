@@ -15,7 +15,7 @@
  * reference is built headless from its sources (baseline/build_ref.sh), baseline/harness.cu runs tiny-cuda-nn's
  * kernel_grid / kernel_grid_backward, kernel_mlp_fused (+ backward), ngp::NerfNetwork and adam_step / ema_step on
  * the seeded inputs of tests/ref_gpu_cases.py, tests/golden/ref_gpu_vectors.npz holds their outputs, and
- * tests/test_ref_fixture_cpu.py checks this oracle against them (grid forward bit-identical; MLP, gradients and
+ * tests/test_ref_gpu_fixture_cpu.py checks this oracle against them (grid forward bit-identical; MLP, gradients and
  * Adam within the tolerances stated there - the reference accumulates in fp16 and sums atomics in arbitrary order).
  * The container formats (msgpack, merge_patch) are pinned to the reference's own JSON library
  * (oracle/ref_json.cc, tests/golden/ref_json_vectors.json.gz), snapshots and loader metadata to a snapshot the
