@@ -31,7 +31,7 @@ struct HostImageF {
 	int width = 0, height = 0;
 	std::vector<float> rgba;
 };
-// OpenEXR, single-part scanline, HALF / FLOAT channels, compression NONE / ZIPS / ZIP (host_exr.cu).
+// OpenEXR, single-part scanline, HALF / FLOAT channels, compression NONE / RLE / ZIPS / ZIP / PIZ (host_exr.cu).
 HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name_for_errors);
 
 // PNG (8 / 16 bit, grey / grey-alpha / RGB / RGBA / palette, non-interlaced) decoded on the host with zlib.

@@ -200,6 +200,8 @@ def _cv2_exr(path):
     if img is None:
         pytest.skip("this OpenCV build cannot read EXR")
     img = img.astype(np.float32)
+    if img.ndim == 2:
+        img = np.stack([img] * 3, -1)
     a = img[:, :, 3:4] if img.shape[2] == 4 else np.ones(img.shape[:2] + (1,), dtype=np.float32)
     return np.concatenate([img[:, :, 2::-1], a], axis=-1)
 
@@ -266,11 +268,80 @@ def test_exr_decoder_on_hand_written_files(ngp, tmp_path, kind):
             want[..., k] = data[n].astype(np.float32)
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
     # unsupported compression is refused, not misread
-    bad = header.replace(attr("compression", "compression", bytes([comp])), attr("compression", "compression", bytes([4])))
-    (tmp_path / "piz.exr").write_bytes(bad + b"\0" * 64)
+    bad = header.replace(attr("compression", "compression", bytes([comp])), attr("compression", "compression", bytes([5])))
+    (tmp_path / "pxr24.exr").write_bytes(bad + b"\0" * 64)
     cw, ch = ctypes.c_int(), ctypes.c_int()
-    assert ngp._lib.lib.ngpb_host_decode_exr(str(tmp_path / "piz.exr").encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0
+    assert ngp._lib.lib.ngpb_host_decode_exr(str(tmp_path / "pxr24.exr").encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0
     assert "not supported" in ngp._lib.lib.ngpb_last_error().decode()
+
+
+def test_exr_decoder_on_openexr_written_fixtures(ngp):
+    """tests/golden/exr/*.exr were written by OpenCV's bundled OpenEXR (make_exr_fixtures.py): PIZ with the 14-bit and the
+    modulo-2^16 wavelet, long Huffman codes, the run-length symbol, RLE, ZIP. The decoded float RGBA must hash to what
+    OpenEXR's own reader returned for the same file."""
+    import hashlib
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "exr")
+    with open(os.path.join(here, "digests.json")) as f:
+        files = json.load(f)["files"]
+    assert len(files) >= 5
+    for name, want in files.items():
+        got = _decode_exr(ngp._lib.lib, os.path.join(here, name + ".exr"))
+        assert got.shape == (want["height"], want["width"], 4), name
+        assert hashlib.sha256(got.tobytes()).hexdigest() == want["sha256"], name
+
+
+@pytest.mark.parametrize("compression", ["NO", "RLE", "ZIPS", "ZIP", "PIZ"])
+def test_exr_decoder_against_opencv_round_trips(ngp, tmp_path, compression):
+    """Every compression tinyexr reads (the reference's loader, src/tinyexr_wrapper.cu:153-260), HALF and FLOAT, 1 / 3 / 4
+    channels, sizes around the chunk heights and below one wavelet level: written and read back by OpenCV's OpenEXR, bit for bit."""
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(7)
+    flag = getattr(cv2, "IMWRITE_EXR_COMPRESSION_" + compression)
+    for (h, w, c) in [(37, 53, 3), (1, 1, 3), (33, 1, 4), (2, 77, 1), (70, 90, 4)]:
+        yy, xx = np.mgrid[0:h, 0:w]
+        for kind in ("noise", "smooth", "flat"):
+            if kind == "noise":
+                img = rng.standard_normal((h, w, c)).astype(np.float32)
+            elif kind == "smooth":
+                img = np.stack([np.sin(xx * 0.05 + k) + np.cos(yy * 0.03 * k) for k in range(c)], -1).astype(np.float32)
+            else:
+                img = np.full((h, w, c), 0.25, np.float32)
+                img[h // 2:, :, 0] = 1.0
+            if c == 1:
+                img = img[..., 0]
+            for pixel_type in (cv2.IMWRITE_EXR_TYPE_HALF, cv2.IMWRITE_EXR_TYPE_FLOAT):
+                path = tmp_path / "t.exr"
+                try:
+                    ok = cv2.imwrite(str(path), img, [cv2.IMWRITE_EXR_COMPRESSION, flag, cv2.IMWRITE_EXR_TYPE, pixel_type])
+                except cv2.error:
+                    ok = False
+                if not ok:
+                    pytest.skip("this OpenCV build cannot write EXR")
+                want = _cv2_exr(path)
+                got = _decode_exr(ngp._lib.lib, path)
+                assert got.shape == want.shape, (h, w, c, kind)
+                assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (h, w, c, kind, pixel_type)
+
+
+def test_exr_decoder_refuses_corrupt_piz_chunks(ngp, tmp_path):
+    """Truncated or bit-flipped PIZ data ends in an error (or other pixels), never in a crash or an out-of-bounds write."""
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "exr")
+    blob = open(os.path.join(here, "piz_half_rgb.exr"), "rb").read()
+    rng = np.random.default_rng(3)
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+    out = np.zeros((37, 53, 4), dtype=np.float32)
+    failures = 0
+    for trial in range(40):
+        bad = bytearray(blob)
+        if trial % 2:
+            bad = bad[:int(rng.integers(400, len(bad)))]
+        else:
+            for k in rng.integers(700, len(bad), size=4):
+                bad[int(k)] ^= 1 << int(rng.integers(0, 8))
+        (tmp_path / "bad.exr").write_bytes(bytes(bad))
+        failures += ngp._lib.lib.ngpb_host_decode_exr(str(tmp_path / "bad.exr").encode(), out.ctypes.data_as(ctypes.c_void_p), out.size, ctypes.byref(cw), ctypes.byref(ch)) != 0
+    assert failures >= 20
 
 
 def _ref_json_vectors():
