@@ -315,11 +315,11 @@ struct JpegDecoder {
 };
 } // namespace
 
-// One image file as RGBA8 texels in device memory. JPEG: nvjpeg decodes on the GPU; PNG: host inflate + upload.
+// One image file as RGBA8 texels in device memory, decoder chosen by content. JPEG: nvjpeg decodes on the GPU; PNG / BMP / TGA / PNM: host decode + upload.
 static void decode_to_device(JpegDecoder& jpeg, const std::string& path, DeviceBuffer& rgb_scratch, DeviceBuffer& out, int& width, int& height, cudaStream_t stream) {
 	const std::string ext = path_extension(path);
 	const std::vector<uint8_t> file = read_file(path);
-	if (ext == "jpg" || ext == "jpeg") {
+	if (is_jpeg_file(file)) {
 		jpeg.init();
 		int n_components = 0, widths[NVJPEG_MAX_COMPONENT], heights[NVJPEG_MAX_COMPONENT];
 		nvjpegChromaSubsampling_t subsampling;
@@ -338,15 +338,15 @@ static void decode_to_device(JpegDecoder& jpeg, const std::string& path, DeviceB
 		NGPB_CUDA_CHECK(cudaGetLastError());
 		return;
 	}
-	if (ext == "png") {
-		const HostImage img = decode_png(file, path);
+	if (ext != "exr") {
+		const HostImage img = decode_image_rgba8(file, path);   // PNG, BMP, TGA, PNM by content (host_image.cu)
 		width = img.width; height = img.height;
 		out.alloc(img.rgba.size(), stream);
 		NGPB_CUDA_CHECK(cudaMemcpyAsync(out.ptr, img.rgba.data(), img.rgba.size(), cudaMemcpyHostToDevice, stream));
 		NGPB_CUDA_CHECK(cudaStreamSynchronize(stream));   // the host image goes away
 		return;
 	}
-	throw std::runtime_error{"ngp-b200: the C++ loader decodes JPEG, PNG and EXR files; '" + path + "' is none of them"};
+	throw std::runtime_error{"ngp-b200: '" + path + "' is an EXR file where an 8-bit image is expected"};
 }
 
 // from_rgba32 (src/common_host.cu:268-298): sRGB8 straight alpha -> linear float, colours multiplied by alpha

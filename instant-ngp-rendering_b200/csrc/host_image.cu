@@ -1,0 +1,257 @@
+// The loader's other 8-bit image formats. The reference decodes every non-EXR dataset image with stb_image
+// (load_stbi, src/common_host.cu:214-217; nerf_loader.cu:571-618), which picks the decoder from the file's content, not
+// its name. JPEG goes to nvjpeg and PNG to host_png.cu; this file adds what is left of stb_image's list that datasets
+// use - BMP, TGA and binary PNM - and the content sniffing in front of them. Output as everywhere: RGBA8, rows top to
+// bottom, alpha 255 where the file has none. Host only.
+#include "host_io.h"
+
+#include <cstring>
+#include <stdexcept>
+
+namespace ngpb {
+
+namespace {
+template <typename T> T rd(const uint8_t* p) { T v; memcpy(&v, p, sizeof(T)); return v; }
+
+[[noreturn]] void fail(const std::string& name, const std::string& why) {
+	throw std::runtime_error{"Could not open image file '" + name + "': " + why};
+}
+
+// position of the lowest set bit and the number of set bits of a channel mask
+int mask_shift(uint32_t m) { int s = 0; while (m && !(m & 1)) { m >>= 1; ++s; } return s; }
+int mask_bits(uint32_t m) { int n = 0; while (m) { n += m & 1; m >>= 1; } return n; }
+// a `bits`-wide channel value widened to 8 bits by bit replication (what stb_image does for 5- and 6-bit channels)
+uint8_t widen(uint32_t v, int bits) {
+	if (bits <= 0) return 0;
+	if (bits >= 8) return (uint8_t)(v >> (bits - 8));
+	uint32_t out = v << (8 - bits);
+	for (int have = bits; have < 8; have += bits) out |= out >> have;
+	return (uint8_t)out;
+}
+
+// ---- BMP: BITMAPCOREHEADER / INFOHEADER / V4 / V5; 1, 4, 8 bit palette, 16 / 24 / 32 bit, BI_RGB and BI_BITFIELDS ----
+HostImage decode_bmp(const std::vector<uint8_t>& f, const std::string& name) {
+	if (f.size() < 26) fail(name, "truncated BMP");
+	const uint32_t data_at = rd<uint32_t>(&f[10]);
+	const uint32_t hsz = rd<uint32_t>(&f[14]);
+	if (hsz != 12 && hsz != 40 && hsz != 56 && hsz != 108 && hsz != 124) fail(name, "unknown BMP header");
+	if (f.size() < 14 + (size_t)hsz) fail(name, "truncated BMP");
+	int w, h, bpp;
+	uint32_t compression = 0, mr = 0, mg = 0, mb = 0, ma = 0;
+	if (hsz == 12) {
+		w = rd<uint16_t>(&f[18]); h = rd<uint16_t>(&f[20]); bpp = rd<uint16_t>(&f[24]);
+	} else {
+		w = rd<int32_t>(&f[18]); h = rd<int32_t>(&f[22]); bpp = rd<uint16_t>(&f[28]);
+		compression = rd<uint32_t>(&f[30]);
+		if (compression == 1 || compression == 2) fail(name, "run-length coded BMPs are not supported");
+		if (compression != 0 && compression != 3) fail(name, "unsupported BMP compression");
+		if (compression == 3 || hsz >= 56) {
+			// masks follow a 40-byte header, or are part of the larger ones
+			if (f.size() < 14 + 40 + 12) fail(name, "truncated BMP");
+			if (compression == 3) { mr = rd<uint32_t>(&f[54]); mg = rd<uint32_t>(&f[58]); mb = rd<uint32_t>(&f[62]); }
+			if (hsz >= 56 && compression == 3) ma = rd<uint32_t>(&f[66]);
+		}
+	}
+	const bool flip = h > 0;
+	if (h < 0) h = -h;
+	if (w <= 0 || h <= 0 || w > (1 << 16) || h > (1 << 16)) fail(name, "bad BMP size");
+	if (bpp != 1 && bpp != 4 && bpp != 8 && bpp != 16 && bpp != 24 && bpp != 32) fail(name, "unsupported BMP bit depth");
+	if (compression == 0) {
+		if (bpp == 16) { mr = 31u << 10; mg = 31u << 5; mb = 31u; }
+		else if (bpp == 32) { mr = 0xFFu << 16; mg = 0xFFu << 8; mb = 0xFFu; ma = 0xFFu << 24; }
+	} else if (bpp != 16 && bpp != 32) {
+		fail(name, "BMP bit fields need 16 or 32 bits per pixel");
+	} else if (!mr || !mg || !mb) {
+		fail(name, "bad BMP channel masks");
+	}
+
+	// palette: right after the header (and after the three masks of a 40-byte BI_BITFIELDS header)
+	uint8_t palette[256][4] = {};
+	if (bpp <= 8) {
+		const size_t entry = hsz == 12 ? 3 : 4;
+		size_t at = 14 + (size_t)hsz;
+		size_t n = (data_at > at ? data_at - at : 0) / entry;
+		if (n > 256) n = 256;
+		if (at + n * entry > f.size()) fail(name, "truncated BMP palette");
+		for (size_t i = 0; i < n; ++i, at += entry) {
+			palette[i][2] = f[at]; palette[i][1] = f[at + 1]; palette[i][0] = f[at + 2]; palette[i][3] = 255;
+		}
+	}
+	const size_t stride = (((size_t)w * bpp + 31) / 32) * 4;
+	if (data_at > f.size() || (f.size() - data_at) / stride < (size_t)h) fail(name, "truncated BMP pixel data");
+
+	HostImage img;
+	img.width = w; img.height = h;
+	img.rgba.resize((size_t)w * h * 4);
+	const int rs = mask_shift(mr), gs = mask_shift(mg), bs = mask_shift(mb), as = mask_shift(ma);
+	const int rb = mask_bits(mr), gb = mask_bits(mg), bb = mask_bits(mb), ab = mask_bits(ma);
+	uint32_t any_alpha = 0;
+	for (int y = 0; y < h; ++y) {
+		const uint8_t* row = &f[data_at + stride * (size_t)y];
+		uint8_t* out = &img.rgba[(size_t)(flip ? h - 1 - y : y) * w * 4];
+		for (int x = 0; x < w; ++x, out += 4) {
+			if (bpp <= 8) {
+				const int per_byte = 8 / bpp;
+				const int idx = (row[x / per_byte] >> (8 - bpp * (x % per_byte + 1))) & ((1 << bpp) - 1);
+				memcpy(out, palette[idx], 4);
+				out[3] = 255;
+			} else if (bpp == 24) {
+				out[0] = row[x * 3 + 2]; out[1] = row[x * 3 + 1]; out[2] = row[x * 3]; out[3] = 255;
+			} else {
+				const uint32_t v = bpp == 16 ? rd<uint16_t>(row + x * 2) : rd<uint32_t>(row + x * 4);
+				out[0] = widen((v & mr) >> rs, rb);
+				out[1] = widen((v & mg) >> gs, gb);
+				out[2] = widen((v & mb) >> bs, bb);
+				out[3] = ma ? widen((v & ma) >> as, ab) : 255;
+				any_alpha |= out[3];
+			}
+		}
+	}
+	// a 32-bit file whose alpha bytes are all zero carries no alpha (stb_image's rule): opaque
+	if (bpp == 32 && ma && any_alpha == 0) for (size_t i = 3; i < img.rgba.size(); i += 4) img.rgba[i] = 255;
+	return img;
+}
+
+// ---- TGA: colour-mapped / true-colour / grey, plain or run-length coded, 8 / 15 / 16 / 24 / 32 bits ----
+bool looks_like_tga(const std::vector<uint8_t>& f) {
+	if (f.size() < 18) return false;
+	const int cmap = f[1], type = f[2] & 7, bits = f[16];
+	if (cmap > 1 || (f[2] & ~0x0B)) return false;
+	if (type != 1 && type != 2 && type != 3) return false;
+	if (cmap == 1) {
+		if (type != 1) return false;
+		const int eb = f[7];
+		if (eb != 8 && eb != 15 && eb != 16 && eb != 24 && eb != 32) return false;
+		if (bits != 8 && bits != 16) return false;
+	} else {
+		if (type == 1) return false;
+		if (bits != 8 && bits != 15 && bits != 16 && bits != 24 && bits != 32) return false;
+	}
+	return rd<uint16_t>(&f[12]) > 0 && rd<uint16_t>(&f[14]) > 0;
+}
+
+// one stored TGA texel of `bits` bits -> RGBA8 (16-bit true colour is 1-5-5-5 with the top bit ignored, as stb_image does)
+void tga_texel(const uint8_t* p, int bits, bool grey, uint8_t* out) {
+	if (grey) {
+		out[0] = out[1] = out[2] = p[0];
+		out[3] = bits == 16 ? p[1] : 255;
+	} else if (bits == 15 || bits == 16) {
+		const uint32_t v = rd<uint16_t>(p);
+		out[0] = widen((v >> 10) & 31, 5); out[1] = widen((v >> 5) & 31, 5); out[2] = widen(v & 31, 5); out[3] = 255;
+	} else {
+		out[0] = p[2]; out[1] = p[1]; out[2] = p[0];
+		out[3] = bits == 32 ? p[3] : 255;
+	}
+}
+
+HostImage decode_tga(const std::vector<uint8_t>& f, const std::string& name) {
+	if (!looks_like_tga(f)) fail(name, "not a supported TGA file");
+	const int id_len = f[0], cmap = f[1], type = f[2] & 7;
+	const bool rle = (f[2] & 8) != 0, grey = type == 3;
+	const int cmap_first = rd<uint16_t>(&f[3]), cmap_len = rd<uint16_t>(&f[5]), cmap_bits = f[7];
+	const int w = rd<uint16_t>(&f[12]), h = rd<uint16_t>(&f[14]), bits = f[16];
+	const bool top_down = (f[17] >> 5) & 1;
+	size_t at = 18 + (size_t)id_len;
+	std::vector<uint8_t> palette;
+	if (cmap) {
+		const size_t eb = (size_t)(cmap_bits + 7) / 8;
+		if (at + eb * cmap_len > f.size()) fail(name, "truncated TGA palette");
+		palette.resize((size_t)cmap_len * 4);
+		for (int i = 0; i < cmap_len; ++i) tga_texel(&f[at + eb * i], cmap_bits, cmap_bits == 8, &palette[(size_t)i * 4]);
+		at += eb * cmap_len;
+	}
+	const size_t texel = (size_t)(bits + 7) / 8;
+	// a run packet expands at most 128 texels from 1 + texel bytes: refuse sizes the file cannot hold before allocating
+	if (at > f.size() || (size_t)w * h > (f.size() - at) * (rle ? 128 : 1) / (rle ? 1 : texel)) fail(name, "truncated TGA pixel data");
+	HostImage img;
+	img.width = w; img.height = h;
+	img.rgba.resize((size_t)w * h * 4);
+	auto store = [&](size_t i, const uint8_t* p) {
+		uint8_t* out = &img.rgba[i * 4];
+		if (cmap) {
+			int idx = (bits == 8 ? p[0] : rd<uint16_t>(p)) - cmap_first;
+			if (idx < 0 || idx >= cmap_len) idx = 0;
+			if (cmap_len > 0) memcpy(out, &palette[(size_t)idx * 4], 4); else { out[0] = out[1] = out[2] = 0; out[3] = 255; }
+		} else {
+			tga_texel(p, bits, grey, out);
+		}
+	};
+	const size_t n = (size_t)w * h;
+	if (!rle) {
+		if (at + n * texel > f.size()) fail(name, "truncated TGA pixel data");
+		for (size_t i = 0; i < n; ++i) store(i, &f[at + i * texel]);
+	} else {
+		size_t i = 0;
+		while (i < n) {
+			if (at >= f.size()) fail(name, "truncated TGA pixel data");
+			const int packet = f[at++];
+			const size_t count = (size_t)(packet & 127) + 1;
+			if (i + count > n) fail(name, "corrupt TGA run");
+			if (packet & 128) {
+				if (at + texel > f.size()) fail(name, "truncated TGA pixel data");
+				for (size_t k = 0; k < count; ++k) store(i++, &f[at]);
+				at += texel;
+			} else {
+				if (at + texel * count > f.size()) fail(name, "truncated TGA pixel data");
+				for (size_t k = 0; k < count; ++k, at += texel) store(i++, &f[at]);
+			}
+		}
+	}
+	if (!top_down) {
+		std::vector<uint8_t> row((size_t)w * 4);
+		for (int y = 0; y < h / 2; ++y) {
+			uint8_t* a = &img.rgba[(size_t)y * w * 4];
+			uint8_t* b = &img.rgba[(size_t)(h - 1 - y) * w * 4];
+			memcpy(row.data(), a, row.size()); memcpy(a, b, row.size()); memcpy(b, row.data(), row.size());
+		}
+	}
+	return img;
+}
+
+// ---- binary PNM: P5 (grey) and P6 (RGB), 8 or 16 bits per sample (16-bit samples keep their high byte) ----
+HostImage decode_pnm(const std::vector<uint8_t>& f, const std::string& name) {
+	size_t at = 2;
+	auto number = [&]() {
+		for (;;) {
+			while (at < f.size() && (f[at] == ' ' || f[at] == '\t' || f[at] == '\n' || f[at] == '\r' || f[at] == '\f' || f[at] == '\v')) ++at;
+			if (at < f.size() && f[at] == '#') { while (at < f.size() && f[at] != '\n' && f[at] != '\r') ++at; continue; }
+			break;
+		}
+		if (at >= f.size() || f[at] < '0' || f[at] > '9') fail(name, "bad PNM header");
+		long v = 0;
+		while (at < f.size() && f[at] >= '0' && f[at] <= '9' && v < (1 << 24)) v = v * 10 + (f[at++] - '0');
+		return (int)v;
+	};
+	const int channels = f[1] == '6' ? 3 : 1;
+	const int w = number(), h = number(), maxval = number();
+	++at;   // the single whitespace byte after maxval
+	if (w <= 0 || h <= 0 || w > (1 << 16) || h > (1 << 16) || maxval <= 0 || maxval > 65535) fail(name, "bad PNM header");
+	const size_t sample = maxval > 255 ? 2 : 1;
+	const size_t n = (size_t)w * h;
+	if (at > f.size() || (f.size() - at) / (sample * channels) < n) fail(name, "truncated PNM pixel data");
+	HostImage img;
+	img.width = w; img.height = h;
+	img.rgba.resize(n * 4);
+	for (size_t i = 0; i < n; ++i) {
+		const uint8_t* p = &f[at + i * channels * sample];
+		uint8_t* out = &img.rgba[i * 4];
+		for (int c = 0; c < 3; ++c) out[c] = p[(channels == 3 ? c : 0) * sample];
+		out[3] = 255;
+	}
+	return img;
+}
+} // namespace
+
+bool is_jpeg_file(const std::vector<uint8_t>& f) { return f.size() > 3 && f[0] == 0xFF && f[1] == 0xD8 && f[2] == 0xFF; }
+
+HostImage decode_image_rgba8(const std::vector<uint8_t>& f, const std::string& name) {
+	static const uint8_t png_magic[8] = {0x89, 'P', 'N', 'G', '\r', '\n', 0x1A, '\n'};
+	if (f.size() >= 8 && memcmp(f.data(), png_magic, 8) == 0) return decode_png(f, name);
+	if (is_jpeg_file(f)) fail(name, "JPEG files are decoded on the device (nvjpeg), not by the host decoder");
+	if (f.size() >= 2 && f[0] == 'B' && f[1] == 'M') return decode_bmp(f, name);
+	if (f.size() >= 3 && f[0] == 'P' && (f[1] == '5' || f[1] == '6')) return decode_pnm(f, name);
+	if (looks_like_tga(f)) return decode_tga(f, name);
+	fail(name, "unknown image type (JPEG, PNG, BMP, TGA, binary PNM and EXR are read)");
+}
+
+} // namespace ngpb

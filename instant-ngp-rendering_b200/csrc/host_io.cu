@@ -198,6 +198,16 @@ extern "C" int ngpb_host_decode_png(const char* path, void* rgba, size_t cap, in
 	} catch (const std::exception& e) { ngpb::set_last_error(e.what()); return NGPB_ERROR; }
 }
 
+extern "C" int ngpb_host_decode_image(const char* path, void* rgba, size_t cap, int* width, int* height) {
+	try {
+		if (!path || !width || !height) throw std::runtime_error{"ngpb_host_decode_image: null argument"};
+		const ngpb::HostImage img = ngpb::decode_image_rgba8(ngpb::read_file(path), path);
+		*width = img.width; *height = img.height;
+		if (rgba && cap >= img.rgba.size()) memcpy(rgba, img.rgba.data(), img.rgba.size());
+		return NGPB_OK;
+	} catch (const std::exception& e) { ngpb::set_last_error(e.what()); return NGPB_ERROR; }
+}
+
 extern "C" int ngpb_host_decode_exr(const char* path, float* rgba, size_t cap_floats, int* width, int* height) {
 	try {
 		if (!path || !width || !height) throw std::runtime_error{"ngpb_host_decode_exr: null argument"};

@@ -385,3 +385,90 @@ def test_merge_patch_against_the_references_json_library(ngp, tmp_path):
         child["parent"] = "parent.json"
         (tmp_path / "child.json").write_text(json.dumps(child))
         assert _config_text(lib, tmp_path / "child.json") == json.loads(v["merged"]), name
+
+
+def _decode_image(lib, path):
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+    assert lib.ngpb_host_decode_image(str(path).encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) == 0, lib.ngpb_last_error().decode()
+    out = np.zeros((ch.value, cw.value, 4), dtype=np.uint8)
+    assert lib.ngpb_host_decode_image(str(path).encode(), out.ctypes.data_as(ctypes.c_void_p), out.size, ctypes.byref(cw), ctypes.byref(ch)) == 0
+    return out
+
+
+@pytest.mark.parametrize("shape", [(13, 17), (1, 1), (8, 3), (30, 64)])
+def test_stb_formats_against_pillow(ngp, tmp_path, shape):
+    """BMP (24 / 32 bit, 8 / 4 / 1 bit palette), TGA (true colour, grey, grey + alpha, colour-mapped, run-length coded, both row
+    orders), binary PGM / PPM and PNG through the content-sniffing decoder the loader uses for every 8-bit file but JPEG
+    (the reference: stb_image behind load_stbi, src/common_host.cu:214-217). Files written by Pillow, texels bit for bit."""
+    Image = pytest.importorskip("PIL.Image")
+    lib = ngp._lib.lib
+    h, w = shape
+    rng = np.random.default_rng(h * 100 + w)
+    rgba = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    rgba[..., 3] |= 1   # a 32-bit BMP whose alpha is zero everywhere reads as opaque (stb_image's rule), tested below
+    rgb, grey = np.ascontiguousarray(rgba[..., :3]), np.ascontiguousarray(rgba[..., 0])
+    opaque = np.concatenate([rgb, np.full((h, w, 1), 255, np.uint8)], -1)
+    grey4 = np.stack([grey] * 3 + [np.full((h, w), 255, np.uint8)], -1)
+    pal = Image.fromarray(rgb).quantize(16)
+    bw = Image.fromarray(grey).convert("1")
+    cases = [
+        ("bmp", Image.fromarray(rgb), {}, opaque), ("bmp", Image.fromarray(rgba), {}, rgba), ("bmp", Image.fromarray(grey), {}, grey4),
+        ("bmp", pal, {}, np.array(pal.convert("RGBA"))), ("bmp", bw, {}, np.array(bw.convert("RGBA"))),
+        ("tga", Image.fromarray(rgb), {}, opaque), ("tga", Image.fromarray(rgba), {"compression": "tga_rle"}, rgba),
+        ("tga", Image.fromarray(grey), {"compression": "tga_rle"}, grey4), ("tga", pal, {}, np.array(pal.convert("RGBA"))),
+        ("tga", Image.fromarray(rgb), {"orientation": 1}, opaque),
+        ("tga", Image.fromarray(np.ascontiguousarray(rgba[..., [0, 3]]), "LA"), {}, np.concatenate([grey4[..., :3], rgba[..., 3:]], -1)),
+        ("ppm", Image.fromarray(rgb), {}, opaque), ("pgm", Image.fromarray(grey), {}, grey4), ("png", Image.fromarray(rgba), {}, rgba),
+    ]
+    for k, (ext, im, kw, want) in enumerate(cases):
+        # the name does not decide the decoder: every file is also read under a wrong extension
+        for name in ("c%d.%s" % (k, ext), "c%d.dat" % k):
+            path = tmp_path / name
+            im.save(str(path), format={"bmp": "BMP", "tga": "TGA", "ppm": "PPM", "pgm": "PPM", "png": "PNG"}[ext], **kw)
+            got = _decode_image(lib, path)
+            assert got.shape == want.shape and np.array_equal(got, want), (k, ext, kw)
+
+
+def test_bmp_bit_fields_and_alpha_rules(ngp, tmp_path):
+    """Hand-written BMPs Pillow does not write: 16-bit 5-6-5 bit fields, 16-bit BI_RGB (5-5-5), top-down rows, a 32-bit file whose
+    alpha bytes are all zero (opaque by stb_image's rule), and the refusals (run-length coding, JPEG handed to the host decoder)."""
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(4)
+    h, w = 5, 7
+
+    def widen(v, bits):
+        v = v.astype(np.uint32) << (8 - bits)
+        return (v | (v >> bits) | (v >> (2 * bits) if bits < 4 else 0)).astype(np.uint8)
+
+    def bmp(bpp, rows, compression=0, masks=b"", height=None):
+        stride = (w * bpp + 31) // 32 * 4
+        data = b"".join(r.tobytes() + b"\0" * (stride - len(r.tobytes())) for r in rows)
+        info = struct.pack("<IiiHHIIiiII", 40, w, h if height is None else height, 1, bpp, compression, len(data), 2835, 2835, 0, 0) + masks
+        return b"BM" + struct.pack("<IHHI", 14 + len(info) + len(data), 0, 0, 14 + len(info)) + info + data
+
+    v565 = rng.integers(0, 1 << 16, (h, w), dtype=np.uint16)
+    (tmp_path / "565.bmp").write_bytes(bmp(16, v565[::-1], 3, struct.pack("<III", 0xF800, 0x07E0, 0x001F)))
+    got = _decode_image(lib, tmp_path / "565.bmp")
+    assert np.array_equal(got[..., 0], widen(v565 >> 11, 5)) and np.array_equal(got[..., 1], widen((v565 >> 5) & 63, 6))
+    assert np.array_equal(got[..., 2], widen(v565 & 31, 5)) and (got[..., 3] == 255).all()
+
+    (tmp_path / "555.bmp").write_bytes(bmp(16, v565, 0, height=-h))   # top-down
+    got = _decode_image(lib, tmp_path / "555.bmp")
+    assert np.array_equal(got[..., 0], widen((v565 >> 10) & 31, 5)) and np.array_equal(got[..., 2], widen(v565 & 31, 5))
+
+    bgr0 = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    bgr0[..., 3] = 0
+    (tmp_path / "x888.bmp").write_bytes(bmp(32, bgr0[::-1]))
+    got = _decode_image(lib, tmp_path / "x888.bmp")
+    assert np.array_equal(got[..., :3], bgr0[..., 2::-1]) and (got[..., 3] == 255).all()
+
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+    (tmp_path / "rle.bmp").write_bytes(bmp(8, np.zeros((h, w), np.uint8), 1))
+    assert lib.ngpb_host_decode_image(str(tmp_path / "rle.bmp").encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0
+    assert "run-length" in lib.ngpb_last_error().decode()
+    (tmp_path / "a.jpg").write_bytes(b"\xff\xd8\xff\xe0" + b"\0" * 64)
+    assert lib.ngpb_host_decode_image(str(tmp_path / "a.jpg").encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0
+    assert "nvjpeg" in lib.ngpb_last_error().decode()
+    (tmp_path / "noise.bin").write_bytes(bytes(rng.integers(128, 256, 64, dtype=np.uint8)))
+    assert lib.ngpb_host_decode_image(str(tmp_path / "noise.bin").encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0
+    assert "unknown image type" in lib.ngpb_last_error().decode()
