@@ -151,12 +151,23 @@ def build_examples(verbose=False):
     return exe
 
 
+def build_integration(verbose=False):
+    """integration/_build/tcnn_caller_{b200,ref}: one caller of the reference's tcnn::cpp facade linked against this library (through
+    integration/tcnn_cpp_api_b200.cpp) and against the reference's own tcnn build. Needs the reference's headers: only where it exists."""
+    script = os.path.join(ROOT, "integration", "build.sh")
+    if os.path.exists(script):
+        _run(["bash", script])
+        if verbose:
+            print("[build] integration/_build is up to date")
+
+
 def build_all(verbose=False):
     build_cuda(verbose)
     build_oracle(verbose)
     build_ref(verbose)
     build_baseline(verbose)
     build_examples(verbose)
+    build_integration(verbose)
     stage_data(verbose)
 
 

@@ -22,7 +22,7 @@ public:
 	size_t n_params() const override { return m_cfg.n_params; }
 	void initialize_params(cudaStream_t stream, Pcg32& rng, float* params_fp32, float scale) override;
 	Json hyperparams() const override { return m_cfg.hyperparams(); }
-	std::string name() const override { return "GridEncoding"; }
+	std::string name() const override { return "Grid"; }   // GridEncodingTemplated::name (grid.h)
 
 	const GridConfig& config() const { return m_cfg; }
 	void set_max_level(float v) { m_max_level = v; }

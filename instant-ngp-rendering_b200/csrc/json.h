@@ -9,6 +9,8 @@
 
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <map>
 #include <memory>
 #include <sstream>
@@ -146,7 +148,17 @@ private:
 			case Type::Bool: o << (m_bool ? "true" : "false"); break;
 			case Type::Number:
 				if (std::floor(m_num) == m_num && std::fabs(m_num) < 1e15) o << (long long)m_num;
-				else { o.precision(9); o << m_num; }
+				else if (!std::isfinite(m_num)) o << "null";   // as nlohmann's dump does
+				else {
+					// the shortest text that reads back as the same double (what nlohmann's dump prints): 0.1 stays "0.1",
+					// a float widened to double keeps all its digits
+					char buf[40];
+					for (int digits = 15; digits <= 17; ++digits) {
+						snprintf(buf, sizeof(buf), "%.*g", digits, m_num);
+						if (strtod(buf, nullptr) == m_num) break;
+					}
+					o << buf;
+				}
 				break;
 			case Type::String: write_string(o, m_str); break;
 			case Type::Binary: { // nlohmann's text form of a binary

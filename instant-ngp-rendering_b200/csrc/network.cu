@@ -75,6 +75,8 @@ NetworkWithInputEncodingModule::NetworkWithInputEncodingModule(uint32_t n_input_
 	if (equals_case_insensitive(otype, "Identity")) {
 		m_has_grid = false;
 		enc_out = n_input_dims;
+		m_identity_scale = encoding.value("scale", 1.0f);
+		m_identity_offset = encoding.value("offset", 0.0f);
 	} else if (equals_case_insensitive(otype, "Grid") || equals_case_insensitive(otype, "HashGrid") ||
 		equals_case_insensitive(otype, "TiledGrid") || equals_case_insensitive(otype, "DenseGrid")) {
 		m_has_grid = true;
@@ -105,7 +107,16 @@ void NetworkWithInputEncodingModule::initialize_params(cudaStream_t stream, Pcg3
 Json NetworkWithInputEncodingModule::hyperparams() const {
 	Json j = Json::object();
 	j["otype"] = "NetworkWithInputEncoding";
-	j["encoding"] = m_has_grid ? m_grid.hyperparams() : m_encoding_json;
+	if (m_has_grid) {
+		j["encoding"] = m_grid.hyperparams();
+	} else {
+		// IdentityEncoding::hyperparams (tcnn encodings/identity.h:171-177)
+		Json id = Json::object();
+		id["otype"] = "Identity";
+		id["scale"] = m_identity_scale;
+		id["offset"] = m_identity_offset;
+		j["encoding"] = id;
+	}
 	Json net = Json::object();
 	net["otype"] = "FullyFusedMLP";
 	net["activation"] = m_mlp.relu ? "ReLU" : "None";
@@ -120,7 +131,7 @@ void NetworkWithInputEncodingModule::encode_tiled(cudaStream_t stream, uint32_t 
 	if (m_has_grid) {
 		grid_forward(stream, m_grid.p, n, params + m_mlp.n_params(), input, in_stride, feat, m_enc_width, 1.0f, true);
 	} else {
-		identity_encode_tiled(stream, n, input, in_stride, m_n_input_dims, 1.0f, 0.0f, feat, m_enc_width);
+		identity_encode_tiled(stream, n, input, in_stride, m_n_input_dims, m_identity_scale, m_identity_offset, feat, m_enc_width);
 	}
 }
 
@@ -180,12 +191,17 @@ std::unique_ptr<Context> NetworkWithInputEncodingModule::forward(cudaStream_t st
 	return std::make_unique<Context>();
 }
 
+__global__ void identity_input_gradient_kernel(uint32_t total, uint32_t n_dims, const __half* __restrict__ dfeat, uint32_t stride, float scale, float* __restrict__ dL_dinput) {
+	const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+	if (e >= total) return;
+	dL_dinput[e] = __half2float(dfeat[(size_t)(e / n_dims) * stride + e % n_dims]) * scale;
+}
+
 void NetworkWithInputEncodingModule::backward(cudaStream_t stream, const Context&, uint32_t n, float* dL_dinput, const __half* dL_doutput,
 	__half* dL_dparams, const float* input, const __half* /*output*/, const __half* params)
 {
 	check_batch(n);
 	if (n == 0) return;
-	if (dL_dinput && !m_has_grid) throw std::runtime_error{"ngp-b200: input gradients through an Identity-encoded network are not available"};
 	if (m_has_grid && !dL_dinput && fused_grid_train_enabled() && fused_grid_supported(m_net, m_grid.p)) {
 		const uint32_t ctas = fused_grid_train_ctas(m_net, n);
 		DeviceBuffer partials{(size_t)ctas * m_mlp.n_params() * sizeof(float), stream};
@@ -211,7 +227,7 @@ void NetworkWithInputEncodingModule::backward(cudaStream_t stream, const Context
 		if (tiles && ggrad) grid_backward(stream, m_grid.p, n, ggrad, input, m_n_input_dims, dfeat.as<__half>(), m_enc_width, 1.0f, true, m_ordered_batches);
 		return;
 	}
-	const bool need_dfeat = m_has_grid && (dL_dparams || dL_dinput);
+	const bool need_dfeat = (m_has_grid && dL_dparams) || dL_dinput;
 	DeviceBuffer feat{tiled_bytes(n, m_enc_width), stream};
 	DeviceBuffer dfeat{need_dfeat ? tiled_bytes(n, m_enc_width) : 0, stream};
 	const uint32_t grid = fused_train_grid(m_net, n);
@@ -233,8 +249,15 @@ void NetworkWithInputEncodingModule::backward(cudaStream_t stream, const Context
 	if (dL_dinput) {
 		DeviceBuffer aos{(size_t)n * m_enc_width * sizeof(__half), stream};
 		tiled_to_aos(stream, n, dfeat.as<__half>(), m_enc_width, aos.as<__half>(), m_enc_width);
-		grid_backward_input(stream, m_grid.p, n, params + m_mlp.n_params(), input, m_n_input_dims, aos.as<__half>(), m_enc_width,
-			dL_dinput, m_n_input_dims, 1.0f);
+		if (m_has_grid) {
+			grid_backward_input(stream, m_grid.p, n, params + m_mlp.n_params(), input, m_n_input_dims, aos.as<__half>(), m_enc_width,
+				dL_dinput, m_n_input_dims, 1.0f);
+		} else {
+			// Identity encoding: dL/dx = scale * dL/dfeature over the unpadded columns (identity_backward, tcnn encodings/identity.h:66-85)
+			const uint32_t total = n * m_n_input_dims;
+			identity_input_gradient_kernel<<<div_round_up(total, 256u), 256, 0, stream>>>(total, m_n_input_dims, aos.as<__half>(), m_enc_width, m_identity_scale, dL_dinput);
+			NGPB_CUDA_CHECK(cudaGetLastError());
+		}
 	}
 }
 

@@ -50,6 +50,7 @@ public:
 private:
 	uint32_t m_n_input_dims;
 	bool m_has_grid = false;
+	float m_identity_scale = 1.0f, m_identity_offset = 0.0f;   // IdentityEncoding (tcnn encodings/identity.h:60-63): y = x * scale + offset
 	bool m_ordered_batches = false;
 	GridConfig m_grid;
 	uint32_t m_enc_width = 0; // padded to 16
