@@ -157,6 +157,9 @@ def build_integration(verbose=False):
     script = os.path.join(ROOT, "integration", "build.sh")
     if os.path.exists(script):
         _run(["bash", script])
+    torch_binding = os.path.join(ROOT, "integration", "build_torch_binding.py")
+    if os.path.exists(torch_binding):
+        _run([sys.executable, torch_binding])   # the reference's bindings.cpp, unmodified, over the same shim
         if verbose:
             print("[build] integration/_build is up to date")
 

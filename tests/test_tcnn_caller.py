@@ -151,3 +151,38 @@ def test_same_caller_on_both_back_ends_live(tmp_path):
     _check_against(ours, lambda case, name: (ref[case, name]["sample"], slice(None)), stats)
     for case in CASES:
         assert _rel_l2(ours[case, "dL_dparams"]["sample"], ref[case, "dL_dparams"]["sample"]) <= 3e-2, case
+
+
+def test_reference_torch_binding_loads_without_a_device():
+    """tcnn/bindings/torch/tinycudann/bindings.cpp, compiled unmodified over the shim (integration/build_torch_binding.py): the
+    extension imports, builds modules from Python dicts and answers the facade's questions. (Running it needs a GPU:
+    tests/test_tinycudann_gpu.py.)"""
+    import glob
+    import sys
+    built = glob.glob(os.path.join(BUILD, "torch", "tinycudann_bindings", "_90_C*.so"))
+    if not built:
+        pytest.skip("the torch binding is not built (integration/build_torch_binding.py needs the reference's sources)")
+    code = (
+        "import sys, json, torch\n"
+        "sys.path.insert(0, %r)\n"
+        "import importlib\n"
+        "C = importlib.import_module('tinycudann_bindings._90_C')\n"
+        "grid = {'otype': 'HashGrid', 'n_levels': 16, 'n_features_per_level': 2, 'log2_hashmap_size': 19, 'base_resolution': 16, 'per_level_scale': 1.3819}\n"
+        "mlp = {'otype': 'FullyFusedMLP', 'activation': 'ReLU', 'output_activation': 'None', 'n_neurons': 64, 'n_hidden_layers': 2}\n"
+        "e = C.create_encoding(3, grid, C.Precision.Fp16)\n"
+        "n = C.create_network_with_input_encoding(3, 4, grid, mlp)\n"
+        "m = C.create_network(32, 16, mlp)\n"
+        "print(json.dumps({'enc': [e.n_params(), e.n_input_dims(), e.n_output_dims(), e.name(), e.hyperparams()],\n"
+        "                  'net': [n.n_params(), n.n_output_dims(), n.name()], 'mlp': [m.n_params(), m.n_output_dims()],\n"
+        "                  'lib': [C.batch_size_granularity(), C.default_loss_scale(C.Precision.Fp16), C.has_networks(), C.preferred_precision() == C.Precision.Fp16,\n"
+        "                          e.param_precision() == C.Precision.Fp16, e.output_precision() == C.Precision.Fp16]}))\n"
+    ) % os.path.join(BUILD, "torch")
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stderr[-2000:]
+    got = json.loads(res.stdout.strip().splitlines()[-1])
+    want = {d.get("case"): d for d in _golden()["describe"]}
+    enc = want["encoding_L16F2"]
+    assert got["enc"] == [enc["n_params"], 3, enc["n_output_dims"], enc["name"], enc["hyperparams"]]
+    assert got["net"] == [12196240 + 32 * 64 + 64 * 64 + 64 * 16, 16, "NetworkWithInputEncoding"]
+    assert got["mlp"] == [want["network_mlp_32_to_16"]["n_params"], 16]
+    assert got["lib"] == [256, 128.0, True, True, True, True]
