@@ -269,6 +269,8 @@ size_t ngpb_host_msgpack_reencode(const void* in, size_t n, void* out, size_t ca
  * sharpness culling, resolved image / alpha / mask paths, NGP camera matrices, lens, scale / offset / up / aabb_scale, flags.
  * Returns the size needed incl. NUL, 0 on failure. */
 size_t ngpb_host_describe_dataset(const char* path, char* buf, size_t cap);
+/* The frame order of the loader: SI::natural::compare of dependencies/NaturalSort as src/nerf_loader.cu:347-349 uses it. 1 when a sorts before b. */
+int ngpb_host_natural_less(const char* a, const char* b);
 int ngpb_host_decode_png(const char* path, void* rgba, size_t cap, int* width, int* height);
 /* The loader's host decoder for 8-bit files other than JPEG, chosen from the file's content as stb_image does
  * (load_stbi, src/common_host.cu:214-217): PNG, BMP, TGA, binary PNM -> RGBA8 rows top to bottom. */

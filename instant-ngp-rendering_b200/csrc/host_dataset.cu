@@ -21,28 +21,58 @@
 namespace ngpb {
 
 // SI::natural::compare: digit runs compare by value, the rest by character
+// SI::natural::compare (dependencies/NaturalSort/natural_sort.hpp:170-236), the order of the reference's frames
+// (src/nerf_loader.cu:347-349), restated with its quirks: characters compare case-folded as unsigned bytes; a digit run meets a
+// digit run by value (leading zeros skipped) unless it follows a '.', where runs compare as fractions; a fraction against an
+// integer run counts as "greater" and the reverse as "equal" (compare_number returns bool from an int function, :140-143);
+// repeated spaces collapse. Pinned to the reference's own header by tests/golden/ref_natural_sort.json.gz.
+static int natural_fold(char c) {
+	const unsigned char u = (unsigned char)c;
+	return u >= 'A' && u <= 'Z' ? u + 32 : u;
+}
+static bool natural_digit(char c) { return c >= '0' && c <= '9'; }
+static int natural_number(const std::string& a, size_t l, size_t le, bool fa, const std::string& b, size_t r, size_t re, bool fb) {
+	if (fa && !fb) return 1;
+	if (!fa && fb) return 0;
+	if (fa) {
+		for (; l < le && r < re; ++l, ++r) if (a[l] != b[r]) return a[l] < b[r] ? -1 : 1;
+		while (l < le && a[l] == '0') ++l;
+		while (r < re && b[r] == '0') ++r;
+		if (l == le && r != re) return -1;
+		if (l != le && r == re) return 1;
+		return 0;
+	}
+	while (l < le && a[l] == '0') ++l;
+	while (r < re && b[r] == '0') ++r;
+	if (le - l != re - r) return le - l < re - r ? -1 : 1;
+	for (; l < le; ++l, ++r) if (a[l] != b[r]) return a[l] < b[r] ? -1 : 1;
+	return 0;
+}
 static bool natural_less(const std::string& a, const std::string& b) {
+	const size_t na = a.size(), nb = b.size();
+	auto at = [](const std::string& s, size_t i) { return i < s.size() ? s[i] : '\0'; };
 	size_t i = 0, j = 0;
-	while (i < a.size() && j < b.size()) {
-		const bool da = isdigit((unsigned char)a[i]) != 0, db = isdigit((unsigned char)b[j]) != 0;
-		if (da && db) {
-			size_t i1 = i, j1 = j;
-			while (i1 < a.size() && isdigit((unsigned char)a[i1])) ++i1;
-			while (j1 < b.size() && isdigit((unsigned char)b[j1])) ++j1;
-			std::string na = a.substr(i, i1 - i), nb = b.substr(j, j1 - j);
-			na.erase(0, std::min(na.find_first_not_of('0'), na.size() - 1));
-			nb.erase(0, std::min(nb.find_first_not_of('0'), nb.size() - 1));
-			if (na.size() != nb.size()) return na.size() < nb.size();
-			if (na != nb) return na < nb;
-			i = i1; j = j1;
-		} else if (da != db) {
-			return da;   // digit runs order before text (the key (0, n) < (1, s) of the Python mirror)
-		} else {
-			if (a[i] != b[j]) return a[i] < b[j];
+	bool space_a = false, space_b = false;
+	while (i < na && j < nb) {
+		while (space_a && i < na && a[i] == ' ') ++i;
+		space_a = at(a, i) == ' ';
+		while (space_b && j < nb && b[j] == ' ') ++j;
+		space_b = at(b, j) == ' ';
+		const char ca = at(a, i), cb = at(b, j);
+		if (!natural_digit(ca) || !natural_digit(cb)) {
+			if (natural_fold(ca) != natural_fold(cb)) return natural_fold(ca) < natural_fold(cb);
 			++i; ++j;
+		} else {
+			size_t ei = i, ej = j;
+			while (ei < na && natural_digit(a[ei])) ++ei;
+			while (ej < nb && natural_digit(b[ej])) ++ej;
+			const int order = natural_number(a, i, ei, i > 0 && a[i - 1] == '.', b, j, ej, j > 0 && b[j - 1] == '.');
+			if (order != 0) return order < 0;
+			i = ei; j = ej;
 		}
 	}
-	return a.size() - i < b.size() - j;
+	if (i >= na && j >= nb) return false;
+	return i >= na;
 }
 
 static float fov_to_focal_length(int resolution, float degrees) {   // common_host.h
@@ -458,6 +488,10 @@ void Testbed::load_training_data(const std::string& path, uint32_t max_images) {
 
 // ---- host-only view of the loader's decisions (no device, no pixels): what the CPU tests compare with loader.py ----------
 #include "../../include/ngp_b200.h"
+
+extern "C" int ngpb_host_natural_less(const char* a, const char* b) {
+	return a && b && ngpb::natural_less(a, b) ? 1 : 0;
+}
 
 extern "C" size_t ngpb_host_describe_dataset(const char* path, char* buf, size_t cap) {
 	using namespace ngpb;

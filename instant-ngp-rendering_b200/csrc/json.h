@@ -188,7 +188,11 @@ private:
 				case '\n': o << "\\n"; break;
 				case '\t': o << "\\t"; break;
 				case '\r': o << "\\r"; break;
-				default: o << c;
+				case '\b': o << "\\b"; break;
+				case '\f': o << "\\f"; break;
+				default:
+					if ((unsigned char)c < 0x20) { char esc[8]; snprintf(esc, sizeof(esc), "\\u%04x", (unsigned)(unsigned char)c); o << esc; }
+					else o << c;
 			}
 		}
 		o << '"';
@@ -212,11 +216,18 @@ private:
 				} else break;
 			}
 		}
+		// containers recurse: a file of 100 000 opening brackets must end in an error, not in a stack overflow
+		int depth = 0;
+		struct Nesting {
+			Parser& p;
+			explicit Nesting(Parser& parser) : p(parser) { if (++p.depth > 512) p.fail("nesting deeper than 512 levels"); }
+			~Nesting() { --p.depth; }
+		};
 		Json parse_value() {
 			if (pos >= s.size()) fail("unexpected end");
 			char c = s[pos];
-			if (c == '{') return parse_object();
-			if (c == '[') return parse_array();
+			if (c == '{') { Nesting n{*this}; return parse_object(); }
+			if (c == '[') { Nesting n{*this}; return parse_array(); }
 			if (c == '"') return Json{parse_string()};
 			if (s.compare(pos, 4, "true") == 0) { pos += 4; return Json{true}; }
 			if (s.compare(pos, 5, "false") == 0) { pos += 5; return Json{false}; }
@@ -228,11 +239,23 @@ private:
 			while (pos < s.size() && (isdigit((unsigned char)s[pos]) || s[pos] == '-' || s[pos] == '+' || s[pos] == '.' || s[pos] == 'e' || s[pos] == 'E')) ++pos;
 			if (start == pos) fail("unexpected character");
 			const std::string lit = s.substr(start, pos - start);
-			try {
-				Json v{std::stod(lit)};
-				v.m_is_int = lit.find_first_of(".eE") == std::string::npos;
-				return v;
-			} catch (...) { fail("bad number"); }
+			char* end = nullptr;
+			const double d = strtod(lit.c_str(), &end);   // subnormals read as they are; nlohmann accepts them too
+			if (end != lit.c_str() + lit.size()) fail("bad number");
+			if (!std::isfinite(d)) fail("number out of range");
+			Json v{d};
+			v.m_is_int = lit.find_first_of(".eE") == std::string::npos;
+			return v;
+		}
+		unsigned parse_hex4() {
+			if (pos + 4 >= s.size()) fail("bad \\u escape");
+			unsigned cp = 0;
+			for (int k = 1; k <= 4; ++k) {
+				const char c = s[pos + k];
+				cp = cp * 16 + (c >= '0' && c <= '9' ? c - '0' : c >= 'a' && c <= 'f' ? c - 'a' + 10 : c >= 'A' && c <= 'F' ? c - 'A' + 10 : (fail("bad \\u escape"), 0));
+			}
+			pos += 4;
+			return cp;
 		}
 		std::string parse_string() {
 			++pos; // opening quote
@@ -247,11 +270,19 @@ private:
 						case 'r': out += '\r'; break;
 						case 'b': out += '\b'; break;
 						case 'f': out += '\f'; break;
-						case 'u': { // keep BMP code points < 0x80 only; others become '?'
-							if (pos + 4 >= s.size()) fail("bad \\u escape");
-							unsigned cp = (unsigned)std::stoul(s.substr(pos + 1, 4), nullptr, 16);
-							out += cp < 0x80 ? (char)cp : '?';
-							pos += 4;
+						case 'u': { // \uXXXX, surrogate pairs included, stored as UTF-8 (file names written by json.dumps arrive this way)
+							unsigned cp = parse_hex4();
+							if (cp >= 0xD800 && cp < 0xDC00 && pos + 2 < s.size() && s[pos + 1] == '\\' && s[pos + 2] == 'u') {
+								pos += 2;
+								const unsigned lo = parse_hex4();
+								if (lo < 0xDC00 || lo > 0xDFFF) fail("bad surrogate pair");
+								cp = 0x10000 + ((cp - 0xD800) << 10) + (lo - 0xDC00);
+							}
+							if (cp >= 0xD800 && cp <= 0xDFFF) fail("bad surrogate pair");
+							if (cp < 0x80) out += (char)cp;
+							else if (cp < 0x800) { out += (char)(0xC0 | (cp >> 6)); out += (char)(0x80 | (cp & 0x3F)); }
+							else if (cp < 0x10000) { out += (char)(0xE0 | (cp >> 12)); out += (char)(0x80 | ((cp >> 6) & 0x3F)); out += (char)(0x80 | (cp & 0x3F)); }
+							else { out += (char)(0xF0 | (cp >> 18)); out += (char)(0x80 | ((cp >> 12) & 0x3F)); out += (char)(0x80 | ((cp >> 6) & 0x3F)); out += (char)(0x80 | (cp & 0x3F)); }
 						} break;
 						default: out += s[pos];
 					}

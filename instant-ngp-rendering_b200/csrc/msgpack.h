@@ -99,6 +99,11 @@ public:
 	MsgpackReader(const uint8_t* data, size_t size) : m_p(data), m_end(data + size) {}
 
 	Json read() {
+		struct Nesting {   // arrays and maps recurse: bound the depth as the JSON parser does
+			int& d;
+			explicit Nesting(int& depth) : d(depth) { if (++d > 512) throw std::runtime_error{"msgpack: nesting deeper than 512 levels"}; }
+			~Nesting() { --d; }
+		} nesting{m_depth};
 		const uint8_t t = byte();
 		if (t <= 0x7f) return Json{(uint32_t)t};
 		if (t >= 0xe0) return Json{(int)(int8_t)t};
@@ -173,6 +178,7 @@ private:
 	}
 	const uint8_t* m_p;
 	const uint8_t* m_end;
+	int m_depth = 0;
 };
 
 inline std::vector<uint8_t> to_msgpack(const Json& j) {

@@ -6,6 +6,7 @@ nerf_matrix_to_ngp nerf_loader.h:101-120, the byte-image fix-ups of convert_rgba
 lens models the NeRF path implements (Perspective and OpenCV). Image files are decoded with OpenCV
 (the reference uses stb_image); everything numeric is the reference's arithmetic in float32.
 """
+import functools
 import json
 import os
 import re
@@ -17,9 +18,82 @@ SUPPORTED_IMAGE_FORMATS = ("png", "jpg", "jpeg", "bmp", "gif", "tga", "pic", "pn
 MASK_COLOR = 0x00FF00FF  # "hot pink", alpha 0: pixels the trainer skips (nerf_loader.cu:610)
 
 
-def _natural_key(s):
-    """SI::natural::compare: digit runs compare by value, the rest by character."""
-    return [(0, int(t)) if t.isdigit() else (1, t) for t in re.split(r"(\d+)", s) if t != ""]
+def _natural_number(a, l, le, fa, b, r, re_, fb):
+    """compare_number (natural_sort.hpp:85-150), its bool-from-int returns included."""
+    if fa and not fb:
+        return 1
+    if not fa and fb:
+        return 0
+    if fa:
+        while l < le and r < re_:
+            if a[l] != b[r]:
+                return -1 if a[l] < b[r] else 1
+            l, r = l + 1, r + 1
+        while l < le and a[l] == 0x30:
+            l += 1
+        while r < re_ and b[r] == 0x30:
+            r += 1
+        return -1 if (l == le and r != re_) else 1 if (l != le and r == re_) else 0
+    while l < le and a[l] == 0x30:
+        l += 1
+    while r < re_ and b[r] == 0x30:
+        r += 1
+    if le - l != re_ - r:
+        return -1 if le - l < re_ - r else 1
+    while l < le:
+        if a[l] != b[r]:
+            return -1 if a[l] < b[r] else 1
+        l, r = l + 1, r + 1
+    return 0
+
+
+def natural_less(sa, sb):
+    """SI::natural::compare (dependencies/NaturalSort/natural_sort.hpp:170-236), the order of the reference's frames
+    (nerf_loader.cu:347-349), on the UTF-8 bytes: case-folded unsigned byte order, digit runs by value, runs after a '.' as
+    fractions, repeated spaces collapsed - quirks included (csrc/host_dataset.cu natural_less is the same restatement; both are
+    pinned to the reference's header by tests/golden/ref_natural_sort.json.gz)."""
+    a, b = sa.encode("utf-8"), sb.encode("utf-8")
+    na, nb = len(a), len(b)
+
+    def at(s, i):
+        return s[i] if i < len(s) else 0
+
+    def fold(c):
+        return c + 32 if 0x41 <= c <= 0x5A else c
+
+    def digit(c):
+        return 0x30 <= c <= 0x39
+    i = j = 0
+    space_a = space_b = False
+    while i < na and j < nb:
+        while space_a and i < na and a[i] == 0x20:
+            i += 1
+        space_a = at(a, i) == 0x20
+        while space_b and j < nb and b[j] == 0x20:
+            j += 1
+        space_b = at(b, j) == 0x20
+        ca, cb = at(a, i), at(b, j)
+        if not digit(ca) or not digit(cb):
+            if fold(ca) != fold(cb):
+                return fold(ca) < fold(cb)
+            i, j = i + 1, j + 1
+        else:
+            ei, ej = i, j
+            while ei < na and digit(a[ei]):
+                ei += 1
+            while ej < nb and digit(b[ej]):
+                ej += 1
+            order = _natural_number(a, i, ei, i > 0 and a[i - 1] == 0x2E, b, j, ej, j > 0 and b[j - 1] == 0x2E)
+            if order != 0:
+                return order < 0
+            i, j = ei, ej
+    if i >= na and j >= nb:
+        return False
+    return i >= na
+
+
+def _natural_cmp(x, y):
+    return -1 if natural_less(x, y) else 1 if natural_less(y, x) else 0
 
 
 def _strip_json_comments(text):
@@ -124,7 +198,7 @@ def describe_dataset(path_or_paths):
         if not isinstance(j.get("frames"), list):
             continue
         base = os.path.dirname(jp)
-        frames = sorted(j["frames"], key=lambda f: _natural_key(f["file_path"]))
+        frames = sorted(j["frames"], key=functools.cmp_to_key(lambda f, g: _natural_cmp(f["file_path"], g["file_path"])))
         for f in frames:
             f["file_path"] = f["file_path"].replace("\\", "/")
         if "n_frames" in j:

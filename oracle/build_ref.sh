@@ -13,5 +13,5 @@ nvcc -std=c++17 --extended-lambda --expt-relaxed-constexpr -O1 -w -shared -Xcomp
 	-DTCNN_MIN_GPU_ARCH=100 -DFMT_HEADER_ONLY -gencode arch=compute_100a,code=sm_100a \
 	"$HERE/ref_host.cu" -o "$HERE/_ref/libref_host.so"
 echo "[build_ref] built $HERE/_ref/libref_host.so"
-g++ -std=c++17 -O1 -w -shared -fPIC -I"$T/dependencies" "$HERE/ref_json.cc" -o "$HERE/_ref/libref_json.so"
+g++ -std=c++17 -O1 -w -shared -fPIC -I"$T/dependencies" -I"$R/dependencies/NaturalSort" "$HERE/ref_json.cc" -o "$HERE/_ref/libref_json.so"
 echo "[build_ref] built $HERE/_ref/libref_json.so"

@@ -51,3 +51,10 @@ extern "C" size_t ref_msgpack_roundtrip(const uint8_t* in, size_t n, uint8_t* ou
 	if (out && cap >= bytes.size()) memcpy(out, bytes.data(), bytes.size());
 	return bytes.size();
 }
+
+// The frame order of the reference's loader (src/nerf_loader.cu:347-349): SI::natural::compare from the vendored
+// dependencies/NaturalSort, as it is. 1 when a sorts before b.
+#include <natural_sort.hpp>
+extern "C" int ref_natural_less(const char* a, const char* b) {
+	return SI::natural::compare<std::string>(std::string{a}, std::string{b}) ? 1 : 0;
+}

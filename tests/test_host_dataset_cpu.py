@@ -126,3 +126,48 @@ def test_describe_reports_the_reference_errors(ngp, tmp_path):
     (tmp_path / "fisheye.json").write_text(json.dumps({"is_fisheye": True, "frames": [{"file_path": "nope.png", "transform_matrix": np.eye(4).tolist()}]}))
     assert lib.ngpb_host_describe_dataset(str(tmp_path / "fisheye.json").encode(), None, 0) == 0
     assert "Perspective or OpenCV" in lib.ngpb_last_error().decode()
+
+
+def test_describe_resolves_non_ascii_file_names(ngp, loader, tmp_path):
+    """transforms.json written by json.dumps escapes non-ASCII names (\\u00e9, surrogate pairs): the C++ parser turns them into the
+    UTF-8 bytes the files carry on disk, so the frames are found - by both loaders, at the same paths."""
+    rng = np.random.default_rng(12)
+    names = ["vues/été_01", "vues/写真_02", "vues/view_\U0001F600_03"]
+    for n in names:
+        _touch(str(tmp_path / (n + ".png")))
+    meta = {"camera_angle_x": 0.7, "w": 64, "h": 48, "frames": [{"file_path": n, "transform_matrix": _pose(rng)} for n in names]}
+    path = tmp_path / "transforms.json"
+    text = json.dumps(meta)
+    assert "\\u00e9" in text and "\\ud83d\\ude00" in text
+    path.write_text(text)
+    got, want = _describe(ngp._lib.lib, path), loader.describe_dataset(str(path))
+    assert got["n_images"] == 3
+    _compare(got, want, loader, 64, 48)
+    assert all(os.path.exists(f["path"]) for f in got["frames"])
+
+
+def test_frame_order_is_the_references_natural_compare(ngp, loader):
+    """tests/golden/ref_natural_sort.json.gz: SI::natural::compare of the reference's vendored NaturalSort header on 9 591 pairs of
+    names (digit runs, fractions after a dot, leading zeros, repeated spaces, case, non-ASCII bytes, its bool-from-int quirks).
+    The C++ loader's order and loader.py's must answer every pair the same way; the live header is asked too where it is built."""
+    import gzip
+    with gzip.open(os.path.join(ROOT, "tests", "golden", "ref_natural_sort.json.gz"), "rb") as f:
+        pairs = json.loads(f.read().decode())["pairs"]
+    assert len(pairs) > 9000 and 0.3 < sum(p[2] for p in pairs) / len(pairs) < 0.7
+    lib = ngp._lib.lib
+    for a, b, want in pairs:
+        assert lib.ngpb_host_natural_less(a.encode(), b.encode()) == want, (a, b, want)
+        assert int(loader.natural_less(a, b)) == want, (a, b, want)
+    ref_path = os.path.join(ROOT, "oracle", "_ref", "libref_json.so")
+    if os.path.exists(ref_path):
+        ref = ctypes.CDLL(ref_path)
+        if hasattr(ref, "ref_natural_less"):
+            ref.ref_natural_less.argtypes = [ctypes.c_char_p, ctypes.c_char_p]
+            rng = np.random.default_rng(3)
+            alphabet = list("aAzZ0159 ._-/") + ["é"]
+            for _ in range(3000):
+                a = "".join(rng.choice(alphabet, size=rng.integers(1, 8)))
+                b = "".join(rng.choice(alphabet, size=rng.integers(1, 8)))
+                if a.rstrip(" ") != a and b.rstrip(" ") != b:
+                    continue   # the reference reads past both ends there (see make_ref_natural_sort.py)
+                assert lib.ngpb_host_natural_less(a.encode(), b.encode()) == ref.ref_natural_less(a.encode(), b.encode()), (a, b)

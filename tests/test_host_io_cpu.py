@@ -472,3 +472,33 @@ def test_bmp_bit_fields_and_alpha_rules(ngp, tmp_path):
     (tmp_path / "noise.bin").write_bytes(bytes(rng.integers(128, 256, 64, dtype=np.uint8)))
     assert lib.ngpb_host_decode_image(str(tmp_path / "noise.bin").encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0
     assert "unknown image type" in lib.ngpb_last_error().decode()
+
+
+def test_parsers_refuse_pathological_nesting(ngp, tmp_path):
+    """A config or snapshot made of 100 000 opening brackets ends in an error message, not in a stack overflow; ordinary depth passes."""
+    lib = ngp._lib.lib
+    (tmp_path / "deep.json").write_text("[" * 100000)
+    assert lib.ngpb_host_load_network_config(str(tmp_path / "deep.json").encode(), None, 0) == 0
+    assert "nesting" in lib.ngpb_last_error().decode()
+    blob = bytes([0x91]) * 100000
+    assert lib.ngpb_host_msgpack_reencode(blob, len(blob), None, 0) == 0
+    assert "nesting" in lib.ngpb_last_error().decode()
+    ok = {"a": 1}
+    for _ in range(100):
+        ok = {"n": [ok]}
+    (tmp_path / "ok.json").write_text(json.dumps(ok))
+    assert lib.ngpb_host_load_network_config(str(tmp_path / "ok.json").encode(), None, 0) > 0
+
+
+def test_json_text_keeps_every_digit_of_a_double(ngp, tmp_path):
+    """Json::dump prints the shortest text that reads back as the same double (nlohmann's rule): a learning rate keeps its digits,
+    0.1 stays 0.1, a float widened to double shows as what it is, non-finite values become null."""
+    lib = ngp._lib.lib
+    vals = {"lr": 0.0012345678901234567, "tenth": 0.1, "third": 1.0 / 3.0, "widened": float(np.float32(1.3819)), "big": 1.5e300, "tiny": 4.9e-324, "int": 7, "neg": -2.5}
+    (tmp_path / "v.json").write_text(json.dumps(vals))
+    n = lib.ngpb_host_load_network_config(str(tmp_path / "v.json").encode(), None, 0)
+    buf = ctypes.create_string_buffer(n)
+    lib.ngpb_host_load_network_config(str(tmp_path / "v.json").encode(), buf, n)
+    text = buf.value.decode()
+    assert json.loads(text) == vals
+    assert '"tenth":0.1,' in text and '"widened":1.3818999528884888' in text and '"int":7' in text
