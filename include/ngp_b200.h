@@ -277,6 +277,9 @@ int ngpb_host_decode_png(const char* path, void* rgba, size_t cap, int* width, i
 int ngpb_host_decode_image(const char* path, void* rgba, size_t cap, int* width, int* height);
 /* The loader's OpenEXR reader (single-part scanline, HALF / FLOAT, NONE / RLE / ZIPS / ZIP / PIZ): float RGBA rows top to bottom. */
 int ngpb_host_decode_exr(const char* path, float* rgba, size_t cap_floats, int* width, int* height);
+/* The same reader with the channel rule of NeRF frames (load_exr_to_gpu, src/tinyexr_wrapper.cu:153-258): R / G / B / A by name,
+ * absent colours 0, absent alpha 1; ngpb_host_decode_exr follows the image mode's LoadEXR (a one-channel file fills all four). */
+int ngpb_host_decode_exr_frame(const char* path, float* rgba, size_t cap_floats, int* width, int* height);
 /* Testbed::train(batch_size), src/testbed.cu:4020-4109. Returns once the step's counters (loss,
  * measured batch sizes) are on the host; the backward pass and the optimizer may still be running on
  * the testbed's stream - later calls on this testbed are ordered behind them. */

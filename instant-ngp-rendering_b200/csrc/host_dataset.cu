@@ -393,7 +393,7 @@ __global__ void rgba8_to_linear_premultiplied_kernel(uint32_t n, const uint32_t*
 void Testbed::load_image_file(const std::string& path) {
 	const std::string ext = path_extension(path);
 	if (ext == "exr") {
-		const HostImageF img = decode_exr(read_file(path), path);
+		const HostImageF img = decode_exr(read_file(path), path, ExrChannelRule::Image);
 		set_image(img.rgba.data(), kImageFloat, img.width, img.height);
 		return;
 	}
@@ -434,7 +434,7 @@ void Testbed::load_training_data(const std::string& path, uint32_t max_images) {
 		int w = 0, h = 0;
 		if (path_extension(fr.path) == "exr") {
 			// load_exr_to_gpu (src/tinyexr_wrapper.cu): linear RGBA halves; fix_premult turns straight colours into premultiplied ones
-			const HostImageF img = decode_exr(read_file(fr.path), fr.path);
+			const HostImageF img = decode_exr(read_file(fr.path), fr.path, ExrChannelRule::Dataset);
 			w = img.width; h = img.height;
 			std::vector<__half> texels((size_t)w * h * 4);
 			for (size_t p = 0; p < (size_t)w * h; ++p) {

@@ -1,8 +1,8 @@
 // OpenEXR reader for the loader (the reference reads EXR through tinyexr, src/tinyexr_wrapper.cu, which is not part of
 // this image): single-part scanline files, HALF and FLOAT channels, compression NONE / RLE / ZIPS / ZIP / PIZ - the set
 // tinyexr decodes (data/image/albert.exr is FLOAT RGBA, ZIP; PIZ is what most DCC tools write by default). PXR24 / B44 /
-// DWA, tiled and multi-part files are refused with a message. Output: float RGBA, rows top to bottom (a missing alpha is
-// 1, a single luminance channel Y is replicated). Host only; zlib does the inflate; the PIZ stages (Huffman, 2-D Haar
+// DWA, tiled and multi-part files are refused with a message. Output: float RGBA, rows top to bottom; which channels land
+// where follows the reference's two readers (ExrChannelRule in host_io.h). Host only; zlib does the inflate; the PIZ stages (Huffman, 2-D Haar
 // wavelet, value LUT) follow the OpenEXR file-format description.
 #include "host_io.h"
 
@@ -312,7 +312,7 @@ bool piz_uncompress(const uint8_t* src, size_t n_src, const std::vector<ExrChann
 }
 } // namespace
 
-HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name) {
+HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name, ExrChannelRule rule) {
 	auto fail = [&](const std::string& why) -> void { throw std::runtime_error{"Could not load image file '" + name + "': " + why}; };
 	if (file.size() < 8 || rd<uint32_t>(file.data()) != 20000630u) fail("not an OpenEXR file");
 	const uint32_t version = rd<uint32_t>(file.data() + 4);
@@ -379,8 +379,24 @@ HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name)
 		else if (n == "A") { target[c] = 3; has_alpha = true; }
 	}
 	int grey = -1;
-	if (!has_rgb) for (size_t c = 0; c < channels.size(); ++c) if (channels[c].name == "Y") grey = (int)c;
-	if (!has_rgb && grey < 0) fail("no R, G, B or Y channel");
+	if (rule == ExrChannelRule::Image) {
+		// LoadEXR (tinyexr.h): a one-channel file of any name fills all four outputs with it; otherwise R, G and B must exist
+		if (channels.size() == 1) {
+			grey = 0;
+			target[0] = -1;
+			has_alpha = true;
+		} else {
+			for (int k = 0; k < 3; ++k) {
+				bool found = false;
+				for (size_t c = 0; c < channels.size(); ++c) found = found || target[c] == k;
+				if (!found) fail(std::string{"RGB"[k]} + " channel not found");
+			}
+		}
+	} else {
+		// load_exr_to_gpu (src/tinyexr_wrapper.cu:192-244): channels by name, absent ones stay 0, one pixel type for all
+		for (const ExrChannel& ch : channels) if (ch.pixel_type != channels[0].pixel_type) fail("Can't handle EXR images with mixed channel types");
+	}
+	(void)has_rgb;
 
 	const int n_blocks = (h + lines_per_block - 1) / lines_per_block;
 	if (pos + (size_t)n_blocks * 8 > file.size()) fail("truncated offset table");
@@ -423,7 +439,7 @@ HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name)
 				if (t >= 0) {
 					for (int x = 0; x < w; ++x) {
 						const float v = is_half ? __half2float(rd<__half>(p + (size_t)x * 2)) : rd<float>(p + (size_t)x * 4);
-						if (t == 4) { out[x * 4] = out[x * 4 + 1] = out[x * 4 + 2] = v; }
+						if (t == 4) { out[x * 4] = out[x * 4 + 1] = out[x * 4 + 2] = out[x * 4 + 3] = v; }
 						else out[x * 4 + t] = v;
 					}
 				}

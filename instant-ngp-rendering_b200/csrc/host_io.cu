@@ -211,7 +211,17 @@ extern "C" int ngpb_host_decode_image(const char* path, void* rgba, size_t cap, 
 extern "C" int ngpb_host_decode_exr(const char* path, float* rgba, size_t cap_floats, int* width, int* height) {
 	try {
 		if (!path || !width || !height) throw std::runtime_error{"ngpb_host_decode_exr: null argument"};
-		const ngpb::HostImageF img = ngpb::decode_exr(ngpb::read_file(path), path);
+		const ngpb::HostImageF img = ngpb::decode_exr(ngpb::read_file(path), path, ngpb::ExrChannelRule::Image);
+		*width = img.width; *height = img.height;
+		if (rgba && cap_floats >= img.rgba.size()) memcpy(rgba, img.rgba.data(), img.rgba.size() * sizeof(float));
+		return NGPB_OK;
+	} catch (const std::exception& e) { ngpb::set_last_error(e.what()); return NGPB_ERROR; }
+}
+
+extern "C" int ngpb_host_decode_exr_frame(const char* path, float* rgba, size_t cap_floats, int* width, int* height) {
+	try {
+		if (!path || !width || !height) throw std::runtime_error{"ngpb_host_decode_exr_frame: null argument"};
+		const ngpb::HostImageF img = ngpb::decode_exr(ngpb::read_file(path), path, ngpb::ExrChannelRule::Dataset);
 		*width = img.width; *height = img.height;
 		if (rgba && cap_floats >= img.rgba.size()) memcpy(rgba, img.rgba.data(), img.rgba.size() * sizeof(float));
 		return NGPB_OK;

@@ -32,7 +32,13 @@ struct HostImageF {
 	std::vector<float> rgba;
 };
 // OpenEXR, single-part scanline, HALF / FLOAT channels, compression NONE / RLE / ZIPS / ZIP / PIZ (host_exr.cu).
-HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name_for_errors);
+// The reference reads EXR files through two doors with different channel rules:
+//   Image    tinyexr's LoadEXR behind load_exr (image mode, src/tinyexr_wrapper.cu:125-151): a one-channel file fills R, G, B and A
+//            with that channel; otherwise R, G, B must exist ("R channel not found") and a missing A is 1
+//   Dataset  load_exr_to_gpu (NeRF frames, :153-258): R / G / B / A by name, absent colour channels are 0, absent A is 1,
+//            mixed HALF / FLOAT channels are refused
+enum class ExrChannelRule { Image, Dataset };
+HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name_for_errors, ExrChannelRule rule);
 
 // PNG (8 / 16 bit, grey / grey-alpha / RGB / RGBA / palette, non-interlaced) decoded on the host with zlib.
 HostImage decode_png(const std::vector<uint8_t>& file, const std::string& name_for_errors);

@@ -15,3 +15,5 @@ nvcc -std=c++17 --extended-lambda --expt-relaxed-constexpr -O1 -w -shared -Xcomp
 echo "[build_ref] built $HERE/_ref/libref_host.so"
 g++ -std=c++17 -O1 -w -shared -fPIC -I"$T/dependencies" -I"$R/dependencies/NaturalSort" "$HERE/ref_json.cc" -o "$HERE/_ref/libref_json.so"
 echo "[build_ref] built $HERE/_ref/libref_json.so"
+g++ -std=c++17 -O1 -w -shared -fPIC -I"$R/dependencies/stb_image" -I"$R/dependencies/tinyexr" "$HERE/ref_images.cc" -o "$HERE/_ref/libref_images.so"
+echo "[build_ref] built $HERE/_ref/libref_images.so"

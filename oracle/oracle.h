@@ -19,7 +19,9 @@
  * Adam within the tolerances stated there - the reference accumulates in fp16 and sums atomics in arbitrary order).
  * The container formats (msgpack, merge_patch) are pinned to the reference's own JSON library
  * (oracle/ref_json.cc, tests/golden/ref_json_vectors.json.gz), snapshots and loader metadata to a snapshot the
- * reference wrote (tests/golden/ref_fox_step5000.snapshot.json).
+ * reference wrote (tests/golden/ref_fox_step5000.snapshot.json), the loader's frame order to the reference's vendored
+ * NaturalSort header (tests/golden/ref_natural_sort.json.gz), and the host image decoders to the reference's vendored
+ * stb_image and tinyexr compiled as they are (oracle/ref_images.cc, tests/test_host_io_cpu.py).
  * One stated departure: the training march places samples on the stepping-space lattice with fixed-polynomial
  * log / exp; against the reference's functions its per-ray counts agree on 99.6 - 99.8 % of rays.
  * What still rests on the restatement alone: the loss kernel's glue and the occupancy update as whole kernels

@@ -201,7 +201,7 @@ def _cv2_exr(path):
         pytest.skip("this OpenCV build cannot read EXR")
     img = img.astype(np.float32)
     if img.ndim == 2:
-        img = np.stack([img] * 3, -1)
+        img = np.stack([img] * 4, -1)   # the reference's reader (tinyexr LoadEXR) spreads a one-channel file over R, G, B and A
     a = img[:, :, 3:4] if img.shape[2] == 4 else np.ones(img.shape[:2] + (1,), dtype=np.float32)
     return np.concatenate([img[:, :, 2::-1], a], axis=-1)
 
@@ -262,7 +262,12 @@ def test_exr_decoder_on_hand_written_files(ngp, tmp_path, kind):
     want = np.zeros((h, w, 4), dtype=np.float32)
     want[..., 3] = data["A"].astype(np.float32) if "A" in data else 1.0
     if "Y" in data:
-        want[..., :3] = data["Y"].astype(np.float32)[..., None]
+        want[...] = data["Y"].astype(np.float32)[..., None]   # image mode: LoadEXR fills all four with a lone channel
+        # the NeRF-frame rule (load_exr_to_gpu) takes channels by name only: nothing named R / G / B / A -> colour 0, alpha 1
+        frame = np.zeros_like(want)
+        cw, ch = ctypes.c_int(), ctypes.c_int()
+        assert ngp._lib.lib.ngpb_host_decode_exr_frame(str(path).encode(), frame.ctypes.data_as(ctypes.c_void_p), frame.size, ctypes.byref(cw), ctypes.byref(ch)) == 0
+        assert not frame[..., :3].any() and (frame[..., 3] == 1.0).all()
     else:
         for k, n in enumerate("RGB"):
             want[..., k] = data[n].astype(np.float32)
@@ -287,7 +292,7 @@ def test_exr_decoder_on_openexr_written_fixtures(ngp):
     for name, want in files.items():
         got = _decode_exr(ngp._lib.lib, os.path.join(here, name + ".exr"))
         assert got.shape == (want["height"], want["width"], 4), name
-        assert hashlib.sha256(got.tobytes()).hexdigest() == want["sha256"], name
+        assert hashlib.sha256(got.tobytes()).hexdigest() == want["sha256"] == want["sha256_tinyexr"], name   # OpenEXR's reader and the reference's tinyexr
 
 
 @pytest.mark.parametrize("compression", ["NO", "RLE", "ZIPS", "ZIP", "PIZ"])
@@ -502,3 +507,97 @@ def test_json_text_keeps_every_digit_of_a_double(ngp, tmp_path):
     text = buf.value.decode()
     assert json.loads(text) == vals
     assert '"tenth":0.1,' in text and '"widened":1.3818999528884888' in text and '"int":7' in text
+
+
+def _ref_images():
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libref_images.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libref_images.so (the reference's stb_image and tinyexr, oracle/build_ref.sh) is not built")
+    return ctypes.CDLL(path)
+
+
+def _ref_stbi(ref, path):
+    w, h, c, why = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.create_string_buffer(200)
+    if ref.ref_stbi_load(str(path).encode(), ctypes.byref(w), ctypes.byref(h), ctypes.byref(c), None, ctypes.c_size_t(0), why, ctypes.c_size_t(200)):
+        return why.value.decode()
+    out = np.zeros((h.value, w.value, 4), np.uint8)
+    ref.ref_stbi_load(str(path).encode(), ctypes.byref(w), ctypes.byref(h), ctypes.byref(c), out.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(out.size), why, ctypes.c_size_t(200))
+    return out
+
+
+def _ref_tinyexr(ref, path):
+    w, h, why = ctypes.c_int(), ctypes.c_int(), ctypes.create_string_buffer(200)
+    if ref.ref_tinyexr_load(str(path).encode(), ctypes.byref(w), ctypes.byref(h), None, ctypes.c_size_t(0), why, ctypes.c_size_t(200)):
+        return why.value.decode()
+    out = np.zeros((h.value, w.value, 4), np.float32)
+    ref.ref_tinyexr_load(str(path).encode(), ctypes.byref(w), ctypes.byref(h), out.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(out.size), why, ctypes.c_size_t(200))
+    return out
+
+
+def test_8bit_decoders_against_the_references_stb_image(ngp, tmp_path):
+    """The reference decodes every non-EXR image with its vendored stb_image (stbi_load(..., 4), src/common_host.cu:214-217). That
+    header, compiled as it is (oracle/ref_images.cc), and this library's host decoders must return the same RGBA8 texels for PNG
+    (8 / 16 bit, grey, grey + alpha, palette, tRNS keys, 1-bit), BMP, TGA and binary PNM files."""
+    ref = _ref_images()
+    Image = pytest.importorskip("PIL.Image")
+    cv2 = pytest.importorskip("cv2")
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(21)
+    h, w = 23, 31
+    rgba = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    rgb, grey, la = np.ascontiguousarray(rgba[..., :3]), np.ascontiguousarray(rgba[..., 0]), np.ascontiguousarray(rgba[..., [0, 3]])
+    pal = Image.fromarray(rgb).quantize(16)
+    files = []
+
+    def save(name, im, **kw):
+        im.save(str(tmp_path / name), **kw)
+        files.append(name)
+    save("rgb.png", Image.fromarray(rgb)); save("rgba.png", Image.fromarray(rgba)); save("grey.png", Image.fromarray(grey)); save("la.png", Image.fromarray(la, "LA"))
+    save("pal.png", pal); save("pal_trns.png", pal, transparency=3); save("bw.png", Image.fromarray(grey).convert("1"))
+    save("rgb_trns.png", Image.fromarray(rgb), transparency=tuple(int(v) for v in rgb[0, 0]))
+    save("grey_trns.png", Image.fromarray(grey), transparency=int(grey[0, 0]))
+    for name, shape in (("rgb16.png", (h, w, 3)), ("grey16.png", (h, w)), ("rgba16.png", (h, w, 4))):
+        assert cv2.imwrite(str(tmp_path / name), rng.integers(0, 65536, shape, dtype=np.uint16))
+        files.append(name)
+    save("rgb.bmp", Image.fromarray(rgb)); save("rgba.bmp", Image.fromarray(rgba)); save("pal.bmp", pal); save("bw.bmp", Image.fromarray(grey).convert("1")); save("grey.bmp", Image.fromarray(grey))
+    save("rgb.tga", Image.fromarray(rgb)); save("rgba_rle.tga", Image.fromarray(rgba), compression="tga_rle"); save("grey_rle.tga", Image.fromarray(grey), compression="tga_rle")
+    save("pal.tga", pal); save("la.tga", Image.fromarray(la, "LA")); save("top.tga", Image.fromarray(rgb), orientation=1)
+    save("rgb.ppm", Image.fromarray(rgb)); save("grey.pgm", Image.fromarray(grey))
+    for name in files:
+        want = _ref_stbi(ref, tmp_path / name)
+        assert not isinstance(want, str), (name, want)
+        got = _decode_image(lib, tmp_path / name)
+        assert got.shape == want.shape and np.array_equal(got, want), name
+
+
+def test_exr_reader_against_the_references_tinyexr(ngp, tmp_path):
+    """tinyexr's LoadEXR as vendored by the reference (what load_exr reads the image mode's file with) against csrc/host_exr.cu on
+    every scanline compression at HALF and FLOAT, on the committed fixtures, on a one-channel file and on the staged albert.exr."""
+    ref = _ref_images()
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    cv2 = pytest.importorskip("cv2")
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(22)
+    paths = sorted(str(p) for p in __import__("pathlib").Path(os.path.dirname(os.path.abspath(__file__)), "golden", "exr").glob("*.exr"))
+    staged = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "data_stage", "albert.exr")
+    if os.path.exists(staged):
+        paths.append(staged)
+    img = rng.standard_normal((37, 53, 4)).astype(np.float32)
+    try:
+        for comp in ("NO", "RLE", "ZIPS", "ZIP", "PIZ"):
+            for tname, t in (("half", cv2.IMWRITE_EXR_TYPE_HALF), ("float", cv2.IMWRITE_EXR_TYPE_FLOAT)):
+                for channels in (3, 4):
+                    p = str(tmp_path / ("%s_%s_%d.exr" % (comp, tname, channels)))
+                    if cv2.imwrite(p, img[..., :channels], [cv2.IMWRITE_EXR_COMPRESSION, getattr(cv2, "IMWRITE_EXR_COMPRESSION_" + comp), cv2.IMWRITE_EXR_TYPE, t]):
+                        paths.append(p)
+        p = str(tmp_path / "one_channel.exr")
+        if cv2.imwrite(p, img[..., 0], [cv2.IMWRITE_EXR_TYPE, cv2.IMWRITE_EXR_TYPE_HALF]):
+            paths.append(p)
+    except cv2.error:
+        pass
+    assert len(paths) >= 5
+    for p in paths:
+        want = _ref_tinyexr(ref, p)
+        assert not isinstance(want, str), (p, want)
+        got = _decode_exr(lib, p)
+        assert got.shape == want.shape and np.array_equal(got.view(np.uint32), want.view(np.uint32)), p
