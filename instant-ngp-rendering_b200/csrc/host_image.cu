@@ -130,14 +130,15 @@ bool looks_like_tga(const std::vector<uint8_t>& f) {
 	return rd<uint16_t>(&f[12]) > 0 && rd<uint16_t>(&f[14]) > 0;
 }
 
-// one stored TGA texel of `bits` bits -> RGBA8 (16-bit true colour is 1-5-5-5 with the top bit ignored, as stb_image does)
+// one stored TGA texel of `bits` bits -> RGBA8. 15 / 16-bit true colour is 1-5-5-5 with the top bit ignored and each 5-bit
+// channel scaled as (v * 255) / 31, stb_image's rule (stbi__tga_read_rgb16) - not the bit replication BMP bit fields get
 void tga_texel(const uint8_t* p, int bits, bool grey, uint8_t* out) {
 	if (grey) {
 		out[0] = out[1] = out[2] = p[0];
 		out[3] = bits == 16 ? p[1] : 255;
 	} else if (bits == 15 || bits == 16) {
 		const uint32_t v = rd<uint16_t>(p);
-		out[0] = widen((v >> 10) & 31, 5); out[1] = widen((v >> 5) & 31, 5); out[2] = widen(v & 31, 5); out[3] = 255;
+		out[0] = (uint8_t)((((v >> 10) & 31) * 255) / 31); out[1] = (uint8_t)((((v >> 5) & 31) * 255) / 31); out[2] = (uint8_t)(((v & 31) * 255) / 31); out[3] = 255;
 	} else {
 		out[0] = p[2]; out[1] = p[1]; out[2] = p[0];
 		out[3] = bits == 32 ? p[3] : 255;
@@ -154,6 +155,10 @@ HostImage decode_tga(const std::vector<uint8_t>& f, const std::string& name) {
 	size_t at = 18 + (size_t)id_len;
 	std::vector<uint8_t> palette;
 	if (cmap) {
+		// stb_image treats the colour map's "first entry index" as a count of BYTES to skip before the map and indexes the map
+		// from 0 (stb_image.h stbi__tga_load: stbi__skip(s, tga_palette_start)); files in the wild have 0 there. Mirrored.
+		at += (size_t)cmap_first;
+		if (cmap_len == 0) fail(name, "bad palette");
 		const size_t eb = (size_t)(cmap_bits + 7) / 8;
 		if (at + eb * cmap_len > f.size()) fail(name, "truncated TGA palette");
 		palette.resize((size_t)cmap_len * 4);
@@ -169,9 +174,9 @@ HostImage decode_tga(const std::vector<uint8_t>& f, const std::string& name) {
 	auto store = [&](size_t i, const uint8_t* p) {
 		uint8_t* out = &img.rgba[i * 4];
 		if (cmap) {
-			int idx = (bits == 8 ? p[0] : rd<uint16_t>(p)) - cmap_first;
-			if (idx < 0 || idx >= cmap_len) idx = 0;
-			if (cmap_len > 0) memcpy(out, &palette[(size_t)idx * 4], 4); else { out[0] = out[1] = out[2] = 0; out[3] = 255; }
+			int idx = bits == 8 ? p[0] : rd<uint16_t>(p);
+			if (idx >= cmap_len) idx = 0;
+			memcpy(out, &palette[(size_t)idx * 4], 4);
 		} else {
 			tga_texel(p, bits, grey, out);
 		}
@@ -208,7 +213,10 @@ HostImage decode_tga(const std::vector<uint8_t>& f, const std::string& name) {
 	return img;
 }
 
-// ---- binary PNM: P5 (grey) and P6 (RGB), 8 or 16 bits per sample (16-bit samples keep their high byte) ----
+// ---- binary PNM: P5 (grey) and P6 (RGB), 8 or 16 bits per sample ----
+// 16-bit samples are big-endian in the file; stb_image reads them as native words and keeps the upper half of those, which on
+// the little-endian hosts the reference runs on is the file's SECOND byte - the low-order one. Mirrored, as the bar is the
+// reference's texels (pinned by tests/test_host_io_cpu.py against the reference's stb_image).
 HostImage decode_pnm(const std::vector<uint8_t>& f, const std::string& name) {
 	size_t at = 2;
 	auto number = [&]() {
@@ -235,7 +243,7 @@ HostImage decode_pnm(const std::vector<uint8_t>& f, const std::string& name) {
 	for (size_t i = 0; i < n; ++i) {
 		const uint8_t* p = &f[at + i * channels * sample];
 		uint8_t* out = &img.rgba[i * 4];
-		for (int c = 0; c < 3; ++c) out[c] = p[(channels == 3 ? c : 0) * sample];
+		for (int c = 0; c < 3; ++c) out[c] = p[(channels == 3 ? c : 0) * sample + (sample - 1)];
 		out[3] = 255;
 	}
 	return img;

@@ -563,6 +563,11 @@ def test_8bit_decoders_against_the_references_stb_image(ngp, tmp_path):
     save("rgb.tga", Image.fromarray(rgb)); save("rgba_rle.tga", Image.fromarray(rgba), compression="tga_rle"); save("grey_rle.tga", Image.fromarray(grey), compression="tga_rle")
     save("pal.tga", pal); save("la.tga", Image.fromarray(la, "LA")); save("top.tga", Image.fromarray(rgb), orientation=1)
     save("rgb.ppm", Image.fromarray(rgb)); save("grey.pgm", Image.fromarray(grey))
+    # 16-bit PNM (stb_image keeps the low-order byte of each big-endian sample), comments and odd white space in the header
+    (tmp_path / "rgb16.ppm").write_bytes(b"P6\n# c\n%d %d\n65535\n" % (w, h) + rng.integers(0, 65536, (h, w, 3), dtype=np.uint16).astype(">u2").tobytes())
+    (tmp_path / "grey16.pgm").write_bytes(b"P5 %d\t%d #x\n 65535\n" % (w, h) + rng.integers(0, 65536, (h, w), dtype=np.uint16).astype(">u2").tobytes())
+    (tmp_path / "max99.ppm").write_bytes(b"P6 #x\n%d\t%d #y\n 99\n" % (w, h) + rng.integers(0, 100, (h, w, 3), dtype=np.uint8).tobytes())
+    files += ["rgb16.ppm", "grey16.pgm", "max99.ppm"]
     for name in files:
         want = _ref_stbi(ref, tmp_path / name)
         assert not isinstance(want, str), (name, want)
@@ -601,3 +606,81 @@ def test_exr_reader_against_the_references_tinyexr(ngp, tmp_path):
         assert not isinstance(want, str), (p, want)
         got = _decode_exr(lib, p)
         assert got.shape == want.shape and np.array_equal(got.view(np.uint32), want.view(np.uint32)), p
+
+
+def test_bmp_and_tga_variants_against_the_references_stb_image(ngp, tmp_path):
+    """Hand-built BMP and TGA files over the header space (Pillow writes only a corner of it) decoded by the reference's stb_image
+    and by csrc/host_image.cu: BMP with 40 / 108 / 124-byte headers, 1 / 4 / 8-bit palettes, 16 / 24 / 32 bits, top-down rows,
+    5-6-5 / 1-5-5-5 / 4-4-4-4 / 8-8-8-8 bit fields; TGA true colour 15 / 16 / 24 / 32 bits (5-bit channels scale as v * 255 / 31),
+    grey 8 / 16, colour maps of 8 / 15 / 16 / 24 / 32-bit entries under 8- and 16-bit indices, run-length packets, both row
+    orders, image-id bytes, and stb_image's reading of the colour map's first-entry field as a byte skip.
+    Left out, because the reference itself does not decode them to defined texels: OS/2 12-byte-header palettes and indices
+    beyond the palette (stb_image reads uninitialised entries), 56-byte headers with bit fields and channel masks wider than
+    8 bits (stb_image refuses both; this library reads them)."""
+    ref = _ref_images()
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(33)
+
+    def bmp(w, h, bpp, hsz=40, compression=0, masks=(0, 0, 0, 0), top_down=False):
+        stride = (w * bpp + 31) // 32 * 4
+        data = bytes(rng.integers(0, 256, stride * h, dtype=np.uint8))
+        pal = bytes(rng.integers(0, 256, (1 << bpp) * 4, dtype=np.uint8)) if bpp <= 8 else b""
+        info = struct.pack("<IiiHHIIiiII", 40, w, -h if top_down else h, 1, bpp, compression, len(data), 2835, 2835, 0, 0)
+        if hsz == 40 and compression == 3:
+            info += struct.pack("<III", *masks[:3])
+        elif hsz > 40:
+            info = struct.pack("<I", hsz) + info[4:] + struct.pack("<IIII", *masks)
+            info += b"\0" * (hsz - len(info))
+        off = 14 + len(info) + len(pal)
+        return b"BM" + struct.pack("<IHHI", off + len(data), 0, 0, off) + info + pal + data
+
+    def tga(w, h, typ, bits, cmap_bits=0, cmap_len=0, cmap_first=0, desc=0, id_len=0, rle=False):
+        hdr = struct.pack("<BBBHHBHHHHBB", id_len, 1 if cmap_len else 0, typ | (8 if rle else 0), cmap_first, cmap_len, cmap_bits, 0, 0, w, h, bits, desc)
+        ident = bytes(rng.integers(0, 256, id_len, dtype=np.uint8))
+        pal = bytes(rng.integers(0, 256, cmap_first + cmap_len * ((cmap_bits + 7) // 8), dtype=np.uint8))
+        tex, n = (bits + 7) // 8, w * h
+        if typ == 1:
+            px = [int(i).to_bytes(tex, "little") for i in rng.integers(0, cmap_len + 3, n)]   # a few indices past the map: entry 0
+        else:
+            px = [bytes(rng.integers(0, 256, tex, dtype=np.uint8)) for _ in range(n)]
+        if not rle:
+            return hdr + ident + pal + b"".join(px)
+        data, i = b"", 0
+        while i < n:
+            c = min(int(rng.integers(1, 129)), n - i)
+            if rng.random() < 0.5:
+                data += bytes([0x80 | (c - 1)]) + px[i]
+                px[i:i + c] = [px[i]] * c
+            else:
+                data += bytes([c - 1]) + b"".join(px[i:i + c])
+            i += c
+        return hdr + ident + pal + data
+
+    cases = []
+    for w, h in ((7, 5), (1, 1), (33, 3)):
+        for bpp in (1, 4, 8, 16, 24, 32):
+            for hsz in (40, 108, 124):
+                for td in (False, True):
+                    cases.append(("bmp %dx%d bpp%d hsz%d td%d" % (w, h, bpp, hsz, td), bmp(w, h, bpp, hsz, top_down=td)))
+        for bpp, masks in ((16, (0xF800, 0x07E0, 0x001F, 0)), (16, (0x7C00, 0x03E0, 0x001F, 0x8000)), (16, (0x0F00, 0x00F0, 0x000F, 0xF000)),
+                           (32, (0xFF0000, 0xFF00, 0xFF, 0xFF000000)), (32, (0xFF, 0xFF00, 0xFF0000, 0))):
+            for hsz in (40, 108, 124):
+                cases.append(("bmp bit fields bpp%d %s hsz%d" % (bpp, [hex(m) for m in masks], hsz), bmp(w, h, bpp, hsz, 3, masks)))
+        for rle in (False, True):
+            for desc in (0, 0x20, 0x10, 0x28):
+                for bits in (15, 16, 24, 32):
+                    cases.append(("tga rgb%d rle%d desc%#x" % (bits, rle, desc), tga(w, h, 2, bits, desc=desc, rle=rle, id_len=int(rng.integers(0, 5)))))
+                for bits in (8, 16):
+                    cases.append(("tga grey%d rle%d desc%#x" % (bits, rle, desc), tga(w, h, 3, bits, desc=desc, rle=rle)))
+                for cb in (8, 15, 16, 24, 32):
+                    for ib in (8, 16):
+                        cases.append(("tga map%d index%d rle%d desc%#x" % (cb, ib, rle, desc), tga(w, h, 1, ib, cmap_bits=cb, cmap_len=19, desc=desc, rle=rle)))
+                cases.append(("tga map first 5 rle%d" % rle, tga(w, h, 1, 8, cmap_bits=24, cmap_len=19, cmap_first=5, desc=desc, rle=rle)))
+    assert len(cases) > 500
+    path = tmp_path / "case.bin"
+    for tag, blob in cases:
+        path.write_bytes(blob)
+        want = _ref_stbi(ref, path)
+        assert not isinstance(want, str), (tag, want)
+        got = _decode_image(lib, path)
+        assert got.shape == want.shape and np.array_equal(got, want), tag
