@@ -40,7 +40,7 @@ struct HostImageF {
 enum class ExrChannelRule { Image, Dataset };
 HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name_for_errors, ExrChannelRule rule);
 
-// PNG (8 / 16 bit, grey / grey-alpha / RGB / RGBA / palette, non-interlaced) decoded on the host with zlib.
+// PNG (8 / 16 bit, grey / grey-alpha / RGB / RGBA / palette, plain or Adam7-interlaced) decoded on the host with zlib.
 HostImage decode_png(const std::vector<uint8_t>& file, const std::string& name_for_errors);
 // Any 8-bit format of the loader but JPEG, picked from the file's content as stb_image does: PNG, BMP, TGA, binary PNM (host_image.cu).
 HostImage decode_image_rgba8(const std::vector<uint8_t>& file, const std::string& name_for_errors);

@@ -1,7 +1,8 @@
 // PNG decoder on zlib for the dataset loader (the reference decodes with stb_image, src/nerf_loader.cu:541-560, which
-// is not part of this image): 8- and 16-bit samples (16 -> 8 by the high byte, as stb_image's conversion), grey /
-// grey-alpha / RGB / RGBA / palette with tRNS, bit depths 1 / 2 / 4 for grey and palette, non-interlaced. Output is
-// 8-bit RGBA, rows top to bottom. Host only.
+// is not linked here; the reference's vendored copy, compiled for the host, pins this file in tests/test_host_io_cpu.py):
+// plain and Adam7-interlaced files, 8- and 16-bit samples (16 -> 8 by the high byte, as stb_image's conversion), grey /
+// grey-alpha / RGB / RGBA / palette with tRNS, bit depths 1 / 2 / 4 for grey and palette. Output is 8-bit RGBA, rows top
+// to bottom. Host only.
 #include "host_io.h"
 
 #include <zlib.h>
@@ -45,7 +46,7 @@ HostImage decode_png(const std::vector<uint8_t>& file, const std::string& name) 
 		pos += 12 + (size_t)len;
 	}
 	if (!have_ihdr || w == 0 || h == 0 || w > (1u << 16) || h > (1u << 16)) fail("missing or implausible header");
-	if (interlace != 0) fail("interlaced (Adam7) files are not supported");
+	if (interlace != 0 && interlace != 1) fail("unknown interlace method");
 	int channels = 0;
 	switch (color) {
 		case 0: channels = 1; break;
@@ -61,7 +62,18 @@ HostImage decode_png(const std::vector<uint8_t>& file, const std::string& name) 
 	const size_t bits_per_pixel = (size_t)channels * depth;
 	const size_t stride = (w * bits_per_pixel + 7) / 8;
 	const size_t bpp = std::max<size_t>(1, bits_per_pixel / 8);   // filter distance in bytes
-	std::vector<uint8_t> raw((stride + 1) * h);
+	// Adam7: seven sub-images (pass p holds the pixels x = x0 + i * dx, y = y0 + j * dy), each filtered on its own
+	static const uint32_t kX0[7] = {0, 4, 0, 2, 0, 1, 0}, kY0[7] = {0, 0, 4, 0, 2, 0, 1}, kDx[7] = {8, 8, 4, 4, 2, 2, 1}, kDy[7] = {8, 8, 8, 4, 4, 2, 2};
+	struct Pass { uint32_t w, h, x0, y0, dx, dy; size_t stride; };
+	std::vector<Pass> passes;
+	if (interlace == 0) passes.push_back({w, h, 0, 0, 1, 1, stride});
+	else for (int p = 0; p < 7; ++p) {
+		const uint32_t pw = (w + kDx[p] - 1 - kX0[p]) / kDx[p], ph = (h + kDy[p] - 1 - kY0[p]) / kDy[p];
+		if (kX0[p] < w && kY0[p] < h && pw && ph) passes.push_back({pw, ph, kX0[p], kY0[p], kDx[p], kDy[p], (pw * bits_per_pixel + 7) / 8});
+	}
+	size_t raw_bytes = 0;
+	for (const Pass& p : passes) raw_bytes += (p.stride + 1) * p.h;
+	std::vector<uint8_t> raw(raw_bytes);
 	{
 		z_stream zs{};
 		if (inflateInit(&zs) != Z_OK) fail("zlib init failed");
@@ -73,27 +85,45 @@ HostImage decode_png(const std::vector<uint8_t>& file, const std::string& name) 
 		if ((rc != Z_STREAM_END && rc != Z_OK && rc != Z_BUF_ERROR) || got != raw.size()) fail("corrupt or truncated image data");
 	}
 
-	// unfilter in place (each scanline is preceded by its filter type)
-	std::vector<uint8_t> prev(stride, 0);
-	std::vector<uint8_t> pix(stride * h);
-	for (uint32_t y = 0; y < h; ++y) {
-		const uint8_t ft = raw[(stride + 1) * y];
-		const uint8_t* src = &raw[(stride + 1) * y + 1];
-		uint8_t* dst = &pix[stride * y];
-		for (size_t i = 0; i < stride; ++i) {
-			const int a = i >= bpp ? dst[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0;
-			int v = src[i];
-			switch (ft) {
-				case 0: break;
-				case 1: v += a; break;
-				case 2: v += b; break;
-				case 3: v += (a + b) / 2; break;
-				case 4: v += paeth(a, b, c); break;
-				default: fail("unknown filter type");
+	// unfilter (each scanline is preceded by its filter type); interlaced passes are scattered into the full-size packed image
+	std::vector<uint8_t> pix(stride * h, 0);
+	size_t raw_at = 0;
+	std::vector<uint8_t> line, prev;
+	for (const Pass& p : passes) {
+		prev.assign(p.stride, 0);
+		line.assign(p.stride, 0);
+		for (uint32_t j = 0; j < p.h; ++j) {
+			const uint8_t ft = raw[raw_at];
+			const uint8_t* src = &raw[raw_at + 1];
+			raw_at += p.stride + 1;
+			uint8_t* dst = interlace == 0 ? &pix[stride * j] : line.data();
+			for (size_t i = 0; i < p.stride; ++i) {
+				const int a = i >= bpp ? dst[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0;
+				int v = src[i];
+				switch (ft) {
+					case 0: break;
+					case 1: v += a; break;
+					case 2: v += b; break;
+					case 3: v += (a + b) / 2; break;
+					case 4: v += paeth(a, b, c); break;
+					default: fail("unknown filter type");
+				}
+				dst[i] = (uint8_t)v;
 			}
-			dst[i] = (uint8_t)v;
+			memcpy(prev.data(), dst, p.stride);
+			if (interlace == 0) continue;
+			uint8_t* out_row = &pix[stride * ((size_t)p.y0 + (size_t)j * p.dy)];
+			for (uint32_t i = 0; i < p.w; ++i) {
+				const size_t x = (size_t)p.x0 + (size_t)i * p.dx;
+				if (bits_per_pixel >= 8) {
+					memcpy(out_row + x * (bits_per_pixel / 8), line.data() + i * (bits_per_pixel / 8), bits_per_pixel / 8);
+				} else {
+					const size_t from = i * bits_per_pixel, to = x * bits_per_pixel;
+					const uint32_t v = (line[from / 8] >> (8 - bits_per_pixel - (from % 8))) & ((1u << bits_per_pixel) - 1u);
+					out_row[to / 8] |= (uint8_t)(v << (8 - bits_per_pixel - (to % 8)));
+				}
+			}
 		}
-		memcpy(prev.data(), dst, stride);
 	}
 
 	HostImage img;

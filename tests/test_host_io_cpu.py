@@ -684,3 +684,65 @@ def test_bmp_and_tga_variants_against_the_references_stb_image(ngp, tmp_path):
         assert not isinstance(want, str), (tag, want)
         got = _decode_image(lib, path)
         assert got.shape == want.shape and np.array_equal(got, want), tag
+
+
+def test_interlaced_png_against_the_references_stb_image(ngp, tmp_path):
+    """Adam7 files (neither Pillow nor OpenCV writes them; the encoder below does, pass by pass with per-line filters) in every
+    colour type and bit depth, at sizes where passes are empty, against stb_image."""
+    ref = _ref_images()
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(44)
+    x0, y0, dx, dy = (0, 4, 0, 2, 0, 1, 0), (0, 0, 4, 0, 2, 0, 1), (8, 8, 4, 4, 2, 2, 1), (8, 8, 8, 4, 4, 2, 2)
+
+    def chunk(tag, data):
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    def pack_row(samples, depth):           # samples: [n] ints of `depth` bits -> packed bytes
+        if depth == 8:
+            return bytes(int(v) for v in samples)
+        if depth == 16:
+            return b"".join(struct.pack(">H", int(v)) for v in samples)
+        bits = "".join(format(int(v), "0%db" % depth) for v in samples)
+        bits += "0" * (-len(bits) % 8)
+        return bytes(int(bits[i:i + 8], 2) for i in range(0, len(bits), 8))
+
+    def encode(w, h, color, depth, extra=b""):
+        channels = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[color]
+        img = rng.integers(0, 1 << depth, (h, w, channels))
+        bpp = max(1, channels * depth // 8)
+        raw = bytearray()
+        for p in range(7):
+            sub = img[y0[p]::dy[p], x0[p]::dx[p]]
+            if sub.shape[0] == 0 or sub.shape[1] == 0:
+                continue
+            prev = None
+            for row in sub:
+                line = pack_row(row.reshape(-1), depth)
+                ft = int(rng.integers(0, 5))
+                up = prev if prev is not None else bytes(len(line))
+                out = bytearray(len(line))
+                for i in range(len(line)):
+                    a = line[i - bpp] if i >= bpp else 0
+                    b = up[i]
+                    c = up[i - bpp] if i >= bpp else 0
+                    pa, pb, pc = abs(b - c), abs(a - c), abs(a + b - 2 * c)
+                    paeth = a if (pa <= pb and pa <= pc) else (b if pb <= pc else c)
+                    out[i] = (line[i] - (0, a, b, (a + b) // 2, paeth)[ft]) & 0xFF
+                raw += bytes([ft]) + out
+                prev = line
+        ihdr = struct.pack(">IIBBBBB", w, h, depth, color, 0, 0, 1)
+        return b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", ihdr) + extra + chunk(b"IDAT", zlib.compress(bytes(raw))) + chunk(b"IEND", b"")
+
+    palette = chunk(b"PLTE", bytes(rng.integers(0, 256, 256 * 3, dtype=np.uint8))) + chunk(b"tRNS", bytes(rng.integers(0, 256, 40, dtype=np.uint8)))
+    n = 0
+    for w, h in ((1, 1), (2, 3), (5, 1), (9, 9), (19, 13), (8, 8)):
+        for color, depths in ((0, (1, 2, 4, 8, 16)), (2, (8, 16)), (3, (1, 2, 4, 8)), (4, (8, 16)), (6, (8, 16))):
+            for depth in depths:
+                path = tmp_path / "a7.png"
+                path.write_bytes(encode(w, h, color, depth, palette if color == 3 else b""))
+                want = _ref_stbi(ref, path)
+                assert not isinstance(want, str), (w, h, color, depth, want)
+                got = _decode_image(lib, path)
+                assert got.shape == want.shape and np.array_equal(got, want), (w, h, color, depth)
+                n += 1
+    assert n == 6 * 15
