@@ -1,10 +1,11 @@
 // The loader's other 8-bit image formats. The reference decodes every non-EXR dataset image with stb_image
 // (load_stbi, src/common_host.cu:214-217; nerf_loader.cu:571-618), which picks the decoder from the file's content, not
 // its name. JPEG goes to nvjpeg and PNG to host_png.cu; this file adds what is left of stb_image's list that datasets
-// use - BMP, TGA and binary PNM - and the content sniffing in front of them. Output as everywhere: RGBA8, rows top to
+// use - BMP, GIF (first frame), TGA and binary PNM - and the content sniffing in front of them. Output as everywhere: RGBA8, rows top to
 // bottom, alpha 255 where the file has none. Host only.
 #include "host_io.h"
 
+#include <algorithm>
 #include <cstring>
 #include <stdexcept>
 
@@ -248,6 +249,150 @@ HostImage decode_pnm(const std::vector<uint8_t>& f, const std::string& name) {
 	}
 	return img;
 }
+
+// ---- GIF: the first frame, as stb_image's stbi_load returns it (stbi__gif_load_next, first_frame) ----
+// Quirks kept because the bar is the reference's texels: pixels of the transparent index are left (0, 0, 0, 0); pixels outside
+// the frame's rectangle take the background colour only when its index is > 0, alpha 255, and with red and blue swapped
+// (stb_image copies its B-G-R-A palette entry as it is); a Graphic Control Extension whose block is not 4 bytes long is not
+// skipped to its terminator. Bytes past the end of the file read as 0, which ends the raster early with what was drawn.
+HostImage decode_gif(const std::vector<uint8_t>& f, const std::string& name) {
+	size_t at = 0;
+	auto get8 = [&]() -> int { return at < f.size() ? f[at++] : 0; };
+	auto get16 = [&]() -> int { const int lo = get8(); return lo | (get8() << 8); };
+	auto skip = [&](int n) { at = std::min(f.size(), at + (size_t)std::max(n, 0)); };
+	if (f.size() < 13 || memcmp(f.data(), "GIF8", 4) != 0 || (f[4] != '7' && f[4] != '9') || f[5] != 'a') fail(name, "not GIF");
+	at = 6;
+	const int gw = get16(), gh = get16(), flags = get8(), bgindex = get8();
+	get8();   // aspect ratio
+	if (gw <= 0 || gh <= 0 || gw > (1 << 16) || gh > (1 << 16)) fail(name, "bad GIF size");
+	uint8_t pal[256][4] = {}, lpal[256][4] = {};   // B, G, R, A as stb_image keeps them
+	auto read_table = [&](uint8_t table[256][4], int n, int transparent) {
+		for (int i = 0; i < n; ++i) {
+			table[i][2] = (uint8_t)get8(); table[i][1] = (uint8_t)get8(); table[i][0] = (uint8_t)get8();
+			table[i][3] = transparent == i ? 0 : 255;
+		}
+	};
+	if (flags & 0x80) read_table(pal, 2 << (flags & 7), -1);
+	if ((size_t)gw * gh > f.size() * 4096) fail(name, "GIF size implausible for the file");
+
+	HostImage img;
+	img.width = gw; img.height = gh;
+	img.rgba.assign((size_t)gw * gh * 4, 0);
+	std::vector<uint8_t> drawn((size_t)gw * gh, 0);
+	int transparent = -1, eflags = 0;
+	for (;;) {
+		const int tag = get8();
+		if (tag == 0x21) {
+			const int ext = get8();
+			int len;
+			if (ext == 0xF9) {
+				len = get8();
+				if (len == 4) {
+					eflags = get8();
+					get16();   // delay
+					if (transparent >= 0) pal[transparent][3] = 255;
+					if (eflags & 0x01) { transparent = get8(); pal[transparent][3] = 0; }
+					else { skip(1); transparent = -1; }
+				} else {
+					skip(len);
+					continue;
+				}
+			}
+			while ((len = get8()) != 0) skip(len);
+		} else if (tag == 0x2C) {
+			const int x = get16(), y = get16(), w = get16(), h = get16();
+			if (x + w > gw || y + h > gh) fail(name, "bad Image Descriptor");
+			const int lflags = get8();
+			const size_t line = (size_t)gw * 4;
+			const size_t start_x = (size_t)x * 4, start_y = (size_t)y * line, max_x = start_x + (size_t)w * 4, max_y = start_y + (size_t)h * line;
+			size_t cur_x = start_x, cur_y = w == 0 ? max_y : start_y, step = (lflags & 0x40) ? 8 * line : line;
+			int parse = (lflags & 0x40) ? 3 : 0;
+			const uint8_t (*table)[4];
+			if (lflags & 0x80) { read_table(lpal, 2 << (lflags & 7), (eflags & 0x01) ? transparent : -1); table = lpal; }
+			else if (flags & 0x80) table = pal;
+			else fail(name, "missing color table");
+
+			auto emit = [&](uint8_t index) {
+				if (cur_y >= max_y) return;
+				const size_t idx = cur_x + cur_y;
+				drawn[idx / 4] = 1;
+				const uint8_t* c = table[index];
+				if (c[3] > 128) { img.rgba[idx] = c[2]; img.rgba[idx + 1] = c[1]; img.rgba[idx + 2] = c[0]; img.rgba[idx + 3] = c[3]; }
+				cur_x += 4;
+				if (cur_x >= max_x) {
+					cur_x = start_x;
+					cur_y += step;
+					while (cur_y >= max_y && parse > 0) {
+						step = ((size_t)1 << parse) * line;
+						cur_y = start_y + (step >> 1);
+						--parse;
+					}
+				}
+			};
+			// LZW, code for code as stbi__process_gif_raster walks it
+			struct Code { int16_t prefix; uint8_t first, suffix; };
+			std::vector<Code> codes(8192);
+			const int lzw_cs = get8();
+			if (lzw_cs > 12) fail(name, "corrupt GIF raster");
+			const int clear = 1 << lzw_cs;
+			bool first = true;
+			int codesize = lzw_cs + 1, codemask = (1 << codesize) - 1, avail = clear + 2, oldcode = -1, valid_bits = 0, len = 0;
+			int32_t bits = 0;
+			for (int c = 0; c < clear && c < 8192; ++c) codes[c] = {-1, (uint8_t)c, (uint8_t)c};
+			std::vector<uint8_t> chain;
+			bool done = false;
+			while (!done) {
+				if (valid_bits < codesize) {
+					if (len == 0) {
+						len = get8();
+						if (len == 0) break;
+					}
+					--len;
+					bits |= (int32_t)get8() << valid_bits;
+					valid_bits += 8;
+					continue;
+				}
+				const int code = bits & codemask;
+				bits >>= codesize;
+				valid_bits -= codesize;
+				if (code == clear) {
+					codesize = lzw_cs + 1; codemask = (1 << codesize) - 1; avail = clear + 2; oldcode = -1; first = false;
+				} else if (code == clear + 1) {
+					skip(len);
+					while ((len = get8()) > 0) skip(len);
+					done = true;
+				} else if (code <= avail) {
+					if (first) fail(name, "no clear code");
+					if (oldcode >= 0) {
+						if (avail + 1 > 8192) fail(name, "too many codes");
+						Code& p = codes[avail++];
+						p.prefix = (int16_t)oldcode;
+						p.first = codes[oldcode].first;
+						p.suffix = code == avail ? p.first : codes[code].first;
+					} else if (code == avail) {
+						fail(name, "illegal code in raster");
+					}
+					chain.clear();
+					for (int c = code; c >= 0; c = codes[c].prefix) chain.push_back(codes[c].suffix);
+					for (size_t k = chain.size(); k-- > 0;) emit(chain[k]);
+					if ((avail & codemask) == 0 && avail <= 0x0FFF) { ++codesize; codemask = (1 << codesize) - 1; }
+					oldcode = code;
+				} else {
+					fail(name, "illegal code in raster");
+				}
+			}
+			if (bgindex > 0) {
+				pal[bgindex][3] = 255;
+				for (size_t p = 0; p < drawn.size(); ++p) if (!drawn[p]) memcpy(&img.rgba[p * 4], pal[bgindex], 4);
+			}
+			return img;
+		} else if (tag == 0x3B) {
+			fail(name, "GIF without an image");
+		} else {
+			fail(name, "unknown code");
+		}
+	}
+}
 } // namespace
 
 bool is_jpeg_file(const std::vector<uint8_t>& f) { return f.size() > 3 && f[0] == 0xFF && f[1] == 0xD8 && f[2] == 0xFF; }
@@ -256,10 +401,11 @@ HostImage decode_image_rgba8(const std::vector<uint8_t>& f, const std::string& n
 	static const uint8_t png_magic[8] = {0x89, 'P', 'N', 'G', '\r', '\n', 0x1A, '\n'};
 	if (f.size() >= 8 && memcmp(f.data(), png_magic, 8) == 0) return decode_png(f, name);
 	if (is_jpeg_file(f)) fail(name, "JPEG files are decoded on the device (nvjpeg), not by the host decoder");
+	if (f.size() >= 4 && memcmp(f.data(), "GIF8", 4) == 0) return decode_gif(f, name);
 	if (f.size() >= 2 && f[0] == 'B' && f[1] == 'M') return decode_bmp(f, name);
 	if (f.size() >= 3 && f[0] == 'P' && (f[1] == '5' || f[1] == '6')) return decode_pnm(f, name);
 	if (looks_like_tga(f)) return decode_tga(f, name);
-	fail(name, "unknown image type (JPEG, PNG, BMP, TGA, binary PNM and EXR are read)");
+	fail(name, "unknown image type (JPEG, PNG, BMP, GIF, TGA, binary PNM and EXR are read)");
 }
 
 } // namespace ngpb

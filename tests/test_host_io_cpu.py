@@ -746,3 +746,99 @@ def test_interlaced_png_against_the_references_stb_image(ngp, tmp_path):
                 assert got.shape == want.shape and np.array_equal(got, want), (w, h, color, depth)
                 n += 1
     assert n == 6 * 15
+
+
+def test_gif_first_frame_against_the_references_stb_image(ngp, tmp_path):
+    """GIF is on the reference loader's list of dataset formats (nerf_loader.cu:315-317) and stbi_load returns its first frame.
+    Pillow-written files (2 / 16 / 256 colours, interlaced, transparent index, background index, animated) and hand-built ones
+    (frame smaller than the screen with and without a background index, local colour tables, extensions, a Graphic Control
+    Extension of odd length, rectangles out of bounds, too many / too few pixels, GIF87a, truncations) give stb_image's texels -
+    its quirks included - or fail where it fails."""
+    ref = _ref_images()
+    Image = pytest.importorskip("PIL.Image")
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(55)
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+
+    def check(tag, path):
+        want = _ref_stbi(ref, path)
+        if isinstance(want, str):
+            assert lib.ngpb_host_decode_image(str(path).encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0, (tag, want)
+            return 0
+        got = _decode_image(lib, path)
+        assert got.shape == want.shape and np.array_equal(got, want), tag
+        return 1
+    n_ok = 0
+    p = tmp_path / "g.gif"
+    for (h, w) in ((13, 17), (1, 1), (64, 50), (200, 3)):
+        noise = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        smooth = np.stack([np.add.outer(np.arange(h) * 3, np.arange(w) * k) % 256 for k in (1, 2, 5)], -1).astype(np.uint8)
+        for arr in (noise, smooth):
+            for colors in (2, 16, 256):
+                im = Image.fromarray(arr).quantize(colors)
+                for kw in ({}, {"interlace": True}, {"interlace": False}, {"transparency": 0}, {"transparency": 1, "interlace": True}, {"background": 1}, {"optimize": True}):
+                    im.save(str(p), **kw)
+                    n_ok += check((h, w, colors, kw), p)
+        frames = [Image.fromarray(rng.integers(0, 256, (h, w, 3), dtype=np.uint8)).quantize(8) for _ in range(3)]
+        frames[0].save(str(p), save_all=True, append_images=frames[1:], duration=40, loop=0)
+        n_ok += check((h, w, "animated"), p)
+    assert n_ok == 4 * (2 * 3 * 7 + 1)
+
+    def lzw_plain(indices, cs):
+        # uncompressed-GIF trick: a clear code often enough that the code size never grows
+        clear, end = 1 << cs, (1 << cs) + 1
+        size = cs + 1
+        bits, nbits, out = 0, 0, bytearray()
+        def put(c):
+            nonlocal bits, nbits
+            bits |= c << nbits; nbits += size
+            while nbits >= 8: out.append(bits & 255); bits >>= 8; nbits -= 8
+        n = 0
+        put(clear)
+        for v in indices:
+            put(int(v)); n += 1
+            if n == (1 << cs) - 2: put(clear); n = 0
+        put(end)
+        if nbits: out.append(bits & 255)
+        data = bytes([cs])
+        for i in range(0, len(out), 255): data += bytes([len(out[i:i+255])]) + bytes(out[i:i+255])
+        return data + b'\0'
+    def gif(gw, gh, bg, gpal, frames, exts=b''):
+        flags = (0x80 | (int(np.log2(len(gpal)//3)) - 1)) if gpal else 0
+        b = b'GIF89a' + struct.pack('<HHBBB', gw, gh, flags, bg, 0) + (gpal or b'') + exts
+        for (x,y,w,h,lpal,interlace,idx,cs,gce) in frames:
+            b += gce
+            lf = (0x80 | (int(np.log2(len(lpal)//3)) - 1)) if lpal else 0
+            if interlace: lf |= 0x40
+            b += b'\x2C' + struct.pack('<HHHHB', x,y,w,h,lf) + (lpal or b'') + lzw_plain(idx, cs)
+        return b + b'\x3B'
+    pal16 = bytes(rng.integers(0,256,48,dtype=np.uint8)); pal4 = bytes(rng.integers(0,256,12,dtype=np.uint8)); pal256=bytes(rng.integers(0,256,768,dtype=np.uint8))
+    gce = lambda fl, tr: b'\x21\xF9\x04' + bytes([fl]) + b'\x05\x00' + bytes([tr]) + b'\0'
+    cases = {
+     'sub-rect bg3': gif(11,9,3,pal16,[(2,1,5,4,None,False,rng.integers(0,16,20),4,b'')]),
+     'sub-rect bg0': gif(11,9,0,pal16,[(2,1,5,4,None,False,rng.integers(0,16,20),4,b'')]),
+     'sub-rect bg3 transparent': gif(11,9,3,pal16,[(2,1,5,4,None,False,rng.integers(0,16,20),4,gce(1,3))]),
+     'local palette': gif(8,8,1,pal16,[(0,0,8,8,pal4,False,rng.integers(0,4,64),2,b'')]),
+     'local palette transparent interlaced': gif(8,9,1,pal16,[(0,0,8,9,pal4,True,rng.integers(0,4,72),2,gce(1,2))]),
+     'no global table': gif(8,8,0,None,[(0,0,8,8,pal4,False,rng.integers(0,4,64),2,b'')]),
+     'no table at all': gif(8,8,0,None,[(0,0,8,8,None,False,rng.integers(0,4,64),2,b'')]),
+     'comment + app ext': gif(8,8,0,pal16,[(0,0,8,8,None,False,rng.integers(0,16,64),4,b'')], exts=b'\x21\xFE\x05hello\0' + b'\x21\xFF\x0BNETSCAPE2.0\x03\x01\x00\x00\0'),
+     'gce odd length': gif(8,8,0,pal16,[(0,0,8,8,None,False,rng.integers(0,16,64),4,b'\x21\xF9\x02\x01\x02\0')]),
+     'rect out of bounds': gif(8,8,0,pal16,[(4,4,8,8,None,False,rng.integers(0,16,64),4,b'')]),
+     'zero width': gif(8,8,2,pal16,[(0,0,0,8,None,False,[],4,b'')]),
+     'too many pixels': gif(4,4,0,pal16,[(0,0,4,4,None,False,rng.integers(0,16,40),4,b'')]),
+     'too few pixels': gif(6,6,5,pal16,[(0,0,6,6,None,False,rng.integers(0,16,20),4,b'')]),
+     '256 colours': gif(20,10,200,pal256,[(3,2,10,5,None,True,rng.integers(0,256,50),8,gce(1,7))]),
+     'only trailer': b'GIF89a' + struct.pack('<HHBBB', 4,4,0x80|3,0,0) + pal16 + b'\x3B',
+     'unknown tag': b'GIF89a' + struct.pack('<HHBBB', 4,4,0x80|3,0,0) + pal16 + b'\x55',
+     'gif87': b'GIF87a' + gif(5,5,0,pal4,[(0,0,5,5,None,False,rng.integers(0,4,25),2,b'')])[6:],
+    }
+    n_ok = 0
+    for tag, blob in cases.items():
+        p.write_bytes(blob)
+        n_ok += check(tag, p)
+    base = cases["256 colours"]
+    for cut in (20, 100, 790, 800, 810, len(base) - 3):
+        p.write_bytes(base[:cut])
+        n_ok += check("cut %d" % cut, p)
+    assert n_ok >= 14
