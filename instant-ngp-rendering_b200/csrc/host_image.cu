@@ -1,7 +1,7 @@
 // The loader's other 8-bit image formats. The reference decodes every non-EXR dataset image with stb_image
 // (load_stbi, src/common_host.cu:214-217; nerf_loader.cu:571-618), which picks the decoder from the file's content, not
 // its name. JPEG goes to nvjpeg and PNG to host_png.cu; this file adds what is left of stb_image's list that datasets
-// use - BMP, GIF (first frame), TGA and binary PNM - and the content sniffing in front of them. Output as everywhere: RGBA8, rows top to
+// use - BMP, GIF (first frame), PSD (flattened composite), TGA and binary PNM - and the content sniffing in front of them. Output as everywhere: RGBA8, rows top to
 // bottom, alpha 255 where the file has none. Host only.
 #include "host_io.h"
 
@@ -393,6 +393,80 @@ HostImage decode_gif(const std::vector<uint8_t>& f, const std::string& name) {
 		}
 	}
 }
+
+// ---- PSD: the flattened composite at the end of the file, RGB mode, 8 or 16 bits, raw or PackBits, as stb_image reads it ----
+// (stbi__psd_load): channels beyond the file's count are 0 (alpha 255); with four or more channels colours are taken off the white
+// matte, pixel * (1 / a) + 255 * (1 - 1 / a) in float and cut to a byte the way the reference's x86 build cuts it; PackBits rows
+// are read as bytes whatever the bit depth. Bytes past the end of the file read as 0.
+HostImage decode_psd(const std::vector<uint8_t>& f, const std::string& name) {
+	size_t at = 0;
+	auto get8 = [&]() -> int { return at < f.size() ? f[at++] : 0; };
+	auto get16 = [&]() -> int { const int hi = get8(); return (hi << 8) | get8(); };
+	auto get32 = [&]() -> uint32_t { const uint32_t hi = (uint32_t)get16(); return (hi << 16) | (uint32_t)get16(); };
+	auto skip = [&](uint32_t n) { at = (size_t)std::min<uint64_t>(f.size(), (uint64_t)at + n); };
+	if (get32() != 0x38425053u) fail(name, "not PSD");
+	if (get16() != 1) fail(name, "wrong version");
+	skip(6);
+	const int channel_count = get16();
+	if (channel_count < 0 || channel_count > 16) fail(name, "wrong channel count");
+	const uint32_t h = get32(), w = get32();
+	if (w == 0 || h == 0 || w > (1u << 16) || h > (1u << 16)) fail(name, "bad PSD size");
+	const int depth = get16();
+	if (depth != 8 && depth != 16) fail(name, "unsupported bit depth");
+	if (get16() != 3) fail(name, "wrong color format");
+	skip(get32());   // colour mode data
+	skip(get32());   // image resources
+	skip(get32());   // layers and masks
+	const int compression = get16();
+	if (compression > 1) fail(name, "bad compression");
+	const size_t n = (size_t)w * h;
+	if (n > f.size() * 4096) fail(name, "PSD size implausible for the file");
+
+	HostImage img;
+	img.width = (int)w; img.height = (int)h;
+	img.rgba.resize(n * 4);
+	if (compression) skip((uint32_t)(h * (uint32_t)channel_count * 2));   // the per-row byte counts
+	for (int c = 0; c < 4; ++c) {
+		uint8_t* p = &img.rgba[c];
+		if (c >= channel_count) {
+			for (size_t i = 0; i < n; ++i, p += 4) *p = c == 3 ? 255 : 0;
+		} else if (compression) {
+			size_t count = 0;
+			while (count < n) {
+				const size_t left = n - count;
+				int len = get8();
+				if (len == 128) continue;
+				if (len < 128) {
+					++len;
+					if ((size_t)len > left) fail(name, "bad RLE data");
+					count += (size_t)len;
+					for (; len; --len, p += 4) *p = (uint8_t)get8();
+				} else {
+					len = 257 - len;
+					if ((size_t)len > left) fail(name, "bad RLE data");
+					const uint8_t v = (uint8_t)get8();
+					count += (size_t)len;
+					for (; len; --len, p += 4) *p = v;
+				}
+				if (at >= f.size() && count < n) { for (; count < n; ++count, p += 4) *p = 0; }   // zeros past the end decode as literals of 0
+			}
+		} else if (depth == 16) {
+			for (size_t i = 0; i < n; ++i, p += 4) *p = (uint8_t)(get16() >> 8);
+		} else {
+			for (size_t i = 0; i < n; ++i, p += 4) *p = (uint8_t)get8();
+		}
+	}
+	if (channel_count >= 4) {
+		for (size_t i = 0; i < n; ++i) {
+			uint8_t* px = &img.rgba[i * 4];
+			if (px[3] != 0 && px[3] != 255) {
+				const float a = px[3] / 255.0f, ra = 1.0f / a, inv_a = 255.0f * (1 - ra);
+				for (int c = 0; c < 3; ++c) px[c] = (uint8_t)(int)(px[c] * ra + inv_a);
+			}
+		}
+	}
+	return img;
+}
 } // namespace
 
 bool is_jpeg_file(const std::vector<uint8_t>& f) { return f.size() > 3 && f[0] == 0xFF && f[1] == 0xD8 && f[2] == 0xFF; }
@@ -403,9 +477,10 @@ HostImage decode_image_rgba8(const std::vector<uint8_t>& f, const std::string& n
 	if (is_jpeg_file(f)) fail(name, "JPEG files are decoded on the device (nvjpeg), not by the host decoder");
 	if (f.size() >= 4 && memcmp(f.data(), "GIF8", 4) == 0) return decode_gif(f, name);
 	if (f.size() >= 2 && f[0] == 'B' && f[1] == 'M') return decode_bmp(f, name);
+	if (f.size() >= 4 && memcmp(f.data(), "8BPS", 4) == 0) return decode_psd(f, name);
 	if (f.size() >= 3 && f[0] == 'P' && (f[1] == '5' || f[1] == '6')) return decode_pnm(f, name);
 	if (looks_like_tga(f)) return decode_tga(f, name);
-	fail(name, "unknown image type (JPEG, PNG, BMP, GIF, TGA, binary PNM and EXR are read)");
+	fail(name, "unknown image type (JPEG, PNG, BMP, GIF, PSD, TGA, binary PNM and EXR are read)");
 }
 
 } // namespace ngpb

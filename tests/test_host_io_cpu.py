@@ -842,3 +842,72 @@ def test_gif_first_frame_against_the_references_stb_image(ngp, tmp_path):
         p.write_bytes(base[:cut])
         n_ok += check("cut %d" % cut, p)
     assert n_ok >= 14
+
+
+def test_psd_composite_against_the_references_stb_image(ngp, tmp_path):
+    """PSD is on the reference loader's list too; stb_image reads the flattened RGB composite. Hand-built files - 1 to 16 channels,
+    8 / 16 bits, raw and PackBits (with no-op bytes), header blocks to skip, every (colour, alpha) byte pair through the
+    white-matte removal, refused variants, truncations - give its texels or fail where it fails."""
+    ref = _ref_images()
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(66)
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+    path = tmp_path / "p.psd"
+
+    def check(tag, blob):
+        path.write_bytes(blob)
+        want = _ref_stbi(ref, path)
+        if isinstance(want, str):
+            assert lib.ngpb_host_decode_image(str(path).encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0, (tag, want)
+            return 0
+        got = _decode_image(lib, path)
+        assert got.shape == want.shape and np.array_equal(got, want), tag
+        return 1
+
+    def packbits(row):
+        out=bytearray(); i=0; n=len(row)
+        while i<n:
+            j=i
+            while j+1<n and row[j+1]==row[i] and j-i<127: j+=1
+            if j>i: out+=bytes([257-(j-i+1)]) + bytes([row[i]]); i=j+1
+            else:
+                j=i
+                while j+1<n and (j+2>=n or row[j+1]!=row[j+2]) and j-i<127: j+=1
+                out+=bytes([j-i]) + bytes(row[i:j+1]); i=j+1
+            if rng.random()<0.1: out+=b'\x80'
+        return bytes(out)
+    def psd(w,h,channels,depth,compression,mode=3,version=1,extra=(0,0,0),planes=None):
+        b = b'8BPS' + struct.pack('>H6xHIIHH', version, channels, h, w, depth, mode)
+        for n in extra: b += struct.pack('>I', n) + bytes(rng.integers(0,256,n,dtype=np.uint8))
+        b += struct.pack('>H', compression)
+        if planes is None:
+            planes = [rng.integers(0,1<<depth,(h,w)) for _ in range(channels)]
+            for p in planes[:3]: p[:h//2] = p[0,0]    # runs
+        if compression == 0:
+            for p in planes: b += p.astype('>u1' if depth==8 else '>u2').tobytes()
+        else:
+            rows = [[packbits(list(p[y].astype(np.uint8))) for y in range(h)] for p in planes]
+            for r in rows:
+                for x in r: b += struct.pack('>H', len(x))
+            for r in rows:
+                for x in r: b += x
+        return b
+    n_ok = 0
+    for w, h in ((7, 5), (1, 1), (33, 4)):
+        for channels in (1, 2, 3, 4, 5, 16):
+            for depth in (8, 16):
+                for comp in (0, 1):
+                    n_ok += check((w, h, channels, depth, comp), psd(w, h, channels, depth, comp, extra=tuple(int(v) for v in rng.integers(0, 9, 3))))
+    col, al = np.meshgrid(np.arange(256), np.arange(256))
+    n_ok += check("matte sweep", psd(256, 256, 4, 8, 0, planes=[col, (col * 7) % 256, 255 - col, al]))
+    assert n_ok == 3 * 6 * 2 * 2 + 1
+    plain = psd(4, 4, 3, 8, 0)
+    for tag, blob in (("mode 1", psd(4, 4, 1, 8, 0, mode=1)), ("version 2", psd(4, 4, 3, 8, 0, version=2)), ("17 channels", psd(4, 4, 17, 8, 0)),
+                      ("depth 32", plain[:22] + b"\0\x20" + plain[24:]), ("compression 2", plain[:38] + b"\0\x02" + plain[40:])):
+        assert check(tag, blob) == 0, tag
+    base = psd(9, 7, 4, 8, 1)
+    for cut in (10, 30, 60, len(base) - 20, len(base) - 1):
+        check("cut %d" % cut, base[:cut])
+    base = psd(9, 7, 3, 16, 0)
+    for cut in (45, 100, len(base) - 1):
+        check("raw cut %d" % cut, base[:cut])
