@@ -1,7 +1,7 @@
 // The loader's other 8-bit image formats. The reference decodes every non-EXR dataset image with stb_image
 // (load_stbi, src/common_host.cu:214-217; nerf_loader.cu:571-618), which picks the decoder from the file's content, not
 // its name. JPEG goes to nvjpeg and PNG to host_png.cu; this file adds what is left of stb_image's list that datasets
-// use - BMP, GIF (first frame), PSD (flattened composite), TGA and binary PNM - and the content sniffing in front of them. Output as everywhere: RGBA8, rows top to
+// use - BMP, GIF (first frame), PSD (flattened composite), Softimage PIC, TGA and binary PNM - and the content sniffing in front of them. Output as everywhere: RGBA8, rows top to
 // bottom, alpha 255 where the file has none. Host only.
 #include "host_io.h"
 
@@ -467,6 +467,87 @@ HostImage decode_psd(const std::vector<uint8_t>& f, const std::string& name) {
 	}
 	return img;
 }
+
+// ---- Softimage PIC, as stb_image reads it (stbi__pic_load): up to 10 channel packets of 8 bits, raw / pure RLE / mixed RLE ----
+bool looks_like_pic(const std::vector<uint8_t>& f) {
+	return f.size() >= 92 && f[0] == 0x53 && f[1] == 0x80 && f[2] == 0xF6 && f[3] == 0x34 && memcmp(&f[88], "PICT", 4) == 0;
+}
+
+HostImage decode_pic(const std::vector<uint8_t>& f, const std::string& name) {
+	size_t at = 92;
+	auto eof = [&]() { return at >= f.size(); };
+	auto get8 = [&]() -> int { return at < f.size() ? f[at++] : 0; };
+	auto get16 = [&]() -> int { const int hi = get8(); return (hi << 8) | get8(); };
+	const int w = get16(), h = get16();
+	if (eof()) fail(name, "file too short (pic header)");
+	if (w <= 0 || h <= 0) fail(name, "bad PIC size");
+	at += 8;   // ratio, fields, pad
+	struct Packet { int type, channel; };
+	std::vector<Packet> packets;
+	int chained;
+	do {
+		if (packets.size() == 10) fail(name, "too many packets");
+		chained = get8();
+		const int size = get8(), type = get8(), channel = get8();
+		if (eof()) fail(name, "file too short (reading packets)");
+		if (size != 8) fail(name, "packet isn't 8bpp");
+		packets.push_back({type, channel});
+	} while (chained);
+	if ((size_t)w * h > f.size() * 65536) fail(name, "PIC size implausible for the file");
+
+	HostImage img;
+	img.width = w; img.height = h;
+	img.rgba.assign((size_t)w * h * 4, 0xFF);
+	auto readval = [&](int channel, uint8_t* dest) {
+		for (int i = 0, mask = 0x80; i < 4; ++i, mask >>= 1) {
+			if (channel & mask) {
+				if (eof()) fail(name, "PIC file too short");
+				dest[i] = (uint8_t)get8();
+			}
+		}
+	};
+	auto copyval = [](int channel, uint8_t* dest, const uint8_t* src) {
+		for (int i = 0, mask = 0x80; i < 4; ++i, mask >>= 1) if (channel & mask) dest[i] = src[i];
+	};
+	for (int y = 0; y < h; ++y) {
+		for (const Packet& p : packets) {
+			uint8_t* dest = &img.rgba[(size_t)y * w * 4];
+			if (p.type == 0) {
+				for (int x = 0; x < w; ++x, dest += 4) readval(p.channel, dest);
+			} else if (p.type == 1) {
+				for (int left = w; left > 0;) {
+					int count = get8();
+					if (eof()) fail(name, "file too short (pure read count)");
+					if (count > left) count = (uint8_t)left;
+					uint8_t value[4] = {};
+					readval(p.channel, value);
+					for (int i = 0; i < count; ++i, dest += 4) copyval(p.channel, dest, value);
+					left -= count;
+				}
+			} else if (p.type == 2) {
+				for (int left = w; left > 0;) {
+					int count = get8();
+					if (eof()) fail(name, "file too short (mixed read count)");
+					if (count >= 128) {
+						count = count == 128 ? get16() : count - 127;
+						if (count > left) fail(name, "scanline overrun");
+						uint8_t value[4] = {};
+						readval(p.channel, value);
+						for (int i = 0; i < count; ++i, dest += 4) copyval(p.channel, dest, value);
+					} else {
+						++count;
+						if (count > left) fail(name, "scanline overrun");
+						for (int i = 0; i < count; ++i, dest += 4) readval(p.channel, dest);
+					}
+					left -= count;
+				}
+			} else {
+				fail(name, "packet has bad compression type");
+			}
+		}
+	}
+	return img;
+}
 } // namespace
 
 bool is_jpeg_file(const std::vector<uint8_t>& f) { return f.size() > 3 && f[0] == 0xFF && f[1] == 0xD8 && f[2] == 0xFF; }
@@ -478,9 +559,10 @@ HostImage decode_image_rgba8(const std::vector<uint8_t>& f, const std::string& n
 	if (f.size() >= 4 && memcmp(f.data(), "GIF8", 4) == 0) return decode_gif(f, name);
 	if (f.size() >= 2 && f[0] == 'B' && f[1] == 'M') return decode_bmp(f, name);
 	if (f.size() >= 4 && memcmp(f.data(), "8BPS", 4) == 0) return decode_psd(f, name);
+	if (looks_like_pic(f)) return decode_pic(f, name);
 	if (f.size() >= 3 && f[0] == 'P' && (f[1] == '5' || f[1] == '6')) return decode_pnm(f, name);
 	if (looks_like_tga(f)) return decode_tga(f, name);
-	fail(name, "unknown image type (JPEG, PNG, BMP, GIF, PSD, TGA, binary PNM and EXR are read)");
+	fail(name, "unknown image type (JPEG, PNG, BMP, GIF, PSD, PIC, TGA, binary PNM and EXR are read)");
 }
 
 } // namespace ngpb

@@ -911,3 +911,59 @@ def test_psd_composite_against_the_references_stb_image(ngp, tmp_path):
     base = psd(9, 7, 3, 16, 0)
     for cut in (45, 100, len(base) - 1):
         check("raw cut %d" % cut, base[:cut])
+
+
+def test_softimage_pic_against_the_references_stb_image(ngp, tmp_path):
+    """The last dataset format on the reference loader's list (nerf_loader.cu:315-317): Softimage PIC with raw, pure-RLE and
+    mixed-RLE channel packets (16-bit run counts included), channels split over several packets, alpha present or not; bad
+    packets, overruns and truncations fail where stb_image fails."""
+    ref = _ref_images()
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(77)
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+    path = tmp_path / "p.pic"
+
+    def check(tag, blob):
+        path.write_bytes(blob)
+        want = _ref_stbi(ref, path)
+        if isinstance(want, str):
+            assert lib.ngpb_host_decode_image(str(path).encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0, (tag, want)
+            return 0
+        got = _decode_image(lib, path)
+        assert got.shape == want.shape and np.array_equal(got, want), tag
+        return 1
+
+    def pic(w, h, packets, tail=b''):
+        # packets: list of (type, channel mask); channel bit 0x80 R, 0x40 G, 0x20 B, 0x10 A
+        b = b'\x53\x80\xF6\x34' + struct.pack('>f', 0.0) + bytes(80) + b'PICT' + struct.pack('>HHfHH', w, h, 1.0, 3, 0)
+        for k,(typ,chan) in enumerate(packets): b += bytes([1 if k+1 < len(packets) else 0, 8, typ, chan])
+        for y in range(h):
+            for typ,chan in packets:
+                n = bin(chan & 0xF0).count('1')
+                if typ == 0: b += bytes(rng.integers(0,256,w*n,dtype=np.uint8))
+                elif typ == 1:
+                    left = w
+                    while left > 0:
+                        c = int(rng.integers(1, min(left,255)+1)); b += bytes([c]) + bytes(rng.integers(0,256,n,dtype=np.uint8)); left -= c
+                else:
+                    left = w
+                    while left > 0:
+                        r = rng.random()
+                        if r < 0.4: c = int(rng.integers(1, min(left,128)+1)); b += bytes([c-1]) + bytes(rng.integers(0,256,c*n,dtype=np.uint8))
+                        elif r < 0.8 and left >= 2: c = int(rng.integers(2, min(left,128)+1)); b += bytes([c+127]) + bytes(rng.integers(0,256,n,dtype=np.uint8))
+                        else: c = int(rng.integers(1, left+1)); b += bytes([128]) + struct.pack('>H', c) + bytes(rng.integers(0,256,n,dtype=np.uint8))
+                        left -= c
+        return b + tail
+    n_ok = 0
+    for w, h in ((7, 5), (1, 1), (300, 3)):
+        for typ in (0, 1, 2):
+            for packets in ([(typ, 0xE0)], [(typ, 0xF0)], [(typ, 0xE0), (2 - typ, 0x10)], [(typ, 0x80), (typ, 0x40), (0, 0x20), (1, 0x10)], [(typ, 0x80)]):
+                n_ok += check((w, h, packets), pic(w, h, packets))
+    assert n_ok == 45
+    plain = pic(4, 4, [(0, 0xE0)])
+    for tag, blob in (("bad type", pic(4, 4, [(3, 0xE0)])), ("11 packets", pic(4, 4, [(0, 0x80)] * 11)), ("16 bpp", plain[:105] + b"\x10" + plain[106:]),
+                      ("overrun", pic(4, 1, [(2, 0xE0)])[:108] + bytes([127 + 6, 1, 2, 3]))):
+        assert check(tag, blob) == 0, tag
+    base = pic(9, 7, [(2, 0xE0), (1, 0x10)])
+    for cut in (95, 96, 100, 107, 112, 150, len(base) - 1):
+        assert check("cut %d" % cut, base[:cut]) == 0
