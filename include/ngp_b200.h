@@ -272,8 +272,10 @@ size_t ngpb_host_describe_dataset(const char* path, char* buf, size_t cap);
 /* The frame order of the loader: SI::natural::compare of dependencies/NaturalSort as src/nerf_loader.cu:347-349 uses it. 1 when a sorts before b. */
 int ngpb_host_natural_less(const char* a, const char* b);
 int ngpb_host_decode_png(const char* path, void* rgba, size_t cap, int* width, int* height);
-/* The loader's host decoder for 8-bit files other than JPEG, chosen from the file's content as stb_image does
- * (load_stbi, src/common_host.cu:214-217): PNG, BMP, GIF (first frame), PSD (composite), PIC, TGA, binary PNM -> RGBA8 rows top to bottom. */
+/* The loader's host decoders for 8-bit files, chosen from the file's content as stb_image does (load_stbi,
+ * src/common_host.cu:214-217): JPEG (baseline / progressive, with stb_image's IDCT / upsampling / colour arithmetic), PNG, BMP,
+ * GIF (first frame), PSD (composite), PIC, TGA, binary PNM -> RGBA8 rows top to bottom, the texels stbi_load(..., 4) returns.
+ * (ngpb_testbed_load_training_data decodes JPEG on the device with nvjpeg unless NGPB_JPEG_DECODER=host.) */
 int ngpb_host_decode_image(const char* path, void* rgba, size_t cap, int* width, int* height);
 /* The loader's OpenEXR reader (single-part scanline, HALF / FLOAT, NONE / RLE / ZIPS / ZIP / PIZ): float RGBA rows top to bottom. */
 int ngpb_host_decode_exr(const char* path, float* rgba, size_t cap_floats, int* width, int* height);

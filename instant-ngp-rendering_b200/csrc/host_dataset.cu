@@ -349,7 +349,11 @@ struct JpegDecoder {
 static void decode_to_device(JpegDecoder& jpeg, const std::string& path, DeviceBuffer& rgb_scratch, DeviceBuffer& out, int& width, int& height, cudaStream_t stream) {
 	const std::string ext = path_extension(path);
 	const std::vector<uint8_t> file = read_file(path);
-	if (is_jpeg_file(file)) {
+	// NGPB_JPEG_DECODER=host: JPEG on the host with stb_image's arithmetic (host_jpeg.cu) - the reference loader's texels bit for
+	// bit, at host speed; the default decodes on the device with nvjpeg, whose IDCT and upsampling round differently (about one
+	// level, tests/test_host_files_gpu.py)
+	static const bool host_jpeg = getenv("NGPB_JPEG_DECODER") && std::string{getenv("NGPB_JPEG_DECODER")} == "host";
+	if (is_jpeg_file(file) && !host_jpeg) {
 		jpeg.init();
 		int n_components = 0, widths[NVJPEG_MAX_COMPONENT], heights[NVJPEG_MAX_COMPONENT];
 		nvjpegChromaSubsampling_t subsampling;

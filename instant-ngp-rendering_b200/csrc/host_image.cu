@@ -1,6 +1,6 @@
 // The loader's other 8-bit image formats. The reference decodes every non-EXR dataset image with stb_image
 // (load_stbi, src/common_host.cu:214-217; nerf_loader.cu:571-618), which picks the decoder from the file's content, not
-// its name. JPEG goes to nvjpeg and PNG to host_png.cu; this file adds what is left of stb_image's list that datasets
+// its name. JPEG goes to host_jpeg.cu (nvjpeg in the loader's default path) and PNG to host_png.cu; this file adds what is left of stb_image's list that datasets
 // use - BMP, GIF (first frame), PSD (flattened composite), Softimage PIC, TGA and binary PNM - and the content sniffing in front of them. Output as everywhere: RGBA8, rows top to
 // bottom, alpha 255 where the file has none. Host only.
 #include "host_io.h"
@@ -555,7 +555,7 @@ bool is_jpeg_file(const std::vector<uint8_t>& f) { return f.size() > 3 && f[0] =
 HostImage decode_image_rgba8(const std::vector<uint8_t>& f, const std::string& name) {
 	static const uint8_t png_magic[8] = {0x89, 'P', 'N', 'G', '\r', '\n', 0x1A, '\n'};
 	if (f.size() >= 8 && memcmp(f.data(), png_magic, 8) == 0) return decode_png(f, name);
-	if (is_jpeg_file(f)) fail(name, "JPEG files are decoded on the device (nvjpeg), not by the host decoder");
+	if (is_jpeg_file(f)) return decode_jpeg(f, name);
 	if (f.size() >= 4 && memcmp(f.data(), "GIF8", 4) == 0) return decode_gif(f, name);
 	if (f.size() >= 2 && f[0] == 'B' && f[1] == 'M') return decode_bmp(f, name);
 	if (f.size() >= 4 && memcmp(f.data(), "8BPS", 4) == 0) return decode_psd(f, name);

@@ -42,8 +42,10 @@ HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name_
 
 // PNG (8 / 16 bit, grey / grey-alpha / RGB / RGBA / palette, plain or Adam7-interlaced) decoded on the host with zlib.
 HostImage decode_png(const std::vector<uint8_t>& file, const std::string& name_for_errors);
-// Any 8-bit format of the loader but JPEG, picked from the file's content as stb_image does: PNG, BMP, GIF, PSD, PIC, TGA, binary PNM (host_image.cu).
+// Any 8-bit format of the loader, picked from the file's content as stb_image does: JPEG (host_jpeg.cu), PNG, BMP, GIF, PSD, PIC, TGA, binary PNM (host_image.cu).
 HostImage decode_image_rgba8(const std::vector<uint8_t>& file, const std::string& name_for_errors);
 bool is_jpeg_file(const std::vector<uint8_t>& file);
+// JPEG on the host with stb_image's arithmetic after entropy decoding, so the texels are the reference loader's (host_jpeg.cu).
+HostImage decode_jpeg(const std::vector<uint8_t>& file, const std::string& name_for_errors);
 
 } // namespace ngpb
