@@ -30,7 +30,10 @@ typedef struct ngpb_module ngpb_module_t;   /* tcnn::cpp::Module, tcnn/include/t
 typedef struct ngpb_context ngpb_context_t; /* tcnn::cpp::Context, cpp_api.h:82-84 */
 
 /* ---- library ------------------------------------------------------------------------- */
+/* Text of the last failure on the calling thread: what the reference throws as std::runtime_error from CHECK_THROW /
+ * CUDA_CHECK_THROW (tcnn common_host.h) arrives here, behind the int status. No reference counterpart as a function. */
 const char* ngpb_last_error(void);
+/* Library version (no reference counterpart; NGP_VERSION of src/main.cu:186 is a build string). */
 int ngpb_version(void);
 /* 1 when a CUDA device is usable from this process, else 0 (never an error). */
 int ngpb_has_device(void);
@@ -196,7 +199,9 @@ typedef struct {
 	uint32_t* compact_src;       /* [max_samples_compacted] or NULL: row of `coords` each compacted sample was copied from (no reference counterpart) */
 } ngpb_nerf_train_buffers_t;
 
-/* rng_state = {state, inc} of the step's pcg32 (m_rng). Counters must be zeroed by the caller. */
+/* generate_training_samples_nerf (src/testbed_nerf.cu:679-838) and compute_loss_kernel_train_nerf with its compaction
+ * (:841-1160), with the buffers Testbed::train_nerf_step hands them (:2730-2870).
+ * rng_state = {state, inc} of the step's pcg32 (m_rng). Counters must be zeroed by the caller. */
 int ngpb_nerf_generate_training_samples(void* stream, const ngpb_nerf_train_config_t* cfg, const ngpb_nerf_train_buffers_t* buf, const uint64_t* rng_state);
 int ngpb_nerf_compute_loss_and_compact(void* stream, const ngpb_nerf_train_config_t* cfg, const ngpb_nerf_train_buffers_t* buf, const uint64_t* rng_state);
 /* update_density_grid_mean_and_bitfield (:2362-2379): grid float [(max_cascade+1) * 128^3] in Morton
@@ -370,6 +375,8 @@ int ngpb_testbed_render(ngpb_testbed_t* t, uint32_t width, uint32_t height, uint
  * lens_mode 0 Perspective, 1 OpenCV (k1, k2, p1, p2 in lens_params[0..3]; 7 floats or NULL). */
 int ngpb_testbed_set_render_lens(ngpb_testbed_t* t, int lens_mode, const float* lens_params);
 
+/* Testbed::render_ground_truth as scripts/run.py uses it for PSNR (src/testbed.cu:4592-4608): the training image of `view`
+ * drawn over the frame by overlay_image_kernel (src/render_buffer.cu:348-411). rgba: device float [height][width][4]. */
 int ngpb_testbed_overlay_ground_truth(ngpb_testbed_t* t, uint32_t width, uint32_t height, int linear, uint32_t view, int fov_axis, float zoom, float alpha, float* rgba);
 
 /* Neural-image mode (ETestbedMode::Image; Testbed::load_image, train_image, render_image,
@@ -402,7 +409,7 @@ int ngpb_probe_scatter_vec(void* stream, void* table, uint32_t log2_entries, uin
 /* `passes` coalesced 16-byte-per-lane reads of buf through L2 only (ld.global.cg): the L2 -> SM bandwidth peak */
 int ngpb_probe_l2_stream(void* stream, const void* buf, size_t bytes, uint32_t passes, uint32_t blocks, uint32_t* sink);
 
-/* ---- self test of the tcgen05 operand views (tc_device.cuh) --------------------------------
+/* ---- self test of the tcgen05 operand views (tc_device.cuh); diagnostics, no reference counterpart ----
  * mode 0: D[128xN] = X[128xK] W[NxK]^T; mode 1: D[128xN] = X[128xK] W[KxN];
  * mode 2: D[64xN] = X[128x64]^T W[128xN]. fp16 row-major inputs, fp32 row-major D (device). */
 int ngpb_selftest_umma(void* stream, int mode, uint32_t K, uint32_t N, const void* X, const void* W, float* D);
