@@ -139,8 +139,8 @@ def test_adam_ema_restatement_against_reference_kernels(ref):
         m2 = np.where(active, beta2 * m2 + (f(1) - beta2) * (g * g), m2).astype(f)
         steps = np.where(active, steps + 1, steps).astype(np.uint32)
         t = steps.astype(np.float32)
-        lr = (lr0 * np.sqrt(f(1) - np.power(beta2, t, dtype=f)) / (f(1) - np.power(beta1, t, dtype=f))).astype(f)
-        with np.errstate(divide="ignore", invalid="ignore"):
+        with np.errstate(divide="ignore", invalid="ignore"):   # entries that have never stepped (t = 0) divide 0 by 0; they are not `active`
+            lr = (lr0 * np.sqrt(f(1) - np.power(beta2, t, dtype=f)) / (f(1) - np.power(beta1, t, dtype=f))).astype(f)
             eff = (lr / (np.sqrt(m2) + eps)).astype(f)
         new_w = (w32 - eff * m1).astype(f)
         w32 = np.where(active, new_w, w32).astype(f)
