@@ -282,7 +282,7 @@ int ngpb_host_decode_png(const char* path, void* rgba, size_t cap, int* width, i
  * GIF (first frame), PSD (composite), PIC, TGA, binary PNM -> RGBA8 rows top to bottom, the texels stbi_load(..., 4) returns.
  * (ngpb_testbed_load_training_data decodes JPEG on the device with nvjpeg unless NGPB_JPEG_DECODER=host.) */
 int ngpb_host_decode_image(const char* path, void* rgba, size_t cap, int* width, int* height);
-/* The loader's OpenEXR reader (single-part scanline, HALF / FLOAT, NONE / RLE / ZIPS / ZIP / PIZ): float RGBA rows top to bottom. */
+/* The loader's OpenEXR reader (single-part scanline or tiled, HALF / FLOAT, NONE / RLE / ZIPS / ZIP / PIZ): float RGBA rows top to bottom. */
 int ngpb_host_decode_exr(const char* path, float* rgba, size_t cap_floats, int* width, int* height);
 /* The same reader with the channel rule of NeRF frames (load_exr_to_gpu, src/tinyexr_wrapper.cu:153-258): R / G / B / A by name,
  * absent colours 0, absent alpha 1; ngpb_host_decode_exr follows the image mode's LoadEXR (a one-channel file fills all four). */

@@ -1,7 +1,7 @@
 // OpenEXR reader for the loader (the reference reads EXR through tinyexr, src/tinyexr_wrapper.cu, which is not part of
-// this image): single-part scanline files, HALF and FLOAT channels, compression NONE / RLE / ZIPS / ZIP / PIZ - the set
+// this image): single-part scanline and tiled (full-resolution level) files, HALF and FLOAT channels, compression NONE / RLE / ZIPS / ZIP / PIZ - the set
 // tinyexr decodes (data/image/albert.exr is FLOAT RGBA, ZIP; PIZ is what most DCC tools write by default). PXR24 / B44 /
-// DWA, tiled and multi-part files are refused with a message. Output: float RGBA, rows top to bottom; which channels land
+// DWA, deep and multi-part files are refused with a message. Output: float RGBA, rows top to bottom; which channels land
 // where follows the reference's two readers (ExrChannelRule in host_io.h). Host only; zlib does the inflate; the PIZ stages (Huffman, 2-D Haar
 // wavelet, value LUT) follow the OpenEXR file-format description.
 #include "host_io.h"
@@ -317,11 +317,12 @@ HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name,
 	if (file.size() < 8 || rd<uint32_t>(file.data()) != 20000630u) fail("not an OpenEXR file");
 	const uint32_t version = rd<uint32_t>(file.data() + 4);
 	if ((version & 0xFF) != 2) fail("unsupported OpenEXR version");
-	if (version & 0x200) fail("tiled files are not supported");
+	const bool tiled = (version & 0x200) != 0;
 	if (version & 0x1800) fail("deep / multi-part files are not supported");
 
 	std::vector<ExrChannel> channels;
 	int compression = -1, xmin = 0, ymin = 0, xmax = -1, ymax = -1;
+	uint32_t tile_w = 0, tile_h = 0, tile_mode = 0;
 	size_t pos = 8;
 	auto cstr = [&]() {
 		const size_t start = pos;
@@ -351,6 +352,7 @@ HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name,
 				channels.push_back(ch);
 			}
 		} else if (attr == "compression") compression = v[0];
+		else if (attr == "tiles" && size >= 9) { tile_w = rd<uint32_t>(v); tile_h = rd<uint32_t>(v + 4); tile_mode = v[8]; }
 		else if (attr == "dataWindow") { xmin = rd<int32_t>(v); ymin = rd<int32_t>(v + 4); xmax = rd<int32_t>(v + 8); ymax = rd<int32_t>(v + 12); }
 		pos += size;
 	}
@@ -363,10 +365,10 @@ HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name,
 		case 4: lines_per_block = 32; break;
 		default: fail("compression type " + std::to_string(compression) + " is not supported (NONE, RLE, ZIPS, ZIP and PIZ are)");
 	}
-	size_t bytes_per_line = 0;
+	size_t bytes_per_pixel_column = 0;   // bytes one pixel takes over all channels
 	for (const ExrChannel& ch : channels) {
 		if (ch.pixel_type != 1 && ch.pixel_type != 2) fail("UINT channels are not supported");
-		bytes_per_line += (size_t)w * (ch.pixel_type == 1 ? 2 : 4);
+		bytes_per_pixel_column += ch.pixel_type == 1 ? 2 : 4;
 	}
 	// where each stored channel goes in the RGBA output (-1: ignored)
 	std::vector<int> target(channels.size(), -1);
@@ -398,28 +400,48 @@ HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name,
 	}
 	(void)has_rgb;
 
-	const int n_blocks = (h + lines_per_block - 1) / lines_per_block;
+	// tiled files (tinyexr reads the full-resolution level of them): one chunk per tile, the tiles of lower levels after them
+	if (tiled && (tile_w == 0 || tile_h == 0 || tile_w > (1u << 16) || tile_h > (1u << 16))) fail("bad tile description");
+	int n_blocks = (h + lines_per_block - 1) / lines_per_block;
+	if (tiled) {
+		const uint64_t nx = ((uint64_t)w + tile_w - 1) / tile_w, ny = ((uint64_t)h + tile_h - 1) / tile_h;
+		(void)tile_mode;   // mip / rip files: tinyexr reads the first nx * ny offsets as the full-resolution level, and so does this
+		n_blocks = (int)(nx * ny);
+	}
 	if (pos + (size_t)n_blocks * 8 > file.size()) fail("truncated offset table");
 	HostImageF img;
 	img.width = w; img.height = h;
 	img.rgba.assign((size_t)w * h * 4, 0.0f);
 	if (!has_alpha) for (size_t i = 0; i < (size_t)w * h; ++i) img.rgba[i * 4 + 3] = 1.0f;
 	std::vector<uint8_t> raw, tmp;
+	// one chunk = one rectangle of the image: a block of scanlines, or a tile (clipped at the right and bottom edges)
 	for (int b = 0; b < n_blocks; ++b) {
 		const uint64_t off = rd<uint64_t>(&file[pos + (size_t)b * 8]);
-		if (off + 8 > file.size()) fail("bad chunk offset");
-		const int y0 = rd<int32_t>(&file[off]) - ymin;
-		const uint32_t packed = rd<uint32_t>(&file[off + 4]);
-		if (y0 < 0 || y0 >= h || off + 8 + packed > file.size()) fail("bad chunk");
-		const int lines = std::min(lines_per_block, h - y0);
-		const size_t unpacked = bytes_per_line * lines;
-		const uint8_t* src = &file[off + 8];
+		const size_t head = tiled ? 20 : 8;
+		if (off + head > file.size()) fail("bad chunk offset");
+		int x0 = 0, y0, bw = w, lines;
+		if (tiled) {
+			const int tx = rd<int32_t>(&file[off]), ty = rd<int32_t>(&file[off + 4]);
+			if (rd<int32_t>(&file[off + 8]) != 0 || rd<int32_t>(&file[off + 12]) != 0) fail("tiles of a lower-resolution level are not supported");
+			if (tx < 0 || ty < 0 || (uint64_t)tx * tile_w >= (uint64_t)w || (uint64_t)ty * tile_h >= (uint64_t)h) fail("bad tile");
+			x0 = tx * (int)tile_w; y0 = ty * (int)tile_h;
+			bw = std::min((int)tile_w, w - x0);
+			lines = std::min((int)tile_h, h - y0);
+		} else {
+			y0 = rd<int32_t>(&file[off]) - ymin;
+			if (y0 < 0 || y0 >= h) fail("bad chunk");
+			lines = std::min(lines_per_block, h - y0);
+		}
+		const uint32_t packed = rd<uint32_t>(&file[off + head - 4]);
+		if (off + head + packed > file.size()) fail("bad chunk");
+		const size_t unpacked = bytes_per_pixel_column * (size_t)bw * lines;
+		const uint8_t* src = &file[off + head];
 		raw.resize(unpacked);
 		if (compression == 0 || packed == unpacked) {
 			if (packed != unpacked) fail("bad uncompressed chunk size");
 			memcpy(raw.data(), src, unpacked);
 		} else if (compression == 4) {
-			if (!piz_uncompress(src, packed, channels, w, lines, raw.data(), unpacked)) fail("corrupt PIZ chunk");
+			if (!piz_uncompress(src, packed, channels, bw, lines, raw.data(), unpacked)) fail("corrupt PIZ chunk");
 		} else if (compression == 1) {
 			tmp.resize(unpacked);
 			if (!rle_expand(src, packed, tmp)) fail("corrupt RLE chunk");
@@ -432,18 +454,18 @@ HostImageF decode_exr(const std::vector<uint8_t>& file, const std::string& name,
 		}
 		const uint8_t* p = raw.data();
 		for (int l = 0; l < lines; ++l) {
-			float* out = &img.rgba[(size_t)(y0 + l) * w * 4];
+			float* out = &img.rgba[((size_t)(y0 + l) * w + x0) * 4];
 			for (size_t c = 0; c < channels.size(); ++c) {
 				const bool is_half = channels[c].pixel_type == 1;
 				const int t = (int)c == grey ? 4 : target[c];
 				if (t >= 0) {
-					for (int x = 0; x < w; ++x) {
+					for (int x = 0; x < bw; ++x) {
 						const float v = is_half ? __half2float(rd<__half>(p + (size_t)x * 2)) : rd<float>(p + (size_t)x * 4);
 						if (t == 4) { out[x * 4] = out[x * 4 + 1] = out[x * 4 + 2] = out[x * 4 + 3] = v; }
 						else out[x * 4 + t] = v;
 					}
 				}
-				p += (size_t)w * (is_half ? 2 : 4);
+				p += (size_t)bw * (is_half ? 2 : 4);
 			}
 		}
 	}

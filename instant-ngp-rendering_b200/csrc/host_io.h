@@ -31,7 +31,7 @@ struct HostImageF {
 	int width = 0, height = 0;
 	std::vector<float> rgba;
 };
-// OpenEXR, single-part scanline, HALF / FLOAT channels, compression NONE / RLE / ZIPS / ZIP / PIZ (host_exr.cu).
+// OpenEXR, single-part scanline or tiled, HALF / FLOAT channels, compression NONE / RLE / ZIPS / ZIP / PIZ (host_exr.cu).
 // The reference reads EXR files through two doors with different channel rules:
 //   Image    tinyexr's LoadEXR behind load_exr (image mode, src/tinyexr_wrapper.cu:125-151): a one-channel file fills R, G, B and A
 //            with that channel; otherwise R, G, B must exist ("R channel not found") and a missing A is 1

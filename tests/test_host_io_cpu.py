@@ -1047,3 +1047,63 @@ def test_jpeg_decoder_refuses_broken_streams(ngp, tmp_path):
             rc = lib.ngpb_host_decode_image(str(tmp_path / "c.jpg").encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch))
             if rc == 0 and cw.value * ch.value * 4 == out.size:
                 assert lib.ngpb_host_decode_image(str(tmp_path / "c.jpg").encode(), out.ctypes.data_as(ctypes.c_void_p), out.size, ctypes.byref(cw), ctypes.byref(ch)) == 0
+
+
+def test_tiled_exr_against_the_references_tinyexr(ngp, tmp_path):
+    """Single-part tiled EXR files (full-resolution level), as tinyexr reads them: hand-written here - HALF / FLOAT, 1 / 3 / 4
+    channels, NONE / ZIP / ZIPS, tiles larger than the image and clipped at its edges, a data window away from the origin, chunks
+    stored in reverse order, the mip flag set - texel for texel against the reference's vendored tinyexr."""
+    ref = _ref_images()
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(99)
+
+    def tiled_exr(w, h, tw, th, names, dtype, comp, mode=0, xmin=0, ymin=0, order=None):
+        data = {n: rng.standard_normal((h, w)).astype(dtype) for n in names}
+        def attr(name, typ, val): return name.encode() + b"\0" + typ.encode() + b"\0" + struct.pack("<I", len(val)) + val
+        chlist = b"".join(n.encode() + b"\0" + struct.pack("<iBBBBii", 1 if dtype == np.float16 else 2, 0, 0, 0, 0, 1, 1) for n in names) + b"\0"
+        box = struct.pack("<4i", xmin, ymin, xmin + w - 1, ymin + h - 1)
+        header = struct.pack("<II", 20000630, 2 | 0x200) + attr("channels", "chlist", chlist) + attr("compression", "compression", bytes([comp])) + \
+            attr("dataWindow", "box2i", box) + attr("displayWindow", "box2i", box) + attr("lineOrder", "lineOrder", b"\0") + attr("pixelAspectRatio", "float", struct.pack("<f", 1.0)) + \
+            attr("screenWindowCenter", "v2f", struct.pack("<2f", 0, 0)) + attr("screenWindowWidth", "float", struct.pack("<f", 1.0)) + attr("tiles", "tiledesc", struct.pack("<IIB", tw, th, mode)) + b"\0"
+        nx, ny = (w + tw - 1) // tw, (h + th - 1) // th
+        chunks = []
+        for ty in range(ny):
+            for tx in range(nx):
+                x0, y0 = tx * tw, ty * th
+                raw = b"".join(data[n][y, x0:x0 + tw].tobytes() for y in range(y0, min(y0 + th, h)) for n in names)
+                if comp == 0: packed = raw
+                else:
+                    b = np.frombuffer(raw, dtype=np.uint8); inter = np.concatenate([b[0::2], b[1::2]]).astype(np.int32); pred = inter.copy(); pred[1:] = (inter[1:] - inter[:-1] + 128 + 256) & 0xFF
+                    packed = zlib.compress(pred.astype(np.uint8).tobytes())
+                    if len(packed) >= len(raw): packed = raw
+                chunks.append(struct.pack("<iiiiI", tx, ty, 0, 0, len(packed)) + packed)
+        idx = list(range(len(chunks)))
+        if order == 'reversed': file_order = idx[::-1]
+        else: file_order = idx
+        offs = [0] * len(chunks); pos = len(header) + 8 * len(chunks); body = b""
+        for k in file_order: offs[k] = pos + len(body) - 0; body += chunks[k]
+        offs = [o for o in offs]
+        return header + struct.pack("<%dQ" % len(offs), *offs) + body, data
+    path = tmp_path / "t.exr"
+
+    def check(tag, blob):
+        path.write_bytes(blob)
+        want = _ref_tinyexr(ref, path)
+        assert not isinstance(want, str), (tag, want)
+        got = _decode_exr(lib, path)
+        assert got.shape == want.shape and np.array_equal(got.view(np.uint32), want.view(np.uint32)), tag
+    for (w, h, tw, th) in ((37, 29, 16, 16), (64, 64, 32, 32), (5, 3, 8, 8), (33, 17, 7, 5), (100, 9, 64, 4)):
+        for names, dtype in ((["B", "G", "R"], np.float16), (["A", "B", "G", "R"], np.float32), (["Y"], np.float16)):
+            for comp in (0, 3, 2):
+                check((w, h, tw, th, names, comp), tiled_exr(w, h, tw, th, names, dtype, comp)[0])
+    check("offset window", tiled_exr(37, 29, 16, 16, ["B", "G", "R"], np.float16, 3, xmin=-5, ymin=7)[0])
+    check("reversed file order", tiled_exr(37, 29, 16, 16, ["B", "G", "R"], np.float16, 3, order="reversed")[0])
+    check("mip mode flag", tiled_exr(32, 32, 16, 16, ["B", "G", "R"], np.float16, 0, mode=1)[0])
+    # a tile of a lower level is refused, as tinyexr refuses it
+    blob = bytearray(tiled_exr(32, 32, 16, 16, ["B", "G", "R"], np.float16, 0)[0])
+    first = struct.unpack_from("<Q", blob, blob.index(b"tiledesc") + 8 + 1 + 4 + 9 + 1)[0]
+    struct.pack_into("<i", blob, first + 8, 1)
+    path.write_bytes(bytes(blob))
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+    assert lib.ngpb_host_decode_exr(str(path).encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0
+    assert isinstance(_ref_tinyexr(ref, path), str)
