@@ -287,6 +287,9 @@ int ngpb_host_decode_exr(const char* path, float* rgba, size_t cap_floats, int* 
 /* The same reader with the channel rule of NeRF frames (load_exr_to_gpu, src/tinyexr_wrapper.cu:153-258): R / G / B / A by name,
  * absent colours 0, absent alpha 1; ngpb_host_decode_exr follows the image mode's LoadEXR (a one-channel file fills all four). */
 int ngpb_host_decode_exr_frame(const char* path, float* rgba, size_t cap_floats, int* width, int* height);
+/* Radiance HDR (RGBE) as float RGBA, alpha 1: stbi_loadf(..., 4), the image mode's reader for such files (load_stbi_gpu,
+ * src/common_host.cu:268-299). ngpb_host_decode_image gives the same file as bytes the way stbi_load does (gamma 1 / 2.2). */
+int ngpb_host_decode_hdr(const char* path, float* rgba, size_t cap_floats, int* width, int* height);
 /* Testbed::train(batch_size), src/testbed.cu:4020-4109. Returns once the step's counters (loss,
  * measured batch sizes) are on the host; the backward pass and the optimizer may still be running on
  * the testbed's stream - later calls on this testbed are ordered behind them. */

@@ -109,6 +109,7 @@ SIGNATURES = {
     "ngpb_host_decode_png": (c_int, [c_cp, c_vp, c_sz, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "ngpb_host_natural_less": (c_int, [c_cp, c_cp]),
     "ngpb_host_decode_image": (c_int, [c_cp, c_vp, c_sz, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
+    "ngpb_host_decode_hdr": (c_int, [c_cp, c_vp, c_sz, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "ngpb_host_decode_exr_frame": (c_int, [c_cp, c_vp, c_sz, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "ngpb_host_decode_exr": (c_int, [c_cp, c_vp, c_sz, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "ngpb_testbed_train": (c_int, [c_vp, c_u32]),

@@ -401,6 +401,11 @@ void Testbed::load_image_file(const std::string& path) {
 		set_image(img.rgba.data(), kImageFloat, img.width, img.height);
 		return;
 	}
+	if (is_hdr_file(read_file(path))) {   // load_stbi_gpu (src/common_host.cu:268-299): Radiance files, told by content, keep their floats (stbi_loadf)
+		const HostImageF img = decode_hdr(read_file(path), path);
+		set_image(img.rgba.data(), kImageFloat, img.width, img.height);
+		return;
+	}
 	JpegDecoder jpeg;
 	DeviceBuffer rgb_scratch, rgba8, linear;
 	int w = 0, h = 0;

@@ -6,6 +6,7 @@
 #include "host_io.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <stdexcept>
 
@@ -548,8 +549,123 @@ HostImage decode_pic(const std::vector<uint8_t>& f, const std::string& name) {
 	}
 	return img;
 }
+
+// ---- Radiance HDR (RGBE), as stb_image reads it: stbi_loadf gives the floats (the image mode's path, load_stbi_gpu,
+// src/common_host.cu:268-299), stbi_load turns them into bytes with gamma 1 / 2.2 (what a dataset frame would get) ----
+bool looks_like_hdr(const std::vector<uint8_t>& f) {
+	return (f.size() >= 11 && memcmp(f.data(), "#?RADIANCE\n", 11) == 0) || (f.size() >= 7 && memcmp(f.data(), "#?RGBE\n", 7) == 0);
+}
+
+void rgbe_to_float(float* out, const uint8_t* in) {
+	if (in[3] != 0) {
+		const float f1 = (float)ldexp(1.0f, in[3] - (int)(128 + 8));
+		out[0] = in[0] * f1; out[1] = in[1] * f1; out[2] = in[2] * f1;
+	} else {
+		out[0] = out[1] = out[2] = 0;
+	}
+	out[3] = 1;
+}
 } // namespace
 
+HostImageF decode_hdr(const std::vector<uint8_t>& f, const std::string& name) {
+	size_t at = 0;
+	auto eof = [&]() { return at >= f.size(); };
+	auto get8 = [&]() -> int { return at < f.size() ? f[at++] : 0; };
+	auto token = [&]() {   // one header line, at most 1023 characters of it
+		std::string t;
+		char c = (char)get8();
+		while (!eof() && c != '\n') {
+			t += c;
+			if (t.size() == 1023) { while (!eof() && get8() != '\n') {} break; }
+			c = (char)get8();
+		}
+		return t;
+	};
+	const std::string magic = token();
+	if (magic != "#?RADIANCE" && magic != "#?RGBE") fail(name, "not HDR");
+	bool valid = false;
+	for (;;) {
+		const std::string t = token();
+		if (t.empty()) break;
+		if (t == "FORMAT=32-bit_rle_rgbe") valid = true;
+	}
+	if (!valid) fail(name, "unsupported format");
+	const std::string dims = token();
+	if (dims.compare(0, 3, "-Y ") != 0) fail(name, "unsupported data layout");
+	char* rest = nullptr;
+	const int height = (int)strtol(dims.c_str() + 3, &rest, 10);
+	while (*rest == ' ') ++rest;
+	if (strncmp(rest, "+X ", 3) != 0) fail(name, "unsupported data layout");
+	const int width = (int)strtol(rest + 3, nullptr, 10);
+	if (width <= 0 || height <= 0 || width > (1 << 24) || height > (1 << 24)) fail(name, "bad HDR size");
+	if ((size_t)width * height > f.size() * 4096) fail(name, "HDR size implausible for the file");
+
+	HostImageF img;
+	img.width = width; img.height = height;
+	img.rgba.assign((size_t)width * height * 4, 0.0f);
+	const size_t n = (size_t)width * height;
+	auto flat_from = [&](size_t first) {
+		for (size_t i = first; i < n; ++i) {
+			uint8_t rgbe[4];
+			for (int k = 0; k < 4; ++k) rgbe[k] = (uint8_t)get8();
+			rgbe_to_float(&img.rgba[i * 4], rgbe);
+		}
+	};
+	if (width < 8 || width >= 32768) {
+		flat_from(0);
+		return img;
+	}
+	std::vector<uint8_t> scanline((size_t)width * 4);
+	for (int j = 0; j < height; ++j) {
+		const int c1 = get8(), c2 = get8();
+		int len = get8();
+		if (c1 != 2 || c2 != 2 || (len & 0x80)) {
+			// not a run-length coded line: stb_image takes these four bytes as the FIRST pixel of the picture and reads all the
+			// others flat from here, whichever line it was on
+			const uint8_t rgbe[4] = {(uint8_t)c1, (uint8_t)c2, (uint8_t)len, (uint8_t)get8()};
+			rgbe_to_float(&img.rgba[0], rgbe);
+			flat_from(1);
+			return img;
+		}
+		len = (len << 8) | get8();
+		if (len != width) fail(name, "invalid decoded scanline length");
+		for (int k = 0; k < 4; ++k) {
+			for (int i = 0; i < width;) {
+				const int left = width - i;
+				int count = get8();
+				if (count > 128) {
+					const uint8_t value = (uint8_t)get8();
+					count -= 128;
+					if (count == 0 || count > left) fail(name, "bad RLE data in HDR");
+					for (int z = 0; z < count; ++z) scanline[(size_t)i++ * 4 + k] = value;
+				} else {
+					if (count == 0 || count > left) fail(name, "bad RLE data in HDR");
+					for (int z = 0; z < count; ++z) scanline[(size_t)i++ * 4 + k] = (uint8_t)get8();
+				}
+			}
+		}
+		for (int i = 0; i < width; ++i) rgbe_to_float(&img.rgba[((size_t)j * width + i) * 4], &scanline[(size_t)i * 4]);
+	}
+	return img;
+}
+
+namespace {
+// stbi__hdr_to_ldr: pow(v, 1 / 2.2) * 255 + 0.5, cut to [0, 255]; alpha linear
+HostImage hdr_to_bytes(const HostImageF& src) {
+	HostImage img;
+	img.width = src.width; img.height = src.height;
+	img.rgba.resize(src.rgba.size());
+	for (size_t i = 0; i < src.rgba.size(); ++i) {
+		float z = (i & 3) == 3 ? src.rgba[i] * 255 + 0.5f : (float)pow((double)(src.rgba[i] * 1.0f), (double)(1.0f / 2.2f)) * 255 + 0.5f;
+		if (z < 0) z = 0;
+		if (z > 255) z = 255;
+		img.rgba[i] = (uint8_t)(int)z;
+	}
+	return img;
+}
+} // namespace
+
+bool is_hdr_file(const std::vector<uint8_t>& f) { return looks_like_hdr(f); }
 bool is_jpeg_file(const std::vector<uint8_t>& f) { return f.size() > 3 && f[0] == 0xFF && f[1] == 0xD8 && f[2] == 0xFF; }
 
 HostImage decode_image_rgba8(const std::vector<uint8_t>& f, const std::string& name) {
@@ -560,9 +676,10 @@ HostImage decode_image_rgba8(const std::vector<uint8_t>& f, const std::string& n
 	if (f.size() >= 2 && f[0] == 'B' && f[1] == 'M') return decode_bmp(f, name);
 	if (f.size() >= 4 && memcmp(f.data(), "8BPS", 4) == 0) return decode_psd(f, name);
 	if (looks_like_pic(f)) return decode_pic(f, name);
+	if (looks_like_hdr(f)) return hdr_to_bytes(decode_hdr(f, name));
 	if (f.size() >= 3 && f[0] == 'P' && (f[1] == '5' || f[1] == '6')) return decode_pnm(f, name);
 	if (looks_like_tga(f)) return decode_tga(f, name);
-	fail(name, "unknown image type (JPEG, PNG, BMP, GIF, PSD, PIC, TGA, binary PNM and EXR are read)");
+	fail(name, "unknown image type (JPEG, PNG, BMP, GIF, PSD, PIC, TGA, binary PNM, Radiance HDR and EXR are read)");
 }
 
 } // namespace ngpb

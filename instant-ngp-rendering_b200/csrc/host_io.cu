@@ -218,6 +218,16 @@ extern "C" int ngpb_host_decode_exr(const char* path, float* rgba, size_t cap_fl
 	} catch (const std::exception& e) { ngpb::set_last_error(e.what()); return NGPB_ERROR; }
 }
 
+extern "C" int ngpb_host_decode_hdr(const char* path, float* rgba, size_t cap_floats, int* width, int* height) {
+	try {
+		if (!path || !width || !height) throw std::runtime_error{"ngpb_host_decode_hdr: null argument"};
+		const ngpb::HostImageF img = ngpb::decode_hdr(ngpb::read_file(path), path);
+		*width = img.width; *height = img.height;
+		if (rgba && cap_floats >= img.rgba.size()) memcpy(rgba, img.rgba.data(), img.rgba.size() * sizeof(float));
+		return NGPB_OK;
+	} catch (const std::exception& e) { ngpb::set_last_error(e.what()); return NGPB_ERROR; }
+}
+
 extern "C" int ngpb_host_decode_exr_frame(const char* path, float* rgba, size_t cap_floats, int* width, int* height) {
 	try {
 		if (!path || !width || !height) throw std::runtime_error{"ngpb_host_decode_exr_frame: null argument"};

@@ -45,6 +45,9 @@ HostImage decode_png(const std::vector<uint8_t>& file, const std::string& name_f
 // Any 8-bit format of the loader, picked from the file's content as stb_image does: JPEG (host_jpeg.cu), PNG, BMP, GIF, PSD, PIC, TGA, binary PNM (host_image.cu).
 HostImage decode_image_rgba8(const std::vector<uint8_t>& file, const std::string& name_for_errors);
 bool is_jpeg_file(const std::vector<uint8_t>& file);
+// Radiance HDR (RGBE) as floats, alpha 1: what stbi_loadf(..., 4) returns (the image mode's reader for *.hdr files).
+HostImageF decode_hdr(const std::vector<uint8_t>& file, const std::string& name_for_errors);
+bool is_hdr_file(const std::vector<uint8_t>& file);   // stbi_is_hdr
 // JPEG on the host with stb_image's arithmetic after entropy decoding, so the texels are the reference loader's (host_jpeg.cu).
 HostImage decode_jpeg(const std::vector<uint8_t>& file, const std::string& name_for_errors);
 

@@ -26,6 +26,20 @@ extern "C" int ref_stbi_load(const char* path, int* w, int* h, int* comp, uint8_
 	return 0;
 }
 
+// stbi_loadf(path, &w, &h, &comp, 4): float RGBA (Radiance HDR files as they are, others through stb_image's ldr-to-hdr curve).
+extern "C" int ref_stbi_loadf(const char* path, int* w, int* h, float* out, size_t cap_floats, char* why, size_t why_cap) {
+	int comp = 0;
+	float* img = stbi_loadf(path, w, h, &comp, 4);
+	if (!img) {
+		if (why && why_cap) { strncpy(why, stbi_failure_reason(), why_cap - 1); why[why_cap - 1] = 0; }
+		return 1;
+	}
+	const size_t n = (size_t)*w * *h * 4;
+	if (out && cap_floats >= n) memcpy(out, img, n * sizeof(float));
+	stbi_image_free(img);
+	return 0;
+}
+
 // LoadEXR (the simple API behind load_exr): float RGBA rows top to bottom.
 extern "C" int ref_tinyexr_load(const char* path, int* w, int* h, float* out, size_t cap_floats, char* why, size_t why_cap) {
 	float* rgba = nullptr;

@@ -1107,3 +1107,72 @@ def test_tiled_exr_against_the_references_tinyexr(ngp, tmp_path):
     cw, ch = ctypes.c_int(), ctypes.c_int()
     assert lib.ngpb_host_decode_exr(str(path).encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0
     assert isinstance(_ref_tinyexr(ref, path), str)
+
+
+def test_radiance_hdr_against_the_references_stb_image(ngp, tmp_path):
+    """Radiance RGBE files both ways stb_image hands them out: stbi_loadf floats (the image mode keeps them, load_stbi_gpu,
+    src/common_host.cu:268-299) and stbi_load bytes (gamma 1 / 2.2). OpenCV-written files, run-length coded and flat, and
+    hand-built ones: the #?RGBE magic, flat data under a width of 8 or more, a later line that is not run-length coded (stb_image
+    restarts from the first pixel there), refused headers, bad runs, truncation."""
+    ref = _ref_images()
+    cv2 = pytest.importorskip("cv2")
+    lib = ngp._lib.lib
+    rng = np.random.default_rng(111)
+    cw, ch = ctypes.c_int(), ctypes.c_int()
+    path = tmp_path / "h.hdr"
+
+    def ref_float(p):
+        w, h, why = ctypes.c_int(), ctypes.c_int(), ctypes.create_string_buffer(200)
+        if ref.ref_stbi_loadf(str(p).encode(), ctypes.byref(w), ctypes.byref(h), None, ctypes.c_size_t(0), why, ctypes.c_size_t(200)):
+            return why.value.decode()
+        out = np.zeros((h.value, w.value, 4), np.float32)
+        ref.ref_stbi_loadf(str(p).encode(), ctypes.byref(w), ctypes.byref(h), out.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(out.size), why, ctypes.c_size_t(200))
+        return out
+
+    def check(tag):
+        want_f, want_b = ref_float(path), _ref_stbi(ref, path)
+        if isinstance(want_f, str):
+            assert isinstance(want_b, str)
+            assert lib.ngpb_host_decode_hdr(str(path).encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0, (tag, want_f)
+            assert lib.ngpb_host_decode_image(str(path).encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) != 0, (tag, want_b)
+            return 0
+        assert lib.ngpb_host_decode_hdr(str(path).encode(), None, 0, ctypes.byref(cw), ctypes.byref(ch)) == 0, (tag, lib.ngpb_last_error().decode())
+        got_f = np.zeros((ch.value, cw.value, 4), np.float32)
+        assert lib.ngpb_host_decode_hdr(str(path).encode(), got_f.ctypes.data_as(ctypes.c_void_p), got_f.size, ctypes.byref(cw), ctypes.byref(ch)) == 0
+        assert got_f.shape == want_f.shape and np.array_equal(got_f.view(np.uint32), want_f.view(np.uint32)), tag
+        got_b = _decode_image(lib, path)
+        assert got_b.shape == want_b.shape and np.array_equal(got_b, want_b), tag
+        return 1
+    n_ok = 0
+    for (h, w) in ((13, 17), (1, 1), (5, 7), (9, 8), (40, 300)):
+        img = np.exp(rng.standard_normal((h, w, 3)) * 2).astype(np.float32)
+        img[:h // 2] = 0.5
+        img[0, 0] = 0
+        for comp in (0, 1):
+            if not cv2.imwrite(str(path), img, [cv2.IMWRITE_HDR_COMPRESSION, comp]):
+                pytest.skip("this OpenCV build cannot write Radiance HDR")
+            n_ok += check((h, w, comp))
+    assert n_ok == 10
+
+    def hdr(w,h,body,magic=b'#?RADIANCE', fmt=b'FORMAT=32-bit_rle_rgbe', res=None, extra=b'EXPOSURE=1.0\n'):
+        return magic+b'\n'+extra+fmt+b'\n\n'+(res or (b'-Y %d +X %d' % (h,w)))+b'\n'+body
+    w,h=12,4
+    flat = bytes(rng.integers(0,256,w*h*4,dtype=np.uint8))
+    def rle_line(w):
+        out = bytes([2,2,w>>8,w&255])
+        for k in range(4):
+            i=0
+            while i<w:
+                c=min(int(rng.integers(1,60)), w-i)
+                if rng.random()<0.5: out += bytes([128+c, int(rng.integers(0,256))])
+                else: out += bytes([c]) + bytes(rng.integers(0,256,c,dtype=np.uint8))
+                i+=c
+        return out
+    cases = {'flat wide': hdr(w,h,flat), 'rgbe magic': hdr(w,h,b''.join(rle_line(w) for _ in range(h)), magic=b'#?RGBE'),
+             'line 3 flat': hdr(w,h,rle_line(w)+rle_line(w)+flat), 'no format': hdr(w,h,flat,fmt=b'FORMAT=32-bit_rle_xyze'), '+Y layout': hdr(w,h,flat,res=b'+Y 4 +X 12'),
+             'bad magic': hdr(w,h,flat,magic=b'#?RADIANC'), 'wrong len': hdr(w,h,bytes([2,2,0,11])+flat), 'zero run': hdr(w,h,bytes([2,2,0,12,128,0])+flat), 'truncated': hdr(w,h,rle_line(w))}
+    n_ok = 0
+    for tag, blob in cases.items():
+        path.write_bytes(blob)
+        n_ok += check(tag)
+    assert n_ok == 4
